@@ -1,0 +1,178 @@
+/*
+ * slider_b200.h — C ABI of libslider_b200.so (sm_100a only).
+ *
+ * Drop-in boundary for the concept-slider hot path of ntc-ai/sliders-conceptmod.
+ * The reference has no native boundary (it is pure PyTorch); each entry point
+ * below names the reference Python call site whose arithmetic it replaces.
+ * Paths are relative to the reference checkout.
+ *
+ * Conventions
+ *  - every pointer is a CUDA device pointer into caller-owned memory unless
+ *    stated otherwise; the library never allocates or frees caller memory;
+ *  - `stream` is a cudaStream_t passed as void*; all calls are asynchronous;
+ *  - return 0 on success, non-zero error code otherwise; no C++ exception and
+ *    no exit() crosses the boundary; slider_last_error() returns thread-local
+ *    text describing the last failure on the calling thread;
+ *  - activations of conv layers are NHWC ("channels_last") in memory;
+ *    linear layers are row-major [M, K].
+ */
+#ifndef SLIDER_B200_H
+#define SLIDER_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SLIDER_ABI_VERSION 1
+
+enum slider_dtype { SLIDER_F32 = 0, SLIDER_BF16 = 1 };
+
+enum slider_status {
+  SLIDER_OK = 0,
+  SLIDER_ERR_BAD_ARG = 1,     /* null pointer, bad shape, misalignment        */
+  SLIDER_ERR_UNSUPPORTED = 2, /* dtype / rank / geometry not implemented      */
+  SLIDER_ERR_CUDA = 3,        /* a CUDA runtime / driver call failed          */
+  SLIDER_ERR_WORKSPACE = 4    /* caller workspace too small                   */
+};
+
+int slider_version(void);
+const char* slider_last_error(void);
+/* Number of kernel launches issued by this library since load (all threads). */
+int64_t slider_launch_count(void);
+
+/* ---------------------------------------------------------------------------
+ * Layer geometry shared by the LoRA entry points.
+ * A Linear layer is the degenerate conv: batch=1, height=1, width=M, kh=kw=1.
+ * Only stride-1 convolutions with symmetric padding are handled here.
+ * ------------------------------------------------------------------------- */
+typedef struct slider_layer_geom {
+  int32_t dtype;   /* enum slider_dtype of x / W / A / B / y                 */
+  int32_t batch;   /* NHWC batch                                             */
+  int32_t height;
+  int32_t width;
+  int32_t cin;     /* K per tap                                              */
+  int32_t cout;    /* N                                                      */
+  int32_t kh, kw;  /* 1x1 or 3x3                                             */
+  int32_t pad;     /* 0 for 1x1, 1 for 3x3                                   */
+  int32_t rank;    /* LoRA rank r, 0..16                                     */
+} slider_layer_geom;
+
+/*
+ * Fused base + low-rank forward.  Replaces LoRAModule.forward
+ * (conceptmod/textsliders/lora.py:134-138, trainscripts/imagesliders/lora.py:107-111):
+ *     y = conv(x, W) + bias + s * conv1x1(conv(x, A), B),   s = multiplier*alpha/rank
+ *
+ *   x     [batch,height,width,cin]                     activations (NHWC)
+ *   W     [cout, kh*kw, cin]   tap-major ("KRSC")      frozen base weight
+ *   bias  [cout] or NULL
+ *   A     [rank, kh*kw, cin]   tap-major               lora_down.weight
+ *   B     [cout, rank]                                 lora_up.weight
+ *   h_out [batch*height*width, rank] fp32 or NULL      x (*) A, saved for backward
+ *   y     [batch,height,width,cout]
+ * s == 0 and h_out == NULL selects the plain-GEMM path (adapter switched off,
+ * lora.py:299-301).  One tcgen05/TMA kernel launch.
+ */
+int slider_lora_forward(const slider_layer_geom* g, void* y, const void* x,
+                        const void* W, const void* bias, const void* A,
+                        const void* B, float* h_out, float s, void* stream);
+
+/*
+ * Low-rank part of the backward of the layer above (autograd of lora.py:134-138,
+ * triggered by loss.backward() at conceptmod/textsliders/train_lora.py:298):
+ *     dh = s * gy . B          [M, rank]  -> dh_out (element dtype, padded to 16)
+ *     dB = s * gy^T . h        [cout, rank]
+ *     dA = dh^T (*) x          [rank, kh*kw, cin]
+ *   gy     [batch,height,width,cout]  upstream gradient
+ *   h      [M, rank] fp32 saved by the forward
+ *   dA,dB  fp32 accumulators; `accumulate` != 0 adds to their current content
+ *          (two-sided image-slider objective, train_lora-scale.py:303-332)
+ *   dh_out [M, 16] element dtype, columns >= rank are zero; consumed by
+ *          slider_lora_input_grad
+ *   ws     caller workspace of slider_lora_grad_workspace_bytes(g) bytes
+ */
+size_t slider_lora_grad_workspace_bytes(const slider_layer_geom* g);
+int slider_lora_grad(const slider_layer_geom* g, float* dA, float* dB,
+                     void* dh_out, const void* gy, const void* x,
+                     const float* h, const void* B, float s, int accumulate,
+                     void* ws, size_t ws_bytes, void* stream);
+
+/*
+ * Input gradient:  dx = convT(gy, W) + convT(dh, A)   (one tcgen05 launch).
+ *   Wt  [cin, kh*kw, cout]  frozen, taps flipped: Wt[c][t][n] = W[n][T-1-t][c]
+ *   At  [cin, kh*kw, 16]    At[c][t][j] = A[j][T-1-t][c], j >= rank zero;
+ *                           produced by slider_lora_pack_at
+ *   dh  [M, 16]             from slider_lora_grad (NULL => base term only)
+ */
+int slider_lora_pack_at(const slider_layer_geom* g, void* At, const void* A,
+                        void* stream);
+int slider_lora_input_grad(const slider_layer_geom* g, void* dx, const void* gy,
+                           const void* Wt, const void* dh, const void* At,
+                           void* stream);
+
+/* One-time repack of a frozen base weight [cout, kh*kw, cin] into the Wt layout. */
+int slider_pack_wt(const slider_layer_geom* g, void* Wt, const void* W,
+                   void* stream);
+
+/*
+ * Slider guidance objective, forward and gradient in one pass.  Replaces
+ * PromptEmbedsPair._enhance/_erase + MSELoss
+ * (trainscripts/imagesliders/prompt_util.py:108-148,
+ *  conceptmod/textsliders/prompt_util.py:134-174) and its autograd:
+ *     tgt  = n + sign*g*(p - q);  loss = mean((t - tgt)^2);
+ *     grad = 2*(t - tgt)/n_elem            (grad may be NULL)
+ * sign = +1 enhance, -1 erase.  p == NULL selects plain MSE(t, n)
+ * (image sliders, trainscripts/imagesliders/train_lora-scale.py:303,327).
+ * loss_out: one fp32.  ws: slider_loss_workspace_bytes() bytes, zero-filled by
+ * the caller once; the kernel leaves it zeroed.  Deterministic reduction.
+ */
+size_t slider_loss_workspace_bytes(void);
+int slider_guidance_loss(float* loss_out, void* grad, const void* t,
+                         const void* p, const void* n, const void* q,
+                         int64_t n_elem, float g, int sign, int dtype, void* ws,
+                         size_t ws_bytes, void* stream);
+
+/*
+ * Classifier-free guidance + affine scheduler step.  Replaces
+ * train_util.predict_noise tail (conceptmod/textsliders/train_util.py:297-300)
+ * and scheduler.step (train_util.py:324; DDIM restated in
+ * trainscripts/imagesliders/train_lora-scale.py:31-39):
+ *     eps = eps_u + g*(eps_c - eps_u)
+ *     out = c_x*x + c_eps*eps + c_noise*noise
+ * x == NULL  -> out = eps                (pure CFG combine)
+ * eps_u == NULL -> out = c_x*x + c_noise*noise   (scheduler.add_noise)
+ * noise may be NULL.  dev_coef, if non-NULL, is a device float[4]
+ * {g, c_x, c_eps, c_noise} that overrides the host scalars (CUDA-graph replay).
+ */
+int slider_cfg_step(void* out, const void* x, const void* eps_u,
+                    const void* eps_c, const void* noise, int64_t n_elem,
+                    float g, float c_x, float c_eps, float c_noise,
+                    const float* dev_coef, int dtype, void* stream);
+
+/* x *= *dev_scalar  (chain rule for a non-unit upstream loss gradient). */
+int slider_scale_by_device_scalar(void* x, const float* dev_scalar,
+                                  int64_t n_elem, int dtype, void* stream);
+
+/*
+ * Flat-buffer AdamW over the contiguous LoRA parameter / gradient buffers
+ * (torch.optim.AdamW built at conceptmod/textsliders/train_lora.py:80-89 and
+ * train_lora_xl.py:104-105; clip_grad_norm_ at train_lora_xl.py:349).
+ *   p      element dtype, updated in place;  grad fp32;  m, v fp32 state
+ *   grad_scale_dev: optional device float multiplied into grad (1/world_size
+ *   and/or the clip coefficient); NULL => 1.
+ */
+int slider_adamw_flat(void* p, const float* grad, float* m, float* v,
+                      int64_t n_elem, float lr, float beta1, float beta2,
+                      float eps, float weight_decay, int step,
+                      const float* grad_scale_dev, int dtype, void* stream);
+/* out[0] = min(1, max_norm/(||grad||_2*pre_scale + 1e-6)) * pre_scale */
+int slider_clip_coef(float* out, const float* grad, int64_t n_elem,
+                     float max_norm, float pre_scale, void* ws, size_t ws_bytes,
+                     void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SLIDER_B200_H */

@@ -1,0 +1,92 @@
+"""ctypes binding of libslider_b200.so (the C ABI declared in include/slider_b200.h).
+
+There is no CPU or PyTorch fallback: if the shared library is missing or a call fails,
+an exception is raised.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+import torch
+
+PKG_DIR = Path(__file__).resolve().parent
+LIB_PATH = PKG_DIR / "libslider_b200.so"
+
+SLIDER_F32, SLIDER_BF16 = 0, 1
+
+
+class LayerGeom(C.Structure):
+    """Mirror of `slider_layer_geom`."""
+
+    _fields_ = [(n, C.c_int32) for n in
+                ("dtype", "batch", "height", "width", "cin", "cout", "kh", "kw", "pad", "rank")]
+
+
+_vp, _fp, _i64, _f, _i, _sz = C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_int, C.c_size_t
+_G = C.POINTER(LayerGeom)
+
+_SIGNATURES = {
+    "slider_version": (C.c_int, []),
+    "slider_last_error": (C.c_char_p, []),
+    "slider_launch_count": (C.c_int64, []),
+    "slider_lora_forward": (C.c_int, [_G, _vp, _vp, _vp, _vp, _vp, _vp, _fp, _f, _vp]),
+    "slider_lora_grad_workspace_bytes": (_sz, [_G]),
+    "slider_lora_grad": (C.c_int, [_G, _fp, _fp, _vp, _vp, _vp, _fp, _vp, _f, _i, _vp, _sz, _vp]),
+    "slider_lora_pack_at": (C.c_int, [_G, _vp, _vp, _vp]),
+    "slider_lora_input_grad": (C.c_int, [_G, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "slider_pack_wt": (C.c_int, [_G, _vp, _vp, _vp]),
+    "slider_loss_workspace_bytes": (_sz, []),
+    "slider_guidance_loss": (C.c_int, [_fp, _vp, _vp, _vp, _vp, _vp, _i64, _f, _i, _i, _vp, _sz, _vp]),
+    "slider_cfg_step": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _f, _f, _f, _f, _fp, _i, _vp]),
+    "slider_scale_by_device_scalar": (C.c_int, [_vp, _fp, _i64, _i, _vp]),
+    "slider_adamw_flat": (C.c_int, [_vp, _fp, _fp, _fp, _i64, _f, _f, _f, _f, _f, _i, _fp, _i, _vp]),
+    "slider_clip_coef": (C.c_int, [_fp, _fp, _i64, _f, _f, _vp, _sz, _vp]),
+}
+
+EXPORTS = tuple(_SIGNATURES)
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """Load the library (once). Raises if it has not been built."""
+    global _lib
+    if _lib is None:
+        if not LIB_PATH.exists():
+            raise RuntimeError(
+                f"{LIB_PATH} not found: build it with `python -m sliders_conceptmod_b200.build` "
+                "(there is no fallback path)")
+        h = C.CDLL(str(LIB_PATH))
+        for name, (res, args) in _SIGNATURES.items():
+            fn = getattr(h, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = h
+    return _lib
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        raise RuntimeError(f"libslider_b200 error {rc}: {lib().slider_last_error().decode()}")
+
+
+def dtype_code(dt: torch.dtype) -> int:
+    if dt == torch.float32:
+        return SLIDER_F32
+    if dt == torch.bfloat16:
+        return SLIDER_BF16
+    raise TypeError(f"libslider_b200 supports float32 and bfloat16, got {dt}")
+
+
+def ptr(t: torch.Tensor | None):
+    return None if t is None else t.data_ptr()
+
+
+def stream_ptr() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def require_cuda(*tensors: torch.Tensor | None) -> None:
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("sliders_conceptmod_b200 kernels need CUDA tensors (sm_100a); no CPU path exists")

@@ -1,0 +1,93 @@
+// Shared host/device helpers for libslider_b200 (sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+#include <atomic>
+
+#include "../../include/slider_b200.h"
+
+namespace slider {
+
+// ---- error plumbing ---------------------------------------------------------
+void set_error(const char* fmt, ...);
+extern std::atomic<long long> g_launches;
+
+#define SLIDER_CHECK_ARG(cond, ...)                  \
+  do {                                               \
+    if (!(cond)) {                                   \
+      ::slider::set_error(__VA_ARGS__);              \
+      return SLIDER_ERR_BAD_ARG;                     \
+    }                                                \
+  } while (0)
+
+#define SLIDER_CUDA(call)                                                     \
+  do {                                                                        \
+    cudaError_t e__ = (call);                                                 \
+    if (e__ != cudaSuccess) {                                                 \
+      ::slider::set_error("%s failed: %s (%s:%d)", #call,                     \
+                          cudaGetErrorString(e__), __FILE__, __LINE__);       \
+      return SLIDER_ERR_CUDA;                                                 \
+    }                                                                         \
+  } while (0)
+
+inline int post_launch(const char* what) {
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  cudaError_t e = cudaPeekAtLastError();
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    set_error("launch of %s failed: %s", what, cudaGetErrorString(e));
+    return SLIDER_ERR_CUDA;
+  }
+  return SLIDER_OK;
+}
+
+int sm_count();
+
+// ---- element access ---------------------------------------------------------
+template <typename T> struct Elem;
+template <> struct Elem<float> {
+  static constexpr int kVec = 4;  // elements per 16-byte access
+  __device__ static inline void load(const float* p, float (&v)[4]) {
+    float4 t = *reinterpret_cast<const float4*>(p);
+    v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+  }
+  __device__ static inline void store(float* p, const float (&v)[4]) {
+    *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+  }
+  __device__ static inline float to_f(float x) { return x; }
+  __device__ static inline float from_f(float x) { return x; }
+};
+template <> struct Elem<__nv_bfloat16> {
+  static constexpr int kVec = 8;
+  __device__ static inline void load(const __nv_bfloat16* p, float (&v)[8]) {
+    uint4 t = *reinterpret_cast<const uint4*>(p);
+    const uint32_t w[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      v[2 * i] = __uint_as_float(w[i] << 16);
+      v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+    }
+  }
+  __device__ static inline void store(__nv_bfloat16* p, const float (&v)[8]) {
+    uint32_t w[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+      w[i] = *reinterpret_cast<uint32_t*>(&h);
+    }
+    *reinterpret_cast<uint4*>(p) = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+  __device__ static inline float to_f(__nv_bfloat16 x) { return __bfloat162float(x); }
+  __device__ static inline __nv_bfloat16 from_f(float x) { return __float2bfloat16_rn(x); }
+};
+
+__device__ inline float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+}  // namespace slider

@@ -1,0 +1,451 @@
+// Fused base + low-rank implicit GEMM for sm_100a (tcgen05 + TMEM + TMA).
+//
+//   y[pix, n] = sum_{tap,c} x[pix + d(tap), c] * W[n, tap, c] + bias[n]
+//             + s * sum_j ( sum_{tap,c} x[pix + d(tap), c] * A[j, tap, c] ) * Bup[n, j]
+//
+// One persistent CTA per SM, 6 warps:
+//   warp 0      TMA producer  (4-D box loads of NHWC activations: padding = TMA OOB zero fill,
+//                              3-D box loads of the tap-major weights)
+//   warp 1      TMEM allocator + single-thread tcgen05.mma issuer
+//   warps 2..5  epilogue: tcgen05.ld -> registers -> (+bias, + s*h.Bup) -> global
+// The rank-r intermediate h = x (*) A lives in 16 extra TMEM columns next to the main
+// accumulator: it is produced by a second, N=16 MMA that re-uses the activation tile already
+// staged in shared memory, and is folded into the output in the epilogue with r FMAs per
+// element.  The accumulators are double buffered so the epilogue of tile i overlaps the
+// main loop of tile i+1.
+//
+// The same kernel computes the input gradient ("extended-K" mode): activations = gy,
+// weights = Wt, and one extra 16-wide K block per tap whose operands are dh and At.
+#include "common.cuh"
+#include "ptx.cuh"
+#include "tmap.cuh"
+
+namespace slider {
+
+constexpr int BM = 128;          // pixels (GEMM rows) per tile
+constexpr int BN = 160;          // output channels per tile; divides 320/640/960/1280/1920/2560
+constexpr int HCOLS = 16;        // TMEM columns of the low-rank accumulator (rank padded to 16)
+constexpr int ROW_BYTES = 128;   // K-block row = one 128-byte swizzle row
+constexpr int NSTAGES = 5;
+constexpr int ACC_STAGES = 2;
+constexpr int A_BYTES = BM * ROW_BYTES;      // 16 KB
+constexpr int B_BYTES = BN * ROW_BYTES;      // 20 KB
+constexpr int L_BYTES = HCOLS * ROW_BYTES;   // 2 KB
+constexpr int STAGE_BYTES = A_BYTES + B_BYTES + L_BYTES;
+constexpr int EXT_ELEMS = 16;    // width of the extended-K operand (dh / At), in elements
+constexpr int TMEM_COLS = 512;
+constexpr int kGemmThreads = 192;
+constexpr int EPI_FLOATS = BN * 16 + BN;     // s*Bup (rank padded to <=16) + bias
+constexpr size_t SMEM_BYTES = 1024 /*align slack*/ + (size_t)NSTAGES * STAGE_BYTES + EPI_FLOATS * 4 + 256;
+
+template <typename T> struct GemmTraits;
+template <> struct GemmTraits<__nv_bfloat16> {
+  static constexpr int kBK = 64;       // elements per 128-byte row
+  static constexpr uint32_t kFmt = 1;  // bf16
+  static constexpr int kExtRowBytes = EXT_ELEMS * 2;
+  __device__ static inline void mma(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) {
+    ptx::mma_f16(d, a, b, idesc, acc);
+  }
+};
+template <> struct GemmTraits<float> {
+  static constexpr int kBK = 32;
+  static constexpr uint32_t kFmt = 2;  // tf32
+  static constexpr int kExtRowBytes = EXT_ELEMS * 4;
+  __device__ static inline void mma(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) {
+    ptx::mma_tf32(d, a, b, idesc, acc);
+  }
+};
+
+struct GemmParams {
+  int TW, TH, TB, rows;   // tile box in pixels; rows = TW*TH*TB <= 128
+  int W, H, B;
+  int mt_w, mt_h, mt_b;   // number of pixel tiles per dimension
+  int n_tiles, N;
+  int taps, kw, pad, cblocks;
+  int rank;
+  float s;
+  int lora;               // accumulate h and apply it in the epilogue
+  int ext;                // extended-K operand pair present (input-gradient mode)
+  int total_tiles;
+  void* y;
+  const void* bias;
+  const void* Bup;
+  float* h_out;
+};
+
+struct TileCoord { int w0, h0, b0, n0, n_blk; };
+
+__device__ __forceinline__ TileCoord tile_coord(const GemmParams& p, int tile) {
+  TileCoord t;
+  t.n_blk = tile % p.n_tiles;
+  int mi = tile / p.n_tiles;
+  int wt = mi % p.mt_w; mi /= p.mt_w;
+  int ht = mi % p.mt_h;
+  int bt = mi / p.mt_h;
+  t.w0 = wt * p.TW; t.h0 = ht * p.TH; t.b0 = bt * p.TB; t.n0 = t.n_blk * BN;
+  return t;
+}
+
+template <typename T, int R4>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
+                 const __grid_constant__ CUtensorMap tmL, const __grid_constant__ CUtensorMap tmXe,
+                 const __grid_constant__ CUtensorMap tmWe, const GemmParams p) {
+  using Tr = GemmTraits<T>;
+  constexpr int BK = Tr::kBK;
+  constexpr int KSTEPS = ROW_BYTES / 32;   // one tcgen05.mma consumes 32 bytes of K per row
+  constexpr int EXT_KSTEPS = Tr::kExtRowBytes / 32;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  float* s_epi = reinterpret_cast<float*>(smem + (size_t)NSTAGES * STAGE_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_epi + EPI_FLOATS);
+  uint64_t* full_bar = bars;                      // [NSTAGES]  TMA -> MMA
+  uint64_t* empty_bar = bars + NSTAGES;           // [NSTAGES]  MMA -> TMA
+  uint64_t* tfull_bar = bars + 2 * NSTAGES;       // [ACC_STAGES] MMA -> epilogue
+  uint64_t* tempty_bar = tfull_bar + ACC_STAGES;  // [ACC_STAGES] epilogue -> MMA
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + ACC_STAGES);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tmA);
+    ptx::prefetch_tmap(&tmW);
+    if (p.lora) ptx::prefetch_tmap(&tmL);
+    if (p.ext) { ptx::prefetch_tmap(&tmXe); ptx::prefetch_tmap(&tmWe); }
+    for (int i = 0; i < NSTAGES; ++i) {
+      ptx::mbar_init(ptx::smem_u32(full_bar + i), 1);
+      ptx::mbar_init(ptx::smem_u32(empty_bar + i), 1);
+    }
+    for (int i = 0; i < ACC_STAGES; ++i) {
+      ptx::mbar_init(ptx::smem_u32(tfull_bar + i), 1);
+      ptx::mbar_init(ptx::smem_u32(tempty_bar + i), 4);  // one arrive per epilogue warp
+    }
+    ptx::fence_mbar_init();
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(ptx::smem_u32(tmem_slot), TMEM_COLS);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t smem_base = ptx::smem_u32(smem);
+
+  const uint32_t main_tx = (uint32_t)(p.rows * ROW_BYTES + B_BYTES + (p.lora ? L_BYTES : 0));
+  const uint32_t ext_tx = (uint32_t)((p.rows + BN) * Tr::kExtRowBytes);
+
+  if (warp == 0 && lane == 0) {
+    // ===================== TMA producer =====================
+    uint32_t stage = 0, phase = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+      const TileCoord tc = tile_coord(p, tile);
+      for (int tap = 0; tap < p.taps; ++tap) {
+        const int dy = tap / p.kw - p.pad, dx = tap % p.kw - p.pad;
+        for (int cb = 0; cb < p.cblocks; ++cb) {
+          ptx::mbar_wait(ptx::smem_u32(empty_bar + stage), phase ^ 1);
+          const uint32_t sa = smem_base + stage * STAGE_BYTES;
+          const uint32_t fb = ptx::smem_u32(full_bar + stage);
+          ptx::mbar_arrive_expect_tx(fb, main_tx);
+          ptx::tma_load_4d(sa, &tmA, fb, cb * BK, tc.w0 + dx, tc.h0 + dy, tc.b0);
+          ptx::tma_load_3d(sa + A_BYTES, &tmW, fb, cb * BK, tap, tc.n0);
+          if (p.lora) ptx::tma_load_3d(sa + A_BYTES + B_BYTES, &tmL, fb, cb * BK, tap, 0);
+          if (++stage == NSTAGES) { stage = 0; phase ^= 1; }
+        }
+        if (p.ext) {
+          ptx::mbar_wait(ptx::smem_u32(empty_bar + stage), phase ^ 1);
+          const uint32_t sa = smem_base + stage * STAGE_BYTES;
+          const uint32_t fb = ptx::smem_u32(full_bar + stage);
+          ptx::mbar_arrive_expect_tx(fb, ext_tx);
+          ptx::tma_load_4d(sa, &tmXe, fb, 0, tc.w0 + dx, tc.h0 + dy, tc.b0);
+          ptx::tma_load_3d(sa + A_BYTES, &tmWe, fb, 0, tap, tc.n0);
+          if (++stage == NSTAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1 && lane == 0) {
+    // ===================== MMA issuer =====================
+    constexpr uint32_t idesc_main = ptx::make_idesc(Tr::kFmt, BM, BN);
+    constexpr uint32_t idesc_h = ptx::make_idesc(Tr::kFmt, BM, HCOLS);
+    uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+      ptx::mbar_wait(ptx::smem_u32(tempty_bar + as), aphase ^ 1);
+      ptx::tc_fence_after();
+      const uint32_t d_main = tmem_base + as * (BN + HCOLS);
+      const uint32_t d_h = d_main + BN;
+      uint32_t acc = 0;
+      for (int tap = 0; tap < p.taps; ++tap) {
+        for (int cb = 0; cb < p.cblocks; ++cb) {
+          ptx::mbar_wait(ptx::smem_u32(full_bar + stage), phase);
+          ptx::tc_fence_after();
+          const uint32_t sa = smem_base + stage * STAGE_BYTES;
+          const uint64_t da = ptx::smem_desc_kmajor(sa, ROW_BYTES);
+          const uint64_t db = ptx::smem_desc_kmajor(sa + A_BYTES, ROW_BYTES);
+          const uint64_t dl = ptx::smem_desc_kmajor(sa + A_BYTES + B_BYTES, ROW_BYTES);
+#pragma unroll
+          for (int k = 0; k < KSTEPS; ++k) {
+            Tr::mma(d_main, da + 2 * k, db + 2 * k, idesc_main, acc | (uint32_t)k);
+            if (p.lora) Tr::mma(d_h, da + 2 * k, dl + 2 * k, idesc_h, acc | (uint32_t)k);
+          }
+          acc = 1;
+          ptx::mma_commit(ptx::smem_u32(empty_bar + stage));
+          if (++stage == NSTAGES) { stage = 0; phase ^= 1; }
+        }
+        if (p.ext) {
+          ptx::mbar_wait(ptx::smem_u32(full_bar + stage), phase);
+          ptx::tc_fence_after();
+          const uint32_t sa = smem_base + stage * STAGE_BYTES;
+          const uint64_t da = ptx::smem_desc_kmajor(sa, Tr::kExtRowBytes);
+          const uint64_t db = ptx::smem_desc_kmajor(sa + A_BYTES, Tr::kExtRowBytes);
+#pragma unroll
+          for (int k = 0; k < EXT_KSTEPS; ++k) Tr::mma(d_main, da + 2 * k, db + 2 * k, idesc_main, 1u);
+          ptx::mma_commit(ptx::smem_u32(empty_bar + stage));
+          if (++stage == NSTAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+      ptx::mma_commit(ptx::smem_u32(tfull_bar + as));
+      if (++as == ACC_STAGES) { as = 0; aphase ^= 1; }
+    }
+  } else if (warp >= 2) {
+    // ===================== epilogue =====================
+    const int q = warp & 3;               // TMEM lane quarter this warp may read
+    const int row = q * 32 + lane;        // tile row == TMEM lane
+    const int et = threadIdx.x - 64;      // 0..127 among epilogue threads
+    float* s_bias = s_epi + BN * 16;
+    uint32_t as = 0, aphase = 0;
+    T* __restrict__ y = reinterpret_cast<T*>(p.y);
+    const T* __restrict__ bias = reinterpret_cast<const T*>(p.bias);
+    const T* __restrict__ Bup = reinterpret_cast<const T*>(p.Bup);
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+      const TileCoord tc = tile_coord(p, tile);
+      // stage s*Bup[n0.., :] and bias[n0..] for this tile (fp32) while the MMAs run
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      for (int i = et; i < BN; i += 128) {
+        const int n = tc.n0 + i;
+        s_bias[i] = (bias != nullptr && n < p.N) ? Elem<T>::to_f(bias[n]) : 0.f;
+        if (R4 > 0) {
+#pragma unroll
+          for (int j = 0; j < 4 * R4; ++j)
+            s_epi[i * (4 * R4) + j] =
+                (n < p.N && j < p.rank) ? p.s * Elem<T>::to_f(Bup[(size_t)n * p.rank + j]) : 0.f;
+        }
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+
+      const int lw = row % p.TW, lh = (row / p.TW) % p.TH, lb = row / (p.TW * p.TH);
+      const bool row_ok = row < p.rows && tc.w0 + lw < p.W && tc.h0 + lh < p.H && tc.b0 + lb < p.B;
+      const size_t pix = ((size_t)(tc.b0 + lb) * p.H + (tc.h0 + lh)) * p.W + (tc.w0 + lw);
+
+      ptx::mbar_wait(ptx::smem_u32(tfull_bar + as), aphase);
+      ptx::tc_fence_after();
+      const uint32_t t_main = tmem_base + ((uint32_t)(q * 32) << 16) + as * (BN + HCOLS);
+
+      float hv[R4 > 0 ? 4 * R4 : 1];
+      if (R4 > 0) {
+        uint32_t hr[16];
+        ptx::tmem_ld_32x16(t_main + BN, hr);
+        ptx::tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 4 * R4; ++j) hv[j] = __uint_as_float(hr[j]);
+        if (p.h_out != nullptr && tc.n_blk == 0 && row_ok) {
+          for (int j = 0; j < p.rank; ++j) p.h_out[pix * p.rank + j] = __uint_as_float(hr[j]);
+        }
+      }
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t v[32];
+        ptx::tmem_ld_32x32(t_main + c * 32, v);
+        ptx::tmem_ld_wait();
+        const int nb = tc.n0 + c * 32;
+#pragma unroll
+        for (int g8 = 0; g8 < 4; ++g8) {
+          float o[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const int i = c * 32 + g8 * 8 + k;
+            float a = __uint_as_float(v[g8 * 8 + k]) + s_bias[i];
+            if (R4 > 0) {
+              const float4* bp = reinterpret_cast<const float4*>(s_epi + i * (4 * R4));
+#pragma unroll
+              for (int j4 = 0; j4 < R4; ++j4) {
+                const float4 b = bp[j4];
+                a = fmaf(hv[4 * j4 + 0], b.x, a);
+                a = fmaf(hv[4 * j4 + 1], b.y, a);
+                a = fmaf(hv[4 * j4 + 2], b.z, a);
+                a = fmaf(hv[4 * j4 + 3], b.w, a);
+              }
+            }
+            o[k] = a;
+          }
+          if (row_ok && nb + g8 * 8 < p.N) {
+            T* dst = y + pix * (size_t)p.N + nb + g8 * 8;
+            if (sizeof(T) == 2) {
+              Elem<__nv_bfloat16>::store(reinterpret_cast<__nv_bfloat16*>(dst), o);
+            } else {
+              float* d = reinterpret_cast<float*>(dst);
+              *reinterpret_cast<float4*>(d) = make_float4(o[0], o[1], o[2], o[3]);
+              *reinterpret_cast<float4*>(d + 4) = make_float4(o[4], o[5], o[6], o[7]);
+            }
+          }
+        }
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(tempty_bar + as));
+      if (++as == ACC_STAGES) { as = 0; aphase ^= 1; }
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+}  // namespace slider
+
+// =================================== host side ===================================
+namespace slider {
+
+struct TileGeom { int TW, TH, TB; };
+
+static TileGeom choose_tile(int W, int H, int B) {
+  TileGeom t;
+  t.TW = W < BM ? W : BM;
+  int rest = BM / t.TW;
+  t.TH = H < rest ? H : rest;
+  if (t.TH < 1) t.TH = 1;
+  rest = BM / (t.TW * t.TH);
+  t.TB = B < rest ? B : rest;
+  if (t.TB < 1) t.TB = 1;
+  return t;
+}
+
+static inline int esize(int dtype) { return dtype == SLIDER_BF16 ? 2 : 4; }
+
+template <typename T>
+static int launch_gemm(int r4, const CUtensorMap& a, const CUtensorMap& w, const CUtensorMap& l,
+                       const CUtensorMap& xe, const CUtensorMap& we, const GemmParams& p, cudaStream_t st) {
+  void (*kern)(CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, GemmParams) = nullptr;
+  switch (r4) {
+    case 0: kern = lora_gemm_kernel<T, 0>; break;
+    case 1: kern = lora_gemm_kernel<T, 1>; break;
+    case 2: kern = lora_gemm_kernel<T, 2>; break;
+    default: kern = lora_gemm_kernel<T, 4>; break;
+  }
+  static thread_local const void* configured[8] = {nullptr};
+  bool done = false;
+  for (auto c : configured) done |= (c == (const void*)kern);
+  if (!done) {
+    SLIDER_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
+    for (auto& c : configured) if (c == nullptr) { c = (const void*)kern; break; }
+  }
+  int grid = p.total_tiles < sm_count() ? p.total_tiles : sm_count();
+  kern<<<grid, kGemmThreads, SMEM_BYTES, st>>>(a, w, l, xe, we, p);
+  return post_launch("lora_gemm_kernel");
+}
+
+// Shared driver for forward (lora epilogue) and input-gradient (extended-K) modes.
+//   act      [B,H,W,kc]      activations (x or gy)
+//   wgt      [nn, taps, kc]  weights (W or Wt)
+//   lo       [rank, taps, kc] lora_down (forward only)
+//   xe / we  [B,H,W,16] / [nn, taps, 16]  extended-K pair (input gradient only)
+static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const void* act, const void* wgt,
+                    const void* bias, const void* lo, const void* Bup, float* h_out, float s, const void* xe,
+                    const void* we, cudaStream_t st) {
+  const int es = esize(g->dtype);
+  const int taps = g->kh * g->kw;
+  const int bk = ROW_BYTES / es;
+  SLIDER_CHECK_ARG(g->dtype == SLIDER_BF16 || g->dtype == SLIDER_F32, "lora gemm: unsupported dtype %d", g->dtype);
+  SLIDER_CHECK_ARG(g->kh == g->kw && (g->kh == 1 || g->kh == 3) && g->pad == (g->kh - 1) / 2,
+                   "lora gemm: only 1x1/pad0 and 3x3/pad1 stride-1 kernels (got %dx%d pad %d)", g->kh, g->kw, g->pad);
+  SLIDER_CHECK_ARG(g->batch > 0 && g->height > 0 && g->width > 0 && kc > 0 && nn > 0, "lora gemm: empty shape");
+  SLIDER_CHECK_ARG((kc * es) % 16 == 0 && (nn * es) % 16 == 0,
+                   "lora gemm: channel counts must be multiples of %d (cin %d, cout %d)", 16 / es, g->cin, g->cout);
+  SLIDER_CHECK_ARG(g->rank >= 0 && g->rank <= 16, "lora gemm: rank %d not in 0..16", g->rank);
+  SLIDER_CHECK_ARG(((uintptr_t)act & 15) == 0 && ((uintptr_t)wgt & 15) == 0 && ((uintptr_t)y & 15) == 0,
+                   "lora gemm: pointers must be 16-byte aligned");
+
+  const bool lora = lo != nullptr && g->rank > 0 && (s != 0.f || h_out != nullptr);
+  const bool ext = xe != nullptr;
+  const TileGeom tg = choose_tile(g->width, g->height, g->batch);
+
+  GemmParams p;
+  p.TW = tg.TW; p.TH = tg.TH; p.TB = tg.TB; p.rows = tg.TW * tg.TH * tg.TB;
+  p.W = g->width; p.H = g->height; p.B = g->batch;
+  p.mt_w = (g->width + tg.TW - 1) / tg.TW;
+  p.mt_h = (g->height + tg.TH - 1) / tg.TH;
+  p.mt_b = (g->batch + tg.TB - 1) / tg.TB;
+  p.n_tiles = (nn + BN - 1) / BN; p.N = nn;
+  p.taps = taps; p.kw = g->kw; p.pad = g->pad; p.cblocks = (kc + bk - 1) / bk;
+  p.rank = g->rank; p.s = s; p.lora = lora ? 1 : 0; p.ext = ext ? 1 : 0;
+  p.total_tiles = p.mt_w * p.mt_h * p.mt_b * p.n_tiles;
+  p.y = y; p.bias = bias; p.Bup = Bup; p.h_out = lora ? h_out : nullptr;
+  if (lora) {
+    SLIDER_CHECK_ARG(Bup != nullptr, "lora gemm: lora_up weight is NULL");
+    SLIDER_CHECK_ARG((g->rank * taps * kc * es) % 16 == 0 && ((uintptr_t)lo & 15) == 0, "lora gemm: lora_down misaligned");
+  }
+
+  CUtensorMap mA, mW, mL, mXe, mWe;
+  int rc;
+  {
+    uint64_t dims[4] = {(uint64_t)kc, (uint64_t)g->width, (uint64_t)g->height, (uint64_t)g->batch};
+    uint64_t str[3] = {(uint64_t)kc * es, (uint64_t)kc * es * g->width, (uint64_t)kc * es * g->width * g->height};
+    uint32_t box[4] = {(uint32_t)bk, (uint32_t)tg.TW, (uint32_t)tg.TH, (uint32_t)tg.TB};
+    if ((rc = make_tmap(&mA, g->dtype, 4, act, dims, str, box, ROW_BYTES))) return rc;
+  }
+  {
+    uint64_t dims[3] = {(uint64_t)kc, (uint64_t)taps, (uint64_t)nn};
+    uint64_t str[2] = {(uint64_t)kc * es, (uint64_t)kc * es * taps};
+    uint32_t box[3] = {(uint32_t)bk, 1u, (uint32_t)BN};
+    if ((rc = make_tmap(&mW, g->dtype, 3, wgt, dims, str, box, ROW_BYTES))) return rc;
+  }
+  mL = mW; mXe = mA; mWe = mW;
+  if (lora) {
+    uint64_t dims[3] = {(uint64_t)kc, (uint64_t)taps, (uint64_t)g->rank};
+    uint64_t str[2] = {(uint64_t)kc * es, (uint64_t)kc * es * taps};
+    uint32_t box[3] = {(uint32_t)bk, 1u, (uint32_t)HCOLS};
+    if ((rc = make_tmap(&mL, g->dtype, 3, lo, dims, str, box, ROW_BYTES))) return rc;
+  }
+  if (ext) {
+    SLIDER_CHECK_ARG(we != nullptr && ((uintptr_t)xe & 15) == 0 && ((uintptr_t)we & 15) == 0, "lora gemm: bad ext operands");
+    const uint32_t eb = EXT_ELEMS * es;
+    uint64_t dims[4] = {(uint64_t)EXT_ELEMS, (uint64_t)g->width, (uint64_t)g->height, (uint64_t)g->batch};
+    uint64_t str[3] = {(uint64_t)eb, (uint64_t)eb * g->width, (uint64_t)eb * g->width * g->height};
+    uint32_t box[4] = {(uint32_t)EXT_ELEMS, (uint32_t)tg.TW, (uint32_t)tg.TH, (uint32_t)tg.TB};
+    if ((rc = make_tmap(&mXe, g->dtype, 4, xe, dims, str, box, eb))) return rc;
+    uint64_t wdims[3] = {(uint64_t)EXT_ELEMS, (uint64_t)taps, (uint64_t)nn};
+    uint64_t wstr[2] = {(uint64_t)eb, (uint64_t)eb * taps};
+    uint32_t wbox[3] = {(uint32_t)EXT_ELEMS, 1u, (uint32_t)BN};
+    if ((rc = make_tmap(&mWe, g->dtype, 3, we, wdims, wstr, wbox, eb))) return rc;
+  }
+  const int r4 = !lora ? 0 : (g->rank <= 4 ? 1 : (g->rank <= 8 ? 2 : 4));
+  if (g->dtype == SLIDER_BF16) return launch_gemm<__nv_bfloat16>(r4, mA, mW, mL, mXe, mWe, p, st);
+  return launch_gemm<float>(r4, mA, mW, mL, mXe, mWe, p, st);
+}
+
+}  // namespace slider
+
+using namespace slider;
+
+extern "C" {
+
+int slider_lora_forward(const slider_layer_geom* g, void* y, const void* x, const void* W, const void* bias,
+                        const void* A, const void* B, float* h_out, float s, void* stream) {
+  SLIDER_CHECK_ARG(g && y && x && W, "lora_forward: null pointer");
+  return run_gemm(g, g->cin, g->cout, y, x, W, bias, A, B, h_out, s, nullptr, nullptr, (cudaStream_t)stream);
+}
+
+int slider_lora_input_grad(const slider_layer_geom* g, void* dx, const void* gy, const void* Wt, const void* dh,
+                           const void* At, void* stream) {
+  SLIDER_CHECK_ARG(g && dx && gy && Wt, "lora_input_grad: null pointer");
+  SLIDER_CHECK_ARG((dh == nullptr) == (At == nullptr), "lora_input_grad: dh and At must both be set or both NULL");
+  return run_gemm(g, g->cout, g->cin, dx, gy, Wt, nullptr, nullptr, nullptr, nullptr, 0.f, dh, At,
+                  (cudaStream_t)stream);
+}
+
+}  // extern "C"

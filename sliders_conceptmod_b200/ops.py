@@ -1,0 +1,177 @@
+"""Tensor-level wrappers over the C ABI (one function per exported kernel entry point).
+
+All tensors are CUDA tensors; activations of conv layers are NHWC-contiguous
+(`[B, H, W, C]`), linear activations are `[M, K]`.  Nothing here computes on the host.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import LayerGeom, check, dtype_code, lib, ptr, require_cuda, stream_ptr
+
+
+def make_geom(dtype: torch.dtype, batch: int, height: int, width: int, cin: int, cout: int,
+              ksize: int = 1, rank: int = 0) -> LayerGeom:
+    return LayerGeom(dtype_code(dtype), batch, height, width, cin, cout, ksize, ksize, (ksize - 1) // 2, rank)
+
+
+def _act_dims(x: torch.Tensor) -> tuple[int, int, int]:
+    if x.dim() == 4:
+        return x.shape[0], x.shape[1], x.shape[2]
+    if x.dim() == 2:
+        return 1, 1, x.shape[0]
+    raise ValueError(f"expected [B,H,W,C] or [M,K] activations, got {tuple(x.shape)}")
+
+
+def lora_forward(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None, a: torch.Tensor | None,
+                 b: torch.Tensor | None, s: float, ksize: int = 1, want_h: bool = False):
+    """y = conv(x, w) + bias + s * (conv(x, a) @ b^T).   (lora.py:134-138)
+
+    x [B,H,W,Cin] | [M,Cin];  w [Cout, k*k, Cin];  a [r, k*k, Cin];  b [Cout, r].
+    Returns (y, h) with h = conv(x, a) in fp32 ([pixels, r]) when want_h else None.
+    """
+    require_cuda(x, w, bias, a, b)
+    assert x.is_contiguous() and w.is_contiguous()
+    B, H, W = _act_dims(x)
+    cin, cout = x.shape[-1], w.shape[0]
+    rank = 0 if a is None else a.shape[0]
+    g = make_geom(x.dtype, B, H, W, cin, cout, ksize, rank)
+    y = torch.empty(*x.shape[:-1], cout, device=x.device, dtype=x.dtype)
+    h = torch.empty(B * H * W, rank, device=x.device, dtype=torch.float32) if (want_h and rank > 0) else None
+    check(lib().slider_lora_forward(C.byref(g), ptr(y), ptr(x), ptr(w), ptr(bias), ptr(a), ptr(b), ptr(h),
+                                    float(s), stream_ptr()))
+    return y, h
+
+
+def lora_input_grad(gy: torch.Tensor, wt: torch.Tensor, dh: torch.Tensor | None, at: torch.Tensor | None,
+                    cin: int, ksize: int = 1, rank: int = 0) -> torch.Tensor:
+    """dx = convT(gy, W) + convT(dh, A);  wt [Cin, k*k, Cout] flipped taps, at [Cin, k*k, 16]."""
+    require_cuda(gy, wt, dh, at)
+    assert gy.is_contiguous() and wt.is_contiguous()
+    B, H, W = _act_dims(gy)
+    g = make_geom(gy.dtype, B, H, W, cin, gy.shape[-1], ksize, rank)
+    dx = torch.empty(*gy.shape[:-1], cin, device=gy.device, dtype=gy.dtype)
+    check(lib().slider_lora_input_grad(C.byref(g), ptr(dx), ptr(gy), ptr(wt), ptr(dh), ptr(at), stream_ptr()))
+    return dx
+
+
+_loss_ws: dict[int, torch.Tensor] = {}
+
+
+def _reduce_ws(device: torch.device) -> torch.Tensor:
+    key = device.index if device.index is not None else torch.cuda.current_device()
+    ws = _loss_ws.get(key)
+    if ws is None:
+        ws = torch.zeros(lib().slider_loss_workspace_bytes(), dtype=torch.uint8, device=device)
+        _loss_ws[key] = ws
+    return ws
+
+
+def guidance_loss(t: torch.Tensor, p: torch.Tensor | None, n: torch.Tensor, q: torch.Tensor | None,
+                  guidance: float, sign: int, want_grad: bool = True):
+    """loss = mean((t - (n + sign*g*(p - q)))^2), grad = dloss/dt  (prompt_util.py:108-148).
+
+    Returns (loss fp32 0-dim, grad like t or None).  p is None => plain MSE(t, n).
+    """
+    require_cuda(t, p, n, q)
+    ts = [x.contiguous() for x in (t, n)] + [None if x is None else x.contiguous() for x in (p, q)]
+    t_, n_, p_, q_ = ts
+    for x in (n_, p_, q_):
+        if x is not None and (x.shape != t_.shape or x.dtype != t_.dtype):
+            raise ValueError("guidance_loss: all latents must share shape and dtype")
+    loss = torch.empty((), device=t.device, dtype=torch.float32)
+    grad = torch.empty_like(t_) if want_grad else None
+    ws = _reduce_ws(t.device)
+    check(lib().slider_guidance_loss(ptr(loss), ptr(grad), ptr(t_), ptr(p_), ptr(n_), ptr(q_), t_.numel(),
+                                     float(guidance), int(sign), dtype_code(t_.dtype), ptr(ws), ws.numel(),
+                                     stream_ptr()))
+    return loss, grad
+
+
+def cfg_step(x: torch.Tensor | None, eps_u: torch.Tensor | None, eps_c: torch.Tensor | None,
+             noise: torch.Tensor | None = None, guidance: float = 1.0, c_x: float = 1.0, c_eps: float = 1.0,
+             c_noise: float = 0.0, dev_coef: torch.Tensor | None = None, out: torch.Tensor | None = None):
+    """out = c_x*x + c_eps*(eps_u + g*(eps_c - eps_u)) + c_noise*noise  (train_util.py:297-300,324)."""
+    ref = x if x is not None else eps_u
+    require_cuda(x, eps_u, eps_c, noise, dev_coef)
+    for tns in (x, eps_u, eps_c, noise):
+        if tns is not None and not tns.is_contiguous():
+            raise ValueError("cfg_step: tensors must be contiguous")
+    if out is None:
+        out = torch.empty_like(ref)
+    check(lib().slider_cfg_step(ptr(out), ptr(x), ptr(eps_u), ptr(eps_c), ptr(noise), ref.numel(), float(guidance),
+                                float(c_x), float(c_eps), float(c_noise), ptr(dev_coef), dtype_code(ref.dtype),
+                                stream_ptr()))
+    return out
+
+
+def scale_by_device_scalar(x: torch.Tensor, scalar: torch.Tensor) -> torch.Tensor:
+    require_cuda(x, scalar)
+    assert x.is_contiguous() and scalar.dtype == torch.float32
+    check(lib().slider_scale_by_device_scalar(ptr(x), ptr(scalar), x.numel(), dtype_code(x.dtype), stream_ptr()))
+    return x
+
+
+def launch_count() -> int:
+    return int(lib().slider_launch_count())
+
+
+def pack_wt(w: torch.Tensor, ksize: int = 1) -> torch.Tensor:
+    """Wt[c][t][n] = W[n][T-1-t][c] — one-time re-layout of a frozen base weight [Cout, k*k, Cin]."""
+    require_cuda(w)
+    cout, taps, cin = w.shape
+    g = make_geom(w.dtype, 1, 1, 1, cin, cout, ksize, 0)
+    wt = torch.empty(cin, taps, cout, device=w.device, dtype=w.dtype)
+    check(lib().slider_pack_wt(C.byref(g), ptr(wt), ptr(w.contiguous()), stream_ptr()))
+    return wt
+
+
+def pack_at(a: torch.Tensor, ksize: int = 1) -> torch.Tensor:
+    """At[c][t][j] = A[j][T-1-t][c], rank padded to 16 (operand of the input-gradient GEMM)."""
+    require_cuda(a)
+    rank, taps, cin = a.shape
+    g = make_geom(a.dtype, 1, 1, 1, cin, 8, ksize, rank)
+    at = torch.empty(cin, taps, 16, device=a.device, dtype=a.dtype)
+    check(lib().slider_lora_pack_at(C.byref(g), ptr(at), ptr(a.contiguous()), stream_ptr()))
+    return at
+
+
+def lora_grad(gy: torch.Tensor, x: torch.Tensor, h: torch.Tensor, b: torch.Tensor, s: float, ksize: int,
+              dA: torch.Tensor, dB: torch.Tensor, accumulate: bool = False) -> torch.Tensor:
+    """Low-rank backward (autograd of lora.py:134-138): fills dA [r,k*k,Cin], dB [Cout,r] (fp32) and
+    returns dh [pixels,16] = s * gy @ B (element dtype, zero padded)."""
+    require_cuda(gy, x, h, b, dA, dB)
+    assert gy.is_contiguous() and x.is_contiguous() and h.is_contiguous() and b.is_contiguous()
+    assert dA.dtype == torch.float32 and dB.dtype == torch.float32 and dA.is_contiguous() and dB.is_contiguous()
+    B, H, W = _act_dims(x)
+    rank = b.shape[1]
+    g = make_geom(x.dtype, B, H, W, x.shape[-1], gy.shape[-1], ksize, rank)
+    dh = torch.empty(B * H * W, 16, device=x.device, dtype=x.dtype)
+    check(lib().slider_lora_grad(C.byref(g), ptr(dA), ptr(dB), ptr(dh), ptr(gy), ptr(x), ptr(h), ptr(b), float(s),
+                                 int(bool(accumulate)), None, 0, stream_ptr()))
+    return dh
+
+
+def adamw_flat(p: torch.Tensor, grad: torch.Tensor, m: torch.Tensor, v: torch.Tensor, lr: float, beta1: float,
+               beta2: float, eps: float, weight_decay: float, step: int,
+               grad_scale: torch.Tensor | None = None) -> None:
+    """In-place AdamW over flat buffers (train_lora.py:80-89; train_lora_xl.py:104-105)."""
+    require_cuda(p, grad, m, v, grad_scale)
+    assert p.is_contiguous() and grad.dtype == m.dtype == v.dtype == torch.float32
+    check(lib().slider_adamw_flat(ptr(p), ptr(grad), ptr(m), ptr(v), p.numel(), float(lr), float(beta1),
+                                  float(beta2), float(eps), float(weight_decay), int(step), ptr(grad_scale),
+                                  dtype_code(p.dtype), stream_ptr()))
+
+
+def clip_coef(grad: torch.Tensor, max_norm: float, pre_scale: float = 1.0) -> torch.Tensor:
+    """Device scalar min(1, max_norm/(||grad||*pre_scale+1e-6))*pre_scale (train_lora_xl.py:349)."""
+    require_cuda(grad)
+    assert grad.dtype == torch.float32 and grad.is_contiguous()
+    out = torch.empty((), device=grad.device, dtype=torch.float32)
+    ws = _reduce_ws(grad.device)
+    check(lib().slider_clip_coef(ptr(out), ptr(grad), grad.numel(), float(max_norm), float(pre_scale), ptr(ws),
+                                 ws.numel(), stream_ptr()))
+    return out
