@@ -1,0 +1,334 @@
+"""LoRAModule / LoRANetwork — host-side mirror of the reference adapter API.
+
+Reference: conceptmod/textsliders/lora.py:76-301 (fork) and
+trainscripts/imagesliders/lora.py:49-256 (upstream).  Same constructor arguments, attribute
+names (`lora_down`, `lora_up`, `scale`, `multiplier`, buffer `alpha`), forward-patching semantics,
+naming of the saved keys, `with network:` / `set_lora_slider` behaviour.  The arithmetic of
+`LoRAModule.forward` and its autograd is NOT done with torch ops: it is one call into
+libslider_b200 (fused base+low-rank tcgen05 GEMM) and, in backward, the low-rank gradient kernels
+plus the extended-K input-gradient GEMM.
+"""
+from __future__ import annotations
+
+import math
+import os
+from typing import List, Literal, Optional
+
+import torch
+import torch.nn as nn
+
+from . import ops
+
+UNET_TARGET_REPLACE_MODULE_TRANSFORMER = ["Attention"]
+UNET_TARGET_REPLACE_MODULE_CONV = ["ResnetBlock2D", "Downsample2D", "Upsample2D", "DownBlock2D", "UpBlock2D"]
+LORA_PREFIX_UNET = "lora_unet"
+DEFAULT_TARGET_REPLACE = UNET_TARGET_REPLACE_MODULE_TRANSFORMER
+
+TRAINING_METHODS = Literal[
+    "noxattn", "innoxattn", "selfattn", "xattn", "full", "xattn-strict", "noxattn-hspace", "noxattn-hspace-last",
+]
+
+
+class _FusedLoRAFn(torch.autograd.Function):
+    """y = conv(x, W) + b + s*(conv(x, A) . B^T) on [B,H,W,C] / [M,K] activations (lora.py:134-138)."""
+
+    @staticmethod
+    def forward(ctx, x, a_w, b_w, mod: "LoRAModule"):
+        s = float(mod.multiplier) * float(mod.scale)
+        k = mod._ksize
+        a_p, b_p = mod._packed_down(a_w), mod._packed_up(b_w)
+        need_x, need_a, need_b = ctx.needs_input_grad[0], ctx.needs_input_grad[1], ctx.needs_input_grad[2]
+        train_lora = (need_a or need_b) and s != 0.0
+        y, h = ops.lora_forward(x, mod._packed_base(), mod._bias(), a_p, b_p, s, ksize=k, want_h=train_lora)
+        ctx.mod, ctx.s, ctx.train_lora = mod, s, train_lora
+        ctx.save_for_backward(x if train_lora else None, h, a_p, b_p)
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        mod, s = ctx.mod, ctx.s
+        x, h, a_p, b_p = ctx.saved_tensors
+        gy = gy.contiguous()
+        k, r = mod._ksize, mod.lora_dim
+        dx = ga = gb = dh = None
+        if ctx.train_lora:
+            flat = mod._flat_grads
+            if flat is not None:
+                dA, dB = flat
+                dh = ops.lora_grad(gy, x, h, b_p, s, k, dA, dB, accumulate=True)
+            else:
+                dA = torch.empty(a_p.shape, device=gy.device, dtype=torch.float32)
+                dB = torch.empty(b_p.shape, device=gy.device, dtype=torch.float32)
+                dh = ops.lora_grad(gy, x, h, b_p, s, k, dA, dB, accumulate=False)
+                ga = mod._unpack_down_grad(dA)
+                gb = dB.to(b_p.dtype).reshape(mod.lora_up.weight.shape)
+        if ctx.needs_input_grad[0]:
+            at = ops.pack_at(a_p, k) if dh is not None else None
+            dx = ops.lora_input_grad(gy, mod._packed_base_t(), dh, at, mod._cin, k, r if dh is not None else 0)
+        return dx, ga, gb, None
+
+
+class LoRAModule(nn.Module):
+    """replaces forward method of the original Linear / Conv2d, instead of replacing the module
+    (reference lora.py:76-138)."""
+
+    def __init__(self, lora_name, org_module: nn.Module, multiplier=1.0, lora_dim=4, alpha=None):
+        """if alpha == 0 or None, alpha is rank (no scaling)."""
+        super().__init__()
+        self.lora_name = lora_name
+        self.lora_dim = lora_dim
+        cls = org_module.__class__.__name__
+        if "Linear" in cls:
+            in_dim, out_dim = org_module.in_features, org_module.out_features
+            self.lora_down = nn.Linear(in_dim, lora_dim, bias=False)
+            self.lora_up = nn.Linear(lora_dim, out_dim, bias=False)
+            self._ksize, self._stride, self._is_conv = 1, 1, False
+        elif "Conv" in cls:
+            in_dim, out_dim = org_module.in_channels, org_module.out_channels
+            self.lora_dim = min(self.lora_dim, in_dim, out_dim)
+            if self.lora_dim != lora_dim:
+                print(f"{lora_name} dim (rank) is changed to: {self.lora_dim}")
+            ks, st, pd = org_module.kernel_size, org_module.stride, org_module.padding
+            self.lora_down = nn.Conv2d(in_dim, self.lora_dim, ks, st, pd, bias=False)
+            self.lora_up = nn.Conv2d(self.lora_dim, out_dim, (1, 1), (1, 1), bias=False)
+            ok = (ks[0] == ks[1] and ks[0] in (1, 3) and st[0] == st[1] and st[0] in (1, 2)
+                  and tuple(pd) == ((ks[0] - 1) // 2,) * 2 and org_module.groups == 1
+                  and tuple(org_module.dilation) == (1, 1) and (st[0] == 1 or ks[0] == 3))
+            if not ok:
+                raise NotImplementedError(
+                    f"{lora_name}: conv geometry k={ks} s={st} p={pd} is outside the fused kernel's coverage")
+            self._ksize, self._stride, self._is_conv = ks[0], st[0], True
+        else:
+            raise NotImplementedError(f"{lora_name}: cannot wrap {cls}")
+        self._cin, self._cout = in_dim, out_dim
+
+        if type(alpha) == torch.Tensor:
+            alpha = alpha.detach().numpy()
+        alpha = lora_dim if alpha is None or alpha == 0 else alpha
+        self.scale = alpha / self.lora_dim
+        self.register_buffer("alpha", torch.tensor(alpha))
+
+        nn.init.kaiming_uniform_(self.lora_down.weight, a=1)   # fork: a=1; upstream: a=sqrt(5)
+        nn.init.zeros_(self.lora_up.weight)
+
+        self.multiplier = multiplier
+        self.org_module = org_module  # removed in apply_to (reference keeps it out of state_dict)
+        self._flat_grads = None
+        self._cache = {}
+
+    def apply_to(self):
+        self.org_forward = self.org_module.forward
+        self.org_module.forward = self.forward
+        self.__dict__["_org"] = self.org_module       # plain reference, not a registered submodule
+        del self.org_module
+
+    # ---- operand views / one-time re-layouts ------------------------------------------------
+    def _bias(self):
+        return self._org.bias
+
+    def _packed_base(self) -> torch.Tensor:
+        """Frozen base weight as [Cout, k*k, Cin] (tap-major).  Conv weights are switched to
+        channels_last storage in place once, so this is a view, not a copy."""
+        w = self._org.weight
+        key = ("w", w.data_ptr(), w._version, w.dtype)
+        hit = self._cache.get("w")
+        if hit is not None and hit[0] == key:
+            return hit[1]
+        if self._is_conv and self._ksize > 1:
+            if not w.is_contiguous(memory_format=torch.channels_last):
+                w.data = w.data.contiguous(memory_format=torch.channels_last)
+            p = w.detach().permute(0, 2, 3, 1).reshape(self._cout, self._ksize * self._ksize, self._cin)
+            key = ("w", w.data_ptr(), w._version, w.dtype)
+        else:
+            p = w.detach().reshape(self._cout, 1, self._cin)
+        assert p.is_contiguous()
+        self._cache["w"] = (key, p)
+        self._cache.pop("wt", None)
+        return p
+
+    def _packed_base_t(self) -> torch.Tensor:
+        w = self._packed_base()
+        hit = self._cache.get("wt")
+        if hit is None:
+            hit = ops.pack_wt(w, self._ksize)
+            self._cache["wt"] = hit
+        return hit
+
+    def _packed_down(self, a_w: torch.Tensor) -> torch.Tensor:
+        r, T = self.lora_dim, self._ksize * self._ksize
+        if not self._is_conv or self._ksize == 1:
+            return a_w.detach().reshape(r, 1, self._cin)
+        a = a_w.detach().permute(0, 2, 3, 1)
+        return (a if a.is_contiguous() else a.contiguous()).reshape(r, T, self._cin)
+
+    def _packed_up(self, b_w: torch.Tensor) -> torch.Tensor:
+        return b_w.detach().reshape(self._cout, self.lora_dim)
+
+    def _unpack_down_grad(self, dA: torch.Tensor) -> torch.Tensor:
+        w = self.lora_down.weight
+        if not self._is_conv:
+            return dA.reshape(w.shape).to(w.dtype)
+        g = dA.reshape(self.lora_dim, self._ksize, self._ksize, self._cin).permute(0, 3, 1, 2)
+        return g.to(w.dtype)
+
+    # ---- forward ----------------------------------------------------------------------------
+    def forward(self, x):
+        if not x.is_cuda:
+            raise RuntimeError("LoRAModule.forward runs on sm_100a only (libslider_b200); got a CPU tensor")
+        a_w, b_w = self.lora_down.weight, self.lora_up.weight
+        if a_w.dtype != x.dtype:
+            raise TypeError(f"{self.lora_name}: activation dtype {x.dtype} != LoRA dtype {a_w.dtype}")
+        if self._is_conv:
+            xn = x.permute(0, 2, 3, 1)
+            if not xn.is_contiguous():
+                xn = xn.contiguous()
+            y = _FusedLoRAFn.apply(xn, a_w, b_w, self)
+            if self._stride == 2:   # stride-2 pad-1 conv == stride-1 pad-1 conv sampled at even pixels
+                y = y[:, ::2, ::2, :].contiguous()
+            return y.permute(0, 3, 1, 2)
+        lead = x.shape[:-1]
+        x2 = x.reshape(-1, self._cin)
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        y = _FusedLoRAFn.apply(x2, a_w, b_w, self)
+        return y.reshape(*lead, self._cout)
+
+
+class LoRANetwork(nn.Module):
+    """Reference conceptmod/textsliders/lora.py:141-301; also accepts the upstream positional form
+    `LoRANetwork(unet, rank, multiplier, alpha, train_method)` (trainscripts/imagesliders/lora.py:114-121)."""
+
+    def __init__(self, unet, rank: int = 4, multiplier: float = 1.0, delimiter: str = "_", alpha: float = 1.0,
+                 target_replace=DEFAULT_TARGET_REPLACE, prefix=LORA_PREFIX_UNET,
+                 train_method: TRAINING_METHODS = "full") -> None:
+        super().__init__()
+        if not isinstance(delimiter, str):          # upstream call order: (unet, rank, multiplier, alpha, method)
+            if isinstance(alpha, str):
+                train_method = alpha
+            alpha, delimiter = delimiter, "_"
+        self.lora_scale = 1
+        self.multiplier = multiplier
+        self.lora_dim = rank
+        self.alpha = alpha
+        self.module = LoRAModule
+        self.unet_loras = self.create_modules(prefix, unet, target_replace, delimiter, self.lora_dim,
+                                              self.multiplier, train_method=train_method)
+        lora_names = set()
+        for lora in self.unet_loras:
+            assert lora.lora_name not in lora_names, f"duplicated lora name: {lora.lora_name}. {lora_names}"
+            lora_names.add(lora.lora_name)
+        for lora in self.unet_loras:
+            lora.apply_to()
+            self.add_module(lora.lora_name, lora)
+        self.flat_param = None
+        self.flat_grad = None
+        del unet
+
+    def create_modules(self, prefix: str, root_module: nn.Module, target_replace_modules: List[str],
+                       delimiter: str, rank: int, multiplier: float, train_method: TRAINING_METHODS) -> list:
+        loras, names = [], []
+        for name, module in root_module.named_modules():
+            if train_method in ("noxattn", "noxattn-hspace", "noxattn-hspace-last"):
+                if "attn2" in name or "time_embed" in name:
+                    continue
+            elif train_method == "innoxattn":
+                if "attn2" in name:
+                    continue
+            elif train_method == "selfattn":
+                if "attn1" not in name:
+                    continue
+            elif train_method in ("xattn", "xattn-strict"):
+                if "attn2" not in name:
+                    continue
+            elif train_method == "full":
+                pass
+            else:
+                raise NotImplementedError(f"train_method: {train_method} is not implemented.")
+            if module.__class__.__name__ in target_replace_modules:
+                for child_name, child_module in module.named_modules():
+                    if "add_" in child_name:
+                        continue
+                    if child_module.__class__.__name__ in ["Linear", "Conv2d", "LoRACompatibleLinear",
+                                                           "LoRACompatibleConv"]:
+                        if train_method == "xattn-strict" and "out" in child_name:
+                            continue
+                        if train_method == "noxattn-hspace" and "mid_block" not in name:
+                            continue
+                        if train_method == "noxattn-hspace-last":
+                            if "mid_block" not in name or ".1" not in name or "conv2" not in child_name:
+                                continue
+                        lora_name = (prefix + "." + name + "." + child_name).replace(".", delimiter)
+                        # constructed even when dropped as a duplicate: keeps the RNG stream of the reference
+                        lora = self.module(lora_name, child_module, multiplier, rank, self.alpha)
+                        if lora_name not in names:
+                            loras.append(lora)
+                            names.append(lora_name)
+        return loras
+
+    def prepare_optimizer_params(self):
+        all_params = []
+        if self.unet_loras:
+            params = []
+            [params.extend(lora.parameters()) for lora in self.unet_loras]
+            all_params.append({"params": params})
+        return all_params
+
+    def get_state_dict(self, dtype=None):
+        state_dict = self.state_dict()
+        for key in list(state_dict.keys()):
+            v = state_dict[key].detach().clone().to("cpu")
+            state_dict[key] = v.to(dtype).contiguous() if dtype is not None else v.contiguous()
+        return state_dict
+
+    def save_weights(self, file, dtype=None, metadata: Optional[dict] = None):
+        state_dict = self.get_state_dict(dtype)
+        if os.path.splitext(file)[1] == ".safetensors":
+            from safetensors.torch import save_file
+            save_file(state_dict, file, metadata)
+        else:
+            torch.save(state_dict, file)
+
+    def set_lora_slider(self, scale):
+        self.lora_scale = scale
+
+    def __enter__(self):
+        for lora in self.unet_loras:
+            lora.multiplier = 1.0 * self.lora_scale
+
+    def __exit__(self, exc_type, exc_value, tb):
+        for lora in self.unet_loras:
+            lora.multiplier = 0
+
+    # ---- B200 extension: one contiguous parameter buffer + one fp32 gradient buffer ------------
+    def flatten(self):
+        """Re-home every LoRA factor in ONE flat parameter buffer and allocate ONE flat fp32 gradient
+        buffer with the same element order.  The gradient kernels then accumulate straight into that
+        buffer (no per-tensor .grad), so data-parallel training needs a single all-reduce and a single
+        fused AdamW launch.  Conv `lora_down` factors are stored tap-major
+        (channels_last strides): state_dict()/save_weights() are unchanged.  Call after `.to(device, dtype)`.
+        """
+        params = [p for lora in self.unet_loras for p in (lora.lora_down.weight, lora.lora_up.weight)]
+        dev, dt = params[0].device, params[0].dtype
+        total = sum(p.numel() for p in params)
+        flat = torch.empty(total, device=dev, dtype=dt)
+        gflat = torch.zeros(total, device=dev, dtype=torch.float32)
+        off = 0
+        for lora in self.unet_loras:
+            a, b = lora.lora_down.weight, lora.lora_up.weight
+            r, T = lora.lora_dim, lora._ksize * lora._ksize
+            na, nb = a.numel(), b.numel()
+            fa, fb = flat[off:off + na], flat[off + na:off + na + nb]
+            if lora._is_conv:
+                fa4 = fa.view(r, lora._ksize, lora._ksize, lora._cin).permute(0, 3, 1, 2)
+                fa4.copy_(a.data)
+                a.data = fa4
+            else:
+                fa.view_as(a).copy_(a.data)
+                a.data = fa.view_as(a)
+            fb.view_as(b).copy_(b.data)
+            b.data = fb.view_as(b)
+            lora._flat_grads = (gflat[off:off + na].view(r, T, lora._cin),
+                                gflat[off + na:off + na + nb].view(lora._cout, r))
+            off += na + nb
+        self.flat_param, self.flat_grad = flat, gflat
+        return flat, gflat

@@ -1,0 +1,383 @@
+"""Random-init stand-in for diffusers' `UNet2DConditionModel` (SD-1.x and SD-XL shapes).
+
+diffusers is not installable here (no network), so the substrate the slider path runs on is
+rebuilt from the published SD-1.4 / SD-XL UNet configs.  Only what the hot
+path needs is mirrored: the *class names* and *attribute names* that
+`LoRANetwork.create_modules` (reference conceptmod/textsliders/lora.py:194-251) matches on, so
+the same 150 / 280 / 346 LoRA keys come out, and the call signature
+`unet(latents, t, encoder_hidden_states=..., added_cond_kwargs=...).sample`
+(reference conceptmod/textsliders/train_util.py:290-294, 471-476).
+
+Activations are kept channels_last (NHWC in memory) end to end so the wrapped Conv2d layers can
+hand their input to the TMA-fed implicit-GEMM kernel without a transpose.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass, field
+from types import SimpleNamespace
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+
+@dataclass
+class UNetConfig:
+    in_channels: int = 4
+    out_channels: int = 4
+    sample_size: int = 64
+    block_out_channels: tuple = (320, 640, 1280, 1280)
+    down_block_types: tuple = ("CrossAttnDownBlock2D", "CrossAttnDownBlock2D", "CrossAttnDownBlock2D", "DownBlock2D")
+    up_block_types: tuple = ("UpBlock2D", "CrossAttnUpBlock2D", "CrossAttnUpBlock2D", "CrossAttnUpBlock2D")
+    layers_per_block: int = 2
+    transformer_layers_per_block: tuple = (1, 1, 1, 1)
+    attention_head_dim: tuple = (8, 8, 8, 8)       # SD-1.x: number of heads; XL: see num_heads_from_dim
+    head_dim_is_heads: bool = True
+    cross_attention_dim: int = 768
+    use_linear_projection: bool = False
+    addition_embed: bool = False                   # SD-XL text_time conditioning
+    addition_time_embed_dim: int = 256
+    projection_class_embeddings_input_dim: int = 2816
+    norm_num_groups: int = 32
+
+    @staticmethod
+    def sd14() -> "UNetConfig":
+        return UNetConfig()
+
+    @staticmethod
+    def sdxl() -> "UNetConfig":
+        return UNetConfig(
+            sample_size=128, block_out_channels=(320, 640, 1280),
+            down_block_types=("DownBlock2D", "CrossAttnDownBlock2D", "CrossAttnDownBlock2D"),
+            up_block_types=("CrossAttnUpBlock2D", "CrossAttnUpBlock2D", "UpBlock2D"),
+            transformer_layers_per_block=(1, 2, 10), attention_head_dim=(5, 10, 20), cross_attention_dim=2048,
+            use_linear_projection=True, addition_embed=True)
+
+    @staticmethod
+    def tiny(cross_attention_dim: int = 64) -> "UNetConfig":
+        """Small config with the same topology (tests, CPU oracle runs)."""
+        return UNetConfig(sample_size=16, block_out_channels=(32, 64), layers_per_block=1,
+                          down_block_types=("CrossAttnDownBlock2D", "DownBlock2D"),
+                          up_block_types=("UpBlock2D", "CrossAttnUpBlock2D"),
+                          transformer_layers_per_block=(1, 1), attention_head_dim=(2, 2),
+                          cross_attention_dim=cross_attention_dim, norm_num_groups=8)
+
+
+def timestep_embedding(t: torch.Tensor, dim: int, flip_sin_to_cos: bool = True, shift: float = 0.0) -> torch.Tensor:
+    half = dim // 2
+    exponent = -math.log(10000.0) * torch.arange(half, dtype=torch.float32, device=t.device) / (half - shift)
+    emb = t[:, None].float() * torch.exp(exponent)[None, :]
+    emb = torch.cat([torch.sin(emb), torch.cos(emb)], dim=-1)
+    if flip_sin_to_cos:
+        emb = torch.cat([emb[:, half:], emb[:, :half]], dim=-1)
+    return emb
+
+
+class Timesteps(nn.Module):
+    def __init__(self, dim: int):
+        super().__init__()
+        self.dim = dim
+
+    def forward(self, t):
+        return timestep_embedding(t, self.dim, True, 0.0)
+
+
+class TimestepEmbedding(nn.Module):
+    def __init__(self, in_dim: int, dim: int):
+        super().__init__()
+        self.linear_1 = nn.Linear(in_dim, dim)
+        self.act = nn.SiLU()
+        self.linear_2 = nn.Linear(dim, dim)
+
+    def forward(self, x):
+        return self.linear_2(self.act(self.linear_1(x)))
+
+
+class ResnetBlock2D(nn.Module):
+    def __init__(self, in_ch: int, out_ch: int, temb_ch: int, groups: int):
+        super().__init__()
+        self.norm1 = nn.GroupNorm(groups, in_ch, eps=1e-5)
+        self.conv1 = nn.Conv2d(in_ch, out_ch, 3, padding=1)
+        self.time_emb_proj = nn.Linear(temb_ch, out_ch)
+        self.norm2 = nn.GroupNorm(groups, out_ch, eps=1e-5)
+        self.dropout = nn.Dropout(0.0)
+        self.conv2 = nn.Conv2d(out_ch, out_ch, 3, padding=1)
+        self.nonlinearity = nn.SiLU()
+        self.conv_shortcut = nn.Conv2d(in_ch, out_ch, 1) if in_ch != out_ch else None
+
+    def forward(self, x, temb):
+        h = self.conv1(self.nonlinearity(self.norm1(x)))
+        t = self.time_emb_proj(self.nonlinearity(temb))[:, :, None, None]
+        h = h + t
+        h = self.conv2(self.dropout(self.nonlinearity(self.norm2(h))))
+        if self.conv_shortcut is not None:
+            x = self.conv_shortcut(x)
+        return x + h
+
+
+class Downsample2D(nn.Module):
+    def __init__(self, ch: int):
+        super().__init__()
+        self.conv = nn.Conv2d(ch, ch, 3, stride=2, padding=1)
+
+    def forward(self, x):
+        return self.conv(x)
+
+
+class Upsample2D(nn.Module):
+    def __init__(self, ch: int):
+        super().__init__()
+        self.conv = nn.Conv2d(ch, ch, 3, padding=1)
+
+    def forward(self, x):
+        x = F.interpolate(x, scale_factor=2.0, mode="nearest")
+        return self.conv(x)
+
+
+class Attention(nn.Module):
+    def __init__(self, query_dim: int, cross_dim: int | None, heads: int, dim_head: int):
+        super().__init__()
+        inner = heads * dim_head
+        self.heads = heads
+        cross_dim = cross_dim if cross_dim is not None else query_dim
+        self.to_q = nn.Linear(query_dim, inner, bias=False)
+        self.to_k = nn.Linear(cross_dim, inner, bias=False)
+        self.to_v = nn.Linear(cross_dim, inner, bias=False)
+        self.to_out = nn.ModuleList([nn.Linear(inner, query_dim), nn.Dropout(0.0)])
+
+    def forward(self, x, context=None):
+        ctx = x if context is None else context
+        B, L, _ = x.shape
+        q, k, v = self.to_q(x), self.to_k(ctx), self.to_v(ctx)
+        q = q.view(B, L, self.heads, -1).transpose(1, 2)
+        k = k.view(B, ctx.shape[1], self.heads, -1).transpose(1, 2)
+        v = v.view(B, ctx.shape[1], self.heads, -1).transpose(1, 2)
+        o = F.scaled_dot_product_attention(q, k, v)
+        o = o.transpose(1, 2).reshape(B, L, -1)
+        return self.to_out[1](self.to_out[0](o))
+
+
+class GEGLU(nn.Module):
+    def __init__(self, dim_in: int, dim_out: int):
+        super().__init__()
+        self.proj = nn.Linear(dim_in, dim_out * 2)
+
+    def forward(self, x):
+        x, gate = self.proj(x).chunk(2, dim=-1)
+        return x * F.gelu(gate)
+
+
+class FeedForward(nn.Module):
+    def __init__(self, dim: int):
+        super().__init__()
+        self.net = nn.ModuleList([GEGLU(dim, dim * 4), nn.Dropout(0.0), nn.Linear(dim * 4, dim)])
+
+    def forward(self, x):
+        for m in self.net:
+            x = m(x)
+        return x
+
+
+class BasicTransformerBlock(nn.Module):
+    def __init__(self, dim: int, heads: int, dim_head: int, cross_dim: int):
+        super().__init__()
+        self.norm1 = nn.LayerNorm(dim)
+        self.attn1 = Attention(dim, None, heads, dim_head)
+        self.norm2 = nn.LayerNorm(dim)
+        self.attn2 = Attention(dim, cross_dim, heads, dim_head)
+        self.norm3 = nn.LayerNorm(dim)
+        self.ff = FeedForward(dim)
+
+    def forward(self, x, context):
+        x = x + self.attn1(self.norm1(x))
+        x = x + self.attn2(self.norm2(x), context)
+        return x + self.ff(self.norm3(x))
+
+
+class Transformer2DModel(nn.Module):
+    def __init__(self, ch: int, heads: int, dim_head: int, depth: int, cross_dim: int, linear_proj: bool, groups: int):
+        super().__init__()
+        self.linear_proj = linear_proj
+        self.norm = nn.GroupNorm(groups, ch, eps=1e-6)
+        self.proj_in = nn.Linear(ch, ch) if linear_proj else nn.Conv2d(ch, ch, 1)
+        self.transformer_blocks = nn.ModuleList(
+            [BasicTransformerBlock(ch, heads, dim_head, cross_dim) for _ in range(depth)])
+        self.proj_out = nn.Linear(ch, ch) if linear_proj else nn.Conv2d(ch, ch, 1)
+
+    def forward(self, x, context):
+        B, C, H, W = x.shape
+        res = x
+        h = self.norm(x)
+        if not self.linear_proj:
+            h = self.proj_in(h)
+        h = h.permute(0, 2, 3, 1).reshape(B, H * W, C)   # a view when h is channels_last
+        if self.linear_proj:
+            h = self.proj_in(h)
+        for blk in self.transformer_blocks:
+            h = blk(h, context)
+        if self.linear_proj:
+            h = self.proj_out(h)
+        h = h.reshape(B, H, W, C).permute(0, 3, 1, 2)
+        if not self.linear_proj:
+            h = self.proj_out(h)
+        return h + res
+
+
+def _heads(cfg: UNetConfig, level: int, ch: int) -> tuple[int, int]:
+    n = cfg.attention_head_dim[level]
+    return n, ch // n
+
+
+class CrossAttnDownBlock2D(nn.Module):
+    has_attn = True
+
+    def __init__(self, cfg, level, in_ch, out_ch, temb_ch, add_down):
+        super().__init__()
+        heads, dh = _heads(cfg, level, out_ch)
+        self.resnets = nn.ModuleList()
+        self.attentions = nn.ModuleList()
+        for i in range(cfg.layers_per_block):
+            self.resnets.append(ResnetBlock2D(in_ch if i == 0 else out_ch, out_ch, temb_ch, cfg.norm_num_groups))
+            if self.has_attn:
+                self.attentions.append(Transformer2DModel(out_ch, heads, dh, cfg.transformer_layers_per_block[level],
+                                                          cfg.cross_attention_dim, cfg.use_linear_projection,
+                                                          cfg.norm_num_groups))
+        self.downsamplers = nn.ModuleList([Downsample2D(out_ch)]) if add_down else None
+
+    def forward(self, x, temb, context):
+        outs = []
+        for i, res in enumerate(self.resnets):
+            x = res(x, temb)
+            if self.has_attn:
+                x = self.attentions[i](x, context)
+            outs.append(x)
+        if self.downsamplers is not None:
+            x = self.downsamplers[0](x)
+            outs.append(x)
+        return x, outs
+
+
+class DownBlock2D(CrossAttnDownBlock2D):
+    has_attn = False
+
+    def __init__(self, cfg, level, in_ch, out_ch, temb_ch, add_down):
+        super().__init__(cfg, level, in_ch, out_ch, temb_ch, add_down)
+        del self.attentions
+
+
+class UNetMidBlock2DCrossAttn(nn.Module):
+    def __init__(self, cfg, ch, temb_ch):
+        super().__init__()
+        level = len(cfg.block_out_channels) - 1
+        heads, dh = _heads(cfg, level, ch)
+        self.attentions = nn.ModuleList([Transformer2DModel(ch, heads, dh, cfg.transformer_layers_per_block[level],
+                                                            cfg.cross_attention_dim, cfg.use_linear_projection,
+                                                            cfg.norm_num_groups)])
+        self.resnets = nn.ModuleList([ResnetBlock2D(ch, ch, temb_ch, cfg.norm_num_groups),
+                                      ResnetBlock2D(ch, ch, temb_ch, cfg.norm_num_groups)])
+
+    def forward(self, x, temb, context):
+        x = self.resnets[0](x, temb)
+        x = self.attentions[0](x, context)
+        return self.resnets[1](x, temb)
+
+
+class CrossAttnUpBlock2D(nn.Module):
+    has_attn = True
+
+    def __init__(self, cfg, level, in_ch, out_ch, prev_ch, temb_ch, add_up):
+        super().__init__()
+        heads, dh = _heads(cfg, level, out_ch)
+        n = cfg.layers_per_block + 1
+        self.resnets = nn.ModuleList()
+        self.attentions = nn.ModuleList()
+        for i in range(n):
+            skip = in_ch if i == n - 1 else out_ch
+            rin = prev_ch if i == 0 else out_ch
+            self.resnets.append(ResnetBlock2D(rin + skip, out_ch, temb_ch, cfg.norm_num_groups))
+            if self.has_attn:
+                self.attentions.append(Transformer2DModel(out_ch, heads, dh, cfg.transformer_layers_per_block[level],
+                                                          cfg.cross_attention_dim, cfg.use_linear_projection,
+                                                          cfg.norm_num_groups))
+        self.upsamplers = nn.ModuleList([Upsample2D(out_ch)]) if add_up else None
+
+    def forward(self, x, skips, temb, context):
+        for i, res in enumerate(self.resnets):
+            x = torch.cat([x, skips.pop()], dim=1)
+            x = res(x, temb)
+            if self.has_attn:
+                x = self.attentions[i](x, context)
+        if self.upsamplers is not None:
+            x = self.upsamplers[0](x)
+        return x
+
+
+class UpBlock2D(CrossAttnUpBlock2D):
+    has_attn = False
+
+    def __init__(self, cfg, level, in_ch, out_ch, prev_ch, temb_ch, add_up):
+        super().__init__(cfg, level, in_ch, out_ch, prev_ch, temb_ch, add_up)
+        del self.attentions
+
+
+class UNet2DConditionModel(nn.Module):
+    """Same constructor-free usage as the diffusers class: `unet(x, t, encoder_hidden_states=...)`."""
+
+    def __init__(self, cfg: UNetConfig | None = None):
+        super().__init__()
+        cfg = cfg or UNetConfig.sd14()
+        self.config = cfg
+        boc = cfg.block_out_channels
+        temb_ch = boc[0] * 4
+        self.conv_in = nn.Conv2d(cfg.in_channels, boc[0], 3, padding=1)
+        self.time_proj = Timesteps(boc[0])
+        self.time_embedding = TimestepEmbedding(boc[0], temb_ch)
+        if cfg.addition_embed:
+            self.add_time_proj = Timesteps(cfg.addition_time_embed_dim)
+            self.add_embedding = TimestepEmbedding(cfg.projection_class_embeddings_input_dim, temb_ch)
+        self.down_blocks = nn.ModuleList()
+        out_ch = boc[0]
+        for i, typ in enumerate(cfg.down_block_types):
+            in_ch, out_ch = out_ch, boc[i]
+            cls = CrossAttnDownBlock2D if typ == "CrossAttnDownBlock2D" else DownBlock2D
+            self.down_blocks.append(cls(cfg, i, in_ch, out_ch, temb_ch, add_down=i < len(boc) - 1))
+        self.mid_block = UNetMidBlock2DCrossAttn(cfg, boc[-1], temb_ch)
+        self.up_blocks = nn.ModuleList()
+        rev = list(reversed(boc))
+        out_ch = rev[0]
+        for i, typ in enumerate(cfg.up_block_types):
+            prev_ch, out_ch = out_ch, rev[i]
+            in_ch = rev[min(i + 1, len(boc) - 1)]
+            level = len(boc) - 1 - i
+            cls = CrossAttnUpBlock2D if typ == "CrossAttnUpBlock2D" else UpBlock2D
+            self.up_blocks.append(cls(cfg, level, in_ch, out_ch, prev_ch, temb_ch, add_up=i < len(boc) - 1))
+        self.conv_norm_out = nn.GroupNorm(cfg.norm_num_groups, boc[0], eps=1e-5)
+        self.conv_act = nn.SiLU()
+        self.conv_out = nn.Conv2d(boc[0], cfg.out_channels, 3, padding=1)
+
+    def enable_xformers_memory_efficient_attention(self):  # API parity (train_lora.py:68); SDPA is used
+        return None
+
+    def forward(self, sample, timestep, encoder_hidden_states=None, added_cond_kwargs=None, return_dict=True):
+        B = sample.shape[0]
+        if not torch.is_tensor(timestep):
+            timestep = torch.tensor([timestep], device=sample.device)
+        t = timestep.to(sample.device).reshape(-1).expand(B)
+        emb = self.time_embedding(self.time_proj(t).to(sample.dtype))
+        if self.config.addition_embed:
+            te = added_cond_kwargs["text_embeds"]
+            ids = added_cond_kwargs["time_ids"]
+            tid = self.add_time_proj(ids.flatten()).reshape(ids.shape[0], -1)
+            emb = emb + self.add_embedding(torch.cat([te, tid.to(te.dtype)], dim=-1).to(sample.dtype))
+        x = self.conv_in(sample.contiguous(memory_format=torch.channels_last))
+        skips = [x]
+        for blk in self.down_blocks:
+            x, outs = blk(x, emb, encoder_hidden_states)
+            skips.extend(outs)
+        x = self.mid_block(x, emb, encoder_hidden_states)
+        for blk in self.up_blocks:
+            x = blk(x, skips, emb, encoder_hidden_states)
+        x = self.conv_out(self.conv_act(self.conv_norm_out(x)))
+        x = x.contiguous()
+        return SimpleNamespace(sample=x) if return_dict else (x,)
