@@ -1,0 +1,208 @@
+"""CPU oracle of the concept-slider hot path — TEST INFRASTRUCTURE ONLY.
+
+A plain-PyTorch (CPU) restatement of the reference's arithmetic, each function citing the reference
+lines it follows.  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+legs may import this module; the product package (sliders_conceptmod_b200/) never does.
+
+Pinning: checked against golden vectors produced by importing the reference's own classes in the
+authoring container (tests/golden/make_golden.py -> tests/golden/*.pt, tests/test_oracle_golden.py).
+The scheduler rules live in diffusers==0.20.2, which is absent from /root/reference: DDIM is pinned by
+the in-repo `prev_step` (trainscripts/imagesliders/train_lora-scale.py:31-39); DDPM / Euler-ancestral
+are restated from the published formulas and are "parity unpinned" (see DESIGN.md).
+"""
+from __future__ import annotations
+
+import math
+from types import SimpleNamespace
+
+import torch
+import torch.nn.functional as F
+
+
+# ----------------------------------------------------------------------------- LoRA layer (a1, a2)
+def lora_forward(org_forward, lora_down, lora_up, multiplier, scale, x):
+    """conceptmod/textsliders/lora.py:134-138 — same op order, so bf16 rounds where the reference rounds."""
+    return org_forward(x) + lora_up(lora_down(x)) * multiplier * scale
+
+
+def attach(network):
+    """Re-point every wrapped layer of a (sliders_conceptmod_b200) LoRANetwork at the oracle arithmetic.
+    Module selection / naming stays the product's host logic (pinned separately by golden key lists)."""
+    for m in network.unet_loras:
+        org = m._org
+        base_forward = type(org).forward.__get__(org)     # the un-patched Linear/Conv2d forward
+
+        def fwd(x, m=m, base_forward=base_forward):
+            return lora_forward(base_forward, m.lora_down, m.lora_up, m.multiplier, m.scale, x)
+
+        org.forward = fwd
+    return network
+
+
+# ----------------------------------------------------------------------------- objective (a5)
+def guidance_loss(target, positive, neutral, q, guidance_scale, action):
+    """trainscripts/imagesliders/prompt_util.py:108-148 (q = unconditional) and
+    conceptmod/textsliders/prompt_util.py:134-174 (q = negative), loss_fn = MSELoss() (train_lora.py:96)."""
+    if action == "erase":
+        tgt = neutral - guidance_scale * (positive - q)
+    elif action == "enhance":
+        tgt = neutral + guidance_scale * (positive - q)
+    else:
+        raise ValueError("action must be erase or enhance")
+    return F.mse_loss(target, tgt)
+
+
+# ----------------------------------------------------------------------------- CFG (a6)
+def cfg_combine(noise_pred, guidance_scale):
+    """conceptmod/textsliders/train_util.py:297-300."""
+    u, c = noise_pred.chunk(2)
+    return u + guidance_scale * (c - u)
+
+
+# ----------------------------------------------------------------------------- schedulers (a7)
+def alphas_cumprod():
+    """model_util.py:397-404 constructor arguments: scaled_linear 0.00085 -> 0.012 over 1000 steps."""
+    betas = torch.linspace(0.00085 ** 0.5, 0.012 ** 0.5, 1000, dtype=torch.float32) ** 2
+    return torch.cumprod(1.0 - betas, dim=0)
+
+
+class OracleScheduler:
+    """Minimal scheduler object with the surface the reference loop uses."""
+
+    def __init__(self, kind="ddim", prediction_type="epsilon"):
+        self.kind, self.prediction_type = kind, prediction_type
+        self.alphas_cumprod = alphas_cumprod()
+        self.final_alpha_cumprod = torch.tensor(1.0)
+        self.config = SimpleNamespace(num_train_timesteps=1000)
+        self.init_noise_sigma = torch.tensor(1.0)
+        self.num_inference_steps = None
+        if kind == "euler_a":
+            self._sig_all = ((1 - self.alphas_cumprod.double()) / self.alphas_cumprod.double()).sqrt().numpy()
+            self.set_timesteps(1000)
+
+    def set_timesteps(self, n, device=None):
+        import numpy as np
+        self.num_inference_steps = n
+        if self.kind == "euler_a":
+            ts = np.linspace(0, 999, n, dtype=float)[::-1].copy()
+            sig = np.interp(ts, np.arange(0, 1000), self._sig_all)
+            self.sigmas = torch.from_numpy(np.concatenate([sig, [0.0]]).astype(np.float32))
+            self.timesteps = torch.from_numpy(ts.astype(np.float32))
+            self.init_noise_sigma = self.sigmas.max()
+        else:
+            ratio = 1000 // n
+            self.timesteps = torch.from_numpy((np.arange(0, n) * ratio).round()[::-1].copy().astype(np.int64))
+
+    def _sigma_index(self, t):
+        return int((self.timesteps - float(t)).abs().argmin())
+
+    def scale_model_input(self, sample, t):
+        if self.kind == "euler_a":
+            s = self.sigmas[self._sigma_index(t)]
+            return sample / ((s ** 2 + 1) ** 0.5)
+        return sample
+
+    def add_noise(self, x0, noise, timesteps):
+        a = self.alphas_cumprod[int(torch.as_tensor(timesteps).reshape(-1)[0])]
+        return a ** 0.5 * x0 + (1 - a) ** 0.5 * noise
+
+    def step(self, model_output, timestep, sample, noise=None):
+        if self.kind == "ddim":
+            prev = ddim_prev_step(model_output, int(timestep), self, sample)
+        elif self.kind == "ddpm":
+            prev = ddpm_step(model_output, int(timestep), self, sample, noise)
+        else:
+            prev = euler_a_step(model_output, timestep, self, sample, noise)
+        return SimpleNamespace(prev_sample=prev)
+
+
+def ddim_prev_step(model_output, timestep, scheduler, sample):
+    """trainscripts/imagesliders/train_lora-scale.py:31-39 (eta = 0 DDIM), statement by statement."""
+    prev_timestep = timestep - scheduler.config.num_train_timesteps // scheduler.num_inference_steps
+    alpha_prod_t = scheduler.alphas_cumprod[timestep]
+    alpha_prod_t_prev = scheduler.alphas_cumprod[prev_timestep] if prev_timestep >= 0 else scheduler.final_alpha_cumprod
+    beta_prod_t = 1 - alpha_prod_t
+    if scheduler.prediction_type == "v_prediction":
+        pred_original_sample = alpha_prod_t ** 0.5 * sample - beta_prod_t ** 0.5 * model_output
+        model_output = alpha_prod_t ** 0.5 * model_output + beta_prod_t ** 0.5 * sample
+    else:
+        pred_original_sample = (sample - beta_prod_t ** 0.5 * model_output) / alpha_prod_t ** 0.5
+    pred_sample_direction = (1 - alpha_prod_t_prev) ** 0.5 * model_output
+    return alpha_prod_t_prev ** 0.5 * pred_original_sample + pred_sample_direction
+
+
+def ddpm_step(model_output, t, scheduler, sample, noise):
+    """DDPM ancestral step, variance 'fixed_small' (diffusers 0.20.2 DDPMScheduler.step)."""
+    prev_t = t - 1000 // scheduler.num_inference_steps
+    a_t = scheduler.alphas_cumprod[t]
+    a_p = scheduler.alphas_cumprod[prev_t] if prev_t >= 0 else torch.tensor(1.0)
+    b_t, b_p = 1 - a_t, 1 - a_p
+    cur_a = a_t / a_p
+    cur_b = 1 - cur_a
+    if scheduler.prediction_type == "v_prediction":
+        x0 = a_t ** 0.5 * sample - b_t ** 0.5 * model_output
+    else:
+        x0 = (sample - b_t ** 0.5 * model_output) / a_t ** 0.5
+    mean = (a_p ** 0.5 * cur_b / b_t) * x0 + (cur_a ** 0.5 * b_p / b_t) * sample
+    if t > 0:
+        var = torch.clamp(b_p / b_t * cur_b, min=1e-20)
+        mean = mean + var ** 0.5 * noise
+    return mean
+
+
+def euler_a_step(model_output, timestep, scheduler, sample, noise):
+    """Euler-ancestral step (diffusers 0.20.2 EulerAncestralDiscreteScheduler.step)."""
+    i = scheduler._sigma_index(timestep)
+    sigma = scheduler.sigmas[i]
+    if scheduler.prediction_type == "v_prediction":
+        x0 = model_output * (-sigma / (sigma ** 2 + 1) ** 0.5) + (sample / (sigma ** 2 + 1))
+    else:
+        x0 = sample - sigma * model_output
+    s_from, s_to = scheduler.sigmas[i], scheduler.sigmas[i + 1]
+    s_up = (s_to ** 2 * (s_from ** 2 - s_to ** 2) / s_from ** 2) ** 0.5
+    s_down = (s_to ** 2 - s_up ** 2) ** 0.5
+    derivative = (sample - x0) / sigma
+    return sample + derivative * (s_down - sigma) + noise * s_up
+
+
+# ----------------------------------------------------------------------------- sampler helpers (a6, a7)
+def predict_noise(unet, scheduler, timestep, latents, text_embeddings, guidance_scale=7.5, **unet_kw):
+    """conceptmod/textsliders/train_util.py:276-302 (and :449-489 with added_cond_kwargs)."""
+    x = torch.cat([latents] * 2)
+    x = scheduler.scale_model_input(x, timestep)
+    noise_pred = unet(x, timestep, encoder_hidden_states=text_embeddings, **unet_kw).sample
+    return cfg_combine(noise_pred, guidance_scale)
+
+
+@torch.no_grad()
+def diffusion(unet, scheduler, latents, text_embeddings, total_timesteps=1000, start_timesteps=0,
+              guidance_scale=7.5, noises=None, **unet_kw):
+    """conceptmod/textsliders/train_util.py:306-327."""
+    for i, timestep in enumerate(scheduler.timesteps[start_timesteps:total_timesteps]):
+        noise_pred = predict_noise(unet, scheduler, timestep, latents, text_embeddings, guidance_scale, **unet_kw)
+        z = None if noises is None else noises[i]
+        latents = scheduler.step(noise_pred, timestep, latents, noise=z).prev_sample
+    return latents
+
+
+def train_iteration(unet, network, scheduler, emb, latents, timesteps_to, guidance_scale, action,
+                    max_denoising_steps=50, denoise_guidance=3.0):
+    """One iteration of conceptmod/textsliders/train_lora.py:155-298 up to loss.backward().
+    emb: dict(target, positive, neutral, unconditional) of [b,77,D].  Returns the loss tensor; LoRA
+    gradients are left in .grad."""
+    cat = lambda u, c: torch.cat([u, c])
+    with torch.no_grad():
+        scheduler.set_timesteps(max_denoising_steps)
+        with network:
+            denoised = diffusion(unet, scheduler, latents, cat(emb["unconditional"], emb["target"]),
+                                 start_timesteps=0, total_timesteps=timesteps_to, guidance_scale=denoise_guidance)
+        scheduler.set_timesteps(1000)
+        t = scheduler.timesteps[int(timesteps_to * 1000 / max_denoising_steps)]
+        pos = predict_noise(unet, scheduler, t, denoised, cat(emb["unconditional"], emb["positive"]), 1)
+        neu = predict_noise(unet, scheduler, t, denoised, cat(emb["unconditional"], emb["neutral"]), 1)
+        unc = predict_noise(unet, scheduler, t, denoised, cat(emb["unconditional"], emb["unconditional"]), 1)
+    with network:
+        tgt = predict_noise(unet, scheduler, t, denoised, cat(emb["unconditional"], emb["target"]), 1)
+    loss = guidance_loss(tgt, pos, neu, unc, guidance_scale, action)
+    loss.backward()
+    return loss, dict(denoised=denoised, positive=pos, neutral=neu, unconditional=unc, target=tgt.detach())

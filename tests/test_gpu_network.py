@@ -1,0 +1,108 @@
+"""GPU parity of the LoRA-wrapped UNet (forward, LoRA gradients) and of one full slider training
+iteration against the CPU oracle (oracle/slider_oracle.py), through the product's host API."""
+import copy
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 5e-3), (torch.bfloat16, 5e-2)])
+def test_unet_forward_and_lora_grads(dtype, tol):
+    from helpers import build_pair, cosine
+    from sliders_conceptmod_b200.unet import UNetConfig
+    cfg = UNetConfig.tiny()
+    unet_c, net_c, unet_g, net_g = build_pair(cfg, "cuda", dtype)
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(2, 4, 16, 16, generator=g)
+    emb = torch.randn(2, 77, cfg.cross_attention_dim, generator=g)
+    t = torch.tensor(481)
+    if dtype != torch.float32:
+        x, emb = x.to(dtype).float(), emb.to(dtype).float()
+    net_c.set_lora_slider(1.5); net_g.set_lora_slider(1.5)
+    with net_c:
+        y_c = unet_c(x, t, encoder_hidden_states=emb).sample
+    with net_g:
+        y_g = unet_g(x.to("cuda", dtype), t.cuda(), encoder_hidden_states=emb.to("cuda", dtype)).sample
+    err = (y_g.float().cpu() - y_c).abs().max().item()
+    assert err <= tol * y_c.abs().max().item(), f"forward max-abs {err}"
+    # adapter off == base model
+    y0_c = unet_c(x, t, encoder_hidden_states=emb).sample
+    y0_g = unet_g(x.to("cuda", dtype), t.cuda(), encoder_hidden_states=emb.to("cuda", dtype)).sample
+    assert (y0_g.float().cpu() - y0_c).abs().max().item() <= tol * y0_c.abs().max().item()
+    # gradients into A/B
+    w = torch.randn(y_c.shape, generator=g)
+    (y_c * w).sum().backward()
+    (y_g.float() * w.cuda()).sum().backward()
+    pc = dict(net_c.named_parameters()); pg = dict(net_g.named_parameters())
+    gc = torch.cat([pc[k].grad.flatten() for k in pc])
+    gg = torch.cat([pg[k].grad.float().flatten().cpu() for k in pc])
+    cos = cosine(gc, gg)
+    maxabs = (gc - gg).abs().max().item()
+    print(f"LoRA grad cosine {cos:.6f} max-abs {maxabs:.3e} (scale {gc.abs().max().item():.3e})")
+    assert cos >= 0.999
+
+
+@pytest.mark.parametrize("dtype,ltol", [(torch.float32, 1e-3), (torch.bfloat16, 1e-2)])
+@pytest.mark.parametrize("graphs", [False, True])
+def test_train_iteration_matches_oracle(dtype, ltol, graphs):
+    from helpers import build_pair, cosine
+    from oracle import slider_oracle
+    from sliders_conceptmod_b200 import model_util
+    from sliders_conceptmod_b200.engine import EngineConfig, SliderEngine
+    from sliders_conceptmod_b200.unet import UNetConfig
+    cfg = UNetConfig.tiny()
+    unet_c, net_c, unet_g, net_g = build_pair(cfg, "cuda", dtype)
+    g = torch.Generator().manual_seed(11)
+    # x4: a random-init UNet barely reacts to N(0,1) text embeddings, which makes the objective a
+    # difference of nearly equal tensors and the bf16 *reference itself* 6 % off its fp32 run
+    # (tools/dev_bf16_noise.py); at x4 the loss is well conditioned and the stated tolerances apply.
+    emb = {k: 4.0 * torch.randn(1, 77, cfg.cross_attention_dim, generator=g) for k in
+           ("target", "positive", "neutral", "unconditional")}
+    lat = torch.randn(1, 4, 16, 16, generator=g)
+    if dtype != torch.float32:
+        emb = {k: v.to(dtype).float() for k, v in emb.items()}
+        lat = lat.to(dtype).float()
+    steps_to = 3
+    osched = slider_oracle.OracleScheduler("ddim")
+    loss_c, inter = slider_oracle.train_iteration(unet_c, net_c, osched, emb, lat, steps_to, 4.0, "enhance",
+                                                  max_denoising_steps=10)
+    eng = SliderEngine(unet_g, net_g, model_util.create_noise_scheduler("ddim"),
+                       EngineConfig(max_denoising_steps=10, use_graphs=graphs, lr=1e-3), 1, 128, 128,
+                       (77, cfg.cross_attention_dim), dtype, "cuda")
+    eng.load_pair(emb["target"], emb["positive"], emb["neutral"], emb["unconditional"], 4.0, "enhance")
+    p_before = net_g.flat_param.float().clone()
+    loss_g = eng.train_step(lat, steps_to)
+    torch.cuda.synchronize()
+    rel = abs(loss_g.item() - loss_c.item()) / abs(loss_c.item())
+    print(f"loss oracle {loss_c.item():.6e} cuda {loss_g.item():.6e} rel {rel:.2e}")
+    assert rel <= ltol
+    # flat gradient buffer vs oracle .grad (conv lora_down is stored tap-major in the flat buffer)
+    gc = []
+    for m in net_c.unet_loras:
+        a = m.lora_down.weight.grad
+        gc.append((a.permute(0, 2, 3, 1) if a.dim() == 4 else a).flatten())
+        gc.append(m.lora_up.weight.grad.flatten())
+    gc = torch.cat(gc)
+    gg = net_g.flat_grad.cpu()
+    cos = cosine(gc, gg)
+    print(f"grad cosine {cos:.6f} max-abs {(gc - gg).abs().max().item():.3e} scale {gc.abs().max().item():.3e}")
+    assert cos >= 0.999
+    # updated weights vs torch AdamW on the oracle side
+    opt = torch.optim.AdamW(net_c.prepare_optimizer_params(), lr=1e-3)
+    opt.step()
+    pc = []
+    for m in net_c.unet_loras:
+        a = m.lora_down.weight.data
+        pc.append((a.permute(0, 2, 3, 1) if a.dim() == 4 else a).flatten())
+        pc.append(m.lora_up.weight.data.flatten())
+    pc = torch.cat(pc)
+    pg = net_g.flat_param.float().cpu()
+    d_c, d_g = pc - p_before.cpu(), pg - p_before.cpu()
+    if dtype == torch.float32:
+        # first Adam step is lr*sign(g): compare only where the gradient is not at rounding-noise level
+        big = gc.abs() > 1e-3 * gc.abs().max()
+        assert cosine(d_c[big], d_g[big]) >= 0.999
+    assert cosine(pc, pg) >= 0.999
+    print(f"updated-weight max-abs {(pc - pg).abs().max().item():.3e}")
