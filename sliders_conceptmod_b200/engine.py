@@ -70,6 +70,8 @@ class SliderEngine:
         self.guidance = 1.0
         self.sign = 1
         self._graphs: dict[str, torch.cuda.CUDAGraph] = {}
+        self._graph_launches: dict[str, int] = {}
+        self.kernel_launches = 0        # libslider_b200 kernels issued (directly or by graph replay)
         self._tables = {}
         self._needs_scale = hasattr(scheduler, "_sigmas")        # Euler-ancestral divides the model input
         self._stochastic = any(self.sched.step_coefficients(t)[2] != 0.0 for t in self._table(cfg.max_denoising_steps)[3][:2])
@@ -129,7 +131,9 @@ class SliderEngine:
 
     def _run(self, name: str, body):
         if not self.cfg.use_graphs:
+            n0 = ops.launch_count()
             body()
+            self.kernel_launches += ops.launch_count() - n0
             return
         g = self._graphs.get(name)
         if g is None:
@@ -141,11 +145,14 @@ class SliderEngine:
             torch.cuda.current_stream().wait_stream(side)
             torch.cuda.synchronize()
             g = torch.cuda.CUDAGraph()
+            n0 = ops.launch_count()
             with torch.cuda.graph(g):
                 body()
+            self._graph_launches[name] = ops.launch_count() - n0
             self._graphs[name] = g
-            return              # capture does not execute; fall through to a replay
+            return              # capture does not execute; the caller replays
         g.replay()
+        self.kernel_launches += self._graph_launches[name]
 
     def _exec(self, name, body, restore=()):
         first = self.cfg.use_graphs and name not in self._graphs
@@ -155,6 +162,7 @@ class SliderEngine:
             for t, s in zip(restore, saved):
                 t.copy_(s)
             self._graphs[name].replay()
+            self.kernel_launches += self._graph_launches[name]
 
     # ---- one reference iteration ---------------------------------------------------------------------
     def load_pair(self, target, positive, neutral, unconditional, guidance_scale: float, action: str, xl=None):
@@ -203,5 +211,6 @@ class SliderEngine:
         elif pre != 1.0:
             scale = torch.full((), pre, device=self.device, dtype=torch.float32)
         self.opt_step += 1
+        self.kernel_launches += 1 + (1 if self.cfg.max_grad_norm is not None else 0)
         ops.adamw_flat(self.network.flat_param, g, self.m, self.v, self.lr, self.cfg.betas[0], self.cfg.betas[1],
                        self.cfg.eps, self.cfg.weight_decay, self.opt_step, scale)

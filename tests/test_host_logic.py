@@ -1,0 +1,200 @@
+"""CPU tests of the host-side mirror of the reference API (no kernels are launched)."""
+import math
+import re
+from pathlib import Path
+
+import pytest
+import torch
+import torch.nn as nn
+
+from helpers import ROOT
+from oracle import slider_oracle as O
+from sliders_conceptmod_b200 import config_util, lora, model_util, prompt_util, schedulers, train_util, workload
+from sliders_conceptmod_b200.unet import UNet2DConditionModel, UNetConfig
+
+GOLD = torch.load(Path(__file__).parent / "golden" / "reference_vectors.pt", weights_only=False)
+ATTN = list(lora.UNET_TARGET_REPLACE_MODULE_TRANSFORMER)
+CONV = list(lora.UNET_TARGET_REPLACE_MODULE_CONV)
+
+
+def _keys(cfg, target, method):
+    with torch.device("meta"):
+        u = UNet2DConditionModel(cfg)
+    net = lora.LoRANetwork(u, rank=4, alpha=1.0, target_replace=target, train_method=method)
+    return {k: list(v.shape) for k, v in net.state_dict().items()}, net
+
+
+@pytest.mark.parametrize("name,cfg,target,method,n_mod", [
+    ("sd14_noxattn_c3lier", UNetConfig.sd14(), ATTN + CONV, "noxattn", 150),
+    ("sd14_noxattn_lierla", UNetConfig.sd14(), ATTN, "noxattn", 64),
+    ("sdxl_noxattn_attn", UNetConfig.sdxl(), ATTN, "noxattn", 280),
+    ("sdxl_noxattn_c3lier", UNetConfig.sdxl(), ATTN + CONV, "noxattn", 346),
+])
+def test_key_layout_matches_reference(name, cfg, target, method, n_mod):
+    keys, net = _keys(cfg, target, method)
+    assert keys == GOLD["keys"][name]          # same names, same shapes, same order as the reference class
+    assert len(net.unet_loras) == n_mod
+
+
+@pytest.mark.parametrize("method", ["noxattn", "innoxattn", "selfattn", "xattn", "full", "xattn-strict",
+                                    "noxattn-hspace", "noxattn-hspace-last"])
+def test_train_method_filters(method):
+    keys, _ = _keys(UNetConfig.tiny(), ATTN + CONV, method)
+    assert keys == GOLD["keys"]["tiny_" + method]
+
+
+def test_unknown_train_method_raises():
+    with pytest.raises(NotImplementedError):
+        _keys(UNetConfig.tiny(), ATTN, "outxattn")
+
+
+def test_param_counts_match_survey():
+    _, net = _keys(UNetConfig.sd14(), ATTN + CONV, "noxattn")
+    assert sum(p.numel() for p in net.parameters()) == 2_906_880
+    _, net = _keys(UNetConfig.sdxl(), ATTN, "noxattn")
+    assert sum(p.numel() for p in net.parameters()) == 2_662_400
+
+
+class Attention(nn.Module):          # the class NAME is what create_modules matches (lora.py:225)
+    def __init__(self, child_name, child):
+        super().__init__()
+        self.add_module(child_name, child)
+
+
+class Root(nn.Module):
+    def __init__(self, holder):
+        super().__init__()
+        self.attn1 = holder
+
+
+def test_multiplier_context_and_scale():
+    lin = nn.Linear(16, 24)
+    root = Root(Attention("to_q", lin))
+    net = lora.LoRANetwork(root, rank=4, multiplier=1.0, alpha=1.0, train_method="full")
+    m = net.unet_loras[0]
+    assert m.lora_name == "lora_unet_attn1_to_q"
+    assert m.multiplier == 1.0                      # before the first `with` (lora.py:126)
+    assert m.scale == 0.25 and float(m.alpha) == 1.0
+    net.set_lora_slider(3)
+    with net:
+        assert m.multiplier == 3.0
+    assert m.multiplier == 0                         # lora.py:299-301
+    assert torch.count_nonzero(m.lora_up.weight) == 0           # zero-init up (lora.py:124)
+    assert lin.forward.__self__ is m                 # forward patched, module identity kept (lora.py:129-132)
+    assert "org_module" not in dict(net.named_modules()) and not any("org" in k for k in net.state_dict())
+    # upstream positional signature (unet, rank, multiplier, alpha, train_method)
+    root2 = Root(Attention("to_k", nn.Linear(8, 8)))
+    net2 = lora.LoRANetwork(root2, 4, 1.0, 2.0, "full")
+    assert net2.alpha == 2.0 and net2.unet_loras[0].scale == 0.5
+    with pytest.raises(RuntimeError):
+        lin(torch.randn(2, 16))                      # no CPU arithmetic path
+
+
+def test_alpha_none_and_conv_rank_clamp():
+    conv = nn.Conv2d(2, 8, 3, padding=1)
+    m = lora.LoRAModule("c", conv, 1.0, 4, None)
+    assert m.lora_dim == 2 and m.lora_down.weight.shape == (2, 2, 3, 3) and m.lora_up.weight.shape == (8, 2, 1, 1)
+    assert m.scale == 4 / 2                          # alpha None -> lora_dim argument (lora.py:118-119)
+    with pytest.raises(NotImplementedError):
+        lora.LoRAModule("c5", nn.Conv2d(8, 8, 5, padding=2), 1.0, 4, 1.0)
+
+
+def test_save_weights_formats(tmp_path):
+    _, net = _keys(UNetConfig.tiny(), ATTN + CONV, "noxattn")
+    net = net.to_empty(device="cpu")
+    for p in net.parameters():
+        nn.init.normal_(p)
+    net.save_weights(str(tmp_path / "a.pt"), dtype=torch.bfloat16)
+    net.save_weights(str(tmp_path / "a.safetensors"), dtype=torch.float32, metadata={"k": "v"})
+    sd = torch.load(tmp_path / "a.pt")
+    from safetensors.torch import load_file
+    sf = load_file(str(tmp_path / "a.safetensors"))
+    assert list(sd) == list(net.state_dict()) and set(sf) == set(sd)
+    assert all(v.dtype == torch.bfloat16 for v in sd.values()) and all(v.dtype == torch.float32 for v in sf.values())
+    k = next(k for k in sd if k.endswith("lora_down.weight"))
+    assert torch.equal(sf[k], net.state_dict()[k].float())
+
+
+def test_prompt_settings_and_yaml(tmp_path):
+    ps = prompt_util.PromptSettings(target="x")
+    assert (ps.positive, ps.unconditional, ps.neutral, ps.action, ps.guidance_scale) == ("x", "", "", "erase", 1.0)
+    with pytest.raises(Exception):
+        prompt_util.PromptSettings(positive="y")
+    f = tmp_path / "p.yaml"
+    f.write_text("- target: 'person'\n  positive: 'old person'\n  unconditional: 'young person'\n  neutral: 'person'\n"
+                 "  action: 'enhance'\n  guidance_scale: 4\n")
+    out = prompt_util.load_prompts_from_yaml(str(f), ["male", "female"])
+    assert [p.target for p in out] == ["male person", "female person"] and out[1].unconditional == "female young person"
+    assert len(prompt_util.load_prompts_from_yaml(str(f))) == 1
+    (tmp_path / "e.yaml").write_text("[]")
+    with pytest.raises(ValueError):
+        prompt_util.load_prompts_from_yaml(str(tmp_path / "e.yaml"))
+    with pytest.raises(NotImplementedError):
+        prompt_util.PromptEmbedsPair(torch.nn.L1Loss(), None, None, None, None, ps)
+    pair = prompt_util.PromptEmbedsPair(torch.nn.MSELoss(), 1, 2, 3, 4, 5, ps)     # fork form (7 args)
+    assert pair.negative == 5 and pair.action == "erase"
+    with pytest.raises(TypeError):
+        pair.loss(target_latents=None, positive_latents=None, neutral_latents=None)
+
+
+def test_config_schema(tmp_path):
+    f = tmp_path / "c.yaml"
+    f.write_text("prompts_file: 'p.yaml'\npretrained_model:\n  name_or_path: 'CompVis/stable-diffusion-v1-4'\n"
+                 "network:\n  type: 'c3lier'\n  rank: 4\n  alpha: 1.0\n  training_method: 'noxattn'\n")
+    c = config_util.load_config_from_yaml(str(f))
+    assert c.train.precision == "bfloat16" and c.train.max_denoising_steps == 50 and c.save.per_steps == 200
+    assert config_util.parse_precision("bf16") == torch.bfloat16
+    with pytest.raises(ValueError):
+        config_util.parse_precision("int8")
+    assert "c3lier" in c.json()
+
+
+@pytest.mark.parametrize("kind", ["ddim", "ddpm", "euler_a"])
+@pytest.mark.parametrize("pred", ["epsilon", "v_prediction"])
+def test_scheduler_coefficients_match_oracle_steps(kind, pred):
+    s = model_util.create_noise_scheduler(kind, pred)
+    o = O.OracleScheduler(kind, pred)
+    n = 12 if kind == "euler_a" else 50
+    s.set_timesteps(n); o.set_timesteps(n)
+    assert torch.equal(s.timesteps.float(), o.timesteps.float())
+    assert abs(float(s.init_noise_sigma) - float(o.init_noise_sigma)) < 1e-6
+    g = torch.Generator().manual_seed(0)
+    x, e, z = (torch.randn(1, 4, 8, 8, generator=g, dtype=torch.float64) for _ in range(3))
+    for t in (s.timesteps[0], s.timesteps[n // 2], s.timesteps[-1]):
+        cx, ce, cn = s.step_coefficients(t)
+        ours = cx * x + ce * e + cn * z
+        ref = o.step(e, t, x, noise=z).prev_sample
+        assert torch.allclose(ours, ref.double(), rtol=1e-5, atol=1e-5), (kind, pred, float(t))
+        xin = o.scale_model_input(x, t)
+        assert torch.allclose(xin, x * s.input_scale(t), rtol=1e-6, atol=1e-6)
+
+
+def test_lms_is_flagged_next_row():
+    with pytest.raises(NotImplementedError):
+        model_util.create_noise_scheduler("lms")
+    with pytest.raises(ValueError):
+        model_util.create_noise_scheduler("nope")
+
+
+def test_train_util_host_helpers():
+    s = model_util.create_noise_scheduler("ddim")
+    lat = train_util.get_initial_latents(s, 2, 512, 256, 1, generator=torch.Generator().manual_seed(3))
+    assert lat.shape == (2, 4, 64, 32)
+    emb = train_util.concat_embeddings(torch.zeros(1, 77, 8), torch.ones(1, 77, 8), 2)
+    assert emb.shape == (4, 77, 8) and emb[:2].sum() == 0 and emb[2:].min() == 1
+    ids = train_util.get_add_time_ids(1024, 1024)
+    assert ids.tolist() == [[1024, 1024, 0, 0, 1024, 1024]]
+    assert train_util.get_optimizer("AdamW") is torch.optim.AdamW
+    with pytest.raises(ValueError):
+        train_util.get_optimizer("sgd")
+    p = nn.Parameter(torch.zeros(1)); opt = torch.optim.AdamW([p], lr=1.0)
+    assert isinstance(train_util.get_lr_scheduler("cosine", opt, 100, 0.01), torch.optim.lr_scheduler.CosineAnnealingLR)
+    with pytest.raises(ValueError):
+        train_util.get_lr_scheduler("bogus", opt, 100, 0.01)
+
+
+def test_workload_definitions():
+    wl = workload.WORKLOADS["sd14_text_slider_rank4_512px"]
+    pairs = workload.prompt_pairs(wl, 768)
+    assert len(pairs) == 4 and pairs[0]["target"].shape == (1, 77, 768)
+    assert torch.equal(pairs[0]["target"], workload.prompt_pairs(wl, 768)[0]["target"])     # deterministic

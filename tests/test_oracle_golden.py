@@ -1,0 +1,77 @@
+"""Pins the CPU oracle (oracle/slider_oracle.py) to vectors produced by the reference's own classes
+(tests/golden/make_golden.py).  CPU only."""
+from pathlib import Path
+
+import pytest
+import torch
+import torch.nn as nn
+
+from helpers import ROOT  # noqa: F401  (path setup)
+from oracle import slider_oracle as O
+
+GOLD = torch.load(Path(__file__).parent / "golden" / "reference_vectors.pt", weights_only=False)
+
+
+def _modules(c):
+    W, A, B = c["W"], c["A"], c["B"]
+    if c["kind"] == "linear":
+        org = nn.Linear(W.shape[1], W.shape[0], bias=c["bias"] is not None)
+        down, up = nn.Linear(A.shape[1], A.shape[0], bias=False), nn.Linear(B.shape[1], B.shape[0], bias=False)
+    else:
+        k = W.shape[-1]
+        stride = 2 if c["kind"] == "conv3s2" else 1
+        org = nn.Conv2d(W.shape[1], W.shape[0], k, stride=stride, padding=(k - 1) // 2, bias=c["bias"] is not None)
+        down = nn.Conv2d(A.shape[1], A.shape[0], k, stride=stride, padding=(k - 1) // 2, bias=False)
+        up = nn.Conv2d(B.shape[1], B.shape[0], 1, bias=False)
+    with torch.no_grad():
+        org.weight.copy_(W); down.weight.copy_(A); up.weight.copy_(B)
+        if c["bias"] is not None:
+            org.bias.copy_(c["bias"])
+    return org, down, up
+
+
+@pytest.mark.parametrize("i", range(len(GOLD["lora_cases"])))
+def test_lora_forward_backward(i):
+    c = GOLD["lora_cases"][i]
+    org, down, up = _modules(c)
+    x = c["x"].clone().requires_grad_(True)
+    y = O.lora_forward(org.forward, down, up, c["mult"], c["scale"], x)
+    assert torch.equal(y, c["y"])
+    (y * c["gy"]).sum().backward()
+    assert torch.allclose(x.grad, c["dx"], rtol=0, atol=0)
+    assert torch.equal(down.weight.grad, c["dA"]) and torch.equal(up.weight.grad, c["dB"])
+
+
+@pytest.mark.parametrize("i", range(len(GOLD["loss_cases"])))
+def test_guidance_loss(i):
+    c = GOLD["loss_cases"][i]
+    t = c["t"].clone().requires_grad_(True)
+    loss = O.guidance_loss(t, c["p"], c["n"], c["q"], c["guidance"], c["action"])
+    loss.backward()
+    assert torch.equal(loss.detach(), c["loss"]) and torch.equal(t.grad, c["grad"])
+
+
+@pytest.mark.parametrize("i", range(len(GOLD["ddim_cases"])))
+def test_ddim_prev_step(i):
+    c = GOLD["ddim_cases"][i]
+    s = O.OracleScheduler("ddim")
+    s.set_timesteps(c["n_inf"])
+    assert torch.equal(s.step(c["eps"], c["t"], c["x"]).prev_sample, c["prev"])
+
+
+@pytest.mark.parametrize("i", range(len(GOLD["cfg_cases"])))
+def test_cfg(i):
+    c = GOLD["cfg_cases"][i]
+    assert torch.equal(O.cfg_combine(c["eps2"], c["guidance"]), c["guided"])
+
+
+def test_scheduler_tables():
+    s = O.OracleScheduler("ddim")
+    s.set_timesteps(50)
+    assert s.timesteps[:3].tolist() == [980, 960, 940] and s.timesteps[-1].item() == 0
+    s.set_timesteps(1000)
+    # train_lora.py:209-213: current_timestep = timesteps[int(timesteps_to*1000/50)] = 999 - 20*timesteps_to
+    for tt in (1, 25, 49):
+        assert s.timesteps[int(tt * 1000 / 50)].item() == 999 - 20 * tt
+    ac = O.alphas_cumprod()
+    assert abs(ac[0].item() - 0.99915) < 1e-5 and abs(ac[-1].item() - 0.0046601) < 1e-5
