@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define SLIDER_ABI_VERSION 1
+#define SLIDER_ABI_VERSION 2
 
 enum slider_dtype { SLIDER_F32 = 0, SLIDER_BF16 = 1 };
 
@@ -73,11 +73,19 @@ typedef struct slider_layer_geom {
  *   h_out [batch*height*width, rank] fp32 or NULL      x (*) A, saved for backward
  *   y     [batch,height,width,cout]
  * s == 0 and h_out == NULL selects the plain-GEMM path (adapter switched off,
- * lora.py:299-301).  One tcgen05/TMA kernel launch.
+ * lora.py:299-301).  One tcgen05/TMA kernel launch; M <= 16 rows of a 1x1 layer
+ * (time_emb_proj) take a weight-streaming SIMT kernel instead.
+ *   ws    optional scratch of slider_gemm_workspace_bytes() bytes (16-byte
+ *         aligned, contents don't-care).  When given, tile-starved shapes
+ *         (few output tiles, deep K) run split-K: partial tiles are parked in
+ *         ws and a second small launch reduces them (deterministic order).
+ *         NULL => never split.  ws may be shared by all calls on one stream.
  */
+size_t slider_gemm_workspace_bytes(void);
 int slider_lora_forward(const slider_layer_geom* g, void* y, const void* x,
                         const void* W, const void* bias, const void* A,
-                        const void* B, float* h_out, float s, void* stream);
+                        const void* B, float* h_out, float s, void* ws,
+                        size_t ws_bytes, void* stream);
 
 /*
  * Low-rank part of the backward of the layer above (autograd of lora.py:134-138,
@@ -105,12 +113,13 @@ int slider_lora_grad(const slider_layer_geom* g, float* dA, float* dB,
  *   At  [cin, kh*kw, 16]    At[c][t][j] = A[j][T-1-t][c], j >= rank zero;
  *                           produced by slider_lora_pack_at
  *   dh  [M, 16]             from slider_lora_grad (NULL => base term only)
+ *   ws  as in slider_lora_forward
  */
 int slider_lora_pack_at(const slider_layer_geom* g, void* At, const void* A,
                         void* stream);
 int slider_lora_input_grad(const slider_layer_geom* g, void* dx, const void* gy,
                            const void* Wt, const void* dh, const void* At,
-                           void* stream);
+                           void* ws, size_t ws_bytes, void* stream);
 
 /* One-time repack of a frozen base weight [cout, kh*kw, cin] into the Wt layout. */
 int slider_pack_wt(const slider_layer_geom* g, void* Wt, const void* W,

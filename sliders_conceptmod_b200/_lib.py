@@ -30,11 +30,12 @@ _SIGNATURES = {
     "slider_version": (C.c_int, []),
     "slider_last_error": (C.c_char_p, []),
     "slider_launch_count": (C.c_int64, []),
-    "slider_lora_forward": (C.c_int, [_G, _vp, _vp, _vp, _vp, _vp, _vp, _fp, _f, _vp]),
+    "slider_gemm_workspace_bytes": (_sz, []),
+    "slider_lora_forward": (C.c_int, [_G, _vp, _vp, _vp, _vp, _vp, _vp, _fp, _f, _vp, _sz, _vp]),
     "slider_lora_grad_workspace_bytes": (_sz, [_G]),
     "slider_lora_grad": (C.c_int, [_G, _fp, _fp, _vp, _vp, _vp, _fp, _vp, _f, _i, _vp, _sz, _vp]),
     "slider_lora_pack_at": (C.c_int, [_G, _vp, _vp, _vp]),
-    "slider_lora_input_grad": (C.c_int, [_G, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "slider_lora_input_grad": (C.c_int, [_G, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "slider_pack_wt": (C.c_int, [_G, _vp, _vp, _vp]),
     "slider_loss_workspace_bytes": (_sz, []),
     "slider_guidance_loss": (C.c_int, [_fp, _vp, _vp, _vp, _vp, _vp, _i64, _f, _i, _i, _vp, _sz, _vp]),

@@ -36,6 +36,9 @@ constexpr int EXT_ELEMS = 16;    // width of the extended-K operand (dh / At), i
 constexpr int TMEM_COLS = 512;
 constexpr int kGemmThreads = 192;
 constexpr int EPI_FLOATS = BN * 16 + BN;     // s*Bup (rank padded to <=16) + bias
+constexpr int NCHUNK = BN / 32 + 1;          // 32-column chunks of a split-K partial tile (+1 for h)
+constexpr size_t UNIT_FLOATS = (size_t)NCHUNK * BM * 32;
+constexpr int MAX_UNITS = 160;               // split-K work units the caller workspace must hold
 constexpr size_t SMEM_BYTES = 1024 /*align slack*/ + (size_t)NSTAGES * STAGE_BYTES + EPI_FLOATS * 4 + 256;
 
 template <typename T> struct GemmTraits;
@@ -67,6 +70,11 @@ struct GemmParams {
   int lora;               // accumulate h and apply it in the epilogue
   int ext;                // extended-K operand pair present (input-gradient mode)
   int total_tiles;
+  int per_tap;            // K iterations per tap = cblocks + ext
+  int kiters;             // taps * per_tap
+  int ksplit;             // K partitions per tile (1 = no split)
+  int total_units;        // total_tiles * ksplit
+  float* partial;         // split-K partial tiles, [unit][NCHUNK][128][32] fp32
   void* y;
   const void* bias;
   const void* Bup;
@@ -140,70 +148,67 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (warp == 0 && lane == 0) {
     // ===================== TMA producer =====================
     uint32_t stage = 0, phase = 0;
-    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+    for (int unit = blockIdx.x; unit < p.total_units; unit += gridDim.x) {
+      const int tile = unit / p.ksplit, split = unit - tile * p.ksplit;
       const TileCoord tc = tile_coord(p, tile);
-      for (int tap = 0; tap < p.taps; ++tap) {
+      const int it0 = (int)((long long)split * p.kiters / p.ksplit);
+      const int it1 = (int)((long long)(split + 1) * p.kiters / p.ksplit);
+      int tap = it0 / p.per_tap, j = it0 - tap * p.per_tap;
+      for (int it = it0; it < it1; ++it) {
         const int dy = tap / p.kw - p.pad, dx = tap % p.kw - p.pad;
-        for (int cb = 0; cb < p.cblocks; ++cb) {
-          ptx::mbar_wait(ptx::smem_u32(empty_bar + stage), phase ^ 1);
-          const uint32_t sa = smem_base + stage * STAGE_BYTES;
-          const uint32_t fb = ptx::smem_u32(full_bar + stage);
+        ptx::mbar_wait(ptx::smem_u32(empty_bar + stage), phase ^ 1);
+        const uint32_t sa = smem_base + stage * STAGE_BYTES;
+        const uint32_t fb = ptx::smem_u32(full_bar + stage);
+        if (j < p.cblocks) {
           ptx::mbar_arrive_expect_tx(fb, main_tx);
-          ptx::tma_load_4d(sa, &tmA, fb, cb * BK, tc.w0 + dx, tc.h0 + dy, tc.b0);
-          ptx::tma_load_3d(sa + A_BYTES, &tmW, fb, cb * BK, tap, tc.n0);
-          if (p.lora) ptx::tma_load_3d(sa + A_BYTES + B_BYTES, &tmL, fb, cb * BK, tap, 0);
-          if (++stage == NSTAGES) { stage = 0; phase ^= 1; }
-        }
-        if (p.ext) {
-          ptx::mbar_wait(ptx::smem_u32(empty_bar + stage), phase ^ 1);
-          const uint32_t sa = smem_base + stage * STAGE_BYTES;
-          const uint32_t fb = ptx::smem_u32(full_bar + stage);
+          ptx::tma_load_4d(sa, &tmA, fb, j * BK, tc.w0 + dx, tc.h0 + dy, tc.b0);
+          ptx::tma_load_3d(sa + A_BYTES, &tmW, fb, j * BK, tap, tc.n0);
+          if (p.lora) ptx::tma_load_3d(sa + A_BYTES + B_BYTES, &tmL, fb, j * BK, tap, 0);
+        } else {
           ptx::mbar_arrive_expect_tx(fb, ext_tx);
           ptx::tma_load_4d(sa, &tmXe, fb, 0, tc.w0 + dx, tc.h0 + dy, tc.b0);
           ptx::tma_load_3d(sa + A_BYTES, &tmWe, fb, 0, tap, tc.n0);
-          if (++stage == NSTAGES) { stage = 0; phase ^= 1; }
         }
+        if (++stage == NSTAGES) { stage = 0; phase ^= 1; }
+        if (++j == p.per_tap) { j = 0; ++tap; }
       }
     }
   } else if (warp == 1 && lane == 0) {
     // ===================== MMA issuer =====================
+    // With the adapter on, W tile (BN rows) and lora_down tile (HCOLS rows) are adjacent in shared
+    // memory and their accumulators adjacent in TMEM: ONE tcgen05.mma of N = BN + HCOLS covers both.
     constexpr uint32_t idesc_main = ptx::make_idesc(Tr::kFmt, BM, BN);
-    constexpr uint32_t idesc_h = ptx::make_idesc(Tr::kFmt, BM, HCOLS);
+    constexpr uint32_t idesc_lora = ptx::make_idesc(Tr::kFmt, BM, BN + HCOLS);
+    const uint32_t idesc = p.lora ? idesc_lora : idesc_main;
     uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
-    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+    for (int unit = blockIdx.x; unit < p.total_units; unit += gridDim.x) {
+      const int split = unit % p.ksplit;
+      const int it0 = (int)((long long)split * p.kiters / p.ksplit);
+      const int it1 = (int)((long long)(split + 1) * p.kiters / p.ksplit);
+      int j = it0 % p.per_tap;
       ptx::mbar_wait(ptx::smem_u32(tempty_bar + as), aphase ^ 1);
       ptx::tc_fence_after();
       const uint32_t d_main = tmem_base + as * (BN + HCOLS);
-      const uint32_t d_h = d_main + BN;
       uint32_t acc = 0;
-      for (int tap = 0; tap < p.taps; ++tap) {
-        for (int cb = 0; cb < p.cblocks; ++cb) {
-          ptx::mbar_wait(ptx::smem_u32(full_bar + stage), phase);
-          ptx::tc_fence_after();
-          const uint32_t sa = smem_base + stage * STAGE_BYTES;
+      for (int it = it0; it < it1; ++it) {
+        ptx::mbar_wait(ptx::smem_u32(full_bar + stage), phase);
+        ptx::tc_fence_after();
+        const uint32_t sa = smem_base + stage * STAGE_BYTES;
+        if (j < p.cblocks) {
           const uint64_t da = ptx::smem_desc_kmajor(sa, ROW_BYTES);
           const uint64_t db = ptx::smem_desc_kmajor(sa + A_BYTES, ROW_BYTES);
-          const uint64_t dl = ptx::smem_desc_kmajor(sa + A_BYTES + B_BYTES, ROW_BYTES);
 #pragma unroll
-          for (int k = 0; k < KSTEPS; ++k) {
-            Tr::mma(d_main, da + 2 * k, db + 2 * k, idesc_main, acc | (uint32_t)k);
-            if (p.lora) Tr::mma(d_h, da + 2 * k, dl + 2 * k, idesc_h, acc | (uint32_t)k);
-          }
-          acc = 1;
-          ptx::mma_commit(ptx::smem_u32(empty_bar + stage));
-          if (++stage == NSTAGES) { stage = 0; phase ^= 1; }
-        }
-        if (p.ext) {
-          ptx::mbar_wait(ptx::smem_u32(full_bar + stage), phase);
-          ptx::tc_fence_after();
-          const uint32_t sa = smem_base + stage * STAGE_BYTES;
+          for (int k = 0; k < KSTEPS; ++k) Tr::mma(d_main, da + 2 * k, db + 2 * k, idesc, acc | (uint32_t)k);
+        } else {
           const uint64_t da = ptx::smem_desc_kmajor(sa, Tr::kExtRowBytes);
           const uint64_t db = ptx::smem_desc_kmajor(sa + A_BYTES, Tr::kExtRowBytes);
 #pragma unroll
-          for (int k = 0; k < EXT_KSTEPS; ++k) Tr::mma(d_main, da + 2 * k, db + 2 * k, idesc_main, 1u);
-          ptx::mma_commit(ptx::smem_u32(empty_bar + stage));
-          if (++stage == NSTAGES) { stage = 0; phase ^= 1; }
+          for (int k = 0; k < EXT_KSTEPS; ++k) Tr::mma(d_main, da + 2 * k, db + 2 * k, idesc_main, acc | (uint32_t)k);
         }
+        acc = 1;
+        ptx::mma_commit(ptx::smem_u32(empty_bar + stage));
+        if (++stage == NSTAGES) { stage = 0; phase ^= 1; }
+        if (++j == p.per_tap) j = 0;
       }
       ptx::mma_commit(ptx::smem_u32(tfull_bar + as));
       if (++as == ACC_STAGES) { as = 0; aphase ^= 1; }
@@ -218,8 +223,42 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     T* __restrict__ y = reinterpret_cast<T*>(p.y);
     const T* __restrict__ bias = reinterpret_cast<const T*>(p.bias);
     const T* __restrict__ Bup = reinterpret_cast<const T*>(p.Bup);
-    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
-      const TileCoord tc = tile_coord(p, tile);
+    for (int unit = blockIdx.x; unit < p.total_units; unit += gridDim.x) {
+      if (p.ksplit > 1) {
+        // split-K: park the fp32 partial tile (main + h columns) in the L2-resident workspace,
+        // [unit][chunk][row][32] so that a warp writes 4 KB contiguous; splitk_finalize_kernel reduces.
+        ptx::mbar_wait(ptx::smem_u32(tfull_bar + as), aphase);
+        ptx::tc_fence_after();
+        const uint32_t t_acc = tmem_base + ((uint32_t)(q * 32) << 16) + as * (BN + HCOLS);
+        float* dst = p.partial + (size_t)unit * UNIT_FLOATS + (size_t)row * 32;
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+          uint32_t v[32];
+          ptx::tmem_ld_32x32(t_acc + c * 32, v);
+          ptx::tmem_ld_wait();
+          float4* d4 = reinterpret_cast<float4*>(dst + (size_t)c * BM * 32);
+#pragma unroll
+          for (int k = 0; k < 8; ++k)
+            d4[k] = make_float4(__uint_as_float(v[4 * k]), __uint_as_float(v[4 * k + 1]),
+                                __uint_as_float(v[4 * k + 2]), __uint_as_float(v[4 * k + 3]));
+        }
+        if (R4 > 0) {
+          uint32_t hr[16];
+          ptx::tmem_ld_32x16(t_acc + BN, hr);
+          ptx::tmem_ld_wait();
+          float4* d4 = reinterpret_cast<float4*>(dst + (size_t)(BN / 32) * BM * 32);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            d4[k] = make_float4(__uint_as_float(hr[4 * k]), __uint_as_float(hr[4 * k + 1]),
+                                __uint_as_float(hr[4 * k + 2]), __uint_as_float(hr[4 * k + 3]));
+        }
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(tempty_bar + as));
+        if (++as == ACC_STAGES) { as = 0; aphase ^= 1; }
+        continue;
+      }
+      const TileCoord tc = tile_coord(p, unit);
       // stage s*Bup[n0.., :] and bias[n0..] for this tile (fp32) while the MMAs run
       asm volatile("bar.sync 1, 128;" ::: "memory");
       for (int i = et; i < BN; i += 128) {
@@ -306,6 +345,149 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Split-K finalize: y = sum_splits(partial) + bias + s * h . Bup^T, one thread per (row, 8 columns).
+// Thread order (8-col group, row, chunk) follows the partial layout, so reads are fully coalesced.
+template <typename T, int R4>
+__global__ void __launch_bounds__(256)
+splitk_finalize_kernel(const GemmParams p) {
+  constexpr int PER_TILE = BM * (BN / 8);
+  const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (idx >= (long long)p.total_tiles * PER_TILE) return;
+  const int tile = (int)(idx / PER_TILE);
+  const int rem = (int)(idx - (long long)tile * PER_TILE);
+  const int g = rem & 3, row = (rem >> 2) & (BM - 1), c = rem >> 9;
+  const TileCoord tc = tile_coord(p, tile);
+  const int lw = row % p.TW, lh = (row / p.TW) % p.TH, lb = row / (p.TW * p.TH);
+  const bool row_ok = row < p.rows && tc.w0 + lw < p.W && tc.h0 + lh < p.H && tc.b0 + lb < p.B;
+  const int n = tc.n0 + c * 32 + g * 8;
+  if (!row_ok || n >= p.N) return;
+  const size_t pix = ((size_t)(tc.b0 + lb) * p.H + (tc.h0 + lh)) * p.W + (tc.w0 + lw);
+  const float* src = p.partial + (size_t)tile * p.ksplit * UNIT_FLOATS + ((size_t)c * BM + row) * 32 + g * 8;
+  const float* hsrc = p.partial + (size_t)tile * p.ksplit * UNIT_FLOATS + ((size_t)(BN / 32) * BM + row) * 32;
+  float o[8];
+  float hv[R4 > 0 ? 4 * R4 : 1];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) o[k] = 0.f;
+#pragma unroll
+  for (int j = 0; j < (R4 > 0 ? 4 * R4 : 1); ++j) hv[j] = 0.f;
+#pragma unroll 4
+  for (int s = 0; s < p.ksplit; ++s) {
+    const float4 a = __ldcg(reinterpret_cast<const float4*>(src + (size_t)s * UNIT_FLOATS));
+    const float4 b = __ldcg(reinterpret_cast<const float4*>(src + (size_t)s * UNIT_FLOATS) + 1);
+    o[0] += a.x; o[1] += a.y; o[2] += a.z; o[3] += a.w;
+    o[4] += b.x; o[5] += b.y; o[6] += b.z; o[7] += b.w;
+    if (R4 > 0) {
+#pragma unroll
+      for (int j4 = 0; j4 < R4; ++j4) {
+        const float4 h4 = __ldcg(reinterpret_cast<const float4*>(hsrc + (size_t)s * UNIT_FLOATS) + j4);
+        hv[4 * j4] += h4.x; hv[4 * j4 + 1] += h4.y; hv[4 * j4 + 2] += h4.z; hv[4 * j4 + 3] += h4.w;
+      }
+    }
+  }
+  const T* __restrict__ bias = reinterpret_cast<const T*>(p.bias);
+  const T* __restrict__ Bup = reinterpret_cast<const T*>(p.Bup);
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    float a = o[k] + (bias != nullptr ? Elem<T>::to_f(bias[n + k]) : 0.f);
+    if (R4 > 0) {
+      float l = 0.f;
+#pragma unroll
+      for (int j = 0; j < 4 * R4; ++j)
+        if (j < p.rank) l = fmaf(hv[j], Elem<T>::to_f(Bup[(size_t)(n + k) * p.rank + j]), l);
+      a = fmaf(p.s, l, a);
+    }
+    o[k] = a;
+  }
+  T* dst = reinterpret_cast<T*>(p.y) + pix * (size_t)p.N + n;
+  if (sizeof(T) == 2) {
+    Elem<__nv_bfloat16>::store(reinterpret_cast<__nv_bfloat16*>(dst), o);
+  } else {
+    float* d = reinterpret_cast<float*>(dst);
+    *reinterpret_cast<float4*>(d) = make_float4(o[0], o[1], o[2], o[3]);
+    *reinterpret_cast<float4*>(d + 4) = make_float4(o[4], o[5], o[6], o[7]);
+  }
+  if (R4 > 0 && p.h_out != nullptr && tc.n_blk == 0 && c == 0 && g == 0) {
+#pragma unroll
+    for (int j = 0; j < 4 * R4; ++j)
+      if (j < p.rank) p.h_out[pix * p.rank + j] = hv[j];
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Small-M path (M <= 16 rows, 1x1): time_emb_proj (M = 2).  HBM-bound on the weight matrix:
+// one warp per output channel streams W[n,:] with 16-byte loads; the activation rows live in
+// shared memory (fp32); h = x.A^T is recomputed per CTA (M*r dot products of length K).
+constexpr int GEMV_WARPS = 8;
+template <typename T, int MT>
+__global__ void __launch_bounds__(GEMV_WARPS * 32)
+lora_gemv_kernel(T* __restrict__ y, const T* __restrict__ x, const T* __restrict__ W, const T* __restrict__ bias,
+                 const T* __restrict__ A, const T* __restrict__ Bup, float* __restrict__ h_out, int M, int K, int N,
+                 int rank, float s, int lora) {
+  constexpr int V = Elem<T>::kVec;
+  extern __shared__ float gemv_smem[];
+  float* xs = gemv_smem;                  // [MT][K]
+  float* hs = gemv_smem + (size_t)MT * K; // [MT][16]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int i = threadIdx.x * V; i < MT * K; i += blockDim.x * V) {
+    const int m = i / K;
+    float v[V];
+    if (m < M) Elem<T>::load(x + i, v);
+#pragma unroll
+    for (int k = 0; k < V; ++k) xs[i + k] = m < M ? v[k] : 0.f;
+  }
+  __syncthreads();
+  if (lora) {
+    for (int pr = warp; pr < MT * rank; pr += GEMV_WARPS) {
+      const int m = pr / rank, j = pr - m * rank;
+      float acc = 0.f;
+      for (int k = lane * V; k < K; k += 32 * V) {
+        float av[V];
+        Elem<T>::load(A + (size_t)j * K + k, av);
+#pragma unroll
+        for (int e = 0; e < V; ++e) acc = fmaf(av[e], xs[m * K + k + e], acc);
+      }
+      acc = warp_sum(acc);
+      if (lane == 0) {
+        hs[m * 16 + j] = acc;
+        if (h_out != nullptr && blockIdx.x == 0 && m < M) h_out[m * rank + j] = acc;
+      }
+    }
+    __syncthreads();
+  }
+  const int n = blockIdx.x * GEMV_WARPS + warp;
+  if (n >= N) return;
+  float acc[MT];
+#pragma unroll
+  for (int m = 0; m < MT; ++m) acc[m] = 0.f;
+  const T* wrow = W + (size_t)n * K;
+  for (int k = lane * V; k < K; k += 32 * V) {
+    float wv[V];
+    Elem<T>::load(wrow + k, wv);
+#pragma unroll
+    for (int m = 0; m < MT; ++m) {
+      const float* xr = xs + m * K + k;
+#pragma unroll
+      for (int e = 0; e < V; ++e) acc[m] = fmaf(wv[e], xr[e], acc[m]);
+    }
+  }
+#pragma unroll
+  for (int m = 0; m < MT; ++m) acc[m] = warp_sum(acc[m]);
+  if (lane < MT && lane < M) {
+    float a = 0.f;
+#pragma unroll
+    for (int m = 0; m < MT; ++m) a = (lane == m) ? acc[m] : a;
+    if (bias != nullptr) a += Elem<T>::to_f(bias[n]);
+    if (lora) {
+      float l = 0.f;
+      for (int j = 0; j < rank; ++j) l = fmaf(hs[lane * 16 + j], Elem<T>::to_f(Bup[(size_t)n * rank + j]), l);
+      a = fmaf(s, l, a);
+    }
+    y[(size_t)lane * N + n] = Elem<T>::from_f(a);
+  }
+}
+
 }  // namespace slider
 
 // =================================== host side ===================================
@@ -331,11 +513,12 @@ template <typename T>
 static int launch_gemm(int r4, const CUtensorMap& a, const CUtensorMap& w, const CUtensorMap& l,
                        const CUtensorMap& xe, const CUtensorMap& we, const GemmParams& p, cudaStream_t st) {
   void (*kern)(CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, GemmParams) = nullptr;
+  void (*fin)(GemmParams) = nullptr;
   switch (r4) {
-    case 0: kern = lora_gemm_kernel<T, 0>; break;
-    case 1: kern = lora_gemm_kernel<T, 1>; break;
-    case 2: kern = lora_gemm_kernel<T, 2>; break;
-    default: kern = lora_gemm_kernel<T, 4>; break;
+    case 0: kern = lora_gemm_kernel<T, 0>; fin = splitk_finalize_kernel<T, 0>; break;
+    case 1: kern = lora_gemm_kernel<T, 1>; fin = splitk_finalize_kernel<T, 1>; break;
+    case 2: kern = lora_gemm_kernel<T, 2>; fin = splitk_finalize_kernel<T, 2>; break;
+    default: kern = lora_gemm_kernel<T, 4>; fin = splitk_finalize_kernel<T, 4>; break;
   }
   static thread_local const void* configured[8] = {nullptr};
   bool done = false;
@@ -344,9 +527,29 @@ static int launch_gemm(int r4, const CUtensorMap& a, const CUtensorMap& w, const
     SLIDER_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
     for (auto& c : configured) if (c == nullptr) { c = (const void*)kern; break; }
   }
-  int grid = p.total_tiles < sm_count() ? p.total_tiles : sm_count();
+  int grid = p.total_units < sm_count() ? p.total_units : sm_count();
   kern<<<grid, kGemmThreads, SMEM_BYTES, st>>>(a, w, l, xe, we, p);
-  return post_launch("lora_gemm_kernel");
+  int rc = post_launch("lora_gemm_kernel");
+  if (rc || p.ksplit == 1) return rc;
+  const long long threads = (long long)p.total_tiles * BM * (BN / 8);
+  fin<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(p);
+  return post_launch("splitk_finalize_kernel");
+}
+
+template <typename T>
+static int launch_gemv(const slider_layer_geom* g, int M, void* y, const void* x, const void* W, const void* bias,
+                       const void* A, const void* Bup, float* h_out, float s, bool lora, cudaStream_t st) {
+  const int K = g->cin, N = g->cout;
+  const int mt = M <= 2 ? 2 : (M <= 4 ? 4 : (M <= 8 ? 8 : 16));
+  const size_t smem = ((size_t)mt * K + (size_t)mt * 16) * sizeof(float);
+  const int grid = (N + GEMV_WARPS - 1) / GEMV_WARPS;
+#define GEMV(MT)                                                                                           \
+  lora_gemv_kernel<T, MT><<<grid, GEMV_WARPS * 32, smem, st>>>((T*)y, (const T*)x, (const T*)W, (const T*)bias, \
+                                                               (const T*)A, (const T*)Bup, h_out, M, K, N,  \
+                                                               g->rank, s, lora ? 1 : 0)
+  if (mt == 2) GEMV(2); else if (mt == 4) GEMV(4); else if (mt == 8) GEMV(8); else GEMV(16);
+#undef GEMV
+  return post_launch("lora_gemv_kernel");
 }
 
 // Shared driver for forward (lora epilogue) and input-gradient (extended-K) modes.
@@ -356,7 +559,7 @@ static int launch_gemm(int r4, const CUtensorMap& a, const CUtensorMap& w, const
 //   xe / we  [B,H,W,16] / [nn, taps, 16]  extended-K pair (input gradient only)
 static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const void* act, const void* wgt,
                     const void* bias, const void* lo, const void* Bup, float* h_out, float s, const void* xe,
-                    const void* we, cudaStream_t st) {
+                    const void* we, void* ws, size_t ws_bytes, cudaStream_t st) {
   const int es = esize(g->dtype);
   const int taps = g->kh * g->kw;
   const int bk = ROW_BYTES / es;
@@ -364,14 +567,25 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
   SLIDER_CHECK_ARG(g->kh == g->kw && (g->kh == 1 || g->kh == 3) && g->pad == (g->kh - 1) / 2,
                    "lora gemm: only 1x1/pad0 and 3x3/pad1 stride-1 kernels (got %dx%d pad %d)", g->kh, g->kw, g->pad);
   SLIDER_CHECK_ARG(g->batch > 0 && g->height > 0 && g->width > 0 && kc > 0 && nn > 0, "lora gemm: empty shape");
-  SLIDER_CHECK_ARG((kc * es) % 16 == 0 && (nn * es) % 16 == 0,
-                   "lora gemm: channel counts must be multiples of %d (cin %d, cout %d)", 16 / es, g->cin, g->cout);
+  SLIDER_CHECK_ARG(kc % 8 == 0 && nn % 8 == 0,
+                   "lora gemm: channel counts must be multiples of 8 (cin %d, cout %d)", g->cin, g->cout);
   SLIDER_CHECK_ARG(g->rank >= 0 && g->rank <= 16, "lora gemm: rank %d not in 0..16", g->rank);
   SLIDER_CHECK_ARG(((uintptr_t)act & 15) == 0 && ((uintptr_t)wgt & 15) == 0 && ((uintptr_t)y & 15) == 0,
                    "lora gemm: pointers must be 16-byte aligned");
 
   const bool lora = lo != nullptr && g->rank > 0 && (s != 0.f || h_out != nullptr);
   const bool ext = xe != nullptr;
+  if (lora) SLIDER_CHECK_ARG(Bup != nullptr, "lora gemm: lora_up weight is NULL");
+  {
+    // small-M path: a 128-row tensor-core tile would be > 87 % padding and the op is weight-bandwidth bound
+    const long long M = (long long)g->batch * g->height * g->width;
+    const size_t mt = M <= 2 ? 2 : (M <= 4 ? 4 : (M <= 8 ? 8 : 16));
+    if (!ext && taps == 1 && M <= 16 && mt * kc * sizeof(float) <= 40 * 1024) {
+      if (g->dtype == SLIDER_BF16)
+        return launch_gemv<__nv_bfloat16>(g, (int)M, y, act, wgt, bias, lo, Bup, lora ? h_out : nullptr, s, lora, st);
+      return launch_gemv<float>(g, (int)M, y, act, wgt, bias, lo, Bup, lora ? h_out : nullptr, s, lora, st);
+    }
+  }
   const TileGeom tg = choose_tile(g->width, g->height, g->batch);
 
   GemmParams p;
@@ -384,9 +598,22 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
   p.taps = taps; p.kw = g->kw; p.pad = g->pad; p.cblocks = (kc + bk - 1) / bk;
   p.rank = g->rank; p.s = s; p.lora = lora ? 1 : 0; p.ext = ext ? 1 : 0;
   p.total_tiles = p.mt_w * p.mt_h * p.mt_b * p.n_tiles;
+  p.per_tap = p.cblocks + (ext ? 1 : 0);
+  p.kiters = taps * p.per_tap;
+  // split-K when the tile count leaves more than half of the SMs idle and K is deep enough
+  p.ksplit = 1;
+  p.partial = reinterpret_cast<float*>(ws);
+  if (ws != nullptr && ((uintptr_t)ws & 15) == 0 && p.total_tiles * 2 <= sm_count()) {
+    int ks = sm_count() / p.total_tiles;
+    const int by_depth = p.kiters / 6;
+    if (ks > by_depth) ks = by_depth;
+    const long long cap = (long long)(ws_bytes / (UNIT_FLOATS * sizeof(float)));
+    if ((long long)ks * p.total_tiles > cap) ks = (int)(cap / p.total_tiles);
+    if (ks >= 2) p.ksplit = ks;
+  }
+  p.total_units = p.total_tiles * p.ksplit;
   p.y = y; p.bias = bias; p.Bup = Bup; p.h_out = lora ? h_out : nullptr;
   if (lora) {
-    SLIDER_CHECK_ARG(Bup != nullptr, "lora gemm: lora_up weight is NULL");
     SLIDER_CHECK_ARG((g->rank * taps * kc * es) % 16 == 0 && ((uintptr_t)lo & 15) == 0, "lora gemm: lora_down misaligned");
   }
 
@@ -434,17 +661,21 @@ using namespace slider;
 
 extern "C" {
 
+size_t slider_gemm_workspace_bytes(void) { return (size_t)MAX_UNITS * UNIT_FLOATS * sizeof(float); }
+
 int slider_lora_forward(const slider_layer_geom* g, void* y, const void* x, const void* W, const void* bias,
-                        const void* A, const void* B, float* h_out, float s, void* stream) {
+                        const void* A, const void* B, float* h_out, float s, void* ws, size_t ws_bytes,
+                        void* stream) {
   SLIDER_CHECK_ARG(g && y && x && W, "lora_forward: null pointer");
-  return run_gemm(g, g->cin, g->cout, y, x, W, bias, A, B, h_out, s, nullptr, nullptr, (cudaStream_t)stream);
+  return run_gemm(g, g->cin, g->cout, y, x, W, bias, A, B, h_out, s, nullptr, nullptr, ws, ws_bytes,
+                  (cudaStream_t)stream);
 }
 
 int slider_lora_input_grad(const slider_layer_geom* g, void* dx, const void* gy, const void* Wt, const void* dh,
-                           const void* At, void* stream) {
+                           const void* At, void* ws, size_t ws_bytes, void* stream) {
   SLIDER_CHECK_ARG(g && dx && gy && Wt, "lora_input_grad: null pointer");
   SLIDER_CHECK_ARG((dh == nullptr) == (At == nullptr), "lora_input_grad: dh and At must both be set or both NULL");
-  return run_gemm(g, g->cout, g->cin, dx, gy, Wt, nullptr, nullptr, nullptr, nullptr, 0.f, dh, At,
+  return run_gemm(g, g->cout, g->cin, dx, gy, Wt, nullptr, nullptr, nullptr, nullptr, 0.f, dh, At, ws, ws_bytes,
                   (cudaStream_t)stream);
 }
 

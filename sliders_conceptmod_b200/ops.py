@@ -26,6 +26,19 @@ def _act_dims(x: torch.Tensor) -> tuple[int, int, int]:
     raise ValueError(f"expected [B,H,W,C] or [M,K] activations, got {tuple(x.shape)}")
 
 
+_gemm_ws: dict[int, torch.Tensor] = {}
+
+
+def _gemm_workspace(device: torch.device) -> torch.Tensor:
+    """Per-device split-K scratch (contents don't-care; every call on the stream may share it)."""
+    key = device.index if device.index is not None else torch.cuda.current_device()
+    ws = _gemm_ws.get(key)
+    if ws is None:
+        ws = torch.empty(lib().slider_gemm_workspace_bytes(), dtype=torch.uint8, device=device)
+        _gemm_ws[key] = ws
+    return ws
+
+
 def lora_forward(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None, a: torch.Tensor | None,
                  b: torch.Tensor | None, s: float, ksize: int = 1, want_h: bool = False):
     """y = conv(x, w) + bias + s * (conv(x, a) @ b^T).   (lora.py:134-138)
@@ -41,8 +54,9 @@ def lora_forward(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None, a:
     g = make_geom(x.dtype, B, H, W, cin, cout, ksize, rank)
     y = torch.empty(*x.shape[:-1], cout, device=x.device, dtype=x.dtype)
     h = torch.empty(B * H * W, rank, device=x.device, dtype=torch.float32) if (want_h and rank > 0) else None
+    ws = _gemm_workspace(x.device)
     check(lib().slider_lora_forward(C.byref(g), ptr(y), ptr(x), ptr(w), ptr(bias), ptr(a), ptr(b), ptr(h),
-                                    float(s), stream_ptr()))
+                                    float(s), ptr(ws), ws.numel(), stream_ptr()))
     return y, h
 
 
@@ -54,7 +68,9 @@ def lora_input_grad(gy: torch.Tensor, wt: torch.Tensor, dh: torch.Tensor | None,
     B, H, W = _act_dims(gy)
     g = make_geom(gy.dtype, B, H, W, cin, gy.shape[-1], ksize, rank)
     dx = torch.empty(*gy.shape[:-1], cin, device=gy.device, dtype=gy.dtype)
-    check(lib().slider_lora_input_grad(C.byref(g), ptr(dx), ptr(gy), ptr(wt), ptr(dh), ptr(at), stream_ptr()))
+    ws = _gemm_workspace(gy.device)
+    check(lib().slider_lora_input_grad(C.byref(g), ptr(dx), ptr(gy), ptr(wt), ptr(dh), ptr(at), ptr(ws), ws.numel(),
+                                       stream_ptr()))
     return dx
 
 

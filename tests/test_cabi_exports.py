@@ -28,10 +28,10 @@ def test_library_builds_and_exports_header_symbols():
 
 def test_version_and_error_string_without_gpu():
     h = _lib.lib()
-    assert h.slider_version() == 1
+    assert h.slider_version() == 2
     assert isinstance(h.slider_last_error(), bytes)
     g = _lib.LayerGeom(1, 1, 1, 8, 8, 8, 5, 5, 2, 4)       # 5x5 kernel: rejected before any CUDA call
-    rc = h.slider_lora_forward(ctypes.byref(g), 16, 16, 16, None, None, None, None, 1.0, None)
+    rc = h.slider_lora_forward(ctypes.byref(g), 16, 16, 16, None, None, None, None, 1.0, None, 0, None)
     assert rc == 1 and b"1x1" in h.slider_last_error()
 
 

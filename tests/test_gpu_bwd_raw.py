@@ -13,6 +13,8 @@ CASES = [
     (2, 8, 8, 128, 320, 3, 4),
     (1, 24, 40, 64, 64, 3, 8),
     (2, 32, 32, 320, 640, 1, 16),
+    (2, 8, 8, 1280, 640, 3, 4),      # split-K in the extended-K input-gradient GEMM
+    (1, 1, 256, 1280, 1280, 1, 4),
 ]
 
 

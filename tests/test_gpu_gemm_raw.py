@@ -33,6 +33,16 @@ CASES = [
     (2, 64, 64, 320, 320, 3, 4),
     (1, 24, 40, 64, 64, 3, 8),
     (2, 32, 32, 640, 640, 1, 16),
+    # tile-starved shapes -> split-K + finalize
+    (2, 16, 16, 1280, 1280, 3, 4),
+    (2, 8, 8, 1280, 1280, 3, 4),
+    (2, 8, 8, 2560, 1280, 3, 8),
+    (1, 1, 512, 1280, 1280, 1, 4),
+    (1, 7, 9, 640, 320, 3, 4),
+    # M <= 16 rows of a 1x1 layer -> weight-streaming GEMV path (time_emb_proj)
+    (1, 1, 2, 1280, 1280, 1, 4),
+    (1, 1, 16, 320, 640, 1, 8),
+    (1, 1, 5, 640, 320, 1, 4),
 ]
 
 

@@ -29,6 +29,7 @@ SHAPES = [
     (1, 1, 8192, 320, 320, 1), (1, 1, 2048, 640, 640, 1), (1, 1, 512, 1280, 1280, 1),
     (1, 1, 2048, 1280, 1280, 1), (1, 1, 8192, 640, 640, 1), (1, 1, 65536, 640, 640, 1), (1, 1, 16384, 1280, 1280, 1),
     (2, 64, 64, 320, 320, 3), (2, 32, 32, 640, 640, 3), (2, 16, 16, 1280, 1280, 3), (2, 8, 8, 1280, 1280, 3),
+    (1, 1, 2, 1280, 1280, 1), (1, 1, 2, 1280, 320, 1), (2, 8, 8, 2560, 1280, 3),
     (2, 64, 64, 640, 320, 3), (2, 16, 16, 2560, 1280, 3), (16, 128, 128, 320, 320, 3), (16, 64, 64, 640, 640, 3),
 ]
 
