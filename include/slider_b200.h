@@ -121,6 +121,12 @@ int slider_lora_input_grad(const slider_layer_geom* g, void* dx, const void* gy,
                            const void* Wt, const void* dh, const void* At,
                            void* ws, size_t ws_bytes, void* stream);
 
+/* Profiling aid: when buf != NULL, every lora_gemm_kernel CTA writes 8 clock64()
+ * stamps (entry, setup done, first TMA issued, first operands landed, last MMA
+ * committed, accumulator visible to the epilogue, epilogue done, exit) to
+ * buf[cta*8 ..]; buf must hold 148*8 int64.  NULL switches it off. */
+int slider_debug_gemm_trace(void* buf);
+
 /* One-time repack of a frozen base weight [cout, kh*kw, cin] into the Wt layout. */
 int slider_pack_wt(const slider_layer_geom* g, void* Wt, const void* W,
                    void* stream);

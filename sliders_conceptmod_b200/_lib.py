@@ -31,6 +31,7 @@ _SIGNATURES = {
     "slider_last_error": (C.c_char_p, []),
     "slider_launch_count": (C.c_int64, []),
     "slider_gemm_workspace_bytes": (_sz, []),
+    "slider_debug_gemm_trace": (C.c_int, [_vp]),
     "slider_lora_forward": (C.c_int, [_G, _vp, _vp, _vp, _vp, _vp, _vp, _fp, _f, _vp, _sz, _vp]),
     "slider_lora_grad_workspace_bytes": (_sz, [_G]),
     "slider_lora_grad": (C.c_int, [_G, _fp, _fp, _vp, _vp, _vp, _fp, _vp, _f, _i, _vp, _sz, _vp]),

@@ -26,7 +26,7 @@ constexpr int BM = 128;          // pixels (GEMM rows) per tile
 constexpr int BN = 160;          // output channels per tile; divides 320/640/960/1280/1920/2560
 constexpr int HCOLS = 16;        // TMEM columns of the low-rank accumulator (rank padded to 16)
 constexpr int ROW_BYTES = 128;   // K-block row = one 128-byte swizzle row
-constexpr int NSTAGES = 5;
+constexpr int NSTAGES = 4;
 constexpr int ACC_STAGES = 2;
 constexpr int A_BYTES = BM * ROW_BYTES;      // 16 KB
 constexpr int B_BYTES = BN * ROW_BYTES;      // 20 KB
@@ -39,13 +39,19 @@ constexpr int EPI_FLOATS = BN * 16 + BN;     // s*Bup (rank padded to <=16) + bi
 constexpr int NCHUNK = BN / 32 + 1;          // 32-column chunks of a split-K partial tile (+1 for h)
 constexpr size_t UNIT_FLOATS = (size_t)NCHUNK * BM * 32;
 constexpr int MAX_UNITS = 160;               // split-K work units the caller workspace must hold
-constexpr size_t SMEM_BYTES = 1024 /*align slack*/ + (size_t)NSTAGES * STAGE_BYTES + EPI_FLOATS * 4 + 256;
+constexpr int OUT_BUFS = 3;                  // staging buffers of the TMA-store epilogue (one 32-column chunk each)
+constexpr int OUT_BYTES = BM * 32 * 4;       // 16 KB: 128 rows x 32 fp32 (bf16 output uses half of it)
+constexpr size_t SMEM_BYTES = 1024 /*align slack*/ + (size_t)NSTAGES * STAGE_BYTES + (size_t)OUT_BUFS * OUT_BYTES +
+                              EPI_FLOATS * 4 + 256;
 
 template <typename T> struct GemmTraits;
 template <> struct GemmTraits<__nv_bfloat16> {
   static constexpr int kBK = 64;       // elements per 128-byte row
   static constexpr uint32_t kFmt = 1;  // bf16
   static constexpr int kExtRowBytes = EXT_ELEMS * 2;
+  static constexpr bool kSplit3 = false;
+  static constexpr int kStages = NSTAGES;
+  static constexpr int kStageStride = STAGE_BYTES;
   __device__ static inline void mma(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) {
     ptx::mma_f16(d, a, b, idesc, acc);
   }
@@ -54,6 +60,12 @@ template <> struct GemmTraits<float> {
   static constexpr int kBK = 32;
   static constexpr uint32_t kFmt = 2;  // tf32
   static constexpr int kExtRowBytes = EXT_ELEMS * 4;
+  // fp32 storage: error-compensated 3xTF32.  Every landed stage is split in shared memory into
+  // hi = x with the 13 low mantissa bits cleared (exact in tf32) and lo = x - hi (second half of the
+  // stage slot), and each K step issues hi.hi + lo.hi + hi.lo into the same accumulator (~2^-21 rel).
+  static constexpr bool kSplit3 = true;
+  static constexpr int kStages = NSTAGES / 2;
+  static constexpr int kStageStride = 2 * STAGE_BYTES;
   __device__ static inline void mma(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) {
     ptx::mma_tf32(d, a, b, idesc, acc);
   }
@@ -75,6 +87,7 @@ struct GemmParams {
   int ksplit;             // K partitions per tile (1 = no split)
   int total_units;        // total_tiles * ksplit
   float* partial;         // split-K partial tiles, [unit][NCHUNK][128][32] fp32
+  long long* trace;       // debug: 8 clock64() stamps per CTA (NULL = off)
   void* y;
   const void* bias;
   const void* Bup;
@@ -98,7 +111,8 @@ template <typename T, int R4>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                  const __grid_constant__ CUtensorMap tmL, const __grid_constant__ CUtensorMap tmXe,
-                 const __grid_constant__ CUtensorMap tmWe, const GemmParams p) {
+                 const __grid_constant__ CUtensorMap tmWe, const __grid_constant__ CUtensorMap tmY,
+                 const __grid_constant__ CUtensorMap tmP, const GemmParams p) {
   using Tr = GemmTraits<T>;
   constexpr int BK = Tr::kBK;
   constexpr int KSTEPS = ROW_BYTES / 32;   // one tcgen05.mma consumes 32 bytes of K per row
@@ -106,25 +120,31 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  float* s_epi = reinterpret_cast<float*>(smem + (size_t)NSTAGES * STAGE_BYTES);
+  uint8_t* s_out = smem + (size_t)NSTAGES * STAGE_BYTES;   // OUT_BUFS x 16 KB, 1024-aligned (swizzled staging)
+  float* s_epi = reinterpret_cast<float*>(s_out + (size_t)OUT_BUFS * OUT_BYTES);
   uint64_t* bars = reinterpret_cast<uint64_t*>(s_epi + EPI_FLOATS);
   uint64_t* full_bar = bars;                      // [NSTAGES]  TMA -> MMA
   uint64_t* empty_bar = bars + NSTAGES;           // [NSTAGES]  MMA -> TMA
   uint64_t* tfull_bar = bars + 2 * NSTAGES;       // [ACC_STAGES] MMA -> epilogue
   uint64_t* tempty_bar = tfull_bar + ACC_STAGES;  // [ACC_STAGES] epilogue -> MMA
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + ACC_STAGES);
+  uint64_t* xf_bar = tempty_bar + ACC_STAGES;     // [NSTAGES] hi/lo split done (fp32 only) -> MMA
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(xf_bar + NSTAGES);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+#define SLIDER_TRACE(slot) do { if (p.trace != nullptr) p.trace[blockIdx.x * 8 + (slot)] = clock64(); } while (0)
+  if (threadIdx.x == 0) SLIDER_TRACE(0);
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tmA);
     ptx::prefetch_tmap(&tmW);
     if (p.lora) ptx::prefetch_tmap(&tmL);
     if (p.ext) { ptx::prefetch_tmap(&tmXe); ptx::prefetch_tmap(&tmWe); }
+    if (p.ksplit > 1) ptx::prefetch_tmap(&tmP); else ptx::prefetch_tmap(&tmY);
     for (int i = 0; i < NSTAGES; ++i) {
       ptx::mbar_init(ptx::smem_u32(full_bar + i), 1);
       ptx::mbar_init(ptx::smem_u32(empty_bar + i), 1);
+      ptx::mbar_init(ptx::smem_u32(xf_bar + i), 4);      // one arrive per epilogue warp
     }
     for (int i = 0; i < ACC_STAGES; ++i) {
       ptx::mbar_init(ptx::smem_u32(tfull_bar + i), 1);
@@ -141,6 +161,7 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const uint32_t smem_base = ptx::smem_u32(smem);
+  if (threadIdx.x == 0) SLIDER_TRACE(1);
 
   const uint32_t main_tx = (uint32_t)(p.rows * ROW_BYTES + B_BYTES + (p.lora ? L_BYTES : 0));
   const uint32_t ext_tx = (uint32_t)((p.rows + BN) * Tr::kExtRowBytes);
@@ -149,15 +170,18 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // ===================== TMA producer =====================
     uint32_t stage = 0, phase = 0;
     for (int unit = blockIdx.x; unit < p.total_units; unit += gridDim.x) {
-      const int tile = unit / p.ksplit, split = unit - tile * p.ksplit;
+      const int tile = p.ksplit > 1 ? unit / p.ksplit : unit, split = unit - tile * p.ksplit;
       const TileCoord tc = tile_coord(p, tile);
-      const int it0 = (int)((long long)split * p.kiters / p.ksplit);
-      const int it1 = (int)((long long)(split + 1) * p.kiters / p.ksplit);
-      int tap = it0 / p.per_tap, j = it0 - tap * p.per_tap;
+      int it0 = 0, it1 = p.kiters, tap = 0, j = 0;
+      if (p.ksplit > 1) {
+        it0 = split * p.kiters / p.ksplit;
+        it1 = (split + 1) * p.kiters / p.ksplit;
+        tap = it0 / p.per_tap; j = it0 - tap * p.per_tap;
+      }
       for (int it = it0; it < it1; ++it) {
         const int dy = tap / p.kw - p.pad, dx = tap % p.kw - p.pad;
         ptx::mbar_wait(ptx::smem_u32(empty_bar + stage), phase ^ 1);
-        const uint32_t sa = smem_base + stage * STAGE_BYTES;
+        const uint32_t sa = smem_base + stage * Tr::kStageStride;
         const uint32_t fb = ptx::smem_u32(full_bar + stage);
         if (j < p.cblocks) {
           ptx::mbar_arrive_expect_tx(fb, main_tx);
@@ -169,7 +193,8 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           ptx::tma_load_4d(sa, &tmXe, fb, 0, tc.w0 + dx, tc.h0 + dy, tc.b0);
           ptx::tma_load_3d(sa + A_BYTES, &tmWe, fb, 0, tap, tc.n0);
         }
-        if (++stage == NSTAGES) { stage = 0; phase ^= 1; }
+        if (unit == (int)blockIdx.x && it == it0) SLIDER_TRACE(2);
+        if (++stage == Tr::kStages) { stage = 0; phase ^= 1; }
         if (++j == p.per_tap) { j = 0; ++tap; }
       }
     }
@@ -182,85 +207,139 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const uint32_t idesc = p.lora ? idesc_lora : idesc_main;
     uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
     for (int unit = blockIdx.x; unit < p.total_units; unit += gridDim.x) {
-      const int split = unit % p.ksplit;
-      const int it0 = (int)((long long)split * p.kiters / p.ksplit);
-      const int it1 = (int)((long long)(split + 1) * p.kiters / p.ksplit);
-      int j = it0 % p.per_tap;
+      int it0 = 0, it1 = p.kiters, j = 0;
+      if (p.ksplit > 1) {
+        const int split = unit % p.ksplit;
+        it0 = split * p.kiters / p.ksplit;
+        it1 = (split + 1) * p.kiters / p.ksplit;
+        j = it0 % p.per_tap;
+      }
       ptx::mbar_wait(ptx::smem_u32(tempty_bar + as), aphase ^ 1);
       ptx::tc_fence_after();
       const uint32_t d_main = tmem_base + as * (BN + HCOLS);
       uint32_t acc = 0;
       for (int it = it0; it < it1; ++it) {
-        ptx::mbar_wait(ptx::smem_u32(full_bar + stage), phase);
+        ptx::mbar_wait(ptx::smem_u32((Tr::kSplit3 ? xf_bar : full_bar) + stage), phase);
         ptx::tc_fence_after();
-        const uint32_t sa = smem_base + stage * STAGE_BYTES;
-        if (j < p.cblocks) {
-          const uint64_t da = ptx::smem_desc_kmajor(sa, ROW_BYTES);
-          const uint64_t db = ptx::smem_desc_kmajor(sa + A_BYTES, ROW_BYTES);
+        if (unit == (int)blockIdx.x && it == it0) SLIDER_TRACE(3);
+        const uint32_t sa = smem_base + stage * Tr::kStageStride;
+        const bool main_blk = j < p.cblocks;
+        const uint32_t rb = main_blk ? (uint32_t)ROW_BYTES : (uint32_t)Tr::kExtRowBytes;
+        const uint32_t id = main_blk ? idesc : idesc_main;
+        const int ksteps = main_blk ? KSTEPS : EXT_KSTEPS;
+        const uint64_t da = ptx::smem_desc_kmajor(sa, rb);
+        const uint64_t db = ptx::smem_desc_kmajor(sa + A_BYTES, rb);
+        if (Tr::kSplit3) {
+          const uint64_t da_lo = ptx::smem_desc_kmajor(sa + STAGE_BYTES, rb);
+          const uint64_t db_lo = ptx::smem_desc_kmajor(sa + STAGE_BYTES + A_BYTES, rb);
+          for (int k = 0; k < ksteps; ++k) {
+            Tr::mma(d_main, da_lo + 2 * k, db + 2 * k, id, acc | (uint32_t)k);
+            Tr::mma(d_main, da + 2 * k, db_lo + 2 * k, id, 1u);
+            Tr::mma(d_main, da + 2 * k, db + 2 * k, id, 1u);
+          }
+        } else if (main_blk) {
 #pragma unroll
-          for (int k = 0; k < KSTEPS; ++k) Tr::mma(d_main, da + 2 * k, db + 2 * k, idesc, acc | (uint32_t)k);
+          for (int k = 0; k < KSTEPS; ++k) Tr::mma(d_main, da + 2 * k, db + 2 * k, id, acc | (uint32_t)k);
         } else {
-          const uint64_t da = ptx::smem_desc_kmajor(sa, Tr::kExtRowBytes);
-          const uint64_t db = ptx::smem_desc_kmajor(sa + A_BYTES, Tr::kExtRowBytes);
 #pragma unroll
-          for (int k = 0; k < EXT_KSTEPS; ++k) Tr::mma(d_main, da + 2 * k, db + 2 * k, idesc_main, acc | (uint32_t)k);
+          for (int k = 0; k < EXT_KSTEPS; ++k) Tr::mma(d_main, da + 2 * k, db + 2 * k, id, acc | (uint32_t)k);
         }
         acc = 1;
         ptx::mma_commit(ptx::smem_u32(empty_bar + stage));
-        if (++stage == NSTAGES) { stage = 0; phase ^= 1; }
+        if (++stage == Tr::kStages) { stage = 0; phase ^= 1; }
         if (++j == p.per_tap) j = 0;
       }
       ptx::mma_commit(ptx::smem_u32(tfull_bar + as));
+      if (unit == (int)blockIdx.x) SLIDER_TRACE(4);
       if (++as == ACC_STAGES) { as = 0; aphase ^= 1; }
     }
   } else if (warp >= 2) {
     // ===================== epilogue =====================
+    // Per 32-column chunk: tcgen05.ld -> registers -> (+bias + s*h.Bup^T, cast) -> swizzled shared staging
+    // -> one TMA store (box {32 ch, TW, TH, TB}: fully coalesced, clips out-of-range pixels/channels).
+    // Three staging buffers and one named barrier per chunk: before the barrier of chunk c the issuing
+    // thread waits until at most one store (c-1) still reads shared memory, so the buffer the threads
+    // fill next (chunk c+1, last used by store c-2) is free once they pass that barrier.
     const int q = warp & 3;               // TMEM lane quarter this warp may read
     const int row = q * 32 + lane;        // tile row == TMEM lane
     const int et = threadIdx.x - 64;      // 0..127 among epilogue threads
     float* s_bias = s_epi + BN * 16;
-    uint32_t as = 0, aphase = 0;
-    T* __restrict__ y = reinterpret_cast<T*>(p.y);
+    const uint32_t out_base = ptx::smem_u32(s_out);
+    const uint32_t epi_s = ptx::smem_u32(s_epi), bias_s = ptx::smem_u32(s_bias);
+    uint32_t as = 0, aphase = 0, ob = 0, xs = 0, xphase = 0;
     const T* __restrict__ bias = reinterpret_cast<const T*>(p.bias);
     const T* __restrict__ Bup = reinterpret_cast<const T*>(p.Bup);
     for (int unit = blockIdx.x; unit < p.total_units; unit += gridDim.x) {
+      if (Tr::kSplit3) {
+        // fp32: split every stage of this unit into hi / lo before the MMA warp may consume it
+        int n_it = p.kiters;
+        if (p.ksplit > 1) {
+          const int split = unit % p.ksplit;
+          n_it = (split + 1) * p.kiters / p.ksplit - split * p.kiters / p.ksplit;
+        }
+        for (int it = 0; it < n_it; ++it) {
+          ptx::mbar_wait(ptx::smem_u32(full_bar + xs), xphase);
+          float4* hi = reinterpret_cast<float4*>(smem + (size_t)xs * Tr::kStageStride);
+          float4* lo = reinterpret_cast<float4*>(smem + (size_t)xs * Tr::kStageStride + STAGE_BYTES);
+          for (int i = et; i < STAGE_BYTES / 16; i += 128) {
+            const float4 v = hi[i];
+            float4 h4, l4;
+            h4.x = __uint_as_float(__float_as_uint(v.x) & 0xffffe000u); l4.x = v.x - h4.x;
+            h4.y = __uint_as_float(__float_as_uint(v.y) & 0xffffe000u); l4.y = v.y - h4.y;
+            h4.z = __uint_as_float(__float_as_uint(v.z) & 0xffffe000u); l4.z = v.z - h4.z;
+            h4.w = __uint_as_float(__float_as_uint(v.w) & 0xffffe000u); l4.w = v.w - h4.w;
+            hi[i] = h4;
+            lo[i] = l4;
+          }
+          ptx::fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(xf_bar + xs));
+          if (++xs == (uint32_t)Tr::kStages) { xs = 0; xphase ^= 1; }
+        }
+      }
       if (p.ksplit > 1) {
         // split-K: park the fp32 partial tile (main + h columns) in the L2-resident workspace,
-        // [unit][chunk][row][32] so that a warp writes 4 KB contiguous; splitk_finalize_kernel reduces.
+        // [unit][chunk][row][32]; splitk_finalize_kernel reduces over the splits in a fixed order.
         ptx::mbar_wait(ptx::smem_u32(tfull_bar + as), aphase);
         ptx::tc_fence_after();
+        if (et == 0 && unit == (int)blockIdx.x) SLIDER_TRACE(5);
         const uint32_t t_acc = tmem_base + ((uint32_t)(q * 32) << 16) + as * (BN + HCOLS);
-        float* dst = p.partial + (size_t)unit * UNIT_FLOATS + (size_t)row * 32;
+        const int nch = (R4 > 0) ? NCHUNK : NCHUNK - 1;
 #pragma unroll 1
-        for (int c = 0; c < BN / 32; ++c) {
+        for (int c = 0; c < nch; ++c) {
           uint32_t v[32];
-          ptx::tmem_ld_32x32(t_acc + c * 32, v);
+          if (c < BN / 32) {
+            ptx::tmem_ld_32x32(t_acc + c * 32, v);
+          } else {
+            uint32_t hr[16];
+            ptx::tmem_ld_32x16(t_acc + BN, hr);
+#pragma unroll
+            for (int k = 0; k < 16; ++k) { v[k] = hr[k]; v[16 + k] = 0u; }
+          }
           ptx::tmem_ld_wait();
-          float4* d4 = reinterpret_cast<float4*>(dst + (size_t)c * BM * 32);
+          const uint32_t dst = out_base + ob * OUT_BYTES + row * 128;
 #pragma unroll
           for (int k = 0; k < 8; ++k)
-            d4[k] = make_float4(__uint_as_float(v[4 * k]), __uint_as_float(v[4 * k + 1]),
-                                __uint_as_float(v[4 * k + 2]), __uint_as_float(v[4 * k + 3]));
-        }
-        if (R4 > 0) {
-          uint32_t hr[16];
-          ptx::tmem_ld_32x16(t_acc + BN, hr);
-          ptx::tmem_ld_wait();
-          float4* d4 = reinterpret_cast<float4*>(dst + (size_t)(BN / 32) * BM * 32);
-#pragma unroll
-          for (int k = 0; k < 4; ++k)
-            d4[k] = make_float4(__uint_as_float(hr[4 * k]), __uint_as_float(hr[4 * k + 1]),
-                                __uint_as_float(hr[4 * k + 2]), __uint_as_float(hr[4 * k + 3]));
+            ptx::st_shared_v4(dst + ((k ^ (row & 7)) << 4), v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+          ptx::fence_proxy_async_smem();
+          if (et == 0) ptx::bulk_wait_read<1>();     // buffer of the NEXT chunk (store c-2) is free past the barrier
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          if (et == 0) {
+            ptx::tma_store_2d(&tmP, out_base + ob * OUT_BYTES, 0, (unit * NCHUNK + c) * BM);
+            ptx::bulk_commit();
+          }
+          if (++ob == OUT_BUFS) ob = 0;
         }
         ptx::tc_fence_before();
         __syncwarp();
+        if (et == 0 && unit == (int)blockIdx.x) SLIDER_TRACE(6);
         if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(tempty_bar + as));
         if (++as == ACC_STAGES) { as = 0; aphase ^= 1; }
         continue;
       }
       const TileCoord tc = tile_coord(p, unit);
       // stage s*Bup[n0.., :] and bias[n0..] for this tile (fp32) while the MMAs run
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      asm volatile("bar.sync 2, 128;" ::: "memory");
       for (int i = et; i < BN; i += 128) {
         const int n = tc.n0 + i;
         s_bias[i] = (bias != nullptr && n < p.N) ? Elem<T>::to_f(bias[n]) : 0.f;
@@ -271,14 +350,11 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 (n < p.N && j < p.rank) ? p.s * Elem<T>::to_f(Bup[(size_t)n * p.rank + j]) : 0.f;
         }
       }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-
-      const int lw = row % p.TW, lh = (row / p.TW) % p.TH, lb = row / (p.TW * p.TH);
-      const bool row_ok = row < p.rows && tc.w0 + lw < p.W && tc.h0 + lh < p.H && tc.b0 + lb < p.B;
-      const size_t pix = ((size_t)(tc.b0 + lb) * p.H + (tc.h0 + lh)) * p.W + (tc.w0 + lw);
+      asm volatile("bar.sync 2, 128;" ::: "memory");
 
       ptx::mbar_wait(ptx::smem_u32(tfull_bar + as), aphase);
       ptx::tc_fence_after();
+      if (et == 0 && unit == (int)blockIdx.x) SLIDER_TRACE(5);
       const uint32_t t_main = tmem_base + ((uint32_t)(q * 32) << 16) + as * (BN + HCOLS);
 
       float hv[R4 > 0 ? 4 * R4 : 1];
@@ -288,28 +364,36 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         ptx::tmem_ld_wait();
 #pragma unroll
         for (int j = 0; j < 4 * R4; ++j) hv[j] = __uint_as_float(hr[j]);
-        if (p.h_out != nullptr && tc.n_blk == 0 && row_ok) {
-          for (int j = 0; j < p.rank; ++j) p.h_out[pix * p.rank + j] = __uint_as_float(hr[j]);
+        if (p.h_out != nullptr && tc.n_blk == 0) {
+          const int lw = row % p.TW, lh = (row / p.TW) % p.TH, lb = row / (p.TW * p.TH);
+          const bool row_ok = row < p.rows && tc.w0 + lw < p.W && tc.h0 + lh < p.H && tc.b0 + lb < p.B;
+          const size_t pix = ((size_t)(tc.b0 + lb) * p.H + (tc.h0 + lh)) * p.W + (tc.w0 + lw);
+          if (row_ok) {
+#pragma unroll
+            for (int j = 0; j < 4 * R4; ++j)
+              if (j < p.rank) p.h_out[pix * p.rank + j] = hv[j];
+          }
         }
       }
+      const int n_chunks = min(BN / 32, (p.N - tc.n0 + 31) / 32);
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
+      for (int c = 0; c < n_chunks; ++c) {
         uint32_t v[32];
         ptx::tmem_ld_32x32(t_main + c * 32, v);
         ptx::tmem_ld_wait();
-        const int nb = tc.n0 + c * 32;
+        const uint32_t dst = out_base + ob * OUT_BYTES + row * (32 * (int)sizeof(T));
 #pragma unroll
         for (int g8 = 0; g8 < 4; ++g8) {
           float o[8];
 #pragma unroll
           for (int k = 0; k < 8; ++k) {
             const int i = c * 32 + g8 * 8 + k;
-            float a = __uint_as_float(v[g8 * 8 + k]) + s_bias[i];
+            // explicit ld.shared: the generic pointers derived from the re-aligned base compile to LD.E
+            float a = __uint_as_float(v[g8 * 8 + k]) + ptx::ld_shared_f32(bias_s + i * 4);
             if (R4 > 0) {
-              const float4* bp = reinterpret_cast<const float4*>(s_epi + i * (4 * R4));
 #pragma unroll
               for (int j4 = 0; j4 < R4; ++j4) {
-                const float4 b = bp[j4];
+                const float4 b = ptx::ld_shared_f4(epi_s + i * (16 * R4) + j4 * 16);
                 a = fmaf(hv[4 * j4 + 0], b.x, a);
                 a = fmaf(hv[4 * j4 + 1], b.y, a);
                 a = fmaf(hv[4 * j4 + 2], b.z, a);
@@ -318,23 +402,37 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             }
             o[k] = a;
           }
-          if (row_ok && nb + g8 * 8 < p.N) {
-            T* dst = y + pix * (size_t)p.N + nb + g8 * 8;
-            if (sizeof(T) == 2) {
-              Elem<__nv_bfloat16>::store(reinterpret_cast<__nv_bfloat16*>(dst), o);
-            } else {
-              float* d = reinterpret_cast<float*>(dst);
-              *reinterpret_cast<float4*>(d) = make_float4(o[0], o[1], o[2], o[3]);
-              *reinterpret_cast<float4*>(d + 4) = make_float4(o[4], o[5], o[6], o[7]);
+          if (sizeof(T) == 2) {      // 64-byte rows, SWIZZLE_64B: 16-byte chunk ^= (row >> 1) & 3
+            uint32_t w[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              __nv_bfloat162 h2 = __floats2bfloat162_rn(o[2 * k], o[2 * k + 1]);
+              w[k] = *reinterpret_cast<uint32_t*>(&h2);
             }
+            ptx::st_shared_v4(dst + ((g8 ^ ((row >> 1) & 3)) << 4), w[0], w[1], w[2], w[3]);
+          } else {                   // 128-byte rows, SWIZZLE_128B: 16-byte chunk ^= row & 7
+            ptx::st_shared_v4(dst + (((2 * g8) ^ (row & 7)) << 4), __float_as_uint(o[0]), __float_as_uint(o[1]),
+                              __float_as_uint(o[2]), __float_as_uint(o[3]));
+            ptx::st_shared_v4(dst + (((2 * g8 + 1) ^ (row & 7)) << 4), __float_as_uint(o[4]), __float_as_uint(o[5]),
+                              __float_as_uint(o[6]), __float_as_uint(o[7]));
           }
         }
+        ptx::fence_proxy_async_smem();
+        if (et == 0) ptx::bulk_wait_read<1>();       // buffer of the NEXT chunk (store c-2) is free past the barrier
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (et == 0) {
+          ptx::tma_store_4d(&tmY, out_base + ob * OUT_BYTES, tc.n0 + c * 32, tc.w0, tc.h0, tc.b0);
+          ptx::bulk_commit();
+        }
+        if (++ob == OUT_BUFS) ob = 0;
       }
       ptx::tc_fence_before();
       __syncwarp();
+      if (et == 0 && unit == (int)blockIdx.x) SLIDER_TRACE(6);
       if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(tempty_bar + as));
       if (++as == ACC_STAGES) { as = 0; aphase ^= 1; }
     }
+    if (et == 0) ptx::bulk_wait_all();    // all TMA stores of this CTA have landed before it exits
   }
 
   ptx::tc_fence_before();
@@ -343,6 +441,8 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     ptx::tc_fence_after();
     ptx::tmem_dealloc(tmem_base, TMEM_COLS);
   }
+  if (threadIdx.x == 0) SLIDER_TRACE(7);
+#undef SLIDER_TRACE
 }
 
 
@@ -495,6 +595,8 @@ namespace slider {
 
 struct TileGeom { int TW, TH, TB; };
 
+static long long* g_gemm_trace = nullptr;   // set by slider_debug_gemm_trace (profiling aid)
+
 static TileGeom choose_tile(int W, int H, int B) {
   TileGeom t;
   t.TW = W < BM ? W : BM;
@@ -511,8 +613,10 @@ static inline int esize(int dtype) { return dtype == SLIDER_BF16 ? 2 : 4; }
 
 template <typename T>
 static int launch_gemm(int r4, const CUtensorMap& a, const CUtensorMap& w, const CUtensorMap& l,
-                       const CUtensorMap& xe, const CUtensorMap& we, const GemmParams& p, cudaStream_t st) {
-  void (*kern)(CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, GemmParams) = nullptr;
+                       const CUtensorMap& xe, const CUtensorMap& we, const CUtensorMap& my, const CUtensorMap& mp,
+                       const GemmParams& p, cudaStream_t st) {
+  void (*kern)(CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap,
+               GemmParams) = nullptr;
   void (*fin)(GemmParams) = nullptr;
   switch (r4) {
     case 0: kern = lora_gemm_kernel<T, 0>; fin = splitk_finalize_kernel<T, 0>; break;
@@ -528,7 +632,7 @@ static int launch_gemm(int r4, const CUtensorMap& a, const CUtensorMap& w, const
     for (auto& c : configured) if (c == nullptr) { c = (const void*)kern; break; }
   }
   int grid = p.total_units < sm_count() ? p.total_units : sm_count();
-  kern<<<grid, kGemmThreads, SMEM_BYTES, st>>>(a, w, l, xe, we, p);
+  kern<<<grid, kGemmThreads, SMEM_BYTES, st>>>(a, w, l, xe, we, my, mp, p);
   int rc = post_launch("lora_gemm_kernel");
   if (rc || p.ksplit == 1) return rc;
   const long long threads = (long long)p.total_tiles * BM * (BN / 8);
@@ -612,6 +716,7 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
     if (ks >= 2) p.ksplit = ks;
   }
   p.total_units = p.total_tiles * p.ksplit;
+  p.trace = g_gemm_trace;
   p.y = y; p.bias = bias; p.Bup = Bup; p.h_out = lora ? h_out : nullptr;
   if (lora) {
     SLIDER_CHECK_ARG((g->rank * taps * kc * es) % 16 == 0 && ((uintptr_t)lo & 15) == 0, "lora gemm: lora_down misaligned");
@@ -650,9 +755,23 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
     uint32_t wbox[3] = {(uint32_t)EXT_ELEMS, 1u, (uint32_t)BN};
     if ((rc = make_tmap(&mWe, g->dtype, 3, we, wdims, wstr, wbox, eb))) return rc;
   }
+  CUtensorMap mY, mP;
+  {
+    uint64_t dims[4] = {(uint64_t)nn, (uint64_t)g->width, (uint64_t)g->height, (uint64_t)g->batch};
+    uint64_t str[3] = {(uint64_t)nn * es, (uint64_t)nn * es * g->width, (uint64_t)nn * es * g->width * g->height};
+    uint32_t box[4] = {32u, (uint32_t)tg.TW, (uint32_t)tg.TH, (uint32_t)tg.TB};
+    if ((rc = make_tmap(&mY, g->dtype, 4, y, dims, str, box, 32 * es))) return rc;
+  }
+  mP = mY;
+  if (p.ksplit > 1) {
+    uint64_t dims[2] = {32u, (uint64_t)p.total_units * NCHUNK * BM};
+    uint64_t str[1] = {128u};
+    uint32_t box[2] = {32u, (uint32_t)BM};
+    if ((rc = make_tmap(&mP, SLIDER_F32, 2, ws, dims, str, box, 128))) return rc;
+  }
   const int r4 = !lora ? 0 : (g->rank <= 4 ? 1 : (g->rank <= 8 ? 2 : 4));
-  if (g->dtype == SLIDER_BF16) return launch_gemm<__nv_bfloat16>(r4, mA, mW, mL, mXe, mWe, p, st);
-  return launch_gemm<float>(r4, mA, mW, mL, mXe, mWe, p, st);
+  if (g->dtype == SLIDER_BF16) return launch_gemm<__nv_bfloat16>(r4, mA, mW, mL, mXe, mWe, mY, mP, p, st);
+  return launch_gemm<float>(r4, mA, mW, mL, mXe, mWe, mY, mP, p, st);
 }
 
 }  // namespace slider
@@ -660,6 +779,8 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
 using namespace slider;
 
 extern "C" {
+
+int slider_debug_gemm_trace(void* buf) { g_gemm_trace = reinterpret_cast<long long*>(buf); return SLIDER_OK; }
 
 size_t slider_gemm_workspace_bytes(void) { return (size_t)MAX_UNITS * UNIT_FLOATS * sizeof(float); }
 

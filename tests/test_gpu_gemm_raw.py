@@ -68,12 +68,12 @@ def test_lora_forward_matches_torch(case, dtype):
     torch.cuda.synchronize()
     yr, hr = _ref_forward(xd.float(), wd.float(), bd.float(), ad.float(), bbd.float(), s, k)
     y = y.float().reshape(yr.shape)
-    tol = 2e-2 if dtype == torch.bfloat16 else 3e-3
+    tol = 2e-2 if dtype == torch.bfloat16 else 5e-5     # fp32 storage = error-compensated 3xTF32 (fp32 accumulate over K up to 23040)
     err = (y - yr).abs().max().item()
     scale = yr.abs().max().item()
     assert err <= tol * scale, f"max-abs {err} vs scale {scale}"
     herr = (h - hr).abs().max().item()
-    assert herr <= (1e-3 if dtype == torch.bfloat16 else 3e-3) * hr.abs().max().item() + 1e-6
+    assert herr <= (1e-3 if dtype == torch.bfloat16 else 2e-5) * hr.abs().max().item() + 1e-6
     # adapter off: plain GEMM path
     y0, _ = ops.lora_forward(xin, wd, bd, ad, bbd, 0.0, ksize=k)
     y0r, _ = _ref_forward(xd.float(), wd.float(), bd.float(), None, None, 0.0, k)
