@@ -166,6 +166,24 @@ int slider_cfg_step(void* out, const void* x, const void* eps_u,
                     float g, float c_x, float c_eps, float c_noise,
                     const float* dev_coef, int dtype, void* stream);
 
+/*
+ * NHWC GroupNorm with optional per-(batch,channel) pre-add and SiLU — the producer of every
+ * wrapped convolution's input in the UNet's ResnetBlock2D (the reference
+ * delegates to diffusers: norm1 -> SiLU -> conv1, "+ time_emb_proj(temb)" -> norm2 -> SiLU -> conv2):
+ *     z = x + chan_add[b, c];  y = act((z - mean_g) * rstd_g * gamma[c] + beta[c])
+ *   x, y      [batch, hw, channels]  channels innermost (multiple of 8), element dtype
+ *   chan_add  [batch, channels] or NULL;  gamma, beta [channels] or NULL
+ *   silu      != 0 applies SiLU
+ *   ws        slider_groupnorm_workspace_bytes(batch, groups) bytes, zero-filled ONCE by the caller
+ *             (the kernels leave the ticket words zero); may be shared by calls on one stream.
+ * Two launches (statistics, apply); deterministic reduction order.
+ */
+size_t slider_groupnorm_workspace_bytes(int batch, int groups);
+int slider_groupnorm_nhwc(void* y, const void* x, const void* chan_add,
+                          const void* gamma, const void* beta, int batch, int hw,
+                          int channels, int groups, float eps, int silu, int dtype,
+                          void* ws, size_t ws_bytes, void* stream);
+
 /* x *= *dev_scalar  (chain rule for a non-unit upstream loss gradient). */
 int slider_scale_by_device_scalar(void* x, const float* dev_scalar,
                                   int64_t n_elem, int dtype, void* stream);

@@ -1,0 +1,242 @@
+// NHWC GroupNorm (+ per-(batch,channel) pre-add, + SiLU) for the UNet layers that feed the fused
+// LoRA convolutions (ResnetBlock2D: norm1 -> SiLU -> conv1, "+ time embedding" -> norm2 -> SiLU -> conv2).
+// HBM-bound: x is read twice (statistics, apply) and y written once; channels are innermost so every
+// access is a 16-byte vector and the result is already in the layout the implicit-GEMM kernel loads.
+//
+//   z = x + chan_add[b, c]                      (optional: the time-embedding projection)
+//   y = act((z - mean_g) * rstd_g * gamma[c] + beta[c]),   act = SiLU or identity
+//
+// Statistics are reduced deterministically: fixed per-thread channel ownership, per-chunk partials,
+// and the last block of a batch item (ticket) combines the partials in index order.
+#include "common.cuh"
+
+namespace slider {
+
+struct GnParams {
+  int B, HW, C, G, cpg;
+  int NV;          // 8-channel vectors per pixel
+  int PL;          // pixel lanes per block (threads = PL * NV <= 512)
+  int chunks;      // pixel chunks per batch item (stats grid.x)
+  int ppc;         // pixels per chunk
+  float eps;
+  int silu;
+};
+
+constexpr int GN_MAX_THREADS = 512;
+constexpr int GN_TICKETS = 64;      // max batch; ticket slots at the head of the workspace
+
+template <typename T> struct Vec8;
+template <> struct Vec8<__nv_bfloat16> {
+  __device__ static inline void load(const __nv_bfloat16* p, float (&v)[8]) { Elem<__nv_bfloat16>::load(p, v); }
+  __device__ static inline void store(__nv_bfloat16* p, const float (&v)[8]) { Elem<__nv_bfloat16>::store(p, v); }
+};
+template <> struct Vec8<float> {
+  __device__ static inline void load(const float* p, float (&v)[8]) {
+    const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+  }
+  __device__ static inline void store(float* p, const float (&v)[8]) {
+    *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+    *reinterpret_cast<float4*>(p + 4) = make_float4(v[4], v[5], v[6], v[7]);
+  }
+};
+
+// ---- pass 1: per-(batch, group) mean / rstd ------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(GN_MAX_THREADS)
+gn_stats_kernel(const T* __restrict__ x, const T* __restrict__ chan_add, float* __restrict__ partial,
+                float* __restrict__ stats, unsigned* __restrict__ ticket, const GnParams p) {
+  extern __shared__ __align__(16) float gn_smem[];
+  float* s_sum = gn_smem;                       // [PL][C]
+  float* s_sq = gn_smem + (size_t)p.PL * p.C;   // [PL][C]
+  __shared__ bool s_last;
+  const int b = blockIdx.y, chunk = blockIdx.x;
+  const int tid = threadIdx.x;
+  const int pl = tid / p.NV, v = tid - pl * p.NV;
+  if (pl < p.PL) {
+    float add[8], sum[8], sq[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { add[k] = 0.f; sum[k] = 0.f; sq[k] = 0.f; }
+    if (chan_add != nullptr) Vec8<T>::load(chan_add + (size_t)b * p.C + v * 8, add);
+    const int p0 = chunk * p.ppc;
+    const int p1 = min(p.HW, p0 + p.ppc);
+    const T* xb = x + ((size_t)b * p.HW) * p.C + v * 8;
+    for (int pix = p0 + pl; pix < p1; pix += p.PL) {
+      float xv[8];
+      Vec8<T>::load(xb + (size_t)pix * p.C, xv);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float z = xv[k] + add[k];
+        sum[k] += z;
+        sq[k] = fmaf(z, z, sq[k]);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      s_sum[pl * p.C + v * 8 + k] = sum[k];
+      s_sq[pl * p.C + v * 8 + k] = sq[k];
+    }
+  }
+  __syncthreads();
+  if (tid < p.G) {
+    float a = 0.f, q = 0.f;
+    for (int l = 0; l < p.PL; ++l)
+      for (int c = tid * p.cpg; c < (tid + 1) * p.cpg; ++c) { a += s_sum[l * p.C + c]; q += s_sq[l * p.C + c]; }
+    float* dst = partial + (((size_t)b * p.chunks + chunk) * p.G + tid) * 2;
+    dst[0] = a; dst[1] = q;
+    __threadfence();
+  }
+  __syncthreads();
+  if (tid == 0) {
+    const unsigned t = atomicAdd(ticket + b, 1u);
+    s_last = (t == (unsigned)p.chunks - 1);
+  }
+  __syncthreads();
+  if (s_last) {
+    __threadfence();
+    if (tid < p.G) {
+      double a = 0.0, q = 0.0;
+      for (int ch = 0; ch < p.chunks; ++ch) {
+        const float* src = partial + (((size_t)b * p.chunks + ch) * p.G + tid) * 2;
+        a += (double)__ldcg(src);
+        q += (double)__ldcg(src + 1);
+      }
+      const double n = (double)p.cpg * (double)p.HW;
+      const double mean = a / n;
+      double var = q / n - mean * mean;
+      if (var < 0.0) var = 0.0;
+      stats[((size_t)b * p.G + tid) * 2] = (float)mean;
+      stats[((size_t)b * p.G + tid) * 2 + 1] = (float)(1.0 / sqrt(var + (double)p.eps));
+    }
+    if (tid == 0) ticket[b] = 0u;
+  }
+}
+
+// ---- pass 2: normalise, affine, activation -----------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+gn_apply_kernel(T* __restrict__ y, const T* __restrict__ x, const T* __restrict__ chan_add,
+                const T* __restrict__ gamma, const T* __restrict__ beta, const float* __restrict__ stats,
+                const GnParams p, int chunks, int ppc) {
+  extern __shared__ __align__(16) float gn_smem[];
+  float* s_scale = gn_smem;         // [C]
+  float* s_shift = gn_smem + p.C;   // [C]
+  const int b = blockIdx.y;
+  for (int c = threadIdx.x; c < p.C; c += blockDim.x) {
+    const int g = c / p.cpg;
+    const float mean = stats[((size_t)b * p.G + g) * 2], rstd = stats[((size_t)b * p.G + g) * 2 + 1];
+    const float ga = gamma ? Elem<T>::to_f(gamma[c]) : 1.f, be = beta ? Elem<T>::to_f(beta[c]) : 0.f;
+    const float add = chan_add ? Elem<T>::to_f(chan_add[(size_t)b * p.C + c]) : 0.f;
+    s_scale[c] = rstd * ga;
+    s_shift[c] = fmaf(add - mean, rstd * ga, be);
+  }
+  __syncthreads();
+  const int p0 = blockIdx.x * ppc;
+  const int p1 = min(p.HW, p0 + ppc);
+  if (p0 >= p1) return;
+  const long long total = (long long)(p1 - p0) * p.NV;
+  const T* xb = x + ((size_t)b * p.HW + p0) * p.C;
+  T* yb = y + ((size_t)b * p.HW + p0) * p.C;
+  int v = threadIdx.x % p.NV;
+  const int dv = blockDim.x % p.NV;
+  for (long long idx = threadIdx.x; idx < total; idx += blockDim.x) {
+    float xv[8], o[8];
+    Vec8<T>::load(xb + idx * 8, xv);
+    const float4 sc0 = *reinterpret_cast<const float4*>(s_scale + v * 8), sc1 = *reinterpret_cast<const float4*>(s_scale + v * 8 + 4);
+    const float4 sh0 = *reinterpret_cast<const float4*>(s_shift + v * 8), sh1 = *reinterpret_cast<const float4*>(s_shift + v * 8 + 4);
+    const float sc[8] = {sc0.x, sc0.y, sc0.z, sc0.w, sc1.x, sc1.y, sc1.z, sc1.w};
+    const float sh[8] = {sh0.x, sh0.y, sh0.z, sh0.w, sh1.x, sh1.y, sh1.z, sh1.w};
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      float u = fmaf(xv[k], sc[k], sh[k]);
+      if (p.silu) u = u / (1.f + __expf(-u));
+      o[k] = u;
+    }
+    Vec8<T>::store(yb + idx * 8, o);
+    v += dv;
+    if (v >= p.NV) v -= p.NV;
+  }
+}
+
+template <typename T>
+static int groupnorm_impl(void* y, const void* x, const void* chan_add, const void* gamma, const void* beta,
+                          float* ws, GnParams p, cudaStream_t st) {
+  // workspace layout: tickets [64] (zero on entry, left zero) | stats [B][G][2] | partial [B][chunks][G][2]
+  unsigned* ticket = reinterpret_cast<unsigned*>(ws);
+  float* stats = ws + GN_TICKETS;
+  float* partial = stats + (size_t)p.B * p.G * 2;
+  {
+    dim3 grid(p.chunks, p.B);
+    const size_t smem = (size_t)p.PL * p.C * 2 * sizeof(float);
+    int threads = p.PL * p.NV > p.G ? p.PL * p.NV : p.G;
+    threads = (threads + 31) / 32 * 32;
+    gn_stats_kernel<T><<<grid, threads, smem, st>>>(
+        (const T*)x, (const T*)chan_add, partial, stats, ticket, p);
+    int rc = post_launch("gn_stats_kernel");
+    if (rc) return rc;
+  }
+  {
+    int chunks = (sm_count() * 4 + p.B - 1) / p.B;
+    int ppc = (p.HW + chunks - 1) / chunks;
+    if (ppc < 4) ppc = 4;
+    chunks = (p.HW + ppc - 1) / ppc;
+    dim3 grid(chunks, p.B);
+    gn_apply_kernel<T><<<grid, 256, (size_t)p.C * 2 * sizeof(float), st>>>(
+        (T*)y, (const T*)x, (const T*)chan_add, (const T*)gamma, (const T*)beta, stats, p, chunks, ppc);
+  }
+  return post_launch("gn_apply_kernel");
+}
+
+static int gn_plan(GnParams* p, int B, int HW, int C, int G, float eps, int silu) {
+  SLIDER_CHECK_ARG(B > 0 && HW > 0 && C > 0 && G > 0 && C % G == 0, "groupnorm: bad shape B %d HW %d C %d G %d", B, HW, C, G);
+  SLIDER_CHECK_ARG(C % 8 == 0 && C <= 4096, "groupnorm: channels must be a multiple of 8 and <= 4096 (got %d)", C);
+  SLIDER_CHECK_ARG(G <= GN_MAX_THREADS, "groupnorm: too many groups (%d)", G);
+  p->B = B; p->HW = HW; p->C = C; p->G = G; p->cpg = C / G; p->eps = eps; p->silu = silu;
+  p->NV = C / 8;
+  p->PL = GN_MAX_THREADS / p->NV;
+  if (p->PL < 1) p->PL = 1;
+  if (p->PL > HW) p->PL = HW;
+  int chunks = (sm_count() * 2 + B - 1) / B;
+  int ppc = (HW + chunks - 1) / chunks;
+  if (ppc < p->PL) ppc = p->PL;
+  chunks = (HW + ppc - 1) / ppc;
+  p->chunks = chunks; p->ppc = ppc;
+  return SLIDER_OK;
+}
+
+}  // namespace slider
+
+using namespace slider;
+
+extern "C" {
+
+size_t slider_groupnorm_workspace_bytes(int batch, int groups) {
+  // tickets + stats + partials (batch * chunks <= 2 * SMs + 2 * batch)
+  return ((size_t)GN_TICKETS + (size_t)batch * groups * 2 +
+          ((size_t)sm_count() * 2 + 2 * (size_t)batch) * groups * 2) * sizeof(float);
+}
+
+int slider_groupnorm_nhwc(void* y, const void* x, const void* chan_add, const void* gamma, const void* beta,
+                          int batch, int hw, int channels, int groups, float eps, int silu, int dtype, void* ws,
+                          size_t ws_bytes, void* stream) {
+  SLIDER_CHECK_ARG(y && x && ws, "groupnorm: null pointer");
+  SLIDER_CHECK_ARG((((uintptr_t)y | (uintptr_t)x | (uintptr_t)chan_add | (uintptr_t)ws) & 15) == 0,
+                   "groupnorm: pointers must be 16-byte aligned");
+  GnParams p;
+  int rc = gn_plan(&p, batch, hw, channels, groups, eps, silu);
+  if (rc) return rc;
+  SLIDER_CHECK_ARG(p.NV <= GN_MAX_THREADS, "groupnorm: channels %d exceed the kernel's 4096 limit", channels);
+  SLIDER_CHECK_ARG(batch <= GN_TICKETS, "groupnorm: batch %d > %d", batch, GN_TICKETS);
+  const size_t need = ((size_t)GN_TICKETS + (size_t)batch * groups * 2 + (size_t)batch * p.chunks * groups * 2) * sizeof(float);
+  if (ws_bytes < need) {
+    set_error("groupnorm: workspace %zu < %zu bytes", ws_bytes, need);
+    return SLIDER_ERR_WORKSPACE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == SLIDER_BF16) return groupnorm_impl<__nv_bfloat16>(y, x, chan_add, gamma, beta, (float*)ws, p, st);
+  if (dtype == SLIDER_F32) return groupnorm_impl<float>(y, x, chan_add, gamma, beta, (float*)ws, p, st);
+  set_error("groupnorm: unsupported dtype %d", dtype);
+  return SLIDER_ERR_UNSUPPORTED;
+}
+
+}  // extern "C"

@@ -131,6 +131,33 @@ def scale_by_device_scalar(x: torch.Tensor, scalar: torch.Tensor) -> torch.Tenso
     return x
 
 
+_gn_ws: dict[int, torch.Tensor] = {}
+
+
+def groupnorm_nhwc(x: torch.Tensor, groups: int, gamma: torch.Tensor | None, beta: torch.Tensor | None,
+                   eps: float = 1e-5, silu: bool = False, chan_add: torch.Tensor | None = None) -> torch.Tensor:
+    """y = act(GroupNorm(x + chan_add[:, None, :])) on NHWC data.  x [B, ..., C] contiguous (C innermost),
+    chan_add [B, C] (the time-embedding projection of ResnetBlock2D) or None."""
+    require_cuda(x, gamma, beta, chan_add)
+    assert x.is_contiguous()
+    B, Cc = x.shape[0], x.shape[-1]
+    hw = x.numel() // (B * Cc)
+    key = x.device.index if x.device.index is not None else torch.cuda.current_device()
+    need = lib().slider_groupnorm_workspace_bytes(int(B), int(groups))
+    ws = _gn_ws.get(key)
+    if ws is None or ws.numel() < need:
+        ws = torch.zeros(max(need, 1 << 20), dtype=torch.uint8, device=x.device)
+        _gn_ws[key] = ws
+    if chan_add is not None:
+        chan_add = chan_add.contiguous()
+        assert chan_add.shape == (B, Cc) and chan_add.dtype == x.dtype
+    y = torch.empty_like(x)
+    check(lib().slider_groupnorm_nhwc(ptr(y), ptr(x), ptr(chan_add), ptr(gamma), ptr(beta), int(B), int(hw), int(Cc),
+                                      int(groups), float(eps), int(bool(silu)), dtype_code(x.dtype), ptr(ws),
+                                      ws.numel(), stream_ptr()))
+    return y
+
+
 def launch_count() -> int:
     return int(lib().slider_launch_count())
 

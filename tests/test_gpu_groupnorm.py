@@ -1,0 +1,37 @@
+"""GPU parity of the NHWC GroupNorm(+pre-add, +SiLU) kernels against torch.nn.functional.group_norm in fp32."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+CASES = [  # B, H, W, C, G
+    (2, 64, 64, 320, 32), (2, 32, 32, 640, 32), (2, 16, 16, 1280, 32), (2, 8, 8, 2560, 32), (2, 16, 16, 1920, 32),
+    (6, 32, 32, 960, 32), (1, 16, 16, 32, 8), (3, 5, 7, 64, 8), (2, 128, 128, 320, 32),
+]
+
+
+@pytest.mark.parametrize("case", CASES)
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("silu,with_add", [(True, False), (True, True), (False, False)])
+def test_groupnorm_nhwc_matches_torch(case, dtype, silu, with_add):
+    from sliders_conceptmod_b200 import ops
+    B, H, W, C, G = case
+    gen = torch.Generator(device="cuda").manual_seed(7)
+    x = (torch.randn(B, H, W, C, device="cuda", generator=gen) * 1.7 + 0.3).to(dtype)
+    gamma = (1 + 0.2 * torch.randn(C, device="cuda", generator=gen)).to(dtype)
+    beta = (0.1 * torch.randn(C, device="cuda", generator=gen)).to(dtype)
+    add = torch.randn(B, C, device="cuda", generator=gen).to(dtype) if with_add else None
+    for _ in range(2):      # twice: the ticket words must be left re-armed
+        y = ops.groupnorm_nhwc(x, G, gamma, beta, 1e-5, silu, add)
+    torch.cuda.synchronize()
+    xr = x.float().permute(0, 3, 1, 2)
+    if add is not None:
+        xr = xr + add.float()[:, :, None, None]
+    yr = F.group_norm(xr, G, gamma.float(), beta.float(), 1e-5)
+    if silu:
+        yr = F.silu(yr)
+    yr = yr.permute(0, 2, 3, 1)
+    err = (y.float() - yr).abs().max().item()
+    tol = 3e-2 if dtype == torch.bfloat16 else 2e-5
+    assert err <= tol * max(1.0, yr.abs().max().item()), f"max-abs {err}"
