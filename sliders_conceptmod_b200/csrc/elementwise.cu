@@ -160,24 +160,56 @@ scale_by_scalar_kernel(T* __restrict__ x, const float* __restrict__ sc, int64_t 
 }
 
 // ---- flat AdamW ----------------------------------------------------------------
+__device__ __forceinline__ float adamw_one(float& pi, float g, float& mi, float& vi, float b1, float b2, float eps,
+                                           float decay, float step, float rsqrt_bc2) {
+  mi = fmaf(b1, mi, (1.f - b1) * g);
+  vi = fmaf(b2, vi, (1.f - b2) * g * g);
+  pi *= decay;
+  pi -= step * (mi / (sqrtf(vi) * rsqrt_bc2 + eps));
+  return pi;
+}
+
+// 4 elements per thread: 16-byte accesses to grad / m / v (fp32) and 8- or 16-byte accesses to p.
 template <typename T>
 __global__ void __launch_bounds__(kThreads)
 adamw_flat_kernel(T* __restrict__ p, const float* __restrict__ grad, float* __restrict__ m,
                   float* __restrict__ v, int64_t n_elem, float lr, float b1, float b2, float eps,
                   float wd, float bc1, float rsqrt_bc2, const float* __restrict__ gs_dev) {
   const float gs = gs_dev ? __ldg(gs_dev) : 1.f;
-  const float step = lr / bc1;
-  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n_elem;
-       i += (int64_t)gridDim.x * kThreads) {
-    float g = grad[i] * gs;
-    float pi = Elem<T>::to_f(p[i]);
-    float mi = fmaf(b1, m[i], (1.f - b1) * g);
-    float vi = fmaf(b2, v[i], (1.f - b2) * g * g);
-    m[i] = mi; v[i] = vi;
-    pi *= (1.f - lr * wd);
-    float denom = sqrtf(vi) * rsqrt_bc2 + eps;
-    pi -= step * (mi / denom);
-    p[i] = Elem<T>::from_f(pi);
+  const float step = lr / bc1, decay = 1.f - lr * wd;
+  const int64_t n4 = n_elem / 4;
+  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n4; i += (int64_t)gridDim.x * kThreads) {
+    const float4 g4 = __ldcs(reinterpret_cast<const float4*>(grad) + i);
+    float4 m4 = reinterpret_cast<float4*>(m)[i], v4 = reinterpret_cast<float4*>(v)[i];
+    float pv[4];
+    if (sizeof(T) == 2) {
+      const uint2 t = reinterpret_cast<const uint2*>(p)[i];
+      pv[0] = __uint_as_float(t.x << 16); pv[1] = __uint_as_float(t.x & 0xffff0000u);
+      pv[2] = __uint_as_float(t.y << 16); pv[3] = __uint_as_float(t.y & 0xffff0000u);
+    } else {
+      const float4 t = reinterpret_cast<const float4*>(p)[i];
+      pv[0] = t.x; pv[1] = t.y; pv[2] = t.z; pv[3] = t.w;
+    }
+    adamw_one(pv[0], g4.x * gs, m4.x, v4.x, b1, b2, eps, decay, step, rsqrt_bc2);
+    adamw_one(pv[1], g4.y * gs, m4.y, v4.y, b1, b2, eps, decay, step, rsqrt_bc2);
+    adamw_one(pv[2], g4.z * gs, m4.z, v4.z, b1, b2, eps, decay, step, rsqrt_bc2);
+    adamw_one(pv[3], g4.w * gs, m4.w, v4.w, b1, b2, eps, decay, step, rsqrt_bc2);
+    reinterpret_cast<float4*>(m)[i] = m4;
+    reinterpret_cast<float4*>(v)[i] = v4;
+    if (sizeof(T) == 2) {
+      __nv_bfloat162 lo = __floats2bfloat162_rn(pv[0], pv[1]), hi = __floats2bfloat162_rn(pv[2], pv[3]);
+      reinterpret_cast<uint2*>(p)[i] = make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
+    } else {
+      reinterpret_cast<float4*>(p)[i] = make_float4(pv[0], pv[1], pv[2], pv[3]);
+    }
+  }
+  if (blockIdx.x == 0) {
+    for (int64_t i = n4 * 4 + threadIdx.x; i < n_elem; i += kThreads) {
+      float pi = Elem<T>::to_f(p[i]), mi = m[i], vi = v[i];
+      adamw_one(pi, grad[i] * gs, mi, vi, b1, b2, eps, decay, step, rsqrt_bc2);
+      m[i] = mi; v[i] = vi;
+      p[i] = Elem<T>::from_f(pi);
+    }
   }
 }
 
@@ -271,10 +303,11 @@ int slider_adamw_flat(void* p, const float* grad, float* m, float* v, int64_t n_
                       float beta2, float eps, float weight_decay, int step, const float* grad_scale_dev,
                       int dtype, void* stream) {
   SLIDER_CHECK_ARG(p && grad && m && v && n_elem > 0 && step >= 1, "adamw_flat: bad argument");
+  SLIDER_CHECK_ARG(aligned16(p) && aligned16(grad) && aligned16(m) && aligned16(v), "adamw_flat: buffers must be 16-byte aligned");
   cudaStream_t st = (cudaStream_t)stream;
   const float bc1 = 1.f - powf(beta1, (float)step);
   const float rsqrt_bc2 = 1.f / sqrtf(1.f - powf(beta2, (float)step));
-  const int grid = grid_for(n_elem, 4);
+  const int grid = grid_for(n_elem / 4 + 1, 2);
   if (dtype == SLIDER_F32)
     adamw_flat_kernel<float><<<grid, kThreads, 0, st>>>((float*)p, grad, m, v, n_elem, lr, beta1, beta2, eps,
                                                         weight_decay, bc1, rsqrt_bc2, grad_scale_dev);

@@ -1,5 +1,5 @@
-// Low-rank side of the backward pass (SIMT, bandwidth-class work):
-//   rowdot    dh[p, j]     = s * sum_n gy[p, n] * B[n, j]                (warp per pixel)
+// Low-rank side of the backward pass (bandwidth-class work):
+//   dh[p, j]  = s * sum_n gy[p, n] * B[n, j]      tensor cores: the forward GEMM kernel on gy x (s B)^T
 //   colreduce dB[n, j]     = s * sum_p gy[p, n] * h[p, j]
 //             dA[j, t, c]  =     sum_p x[p + d(t), c] * dh[p, j]
 //   pack_at / pack_wt      operand re-layouts for the input-gradient GEMM.
@@ -8,130 +8,153 @@
 
 namespace slider {
 
-// ------------------------------------------------------------------ rowdot
-template <typename T, int R4>
-__global__ void __launch_bounds__(256)
-rowdot_kernel(T* __restrict__ dh, const T* __restrict__ gy, const T* __restrict__ Bup, int64_t M, int N,
-              int rank, float s) {
-  constexpr int V = Elem<T>::kVec;
-  constexpr int RP = 4 * R4;
-  const int lane = threadIdx.x & 31;
-  const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
-  if (row >= M) return;
-  float acc[RP];
-#pragma unroll
-  for (int j = 0; j < RP; ++j) acc[j] = 0.f;
-  const T* grow = gy + row * (int64_t)N;
-  for (int n = lane * V; n < N; n += 32 * V) {
-    float gv[V];
-    Elem<T>::load(grow + n, gv);
-#pragma unroll
-    for (int k = 0; k < V; ++k) {
-      const T* b = Bup + (int64_t)(n + k) * rank;
-#pragma unroll
-      for (int j = 0; j < RP; ++j)
-        if (j < rank) acc[j] = fmaf(gv[k], Elem<T>::to_f(b[j]), acc[j]);
-    }
-  }
-  float mine = 0.f;
-#pragma unroll
-  for (int j = 0; j < RP; ++j) {
-    const float t = warp_sum(acc[j]);
-    if (lane == j) mine = t * s;
-  }
-  if (lane < 16) dh[row * 16 + lane] = Elem<T>::from_f(lane < rank ? mine : 0.f);
+// --------------------------------------------------------------- pack_bt
+// Bt[j][n] = s * B[n][j] (j < rank, else 0): the [16, N] K-major weight of the dh = gy . (s B) GEMM.
+template <typename T>
+__global__ void pack_bt_kernel(T* __restrict__ Bt, const T* __restrict__ Bup, int N, int rank, float s) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 16 * N) return;
+  const int j = i / N, n = i - j * N;
+  Bt[i] = j < rank ? Elem<T>::from_f(s * Elem<T>::to_f(Bup[(size_t)n * rank + j])) : Elem<T>::from_f(0.f);
 }
 
 // --------------------------------------------------------------- colreduce
-// out[c, j, t] (generic strides) (+)= scale * sum_p X[p + d(t), c] * v[p, j]
-// Each thread owns 2 adjacent channels; 64 channel pairs x 4 row lanes per CTA.
+// out[c, j, t] (generic strides) += scale * sum_p X[p + d(t), c] * V[p, j0 + j],  j = 0..3
+// HBM-bound on X (gy for dB, x for dA), which is read exactly once with vector loads:
+//   * a thread owns CH adjacent channels (16-byte loads for 1x1, 8/16-byte for 3x3) and keeps
+//     TAPS x CH x 4 fp32 accumulators; PL pixel lanes share a CTA;
+//   * the V rows (h fp32 / dh) of the CTA's pixel range (+ halo for 3x3) are staged once in shared memory
+//     as float4, so the inner loop is one broadcast LDS.128 per tap;
+//   * lanes are reduced through shared memory, then one fp32 atomicAdd per output element and CTA.
 struct ColReduceParams {
   int B, H, W, C;        // X is [B,H,W,C]
-  int taps, kw, pad;
-  int rank, vstride;     // v is [pixels, vstride]
-  int rows_per_cta;
+  int kw, pad;
+  int rank, vstride;     // V is [pixels, vstride]
+  int NVT;               // channel-vector threads per pixel lane (covering CB = NVT*CH channels per block)
+  int PL;                // pixel lanes
+  int cpi;               // chunks per image
+  int ppc;               // pixels per chunk
   int64_t oc, oj, ot;    // output strides for (channel, rank index, tap)
   float scale;
 };
 
-template <typename T, typename VT, int TAPS>
-__global__ void __launch_bounds__(256)
-colreduce_kernel(float* __restrict__ out, const T* __restrict__ X, const VT* __restrict__ v,
+template <typename T, int CH> struct ChanVec;
+template <> struct ChanVec<__nv_bfloat16, 8> {
+  __device__ static inline void load(const __nv_bfloat16* p, float (&v)[8]) { Elem<__nv_bfloat16>::load(p, v); }
+};
+template <> struct ChanVec<__nv_bfloat16, 4> {
+  __device__ static inline void load(const __nv_bfloat16* p, float (&v)[4]) {
+    const uint2 t = *reinterpret_cast<const uint2*>(p);
+    v[0] = __uint_as_float(t.x << 16); v[1] = __uint_as_float(t.x & 0xffff0000u);
+    v[2] = __uint_as_float(t.y << 16); v[3] = __uint_as_float(t.y & 0xffff0000u);
+  }
+};
+template <> struct ChanVec<float, 8> {
+  __device__ static inline void load(const float* p, float (&v)[8]) {
+    const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+  }
+};
+template <> struct ChanVec<float, 4> {
+  __device__ static inline void load(const float* p, float (&v)[4]) {
+    const float4 a = *reinterpret_cast<const float4*>(p);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+  }
+};
+
+template <typename T, typename VT, int TAPS, int CH>
+__global__ void __launch_bounds__(TAPS == 1 ? 512 : 256)
+colreduce_kernel(float* __restrict__ out, const T* __restrict__ X, const VT* __restrict__ V,
                  const ColReduceParams p, int j0) {
-  const int cp = threadIdx.x & 63;   // channel pair within the CTA
-  const int rl = threadIdx.x >> 6;   // row lane 0..3
-  const int c = (blockIdx.x * 64 + cp) * 2;
-  const int64_t P = (int64_t)p.B * p.H * p.W;
-  const int64_t r0 = (int64_t)blockIdx.y * p.rows_per_cta;
-  int64_t r1 = r0 + p.rows_per_cta;
-  if (r1 > P) r1 = P;
-  const bool c_ok = c < p.C;
-  float acc[TAPS][2][4];
+  extern __shared__ __align__(16) float cr_smem[];
+  const int HW = p.H * p.W;
+  const int img = blockIdx.x / p.cpi, chunk = blockIdx.x - img * p.cpi;
+  const int q0 = chunk * p.ppc;
+  const int q1 = min(HW, q0 + p.ppc);
+  const int halo = TAPS > 1 ? p.pad * (p.W + 1) : 0;
+  const int v0 = max(0, q0 - halo), v1 = min(HW, q1 + halo);   // V pixels staged: [v0, v1) of image img
+  float4* s_v = reinterpret_cast<float4*>(cr_smem);
+  for (int i = threadIdx.x; i < v1 - v0; i += blockDim.x) {
+    const VT* vp = V + ((size_t)img * HW + v0 + i) * p.vstride + j0;
+    float4 f;
+    f.x = Elem<VT>::to_f(vp[0]);
+    f.y = (j0 + 1 < p.rank) ? Elem<VT>::to_f(vp[1]) : 0.f;
+    f.z = (j0 + 2 < p.rank) ? Elem<VT>::to_f(vp[2]) : 0.f;
+    f.w = (j0 + 3 < p.rank) ? Elem<VT>::to_f(vp[3]) : 0.f;
+    s_v[i] = f;
+  }
+  __syncthreads();
+  const int pl = threadIdx.x / p.NVT, v = threadIdx.x - pl * p.NVT;
+  const int c = (blockIdx.y * p.NVT + v) * CH;
+  const bool active = pl < p.PL && c < p.C;
+  float acc[TAPS][CH][4];
 #pragma unroll
   for (int t = 0; t < TAPS; ++t)
 #pragma unroll
-    for (int k = 0; k < 2; ++k)
+    for (int k = 0; k < CH; ++k)
 #pragma unroll
       for (int j = 0; j < 4; ++j) acc[t][k][j] = 0.f;
-
-  for (int64_t q = r0 + rl; q < r1; q += 4) {
-    float x0 = 0.f, x1 = 0.f;
-    if (c_ok) {
-      x0 = Elem<T>::to_f(X[q * p.C + c]);
-      x1 = Elem<T>::to_f(X[q * p.C + c + 1]);
-    }
-    int w = 0, h = 0, b = 0;
-    if (TAPS > 1) {
-      w = (int)(q % p.W);
-      const int64_t t2 = q / p.W;
-      h = (int)(t2 % p.H);
-      b = (int)(t2 / p.H);
-    }
+  if (active) {
+    const T* xb = X + ((size_t)img * HW) * p.C + c;
+    // software pipeline: the X vectors of the next two pixels are in flight while this one is consumed
+    float xn0[CH], xn1[CH];
+    int q = q0 + pl;
+    if (q < q1) ChanVec<T, CH>::load(xb + (size_t)q * p.C, xn0);
+    if (q + p.PL < q1) ChanVec<T, CH>::load(xb + (size_t)(q + p.PL) * p.C, xn1);
+    for (; q < q1; q += p.PL) {
+      float xv[CH];
 #pragma unroll
-    for (int t = 0; t < TAPS; ++t) {
-      int64_t pv = q;
-      bool ok = true;
-      if (TAPS > 1) {
-        // x[q] meets dh[p] where q = p + d(t)  =>  p = q - d(t)
-        const int ph = h - (t / p.kw - p.pad), pw = w - (t % p.kw - p.pad);
-        ok = ph >= 0 && ph < p.H && pw >= 0 && pw < p.W;
-        pv = ((int64_t)b * p.H + ph) * p.W + pw;
-      }
-      if (ok) {
-        const VT* vp = v + pv * p.vstride + j0;
+      for (int k = 0; k < CH; ++k) { xv[k] = xn0[k]; xn0[k] = xn1[k]; }
+      if (q + 2 * p.PL < q1) ChanVec<T, CH>::load(xb + (size_t)(q + 2 * p.PL) * p.C, xn1);
+      if (TAPS == 1) {
+        const float4 f = s_v[q - v0];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          if (j0 + j < p.rank) {
-            const float vv = Elem<VT>::to_f(vp[j]);
-            acc[t][0][j] = fmaf(x0, vv, acc[t][0][j]);
-            acc[t][1][j] = fmaf(x1, vv, acc[t][1][j]);
+        for (int k = 0; k < CH; ++k) {
+          acc[0][k][0] = fmaf(xv[k], f.x, acc[0][k][0]);
+          acc[0][k][1] = fmaf(xv[k], f.y, acc[0][k][1]);
+          acc[0][k][2] = fmaf(xv[k], f.z, acc[0][k][2]);
+          acc[0][k][3] = fmaf(xv[k], f.w, acc[0][k][3]);
+        }
+      } else {
+        const int h = q / p.W, w = q - h * p.W;
+#pragma unroll
+        for (int t = 0; t < TAPS; ++t) {
+          // x[q] meets dh[pv] where q = pv + d(t)  =>  pv = q - d(t)
+          const int ph = h - (t / 3 - p.pad), pw = w - (t % 3 - p.pad);
+          if (ph >= 0 && ph < p.H && pw >= 0 && pw < p.W) {
+            const float4 f = s_v[ph * p.W + pw - v0];
+#pragma unroll
+            for (int k = 0; k < CH; ++k) {
+              acc[t][k][0] = fmaf(xv[k], f.x, acc[t][k][0]);
+              acc[t][k][1] = fmaf(xv[k], f.y, acc[t][k][1]);
+              acc[t][k][2] = fmaf(xv[k], f.z, acc[t][k][2]);
+              acc[t][k][3] = fmaf(xv[k], f.w, acc[t][k][3]);
+            }
           }
         }
       }
     }
   }
-  // reduce the 4 row lanes through shared memory, then one atomic per output element
-  __shared__ float red[4][64][2 * 4 + 1];
+  // cross-lane reduction tap by tap through shared memory (re-using the V staging area), then atomics
+  float* s_red = cr_smem;     // [PL][NVT*CH*4]
+  const int row = p.NVT * CH * 4;
 #pragma unroll
   for (int t = 0; t < TAPS; ++t) {
     __syncthreads();
+    if (pl < p.PL) {
 #pragma unroll
-    for (int k = 0; k < 2; ++k)
-#pragma unroll
-      for (int j = 0; j < 4; ++j) red[rl][cp][k * 4 + j] = acc[t][k][j];
+      for (int k = 0; k < CH; ++k)
+        *reinterpret_cast<float4*>(s_red + pl * row + (v * CH + k) * 4) =
+            make_float4(acc[t][k][0], acc[t][k][1], acc[t][k][2], acc[t][k][3]);
+    }
     __syncthreads();
-    if (rl == 0 && c_ok) {
-#pragma unroll
-      for (int k = 0; k < 2; ++k)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          if (j0 + j < p.rank) {
-            const float sum = red[0][cp][k * 4 + j] + red[1][cp][k * 4 + j] + red[2][cp][k * 4 + j] +
-                              red[3][cp][k * 4 + j];
-            atomicAdd(out + (int64_t)(c + k) * p.oc + (int64_t)(j0 + j) * p.oj + (int64_t)t * p.ot,
-                      sum * p.scale);
-          }
-        }
+    for (int i = threadIdx.x; i < row; i += blockDim.x) {
+      const int cc = blockIdx.y * p.NVT * CH + i / 4, j = i & 3;
+      if (cc < p.C && j0 + j < p.rank) {
+        float sum = 0.f;
+        for (int l = 0; l < p.PL; ++l) sum += s_red[l * row + i];
+        atomicAdd(out + (int64_t)cc * p.oc + (int64_t)(j0 + j) * p.oj + (int64_t)t * p.ot, sum * p.scale);
+      }
     }
   }
 }
@@ -165,48 +188,82 @@ __global__ void pack_wt_kernel(T* __restrict__ Wt, const T* __restrict__ W, int 
 }
 
 template <typename T, typename VT>
-static int launch_colreduce(float* out, const T* X, const VT* v, ColReduceParams p, cudaStream_t st) {
-  const int64_t P = (int64_t)p.B * p.H * p.W;
-  const int gx = (p.C + 127) / 128;
-  int64_t want = ((int64_t)sm_count() * 4 + gx - 1) / gx;
-  int64_t rows = (P + want - 1) / want;
-  if (rows < 32) rows = 32;
-  rows = (rows + 3) / 4 * 4;
-  p.rows_per_cta = (int)rows;
-  const int gy = (int)((P + rows - 1) / rows);
-  dim3 grid(gx, gy);
+static int launch_colreduce(float* out, const T* X, const VT* v, ColReduceParams p, int taps, cudaStream_t st) {
+  const int CH = taps == 1 ? 8 : 4;
+  const int HW = p.H * p.W;
+  const int max_threads = taps == 1 ? 512 : 256;   // 3x3 keeps 144 accumulators per thread
+  int nvt_all = (p.C + CH - 1) / CH;
+  int cblocks = (nvt_all + max_threads - 1) / max_threads;
+  p.NVT = (nvt_all + cblocks - 1) / cblocks;
+  p.PL = max_threads / p.NVT;
+  if (p.PL < 1) p.PL = 1;
+  // pixel chunks: ~2 CTAs per SM over (images x chunks x channel blocks); chunks never straddle images
+  int want = (sm_count() * 2) / (p.B * cblocks);
+  if (want < 1) want = 1;
+  int ppc = (HW + want - 1) / want;
+  if (ppc < p.PL * 2) ppc = p.PL * 2;
+  if (ppc > HW) ppc = HW;
+  p.ppc = ppc;
+  p.cpi = (HW + ppc - 1) / ppc;
+  const int halo = taps > 1 ? p.pad * (p.W + 1) : 0;
+  size_t smem_v = (size_t)(ppc + 2 * halo) * sizeof(float4);
+  size_t smem_r = (size_t)p.PL * p.NVT * CH * 4 * sizeof(float);
+  size_t smem = smem_v > smem_r ? smem_v : smem_r;
+  if (smem > 200 * 1024) { set_error("colreduce: shared memory %zu too large", smem); return SLIDER_ERR_UNSUPPORTED; }
+  int threads = p.PL * p.NVT;
+  threads = (threads + 31) / 32 * 32;
+  dim3 grid(p.B * p.cpi, cblocks);
   for (int j0 = 0; j0 < p.rank; j0 += 4) {
-    if (p.taps == 1) colreduce_kernel<T, VT, 1><<<grid, 256, 0, st>>>(out, X, v, p, j0);
-    else colreduce_kernel<T, VT, 9><<<grid, 256, 0, st>>>(out, X, v, p, j0);
+    if (taps == 1) {
+      auto k = colreduce_kernel<T, VT, 1, 8>;
+      if (smem > 48 * 1024) SLIDER_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      k<<<grid, threads, smem, st>>>(out, X, v, p, j0);
+    } else {
+      auto k = colreduce_kernel<T, VT, 9, 4>;
+      if (smem > 48 * 1024) SLIDER_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      k<<<grid, threads, smem, st>>>(out, X, v, p, j0);
+    }
     int rc = post_launch("colreduce_kernel");
     if (rc) return rc;
   }
   return SLIDER_OK;
 }
 
+int run_gemm_plain(const slider_layer_geom* g, int kc, int nn, void* y, const void* act, const void* wgt, void* ws,
+                   size_t ws_bytes, cudaStream_t st);   // lora_gemm.cu
+
 template <typename T>
 static int lora_grad_impl(const slider_layer_geom* g, float* dA, float* dB, T* dh, const T* gy, const T* x,
-                          const float* h, const T* Bup, float s, int accumulate, cudaStream_t st) {
+                          const float* h, const T* Bup, float s, int accumulate, void* ws, size_t ws_bytes,
+                          cudaStream_t st) {
   const int taps = g->kh * g->kw;
-  const int64_t M = (int64_t)g->batch * g->height * g->width;
   if (!accumulate) {
     SLIDER_CUDA(cudaMemsetAsync(dA, 0, sizeof(float) * (size_t)g->rank * taps * g->cin, st));
     SLIDER_CUDA(cudaMemsetAsync(dB, 0, sizeof(float) * (size_t)g->cout * g->rank, st));
   }
-  const int grid = (int)((M + 7) / 8);
-  if (g->rank <= 4) rowdot_kernel<T, 1><<<grid, 256, 0, st>>>(dh, gy, Bup, M, g->cout, g->rank, s);
-  else if (g->rank <= 8) rowdot_kernel<T, 2><<<grid, 256, 0, st>>>(dh, gy, Bup, M, g->cout, g->rank, s);
-  else rowdot_kernel<T, 4><<<grid, 256, 0, st>>>(dh, gy, Bup, M, g->cout, g->rank, s);
-  int rc = post_launch("rowdot_kernel");
+  // dh = gy . (s B): a [pixels, Cout] x [Cout, 16] contraction on the tensor cores (same tcgen05 kernel
+  // as the forward, 1x1, no adapter), output already in the zero-padded [pixels, 16] layout.
+  const size_t bt_bytes = (((size_t)16 * g->cout * sizeof(T)) + 255) & ~(size_t)255;
+  if (ws == nullptr || ws_bytes < bt_bytes) {
+    set_error("lora_grad: workspace %zu < %zu bytes", ws_bytes, bt_bytes);
+    return SLIDER_ERR_WORKSPACE;
+  }
+  T* Bt = reinterpret_cast<T*>(ws);
+  pack_bt_kernel<T><<<(16 * g->cout + 255) / 256, 256, 0, st>>>(Bt, Bup, g->cout, g->rank, s);
+  int rc = post_launch("pack_bt_kernel");
+  if (rc) return rc;
+  slider_layer_geom g1 = *g;
+  g1.kh = g1.kw = 1; g1.pad = 0; g1.rank = 0; g1.cin = g->cout; g1.cout = 16;
+  rc = run_gemm_plain(&g1, g->cout, 16, dh, gy, Bt, reinterpret_cast<uint8_t*>(ws) + bt_bytes, ws_bytes - bt_bytes, st);
   if (rc) return rc;
   ColReduceParams pb;
-  pb.B = 1; pb.H = 1; pb.W = (int)M; pb.C = g->cout; pb.taps = 1; pb.kw = 1; pb.pad = 0;
+  pb.B = g->batch; pb.H = g->height; pb.W = g->width; pb.C = g->cout; pb.kw = 1; pb.pad = 0;
   pb.rank = g->rank; pb.vstride = g->rank; pb.oc = g->rank; pb.oj = 1; pb.ot = 0; pb.scale = s;
-  if ((rc = launch_colreduce<T, float>(dB, gy, h, pb, st))) return rc;
+  if ((rc = launch_colreduce<T, float>(dB, gy, h, pb, 1, st))) return rc;
   ColReduceParams pa;
-  pa.B = g->batch; pa.H = g->height; pa.W = g->width; pa.C = g->cin; pa.taps = taps; pa.kw = g->kw; pa.pad = g->pad;
+  pa.B = g->batch; pa.H = g->height; pa.W = g->width; pa.C = g->cin; pa.kw = g->kw; pa.pad = g->pad;
   pa.rank = g->rank; pa.vstride = 16; pa.oc = 1; pa.oj = (int64_t)taps * g->cin; pa.ot = g->cin; pa.scale = 1.f;
-  return launch_colreduce<T, T>(dA, x, dh, pa, st);
+  return launch_colreduce<T, T>(dA, x, dh, pa, taps, st);
 }
 
 }  // namespace slider
@@ -225,12 +282,14 @@ static int check_geom(const slider_layer_geom* g, const char* who) {
 
 extern "C" {
 
-size_t slider_lora_grad_workspace_bytes(const slider_layer_geom* g) { (void)g; return 0; }
+size_t slider_lora_grad_workspace_bytes(const slider_layer_geom* g) {
+  const size_t bt = g ? ((((size_t)16 * g->cout * 4) + 255) & ~(size_t)255) : 0;
+  return bt + slider_gemm_workspace_bytes();
+}
 
 int slider_lora_grad(const slider_layer_geom* g, float* dA, float* dB, void* dh_out, const void* gy, const void* x,
                      const float* h, const void* B, float s, int accumulate, void* ws, size_t ws_bytes,
                      void* stream) {
-  (void)ws; (void)ws_bytes;
   int rc = check_geom(g, "lora_grad");
   if (rc) return rc;
   SLIDER_CHECK_ARG(dA && dB && dh_out && gy && x && h && B, "lora_grad: null pointer");
@@ -238,9 +297,9 @@ int slider_lora_grad(const slider_layer_geom* g, float* dA, float* dB, void* dh_
   cudaStream_t st = (cudaStream_t)stream;
   if (g->dtype == SLIDER_BF16)
     return lora_grad_impl<__nv_bfloat16>(g, dA, dB, (__nv_bfloat16*)dh_out, (const __nv_bfloat16*)gy,
-                                         (const __nv_bfloat16*)x, h, (const __nv_bfloat16*)B, s, accumulate, st);
+                                         (const __nv_bfloat16*)x, h, (const __nv_bfloat16*)B, s, accumulate, ws, ws_bytes, st);
   return lora_grad_impl<float>(g, dA, dB, (float*)dh_out, (const float*)gy, (const float*)x, h, (const float*)B, s,
-                               accumulate, st);
+                               accumulate, ws, ws_bytes, st);
 }
 
 int slider_lora_pack_at(const slider_layer_geom* g, void* At, const void* A, void* stream) {

@@ -774,6 +774,11 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
   return launch_gemm<float>(r4, mA, mW, mL, mXe, mWe, mY, mP, p, st);
 }
 
+int run_gemm_plain(const slider_layer_geom* g, int kc, int nn, void* y, const void* act, const void* wgt, void* ws,
+                   size_t ws_bytes, cudaStream_t st) {
+  return run_gemm(g, kc, nn, y, act, wgt, nullptr, nullptr, nullptr, nullptr, 0.f, nullptr, nullptr, ws, ws_bytes, st);
+}
+
 }  // namespace slider
 
 using namespace slider;

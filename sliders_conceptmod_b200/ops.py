@@ -182,6 +182,18 @@ def pack_at(a: torch.Tensor, ksize: int = 1) -> torch.Tensor:
     return at
 
 
+_grad_ws: dict[int, torch.Tensor] = {}
+
+
+def _grad_workspace(device: torch.device, need: int) -> torch.Tensor:
+    key = device.index if device.index is not None else torch.cuda.current_device()
+    ws = _grad_ws.get(key)
+    if ws is None or ws.numel() < need:
+        ws = torch.empty(need + (1 << 20), dtype=torch.uint8, device=device)
+        _grad_ws[key] = ws
+    return ws
+
+
 def lora_grad(gy: torch.Tensor, x: torch.Tensor, h: torch.Tensor, b: torch.Tensor, s: float, ksize: int,
               dA: torch.Tensor, dB: torch.Tensor, accumulate: bool = False) -> torch.Tensor:
     """Low-rank backward (autograd of lora.py:134-138): fills dA [r,k*k,Cin], dB [Cout,r] (fp32) and
@@ -193,8 +205,9 @@ def lora_grad(gy: torch.Tensor, x: torch.Tensor, h: torch.Tensor, b: torch.Tenso
     rank = b.shape[1]
     g = make_geom(x.dtype, B, H, W, x.shape[-1], gy.shape[-1], ksize, rank)
     dh = torch.empty(B * H * W, 16, device=x.device, dtype=x.dtype)
+    ws = _grad_workspace(x.device, lib().slider_lora_grad_workspace_bytes(C.byref(g)))
     check(lib().slider_lora_grad(C.byref(g), ptr(dA), ptr(dB), ptr(dh), ptr(gy), ptr(x), ptr(h), ptr(b), float(s),
-                                 int(bool(accumulate)), None, 0, stream_ptr()))
+                                 int(bool(accumulate)), ptr(ws), ws.numel(), stream_ptr()))
     return dh
 
 
