@@ -152,6 +152,35 @@ def fused_gemm_roofline(engine, pk: dict, reps: int = 5) -> dict:
             "flops_per_forward": flops}
 
 
+def phase_breakdown(engine, reps: int = 5) -> dict:
+    """Device time of each captured phase of a step (CUDA events around graph replays): one adapter-on CFG denoise
+    forward (x timesteps_to per step), the batched adapter-off predictions, the grad forward+loss+backward, AdamW."""
+    out = {}
+    saved = engine.lat.clone()
+    for name in ("denoise", "predict", "train"):
+        g = engine._graphs.get(name)
+        if g is None:
+            continue
+        g.replay()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            g.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        out[name] = round(e0.elapsed_time(e1) / reps, 3)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        engine.optimizer_step()
+    e1.record()
+    torch.cuda.synchronize()
+    out["optimizer"] = round(e0.elapsed_time(e1) / reps, 3)
+    engine.lat.copy_(saved)
+    return out
+
+
 # --------------------------------------------------------------------------------- CPU arm (oracle port)
 def cpu_reference_sample(wl_name: str, threads: int):
     """Builds the reference's CPU path for the workload: the oracle arithmetic (oracle/slider_oracle.py) over the
@@ -295,6 +324,7 @@ def run_ours(args):
         return
     pk = peaks()
     roof = fused_gemm_roofline(engine, pk)
+    phases = phase_breakdown(engine) if (not args.no_graphs and world == 1) else None   # optimizer_step all-reduces
     value = world * args.steps / sec
     value_e2e = world * args.steps / sec_e2e
     lat_bytes = host_lat[0].numel() * host_lat.element_size()
@@ -309,7 +339,8 @@ def run_ours(args):
                        "l2": "working set (1.7 GB bf16 UNet weights) exceeds the 126 MB L2; no explicit flush"},
             "e2e": {"value": value_e2e, "unit": UNIT, "h2d_bytes_per_step": lat_bytes, "d2h_bytes_per_step": 4,
                     "ms_per_step": sec_e2e / args.steps * 1e3},
-            "gpu_launches": int(launches), "clocks": clk, "roofline": roof, "final_loss": final_loss}
+            "gpu_launches": int(launches), "clocks": clk, "roofline": roof, "final_loss": final_loss,
+            "phases_ms": phases}
     if not args.skip_cpu_baseline and world == 1:
         threads = os.cpu_count() or 1
         sample = cpu_reference_sample(args.workload, threads)

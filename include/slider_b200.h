@@ -184,6 +184,17 @@ int slider_groupnorm_nhwc(void* y, const void* x, const void* chan_add,
                           int channels, int groups, float eps, int silu, int dtype,
                           void* ws, size_t ws_bytes, void* stream);
 
+/*
+ * Row-wise kernels of the UNet's transformer blocks (diffusers BasicTransformerBlock):
+ *   slider_layernorm: y = (x - mean) * rstd * gamma + beta over the last dimension of x [rows, channels]
+ *                     (the producer of the LoRA-wrapped attn1.to_q/k/v inputs);
+ *   slider_geglu:     y[rows, d] = x[:, :d] * gelu(x[:, d:]), x [rows, 2d], exact (erf) GELU.
+ * channels and d must be multiples of 8; gamma / beta may be NULL.
+ */
+int slider_layernorm(void* y, const void* x, const void* gamma, const void* beta,
+                     int64_t rows, int channels, float eps, int dtype, void* stream);
+int slider_geglu(void* y, const void* x, int64_t rows, int d, int dtype, void* stream);
+
 /* x *= *dev_scalar  (chain rule for a non-unit upstream loss gradient). */
 int slider_scale_by_device_scalar(void* x, const float* dev_scalar,
                                   int64_t n_elem, int dtype, void* stream);

@@ -40,6 +40,8 @@ _SIGNATURES = {
     "slider_pack_wt": (C.c_int, [_G, _vp, _vp, _vp]),
     "slider_groupnorm_workspace_bytes": (_sz, [_i, _i]),
     "slider_groupnorm_nhwc": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _i, _i, _vp, _sz, _vp]),
+    "slider_layernorm": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i, _f, _i, _vp]),
+    "slider_geglu": (C.c_int, [_vp, _vp, _i64, _i, _i, _vp]),
     "slider_loss_workspace_bytes": (_sz, []),
     "slider_guidance_loss": (C.c_int, [_fp, _vp, _vp, _vp, _vp, _vp, _i64, _f, _i, _i, _vp, _sz, _vp]),
     "slider_cfg_step": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _f, _f, _f, _f, _fp, _i, _vp]),

@@ -78,14 +78,24 @@ gn_stats_kernel(const T* __restrict__ x, const T* __restrict__ chan_add, float* 
     }
   }
   __syncthreads();
-  if (tid < p.G) {
+  // per-group sums of this chunk: one warp per group (fixed lane -> element map, fixed shuffle tree)
+  const int warp = tid >> 5, lane = tid & 31, nwarps = blockDim.x >> 5;
+  const int per_group = p.PL * p.cpg;
+  for (int g = warp; g < p.G; g += nwarps) {
     float a = 0.f, q = 0.f;
-    for (int l = 0; l < p.PL; ++l)
-      for (int c = tid * p.cpg; c < (tid + 1) * p.cpg; ++c) { a += s_sum[l * p.C + c]; q += s_sq[l * p.C + c]; }
-    float* dst = partial + (((size_t)b * p.chunks + chunk) * p.G + tid) * 2;
-    dst[0] = a; dst[1] = q;
-    __threadfence();
+    for (int i = lane; i < per_group; i += 32) {
+      const int l = i / p.cpg, c = g * p.cpg + (i - l * p.cpg);
+      a += s_sum[l * p.C + c];
+      q += s_sq[l * p.C + c];
+    }
+    a = warp_sum(a);
+    q = warp_sum(q);
+    if (lane == 0) {
+      float* dst = partial + (((size_t)b * p.chunks + chunk) * p.G + g) * 2;
+      dst[0] = a; dst[1] = q;
+    }
   }
+  __threadfence();
   __syncthreads();
   if (tid == 0) {
     const unsigned t = atomicAdd(ticket + b, 1u);
@@ -94,19 +104,26 @@ gn_stats_kernel(const T* __restrict__ x, const T* __restrict__ chan_add, float* 
   __syncthreads();
   if (s_last) {
     __threadfence();
-    if (tid < p.G) {
+    for (int g = warp; g < p.G; g += nwarps) {
       double a = 0.0, q = 0.0;
-      for (int ch = 0; ch < p.chunks; ++ch) {
-        const float* src = partial + (((size_t)b * p.chunks + ch) * p.G + tid) * 2;
+      for (int ch = lane; ch < p.chunks; ch += 32) {
+        const float* src = partial + (((size_t)b * p.chunks + ch) * p.G + g) * 2;
         a += (double)__ldcg(src);
         q += (double)__ldcg(src + 1);
       }
-      const double n = (double)p.cpg * (double)p.HW;
-      const double mean = a / n;
-      double var = q / n - mean * mean;
-      if (var < 0.0) var = 0.0;
-      stats[((size_t)b * p.G + tid) * 2] = (float)mean;
-      stats[((size_t)b * p.G + tid) * 2 + 1] = (float)(1.0 / sqrt(var + (double)p.eps));
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        a += __shfl_xor_sync(0xffffffffu, a, o);
+        q += __shfl_xor_sync(0xffffffffu, q, o);
+      }
+      if (lane == 0) {
+        const double n = (double)p.cpg * (double)p.HW;
+        const double mean = a / n;
+        double var = q / n - mean * mean;
+        if (var < 0.0) var = 0.0;
+        stats[((size_t)b * p.G + g) * 2] = (float)mean;
+        stats[((size_t)b * p.G + g) * 2 + 1] = (float)(1.0 / sqrt(var + (double)p.eps));
+      }
     }
     if (tid == 0) ticket[b] = 0u;
   }

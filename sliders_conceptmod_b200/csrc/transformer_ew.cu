@@ -1,0 +1,115 @@
+// Row-wise elementwise / normalisation kernels of the UNet's transformer blocks: LayerNorm ahead of
+// the LoRA-wrapped attn1 projections and the GEGLU gate of the feed-forward.  HBM-bound, 16-byte accesses.
+#include "common.cuh"
+
+namespace slider {
+
+template <typename T> struct RowVec {
+  static constexpr int V = Elem<T>::kVec;
+};
+
+// ---- LayerNorm over the last dimension: one warp per row ---------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+layernorm_kernel(T* __restrict__ y, const T* __restrict__ x, const T* __restrict__ gamma,
+                 const T* __restrict__ beta, int64_t rows, int C, float eps) {
+  constexpr int V = Elem<T>::kVec;
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const T* xr = x + row * C;
+  T* yr = y + row * C;
+  const int nv = C / V;
+  float sum = 0.f;
+  for (int v = lane; v < nv; v += 32) {
+    float xv[V];
+    Elem<T>::load(xr + v * V, xv);
+#pragma unroll
+    for (int k = 0; k < V; ++k) sum += xv[k];
+  }
+  const float mean = warp_sum(sum) / (float)C;
+  float sq = 0.f;
+  for (int v = lane; v < nv; v += 32) {     // second pass hits L1: centred sum of squares (no cancellation)
+    float xv[V];
+    Elem<T>::load(xr + v * V, xv);
+#pragma unroll
+    for (int k = 0; k < V; ++k) { const float d = xv[k] - mean; sq = fmaf(d, d, sq); }
+  }
+  const float rstd = rsqrtf(warp_sum(sq) / (float)C + eps);
+  for (int v = lane; v < nv; v += 32) {
+    float xv[V], gv[V], bv[V], o[V];
+    Elem<T>::load(xr + v * V, xv);
+    if (gamma) Elem<T>::load(gamma + v * V, gv);
+    if (beta) Elem<T>::load(beta + v * V, bv);
+#pragma unroll
+    for (int k = 0; k < V; ++k) {
+      float u = (xv[k] - mean) * rstd;
+      if (gamma) u *= gv[k];
+      if (beta) u += bv[k];
+      o[k] = u;
+    }
+    Elem<T>::store(yr + v * V, o);
+  }
+}
+
+// ---- GEGLU: y[r, c] = x[r, c] * gelu(x[r, D + c]) (exact erf GELU) -------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+geglu_kernel(T* __restrict__ y, const T* __restrict__ x, int64_t rows, int D) {
+  constexpr int V = Elem<T>::kVec;
+  const int nv = D / V;
+  const int64_t total = rows * nv;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / nv;
+    const int v = (int)(i - r * nv);
+    float a[V], g[V], o[V];
+    Elem<T>::load(x + r * 2 * D + v * V, a);
+    Elem<T>::load(x + r * 2 * D + D + v * V, g);
+#pragma unroll
+    for (int k = 0; k < V; ++k) o[k] = a[k] * (0.5f * g[k] * (1.f + erff(g[k] * 0.70710678118654752f)));
+    Elem<T>::store(y + r * D + v * V, o);
+  }
+}
+
+}  // namespace slider
+
+using namespace slider;
+
+extern "C" {
+
+int slider_layernorm(void* y, const void* x, const void* gamma, const void* beta, int64_t rows, int channels,
+                     float eps, int dtype, void* stream) {
+  SLIDER_CHECK_ARG(y && x && rows > 0 && channels > 0, "layernorm: bad argument");
+  SLIDER_CHECK_ARG(channels % 8 == 0, "layernorm: channels must be a multiple of 8 (got %d)", channels);
+  SLIDER_CHECK_ARG((((uintptr_t)y | (uintptr_t)x | (uintptr_t)gamma | (uintptr_t)beta) & 15) == 0,
+                   "layernorm: pointers must be 16-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  const unsigned grid = (unsigned)((rows + 7) / 8);
+  if (dtype == SLIDER_BF16)
+    layernorm_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((__nv_bfloat16*)y, (const __nv_bfloat16*)x,
+                                                          (const __nv_bfloat16*)gamma, (const __nv_bfloat16*)beta, rows,
+                                                          channels, eps);
+  else if (dtype == SLIDER_F32)
+    layernorm_kernel<float><<<grid, 256, 0, st>>>((float*)y, (const float*)x, (const float*)gamma, (const float*)beta,
+                                                  rows, channels, eps);
+  else { set_error("layernorm: unsupported dtype %d", dtype); return SLIDER_ERR_UNSUPPORTED; }
+  return post_launch("layernorm_kernel");
+}
+
+int slider_geglu(void* y, const void* x, int64_t rows, int d, int dtype, void* stream) {
+  SLIDER_CHECK_ARG(y && x && rows > 0 && d > 0 && d % 8 == 0, "geglu: bad argument");
+  SLIDER_CHECK_ARG((((uintptr_t)y | (uintptr_t)x) & 15) == 0, "geglu: pointers must be 16-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int V = dtype == SLIDER_BF16 ? 8 : 4;
+  int64_t blocks = (rows * (d / V) + 255) / 256;
+  const int64_t cap = (int64_t)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  if (dtype == SLIDER_BF16)
+    geglu_kernel<__nv_bfloat16><<<(unsigned)blocks, 256, 0, st>>>((__nv_bfloat16*)y, (const __nv_bfloat16*)x, rows, d);
+  else if (dtype == SLIDER_F32)
+    geglu_kernel<float><<<(unsigned)blocks, 256, 0, st>>>((float*)y, (const float*)x, rows, d);
+  else { set_error("geglu: unsupported dtype %d", dtype); return SLIDER_ERR_UNSUPPORTED; }
+  return post_launch("geglu_kernel");
+}
+
+}  // extern "C"

@@ -158,6 +158,27 @@ def groupnorm_nhwc(x: torch.Tensor, groups: int, gamma: torch.Tensor | None, bet
     return y
 
 
+def layernorm(x: torch.Tensor, gamma: torch.Tensor | None, beta: torch.Tensor | None, eps: float = 1e-5) -> torch.Tensor:
+    """LayerNorm over the last dimension (diffusers BasicTransformerBlock.norm1/2/3)."""
+    require_cuda(x, gamma, beta)
+    assert x.is_contiguous()
+    C_ = x.shape[-1]
+    y = torch.empty_like(x)
+    check(lib().slider_layernorm(ptr(y), ptr(x), ptr(gamma), ptr(beta), x.numel() // C_, int(C_), float(eps),
+                                 dtype_code(x.dtype), stream_ptr()))
+    return y
+
+
+def geglu(x: torch.Tensor) -> torch.Tensor:
+    """x[..., :d] * gelu(x[..., d:]) for x [..., 2d] (diffusers GEGLU after its projection)."""
+    require_cuda(x)
+    assert x.is_contiguous() and x.shape[-1] % 2 == 0
+    d = x.shape[-1] // 2
+    y = torch.empty(*x.shape[:-1], d, device=x.device, dtype=x.dtype)
+    check(lib().slider_geglu(ptr(y), ptr(x), x.numel() // (2 * d), int(d), dtype_code(x.dtype), stream_ptr()))
+    return y
+
+
 def launch_count() -> int:
     return int(lib().slider_launch_count())
 

@@ -115,6 +115,17 @@ def group_norm_act(norm: nn.GroupNorm, x: torch.Tensor, silu: bool, chan_add: to
     return F.silu(y) if silu else y
 
 
+def _no_grad_cuda(*ts) -> bool:
+    first = ts[0]
+    return first.is_cuda and not (torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in ts))
+
+
+def layer_norm_fused(norm: nn.LayerNorm, x: torch.Tensor) -> torch.Tensor:
+    if _no_grad_cuda(x) and x.shape[-1] % 8 == 0:
+        return ops.layernorm(x.contiguous(), norm.weight, norm.bias, norm.eps)
+    return norm(x)
+
+
 class ResnetBlock2D(nn.Module):
     def __init__(self, in_ch: int, out_ch: int, temb_ch: int, groups: int):
         super().__init__()
@@ -129,7 +140,7 @@ class ResnetBlock2D(nn.Module):
 
     def forward(self, x, temb):
         h = self.conv1(group_norm_act(self.norm1, x, True))
-        t = self.time_emb_proj(self.nonlinearity(temb))
+        t = self.time_emb_proj(temb if getattr(temb, "_silu_applied", False) else self.nonlinearity(temb))
         h = self.conv2(self.dropout(group_norm_act(self.norm2, h, True, chan_add=t)))   # norm2(h + t)
         if self.conv_shortcut is not None:
             x = self.conv_shortcut(x)
@@ -184,7 +195,10 @@ class GEGLU(nn.Module):
         self.proj = nn.Linear(dim_in, dim_out * 2)
 
     def forward(self, x):
-        x, gate = self.proj(x).chunk(2, dim=-1)
+        h = self.proj(x)
+        if _no_grad_cuda(h) and h.shape[-1] % 16 == 0:
+            return ops.geglu(h.contiguous())
+        x, gate = h.chunk(2, dim=-1)
         return x * F.gelu(gate)
 
 
@@ -210,9 +224,9 @@ class BasicTransformerBlock(nn.Module):
         self.ff = FeedForward(dim)
 
     def forward(self, x, context):
-        x = x + self.attn1(self.norm1(x))
-        x = x + self.attn2(self.norm2(x), context)
-        return x + self.ff(self.norm3(x))
+        x = x + self.attn1(layer_norm_fused(self.norm1, x))
+        x = x + self.attn2(layer_norm_fused(self.norm2, x), context)
+        return x + self.ff(layer_norm_fused(self.norm3, x))
 
 
 class Transformer2DModel(nn.Module):
@@ -390,6 +404,9 @@ class UNet2DConditionModel(nn.Module):
             ids = added_cond_kwargs["time_ids"]
             tid = self.add_time_proj(ids.flatten()).reshape(ids.shape[0], -1)
             emb = emb + self.add_embedding(torch.cat([te, tid.to(te.dtype)], dim=-1).to(sample.dtype))
+        # every ResnetBlock2D applies the same SiLU to the same embedding before its time_emb_proj: do it once
+        emb = F.silu(emb)
+        emb._silu_applied = True
         x = self.conv_in(sample.contiguous(memory_format=torch.channels_last))
         skips = [x]
         for blk in self.down_blocks:
