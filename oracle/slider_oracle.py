@@ -186,23 +186,85 @@ def diffusion(unet, scheduler, latents, text_embeddings, total_timesteps=1000, s
 
 
 def train_iteration(unet, network, scheduler, emb, latents, timesteps_to, guidance_scale, action,
-                    max_denoising_steps=50, denoise_guidance=3.0):
-    """One iteration of conceptmod/textsliders/train_lora.py:155-298 up to loss.backward().
-    emb: dict(target, positive, neutral, unconditional) of [b,77,D].  Returns the loss tensor; LoRA
-    gradients are left in .grad."""
+                    max_denoising_steps=50, denoise_guidance=3.0, predict_guidance=1.0, noises=None, pooled=None,
+                    time_ids=None):
+    """One iteration of conceptmod/textsliders/train_lora.py:155-298 up to loss.backward().  With
+    `predict_guidance = denoise_guidance = config.train.cfg`, an `emb["negative"]` entry and `pooled` / `time_ids`
+    (SD-XL added_cond_kwargs, rebuilt per call from the same prompt as the text embedding) it is
+    conceptmod/textsliders/train_lora_xl.py:165-346.  emb / pooled: dict(target, positive, neutral, unconditional
+    [, negative]) of [b,77,D] / [b,1280].  `noises`: the ancestral draws of the partial denoise, in order (euler_a /
+    ddpm).  Returns the loss tensor; LoRA gradients are left in .grad."""
     cat = lambda u, c: torch.cat([u, c])
+
+    def pair(key):
+        kw = {}
+        if pooled is not None:
+            kw["added_cond_kwargs"] = {"text_embeds": cat(pooled["unconditional"], pooled[key]),
+                                       "time_ids": cat(time_ids, time_ids)}
+        return cat(emb["unconditional"], emb[key]), kw
+
+    g = predict_guidance
     with torch.no_grad():
         scheduler.set_timesteps(max_denoising_steps)
         with network:
-            denoised = diffusion(unet, scheduler, latents, cat(emb["unconditional"], emb["target"]),
-                                 start_timesteps=0, total_timesteps=timesteps_to, guidance_scale=denoise_guidance)
+            e, kw = pair("target")
+            denoised = diffusion(unet, scheduler, latents, e, start_timesteps=0, total_timesteps=timesteps_to,
+                                 guidance_scale=denoise_guidance, noises=noises, **kw)
         scheduler.set_timesteps(1000)
         t = scheduler.timesteps[int(timesteps_to * 1000 / max_denoising_steps)]
-        pos = predict_noise(unet, scheduler, t, denoised, cat(emb["unconditional"], emb["positive"]), 1)
-        neu = predict_noise(unet, scheduler, t, denoised, cat(emb["unconditional"], emb["neutral"]), 1)
-        unc = predict_noise(unet, scheduler, t, denoised, cat(emb["unconditional"], emb["unconditional"]), 1)
+        e, kw = pair("positive")
+        pos = predict_noise(unet, scheduler, t, denoised, e, g, **kw)
+        e, kw = pair("neutral")
+        neu = predict_noise(unet, scheduler, t, denoised, e, g, **kw)
+        e, kw = pair("negative" if "negative" in emb else "unconditional")
+        unc = predict_noise(unet, scheduler, t, denoised, e, g, **kw)
     with network:
-        tgt = predict_noise(unet, scheduler, t, denoised, cat(emb["unconditional"], emb["target"]), 1)
+        e, kw = pair("target")
+        tgt = predict_noise(unet, scheduler, t, denoised, e, g, **kw)
     loss = guidance_loss(tgt, pos, neu, unc, guidance_scale, action)
     loss.backward()
     return loss, dict(denoised=denoised, positive=pos, neutral=neu, unconditional=unc, target=tgt.detach())
+
+
+def image_slider_iteration(unet, network, scheduler, emb, lat_low, lat_high, noise, timesteps_to, scale,
+                           max_denoising_steps=50):
+    """One iteration of trainscripts/imagesliders/train_lora-scale.py:196-334 from the encoded latents on: both
+    latents get the SAME noise at timesteps[timesteps_to] (train_util.py:231-233), the adapter at +scale predicts
+    the noise of the "high" latents under the positive prompt, at -scale that of the "low" latents under the
+    neutral prompt; the two MSE losses back-propagate into the same .grad (no zero_grad between, :327-334)."""
+    cat = lambda u, c: torch.cat([u, c])
+    with torch.no_grad():
+        scheduler.set_timesteps(max_denoising_steps)
+        t_add = scheduler.timesteps[timesteps_to:timesteps_to + 1]
+        noisy_low = scheduler.add_noise(lat_low, noise, t_add)
+        noisy_high = scheduler.add_noise(lat_high, noise, t_add)
+        scheduler.set_timesteps(1000)
+        t = scheduler.timesteps[int(timesteps_to * 1000 / max_denoising_steps)]
+    network.set_lora_slider(scale)
+    with network:
+        tgt_high = predict_noise(unet, scheduler, t, noisy_high, cat(emb["unconditional"], emb["positive"]), 1)
+    loss_high = ((tgt_high.float() - noise.float()) ** 2).mean()
+    loss_high.backward()
+    network.set_lora_slider(-scale)
+    with network:
+        tgt_low = predict_noise(unet, scheduler, t, noisy_low, cat(emb["unconditional"], emb["neutral"]), 1)
+    loss_low = ((tgt_low.float() - noise.float()) ** 2).mean()
+    loss_low.backward()
+    return loss_high, loss_low
+
+
+@torch.no_grad()
+def inference_sweep(unet, network, scheduler, text_embeddings, latents, scale, start_noise, guidance_scale,
+                    num_inference_steps, noises=None, **unet_kw):
+    """Denoising loop of eval-scripts/generate_images_sd1.py:150-176 / generate_images_xl.py:325-358: the adapter
+    is off (scale 0) while t > start_noise, then on at `scale`; CFG; scheduler.step."""
+    scheduler.set_timesteps(num_inference_steps)
+    for i, t in enumerate(scheduler.timesteps):
+        network.set_lora_slider(0 if t > start_noise else scale)
+        x = scheduler.scale_model_input(torch.cat([latents] * 2), t)
+        with network:
+            eps = unet(x, t, encoder_hidden_states=text_embeddings, **unet_kw).sample
+        eps = cfg_combine(eps, guidance_scale)
+        z = None if noises is None else noises[i]
+        latents = scheduler.step(eps, t, latents, noise=z).prev_sample
+    return latents

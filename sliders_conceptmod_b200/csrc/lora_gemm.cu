@@ -520,7 +520,21 @@ splitk_finalize_kernel(const GemmParams p) {
 // one warp per output channel streams W[n,:] with 16-byte loads; the activation rows live in
 // shared memory (fp32); h = x.A^T is recomputed per CTA (M*r dot products of length K).
 constexpr int GEMV_WARPS = 8;
-template <typename T, int MT>
+template <typename T> struct Raw16 {
+  __device__ static inline void unpack(const uint4& r, float (&v)[Elem<T>::kVec]);
+};
+template <> __device__ inline void Raw16<__nv_bfloat16>::unpack(const uint4& t, float (&v)[8]) {
+  const uint32_t w[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { v[2 * i] = __uint_as_float(w[i] << 16); v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u); }
+}
+template <> __device__ inline void Raw16<float>::unpack(const uint4& t, float (&v)[4]) {
+  v[0] = __uint_as_float(t.x); v[1] = __uint_as_float(t.y); v[2] = __uint_as_float(t.z); v[3] = __uint_as_float(t.w);
+}
+
+// KC = 16-byte chunks of a weight row per lane (K <= KC * 32 * kVec).  All global loads of a warp (its W row,
+// its lora_down row) are issued before the first barrier, so the kernel pays ONE DRAM latency, not one per chunk.
+template <typename T, int MT, int KC>
 __global__ void __launch_bounds__(GEMV_WARPS * 32)
 lora_gemv_kernel(T* __restrict__ y, const T* __restrict__ x, const T* __restrict__ W, const T* __restrict__ bias,
                  const T* __restrict__ A, const T* __restrict__ Bup, float* __restrict__ h_out, int M, int K, int N,
@@ -530,6 +544,21 @@ lora_gemv_kernel(T* __restrict__ y, const T* __restrict__ x, const T* __restrict
   float* xs = gemv_smem;                  // [MT][K]
   float* hs = gemv_smem + (size_t)MT * K; // [MT][16]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n = blockIdx.x * GEMV_WARPS + warp;
+  const bool n_ok = n < N;
+  uint4 wreg[KC], areg[KC];
+  const int pr0 = warp;                   // first (row m, rank j) pair of this warp for h = x . A^T
+  const bool pr_ok = lora && pr0 < MT * rank;
+  {
+    const uint4* wrow = reinterpret_cast<const uint4*>(W + (size_t)(n_ok ? n : 0) * K);
+    const uint4* arow = reinterpret_cast<const uint4*>(A + (size_t)(pr_ok ? pr0 % rank : 0) * K);
+#pragma unroll
+    for (int c = 0; c < KC; ++c) {
+      const int k = (c * 32 + lane) * V;
+      wreg[c] = (n_ok && k < K) ? __ldg(wrow + c * 32 + lane) : make_uint4(0, 0, 0, 0);
+      areg[c] = (pr_ok && k < K) ? __ldg(arow + c * 32 + lane) : make_uint4(0, 0, 0, 0);
+    }
+  }
   for (int i = threadIdx.x * V; i < MT * K; i += blockDim.x * V) {
     const int m = i / K;
     float v[V];
@@ -542,11 +571,24 @@ lora_gemv_kernel(T* __restrict__ y, const T* __restrict__ x, const T* __restrict
     for (int pr = warp; pr < MT * rank; pr += GEMV_WARPS) {
       const int m = pr / rank, j = pr - m * rank;
       float acc = 0.f;
-      for (int k = lane * V; k < K; k += 32 * V) {
-        float av[V];
-        Elem<T>::load(A + (size_t)j * K + k, av);
+      if (pr == pr0) {
 #pragma unroll
-        for (int e = 0; e < V; ++e) acc = fmaf(av[e], xs[m * K + k + e], acc);
+        for (int c = 0; c < KC; ++c) {
+          const int k = (c * 32 + lane) * V;
+          if (k < K) {
+            float av[V];
+            Raw16<T>::unpack(areg[c], av);
+#pragma unroll
+            for (int e = 0; e < V; ++e) acc = fmaf(av[e], xs[m * K + k + e], acc);
+          }
+        }
+      } else {
+        for (int k = lane * V; k < K; k += 32 * V) {
+          float av[V];
+          Elem<T>::load(A + (size_t)j * K + k, av);
+#pragma unroll
+          for (int e = 0; e < V; ++e) acc = fmaf(av[e], xs[m * K + k + e], acc);
+        }
       }
       acc = warp_sum(acc);
       if (lane == 0) {
@@ -556,20 +598,22 @@ lora_gemv_kernel(T* __restrict__ y, const T* __restrict__ x, const T* __restrict
     }
     __syncthreads();
   }
-  const int n = blockIdx.x * GEMV_WARPS + warp;
-  if (n >= N) return;
+  if (!n_ok) return;
   float acc[MT];
 #pragma unroll
   for (int m = 0; m < MT; ++m) acc[m] = 0.f;
-  const T* wrow = W + (size_t)n * K;
-  for (int k = lane * V; k < K; k += 32 * V) {
-    float wv[V];
-    Elem<T>::load(wrow + k, wv);
 #pragma unroll
-    for (int m = 0; m < MT; ++m) {
-      const float* xr = xs + m * K + k;
+  for (int c = 0; c < KC; ++c) {
+    const int k = (c * 32 + lane) * V;
+    if (k < K) {
+      float wv[V];
+      Raw16<T>::unpack(wreg[c], wv);
 #pragma unroll
-      for (int e = 0; e < V; ++e) acc[m] = fmaf(wv[e], xr[e], acc[m]);
+      for (int m = 0; m < MT; ++m) {
+        const float* xr = xs + m * K + k;
+#pragma unroll
+        for (int e = 0; e < V; ++e) acc[m] = fmaf(wv[e], xr[e], acc[m]);
+      }
     }
   }
 #pragma unroll
@@ -647,12 +691,16 @@ static int launch_gemv(const slider_layer_geom* g, int M, void* y, const void* x
   const int mt = M <= 2 ? 2 : (M <= 4 ? 4 : (M <= 8 ? 8 : 16));
   const size_t smem = ((size_t)mt * K + (size_t)mt * 16) * sizeof(float);
   const int grid = (N + GEMV_WARPS - 1) / GEMV_WARPS;
-#define GEMV(MT)                                                                                           \
-  lora_gemv_kernel<T, MT><<<grid, GEMV_WARPS * 32, smem, st>>>((T*)y, (const T*)x, (const T*)W, (const T*)bias, \
-                                                               (const T*)A, (const T*)Bup, h_out, M, K, N,  \
-                                                               g->rank, s, lora ? 1 : 0)
+  const int V = 16 / (int)sizeof(T);
+  const int kc = (K + 32 * V - 1) / (32 * V);     // 16-byte chunks per lane (caller guarantees <= 8)
+#define GEMV2(MT, KC)                                                                                             \
+  lora_gemv_kernel<T, MT, KC><<<grid, GEMV_WARPS * 32, smem, st>>>((T*)y, (const T*)x, (const T*)W, (const T*)bias, \
+                                                                   (const T*)A, (const T*)Bup, h_out, M, K, N,  \
+                                                                   g->rank, s, lora ? 1 : 0)
+#define GEMV(MT) do { if (kc <= 2) GEMV2(MT, 2); else if (kc <= 4) GEMV2(MT, 4); else GEMV2(MT, 8); } while (0)
   if (mt == 2) GEMV(2); else if (mt == 4) GEMV(4); else if (mt == 8) GEMV(8); else GEMV(16);
 #undef GEMV
+#undef GEMV2
   return post_launch("lora_gemv_kernel");
 }
 
@@ -684,7 +732,8 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
     // small-M path: a 128-row tensor-core tile would be > 87 % padding and the op is weight-bandwidth bound
     const long long M = (long long)g->batch * g->height * g->width;
     const size_t mt = M <= 2 ? 2 : (M <= 4 ? 4 : (M <= 8 ? 8 : 16));
-    if (!ext && taps == 1 && M <= 16 && mt * kc * sizeof(float) <= 40 * 1024) {
+    if (!ext && taps == 1 && M <= 16 && mt * kc * sizeof(float) <= 40 * 1024 && kc * es <= 8 * 32 * 16 &&
+        ((uintptr_t)wgt & 15) == 0 && (lo == nullptr || ((uintptr_t)lo & 15) == 0)) {
       if (g->dtype == SLIDER_BF16)
         return launch_gemv<__nv_bfloat16>(g, (int)M, y, act, wgt, bias, lo, Bup, lora ? h_out : nullptr, s, lora, st);
       return launch_gemv<float>(g, (int)M, y, act, wgt, bias, lo, Bup, lora ? h_out : nullptr, s, lora, st);

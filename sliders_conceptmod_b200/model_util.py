@@ -6,6 +6,7 @@ factory keeps the reference's constructor arguments verbatim.
 """
 from __future__ import annotations
 
+import dataclasses
 import zlib
 from typing import Literal
 
@@ -89,7 +90,10 @@ def load_models(pretrained_model_name_or_path: str, scheduler_name: AVAILABLE_SC
 
 def load_models_xl(pretrained_model_name_or_path: str, scheduler_name: AVAILABLE_SCHEDULERS,
                    weight_dtype: torch.dtype = torch.float32, seed: int = 0):
-    cfg = UNetConfig.tiny(64) if "tiny" in pretrained_model_name_or_path.lower() else UNetConfig.sdxl()
+    if "tiny" in pretrained_model_name_or_path.lower():     # XL topology features at test size
+        cfg = dataclasses.replace(UNetConfig.tiny(64), addition_embed=True, use_linear_projection=True)
+    else:
+        cfg = UNetConfig.sdxl()
     torch.manual_seed(seed)
     unet = UNet2DConditionModel(cfg)
     scheduler = create_noise_scheduler(scheduler_name)

@@ -97,6 +97,12 @@ def guidance_mse(target, positive, neutral, q, guidance_scale: float, sign: int)
     return _GuidanceLossFn.apply(target, positive, neutral, q, float(guidance_scale), int(sign))
 
 
+def plain_mse(target, reference) -> torch.Tensor:
+    """MSELoss()(target, reference) through the same fused kernel (p = q = NULL): the image-slider objective
+    (trainscripts/imagesliders/train_lora-scale.py:303,327), differentiable w.r.t. `target`."""
+    return _GuidanceLossFn.apply(target, None, reference.to(target.dtype), None, 0.0, 1)
+
+
 def _check_loss_fn(loss_fn) -> None:
     if not (isinstance(loss_fn, torch.nn.MSELoss) and loss_fn.reduction == "mean"):
         raise NotImplementedError(
