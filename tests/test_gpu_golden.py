@@ -130,3 +130,39 @@ def test_diffusion_loop_matches_oracle():
             if kind == "euler_a":
                 tu.torch.randn = real
         _close(out, ref, 5e-3, f"diffusion[{kind}]")
+
+
+def test_trainer_reproduces_reference_minitrain(tmp_path):
+    """The drop-in SD-1.x trainer (CUDA kernels, fp32 storage) replays the reference's own unmodified `train()` run
+    (tests/golden/make_golden_minitrain.py): same losses per iteration, same LoRA weight update."""
+    import yaml
+    from sliders_conceptmod_b200 import config_util, prompt_util
+    from sliders_conceptmod_b200.slider_loop import TextSliderTrainer
+    gold = torch.load(Path(__file__).parent / "golden" / "reference_minitrain.pt", weights_only=False)
+    (tmp_path / "prompts.yaml").write_text(yaml.safe_dump(gold["prompts"]))
+    cfg = dict(gold["config"])
+    cfg["prompts_file"] = str(tmp_path / "prompts.yaml")
+    cfg["save"] = dict(cfg["save"], path=str(tmp_path / "out"))
+    (tmp_path / "config.yaml").write_text(yaml.safe_dump(cfg))
+    config = config_util.load_config_from_yaml(str(tmp_path / "config.yaml"))
+    prompts = prompt_util.load_prompts_from_yaml(config.prompts_file, [])
+    tr = TextSliderTrainer(config, prompts, "cuda")
+    checksum = float(sum(p.detach().double().abs().sum() for p in tr.unet.parameters()))
+    assert abs(checksum - gold["unet_checksum"]) < 1e-6 * gold["unet_checksum"], "UNet stand-in init changed"
+    tr.network.load_state_dict(gold["init"])
+    torch.manual_seed(gold["loop_seed"])
+    for i, ref_loss in enumerate(gold["losses"]):
+        loss = tr.iteration(i).item()
+        rel = abs(loss - ref_loss) / abs(ref_loss)
+        print(f"iteration {i}: loss {loss:.6e} reference {ref_loss:.6e} rel {rel:.2e}")
+        assert rel <= 1e-3
+    sd = {k: v.float().cpu() for k, v in tr.network.state_dict().items()}
+    keys = sorted(gold["final"])
+    delta_g = torch.cat([(sd[k] - gold["init"][k]).flatten() for k in keys]).double()
+    delta_r = torch.cat([(gold["final"][k] - gold["init"][k]).flatten() for k in keys]).double()
+    cos = float(delta_g @ delta_r / (delta_g.norm() * delta_r.norm()))
+    wg = torch.cat([sd[k].flatten() for k in keys]).double()
+    wr = torch.cat([gold["final"][k].flatten() for k in keys]).double()
+    wcos = float(wg @ wr / (wg.norm() * wr.norm()))
+    print(f"weight-update cosine {cos:.6f} (|delta| {delta_r.norm():.4f}); final-weight cosine {wcos:.8f}")
+    assert cos >= 0.999 and wcos >= 0.999

@@ -75,3 +75,40 @@ def test_scheduler_tables():
         assert s.timesteps[int(tt * 1000 / 50)].item() == 999 - 20 * tt
     ac = O.alphas_cumprod()
     assert abs(ac[0].item() - 0.99915) < 1e-5 and abs(ac[-1].item() - 0.0046601) < 1e-5
+
+
+def test_train_loop_matches_reference_minitrain():
+    """The oracle's train_iteration, iterated with torch AdamW, against the losses and final LoRA weights produced by
+    the reference's own unmodified `train()` loop (tests/golden/make_golden_minitrain.py)."""
+    from sliders_conceptmod_b200 import model_util, train_util, workload
+    from sliders_conceptmod_b200.lora import LoRANetwork
+    gold = torch.load(Path(__file__).parent / "golden" / "reference_minitrain.pt", weights_only=False)
+    cfg = gold["config"]
+    _, enc, unet, _ = model_util.load_models("tiny-sd", scheduler_name="ddim")
+    unet.eval().requires_grad_(False)
+    checksum = float(sum(p.detach().double().abs().sum() for p in unet.parameters()))
+    assert abs(checksum - gold["unet_checksum"]) < 1e-6 * gold["unet_checksum"], "UNet stand-in init changed"
+    net = LoRANetwork(unet, rank=4, multiplier=1.0, alpha=1.0, target_replace=workload.target_modules(True),
+                      train_method="noxattn")
+    assert set(net.state_dict()) == set(gold["init"])
+    net.load_state_dict(gold["init"])
+    O.attach(net)
+    opt = torch.optim.AdamW(net.prepare_optimizer_params(), lr=cfg["train"]["lr"])
+    sched = O.OracleScheduler("ddim")
+    n_den = cfg["train"]["max_denoising_steps"]
+    embs = [{k: enc.encode([p[k]]) for k in ("target", "positive", "neutral", "unconditional")} for p in gold["prompts"]]
+    torch.manual_seed(gold["loop_seed"])
+    for i, ref_loss in enumerate(gold["losses"]):
+        sched.set_timesteps(n_den)
+        opt.zero_grad()
+        idx = torch.randint(0, len(embs), (1,)).item()
+        timesteps_to = torch.randint(1, n_den, (1,)).item()
+        p = gold["prompts"][idx]
+        latents = train_util.get_initial_latents(sched, p["batch_size"], p["resolution"], p["resolution"], 1)
+        loss, _ = O.train_iteration(unet, net, sched, embs[idx], latents, timesteps_to, p["guidance_scale"], p["action"],
+                                    max_denoising_steps=n_den)
+        opt.step()
+        assert abs(loss.item() - ref_loss) <= 1e-5 * abs(ref_loss), f"iteration {i}: {loss.item()} vs {ref_loss}"
+    sd = net.state_dict()
+    for k, v in gold["final"].items():
+        assert torch.allclose(sd[k], v, rtol=1e-4, atol=1e-6), k
