@@ -74,6 +74,8 @@ class SliderEngine:
         self.kernel_launches = 0        # libslider_b200 kernels issued (directly or by graph replay)
         self._tables = {}
         self._needs_scale = hasattr(scheduler, "_sigmas")        # Euler-ancestral divides the model input
+        if hasattr(unet, "enable_context_cache"):      # cross-attention K/V once per prompt pair (see unet.py)
+            unet.enable_context_cache([self.emb_den, self.emb_pred, self.emb_tgt])
         self._stochastic = any(self.sched.step_coefficients(t)[2] != 0.0 for t in self._table(cfg.max_denoising_steps)[3][:2])
 
     # ---- scheduler tables on the device (one row per denoising step) ---------------------------------
@@ -173,6 +175,8 @@ class SliderEngine:
         self.emb_den.copy_(torch.cat([u, t]))
         self.emb_tgt.copy_(torch.cat([u, t]))
         self.emb_pred.copy_(torch.cat([u, u, u, p, n, u]))
+        if hasattr(self.unet, "refresh_context_cache"):
+            self.unet.refresh_context_cache()
         if (guidance_scale, action) != (self.guidance, "enhance" if self.sign > 0 else "erase"):
             self.guidance, self.sign = float(guidance_scale), (1 if action == "enhance" else -1)
             self._graphs.pop("train", None)     # host scalars are baked into the captured launch

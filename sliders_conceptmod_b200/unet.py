@@ -176,11 +176,22 @@ class Attention(nn.Module):
         self.to_k = nn.Linear(cross_dim, inner, bias=False)
         self.to_v = nn.Linear(cross_dim, inner, bias=False)
         self.to_out = nn.ModuleList([nn.Linear(inner, query_dim), nn.Dropout(0.0)])
+        self._kv_cache = None       # {context.data_ptr(): (k, v)} — see UNet2DConditionModel.enable_context_cache
+
+    def kv_cacheable(self) -> bool:
+        """True when to_k / to_v are plain frozen projections (not LoRA-wrapped: their forward is unpatched)."""
+        return not any("forward" in m.__dict__ or m.weight.requires_grad for m in (self.to_k, self.to_v))
 
     def forward(self, x, context=None):
         ctx = x if context is None else context
         B, L, _ = x.shape
-        q, k, v = self.to_q(x), self.to_k(ctx), self.to_v(ctx)
+        hit = None
+        if context is not None and self._kv_cache is not None:
+            hit = self._kv_cache.get(context.data_ptr())
+        if hit is not None:
+            q, (k, v) = self.to_q(x), hit
+        else:
+            q, k, v = self.to_q(x), self.to_k(ctx), self.to_v(ctx)
         q = q.view(B, L, self.heads, -1).transpose(1, 2)
         k = k.view(B, ctx.shape[1], self.heads, -1).transpose(1, 2)
         v = v.view(B, ctx.shape[1], self.heads, -1).transpose(1, 2)
@@ -389,6 +400,34 @@ class UNet2DConditionModel(nn.Module):
         self.conv_norm_out = nn.GroupNorm(cfg.norm_num_groups, boc[0], eps=1e-5)
         self.conv_act = nn.SiLU()
         self.conv_out = nn.Conv2d(boc[0], cfg.out_channels, 3, padding=1)
+
+    # ---- cross-attention K/V of a fixed prompt: computed once per prompt, not once per UNet call --------------
+    def enable_context_cache(self, contexts):
+        """`contexts`: persistent text-embedding buffers ([B,77,D]) that will be passed as `encoder_hidden_states`
+        by address.  For every cross-attention whose to_k / to_v are frozen and un-wrapped (all of them under the
+        `noxattn` family) K and V depend only on the prompt, so they are kept in persistent buffers and refreshed by
+        `refresh_context_cache()` whenever the buffers' contents change — the reference recomputes them in each of
+        the ~29 UNet calls of an iteration (train_util.py:290-294).  Results are bit-identical."""
+        self._ctx_buffers = list(contexts)
+        self._ctx_attn = [m for n, m in self.named_modules() if isinstance(m, Attention) and n.endswith("attn2")
+                          and m.kv_cacheable()]
+        for m in self._ctx_attn:
+            m._kv_cache = {c.data_ptr(): (torch.empty(c.shape[0], c.shape[1], m.to_k.out_features, device=c.device, dtype=c.dtype),
+                                          torch.empty(c.shape[0], c.shape[1], m.to_v.out_features, device=c.device, dtype=c.dtype))
+                           for c in self._ctx_buffers}
+        self.refresh_context_cache()
+
+    @torch.no_grad()
+    def refresh_context_cache(self):
+        for m in getattr(self, "_ctx_attn", []):
+            for c in self._ctx_buffers:
+                k, v = m._kv_cache[c.data_ptr()]
+                k.copy_(m.to_k(c)); v.copy_(m.to_v(c))
+
+    def disable_context_cache(self):
+        for m in getattr(self, "_ctx_attn", []):
+            m._kv_cache = None
+        self._ctx_attn, self._ctx_buffers = [], []
 
     def enable_xformers_memory_efficient_attention(self):  # API parity (train_lora.py:68); SDPA is used
         return None
