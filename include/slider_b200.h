@@ -88,6 +88,20 @@ int slider_lora_forward(const slider_layer_geom* g, void* y, const void* x,
                         size_t ws_bytes, void* stream);
 
 /*
+ * Several adapters on ONE input in one launch: the self-attention to_q / to_k / to_v of a transformer block
+ * (three LoRAModule.forward calls on the same x, reference diffusers Attention.forward reached from
+ * conceptmod/textsliders/train_util.py:290-294).  Operands are the row-wise concatenations
+ *   W [groups*cout_g, cin]   A [groups*rank, cin]   B [groups*cout_g, rank]   y [M, groups*cout_g]
+ * with g->cout = groups*cout_g and g->rank = the per-adapter rank; output columns of group i get
+ * s * (x . A_i^T) . B_i^T.  Needs groups*rank <= 16, cout_g a multiple of 160, kh = kw = 1, M > 16, s != 0.
+ * No h_out: inference / no-grad forwards only (the grad forward uses slider_lora_forward per adapter).
+ */
+int slider_lora_forward_grouped(const slider_layer_geom* g, void* y, const void* x,
+                                const void* W, const void* bias, const void* A,
+                                const void* B, int groups, float s, void* ws,
+                                size_t ws_bytes, void* stream);
+
+/*
  * Low-rank part of the backward of the layer above (autograd of lora.py:134-138,
  * triggered by loss.backward() at conceptmod/textsliders/train_lora.py:298):
  *     dh = s * gy . B          [M, rank]  -> dh_out (element dtype, padded to 16)

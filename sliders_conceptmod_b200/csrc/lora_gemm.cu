@@ -87,6 +87,7 @@ struct GemmParams {
   int ksplit;             // K partitions per tile (1 = no split)
   int total_units;        // total_tiles * ksplit
   float* partial;         // split-K partial tiles, [unit][NCHUNK][128][32] fp32
+  int group_n;            // grouped adapters: output columns per group (0 = one adapter); group g uses h columns [g*rank, (g+1)*rank)
   long long* trace;       // debug: 8 clock64() stamps per CTA (NULL = off)
   void* y;
   const void* bias;
@@ -360,7 +361,9 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       float hv[R4 > 0 ? 4 * R4 : 1];
       if (R4 > 0) {
         uint32_t hr[16];
-        ptx::tmem_ld_32x16(t_main + BN, hr);
+        // grouped adapters: this tile's group owns `rank` of the 16 h columns, starting at its offset
+        const int hoff = p.group_n > 0 ? (tc.n0 / p.group_n) * p.rank : 0;
+        ptx::tmem_ld_32x16(t_main + BN + hoff, hr);
         ptx::tmem_ld_wait();
 #pragma unroll
         for (int j = 0; j < 4 * R4; ++j) hv[j] = __uint_as_float(hr[j]);
@@ -465,7 +468,8 @@ splitk_finalize_kernel(const GemmParams p) {
   if (!row_ok || n >= p.N) return;
   const size_t pix = ((size_t)(tc.b0 + lb) * p.H + (tc.h0 + lh)) * p.W + (tc.w0 + lw);
   const float* src = p.partial + (size_t)tile * p.ksplit * UNIT_FLOATS + ((size_t)c * BM + row) * 32 + g * 8;
-  const float* hsrc = p.partial + (size_t)tile * p.ksplit * UNIT_FLOATS + ((size_t)(BN / 32) * BM + row) * 32;
+  const float* hsrc = p.partial + (size_t)tile * p.ksplit * UNIT_FLOATS + ((size_t)(BN / 32) * BM + row) * 32 +
+                      (p.group_n > 0 ? (tc.n0 / p.group_n) * p.rank : 0);
   float o[8];
   float hv[R4 > 0 ? 4 * R4 : 1];
 #pragma unroll
@@ -711,7 +715,7 @@ static int launch_gemv(const slider_layer_geom* g, int M, void* y, const void* x
 //   xe / we  [B,H,W,16] / [nn, taps, 16]  extended-K pair (input gradient only)
 static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const void* act, const void* wgt,
                     const void* bias, const void* lo, const void* Bup, float* h_out, float s, const void* xe,
-                    const void* we, void* ws, size_t ws_bytes, cudaStream_t st) {
+                    const void* we, void* ws, size_t ws_bytes, cudaStream_t st, int groups = 1) {
   const int es = esize(g->dtype);
   const int taps = g->kh * g->kw;
   const int bk = ROW_BYTES / es;
@@ -727,12 +731,19 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
 
   const bool lora = lo != nullptr && g->rank > 0 && (s != 0.f || h_out != nullptr);
   const bool ext = xe != nullptr;
+  if (groups > 1) {
+    SLIDER_CHECK_ARG(lora && !ext && taps == 1 && h_out == nullptr, "grouped lora gemm: needs an active 1x1 adapter, no h_out");
+    SLIDER_CHECK_ARG(groups * g->rank <= HCOLS, "grouped lora gemm: groups * rank = %d exceeds %d", groups * g->rank, HCOLS);
+    SLIDER_CHECK_ARG(nn % groups == 0 && (nn / groups) % BN == 0,
+                     "grouped lora gemm: columns per group (%d / %d) must be a multiple of %d", nn, groups, BN);
+    SLIDER_CHECK_ARG((long long)g->batch * g->height * g->width > 16, "grouped lora gemm: needs more than 16 rows");
+  }
   if (lora) SLIDER_CHECK_ARG(Bup != nullptr, "lora gemm: lora_up weight is NULL");
   {
     // small-M path: a 128-row tensor-core tile would be > 87 % padding and the op is weight-bandwidth bound
     const long long M = (long long)g->batch * g->height * g->width;
     const size_t mt = M <= 2 ? 2 : (M <= 4 ? 4 : (M <= 8 ? 8 : 16));
-    if (!ext && taps == 1 && M <= 16 && mt * kc * sizeof(float) <= 40 * 1024 && kc * es <= 8 * 32 * 16 &&
+    if (groups == 1 && !ext && taps == 1 && M <= 16 && mt * kc * sizeof(float) <= 40 * 1024 && kc * es <= 8 * 32 * 16 &&
         ((uintptr_t)wgt & 15) == 0 && (lo == nullptr || ((uintptr_t)lo & 15) == 0)) {
       if (g->dtype == SLIDER_BF16)
         return launch_gemv<__nv_bfloat16>(g, (int)M, y, act, wgt, bias, lo, Bup, lora ? h_out : nullptr, s, lora, st);
@@ -750,6 +761,7 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
   p.n_tiles = (nn + BN - 1) / BN; p.N = nn;
   p.taps = taps; p.kw = g->kw; p.pad = g->pad; p.cblocks = (kc + bk - 1) / bk;
   p.rank = g->rank; p.s = s; p.lora = lora ? 1 : 0; p.ext = ext ? 1 : 0;
+  p.group_n = groups > 1 ? nn / groups : 0;
   p.total_tiles = p.mt_w * p.mt_h * p.mt_b * p.n_tiles;
   p.per_tap = p.cblocks + (ext ? 1 : 0);
   p.kiters = taps * p.per_tap;
@@ -787,7 +799,7 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
   }
   mL = mW; mXe = mA; mWe = mW;
   if (lora) {
-    uint64_t dims[3] = {(uint64_t)kc, (uint64_t)taps, (uint64_t)g->rank};
+    uint64_t dims[3] = {(uint64_t)kc, (uint64_t)taps, (uint64_t)(g->rank * groups)};
     uint64_t str[2] = {(uint64_t)kc * es, (uint64_t)kc * es * taps};
     uint32_t box[3] = {(uint32_t)bk, 1u, (uint32_t)HCOLS};
     if ((rc = make_tmap(&mL, g->dtype, 3, lo, dims, str, box, ROW_BYTES))) return rc;
@@ -844,6 +856,16 @@ int slider_lora_forward(const slider_layer_geom* g, void* y, const void* x, cons
   SLIDER_CHECK_ARG(g && y && x && W, "lora_forward: null pointer");
   return run_gemm(g, g->cin, g->cout, y, x, W, bias, A, B, h_out, s, nullptr, nullptr, ws, ws_bytes,
                   (cudaStream_t)stream);
+}
+
+int slider_lora_forward_grouped(const slider_layer_geom* g, void* y, const void* x, const void* W, const void* bias,
+                                const void* A, const void* B, int groups, float s, void* ws, size_t ws_bytes,
+                                void* stream) {
+  SLIDER_CHECK_ARG(g && y && x && W && A && B, "lora_forward_grouped: null pointer");
+  SLIDER_CHECK_ARG(groups >= 1, "lora_forward_grouped: groups must be >= 1");
+  SLIDER_CHECK_ARG(s != 0.f, "lora_forward_grouped: s == 0 (adapter off) is the plain slider_lora_forward call");
+  return run_gemm(g, g->cin, g->cout, y, x, W, bias, A, B, nullptr, s, nullptr, nullptr, ws, ws_bytes,
+                  (cudaStream_t)stream, groups);
 }
 
 int slider_lora_input_grad(const slider_layer_geom* g, void* dx, const void* gy, const void* Wt, const void* dh,

@@ -194,6 +194,33 @@ class LoRAModule(nn.Module):
         return y.reshape(*lead, self._cout)
 
 
+class _QKVGroup:
+    """to_q / to_k / to_v adapters of one self-attention, issued as ONE grouped launch on the no-grad forwards."""
+
+    def __init__(self, loras, a_cat: torch.Tensor, b_cat: torch.Tensor):
+        self.loras, self.a_cat, self.b_cat = loras, a_cat, b_cat
+        self._w_cat = None
+
+    def usable(self, x: torch.Tensor) -> bool:
+        q = self.loras[0]
+        return (x.is_cuda and not torch.is_grad_enabled() and x.dtype == self.a_cat.dtype
+                and x.numel() // x.shape[-1] > 16 and all(m.multiplier == q.multiplier for m in self.loras))
+
+    def forward(self, x: torch.Tensor):
+        q = self.loras[0]
+        if self._w_cat is None or self._w_cat.dtype != x.dtype or self._w_cat.device != x.device:
+            self._w_cat = torch.cat([m._packed_base() for m in self.loras]).contiguous()      # frozen: built once
+        x2 = x.reshape(-1, q._cin)
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        s = float(q.multiplier) * float(q.scale)
+        if s == 0.0:        # adapter off (outside `with network:`): one plain GEMM over the concatenated weights
+            y, _ = ops.lora_forward(x2, self._w_cat, None, None, None, 0.0)
+        else:
+            y = ops.lora_forward_grouped(x2, self._w_cat, self.a_cat, self.b_cat, 3, s)
+        return y.reshape(*x.shape[:-1], 3 * q._cout).split(q._cout, dim=-1)
+
+
 class LoRANetwork(nn.Module):
     """Reference conceptmod/textsliders/lora.py:141-301; also accepts the upstream positional form
     `LoRANetwork(unet, rank, multiplier, alpha, train_method)` (trainscripts/imagesliders/lora.py:114-121)."""
@@ -312,23 +339,50 @@ class LoRANetwork(nn.Module):
         total = sum(p.numel() for p in params)
         flat = torch.empty(total, device=dev, dtype=dt)
         gflat = torch.zeros(total, device=dev, dtype=torch.float32)
-        off = 0
+        # self-attention q/k/v adapters read the same input: lay their factors out as [A_q;A_k;A_v][B_q;B_k;B_v] so
+        # that the concatenated operands of the grouped launch (ops.lora_forward_grouped) are plain views
+        by_name = {lora.lora_name: lora for lora in self.unet_loras}
+        groups, grouped = [], set()
         for lora in self.unet_loras:
-            a, b = lora.lora_down.weight, lora.lora_up.weight
-            r, T = lora.lora_dim, lora._ksize * lora._ksize
-            na, nb = a.numel(), b.numel()
-            fa, fb = flat[off:off + na], flat[off + na:off + na + nb]
-            if lora._is_conv:
-                fa4 = fa.view(r, lora._ksize, lora._ksize, lora._cin).permute(0, 3, 1, 2)
-                fa4.copy_(a.data)
-                a.data = fa4
+            if lora.lora_name.endswith("attn1_to_q"):
+                stem = lora.lora_name[:-1]
+                trio = [by_name.get(stem + c) for c in "qkv"]
+                if all(m is not None and not m._is_conv and m._cin == lora._cin and m._cout == lora._cout
+                       and m.lora_dim == lora.lora_dim and m._bias() is None for m in trio) \
+                        and 3 * lora.lora_dim <= 16 and lora._cout % 160 == 0:
+                    groups.append(trio)
+                    grouped.update(m.lora_name for m in trio)
+        units = [[m] for m in self.unet_loras if m.lora_name not in grouped] + groups
+        off = 0
+
+        def home(lora, which, start):
+            w = lora.lora_down.weight if which == "a" else lora.lora_up.weight
+            n = w.numel()
+            f = flat[start:start + n]
+            if which == "a" and lora._is_conv:
+                f4 = f.view(lora.lora_dim, lora._ksize, lora._ksize, lora._cin).permute(0, 3, 1, 2)
+                f4.copy_(w.data)
+                w.data = f4
             else:
-                fa.view_as(a).copy_(a.data)
-                a.data = fa.view_as(a)
-            fb.view_as(b).copy_(b.data)
-            b.data = fb.view_as(b)
-            lora._flat_grads = (gflat[off:off + na].view(r, T, lora._cin),
-                                gflat[off + na:off + na + nb].view(lora._cout, r))
-            off += na + nb
+                f.view_as(w).copy_(w.data)
+                w.data = f.view_as(w)
+            g = gflat[start:start + n]
+            return n, (g.view(lora.lora_dim, lora._ksize * lora._ksize, lora._cin) if which == "a"
+                       else g.view(lora._cout, lora.lora_dim))
+
+        for unit in units:
+            start = off
+            ga = []
+            for lora in unit:
+                n, g = home(lora, "a", off)
+                ga.append(g); off += n
+            mid = off
+            for lora, g_a in zip(unit, ga):
+                n, g_b = home(lora, "b", off)
+                lora._flat_grads = (g_a, g_b); off += n
+            if len(unit) == 3:
+                r, K, N = unit[0].lora_dim, unit[0]._cin, unit[0]._cout
+                group = _QKVGroup(unit, flat[start:mid].view(3 * r, 1, K), flat[mid:off].view(3 * N, r))
+                unit[0]._org._qkv_group = group
         self.flat_param, self.flat_grad = flat, gflat
         return flat, gflat

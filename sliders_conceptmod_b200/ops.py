@@ -60,6 +60,22 @@ def lora_forward(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None, a:
     return y, h
 
 
+def lora_forward_grouped(x: torch.Tensor, w_cat: torch.Tensor, a_cat: torch.Tensor, b_cat: torch.Tensor, groups: int,
+                         s: float) -> torch.Tensor:
+    """Several Linear adapters on one input in ONE launch (self-attention to_q/to_k/to_v):
+    x [M, K]; w_cat [groups*Ng, 1, K]; a_cat [groups*r, 1, K]; b_cat [groups*Ng, r] -> y [M, groups*Ng]."""
+    require_cuda(x, w_cat, a_cat, b_cat)
+    N, _, K = w_cat.shape
+    r = a_cat.shape[0] // groups
+    assert x.dim() == 2 and x.is_contiguous() and w_cat.is_contiguous() and a_cat.is_contiguous() and b_cat.is_contiguous()
+    g = make_geom(x.dtype, 1, 1, x.shape[0], K, N, 1, r)
+    y = torch.empty(x.shape[0], N, device=x.device, dtype=x.dtype)
+    ws = _gemm_workspace(x.device)
+    check(lib().slider_lora_forward_grouped(C.byref(g), ptr(y), ptr(x), ptr(w_cat), None, ptr(a_cat), ptr(b_cat),
+                                            int(groups), float(s), ptr(ws), ws.numel(), stream_ptr()))
+    return y
+
+
 def lora_input_grad(gy: torch.Tensor, wt: torch.Tensor, dh: torch.Tensor | None, at: torch.Tensor | None,
                     cin: int, ksize: int = 1, rank: int = 0) -> torch.Tensor:
     """dx = convT(gy, W) + convT(dh, A);  wt [Cin, k*k, Cout] flipped taps, at [Cin, k*k, 16]."""

@@ -188,8 +188,11 @@ class Attention(nn.Module):
         hit = None
         if context is not None and self._kv_cache is not None:
             hit = self._kv_cache.get(context.data_ptr())
+        grp = getattr(self.to_q, "_qkv_group", None) if context is None else None
         if hit is not None:
             q, (k, v) = self.to_q(x), hit
+        elif grp is not None and grp.usable(x):      # LoRANetwork.flatten(): q/k/v adapters in one grouped launch
+            q, k, v = grp.forward(x)
         else:
             q, k, v = self.to_q(x), self.to_k(ctx), self.to_v(ctx)
         q = q.view(B, L, self.heads, -1).transpose(1, 2)

@@ -78,3 +78,27 @@ def test_lora_forward_matches_torch(case, dtype):
     y0, _ = ops.lora_forward(xin, wd, bd, ad, bbd, 0.0, ksize=k)
     y0r, _ = _ref_forward(xd.float(), wd.float(), bd.float(), None, None, 0.0, k)
     assert (y0.float().reshape(y0r.shape) - y0r).abs().max().item() <= tol * y0r.abs().max().item()
+
+
+@pytest.mark.parametrize("M,K,Ng,groups,r", [(8192, 320, 320, 3, 4), (2048, 640, 640, 3, 4), (128, 1280, 1280, 3, 4),
+                                             (300, 320, 160, 4, 4), (512, 640, 320, 2, 8)])
+@pytest.mark.parametrize("dtype,tol", [(torch.bfloat16, 2e-2), (torch.float32, 5e-5)])
+def test_grouped_adapters_one_launch(M, K, Ng, groups, r, dtype, tol):
+    """slider_lora_forward_grouped == the per-adapter calls (to_q / to_k / to_v on one input), incl. split-K shapes."""
+    from sliders_conceptmod_b200 import ops
+    g = torch.Generator().manual_seed(M + K + groups)
+    x = torch.randn(M, K, generator=g).cuda().to(dtype)
+    W = [(torch.randn(Ng, 1, K, generator=g) / K ** 0.5).cuda().to(dtype) for _ in range(groups)]
+    A = [(torch.randn(r, 1, K, generator=g) / K ** 0.5).cuda().to(dtype) for _ in range(groups)]
+    B = [(torch.randn(Ng, r, generator=g) * 0.3).cuda().to(dtype) for _ in range(groups)]
+    s = 0.75
+    y = ops.lora_forward_grouped(x, torch.cat(W).contiguous(), torch.cat(A).contiguous(), torch.cat(B).contiguous(),
+                                 groups, s)
+    xd = x.double()
+    ref = torch.cat([xd @ W[i][:, 0].double().t() + s * (xd @ A[i][:, 0].double().t()) @ B[i].double().t()
+                     for i in range(groups)], dim=1)
+    err = (y.double() - ref).abs().max().item()
+    assert err <= tol * ref.abs().max().item(), f"max-abs {err:.3e} vs scale {ref.abs().max().item():.3e}"
+    # and it is the same arithmetic as the separate launches
+    sep = torch.cat([ops.lora_forward(x, W[i], None, A[i], B[i], s)[0] for i in range(groups)], dim=1)
+    assert (y.float() - sep.float()).abs().max().item() <= tol * ref.abs().max().item()

@@ -106,3 +106,61 @@ def test_train_iteration_matches_oracle(dtype, ltol, graphs):
         assert cosine(d_c[big], d_g[big]) >= 0.999
     assert cosine(pc, pg) >= 0.999
     print(f"updated-weight max-abs {(pc - pg).abs().max().item():.3e}")
+
+
+def test_flattened_network_groups_qkv_adapters():
+    """After LoRANetwork.flatten() the self-attention to_q/to_k/to_v adapters of a block run as ONE grouped launch on
+    no-grad forwards (adapter on) or one plain GEMM (adapter off); results equal the oracle's three separate modules,
+    state_dict / gradients keep their layout."""
+    from helpers import build_pair, cosine
+    from sliders_conceptmod_b200 import ops
+    from sliders_conceptmod_b200.unet import UNetConfig
+    cfg = UNetConfig(sample_size=16, block_out_channels=(320, 320), layers_per_block=1,
+                     down_block_types=("CrossAttnDownBlock2D", "DownBlock2D"),
+                     up_block_types=("UpBlock2D", "CrossAttnUpBlock2D"), transformer_layers_per_block=(1, 1),
+                     attention_head_dim=(8, 8), cross_attention_dim=64, norm_num_groups=32)
+    unet_c, net_c, unet_g, net_g = build_pair(cfg, "cuda", torch.float32)
+    sd_before = {k: v.clone() for k, v in net_g.state_dict().items()}
+    net_g.flatten()
+    groups = [m for m in unet_g.modules() if hasattr(m, "_qkv_group")]
+    n_blocks = sum(1 for n, _ in unet_g.named_modules() if n.endswith("attn1"))
+    assert len(groups) == n_blocks >= 3          # one per transformer block
+    for k, v in net_g.state_dict().items():
+        assert torch.equal(v, sd_before[k]), k
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(2, 4, 16, 16, generator=g)
+    emb = torch.randn(2, 77, cfg.cross_attention_dim, generator=g)
+    t = torch.tensor(481)
+    calls = {"grouped": 0}
+    real = ops.lora_forward_grouped
+
+    def spy(*a, **k):
+        calls["grouped"] += 1
+        return real(*a, **k)
+    ops.lora_forward_grouped = spy
+    try:
+        for scale in (1.5, 0.0):
+            net_c.set_lora_slider(scale); net_g.set_lora_slider(scale)
+            with torch.no_grad(), net_c, net_g:
+                y_c = unet_c(x, t, encoder_hidden_states=emb).sample
+                y_g = unet_g(x.cuda(), t.cuda(), encoder_hidden_states=emb.cuda()).sample
+            err = (y_g.cpu() - y_c).abs().max().item()
+            assert err <= 5e-3 * y_c.abs().max().item(), f"scale {scale}: max-abs {err}"
+    finally:
+        ops.lora_forward_grouped = real
+    assert calls["grouped"] == n_blocks     # adapter on: grouped launch; adapter off (scale 0): plain concatenated GEMM
+    # the grad forward still goes through the per-adapter path and fills the flat gradient buffer
+    net_c.set_lora_slider(1.0); net_g.set_lora_slider(1.0)
+    w = torch.randn(y_c.shape, generator=g)
+    with net_c:
+        (unet_c(x, t, encoder_hidden_states=emb).sample * w).sum().backward()
+    with net_g:
+        (unet_g(x.cuda(), t.cuda(), encoder_hidden_states=emb.cuda()).sample * w.cuda()).sum().backward()
+    def tap_major(lora):      # the flat gradient buffer stores conv lora_down gradients as [r, taps, cin]
+        ga = lora.lora_down.weight.grad
+        if ga.dim() == 4:
+            ga = ga.permute(0, 2, 3, 1)
+        return [ga.reshape(-1), lora.lora_up.weight.grad.reshape(-1)]
+    gc = torch.cat([f for lora in net_c.unet_loras for f in tap_major(lora)])
+    gg = torch.cat([f.flatten().cpu() for lora in net_g.unet_loras for f in lora._flat_grads])
+    assert cosine(gc, gg) >= 0.999
