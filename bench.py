@@ -105,32 +105,51 @@ def fused_gemm_roofline(engine, pk: dict, reps: int = 5) -> dict:
     timed with CUDA events: achieved = sum(algorithmic FLOPs) / sum(launch durations)."""
     from sliders_conceptmod_b200 import ops
     calls = []
-    real = ops.lora_forward
+    real, real_grouped = ops.lora_forward, ops.lora_forward_grouped
 
-    def spy(x, w, bias, a, b, s, ksize=1, want_h=False):
-        calls.append((tuple(x.shape), tuple(w.shape), bias is not None, None if a is None else a.shape[0], s, ksize, x.dtype))
-        return real(x, w, bias, a, b, s, ksize=ksize, want_h=want_h)
+    def spy(x, w, bias, a, b, s, ksize=1, want_h=False, residual=None):
+        calls.append(("single", tuple(x.shape), tuple(w.shape), bias is not None, None if a is None else a.shape[0], s,
+                      ksize, x.dtype, residual is not None))
+        return real(x, w, bias, a, b, s, ksize=ksize, want_h=want_h, residual=residual)
 
-    ops.lora_forward = spy
+    def spy_grouped(x, w_cat, a_cat, b_cat, groups, s):
+        calls.append(("grouped", tuple(x.shape), tuple(w_cat.shape), False, a_cat.shape[0], s, groups, x.dtype, False))
+        return real_grouped(x, w_cat, a_cat, b_cat, groups, s)
+
+    ops.lora_forward, ops.lora_forward_grouped = spy, spy_grouped
     try:
         engine._body_denoise()
     finally:
-        ops.lora_forward = real
+        ops.lora_forward, ops.lora_forward_grouped = real, real_grouped
     torch.cuda.synchronize()
     flops, args = 0.0, []
-    for (xs, ws, has_b, r, s, k, dt) in calls:
+    for (kind, xs, ws, has_b, r, s, k, dt, has_res) in calls:
         M = 1
         for d in xs[:-1]:
             M *= d
         N, T, C = ws
-        flops += 2.0 * M * N * T * C + (2.0 * M * r * (T * C + N) if r else 0.0)
         x = torch.randn(xs, device="cuda", dtype=dt)
         w = torch.randn(ws, device="cuda", dtype=dt) * 0.02
-        a = torch.randn(r, T, C, device="cuda", dtype=dt) * 0.02
-        b = torch.randn(N, r, device="cuda", dtype=dt) * 0.02
+        if kind == "grouped":
+            groups, rg = k, r // k
+            flops += 2.0 * M * N * C + 2.0 * M * r * C + 2.0 * M * rg * N
+            a = torch.randn(r, 1, C, device="cuda", dtype=dt) * 0.02
+            b = torch.randn(N, rg, device="cuda", dtype=dt) * 0.02
+            args.append(("grouped", x, w, a, b, groups, s))
+            continue
+        flops += 2.0 * M * N * T * C + (2.0 * M * r * (T * C + N) if r else 0.0)
+        a = torch.randn(r, T, C, device="cuda", dtype=dt) * 0.02 if r else None
+        b = torch.randn(N, r, device="cuda", dtype=dt) * 0.02 if r else None
         bias = torch.zeros(N, device="cuda", dtype=dt) if has_b else None
-        args.append((x, w, bias, a, b, s, k))
-    run = lambda: [real(x, w, bias, a, b, s, ksize=k) for (x, w, bias, a, b, s, k) in args]
+        res = torch.zeros(*xs[:-1], N, device="cuda", dtype=dt) if has_res else None
+        args.append(("single", x, w, bias, a, b, s, k, res))
+
+    def run():
+        for c in args:
+            if c[0] == "grouped":
+                real_grouped(*c[1:])
+            else:
+                real(c[1], c[2], c[3], c[4], c[5], c[6], ksize=c[7], residual=c[8])
     # capture the launch sequence in a CUDA graph so host-side descriptor encoding is not in the timing
     run(); torch.cuda.synchronize()
     g = torch.cuda.CUDAGraph()

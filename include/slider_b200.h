@@ -88,6 +88,19 @@ int slider_lora_forward(const slider_layer_geom* g, void* y, const void* x,
                         size_t ws_bytes, void* stream);
 
 /*
+ * slider_lora_forward with option flags.
+ *   SLIDER_FWD_ACCUMULATE: y already holds the residual branch and the layer result is ADDED to it by the store
+ *   (TMA reduce-add): `x = x + attn.to_out(...)`, `hidden = conv_shortcut(x) + conv2(h)`, `h + res` around the
+ *   wrapped projections of the UNet blocks (diffusers forward reached from train_util.py:290-294) without a
+ *   separate elementwise kernel.  Rounding equals `residual + module(x)` evaluated in the element dtype.
+ */
+#define SLIDER_FWD_ACCUMULATE 1u
+int slider_lora_forward_ex(const slider_layer_geom* g, void* y, const void* x,
+                           const void* W, const void* bias, const void* A,
+                           const void* B, float* h_out, float s, unsigned flags,
+                           void* ws, size_t ws_bytes, void* stream);
+
+/*
  * Several adapters on ONE input in one launch: the self-attention to_q / to_k / to_v of a transformer block
  * (three LoRAModule.forward calls on the same x, reference diffusers Attention.forward reached from
  * conceptmod/textsliders/train_util.py:290-294).  Operands are the row-wise concatenations

@@ -33,6 +33,7 @@ _SIGNATURES = {
     "slider_gemm_workspace_bytes": (_sz, []),
     "slider_debug_gemm_trace": (C.c_int, [_vp]),
     "slider_lora_forward": (C.c_int, [_G, _vp, _vp, _vp, _vp, _vp, _vp, _fp, _f, _vp, _sz, _vp]),
+    "slider_lora_forward_ex": (C.c_int, [_G, _vp, _vp, _vp, _vp, _vp, _vp, _fp, _f, C.c_uint, _vp, _sz, _vp]),
     "slider_lora_forward_grouped": (C.c_int, [_G, _vp, _vp, _vp, _vp, _vp, _vp, _i, _f, _vp, _sz, _vp]),
     "slider_lora_grad_workspace_bytes": (_sz, [_G]),
     "slider_lora_grad": (C.c_int, [_G, _fp, _fp, _vp, _vp, _vp, _fp, _vp, _f, _i, _vp, _sz, _vp]),

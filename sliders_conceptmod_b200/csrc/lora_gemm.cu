@@ -87,6 +87,7 @@ struct GemmParams {
   int ksplit;             // K partitions per tile (1 = no split)
   int total_units;        // total_tiles * ksplit
   float* partial;         // split-K partial tiles, [unit][NCHUNK][128][32] fp32
+  int accumulate;         // y += result (y holds the residual branch) instead of y = result
   int group_n;            // grouped adapters: output columns per group (0 = one adapter); group g uses h columns [g*rank, (g+1)*rank)
   long long* trace;       // debug: 8 clock64() stamps per CTA (NULL = off)
   void* y;
@@ -424,7 +425,8 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (et == 0) ptx::bulk_wait_read<1>();       // buffer of the NEXT chunk (store c-2) is free past the barrier
         asm volatile("bar.sync 1, 128;" ::: "memory");
         if (et == 0) {
-          ptx::tma_store_4d(&tmY, out_base + ob * OUT_BYTES, tc.n0 + c * 32, tc.w0, tc.h0, tc.b0);
+          if (p.accumulate) ptx::tma_reduce_add_4d(&tmY, out_base + ob * OUT_BYTES, tc.n0 + c * 32, tc.w0, tc.h0, tc.b0);
+          else ptx::tma_store_4d(&tmY, out_base + ob * OUT_BYTES, tc.n0 + c * 32, tc.w0, tc.h0, tc.b0);
           ptx::bulk_commit();
         }
         if (++ob == OUT_BUFS) ob = 0;
@@ -505,6 +507,17 @@ splitk_finalize_kernel(const GemmParams p) {
     o[k] = a;
   }
   T* dst = reinterpret_cast<T*>(p.y) + pix * (size_t)p.N + n;
+  if (p.accumulate) {      // y holds the residual: same two roundings as `residual + module(x)` in element dtype
+    float res[8];
+    if (sizeof(T) == 2) {
+      Elem<__nv_bfloat16>::load(reinterpret_cast<const __nv_bfloat16*>(dst), res);
+    } else {
+      const float4 r0 = *reinterpret_cast<const float4*>(dst), r1 = *(reinterpret_cast<const float4*>(dst) + 1);
+      res[0] = r0.x; res[1] = r0.y; res[2] = r0.z; res[3] = r0.w; res[4] = r1.x; res[5] = r1.y; res[6] = r1.z; res[7] = r1.w;
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) o[k] = Elem<T>::to_f(Elem<T>::from_f(o[k])) + res[k];
+  }
   if (sizeof(T) == 2) {
     Elem<__nv_bfloat16>::store(reinterpret_cast<__nv_bfloat16*>(dst), o);
   } else {
@@ -715,7 +728,7 @@ static int launch_gemv(const slider_layer_geom* g, int M, void* y, const void* x
 //   xe / we  [B,H,W,16] / [nn, taps, 16]  extended-K pair (input gradient only)
 static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const void* act, const void* wgt,
                     const void* bias, const void* lo, const void* Bup, float* h_out, float s, const void* xe,
-                    const void* we, void* ws, size_t ws_bytes, cudaStream_t st, int groups = 1) {
+                    const void* we, void* ws, size_t ws_bytes, cudaStream_t st, int groups = 1, int accumulate = 0) {
   const int es = esize(g->dtype);
   const int taps = g->kh * g->kw;
   const int bk = ROW_BYTES / es;
@@ -743,7 +756,7 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
     // small-M path: a 128-row tensor-core tile would be > 87 % padding and the op is weight-bandwidth bound
     const long long M = (long long)g->batch * g->height * g->width;
     const size_t mt = M <= 2 ? 2 : (M <= 4 ? 4 : (M <= 8 ? 8 : 16));
-    if (groups == 1 && !ext && taps == 1 && M <= 16 && mt * kc * sizeof(float) <= 40 * 1024 && kc * es <= 8 * 32 * 16 &&
+    if (groups == 1 && !accumulate && !ext && taps == 1 && M <= 16 && mt * kc * sizeof(float) <= 40 * 1024 && kc * es <= 8 * 32 * 16 &&
         ((uintptr_t)wgt & 15) == 0 && (lo == nullptr || ((uintptr_t)lo & 15) == 0)) {
       if (g->dtype == SLIDER_BF16)
         return launch_gemv<__nv_bfloat16>(g, (int)M, y, act, wgt, bias, lo, Bup, lora ? h_out : nullptr, s, lora, st);
@@ -762,6 +775,7 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
   p.taps = taps; p.kw = g->kw; p.pad = g->pad; p.cblocks = (kc + bk - 1) / bk;
   p.rank = g->rank; p.s = s; p.lora = lora ? 1 : 0; p.ext = ext ? 1 : 0;
   p.group_n = groups > 1 ? nn / groups : 0;
+  p.accumulate = accumulate ? 1 : 0;
   p.total_tiles = p.mt_w * p.mt_h * p.mt_b * p.n_tiles;
   p.per_tap = p.cblocks + (ext ? 1 : 0);
   p.kiters = taps * p.per_tap;
@@ -856,6 +870,15 @@ int slider_lora_forward(const slider_layer_geom* g, void* y, const void* x, cons
   SLIDER_CHECK_ARG(g && y && x && W, "lora_forward: null pointer");
   return run_gemm(g, g->cin, g->cout, y, x, W, bias, A, B, h_out, s, nullptr, nullptr, ws, ws_bytes,
                   (cudaStream_t)stream);
+}
+
+int slider_lora_forward_ex(const slider_layer_geom* g, void* y, const void* x, const void* W, const void* bias,
+                           const void* A, const void* B, float* h_out, float s, unsigned flags, void* ws,
+                           size_t ws_bytes, void* stream) {
+  SLIDER_CHECK_ARG(g && y && x && W, "lora_forward_ex: null pointer");
+  SLIDER_CHECK_ARG((flags & ~(unsigned)SLIDER_FWD_ACCUMULATE) == 0, "lora_forward_ex: unknown flags 0x%x", flags);
+  return run_gemm(g, g->cin, g->cout, y, x, W, bias, A, B, h_out, s, nullptr, nullptr, ws, ws_bytes,
+                  (cudaStream_t)stream, 1, (flags & SLIDER_FWD_ACCUMULATE) ? 1 : 0);
 }
 
 int slider_lora_forward_grouped(const slider_layer_geom* g, void* y, const void* x, const void* W, const void* bias,

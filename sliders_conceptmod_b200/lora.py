@@ -120,6 +120,7 @@ class LoRAModule(nn.Module):
         self.org_forward = self.org_module.forward
         self.org_module.forward = self.forward
         self.__dict__["_org"] = self.org_module       # plain reference, not a registered submodule
+        self.org_module.__dict__["_lora_module"] = self   # lets the UNet ask for the residual-fused form
         del self.org_module
 
     # ---- operand views / one-time re-layouts ------------------------------------------------
@@ -192,6 +193,35 @@ class LoRAModule(nn.Module):
             x2 = x2.contiguous()
         y = _FusedLoRAFn.apply(x2, a_w, b_w, self)
         return y.reshape(*lead, self._cout)
+
+
+def residual_forward(mod: LoRAModule, x: torch.Tensor, residual: torch.Tensor):
+    """`residual + mod.forward(x)` with the sum formed by the GEMM's store, IN PLACE of `residual` (no-grad
+    forwards only; the caller guarantees nobody else needs `residual`).  Returns None when the layouts do not allow
+    it (the caller then adds with torch)."""
+    a_w, b_w = mod.lora_down.weight, mod.lora_up.weight
+    if a_w.dtype != x.dtype or residual.dtype != x.dtype or mod._stride != 1:
+        return None
+    s = float(mod.multiplier) * float(mod.scale)
+    if mod._is_conv:
+        xn, rn = x.permute(0, 2, 3, 1), residual.permute(0, 2, 3, 1)
+        if not rn.is_contiguous():
+            return None
+        if not xn.is_contiguous():
+            xn = xn.contiguous()
+        y, _ = ops.lora_forward(xn, mod._packed_base(), mod._bias(), mod._packed_down(a_w), mod._packed_up(b_w), s,
+                                ksize=mod._ksize, residual=rn)
+        return y.permute(0, 3, 1, 2)
+    if not residual.is_contiguous() or residual.shape[:-1] != x.shape[:-1]:
+        return None
+    x2 = x.reshape(-1, mod._cin)
+    if not x2.is_contiguous():
+        x2 = x2.contiguous()
+    if x2.shape[0] <= 16:
+        return None
+    y, _ = ops.lora_forward(x2, mod._packed_base(), mod._bias(), mod._packed_down(a_w), mod._packed_up(b_w), s,
+                            residual=residual.view(-1, mod._cout))
+    return y.view(residual.shape)
 
 
 class _QKVGroup:

@@ -40,23 +40,34 @@ def _gemm_workspace(device: torch.device) -> torch.Tensor:
 
 
 def lora_forward(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None, a: torch.Tensor | None,
-                 b: torch.Tensor | None, s: float, ksize: int = 1, want_h: bool = False):
+                 b: torch.Tensor | None, s: float, ksize: int = 1, want_h: bool = False,
+                 residual: torch.Tensor | None = None):
     """y = conv(x, w) + bias + s * (conv(x, a) @ b^T).   (lora.py:134-138)
 
     x [B,H,W,Cin] | [M,Cin];  w [Cout, k*k, Cin];  a [r, k*k, Cin];  b [Cout, r].
     Returns (y, h) with h = conv(x, a) in fp32 ([pixels, r]) when want_h else None.
+    `residual` (contiguous, shaped like y): the result is added INTO it by the store and it is returned as y.
     """
-    require_cuda(x, w, bias, a, b)
+    require_cuda(x, w, bias, a, b, residual)
     assert x.is_contiguous() and w.is_contiguous()
     B, H, W = _act_dims(x)
     cin, cout = x.shape[-1], w.shape[0]
     rank = 0 if a is None else a.shape[0]
     g = make_geom(x.dtype, B, H, W, cin, cout, ksize, rank)
-    y = torch.empty(*x.shape[:-1], cout, device=x.device, dtype=x.dtype)
+    if residual is not None:
+        if not residual.is_contiguous() or residual.dtype != x.dtype or residual.numel() != B * H * W * cout:
+            raise ValueError("lora_forward: residual must be contiguous, of the activation dtype and shaped like y")
+        y = residual
+    else:
+        y = torch.empty(*x.shape[:-1], cout, device=x.device, dtype=x.dtype)
     h = torch.empty(B * H * W, rank, device=x.device, dtype=torch.float32) if (want_h and rank > 0) else None
     ws = _gemm_workspace(x.device)
-    check(lib().slider_lora_forward(C.byref(g), ptr(y), ptr(x), ptr(w), ptr(bias), ptr(a), ptr(b), ptr(h),
-                                    float(s), ptr(ws), ws.numel(), stream_ptr()))
+    if residual is not None:
+        check(lib().slider_lora_forward_ex(C.byref(g), ptr(y), ptr(x), ptr(w), ptr(bias), ptr(a), ptr(b), ptr(h),
+                                           float(s), 1, ptr(ws), ws.numel(), stream_ptr()))
+    else:
+        check(lib().slider_lora_forward(C.byref(g), ptr(y), ptr(x), ptr(w), ptr(bias), ptr(a), ptr(b), ptr(h),
+                                        float(s), ptr(ws), ws.numel(), stream_ptr()))
     return y, h
 
 

@@ -13,6 +13,8 @@ hand their input to the TMA-fed implicit-GEMM kernel without a transpose.
 """
 from __future__ import annotations
 
+import os
+
 import math
 from dataclasses import dataclass, field
 from types import SimpleNamespace
@@ -96,6 +98,10 @@ class TimestepEmbedding(nn.Module):
         return self.linear_2(self.act(self.linear_1(x)))
 
 
+# A/B switch for measurements: SLIDER_DISABLE=residual,qkv,kvcache turns individual host-level fusions off
+_DISABLED = set(filter(None, os.environ.get("SLIDER_DISABLE", "").split(",")))
+
+
 def group_norm_act(norm: nn.GroupNorm, x: torch.Tensor, silu: bool, chan_add: torch.Tensor | None = None):
     """act(GroupNorm(x + chan_add[:, :, None, None])) for a [B,C,H,W] tensor.
 
@@ -120,6 +126,19 @@ def _no_grad_cuda(*ts) -> bool:
     return first.is_cuda and not (torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in ts))
 
 
+def add_residual(mod: nn.Module, x: torch.Tensor, residual: torch.Tensor) -> torch.Tensor:
+    """`residual + mod(x)`.  When `mod` is LoRA-wrapped and no gradient is recorded, the fused GEMM adds its result
+    into `residual` in place (TMA reduce-add store) instead of launching an elementwise kernel — callers pass a
+    `residual` nobody else reads afterwards."""
+    lora = mod.__dict__.get("_lora_module")
+    if lora is not None and _no_grad_cuda(x, residual) and "residual" not in _DISABLED:
+        from .lora import residual_forward
+        out = residual_forward(lora, x, residual)
+        if out is not None:
+            return out
+    return residual + mod(x)
+
+
 def layer_norm_fused(norm: nn.LayerNorm, x: torch.Tensor) -> torch.Tensor:
     if _no_grad_cuda(x) and x.shape[-1] % 8 == 0:
         return ops.layernorm(x.contiguous(), norm.weight, norm.bias, norm.eps)
@@ -141,10 +160,10 @@ class ResnetBlock2D(nn.Module):
     def forward(self, x, temb):
         h = self.conv1(group_norm_act(self.norm1, x, True))
         t = self.time_emb_proj(temb if getattr(temb, "_silu_applied", False) else self.nonlinearity(temb))
-        h = self.conv2(self.dropout(group_norm_act(self.norm2, h, True, chan_add=t)))   # norm2(h + t)
-        if self.conv_shortcut is not None:
-            x = self.conv_shortcut(x)
-        return x + h
+        h = self.dropout(group_norm_act(self.norm2, h, True, chan_add=t))   # norm2(h + t)
+        if self.conv_shortcut is not None:      # fresh tensor: conv2 may accumulate into it
+            return add_residual(self.conv2, h, self.conv_shortcut(x))
+        return x + self.conv2(h)                # x is a skip connection of the up path: keep it intact
 
 
 class Downsample2D(nn.Module):
@@ -182,7 +201,8 @@ class Attention(nn.Module):
         """True when to_k / to_v are plain frozen projections (not LoRA-wrapped: their forward is unpatched)."""
         return not any("forward" in m.__dict__ or m.weight.requires_grad for m in (self.to_k, self.to_v))
 
-    def forward(self, x, context=None):
+    def forward(self, x, context=None, residual=None):
+        """`residual`: when given, returns residual + attention(x) (the caller gives up `residual`)."""
         ctx = x if context is None else context
         B, L, _ = x.shape
         hit = None
@@ -191,7 +211,7 @@ class Attention(nn.Module):
         grp = getattr(self.to_q, "_qkv_group", None) if context is None else None
         if hit is not None:
             q, (k, v) = self.to_q(x), hit
-        elif grp is not None and grp.usable(x):      # LoRANetwork.flatten(): q/k/v adapters in one grouped launch
+        elif grp is not None and "qkv" not in _DISABLED and grp.usable(x):      # LoRANetwork.flatten(): q/k/v adapters in one grouped launch
             q, k, v = grp.forward(x)
         else:
             q, k, v = self.to_q(x), self.to_k(ctx), self.to_v(ctx)
@@ -200,6 +220,8 @@ class Attention(nn.Module):
         v = v.view(B, ctx.shape[1], self.heads, -1).transpose(1, 2)
         o = F.scaled_dot_product_attention(q, k, v)
         o = o.transpose(1, 2).reshape(B, L, -1)
+        if residual is not None:
+            return add_residual(self.to_out[0], o, residual)      # to_out[1] is Dropout(0.0)
         return self.to_out[1](self.to_out[0](o))
 
 
@@ -221,10 +243,11 @@ class FeedForward(nn.Module):
         super().__init__()
         self.net = nn.ModuleList([GEGLU(dim, dim * 4), nn.Dropout(0.0), nn.Linear(dim * 4, dim)])
 
-    def forward(self, x):
-        for m in self.net:
-            x = m(x)
-        return x
+    def forward(self, x, residual=None):
+        x = self.net[1](self.net[0](x))
+        if residual is not None:
+            return add_residual(self.net[2], x, residual)
+        return self.net[2](x)
 
 
 class BasicTransformerBlock(nn.Module):
@@ -238,9 +261,10 @@ class BasicTransformerBlock(nn.Module):
         self.ff = FeedForward(dim)
 
     def forward(self, x, context):
-        x = x + self.attn1(layer_norm_fused(self.norm1, x))
-        x = x + self.attn2(layer_norm_fused(self.norm2, x), context)
-        return x + self.ff(layer_norm_fused(self.norm3, x))
+        # x is this block's private running sum (Transformer2DModel hands in a fresh tensor): branches add into it
+        x = self.attn1(layer_norm_fused(self.norm1, x), residual=x)
+        x = self.attn2(layer_norm_fused(self.norm2, x), context, residual=x)
+        return self.ff(layer_norm_fused(self.norm3, x), residual=x)
 
 
 class Transformer2DModel(nn.Module):
@@ -264,12 +288,14 @@ class Transformer2DModel(nn.Module):
             h = self.proj_in(h)
         for blk in self.transformer_blocks:
             h = blk(h, context)
+        # `res` (the preceding ResNet's output) is only read here: proj_out may add into it
         if self.linear_proj:
+            r = res.permute(0, 2, 3, 1)
+            if r.is_contiguous():
+                return add_residual(self.proj_out, h, r.reshape(B, H * W, C)).reshape(B, H, W, C).permute(0, 3, 1, 2)
             h = self.proj_out(h)
-        h = h.reshape(B, H, W, C).permute(0, 3, 1, 2)
-        if not self.linear_proj:
-            h = self.proj_out(h)
-        return h + res
+            return h.reshape(B, H, W, C).permute(0, 3, 1, 2) + res
+        return add_residual(self.proj_out, h.reshape(B, H, W, C).permute(0, 3, 1, 2), res)
 
 
 def _heads(cfg: UNetConfig, level: int, ch: int) -> tuple[int, int]:
@@ -411,6 +437,8 @@ class UNet2DConditionModel(nn.Module):
         `noxattn` family) K and V depend only on the prompt, so they are kept in persistent buffers and refreshed by
         `refresh_context_cache()` whenever the buffers' contents change — the reference recomputes them in each of
         the ~29 UNet calls of an iteration (train_util.py:290-294).  Results are bit-identical."""
+        if "kvcache" in _DISABLED:
+            return
         self._ctx_buffers = list(contexts)
         self._ctx_attn = [m for n, m in self.named_modules() if isinstance(m, Attention) and n.endswith("attn2")
                           and m.kv_cacheable()]

@@ -102,3 +102,30 @@ def test_grouped_adapters_one_launch(M, K, Ng, groups, r, dtype, tol):
     # and it is the same arithmetic as the separate launches
     sep = torch.cat([ops.lora_forward(x, W[i], None, A[i], B[i], s)[0] for i in range(groups)], dim=1)
     assert (y.float() - sep.float()).abs().max().item() <= tol * ref.abs().max().item()
+
+
+@pytest.mark.parametrize("shape", [(1, 1, 8192, 320, 320, 1), (1, 1, 300, 640, 640, 1), (2, 16, 16, 1280, 1280, 3),
+                                   (2, 32, 32, 640, 320, 1), (2, 20, 12, 64, 96, 3), (1, 1, 128, 1280, 1280, 1)])
+@pytest.mark.parametrize("dtype,tol", [(torch.bfloat16, 2e-2), (torch.float32, 5e-5)])
+def test_residual_accumulate_store(shape, dtype, tol):
+    """SLIDER_FWD_ACCUMULATE: y (pre-loaded with the residual) += layer(x), tile path and split-K path."""
+    from sliders_conceptmod_b200 import ops
+    B, H, W, C, N, k = shape
+    g = torch.Generator().manual_seed(sum(shape))
+    lin = (k == 1 and B == 1 and H == 1)
+    x = torch.randn(*((W, C) if lin else (B, H, W, C)), generator=g).cuda().to(dtype)
+    w = (torch.randn(N, k * k, C, generator=g) / (C * k * k) ** 0.5).cuda().to(dtype)
+    a = (torch.randn(4, k * k, C, generator=g) / (C * k * k) ** 0.5).cuda().to(dtype)
+    b = (torch.randn(N, 4, generator=g) * 0.3).cuda().to(dtype)
+    bias = torch.randn(N, generator=g).cuda().to(dtype)
+    res = torch.randn(*x.shape[:-1], N, generator=g).cuda().to(dtype)
+    for s in (0.5, 0.0):
+        plain, _ = ops.lora_forward(x, w, bias, a, b, s, ksize=k)
+        want = (res.float() + plain.float()).to(dtype)            # `residual + module(x)` in the element dtype
+        r = res.clone()
+        got, _ = ops.lora_forward(x, w, bias, a, b, s, ksize=k, residual=r)
+        assert got.data_ptr() == r.data_ptr()
+        err = (got.float() - want.float()).abs().max().item()
+        assert err <= tol * want.float().abs().max().item(), f"s={s}: max-abs {err:.3e}"
+        if dtype == torch.bfloat16:       # same two roundings as torch: at most 1 bf16 ulp apart, mostly identical
+            assert (got != want).float().mean().item() < 0.02
