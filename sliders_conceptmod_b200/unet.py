@@ -100,6 +100,7 @@ class TimestepEmbedding(nn.Module):
 
 # A/B switch for measurements: SLIDER_DISABLE=residual,qkv,kvcache turns individual host-level fusions off
 _DISABLED = set(filter(None, os.environ.get("SLIDER_DISABLE", "").split(",")))
+_ENABLED = set(filter(None, os.environ.get("SLIDER_ENABLE", "").split(",")))
 
 
 def group_norm_act(norm: nn.GroupNorm, x: torch.Tensor, silu: bool, chan_add: torch.Tensor | None = None):
@@ -126,17 +127,55 @@ def _no_grad_cuda(*ts) -> bool:
     return first.is_cuda and not (torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in ts))
 
 
-def add_residual(mod: nn.Module, x: torch.Tensor, residual: torch.Tensor) -> torch.Tensor:
-    """`residual + mod(x)`.  When `mod` is LoRA-wrapped and no gradient is recorded, the fused GEMM adds its result
-    into `residual` in place (TMA reduce-add store) instead of launching an elementwise kernel — callers pass a
-    `residual` nobody else reads afterwards."""
+def fused_linear(mod: nn.Module, x: torch.Tensor, residual: torch.Tensor | None = None) -> torch.Tensor:
+    """`mod(x)` (+ `residual`) for an nn.Linear on [..., K] or a 1x1 nn.Conv2d on [B,C,H,W].
+
+    On no-grad CUDA forwards every such projection of the UNet runs in libslider's tcgen05 GEMM: LoRA-wrapped modules
+    through their patched forward (adapter fused); frozen un-wrapped ones (attn2, feed-forward, proj_in/out — SURVEY
+    8 f1) stay on cuBLAS unless SLIDER_ENABLE=plain routes them through the same kernel's plain path.  With `residual` the sum is formed by the kernel's store IN PLACE of
+    `residual` (TMA reduce-add) instead of an elementwise kernel — callers pass a `residual` nobody else reads
+    afterwards.  Everything else (CPU oracle, grad-recording forward) is the plain PyTorch expression."""
+    fused = _no_grad_cuda(x, residual) and x.dtype == mod.weight.dtype
     lora = mod.__dict__.get("_lora_module")
-    if lora is not None and _no_grad_cuda(x, residual) and "residual" not in _DISABLED:
-        from .lora import residual_forward
-        out = residual_forward(lora, x, residual)
-        if out is not None:
-            return out
-    return residual + mod(x)
+    if fused and lora is not None:
+        if residual is not None and "residual" not in _DISABLED:
+            from .lora import residual_forward
+            out = residual_forward(lora, x, residual)
+            if out is not None:
+                return out
+        fused = False
+    # frozen un-wrapped projections: cuBLAS is measured ~2.5 % faster per denoise forward than the plain path of the
+    # fused kernel on these small shapes (tools/ab_fusions.sh), so this routing is opt-in: SLIDER_ENABLE=plain
+    if fused and lora is None and "plain" in _ENABLED and not mod.weight.requires_grad:
+        res = residual if "residual" not in _DISABLED else None
+        if isinstance(mod, nn.Linear):
+            K, N = mod.in_features, mod.out_features
+            x2 = x.reshape(-1, K)
+            ok = x2.shape[0] > 16 and K % 8 == 0 and N % 8 == 0 and (res is None or res.is_contiguous())
+            if ok:
+                if not x2.is_contiguous():
+                    x2 = x2.contiguous()
+                y, _ = ops.lora_forward(x2, mod.weight.view(N, 1, K), mod.bias, None, None, 0.0,
+                                        residual=None if res is None else res.view(-1, N))
+                y = y.view(*x.shape[:-1], N)
+                return y if (res is not None or residual is None) else residual + y
+        elif isinstance(mod, nn.Conv2d) and mod.kernel_size == (1, 1) and mod.stride == (1, 1) and mod.groups == 1:
+            K, N = mod.in_channels, mod.out_channels
+            rn = None if res is None else res.permute(0, 2, 3, 1)
+            if K % 8 == 0 and N % 8 == 0 and (rn is None or rn.is_contiguous()):
+                xn = x.permute(0, 2, 3, 1)
+                if not xn.is_contiguous():
+                    xn = xn.contiguous()
+                y, _ = ops.lora_forward(xn, mod.weight.reshape(N, 1, K), mod.bias, None, None, 0.0, residual=rn)
+                y = y.permute(0, 3, 1, 2)
+                return y if (res is not None or residual is None) else residual + y
+    y = mod(x)
+    return y if residual is None else residual + y
+
+
+def add_residual(mod: nn.Module, x: torch.Tensor, residual: torch.Tensor) -> torch.Tensor:
+    """`residual + mod(x)`; see fused_linear (3x3 LoRA-wrapped convolutions take the same in-place store)."""
+    return fused_linear(mod, x, residual)
 
 
 def layer_norm_fused(norm: nn.LayerNorm, x: torch.Tensor) -> torch.Tensor:
@@ -210,11 +249,11 @@ class Attention(nn.Module):
             hit = self._kv_cache.get(context.data_ptr())
         grp = getattr(self.to_q, "_qkv_group", None) if context is None else None
         if hit is not None:
-            q, (k, v) = self.to_q(x), hit
+            q, (k, v) = fused_linear(self.to_q, x), hit
         elif grp is not None and "qkv" not in _DISABLED and grp.usable(x):      # LoRANetwork.flatten(): q/k/v adapters in one grouped launch
             q, k, v = grp.forward(x)
         else:
-            q, k, v = self.to_q(x), self.to_k(ctx), self.to_v(ctx)
+            q, k, v = fused_linear(self.to_q, x), fused_linear(self.to_k, ctx), fused_linear(self.to_v, ctx)
         q = q.view(B, L, self.heads, -1).transpose(1, 2)
         k = k.view(B, ctx.shape[1], self.heads, -1).transpose(1, 2)
         v = v.view(B, ctx.shape[1], self.heads, -1).transpose(1, 2)
@@ -222,7 +261,7 @@ class Attention(nn.Module):
         o = o.transpose(1, 2).reshape(B, L, -1)
         if residual is not None:
             return add_residual(self.to_out[0], o, residual)      # to_out[1] is Dropout(0.0)
-        return self.to_out[1](self.to_out[0](o))
+        return self.to_out[1](fused_linear(self.to_out[0], o))
 
 
 class GEGLU(nn.Module):
@@ -231,7 +270,7 @@ class GEGLU(nn.Module):
         self.proj = nn.Linear(dim_in, dim_out * 2)
 
     def forward(self, x):
-        h = self.proj(x)
+        h = fused_linear(self.proj, x)
         if _no_grad_cuda(h) and h.shape[-1] % 16 == 0:
             return ops.geglu(h.contiguous())
         x, gate = h.chunk(2, dim=-1)
@@ -247,7 +286,7 @@ class FeedForward(nn.Module):
         x = self.net[1](self.net[0](x))
         if residual is not None:
             return add_residual(self.net[2], x, residual)
-        return self.net[2](x)
+        return fused_linear(self.net[2], x)
 
 
 class BasicTransformerBlock(nn.Module):
@@ -282,10 +321,10 @@ class Transformer2DModel(nn.Module):
         res = x
         h = group_norm_act(self.norm, x, False)
         if not self.linear_proj:
-            h = self.proj_in(h)
+            h = fused_linear(self.proj_in, h)
         h = h.permute(0, 2, 3, 1).reshape(B, H * W, C)   # a view when h is channels_last
         if self.linear_proj:
-            h = self.proj_in(h)
+            h = fused_linear(self.proj_in, h)
         for blk in self.transformer_blocks:
             h = blk(h, context)
         # `res` (the preceding ResNet's output) is only read here: proj_out may add into it
@@ -293,7 +332,7 @@ class Transformer2DModel(nn.Module):
             r = res.permute(0, 2, 3, 1)
             if r.is_contiguous():
                 return add_residual(self.proj_out, h, r.reshape(B, H * W, C)).reshape(B, H, W, C).permute(0, 3, 1, 2)
-            h = self.proj_out(h)
+            h = fused_linear(self.proj_out, h)
             return h.reshape(B, H, W, C).permute(0, 3, 1, 2) + res
         return add_residual(self.proj_out, h.reshape(B, H, W, C).permute(0, 3, 1, 2), res)
 
