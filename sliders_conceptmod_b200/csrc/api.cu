@@ -1,4 +1,5 @@
 // Library-wide state: version, thread-local error text, launch counter.
+#include <stdlib.h>
 #include "common.cuh"
 #include <string.h>
 
@@ -12,6 +13,15 @@ void set_error(const char* fmt, ...) {
   va_start(ap, fmt);
   vsnprintf(t_err, sizeof(t_err), fmt, ap);
   va_end(ap);
+}
+
+bool pdl_enabled() {
+  static int cached = -1;
+  if (cached < 0) {
+    const char* e = getenv("SLIDER_PDL");
+    cached = (e != nullptr && e[0] == '1') ? 1 : 0;      // measured neutral-to-slightly-negative on B200 (profiles/r01_ab_pdl.txt): opt-in
+  }
+  return cached == 1;
 }
 
 int sm_count() {

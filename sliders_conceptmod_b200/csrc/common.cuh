@@ -46,6 +46,29 @@ inline int post_launch(const char* what) {
 
 int sm_count();
 
+// ---- programmatic dependent launch (PDL) -----------------------------------------------------
+// Every forward-path kernel starts with pdl_trigger() + pdl_wait(): the next kernel in the stream may be made
+// resident while this one still runs (its launch latency and prologue overlap our tail), and nothing of ours
+// touches global memory before the previous kernel has completed and flushed.  Both are no-ops for a launch
+// without the attribute, which is only set when SLIDER_PDL=1 is in the environment (opt-in: the A/B on B200 showed
+// no gain, profiles/r01_ab_pdl.txt).
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+bool pdl_enabled();
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                              Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
 // ---- element access ---------------------------------------------------------
 template <typename T> struct Elem;
 template <> struct Elem<float> {

@@ -115,6 +115,8 @@ __global__ void __launch_bounds__(kThreads)
 cfg_step_kernel(T* __restrict__ out, const T* __restrict__ x, const T* __restrict__ eu,
                 const T* __restrict__ ec, const T* __restrict__ nz, int64_t n_elem, float g,
                 float cx, float ce, float cn, const float* __restrict__ dev_coef) {
+  pdl_trigger();
+  pdl_wait();
   constexpr int V = Elem<T>::kVec;
   if (dev_coef != nullptr) {
     g = __ldg(dev_coef); cx = __ldg(dev_coef + 1); ce = __ldg(dev_coef + 2); cn = __ldg(dev_coef + 3);
@@ -273,14 +275,13 @@ int slider_cfg_step(void* out, const void* x, const void* eps_u, const void* eps
   cudaStream_t st = (cudaStream_t)stream;
   if (dtype == SLIDER_F32) {
     const int grid = grid_for(n_elem / 4, 2);
-    cfg_step_kernel<float><<<grid, kThreads, 0, st>>>((float*)out, (const float*)x, (const float*)eps_u,
-                                                      (const float*)eps_c, (const float*)noise, n_elem, g,
-                                                      c_x, c_eps, c_noise, dev_coef);
+    launch_pdl(cfg_step_kernel<float>, dim3(grid), dim3(kThreads), 0, st, (float*)out, (const float*)x,
+               (const float*)eps_u, (const float*)eps_c, (const float*)noise, n_elem, g, c_x, c_eps, c_noise, dev_coef);
   } else if (dtype == SLIDER_BF16) {
     typedef __nv_bfloat16 T;
     const int grid = grid_for(n_elem / 8, 2);
-    cfg_step_kernel<T><<<grid, kThreads, 0, st>>>((T*)out, (const T*)x, (const T*)eps_u, (const T*)eps_c,
-                                                  (const T*)noise, n_elem, g, c_x, c_eps, c_noise, dev_coef);
+    launch_pdl(cfg_step_kernel<T>, dim3(grid), dim3(kThreads), 0, st, (T*)out, (const T*)x, (const T*)eps_u,
+               (const T*)eps_c, (const T*)noise, n_elem, g, c_x, c_eps, c_noise, dev_coef);
   } else {
     set_error("cfg_step: unsupported dtype %d", dtype);
     return SLIDER_ERR_UNSUPPORTED;

@@ -49,6 +49,8 @@ template <typename T>
 __global__ void __launch_bounds__(GN_MAX_THREADS)
 gn_stats_kernel(const T* __restrict__ x, const T* __restrict__ chan_add, float* __restrict__ partial,
                 const GnParams p) {
+  pdl_trigger();
+  pdl_wait();
   extern __shared__ __align__(16) float gn_smem[];
   float* s_sum = gn_smem;                       // [PL][C]
   float* s_sq = gn_smem + (size_t)p.PL * p.C;   // [PL][C]
@@ -106,6 +108,8 @@ __global__ void __launch_bounds__(256)
 gn_apply_kernel(T* __restrict__ y, const T* __restrict__ x, const T* __restrict__ chan_add,
                 const T* __restrict__ gamma, const T* __restrict__ beta, const float* __restrict__ partial,
                 const GnParams p, int chunks, int ppc) {
+  pdl_trigger();
+  pdl_wait();
   extern __shared__ __align__(16) float gn_smem[];
   float* s_scale = gn_smem;             // [C]
   float* s_shift = gn_smem + p.C;       // [C]
@@ -193,8 +197,7 @@ static int groupnorm_impl(void* y, const void* x, const void* chan_add, const vo
     const size_t smem = (size_t)p.PL * p.C * 2 * sizeof(float);
     int threads = p.PL * p.NV > p.G ? p.PL * p.NV : p.G;
     threads = (threads + 31) / 32 * 32;
-    gn_stats_kernel<T><<<grid, threads, smem, st>>>(
-        (const T*)x, (const T*)chan_add, partial, p);
+    launch_pdl(gn_stats_kernel<T>, grid, dim3(threads), smem, st, (const T*)x, (const T*)chan_add, partial, p);
     int rc = post_launch("gn_stats_kernel");
     if (rc) return rc;
   }
@@ -204,8 +207,9 @@ static int groupnorm_impl(void* y, const void* x, const void* chan_add, const vo
     if (ppc < 4) ppc = 4;
     chunks = (p.HW + ppc - 1) / ppc;
     dim3 grid(chunks, p.B);
-    gn_apply_kernel<T><<<grid, 256, ((size_t)p.C * 2 + (size_t)p.G * 2) * sizeof(float) + 256 * 2 * sizeof(double) + 16, st>>>(
-        (T*)y, (const T*)x, (const T*)chan_add, (const T*)gamma, (const T*)beta, partial, p, chunks, ppc);
+    launch_pdl(gn_apply_kernel<T>, grid, dim3(256),
+               ((size_t)p.C * 2 + (size_t)p.G * 2) * sizeof(float) + 256 * 2 * sizeof(double) + 16, st,
+               (T*)y, (const T*)x, (const T*)chan_add, (const T*)gamma, (const T*)beta, (const float*)partial, p, chunks, ppc);
   }
   return post_launch("gn_apply_kernel");
 }

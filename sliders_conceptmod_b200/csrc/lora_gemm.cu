@@ -135,6 +135,7 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 #define SLIDER_TRACE(slot) do { if (p.trace != nullptr) p.trace[blockIdx.x * 8 + (slot)] = clock64(); } while (0)
+  pdl_trigger();
   if (threadIdx.x == 0) SLIDER_TRACE(0);
 
   if (warp == 0 && lane == 0) {
@@ -161,6 +162,9 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
+  // PDL: barrier init, TMEM allocation and descriptor prefetch above overlap the previous kernel's tail; nothing
+  // below touches global memory before that kernel has completed
+  pdl_wait();
   const uint32_t tmem_base = *tmem_slot;
   const uint32_t smem_base = ptx::smem_u32(smem);
   if (threadIdx.x == 0) SLIDER_TRACE(1);
@@ -457,6 +461,8 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 template <typename T, int R4>
 __global__ void __launch_bounds__(256)
 splitk_finalize_kernel(const GemmParams p) {
+  pdl_trigger();
+  pdl_wait();
   constexpr int PER_TILE = BM * (BN / 8);
   const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
   if (idx >= (long long)p.total_tiles * PER_TILE) return;
@@ -566,13 +572,21 @@ lora_gemv_kernel(T* __restrict__ y, const T* __restrict__ x, const T* __restrict
   uint4 wreg[KC], areg[KC];
   const int pr0 = warp;                   // first (row m, rank j) pair of this warp for h = x . A^T
   const bool pr_ok = lora && pr0 < MT * rank;
+  pdl_trigger();
   {
+    // the frozen base weight is the one large operand and is never written by a preceding kernel: its loads are
+    // issued BEFORE the dependency wait, so under PDL they overlap the previous kernel's tail
     const uint4* wrow = reinterpret_cast<const uint4*>(W + (size_t)(n_ok ? n : 0) * K);
-    const uint4* arow = reinterpret_cast<const uint4*>(A + (size_t)(pr_ok ? pr0 % rank : 0) * K);
 #pragma unroll
     for (int c = 0; c < KC; ++c) {
       const int k = (c * 32 + lane) * V;
       wreg[c] = (n_ok && k < K) ? __ldg(wrow + c * 32 + lane) : make_uint4(0, 0, 0, 0);
+    }
+    pdl_wait();
+    const uint4* arow = reinterpret_cast<const uint4*>(A + (size_t)(pr_ok ? pr0 % rank : 0) * K);
+#pragma unroll
+    for (int c = 0; c < KC; ++c) {
+      const int k = (c * 32 + lane) * V;
       areg[c] = (pr_ok && k < K) ? __ldg(arow + c * 32 + lane) : make_uint4(0, 0, 0, 0);
     }
   }
@@ -693,11 +707,11 @@ static int launch_gemm(int r4, const CUtensorMap& a, const CUtensorMap& w, const
     for (auto& c : configured) if (c == nullptr) { c = (const void*)kern; break; }
   }
   int grid = p.total_units < sm_count() ? p.total_units : sm_count();
-  kern<<<grid, kGemmThreads, SMEM_BYTES, st>>>(a, w, l, xe, we, my, mp, p);
+  launch_pdl(kern, dim3(grid), dim3(kGemmThreads), SMEM_BYTES, st, a, w, l, xe, we, my, mp, p);
   int rc = post_launch("lora_gemm_kernel");
   if (rc || p.ksplit == 1) return rc;
   const long long threads = (long long)p.total_tiles * BM * (BN / 8);
-  fin<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(p);
+  launch_pdl(fin, dim3((unsigned)((threads + 255) / 256)), dim3(256), 0, st, p);
   return post_launch("splitk_finalize_kernel");
 }
 
@@ -711,9 +725,8 @@ static int launch_gemv(const slider_layer_geom* g, int M, void* y, const void* x
   const int V = 16 / (int)sizeof(T);
   const int kc = (K + 32 * V - 1) / (32 * V);     // 16-byte chunks per lane (caller guarantees <= 8)
 #define GEMV2(MT, KC)                                                                                             \
-  lora_gemv_kernel<T, MT, KC><<<grid, GEMV_WARPS * 32, smem, st>>>((T*)y, (const T*)x, (const T*)W, (const T*)bias, \
-                                                                   (const T*)A, (const T*)Bup, h_out, M, K, N,  \
-                                                                   g->rank, s, lora ? 1 : 0)
+  launch_pdl(lora_gemv_kernel<T, MT, KC>, dim3(grid), dim3(GEMV_WARPS * 32), smem, st, (T*)y, (const T*)x, (const T*)W, \
+             (const T*)bias, (const T*)A, (const T*)Bup, h_out, M, K, N, g->rank, s, lora ? 1 : 0)
 #define GEMV(MT) do { if (kc <= 2) GEMV2(MT, 2); else if (kc <= 4) GEMV2(MT, 4); else GEMV2(MT, 8); } while (0)
   if (mt == 2) GEMV(2); else if (mt == 4) GEMV(4); else if (mt == 8) GEMV(8); else GEMV(16);
 #undef GEMV

@@ -13,6 +13,8 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 layernorm_kernel(T* __restrict__ y, const T* __restrict__ x, const T* __restrict__ gamma,
                  const T* __restrict__ beta, int64_t rows, int C, float eps) {
+  pdl_trigger();
+  pdl_wait();
   constexpr int V = Elem<T>::kVec;
   const int lane = threadIdx.x & 31;
   const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -56,6 +58,8 @@ layernorm_kernel(T* __restrict__ y, const T* __restrict__ x, const T* __restrict
 template <typename T>
 __global__ void __launch_bounds__(256)
 geglu_kernel(T* __restrict__ y, const T* __restrict__ x, int64_t rows, int D) {
+  pdl_trigger();
+  pdl_wait();
   constexpr int V = Elem<T>::kVec;
   const int nv = D / V;
   const int64_t total = rows * nv;
@@ -86,12 +90,11 @@ int slider_layernorm(void* y, const void* x, const void* gamma, const void* beta
   cudaStream_t st = (cudaStream_t)stream;
   const unsigned grid = (unsigned)((rows + 7) / 8);
   if (dtype == SLIDER_BF16)
-    layernorm_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((__nv_bfloat16*)y, (const __nv_bfloat16*)x,
-                                                          (const __nv_bfloat16*)gamma, (const __nv_bfloat16*)beta, rows,
-                                                          channels, eps);
+    launch_pdl(layernorm_kernel<__nv_bfloat16>, dim3(grid), dim3(256), 0, st, (__nv_bfloat16*)y, (const __nv_bfloat16*)x,
+               (const __nv_bfloat16*)gamma, (const __nv_bfloat16*)beta, rows, channels, eps);
   else if (dtype == SLIDER_F32)
-    layernorm_kernel<float><<<grid, 256, 0, st>>>((float*)y, (const float*)x, (const float*)gamma, (const float*)beta,
-                                                  rows, channels, eps);
+    launch_pdl(layernorm_kernel<float>, dim3(grid), dim3(256), 0, st, (float*)y, (const float*)x, (const float*)gamma,
+               (const float*)beta, rows, channels, eps);
   else { set_error("layernorm: unsupported dtype %d", dtype); return SLIDER_ERR_UNSUPPORTED; }
   return post_launch("layernorm_kernel");
 }
@@ -105,9 +108,10 @@ int slider_geglu(void* y, const void* x, int64_t rows, int d, int dtype, void* s
   const int64_t cap = (int64_t)sm_count() * 16;
   if (blocks > cap) blocks = cap;
   if (dtype == SLIDER_BF16)
-    geglu_kernel<__nv_bfloat16><<<(unsigned)blocks, 256, 0, st>>>((__nv_bfloat16*)y, (const __nv_bfloat16*)x, rows, d);
+    launch_pdl(geglu_kernel<__nv_bfloat16>, dim3((unsigned)blocks), dim3(256), 0, st, (__nv_bfloat16*)y,
+               (const __nv_bfloat16*)x, rows, d);
   else if (dtype == SLIDER_F32)
-    geglu_kernel<float><<<(unsigned)blocks, 256, 0, st>>>((float*)y, (const float*)x, rows, d);
+    launch_pdl(geglu_kernel<float>, dim3((unsigned)blocks), dim3(256), 0, st, (float*)y, (const float*)x, rows, d);
   else { set_error("geglu: unsupported dtype %d", dtype); return SLIDER_ERR_UNSUPPORTED; }
   return post_launch("geglu_kernel");
 }
