@@ -212,6 +212,26 @@ int slider_groupnorm_nhwc(void* y, const void* x, const void* chan_add,
                           void* ws, size_t ws_bytes, void* stream);
 
 /*
+ * Training form of the same GroupNorm (the grad-recording forward of train_lora.py:275-289 and its backward at
+ * :298).  gamma / beta are frozen (unet.requires_grad_(False), train_lora.py:69), so the backward produces only
+ *     dx   [batch, hw, channels]     gradient w.r.t. x
+ *     dadd [batch, channels] or NULL gradient w.r.t. chan_add (= sum of dx over pixels; flows into time_emb_proj's
+ *                                    LoRA factors)
+ * slider_groupnorm_nhwc_train == slider_groupnorm_nhwc + stats_out [batch, groups, 2] fp32 {mean, rstd}, which the
+ * backward takes back as `stats`.  Backward = two launches (per-chunk partial sums, apply), deterministic order;
+ * ws of slider_groupnorm_bwd_workspace_bytes(batch, channels, groups) bytes, contents don't-care.
+ */
+int slider_groupnorm_nhwc_train(void* y, float* stats_out, const void* x, const void* chan_add,
+                                const void* gamma, const void* beta, int batch, int hw,
+                                int channels, int groups, float eps, int silu, int dtype,
+                                void* ws, size_t ws_bytes, void* stream);
+size_t slider_groupnorm_bwd_workspace_bytes(int batch, int channels, int groups);
+int slider_groupnorm_nhwc_backward(void* dx, void* dadd, const void* gy, const void* x,
+                                   const void* chan_add, const void* gamma, const void* beta,
+                                   const float* stats, int batch, int hw, int channels, int groups,
+                                   int silu, int dtype, void* ws, size_t ws_bytes, void* stream);
+
+/*
  * Row-wise kernels of the UNet's transformer blocks (diffusers BasicTransformerBlock):
  *   slider_layernorm: y = (x - mean) * rstd * gamma + beta over the last dimension of x [rows, channels]
  *                     (the producer of the LoRA-wrapped attn1.to_q/k/v inputs);

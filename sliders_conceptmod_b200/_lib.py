@@ -41,6 +41,9 @@ _SIGNATURES = {
     "slider_lora_input_grad": (C.c_int, [_G, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "slider_pack_wt": (C.c_int, [_G, _vp, _vp, _vp]),
     "slider_groupnorm_workspace_bytes": (_sz, [_i, _i]),
+    "slider_groupnorm_nhwc_train": (C.c_int, [_vp, _fp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _i, _i, _vp, _sz, _vp]),
+    "slider_groupnorm_bwd_workspace_bytes": (_sz, [_i, _i, _i]),
+    "slider_groupnorm_nhwc_backward": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _fp, _i, _i, _i, _i, _i, _i, _vp, _sz, _vp]),
     "slider_groupnorm_nhwc": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _i, _i, _vp, _sz, _vp]),
     "slider_layernorm": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i, _f, _i, _vp]),
     "slider_geglu": (C.c_int, [_vp, _vp, _i64, _i, _i, _vp]),

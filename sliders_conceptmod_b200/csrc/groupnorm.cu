@@ -107,7 +107,7 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 gn_apply_kernel(T* __restrict__ y, const T* __restrict__ x, const T* __restrict__ chan_add,
                 const T* __restrict__ gamma, const T* __restrict__ beta, const float* __restrict__ partial,
-                const GnParams p, int chunks, int ppc) {
+                const GnParams p, int chunks, int ppc, float* __restrict__ stats_out) {
   pdl_trigger();
   pdl_wait();
   extern __shared__ __align__(16) float gn_smem[];
@@ -148,6 +148,10 @@ gn_apply_kernel(T* __restrict__ y, const T* __restrict__ x, const T* __restrict_
       if (var < 0.0) var = 0.0;
       s_stat[2 * g] = (float)mean;
       s_stat[2 * g + 1] = rsqrtf((float)var + p.eps);
+      if (stats_out != nullptr && blockIdx.x == 0) {      // saved for the backward pass: [B][G]{mean, rstd}
+        stats_out[((size_t)b * p.G + g) * 2] = s_stat[2 * g];
+        stats_out[((size_t)b * p.G + g) * 2 + 1] = s_stat[2 * g + 1];
+      }
     }
   }
   __syncthreads();
@@ -189,7 +193,7 @@ gn_apply_kernel(T* __restrict__ y, const T* __restrict__ x, const T* __restrict_
 
 template <typename T>
 static int groupnorm_impl(void* y, const void* x, const void* chan_add, const void* gamma, const void* beta,
-                          float* ws, GnParams p, cudaStream_t st) {
+                          float* ws, GnParams p, cudaStream_t st, float* stats_out = nullptr) {
   // workspace: per-chunk partial sums [B][chunks][G][2]
   float* partial = ws;
   {
@@ -209,9 +213,244 @@ static int groupnorm_impl(void* y, const void* x, const void* chan_add, const vo
     dim3 grid(chunks, p.B);
     launch_pdl(gn_apply_kernel<T>, grid, dim3(256),
                ((size_t)p.C * 2 + (size_t)p.G * 2) * sizeof(float) + 256 * 2 * sizeof(double) + 16, st,
-               (T*)y, (const T*)x, (const T*)chan_add, (const T*)gamma, (const T*)beta, (const float*)partial, p, chunks, ppc);
+               (T*)y, (const T*)x, (const T*)chan_add, (const T*)gamma, (const T*)beta, (const float*)partial, p, chunks, ppc, stats_out);
   }
   return post_launch("gn_apply_kernel");
+}
+
+// ---- backward (frozen gamma / beta: only dx and the gradient of the per-channel pre-add) ---------------------
+//   xhat = (x + add - mean) * rstd,  z = xhat * gamma + beta,  d = gy * gamma * act'(z)
+//   s1_g = sum d,  s2_g = sum d * xhat  over the group     dx = rstd * (d - (s1 + xhat * s2) / n)
+//   dadd[b,c] = sum_pixels dx = rstd * (D_c - HW * s1 / n - (s2 / n) * X_c),  D_c = sum_p d,  X_c = sum_p xhat
+__device__ __forceinline__ float silu_grad(float z) {
+  const float sg = 1.f / (1.f + __expf(-z));
+  return sg * fmaf(z, 1.f - sg, 1.f);
+}
+
+// pass 1: per-chunk partial sums {s1, s2} per group (+ {D_c, X_c} per channel when dadd is wanted)
+template <typename T>
+__global__ void __launch_bounds__(GN_MAX_THREADS)
+gn_bwd_stats_kernel(const T* __restrict__ gy, const T* __restrict__ x, const T* __restrict__ chan_add,
+                    const T* __restrict__ gamma, const T* __restrict__ beta, const float* __restrict__ stats,
+                    float* __restrict__ partial_g, float* __restrict__ partial_c, const GnParams p) {
+  extern __shared__ __align__(16) float gn_smem[];
+  float* s_a = gn_smem;                       // [PL][C] sum d
+  float* s_b = gn_smem + (size_t)p.PL * p.C;  // [PL][C] sum d * xhat
+  float* s_x = gn_smem + (size_t)2 * p.PL * p.C;   // [PL][C] sum xhat (only with partial_c)
+  const int b = blockIdx.y, chunk = blockIdx.x;
+  const int tid = threadIdx.x;
+  const int pl = tid / p.NV, v = tid - pl * p.NV;
+  if (pl < p.PL) {
+    float rs[8], sh[8], ga[8], be[8], A[8], Bq[8], Xs[8];
+    float add[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { add[k] = 0.f; A[k] = 0.f; Bq[k] = 0.f; Xs[k] = 0.f; }
+    if (chan_add != nullptr) Vec8<T>::load(chan_add + (size_t)b * p.C + v * 8, add);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int c = v * 8 + k, g = c / p.cpg;
+      const float mean = stats[((size_t)b * p.G + g) * 2], rstd = stats[((size_t)b * p.G + g) * 2 + 1];
+      rs[k] = rstd;
+      sh[k] = (add[k] - mean) * rstd;
+      ga[k] = gamma ? Elem<T>::to_f(gamma[c]) : 1.f;
+      be[k] = beta ? Elem<T>::to_f(beta[c]) : 0.f;
+    }
+    const int p0 = chunk * p.ppc;
+    const int p1 = min(p.HW, p0 + p.ppc);
+    const size_t base = ((size_t)b * p.HW) * p.C + v * 8;
+#pragma unroll 2
+    for (int pix = p0 + pl; pix < p1; pix += p.PL) {
+      float xv[8], gv[8];
+      Vec8<T>::load(x + base + (size_t)pix * p.C, xv);
+      Vec8<T>::load(gy + base + (size_t)pix * p.C, gv);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float xh = fmaf(xv[k], rs[k], sh[k]);
+        float d = gv[k] * ga[k];
+        if (p.silu) d *= silu_grad(fmaf(xh, ga[k], be[k]));
+        A[k] += d;
+        Bq[k] = fmaf(d, xh, Bq[k]);
+        Xs[k] += xh;
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      s_a[pl * p.C + v * 8 + k] = A[k];
+      s_b[pl * p.C + v * 8 + k] = Bq[k];
+      if (partial_c != nullptr) s_x[pl * p.C + v * 8 + k] = Xs[k];
+    }
+  }
+  __syncthreads();
+  const int warp = tid >> 5, lane = tid & 31, nwarps = blockDim.x >> 5;
+  const int per_group = p.PL * p.cpg;
+  for (int g = warp; g < p.G; g += nwarps) {
+    float a = 0.f, q = 0.f;
+    for (int i = lane; i < per_group; i += 32) {
+      const int l = i / p.cpg, c = g * p.cpg + (i - l * p.cpg);
+      a += s_a[l * p.C + c];
+      q += s_b[l * p.C + c];
+    }
+    a = warp_sum(a);
+    q = warp_sum(q);
+    if (lane == 0) {
+      float* dst = partial_g + (((size_t)b * p.chunks + chunk) * p.G + g) * 2;
+      dst[0] = a; dst[1] = q;
+    }
+  }
+  if (partial_c != nullptr) {       // per-channel sums of this chunk, pixel lanes added in lane order
+    for (int c = tid; c < p.C; c += blockDim.x) {
+      float a = 0.f, xs = 0.f;
+      for (int l = 0; l < p.PL; ++l) { a += s_a[l * p.C + c]; xs += s_x[l * p.C + c]; }
+      float* dst = partial_c + (((size_t)b * p.chunks + chunk) * p.C + c) * 2;
+      dst[0] = a; dst[1] = xs;
+    }
+  }
+}
+
+// pass 2: dx, and dadd by the first ceil(C / 256) blocks of every batch item
+template <typename T>
+__global__ void __launch_bounds__(256)
+gn_bwd_apply_kernel(T* __restrict__ dx, T* __restrict__ dadd, const T* __restrict__ gy, const T* __restrict__ x,
+                    const T* __restrict__ chan_add, const T* __restrict__ gamma, const T* __restrict__ beta,
+                    const float* __restrict__ stats, const float* __restrict__ partial_g,
+                    const float* __restrict__ partial_c, const GnParams p, int chunks, int ppc) {
+  extern __shared__ __align__(16) float gn_smem[];
+  float* s_rs = gn_smem;                // [C] rstd
+  float* s_sh = gn_smem + p.C;          // [C] (add - mean) * rstd
+  float* s_ga = gn_smem + 2 * p.C;      // [C]
+  float* s_be = gn_smem + 3 * p.C;      // [C]
+  float* s_c1 = gn_smem + 4 * p.C;      // [C] s1_g / n
+  float* s_c2 = gn_smem + 5 * p.C;      // [C] s2_g / n
+  float* s_grp = gn_smem + 6 * p.C;     // [G][2]
+  double* s_part = reinterpret_cast<double*>(gn_smem + 6 * p.C + 2 * p.G);   // [nl][G][2]
+  const int b = blockIdx.y;
+  {
+    const int g = threadIdx.x % p.G, l = threadIdx.x / p.G, nl = blockDim.x / p.G;
+    if (l < nl) {
+      double a = 0.0, q = 0.0;
+      const float2* src = reinterpret_cast<const float2*>(partial_g) + ((size_t)b * p.chunks) * p.G + g;
+      int ch = l;
+      for (; ch + 3 * nl < p.chunks; ch += 4 * nl) {
+        const float2 v0 = __ldcg(src + (size_t)ch * p.G), v1 = __ldcg(src + (size_t)(ch + nl) * p.G);
+        const float2 v2 = __ldcg(src + (size_t)(ch + 2 * nl) * p.G), v3 = __ldcg(src + (size_t)(ch + 3 * nl) * p.G);
+        a += (double)v0.x; q += (double)v0.y; a += (double)v1.x; q += (double)v1.y;
+        a += (double)v2.x; q += (double)v2.y; a += (double)v3.x; q += (double)v3.y;
+      }
+      for (; ch < p.chunks; ch += nl) {
+        const float2 v = __ldcg(src + (size_t)ch * p.G);
+        a += (double)v.x; q += (double)v.y;
+      }
+      s_part[(l * p.G + g) * 2] = a;
+      s_part[(l * p.G + g) * 2 + 1] = q;
+    }
+    __syncthreads();
+    if (threadIdx.x < p.G) {
+      double a = 0.0, q = 0.0;
+      for (int i = 0; i < nl; ++i) { a += s_part[(i * p.G + g) * 2]; q += s_part[(i * p.G + g) * 2 + 1]; }
+      const double n = (double)p.cpg * (double)p.HW;
+      s_grp[2 * g] = (float)(a / n);
+      s_grp[2 * g + 1] = (float)(q / n);
+    }
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < p.C; c += blockDim.x) {
+    const int g = c / p.cpg;
+    const float mean = stats[((size_t)b * p.G + g) * 2], rstd = stats[((size_t)b * p.G + g) * 2 + 1];
+    const float add = chan_add ? Elem<T>::to_f(chan_add[(size_t)b * p.C + c]) : 0.f;
+    s_rs[c] = rstd;
+    s_sh[c] = (add - mean) * rstd;
+    s_ga[c] = gamma ? Elem<T>::to_f(gamma[c]) : 1.f;
+    s_be[c] = beta ? Elem<T>::to_f(beta[c]) : 0.f;
+    s_c1[c] = s_grp[2 * g];
+    s_c2[c] = s_grp[2 * g + 1];
+  }
+  __syncthreads();
+  if (dadd != nullptr && (int)blockIdx.x * 256 < p.C) {
+    const int c = blockIdx.x * 256 + threadIdx.x;
+    if (c < p.C) {
+      double D = 0.0, X = 0.0;
+      const float2* src = reinterpret_cast<const float2*>(partial_c) + ((size_t)b * p.chunks) * p.C + c;
+      int ch = 0;
+      for (; ch + 3 < p.chunks; ch += 4) {
+        const float2 v0 = __ldcg(src + (size_t)ch * p.C), v1 = __ldcg(src + (size_t)(ch + 1) * p.C);
+        const float2 v2 = __ldcg(src + (size_t)(ch + 2) * p.C), v3 = __ldcg(src + (size_t)(ch + 3) * p.C);
+        D += (double)v0.x; X += (double)v0.y; D += (double)v1.x; X += (double)v1.y;
+        D += (double)v2.x; X += (double)v2.y; D += (double)v3.x; X += (double)v3.y;
+      }
+      for (; ch < p.chunks; ++ch) {
+        const float2 v = __ldcg(src + (size_t)ch * p.C);
+        D += (double)v.x; X += (double)v.y;
+      }
+      const double r = (double)s_rs[c] * (D - (double)p.HW * (double)s_c1[c] - (double)s_c2[c] * X);
+      dadd[(size_t)b * p.C + c] = Elem<T>::from_f((float)r);
+    }
+  }
+  const int p0 = blockIdx.x * ppc;
+  const int p1 = min(p.HW, p0 + ppc);
+  if (p0 >= p1) return;
+  const long long total = (long long)(p1 - p0) * p.NV;
+  const size_t base = ((size_t)b * p.HW + p0) * p.C;
+  int v = threadIdx.x % p.NV;
+  const int dv = blockDim.x % p.NV;
+  for (long long idx = threadIdx.x; idx < total; idx += blockDim.x) {
+    float xv[8], gv[8], o[8];
+    Vec8<T>::load(x + base + idx * 8, xv);
+    Vec8<T>::load(gy + base + idx * 8, gv);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int c = v * 8 + k;
+      const float xh = fmaf(xv[k], s_rs[c], s_sh[c]);
+      float d = gv[k] * s_ga[c];
+      if (p.silu) d *= silu_grad(fmaf(xh, s_ga[c], s_be[c]));
+      o[k] = s_rs[c] * (d - s_c1[c] - xh * s_c2[c]);
+    }
+    Vec8<T>::store(dx + base + idx * 8, o);
+    v += dv;
+    if (v >= p.NV) v -= p.NV;
+  }
+}
+
+template <typename T>
+static int groupnorm_bwd_impl(void* dx, void* dadd, const void* gy, const void* x, const void* chan_add,
+                              const void* gamma, const void* beta, const float* stats, float* ws, GnParams p,
+                              cudaStream_t st) {
+  float* partial_g = ws;                                             // [B][chunks][G][2]
+  float* partial_c = ws + (size_t)p.B * p.chunks * p.G * 2;          // [B][chunks][C][2]
+  const bool want_add = dadd != nullptr;
+  {
+    dim3 grid(p.chunks, p.B);
+    const size_t smem = (size_t)p.PL * p.C * (want_add ? 3 : 2) * sizeof(float);
+    static thread_local size_t configured = 0;
+    if (smem > 48 * 1024 && smem > configured) {
+      SLIDER_CUDA(cudaFuncSetAttribute(gn_bwd_stats_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      configured = smem;
+    }
+    int threads = p.PL * p.NV > p.G ? p.PL * p.NV : p.G;
+    threads = (threads + 31) / 32 * 32;
+    gn_bwd_stats_kernel<T><<<grid, threads, smem, st>>>((const T*)gy, (const T*)x, (const T*)chan_add, (const T*)gamma,
+                                                        (const T*)beta, stats, partial_g, want_add ? partial_c : nullptr, p);
+    int rc = post_launch("gn_bwd_stats_kernel");
+    if (rc) return rc;
+  }
+  {
+    int chunks = (sm_count() * 4 + p.B - 1) / p.B;
+    int ppc = (p.HW + chunks - 1) / chunks;
+    if (ppc < 4) ppc = 4;
+    chunks = (p.HW + ppc - 1) / ppc;
+    const int min_blocks = want_add ? (p.C + 255) / 256 : 1;     // the dadd slices need that many blocks per item
+    if (chunks < min_blocks) chunks = min_blocks;
+    dim3 grid(chunks, p.B);
+    const size_t smem = ((size_t)p.C * 6 + (size_t)p.G * 2) * sizeof(float) + 256 * 2 * sizeof(double) + 16;
+    static thread_local size_t configured2 = 0;
+    if (smem > 48 * 1024 && smem > configured2) {
+      SLIDER_CUDA(cudaFuncSetAttribute(gn_bwd_apply_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      configured2 = smem;
+    }
+    gn_bwd_apply_kernel<T><<<grid, 256, smem, st>>>((T*)dx, (T*)dadd, (const T*)gy, (const T*)x, (const T*)chan_add,
+                                                    (const T*)gamma, (const T*)beta, stats, partial_g, partial_c, p,
+                                                    chunks, ppc);
+  }
+  return post_launch("gn_bwd_apply_kernel");
 }
 
 static int gn_plan(GnParams* p, int B, int HW, int C, int G, float eps, int silu) {
@@ -266,6 +505,60 @@ int slider_groupnorm_nhwc(void* y, const void* x, const void* chan_add, const vo
   if (dtype == SLIDER_BF16) return groupnorm_impl<__nv_bfloat16>(y, x, chan_add, gamma, beta, (float*)ws, p, st);
   if (dtype == SLIDER_F32) return groupnorm_impl<float>(y, x, chan_add, gamma, beta, (float*)ws, p, st);
   set_error("groupnorm: unsupported dtype %d", dtype);
+  return SLIDER_ERR_UNSUPPORTED;
+}
+
+int slider_groupnorm_nhwc_train(void* y, float* stats_out, const void* x, const void* chan_add, const void* gamma,
+                                const void* beta, int batch, int hw, int channels, int groups, float eps, int silu,
+                                int dtype, void* ws, size_t ws_bytes, void* stream) {
+  SLIDER_CHECK_ARG(y && x && ws && stats_out, "groupnorm_train: null pointer");
+  SLIDER_CHECK_ARG((((uintptr_t)y | (uintptr_t)x | (uintptr_t)chan_add | (uintptr_t)ws) & 15) == 0,
+                   "groupnorm_train: pointers must be 16-byte aligned");
+  GnParams p;
+  int rc = gn_plan(&p, batch, hw, channels, groups, eps, silu);
+  if (rc) return rc;
+  SLIDER_CHECK_ARG(p.NV <= GN_MAX_THREADS && batch <= GN_TICKETS, "groupnorm_train: shape outside the kernel's limits");
+  const size_t need = ((size_t)GN_TICKETS + (size_t)batch * groups * 2 + (size_t)batch * p.chunks * groups * 2) * sizeof(float);
+  if (ws_bytes < need) {
+    set_error("groupnorm_train: workspace %zu < %zu bytes", ws_bytes, need);
+    return SLIDER_ERR_WORKSPACE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == SLIDER_BF16) return groupnorm_impl<__nv_bfloat16>(y, x, chan_add, gamma, beta, (float*)ws, p, st, stats_out);
+  if (dtype == SLIDER_F32) return groupnorm_impl<float>(y, x, chan_add, gamma, beta, (float*)ws, p, st, stats_out);
+  set_error("groupnorm_train: unsupported dtype %d", dtype);
+  return SLIDER_ERR_UNSUPPORTED;
+}
+
+size_t slider_groupnorm_bwd_workspace_bytes(int batch, int channels, int groups) {
+  const size_t chunks = (size_t)sm_count() + 2 * (size_t)batch;       // batch * chunks upper bound (gn_plan)
+  return chunks * ((size_t)groups + (size_t)channels) * 2 * sizeof(float);
+}
+
+int slider_groupnorm_nhwc_backward(void* dx, void* dadd, const void* gy, const void* x, const void* chan_add,
+                                   const void* gamma, const void* beta, const float* stats, int batch, int hw,
+                                   int channels, int groups, int silu, int dtype, void* ws, size_t ws_bytes,
+                                   void* stream) {
+  SLIDER_CHECK_ARG(dx && gy && x && stats && ws, "groupnorm_backward: null pointer");
+  SLIDER_CHECK_ARG((dadd == nullptr) || (chan_add != nullptr), "groupnorm_backward: dadd needs chan_add");
+  SLIDER_CHECK_ARG((((uintptr_t)dx | (uintptr_t)gy | (uintptr_t)x | (uintptr_t)chan_add | (uintptr_t)dadd | (uintptr_t)ws) & 15) == 0,
+                   "groupnorm_backward: pointers must be 16-byte aligned");
+  GnParams p;
+  int rc = gn_plan(&p, batch, hw, channels, groups, 0.f, silu);
+  if (rc) return rc;
+  SLIDER_CHECK_ARG(p.NV <= GN_MAX_THREADS, "groupnorm_backward: channels %d exceed the kernel's 4096 limit", channels);
+  // three per-channel accumulator arrays in shared memory: fewer pixel lanes than the forward when needed
+  while (p.PL > 1 && (size_t)p.PL * p.C * 3 * sizeof(float) > 160 * 1024) p.PL /= 2;
+  const size_t need = (size_t)batch * p.chunks * ((size_t)groups + channels) * 2 * sizeof(float);
+  if (ws_bytes < need) {
+    set_error("groupnorm_backward: workspace %zu < %zu bytes", ws_bytes, need);
+    return SLIDER_ERR_WORKSPACE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == SLIDER_BF16)
+    return groupnorm_bwd_impl<__nv_bfloat16>(dx, dadd, gy, x, chan_add, gamma, beta, stats, (float*)ws, p, st);
+  if (dtype == SLIDER_F32) return groupnorm_bwd_impl<float>(dx, dadd, gy, x, chan_add, gamma, beta, stats, (float*)ws, p, st);
+  set_error("groupnorm_backward: unsupported dtype %d", dtype);
   return SLIDER_ERR_UNSUPPORTED;
 }
 

@@ -162,7 +162,8 @@ _gn_ws: dict[int, torch.Tensor] = {}
 
 
 def groupnorm_nhwc(x: torch.Tensor, groups: int, gamma: torch.Tensor | None, beta: torch.Tensor | None,
-                   eps: float = 1e-5, silu: bool = False, chan_add: torch.Tensor | None = None) -> torch.Tensor:
+                   eps: float = 1e-5, silu: bool = False, chan_add: torch.Tensor | None = None,
+                   want_stats: bool = False):
     """y = act(GroupNorm(x + chan_add[:, None, :])) on NHWC data.  x [B, ..., C] contiguous (C innermost),
     chan_add [B, C] (the time-embedding projection of ResnetBlock2D) or None."""
     require_cuda(x, gamma, beta, chan_add)
@@ -179,10 +180,41 @@ def groupnorm_nhwc(x: torch.Tensor, groups: int, gamma: torch.Tensor | None, bet
         chan_add = chan_add.contiguous()
         assert chan_add.shape == (B, Cc) and chan_add.dtype == x.dtype
     y = torch.empty_like(x)
+    if want_stats:
+        stats = torch.empty(B, groups, 2, device=x.device, dtype=torch.float32)
+        check(lib().slider_groupnorm_nhwc_train(ptr(y), ptr(stats), ptr(x), ptr(chan_add), ptr(gamma), ptr(beta), int(B),
+                                                int(hw), int(Cc), int(groups), float(eps), int(bool(silu)),
+                                                dtype_code(x.dtype), ptr(ws), ws.numel(), stream_ptr()))
+        return y, stats
     check(lib().slider_groupnorm_nhwc(ptr(y), ptr(x), ptr(chan_add), ptr(gamma), ptr(beta), int(B), int(hw), int(Cc),
                                       int(groups), float(eps), int(bool(silu)), dtype_code(x.dtype), ptr(ws),
                                       ws.numel(), stream_ptr()))
     return y
+
+
+_gn_bwd_ws: dict[int, torch.Tensor] = {}
+
+
+def groupnorm_nhwc_backward(gy: torch.Tensor, x: torch.Tensor, stats: torch.Tensor, groups: int,
+                            gamma: torch.Tensor | None, beta: torch.Tensor | None, silu: bool,
+                            chan_add: torch.Tensor | None = None, want_dadd: bool = False):
+    """Backward of groupnorm_nhwc for frozen gamma / beta: returns (dx like x, dadd [B, C] or None)."""
+    require_cuda(gy, x, stats, gamma, beta, chan_add)
+    assert x.is_contiguous() and gy.is_contiguous() and gy.shape == x.shape and gy.dtype == x.dtype
+    B, Cc = x.shape[0], x.shape[-1]
+    hw = x.numel() // (B * Cc)
+    key = x.device.index if x.device.index is not None else torch.cuda.current_device()
+    need = lib().slider_groupnorm_bwd_workspace_bytes(int(B), int(Cc), int(groups))
+    ws = _gn_bwd_ws.get(key)
+    if ws is None or ws.numel() < need:
+        ws = torch.empty(max(need, 1 << 20), dtype=torch.uint8, device=x.device)
+        _gn_bwd_ws[key] = ws
+    dx = torch.empty_like(x)
+    dadd = torch.empty(B, Cc, device=x.device, dtype=x.dtype) if (want_dadd and chan_add is not None) else None
+    check(lib().slider_groupnorm_nhwc_backward(ptr(dx), ptr(dadd), ptr(gy), ptr(x), ptr(chan_add), ptr(gamma), ptr(beta),
+                                               ptr(stats), int(B), int(hw), int(Cc), int(groups), int(bool(silu)),
+                                               dtype_code(x.dtype), ptr(ws), ws.numel(), stream_ptr()))
+    return dx, dadd
 
 
 def layernorm(x: torch.Tensor, gamma: torch.Tensor | None, beta: torch.Tensor | None, eps: float = 1e-5) -> torch.Tensor:

@@ -116,10 +116,38 @@ def group_norm_act(norm: nn.GroupNorm, x: torch.Tensor, silu: bool, chan_add: to
             xn = xn.contiguous()
         y = ops.groupnorm_nhwc(xn, norm.num_groups, norm.weight, norm.bias, norm.eps, silu, chan_add)
         return y.permute(0, 3, 1, 2)
+    if (x.is_cuda and "gn_train" not in _DISABLED and not norm.weight.requires_grad and x.shape[1] % 8 == 0
+            and x.dtype == norm.weight.dtype):
+        # grad-recording forward: same NHWC kernels + a fused NHWC backward (gamma / beta are frozen)
+        y = _GroupNormNHWCFn.apply(x.permute(0, 2, 3, 1), chan_add, norm, silu)
+        return y.permute(0, 3, 1, 2)
     if chan_add is not None:
         x = x + chan_add[:, :, None, None]
     y = norm(x)
     return F.silu(y) if silu else y
+
+
+class _GroupNormNHWCFn(torch.autograd.Function):
+    """act(GroupNorm(x + chan_add)) on NHWC activations with libslider's forward / backward kernel pairs."""
+
+    @staticmethod
+    def forward(ctx, xn, chan_add, norm, silu):
+        xn = xn if xn.is_contiguous() else xn.contiguous()
+        add = None if chan_add is None else chan_add.contiguous()
+        y, stats = ops.groupnorm_nhwc(xn, norm.num_groups, norm.weight, norm.bias, norm.eps, silu, add, want_stats=True)
+        ctx.save_for_backward(xn, add, stats)
+        ctx.norm, ctx.silu = norm, silu
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        xn, add, stats = ctx.saved_tensors
+        norm = ctx.norm
+        gy = gy if gy.is_contiguous() else gy.contiguous()
+        want_dadd = add is not None and ctx.needs_input_grad[1]
+        dx, dadd = ops.groupnorm_nhwc_backward(gy, xn, stats, norm.num_groups, norm.weight, norm.bias, ctx.silu, add,
+                                               want_dadd=want_dadd)
+        return (dx if ctx.needs_input_grad[0] else None), dadd, None, None
 
 
 def _no_grad_cuda(*ts) -> bool:

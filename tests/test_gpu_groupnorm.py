@@ -35,3 +35,39 @@ def test_groupnorm_nhwc_matches_torch(case, dtype, silu, with_add):
     err = (y.float() - yr).abs().max().item()
     tol = 3e-2 if dtype == torch.bfloat16 else 2e-5
     assert err <= tol * max(1.0, yr.abs().max().item()), f"max-abs {err}"
+
+
+@pytest.mark.parametrize("case", CASES)
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("silu,with_add", [(True, False), (True, True), (False, False)])
+def test_groupnorm_nhwc_backward_matches_torch_autograd(case, dtype, silu, with_add):
+    """Training form: forward with saved {mean, rstd} + fused backward (dx, and d chan_add) vs autograd of the fp32
+    torch expression act(group_norm(x + add))."""
+    from sliders_conceptmod_b200 import ops
+    B, H, W, C, G = case
+    gen = torch.Generator(device="cuda").manual_seed(11)
+    x = (torch.randn(B, H, W, C, device="cuda", generator=gen) * 1.7 + 0.3).to(dtype)
+    gy = torch.randn(B, H, W, C, device="cuda", generator=gen).to(dtype)
+    gamma = (1 + 0.2 * torch.randn(C, device="cuda", generator=gen)).to(dtype)
+    beta = (0.1 * torch.randn(C, device="cuda", generator=gen)).to(dtype)
+    add = torch.randn(B, C, device="cuda", generator=gen).to(dtype) if with_add else None
+    y, stats = ops.groupnorm_nhwc(x, G, gamma, beta, 1e-5, silu, add, want_stats=True)
+    dx, dadd = ops.groupnorm_nhwc_backward(gy, x, stats, G, gamma, beta, silu, add, want_dadd=with_add)
+    xr = x.float().permute(0, 3, 1, 2).requires_grad_(True)
+    ar = add.float().requires_grad_(True) if with_add else None
+    z = xr + ar[:, :, None, None] if with_add else xr
+    yr = F.group_norm(z, G, gamma.float(), beta.float(), 1e-5)
+    if silu:
+        yr = F.silu(yr)
+    yr.backward(gy.float().permute(0, 3, 1, 2))
+    assert (y.float() - yr.detach().permute(0, 2, 3, 1)).abs().max().item() <= (3e-2 if dtype == torch.bfloat16 else 2e-5) * max(1.0, yr.abs().max().item())
+    ref = xr.grad.permute(0, 2, 3, 1)
+    err = (dx.float() - ref).abs().max().item()
+    tol = 2e-2 if dtype == torch.bfloat16 else 5e-5
+    assert err <= tol * max(1e-3, ref.abs().max().item()), f"dx max-abs {err} vs {ref.abs().max().item()}"
+    if with_add:
+        err = (dadd.float() - ar.grad).abs().max().item()
+        # a sum over H*W pixels of bf16-rounded terms in the reference vs fp32 accumulation here
+        assert err <= (3e-2 if dtype == torch.bfloat16 else 2e-4) * max(1e-3, ar.grad.abs().max().item()), f"dadd max-abs {err}"
+    else:
+        assert dadd is None
