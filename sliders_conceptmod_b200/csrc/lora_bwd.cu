@@ -25,7 +25,8 @@ __global__ void pack_bt_kernel(T* __restrict__ Bt, const T* __restrict__ Bup, in
 //     TAPS x CH x 4 fp32 accumulators; PL pixel lanes share a CTA;
 //   * the V rows (h fp32 / dh) of the CTA's pixel range (+ halo for 3x3) are staged once in shared memory
 //     as float4, so the inner loop is one broadcast LDS.128 per tap;
-//   * lanes are reduced through shared memory, then one fp32 atomicAdd per output element and CTA.
+//   * a CTA owns a narrow channel slice (4 vector threads) and 64 pixel lanes; lanes are reduced by warp
+//     shuffles, warps through shared memory, then one fp32 atomicAdd per output element and CTA.
 struct ColReduceParams {
   int B, H, W, C;        // X is [B,H,W,C]
   int kw, pad;
@@ -63,7 +64,7 @@ template <> struct ChanVec<float, 4> {
 };
 
 template <typename T, typename VT, int TAPS, int CH>
-__global__ void __launch_bounds__(TAPS == 1 ? 512 : 256)
+__global__ void __launch_bounds__(256)
 colreduce_kernel(float* __restrict__ out, const T* __restrict__ X, const VT* __restrict__ V,
                  const ColReduceParams p, int j0) {
   extern __shared__ __align__(16) float cr_smem[];
@@ -135,26 +136,42 @@ colreduce_kernel(float* __restrict__ out, const T* __restrict__ X, const VT* __r
       }
     }
   }
-  // cross-lane reduction tap by tap through shared memory (re-using the V staging area), then atomics
-  float* s_red = cr_smem;     // [PL][NVT*CH*4]
-  const int row = p.NVT * CH * 4;
+  // cross-lane reduction: the 8 pixel lanes of a warp by shuffles (lane = pixel-lane * 4 + channel-vector thread,
+  // NVT == 4), the warps through shared memory (re-using the V staging area), then one fp32 atomicAdd per output
+  // element and CTA.  A CTA covers only NVT * CH channels, so it issues TAPS * NVT * CH * 4 atomics in total.
+  constexpr int NACC = TAPS * CH * 4;
 #pragma unroll
-  for (int t = 0; t < TAPS; ++t) {
-    __syncthreads();
-    if (pl < p.PL) {
+  for (int t = 0; t < TAPS; ++t)
+#pragma unroll
+    for (int k = 0; k < CH; ++k)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float a = acc[t][k][j];
+        a += __shfl_xor_sync(0xffffffffu, a, 4);
+        a += __shfl_xor_sync(0xffffffffu, a, 8);
+        a += __shfl_xor_sync(0xffffffffu, a, 16);
+        acc[t][k][j] = a;
+      }
+  float* s_red = cr_smem;     // [warps][NVT][NACC]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  __syncthreads();            // every thread is done with the staged V rows
+  if (lane < 4) {
+    float4* dst = reinterpret_cast<float4*>(s_red + ((size_t)warp * 4 + lane) * NACC);
+#pragma unroll
+    for (int t = 0; t < TAPS; ++t)
 #pragma unroll
       for (int k = 0; k < CH; ++k)
-        *reinterpret_cast<float4*>(s_red + pl * row + (v * CH + k) * 4) =
-            make_float4(acc[t][k][0], acc[t][k][1], acc[t][k][2], acc[t][k][3]);
-    }
-    __syncthreads();
-    for (int i = threadIdx.x; i < row; i += blockDim.x) {
-      const int cc = blockIdx.y * p.NVT * CH + i / 4, j = i & 3;
-      if (cc < p.C && j0 + j < p.rank) {
-        float sum = 0.f;
-        for (int l = 0; l < p.PL; ++l) sum += s_red[l * row + i];
-        atomicAdd(out + (int64_t)cc * p.oc + (int64_t)(j0 + j) * p.oj + (int64_t)t * p.ot, sum * p.scale);
-      }
+        dst[t * CH + k] = make_float4(acc[t][k][0], acc[t][k][1], acc[t][k][2], acc[t][k][3]);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 4 * NACC; i += blockDim.x) {
+    const int vv = i / NACC, rem = i - vv * NACC;
+    const int t = rem / (CH * 4), k = (rem >> 2) % CH, j = rem & 3;
+    const int cc = (blockIdx.y * 4 + vv) * CH + k;
+    if (cc < p.C && j0 + j < p.rank) {
+      float sum = 0.f;
+      for (int w = 0; w < nwarps; ++w) sum += s_red[(size_t)w * 4 * NACC + i];
+      atomicAdd(out + (int64_t)cc * p.oc + (int64_t)(j0 + j) * p.oj + (int64_t)t * p.ot, sum * p.scale);
     }
   }
 }
@@ -191,12 +208,13 @@ template <typename T, typename VT>
 static int launch_colreduce(float* out, const T* X, const VT* v, ColReduceParams p, int taps, cudaStream_t st) {
   const int CH = taps == 1 ? 8 : 4;
   const int HW = p.H * p.W;
-  const int max_threads = taps == 1 ? 512 : 256;   // 3x3 keeps 144 accumulators per thread
-  int nvt_all = (p.C + CH - 1) / CH;
-  int cblocks = (nvt_all + max_threads - 1) / max_threads;
-  p.NVT = (nvt_all + cblocks - 1) / cblocks;
+  // a CTA = 4 channel-vector threads (NVT, fixed: the shuffle reduction relies on it) x 64 pixel lanes: a narrow
+  // channel slice keeps the per-CTA output (and its atomics) small, the pixel lanes supply the parallelism
+  const int max_threads = 256;
+  const int nvt_all = (p.C + CH - 1) / CH;
+  const int cblocks = (nvt_all + 3) / 4;
+  p.NVT = 4;
   p.PL = max_threads / p.NVT;
-  if (p.PL < 1) p.PL = 1;
   // pixel chunks: ~2 CTAs per SM over (images x chunks x channel blocks); chunks never straddle images
   int want = (sm_count() * 2) / (p.B * cblocks);
   if (want < 1) want = 1;
@@ -207,11 +225,10 @@ static int launch_colreduce(float* out, const T* X, const VT* v, ColReduceParams
   p.cpi = (HW + ppc - 1) / ppc;
   const int halo = taps > 1 ? p.pad * (p.W + 1) : 0;
   size_t smem_v = (size_t)(ppc + 2 * halo) * sizeof(float4);
-  size_t smem_r = (size_t)p.PL * p.NVT * CH * 4 * sizeof(float);
+  size_t smem_r = (size_t)(max_threads / 32) * p.NVT * taps * CH * 4 * sizeof(float);
   size_t smem = smem_v > smem_r ? smem_v : smem_r;
   if (smem > 200 * 1024) { set_error("colreduce: shared memory %zu too large", smem); return SLIDER_ERR_UNSUPPORTED; }
-  int threads = p.PL * p.NVT;
-  threads = (threads + 31) / 32 * 32;
+  const int threads = max_threads;
   dim3 grid(p.B * p.cpi, cblocks);
   for (int j0 = 0; j0 < p.rank; j0 += 4) {
     if (taps == 1) {
