@@ -226,7 +226,12 @@ class ResnetBlock2D(nn.Module):
 
     def forward(self, x, temb):
         h = self.conv1(group_norm_act(self.norm1, x, True))
-        t = self.time_emb_proj(temb if getattr(temb, "_silu_applied", False) else self.nonlinearity(temb))
+        ready = self.__dict__.pop("_t_ready", None)
+        if ready is not None:       # projected on the side stream at the start of the forward (UNet._prefetch_temb)
+            torch.cuda.current_stream().wait_event(ready[0])
+            t = ready[1]
+        else:
+            t = self.time_emb_proj(temb if getattr(temb, "_silu_applied", False) else self.nonlinearity(temb))
         h = self.dropout(group_norm_act(self.norm2, h, True, chan_add=t))   # norm2(h + t)
         if self.conv_shortcut is not None:      # fresh tensor: conv2 may accumulate into it
             return add_residual(self.conv2, h, self.conv_shortcut(x))
@@ -527,6 +532,28 @@ class UNet2DConditionModel(nn.Module):
             m._kv_cache = None
         self._ctx_attn, self._ctx_buffers = [], []
 
+    def _prefetch_temb(self, emb: torch.Tensor):
+        """All `time_emb_proj(silu(temb))` of the forward depend only on the time embedding: issue them (one small
+        weight-streaming launch each) on a side stream right away, in the order the ResNet blocks will need them, so
+        that they run beside the main branch instead of between its kernels.  Each block waits on its own event."""
+        blocks = self.__dict__.get("_resnet_order")
+        if blocks is None:
+            blocks = [m for m in self.modules() if isinstance(m, ResnetBlock2D)]   # registration order == call order
+            self.__dict__["_resnet_order"] = blocks
+            self.__dict__["_side_streams"] = {}
+        dev = emb.device
+        side = self._side_streams.get(dev)
+        if side is None:
+            side = self._side_streams[dev] = torch.cuda.Stream(device=dev)
+        main = torch.cuda.current_stream(dev)
+        side.wait_stream(main)
+        with torch.cuda.stream(side):
+            for rb in blocks:
+                t = rb.time_emb_proj(emb)
+                ev = torch.cuda.Event()
+                ev.record(side)
+                rb.__dict__["_t_ready"] = (ev, t)
+
     def enable_xformers_memory_efficient_attention(self):  # API parity (train_lora.py:68); SDPA is used
         return None
 
@@ -544,6 +571,8 @@ class UNet2DConditionModel(nn.Module):
         # every ResnetBlock2D applies the same SiLU to the same embedding before its time_emb_proj: do it once
         emb = F.silu(emb)
         emb._silu_applied = True
+        if emb.is_cuda and not torch.is_grad_enabled() and "temb_stream" not in _DISABLED:
+            self._prefetch_temb(emb)
         x = self.conv_in(sample.contiguous(memory_format=torch.channels_last))
         skips = [x]
         for blk in self.down_blocks:
