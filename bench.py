@@ -122,8 +122,11 @@ def fused_gemm_roofline(engine, pk: dict, reps: int = 5) -> dict:
     finally:
         ops.lora_forward, ops.lora_forward_grouped = real, real_grouped
     torch.cuda.synchronize()
-    flops, args = 0.0, []
+    flops, alg_bytes, args = 0.0, 0.0, []
     for (kind, xs, ws, has_b, r, s, k, dt, has_res) in calls:
+        es = 2 if dt == torch.bfloat16 else 4
+        alg_bytes += es * (float(torch.Size(xs).numel()) + float(torch.Size(ws).numel()) +
+                           float(torch.Size(xs[:-1]).numel()) * ws[0] * (2 if has_res else 1))
         M = 1
         for d in xs[:-1]:
             M *= d
@@ -167,8 +170,22 @@ def fused_gemm_roofline(engine, pk: dict, reps: int = 5) -> dict:
     peak = float(pk.get("bf16_tflops_sustained", pk["bf16_tflops"]))
     return {"bound": "tensor", "kernel": "lora_gemm_kernel", "achieved": round(achieved, 1), "peak": peak,
             "peak_source": pk["source"] + ":bf16_tflops_sustained", "unit": "TFLOP/s", "frac": round(achieved / peak, 4),
-            "traffic": None, "launches": len(calls), "avg_launch_us": round(sec / len(calls) * 1e6, 2),
-            "flops_per_forward": flops}
+            "traffic": measured_traffic(), "launches": len(calls), "avg_launch_us": round(sec / len(calls) * 1e6, 2),
+            "flops_per_forward": flops, "algorithmic_bytes_per_launch": round(alg_bytes / len(calls))}
+
+
+def measured_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum per lora_gemm_kernel launch, from the committed `ncu --set full`
+    capture of the same forward (tools/profile_forward.py -> tools/ncu_traffic.py -> profiles/gemm_traffic.json)."""
+    f = ROOT / "profiles" / "gemm_traffic.json"
+    if not f.exists():
+        return None
+    try:
+        ks = json.loads(f.read_text())["kernels"]
+        k = next(v for n, v in ks.items() if "lora_gemm_kernel" in n)
+        return round(k["avg_dram_bytes_per_launch"])
+    except Exception:
+        return None
 
 
 def phase_breakdown(engine, reps: int = 5) -> dict:
