@@ -671,6 +671,7 @@ namespace slider {
 struct TileGeom { int TW, TH, TB; };
 
 static long long* g_gemm_trace = nullptr;   // set by slider_debug_gemm_trace (profiling aid)
+static int g_splitk_depth = 6;      // minimum K blocks per split (slider_debug_splitk_depth)
 
 static TileGeom choose_tile(int W, int H, int B) {
   TileGeom t;
@@ -797,7 +798,7 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
   p.partial = reinterpret_cast<float*>(ws);
   if (ws != nullptr && ((uintptr_t)ws & 15) == 0 && p.total_tiles * 2 <= sm_count()) {
     int ks = sm_count() / p.total_tiles;
-    const int by_depth = p.kiters / 6;
+    const int by_depth = p.kiters / g_splitk_depth;
     if (ks > by_depth) ks = by_depth;
     const long long cap = (long long)(ws_bytes / (UNIT_FLOATS * sizeof(float)));
     if ((long long)ks * p.total_tiles > cap) ks = (int)(cap / p.total_tiles);
@@ -873,6 +874,7 @@ using namespace slider;
 
 extern "C" {
 
+int slider_debug_splitk_depth(int d) { g_splitk_depth = d > 0 ? d : 6; return SLIDER_OK; }
 int slider_debug_gemm_trace(void* buf) { g_gemm_trace = reinterpret_cast<long long*>(buf); return SLIDER_OK; }
 
 size_t slider_gemm_workspace_bytes(void) { return (size_t)MAX_UNITS * UNIT_FLOATS * sizeof(float); }

@@ -5,7 +5,11 @@ import sys
 from pathlib import Path
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
 import torch
-from sliders_conceptmod_b200 import ops
+from sliders_conceptmod_b200 import ops, _lib
+import ctypes
+DEPTH = int(sys.argv[1]) if len(sys.argv) > 1 else 6
+_lib.lib().slider_debug_splitk_depth.argtypes = [ctypes.c_int]
+_lib.lib().slider_debug_splitk_depth(DEPTH)
 
 SHAPES = [(2, 16, 16, 1280, 1280, 3), (2, 8, 8, 1280, 1280, 3), (2, 8, 8, 2560, 1280, 3), (2, 16, 16, 2560, 1280, 3),
           (2, 16, 16, 1920, 1280, 3), (1, 1, 512, 1280, 1280, 1), (1, 1, 512, 5120, 1280, 1), (2, 32, 32, 640, 640, 3),
@@ -31,4 +35,4 @@ for (B, H, W, C, N, k) in SHAPES:
     e1.record(); torch.cuda.synchronize()
     us = e0.elapsed_time(e1) * 1e3 / 160
     flops = 2.0 * B * H * W * N * C * k * k
-    print(json.dumps({"shape": [B, H, W, C, N, k], "us": round(us, 2), "tflops": round(flops / us / 1e6, 1)}), flush=True)
+    print(json.dumps({"depth": DEPTH, "shape": [B, H, W, C, N, k], "us": round(us, 2), "tflops": round(flops / us / 1e6, 1)}), flush=True)
