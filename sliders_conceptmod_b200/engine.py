@@ -203,6 +203,62 @@ class SliderEngine:
         self.optimizer_step()
         return self.loss
 
+    # ---- image-pair slider iteration (trainscripts/imagesliders/train_lora-scale.py:196-340) ------------------
+    def load_image_pair_prompts(self, positive, neutral, unconditional):
+        """Stage the two CFG embedding batches of the image-slider objective: [uncond, positive] for the "high"
+        side, [uncond, neutral] for the "low" side."""
+        b = self.b
+        rep = lambda e: e.to(self.device, self.dtype).repeat_interleave(b, dim=0)
+        u, p, n = rep(unconditional), rep(positive), rep(neutral)
+        self.emb_den.copy_(torch.cat([u, p]))          # high side
+        self.emb_tgt.copy_(torch.cat([u, n]))          # low side
+        if hasattr(self.unet, "refresh_context_cache"):
+            self.unet.refresh_context_cache()
+
+    def _body_image_side(self, emb, scale: float):
+        """noisy = add_noise(side latents, noise, t) -> grad prediction with the adapter at `scale` -> MSE against
+        the noise that was added -> backward into the flat gradient buffer (accumulating)."""
+        noisy = ops.cfg_step(self.lat, None, None, self.noise, dev_coef=self.coef)
+        self.network.set_lora_slider(scale)
+        with self.network:
+            x = torch.cat([noisy] * 2)
+            if self._needs_scale:
+                x = ops.cfg_step(x, None, None, None, dev_coef=self.in_scale)
+            eps = self._unet(x, emb, None)
+            target = train_util._CFGCombineFn.apply(eps, 1.0)
+        from .prompt_util import plain_mse
+        loss = plain_mse(target, self.noise)
+        loss.backward()
+        return loss.detach()
+
+    def image_slider_step(self, lat_low: torch.Tensor, lat_high: torch.Tensor, noise: torch.Tensor, timesteps_to: int,
+                          scale: float):
+        """One optimizer step of the image-pair objective: both sides share `noise` and the timestep; the adapter
+        runs at +scale on the high latents / positive prompt and at -scale on the low latents / neutral prompt; the
+        two backward passes accumulate before ONE AdamW launch.  Each (side, scale) body is a replayed CUDA graph
+        (the scale is a host scalar of the captured launches).  Returns (loss_high, loss_low) device scalars."""
+        if not hasattr(self, "noise"):
+            self.noise = torch.zeros_like(self.lat)
+            self.loss_pair = torch.zeros(2, device=self.device, dtype=torch.float32)
+        n_den = self.cfg.max_denoising_steps
+        t_add = self._table(n_den)[3][timesteps_to]
+        if self._needs_scale:
+            raise NotImplementedError("image_slider_step: add_noise of the sigma-parameterised schedulers is not tabled")
+        a = float(self.sched._ac[int(t_add)])
+        t1000, _, s1000, _ = self._table(1000)
+        idx = int(timesteps_to * 1000 / n_den)
+        self.t_dev.copy_(t1000[idx:idx + 1]); self.in_scale.copy_(s1000[idx])
+        self.coef.copy_(torch.tensor([0.0, a ** 0.5, 0.0, (1.0 - a) ** 0.5]), non_blocking=True)
+        self.noise.copy_(noise.to(self.dtype), non_blocking=True)
+        self.network.flat_grad.zero_()
+        for k, (lat, emb, sc) in enumerate(((lat_high, self.emb_den, float(scale)), (lat_low, self.emb_tgt, -float(scale)))):
+            self.lat.copy_(lat.to(self.dtype), non_blocking=True)
+            name = f"image_{k}_{sc:+.4f}"
+            self._exec(name, lambda emb=emb, sc=sc, k=k: self.loss_pair[k:k + 1].copy_(self._body_image_side(emb, sc).reshape(1)),
+                       restore=(self.network.flat_grad,))      # the warm-up passes of a first capture must not accumulate
+        self.optimizer_step()
+        return self.loss_pair[0], self.loss_pair[1]
+
     def optimizer_step(self):
         g = self.network.flat_grad
         pre = 1.0

@@ -78,8 +78,9 @@ class PairedLatents:
 class ImageSliderTrainer:
     """State of one image-slider run; `iteration(i)` is one pass of the reference loop body (:196-340)."""
 
-    def __init__(self, config, prompts, device, data: PairedLatents, seed=None):
+    def __init__(self, config, prompts, device, data: PairedLatents, seed=None, engine: bool = False):
         self.config, self.device, self.data = config, torch.device(device), data
+        self.use_engine, self.engine, self._staged_pair = engine, None, None
         self.weight_dtype = config_util.parse_precision(config.train.precision)
         self.save_weight_dtype = config_util.parse_precision(config.train.precision)
         if seed is not None:
@@ -134,6 +135,8 @@ class ImageSliderTrainer:
             scale_to_look = abs(random.choice(self.data.unique_scales()))
             lat_low, lat_high = self.data.sample(scale_to_look)
             noise_seed = random.randint(0, 2 * 15)
+            if self.use_engine:
+                return self._engine_iteration(pair, timesteps_to, scale_to_look, lat_low, lat_high, noise_seed)
             denoised_low, low_noise = get_noisy_latents(lat_low, torch.manual_seed(noise_seed), sched, timesteps_to,
                                                         dev, dt)
             denoised_high, high_noise = get_noisy_latents(lat_high, torch.manual_seed(noise_seed), sched, timesteps_to,
@@ -159,6 +162,39 @@ class ImageSliderTrainer:
         self.lr_scheduler.step()
         return loss_high.detach(), loss_low.detach()
 
+    def _engine_iteration(self, pair, timesteps_to, scale, lat_low, lat_high, noise_seed):
+        """Same draws, issued through engine.SliderEngine.image_slider_step: add_noise, the two grad predictions,
+        both losses and backward passes replay as CUDA graphs, gradients land in the flat buffer, one fused AdamW."""
+        from .engine import EngineConfig, SliderEngine
+        cfg = self.config
+        if cfg.train.optimizer.lower() != "adamw":
+            raise NotImplementedError("engine=True implements AdamW (the reference default)")
+        if self.engine is None:
+            ecfg = EngineConfig(max_denoising_steps=cfg.train.max_denoising_steps, lr=cfg.train.lr, use_graphs=True)
+            for k, v in self.optimizer.defaults.items():
+                if k == "betas":
+                    ecfg.betas = tuple(v)
+                elif k == "eps":
+                    ecfg.eps = float(v)
+                elif k == "weight_decay":
+                    ecfg.weight_decay = float(v)
+            h, w = lat_low.shape[-2] * 8, lat_low.shape[-1] * 8
+            self.engine = SliderEngine(self.unet, self.network, self.scheduler, ecfg, pair.batch_size, h, w,
+                                       tuple(pair.target.shape[1:]), self.weight_dtype, self.device)
+        if self._staged_pair is not pair:
+            self.engine.load_image_pair_prompts(pair.positive, pair.neutral, pair.unconditional)
+            self._staged_pair = pair
+        # shared by both sides (:231); leaves the global generator where the eager loop's second draw leaves it
+        noise = torch.randn(lat_low.shape, generator=torch.manual_seed(noise_seed))
+        self.last = dict(pair=pair, timesteps_to=timesteps_to, scale=scale, lat_low=lat_low, lat_high=lat_high,
+                         noise_seed=noise_seed)
+        self.engine.lr = self.optimizer.param_groups[0]["lr"]
+        with torch.enable_grad():
+            loss_high, loss_low = self.engine.image_slider_step(lat_low, lat_high, noise, timesteps_to, scale)
+        self.optimizer.step()               # no .grad attached (flat buffer): only keeps the LR-schedule bookkeeping
+        self.lr_scheduler.step()
+        return loss_high.clone(), loss_low.clone()
+
     def run(self, save_file: bool = True):
         cfg = self.config
         save_path = Path(cfg.save.path)
@@ -175,12 +211,12 @@ class ImageSliderTrainer:
 
 
 def train(config, prompts, device, folder_main=None, folders=None, scales=None, synthetic: int = 0, seed=None,
-          save_file: bool = True):
+          save_file: bool = True, engine: bool = False):
     if scales is None:
         raise TypeError("train() needs scales (and folders or synthetic=N)")       # upstream crashes here
     data = PairedLatents(folder_main, folders, scales, synthetic=synthetic, seed=seed or 0,
                          latent_hw=prompts[0].resolution // 8 if prompts else 32)
-    trainer = ImageSliderTrainer(config, prompts, device, data, seed=seed)
+    trainer = ImageSliderTrainer(config, prompts, device, data, seed=seed, engine=engine)
     losses = trainer.run(save_file=save_file)
     return trainer.network, losses
 
@@ -202,7 +238,8 @@ def main(args):
     scales = [int(s.strip()) for s in args.scales.split(",")]
     if len(scales) != len(folders):
         raise Exception("the number of folders need to match the number of scales")
-    train(config, prompts, device, folder_main=args.folder_main, folders=folders, scales=scales, synthetic=args.synthetic)
+    train(config, prompts, device, folder_main=args.folder_main, folders=folders, scales=scales, synthetic=args.synthetic,
+          engine=args.engine)
 
 
 def build_parser() -> argparse.ArgumentParser:
@@ -221,6 +258,8 @@ def build_parser() -> argparse.ArgumentParser:
                         help="folders with different attribute-scaled images")
     parser.add_argument("--scales", type=str, required=False, default="-2, -1,1, 2",
                         help="scales for different attribute-scaled images")
+    parser.add_argument("--engine", action="store_true",
+                        help="B200 extension: CUDA-graph engine + flat AdamW for the iteration body")
     parser.add_argument("--synthetic", type=int, default=0, help="draw N seeded synthetic latent pairs instead of folders")
     return parser
 

@@ -61,11 +61,15 @@ def config4(steps=6):
         config = config_util.load_config_from_yaml(str(Path(tmp, "c.yaml")))
         ps = prompt_util.load_prompts_from_yaml(config.prompts_file, [])
         data = PairedLatents(scales=[-1, 1], synthetic=8, latent_hw=32, seed=1)
-        tr = ImageSliderTrainer(config, ps, "cuda", data, seed=1)
-        sec = timed(lambda i: tr.iteration(i), steps)
-        print(json.dumps({"config": 4, "workload": "sd14_image_slider_256px", "metric": "image_slider_iterations_per_sec",
-                          "value": round(1 / sec, 3), "ms_per_iteration": round(sec * 1e3, 2),
-                          "note": "eager drop-in loop (2 grad forwards + 2 backwards + torch AdamW per iteration)"}), flush=True)
+        for engine in (False, True):
+            data = PairedLatents(scales=[-1, 1], synthetic=8, latent_hw=32, seed=1)
+            tr = ImageSliderTrainer(config, ps, "cuda", data, seed=1, engine=engine)
+            sec = timed(lambda i: tr.iteration(i), steps, warmup=3)
+            print(json.dumps({"config": 4, "workload": "sd14_image_slider_256px", "metric": "image_slider_iterations_per_sec",
+                              "value": round(1 / sec, 3), "ms_per_iteration": round(sec * 1e3, 2),
+                              "note": ("--engine: two graph-replayed grad forward/backward sides + flat AdamW" if engine else
+                                       "eager drop-in loop (2 grad forwards + 2 backwards + torch AdamW per iteration)")}), flush=True)
+            del tr
     torch.cuda.empty_cache()
 
 
