@@ -193,7 +193,7 @@ def phase_breakdown(engine, reps: int = 5) -> dict:
     forward (x timesteps_to per step), the batched adapter-off predictions, the grad forward+loss+backward, AdamW."""
     out = {}
     saved = engine.lat.clone()
-    for name in ("denoise", "predict", "train"):
+    for name in ("denoise", "predict", "train", "predict_train"):
         g = engine._graphs.get(name)
         if g is None:
             continue

@@ -13,6 +13,8 @@ serves every denoising step, and the three adapter-off predictions share one lau
 """
 from __future__ import annotations
 
+import os
+
 from dataclasses import dataclass
 
 import torch
@@ -33,6 +35,8 @@ class EngineConfig:
     weight_decay: float = 1e-2          # torch.optim.AdamW default
     max_grad_norm: float | None = None  # train_lora_xl.py:349 uses 0.2
     use_graphs: bool = True
+    # predictions on a parallel graph branch beside the grad forward (SLIDER_DISABLE=ptrain: A/B switch)
+    overlap_predict: bool = "ptrain" not in os.environ.get("SLIDER_DISABLE", "")
 
 
 class SliderEngine:
@@ -131,6 +135,26 @@ class SliderEngine:
         loss.backward()
         self.loss.copy_(loss.detach())
 
+    def _body_predict_train(self):
+        """The three adapter-off predictions (one batch-6 forward) do not depend on the grad forward: they run on a
+        second stream — a parallel branch of the captured graph, with its own scratch lane — and join before the
+        loss needs them (train_lora.py:216-289 evaluates them one after the other)."""
+        main = torch.cuda.current_stream()
+        if not hasattr(self, "_predict_stream"):
+            self._predict_stream = torch.cuda.Stream(device=self.device)
+        side = self._predict_stream
+        self.network.flat_grad.zero_()
+        side.wait_stream(main)
+        with torch.cuda.stream(side), ops.workspace_lane(1):
+            self._body_predict()
+        with self.network:
+            eps = self._unet(self._model_input(2), self.emb_tgt, self.xl and self.xl["tgt"])
+            target = train_util._CFGCombineFn.apply(eps, 1.0)
+        main.wait_stream(side)
+        loss = guidance_mse(target, self.positive, self.neutral, self.uncond, self.guidance, self.sign)
+        loss.backward()
+        self.loss.copy_(loss.detach())
+
     def _run(self, name: str, body):
         if not self.cfg.use_graphs:
             n0 = ops.launch_count()
@@ -180,6 +204,7 @@ class SliderEngine:
         if (guidance_scale, action) != (self.guidance, "enhance" if self.sign > 0 else "erase"):
             self.guidance, self.sign = float(guidance_scale), (1 if action == "enhance" else -1)
             self._graphs.pop("train", None)     # host scalars are baked into the captured launch
+            self._graphs.pop("predict_train", None)
         if self.xl is not None and xl is not None:
             for key in self.xl["den"]:
                 cu, ct, cp, cn = (rep(xl[key][r]) for r in ("unconditional", "target", "positive", "neutral"))
@@ -198,8 +223,11 @@ class SliderEngine:
         t1000, _, s1000, ts = self._table(1000)                        # train_lora.py:209-213
         idx = int(timesteps_to * 1000 / n_den)
         self.t_dev.copy_(t1000[idx:idx + 1]); self.in_scale.copy_(s1000[idx])
-        self._exec("predict", self._body_predict)
-        self._exec("train", self._body_train)
+        if self.cfg.use_graphs and self.cfg.overlap_predict:
+            self._exec("predict_train", self._body_predict_train)
+        else:
+            self._exec("predict", self._body_predict)
+            self._exec("train", self._body_train)
         self.optimizer_step()
         return self.loss
 

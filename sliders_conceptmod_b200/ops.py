@@ -26,12 +26,36 @@ def _act_dims(x: torch.Tensor) -> tuple[int, int, int]:
     raise ValueError(f"expected [B,H,W,C] or [M,K] activations, got {tuple(x.shape)}")
 
 
-_gemm_ws: dict[int, torch.Tensor] = {}
+_lane = 0
+
+
+class workspace_lane:
+    """Scratch buffers (split-K partials, GroupNorm partials, ...) are shared by all calls ordered on ONE stream.
+    Work issued concurrently on another stream (a second branch of a captured graph) must use its own set:
+    `with ops.workspace_lane(1): ...` around that branch."""
+
+    def __init__(self, lane: int):
+        self.lane, self.prev = lane, 0
+
+    def __enter__(self):
+        global _lane
+        self.prev, _lane = _lane, self.lane
+
+    def __exit__(self, *exc):
+        global _lane
+        _lane = self.prev
+
+
+def _ws_key(device: torch.device):
+    return (device.index if device.index is not None else torch.cuda.current_device(), _lane)
+
+
+_gemm_ws: dict = {}
 
 
 def _gemm_workspace(device: torch.device) -> torch.Tensor:
     """Per-device split-K scratch (contents don't-care; every call on the stream may share it)."""
-    key = device.index if device.index is not None else torch.cuda.current_device()
+    key = _ws_key(device)
     ws = _gemm_ws.get(key)
     if ws is None:
         ws = torch.empty(lib().slider_gemm_workspace_bytes(), dtype=torch.uint8, device=device)
@@ -105,7 +129,7 @@ _loss_ws: dict[int, torch.Tensor] = {}
 
 
 def _reduce_ws(device: torch.device) -> torch.Tensor:
-    key = device.index if device.index is not None else torch.cuda.current_device()
+    key = _ws_key(device)
     ws = _loss_ws.get(key)
     if ws is None:
         ws = torch.zeros(lib().slider_loss_workspace_bytes(), dtype=torch.uint8, device=device)
@@ -170,7 +194,7 @@ def groupnorm_nhwc(x: torch.Tensor, groups: int, gamma: torch.Tensor | None, bet
     assert x.is_contiguous()
     B, Cc = x.shape[0], x.shape[-1]
     hw = x.numel() // (B * Cc)
-    key = x.device.index if x.device.index is not None else torch.cuda.current_device()
+    key = _ws_key(x.device)
     need = lib().slider_groupnorm_workspace_bytes(int(B), int(groups))
     ws = _gn_ws.get(key)
     if ws is None or ws.numel() < need:
@@ -203,7 +227,7 @@ def groupnorm_nhwc_backward(gy: torch.Tensor, x: torch.Tensor, stats: torch.Tens
     assert x.is_contiguous() and gy.is_contiguous() and gy.shape == x.shape and gy.dtype == x.dtype
     B, Cc = x.shape[0], x.shape[-1]
     hw = x.numel() // (B * Cc)
-    key = x.device.index if x.device.index is not None else torch.cuda.current_device()
+    key = _ws_key(x.device)
     need = lib().slider_groupnorm_bwd_workspace_bytes(int(B), int(Cc), int(groups))
     ws = _gn_bwd_ws.get(key)
     if ws is None or ws.numel() < need:
@@ -266,7 +290,7 @@ _grad_ws: dict[int, torch.Tensor] = {}
 
 
 def _grad_workspace(device: torch.device, need: int) -> torch.Tensor:
-    key = device.index if device.index is not None else torch.cuda.current_device()
+    key = _ws_key(device)
     ws = _grad_ws.get(key)
     if ws is None or ws.numel() < need:
         ws = torch.empty(need + (1 << 20), dtype=torch.uint8, device=device)
