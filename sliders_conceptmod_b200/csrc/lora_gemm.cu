@@ -34,15 +34,40 @@ constexpr int L_BYTES = HCOLS * ROW_BYTES;   // 2 KB
 constexpr int STAGE_BYTES = A_BYTES + B_BYTES + L_BYTES;
 constexpr int EXT_ELEMS = 16;    // width of the extended-K operand (dh / At), in elements
 constexpr int TMEM_COLS = 512;
-constexpr int kGemmThreads = 192;
-constexpr int EPI_FLOATS = BN * 16 + BN;     // s*Bup (rank padded to <=16) + bias
-constexpr int NCHUNK = BN / 32 + 1;          // 32-column chunks of a split-K partial tile (+1 for h)
-constexpr size_t UNIT_FLOATS = (size_t)NCHUNK * BM * 32;
+constexpr int kGemmThreads = 320;            // warp 0 TMA, warp 1 MMA, warps 2..9 epilogue (two groups of four)
+constexpr int kEpiThreads = 256;
+constexpr int HALF_N = BN / 2;               // output columns owned by one epilogue group
+constexpr int OUT_ROW_BYTES = 80;            // staging row of one store chunk: 40 bf16 / 20 fp32 columns; an 80-byte
+                                             // pitch makes the 16-byte st.shared of 8 consecutive rows conflict-free
+constexpr int OUT_BYTES = BM * OUT_ROW_BYTES;   // 10 KB per chunk buffer
+// staging buffers per epilogue group: three when the rank table leaves room (rank <= 8), else two
+__host__ __device__ constexpr int out_bufs_per_group(int r4) { return r4 <= 2 ? 3 : 2; }
+__host__ __device__ constexpr int epi_floats(int r4) { return BN * 4 * (r4 > 0 ? r4 : 1) + BN; }   // s*Bup + bias
+__host__ __device__ constexpr size_t gemm_smem_bytes(int r4) {
+  return 1024 /*align slack*/ + (size_t)NSTAGES * STAGE_BYTES + (size_t)2 * out_bufs_per_group(r4) * OUT_BYTES +
+         (size_t)epi_floats(r4) * 4 + 256;
+}
+constexpr int PCW = OUT_ROW_BYTES / 4;       // fp32 columns per split-K partial chunk
+constexpr int NCHUNK = BN / PCW + 1;         // partial chunks of a split-K unit (+1 for h)
+constexpr size_t UNIT_FLOATS = (size_t)NCHUNK * BM * PCW;
 constexpr int MAX_UNITS = 160;               // split-K work units the caller workspace must hold
-constexpr int OUT_BUFS = 3;                  // staging buffers of the TMA-store epilogue (one 32-column chunk each)
-constexpr int OUT_BYTES = BM * 32 * 4;       // 16 KB: 128 rows x 32 fp32 (bf16 output uses half of it)
-constexpr size_t SMEM_BYTES = 1024 /*align slack*/ + (size_t)NSTAGES * STAGE_BYTES + (size_t)OUT_BUFS * OUT_BYTES +
-                              EPI_FLOATS * 4 + 256;
+
+// Division by a launch-constant through a host-computed multiplier (n < 2^31): the producer's tile -> coordinate
+// chain is on the critical path of every launch and eight hardware divisions cost ~1000 cycles there.
+struct FastDiv {
+  uint32_t d, mul, shr;
+  static FastDiv make(uint32_t d) {
+    FastDiv f; f.d = d; f.mul = 0; f.shr = 0;
+    if (d <= 1) { f.d = 1; return f; }
+    uint32_t l = 0;
+    while ((1u << l) < d) ++l;
+    f.mul = (uint32_t)(((1ull << (31 + l)) + d - 1) / d);
+    f.shr = l - 1;
+    return f;
+  }
+  __device__ __forceinline__ uint32_t div(uint32_t n) const { return d == 1 ? n : (__umulhi(n, mul) >> shr); }
+  __device__ __forceinline__ void divmod(uint32_t n, uint32_t& q, uint32_t& r) const { q = div(n); r = n - q * d; }
+};
 
 template <typename T> struct GemmTraits;
 template <> struct GemmTraits<__nv_bfloat16> {
@@ -89,7 +114,8 @@ struct GemmParams {
   float* partial;         // split-K partial tiles, [unit][NCHUNK][128][32] fp32
   int accumulate;         // y += result (y holds the residual branch) instead of y = result
   int group_n;            // grouped adapters: output columns per group (0 = one adapter); group g uses h columns [g*rank, (g+1)*rank)
-  long long* trace;       // debug: 8 clock64() stamps per CTA (NULL = off)
+  FastDiv fd_n_tiles, fd_mt_w, fd_mt_h, fd_ksplit, fd_per_tap, fd_kw;
+  long long* trace;       // debug: 16 clock64() stamps per CTA (NULL = off)
   void* y;
   const void* bias;
   const void* Bup;
@@ -100,14 +126,46 @@ struct TileCoord { int w0, h0, b0, n0, n_blk; };
 
 __device__ __forceinline__ TileCoord tile_coord(const GemmParams& p, int tile) {
   TileCoord t;
-  t.n_blk = tile % p.n_tiles;
-  int mi = tile / p.n_tiles;
-  int wt = mi % p.mt_w; mi /= p.mt_w;
-  int ht = mi % p.mt_h;
-  int bt = mi / p.mt_h;
-  t.w0 = wt * p.TW; t.h0 = ht * p.TH; t.b0 = bt * p.TB; t.n0 = t.n_blk * BN;
+  uint32_t mi, nb, wt, ht, bt;
+  p.fd_n_tiles.divmod((uint32_t)tile, mi, nb);
+  p.fd_mt_w.divmod(mi, mi, wt);
+  p.fd_mt_h.divmod(mi, bt, ht);
+  t.n_blk = (int)nb;
+  t.w0 = (int)wt * p.TW; t.h0 = (int)ht * p.TH; t.b0 = (int)bt * p.TB; t.n0 = t.n_blk * BN;
   return t;
 }
+
+// K-iteration range [it0, it1) of split `split` of a tile
+__device__ __forceinline__ void split_range(const GemmParams& p, uint32_t split, int& it0, int& it1) {
+  it0 = (int)p.fd_ksplit.div(split * (uint32_t)p.kiters);
+  it1 = (int)p.fd_ksplit.div((split + 1) * (uint32_t)p.kiters);
+}
+
+template <int CW> struct TmemChunk;
+template <> struct TmemChunk<40> {
+  __device__ static __forceinline__ void ld(uint32_t taddr, uint32_t (&v)[40]) {
+    uint32_t a[32], b[8];
+    ptx::tmem_ld_32x32(taddr, a);
+    ptx::tmem_ld_32x8(taddr + 32, b);
+    ptx::tmem_ld_wait();
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = a[i];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[32 + i] = b[i];
+  }
+};
+template <> struct TmemChunk<20> {
+  __device__ static __forceinline__ void ld(uint32_t taddr, uint32_t (&v)[20]) {
+    uint32_t a[16], b[4];
+    ptx::tmem_ld_32x16(taddr, a);
+    ptx::tmem_ld_32x4(taddr + 16, b);
+    ptx::tmem_ld_wait();
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = a[i];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) v[16 + i] = b[i];
+  }
+};
 
 template <typename T, int R4>
 __global__ void __launch_bounds__(kGemmThreads, 1)
@@ -122,9 +180,10 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* s_out = smem + (size_t)NSTAGES * STAGE_BYTES;   // OUT_BUFS x 16 KB, 1024-aligned (swizzled staging)
-  float* s_epi = reinterpret_cast<float*>(s_out + (size_t)OUT_BUFS * OUT_BYTES);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_epi + EPI_FLOATS);
+  constexpr int NB = out_bufs_per_group(R4);               // staging buffers per epilogue group
+  uint8_t* s_out = smem + (size_t)NSTAGES * STAGE_BYTES;   // 2 x NB x 10 KB staging of the TMA-store epilogue
+  float* s_epi = reinterpret_cast<float*>(s_out + (size_t)2 * NB * OUT_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_epi + epi_floats(R4));
   uint64_t* full_bar = bars;                      // [NSTAGES]  TMA -> MMA
   uint64_t* empty_bar = bars + NSTAGES;           // [NSTAGES]  MMA -> TMA
   uint64_t* tfull_bar = bars + 2 * NSTAGES;       // [ACC_STAGES] MMA -> epilogue
@@ -132,11 +191,56 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint64_t* xf_bar = tempty_bar + ACC_STAGES;     // [NSTAGES] hi/lo split done (fp32 only) -> MMA
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(xf_bar + NSTAGES);
 
-  const int warp = threadIdx.x >> 5;
+  // warp index through a shuffle so that the role branches below are provably warp-uniform
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
-#define SLIDER_TRACE(slot) do { if (p.trace != nullptr) p.trace[blockIdx.x * 8 + (slot)] = clock64(); } while (0)
+#define SLIDER_TRACE(slot) do { if (p.trace != nullptr) p.trace[blockIdx.x * 16 + (slot)] = clock64(); } while (0)
   pdl_trigger();
   if (threadIdx.x == 0) SLIDER_TRACE(0);
+
+  const uint32_t smem_base = ptx::smem_u32(smem);
+  const uint32_t main_tx = (uint32_t)(p.rows * ROW_BYTES + B_BYTES + (p.lora ? L_BYTES : 0));
+  const uint32_t ext_tx = (uint32_t)((p.rows + BN) * Tr::kExtRowBytes);
+
+  // ---- TMA producer state (thread 0 only).  The producer issues its first kStages K blocks BEFORE the CTA-wide
+  // barrier below, so the first operand fetch overlaps the TMEM allocation and the other warps' start-up.
+  int pu = (int)blockIdx.x, pit = 0, pit1 = 0, ptap = 0, pj = 0;
+  uint32_t pstage = 0, pphase = 0;
+  TileCoord ptc = {0, 0, 0, 0, 0};
+  bool phave = false;
+  auto prod_begin = [&]() {
+    phave = pu < p.total_units;
+    if (!phave) return;
+    uint32_t tile = (uint32_t)pu, split = 0;
+    if (p.ksplit > 1) p.fd_ksplit.divmod((uint32_t)pu, tile, split);
+    ptc = tile_coord(p, (int)tile);
+    pit = 0; pit1 = p.kiters; ptap = 0; pj = 0;
+    if (p.ksplit > 1) {
+      split_range(p, split, pit, pit1);
+      ptap = (int)p.fd_per_tap.div((uint32_t)pit);
+      pj = pit - ptap * p.per_tap;
+    }
+  };
+  auto prod_issue = [&]() {
+    const int ty = (int)p.fd_kw.div((uint32_t)ptap);
+    const int dy = ty - p.pad, dx = ptap - ty * p.kw - p.pad;
+    ptx::mbar_wait(ptx::smem_u32(empty_bar + pstage), pphase ^ 1);
+    const uint32_t sa = smem_base + pstage * Tr::kStageStride;
+    const uint32_t fb = ptx::smem_u32(full_bar + pstage);
+    if (pj < p.cblocks) {
+      ptx::mbar_arrive_expect_tx(fb, main_tx);
+      ptx::tma_load_4d(sa, &tmA, fb, pj * BK, ptc.w0 + dx, ptc.h0 + dy, ptc.b0);
+      ptx::tma_load_3d(sa + A_BYTES, &tmW, fb, pj * BK, ptap, ptc.n0);
+      if (p.lora) ptx::tma_load_3d(sa + A_BYTES + B_BYTES, &tmL, fb, pj * BK, ptap, 0);
+    } else {
+      ptx::mbar_arrive_expect_tx(fb, ext_tx);
+      ptx::tma_load_4d(sa, &tmXe, fb, 0, ptc.w0 + dx, ptc.h0 + dy, ptc.b0);
+      ptx::tma_load_3d(sa + A_BYTES, &tmWe, fb, 0, ptap, ptc.n0);
+    }
+    if (++pstage == (uint32_t)Tr::kStages) { pstage = 0; pphase ^= 1; }
+    if (++pj == p.per_tap) { pj = 0; ++ptap; }
+    if (++pit == pit1) { pu += (int)gridDim.x; prod_begin(); }
+  };
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tmA);
@@ -147,11 +251,11 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     for (int i = 0; i < NSTAGES; ++i) {
       ptx::mbar_init(ptx::smem_u32(full_bar + i), 1);
       ptx::mbar_init(ptx::smem_u32(empty_bar + i), 1);
-      ptx::mbar_init(ptx::smem_u32(xf_bar + i), 4);      // one arrive per epilogue warp
+      ptx::mbar_init(ptx::smem_u32(xf_bar + i), 8);      // one arrive per epilogue warp
     }
     for (int i = 0; i < ACC_STAGES; ++i) {
       ptx::mbar_init(ptx::smem_u32(tfull_bar + i), 1);
-      ptx::mbar_init(ptx::smem_u32(tempty_bar + i), 4);  // one arrive per epilogue warp
+      ptx::mbar_init(ptx::smem_u32(tempty_bar + i), 8);  // one arrive per epilogue warp
     }
     ptx::fence_mbar_init();
   }
@@ -160,51 +264,34 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     ptx::tmem_relinquish();
   }
   ptx::tc_fence_before();
-  __syncthreads();
+  // CTA-wide start barrier.  Warp 0 only ARRIVES (its lane 0 initialised the mbarriers above and is the one
+  // thread that never needs the TMEM base), so the producer starts fetching operands while the TMEM allocation
+  // and the other warps' start-up are still in flight.
+  if (warp == 0) {
+    __syncwarp();
+    asm volatile("bar.arrive 1, %0;" ::"n"(kGemmThreads) : "memory");
+  } else {
+    asm volatile("bar.sync 1, %0;" ::"n"(kGemmThreads) : "memory");
+  }
   ptx::tc_fence_after();
-  // PDL: barrier init, TMEM allocation and descriptor prefetch above overlap the previous kernel's tail; nothing
-  // below touches global memory before that kernel has completed
+  // PDL: nothing of ours reads global memory before the previous kernel has completed and flushed
   pdl_wait();
-  const uint32_t tmem_base = *tmem_slot;
-  const uint32_t smem_base = ptx::smem_u32(smem);
-  if (threadIdx.x == 0) SLIDER_TRACE(1);
+  const uint32_t tmem_base = warp == 0 ? 0u : *tmem_slot;
+  if (threadIdx.x == 32) SLIDER_TRACE(1);
 
-  const uint32_t main_tx = (uint32_t)(p.rows * ROW_BYTES + B_BYTES + (p.lora ? L_BYTES : 0));
-  const uint32_t ext_tx = (uint32_t)((p.rows + BN) * Tr::kExtRowBytes);
-
-  if (warp == 0 && lane == 0) {
+  // The two issuing roles run in ONE ELECTED lane (elect.sync, not `lane == 0`): ptxas then knows a single thread
+  // is active and feeds UTMALDG / UTCHMMA from uniform registers directly instead of wrapping every issue in an
+  // ELECT + R2UR.BROADCAST waterfall loop (which made the producer, ~500 cycles per K block, the main-loop bound).
+  if (warp == 0 && ptx::elect_one()) {
     // ===================== TMA producer =====================
-    uint32_t stage = 0, phase = 0;
-    for (int unit = blockIdx.x; unit < p.total_units; unit += gridDim.x) {
-      const int tile = p.ksplit > 1 ? unit / p.ksplit : unit, split = unit - tile * p.ksplit;
-      const TileCoord tc = tile_coord(p, tile);
-      int it0 = 0, it1 = p.kiters, tap = 0, j = 0;
-      if (p.ksplit > 1) {
-        it0 = split * p.kiters / p.ksplit;
-        it1 = (split + 1) * p.kiters / p.ksplit;
-        tap = it0 / p.per_tap; j = it0 - tap * p.per_tap;
-      }
-      for (int it = it0; it < it1; ++it) {
-        const int dy = tap / p.kw - p.pad, dx = tap % p.kw - p.pad;
-        ptx::mbar_wait(ptx::smem_u32(empty_bar + stage), phase ^ 1);
-        const uint32_t sa = smem_base + stage * Tr::kStageStride;
-        const uint32_t fb = ptx::smem_u32(full_bar + stage);
-        if (j < p.cblocks) {
-          ptx::mbar_arrive_expect_tx(fb, main_tx);
-          ptx::tma_load_4d(sa, &tmA, fb, j * BK, tc.w0 + dx, tc.h0 + dy, tc.b0);
-          ptx::tma_load_3d(sa + A_BYTES, &tmW, fb, j * BK, tap, tc.n0);
-          if (p.lora) ptx::tma_load_3d(sa + A_BYTES + B_BYTES, &tmL, fb, j * BK, tap, 0);
-        } else {
-          ptx::mbar_arrive_expect_tx(fb, ext_tx);
-          ptx::tma_load_4d(sa, &tmXe, fb, 0, tc.w0 + dx, tc.h0 + dy, tc.b0);
-          ptx::tma_load_3d(sa + A_BYTES, &tmWe, fb, 0, tap, tc.n0);
-        }
-        if (unit == (int)blockIdx.x && it == it0) SLIDER_TRACE(2);
-        if (++stage == Tr::kStages) { stage = 0; phase ^= 1; }
-        if (++j == p.per_tap) { j = 0; ++tap; }
-      }
+    prod_begin();
+    SLIDER_TRACE(8);
+    bool first = true;
+    while (phave) {
+      prod_issue();
+      if (first) { SLIDER_TRACE(2); first = false; }
     }
-  } else if (warp == 1 && lane == 0) {
+  } else if (warp == 1 && ptx::elect_one()) {
     // ===================== MMA issuer =====================
     // With the adapter on, W tile (BN rows) and lora_down tile (HCOLS rows) are adjacent in shared
     // memory and their accumulators adjacent in TMEM: ONE tcgen05.mma of N = BN + HCOLS covers both.
@@ -215,10 +302,10 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     for (int unit = blockIdx.x; unit < p.total_units; unit += gridDim.x) {
       int it0 = 0, it1 = p.kiters, j = 0;
       if (p.ksplit > 1) {
-        const int split = unit % p.ksplit;
-        it0 = split * p.kiters / p.ksplit;
-        it1 = (split + 1) * p.kiters / p.ksplit;
-        j = it0 % p.per_tap;
+        uint32_t tile, split;
+        p.fd_ksplit.divmod((uint32_t)unit, tile, split);
+        split_range(p, split, it0, it1);
+        j = it0 - (int)p.fd_per_tap.div((uint32_t)it0) * p.per_tap;
       }
       ptx::mbar_wait(ptx::smem_u32(tempty_bar + as), aphase ^ 1);
       ptx::tc_fence_after();
@@ -261,33 +348,44 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
   } else if (warp >= 2) {
     // ===================== epilogue =====================
-    // Per 32-column chunk: tcgen05.ld -> registers -> (+bias + s*h.Bup^T, cast) -> swizzled shared staging
-    // -> one TMA store (box {32 ch, TW, TH, TB}: fully coalesced, clips out-of-range pixels/channels).
-    // Three staging buffers and one named barrier per chunk: before the barrier of chunk c the issuing
-    // thread waits until at most one store (c-1) still reads shared memory, so the buffer the threads
-    // fill next (chunk c+1, last used by store c-2) is free once they pass that barrier.
+    // Eight warps = two groups of four; a group covers all 128 accumulator rows (one TMEM lane quarter per warp)
+    // and owns HALF_N = 80 of the tile's columns.  Per 80-byte chunk (40 bf16 / 20 fp32 columns):
+    // tcgen05.ld -> registers -> (+bias + s*h.Bup^T, cast) -> shared staging -> one TMA store (box {chunk, TW, TH,
+    // TB}: clips out-of-range pixels/channels).  NB staging buffers and one named barrier per group: before the
+    // barrier of chunk c the group's issuing thread waits until at most NB-2 stores still read shared memory, so the
+    // buffer the group fills next (chunk c+1, last used by store c+1-NB) is free once its threads pass that barrier.
     const int q = warp & 3;               // TMEM lane quarter this warp may read
     const int row = q * 32 + lane;        // tile row == TMEM lane
-    const int et = threadIdx.x - 64;      // 0..127 among epilogue threads
-    float* s_bias = s_epi + BN * 16;
-    const uint32_t out_base = ptx::smem_u32(s_out);
+    const int et = threadIdx.x - 64;      // 0..255 among epilogue threads
+    const int grp = et >> 7;              // column half owned by this thread's group
+    const int gt = et & 127;
+    constexpr int CW = OUT_ROW_BYTES / (int)sizeof(T);    // columns per store chunk
+    constexpr int CPG = HALF_N / CW;                      // store chunks per group
+    constexpr int PW = 16 / (int)sizeof(T);               // columns per 16-byte piece
+    constexpr int PCPG = HALF_N / PCW;                    // split-K partial chunks per group
+    float* s_bias = s_epi + BN * 4 * (R4 > 0 ? R4 : 1);
+    const uint32_t out_base = ptx::smem_u32(s_out) + (uint32_t)(grp * NB) * OUT_BYTES;
     const uint32_t epi_s = ptx::smem_u32(s_epi), bias_s = ptx::smem_u32(s_bias);
     uint32_t as = 0, aphase = 0, ob = 0, xs = 0, xphase = 0;
     const T* __restrict__ bias = reinterpret_cast<const T*>(p.bias);
     const T* __restrict__ Bup = reinterpret_cast<const T*>(p.Bup);
+#define SLIDER_GROUP_BAR() asm volatile("bar.sync %0, 128;" ::"r"(3 + grp) : "memory")
     for (int unit = blockIdx.x; unit < p.total_units; unit += gridDim.x) {
+      uint32_t tile = (uint32_t)unit, split = 0;
+      if (p.ksplit > 1) p.fd_ksplit.divmod((uint32_t)unit, tile, split);
       if (Tr::kSplit3) {
         // fp32: split every stage of this unit into hi / lo before the MMA warp may consume it
         int n_it = p.kiters;
         if (p.ksplit > 1) {
-          const int split = unit % p.ksplit;
-          n_it = (split + 1) * p.kiters / p.ksplit - split * p.kiters / p.ksplit;
+          int a0, a1;
+          split_range(p, split, a0, a1);
+          n_it = a1 - a0;
         }
         for (int it = 0; it < n_it; ++it) {
           ptx::mbar_wait(ptx::smem_u32(full_bar + xs), xphase);
           float4* hi = reinterpret_cast<float4*>(smem + (size_t)xs * Tr::kStageStride);
           float4* lo = reinterpret_cast<float4*>(smem + (size_t)xs * Tr::kStageStride + STAGE_BYTES);
-          for (int i = et; i < STAGE_BYTES / 16; i += 128) {
+          for (int i = et; i < STAGE_BYTES / 16; i += kEpiThreads) {
             const float4 v = hi[i];
             float4 h4, l4;
             h4.x = __uint_as_float(__float_as_uint(v.x) & 0xffffe000u); l4.x = v.x - h4.x;
@@ -305,36 +403,44 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
       if (p.ksplit > 1) {
         // split-K: park the fp32 partial tile (main + h columns) in the L2-resident workspace,
-        // [unit][chunk][row][32]; splitk_finalize_kernel reduces over the splits in a fixed order.
-        ptx::mbar_wait(ptx::smem_u32(tfull_bar + as), aphase);
+        // [unit][chunk][row][PCW]; splitk_finalize_kernel reduces over the splits in a fixed order.
+        // one warp polls the accumulator-ready mbarrier, the others sleep on the hardware barrier: eight warps
+        // spinning on try_wait steal shared-memory cycles from the operand pipeline for the whole main loop
+        if (et < 32) ptx::mbar_wait(ptx::smem_u32(tfull_bar + as), aphase);
+        asm volatile("bar.sync 2, 256;" ::: "memory");
         ptx::tc_fence_after();
         if (et == 0 && unit == (int)blockIdx.x) SLIDER_TRACE(5);
         const uint32_t t_acc = tmem_base + ((uint32_t)(q * 32) << 16) + as * (BN + HCOLS);
-        const int nch = (R4 > 0) ? NCHUNK : NCHUNK - 1;
+        const int nmine = PCPG + ((grp == 0 && R4 > 0) ? 1 : 0);   // group 0 also parks the h columns
 #pragma unroll 1
-        for (int c = 0; c < nch; ++c) {
-          uint32_t v[32];
-          if (c < BN / 32) {
-            ptx::tmem_ld_32x32(t_acc + c * 32, v);
+        for (int ci = 0; ci < nmine; ++ci) {
+          uint32_t v[PCW];
+          int chunk;
+          if (ci < PCPG) {
+            chunk = grp * PCPG + ci;
+            TmemChunk<PCW>::ld(t_acc + chunk * PCW, v);
           } else {
+            chunk = NCHUNK - 1;
             uint32_t hr[16];
             ptx::tmem_ld_32x16(t_acc + BN, hr);
+            ptx::tmem_ld_wait();
 #pragma unroll
-            for (int k = 0; k < 16; ++k) { v[k] = hr[k]; v[16 + k] = 0u; }
+            for (int k = 0; k < 16; ++k) v[k] = hr[k];
+#pragma unroll
+            for (int k = 16; k < PCW; ++k) v[k] = 0u;
           }
-          ptx::tmem_ld_wait();
-          const uint32_t dst = out_base + ob * OUT_BYTES + row * 128;
+          const uint32_t dst = out_base + ob * OUT_BYTES + row * OUT_ROW_BYTES;
 #pragma unroll
-          for (int k = 0; k < 8; ++k)
-            ptx::st_shared_v4(dst + ((k ^ (row & 7)) << 4), v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+          for (int k = 0; k < OUT_ROW_BYTES / 16; ++k)
+            ptx::st_shared_v4(dst + k * 16, v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
           ptx::fence_proxy_async_smem();
-          if (et == 0) ptx::bulk_wait_read<1>();     // buffer of the NEXT chunk (store c-2) is free past the barrier
-          asm volatile("bar.sync 1, 128;" ::: "memory");
-          if (et == 0) {
-            ptx::tma_store_2d(&tmP, out_base + ob * OUT_BYTES, 0, (unit * NCHUNK + c) * BM);
+          if (gt == 0) ptx::bulk_wait_read<NB - 2>();   // buffer of chunk c+1 (last read by store c+1-NB) is free past the barrier
+          SLIDER_GROUP_BAR();
+          if (gt == 0) {
+            ptx::tma_store_2d(&tmP, out_base + ob * OUT_BYTES, 0, (unit * NCHUNK + chunk) * BM);
             ptx::bulk_commit();
           }
-          if (++ob == OUT_BUFS) ob = 0;
+          if (++ob == (uint32_t)NB) ob = 0;
         }
         ptx::tc_fence_before();
         __syncwarp();
@@ -345,8 +451,8 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
       const TileCoord tc = tile_coord(p, unit);
       // stage s*Bup[n0.., :] and bias[n0..] for this tile (fp32) while the MMAs run
-      asm volatile("bar.sync 2, 128;" ::: "memory");
-      for (int i = et; i < BN; i += 128) {
+      asm volatile("bar.sync 2, 256;" ::: "memory");
+      for (int i = et; i < BN; i += kEpiThreads) {
         const int n = tc.n0 + i;
         s_bias[i] = (bias != nullptr && n < p.N) ? Elem<T>::to_f(bias[n]) : 0.f;
         if (R4 > 0) {
@@ -356,9 +462,11 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 (n < p.N && j < p.rank) ? p.s * Elem<T>::to_f(Bup[(size_t)n * p.rank + j]) : 0.f;
         }
       }
-      asm volatile("bar.sync 2, 128;" ::: "memory");
-
-      ptx::mbar_wait(ptx::smem_u32(tfull_bar + as), aphase);
+      // one warp polls the accumulator-ready mbarrier, the others sleep on the hardware barrier (which also
+      // publishes the tables staged above): eight warps spinning on try_wait steal shared-memory cycles from the
+      // operand pipeline for the whole main loop
+      if (et < 32) ptx::mbar_wait(ptx::smem_u32(tfull_bar + as), aphase);
+      asm volatile("bar.sync 2, 256;" ::: "memory");
       ptx::tc_fence_after();
       if (et == 0 && unit == (int)blockIdx.x) SLIDER_TRACE(5);
       const uint32_t t_main = tmem_base + ((uint32_t)(q * 32) << 16) + as * (BN + HCOLS);
@@ -372,7 +480,7 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         ptx::tmem_ld_wait();
 #pragma unroll
         for (int j = 0; j < 4 * R4; ++j) hv[j] = __uint_as_float(hr[j]);
-        if (p.h_out != nullptr && tc.n_blk == 0) {
+        if (p.h_out != nullptr && tc.n_blk == 0 && grp == 1) {
           const int lw = row % p.TW, lh = (row / p.TW) % p.TH, lb = row / (p.TW * p.TH);
           const bool row_ok = row < p.rows && tc.w0 + lw < p.W && tc.h0 + lh < p.H && tc.b0 + lb < p.B;
           const size_t pix = ((size_t)(tc.b0 + lb) * p.H + (tc.h0 + lh)) * p.W + (tc.w0 + lw);
@@ -383,21 +491,21 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           }
         }
       }
-      const int n_chunks = min(BN / 32, (p.N - tc.n0 + 31) / 32);
 #pragma unroll 1
-      for (int c = 0; c < n_chunks; ++c) {
-        uint32_t v[32];
-        ptx::tmem_ld_32x32(t_main + c * 32, v);
-        ptx::tmem_ld_wait();
-        const uint32_t dst = out_base + ob * OUT_BYTES + row * (32 * (int)sizeof(T));
+      for (int ci = 0; ci < CPG; ++ci) {
+        const int col0 = grp * HALF_N + ci * CW;
+        if (tc.n0 + col0 >= p.N) break;              // ragged last column tile (uniform over the group)
+        uint32_t v[CW];
+        TmemChunk<CW>::ld(t_main + col0, v);
+        const uint32_t dst = out_base + ob * OUT_BYTES + row * OUT_ROW_BYTES;
 #pragma unroll
-        for (int g8 = 0; g8 < 4; ++g8) {
-          float o[8];
+        for (int pc = 0; pc < OUT_ROW_BYTES / 16; ++pc) {
+          float o[PW];
 #pragma unroll
-          for (int k = 0; k < 8; ++k) {
-            const int i = c * 32 + g8 * 8 + k;
+          for (int k = 0; k < PW; ++k) {
+            const int i = col0 + pc * PW + k;
             // explicit ld.shared: the generic pointers derived from the re-aligned base compile to LD.E
-            float a = __uint_as_float(v[g8 * 8 + k]) + ptx::ld_shared_f32(bias_s + i * 4);
+            float a = __uint_as_float(v[pc * PW + k]) + ptx::ld_shared_f32(bias_s + i * 4);
             if (R4 > 0) {
 #pragma unroll
               for (int j4 = 0; j4 < R4; ++j4) {
@@ -410,30 +518,28 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             }
             o[k] = a;
           }
-          if (sizeof(T) == 2) {      // 64-byte rows, SWIZZLE_64B: 16-byte chunk ^= (row >> 1) & 3
+          if (sizeof(T) == 2) {
             uint32_t w[4];
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-              __nv_bfloat162 h2 = __floats2bfloat162_rn(o[2 * k], o[2 * k + 1]);
+              __nv_bfloat162 h2 = __floats2bfloat162_rn(o[(2 * k) % PW], o[(2 * k + 1) % PW]);
               w[k] = *reinterpret_cast<uint32_t*>(&h2);
             }
-            ptx::st_shared_v4(dst + ((g8 ^ ((row >> 1) & 3)) << 4), w[0], w[1], w[2], w[3]);
-          } else {                   // 128-byte rows, SWIZZLE_128B: 16-byte chunk ^= row & 7
-            ptx::st_shared_v4(dst + (((2 * g8) ^ (row & 7)) << 4), __float_as_uint(o[0]), __float_as_uint(o[1]),
-                              __float_as_uint(o[2]), __float_as_uint(o[3]));
-            ptx::st_shared_v4(dst + (((2 * g8 + 1) ^ (row & 7)) << 4), __float_as_uint(o[4]), __float_as_uint(o[5]),
-                              __float_as_uint(o[6]), __float_as_uint(o[7]));
+            ptx::st_shared_v4(dst + pc * 16, w[0], w[1], w[2], w[3]);
+          } else {
+            ptx::st_shared_v4(dst + pc * 16, __float_as_uint(o[0]), __float_as_uint(o[1]), __float_as_uint(o[2 % PW]),
+                              __float_as_uint(o[3 % PW]));
           }
         }
         ptx::fence_proxy_async_smem();
-        if (et == 0) ptx::bulk_wait_read<1>();       // buffer of the NEXT chunk (store c-2) is free past the barrier
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-        if (et == 0) {
-          if (p.accumulate) ptx::tma_reduce_add_4d(&tmY, out_base + ob * OUT_BYTES, tc.n0 + c * 32, tc.w0, tc.h0, tc.b0);
-          else ptx::tma_store_4d(&tmY, out_base + ob * OUT_BYTES, tc.n0 + c * 32, tc.w0, tc.h0, tc.b0);
+        if (gt == 0) ptx::bulk_wait_read<NB - 2>();     // buffer of chunk c+1 (last read by store c+1-NB) is free past the barrier
+        SLIDER_GROUP_BAR();
+        if (gt == 0) {
+          if (p.accumulate) ptx::tma_reduce_add_4d(&tmY, out_base + ob * OUT_BYTES, tc.n0 + col0, tc.w0, tc.h0, tc.b0);
+          else ptx::tma_store_4d(&tmY, out_base + ob * OUT_BYTES, tc.n0 + col0, tc.w0, tc.h0, tc.b0);
           ptx::bulk_commit();
         }
-        if (++ob == OUT_BUFS) ob = 0;
+        if (++ob == (uint32_t)NB) ob = 0;
       }
       ptx::tc_fence_before();
       __syncwarp();
@@ -441,7 +547,8 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(tempty_bar + as));
       if (++as == ACC_STAGES) { as = 0; aphase ^= 1; }
     }
-    if (et == 0) ptx::bulk_wait_all();    // all TMA stores of this CTA have landed before it exits
+    if (gt == 0) ptx::bulk_wait_all();    // all TMA stores of this group have landed before the CTA exits
+#undef SLIDER_GROUP_BAR
   }
 
   ptx::tc_fence_before();
@@ -456,82 +563,109 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
 
 // ---------------------------------------------------------------------------------------------
-// Split-K finalize: y = sum_splits(partial) + bias + s * h . Bup^T, one thread per (row, 8 columns).
-// Thread order (8-col group, row, chunk) follows the partial layout, so reads are fully coalesced.
+// Split-K finalize: y = sum_splits(partial) + bias + s * h . Bup^T.  One thread per (row, 4-column piece, chunk c)
+// also owns the same piece of chunk c + 4, so the row's h partials are read once per 8 output columns.
+// Thread order (piece, row, chunk) follows the partial layout, so reads are fully coalesced.
 template <typename T, int R4>
 __global__ void __launch_bounds__(256)
 splitk_finalize_kernel(const GemmParams p) {
   pdl_trigger();
   pdl_wait();
-  constexpr int PER_TILE = BM * (BN / 8);
+  constexpr int PIECES = PCW / 4;                  // 16-byte pieces per partial row
+  constexpr int HC = (NCHUNK - 1) / 2;             // chunk pairs (c, c + HC)
+  constexpr int PER_TILE = BM * PIECES * HC;
   const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
   if (idx >= (long long)p.total_tiles * PER_TILE) return;
   const int tile = (int)(idx / PER_TILE);
   const int rem = (int)(idx - (long long)tile * PER_TILE);
-  const int g = rem & 3, row = (rem >> 2) & (BM - 1), c = rem >> 9;
+  const int pc = rem % PIECES, row = (rem / PIECES) & (BM - 1), c = rem / (PIECES * BM);
   const TileCoord tc = tile_coord(p, tile);
   const int lw = row % p.TW, lh = (row / p.TW) % p.TH, lb = row / (p.TW * p.TH);
   const bool row_ok = row < p.rows && tc.w0 + lw < p.W && tc.h0 + lh < p.H && tc.b0 + lb < p.B;
-  const int n = tc.n0 + c * 32 + g * 8;
-  if (!row_ok || n >= p.N) return;
+  const int n0 = tc.n0 + c * PCW + pc * 4, n1 = n0 + HC * PCW;
+  if (!row_ok || n0 >= p.N) return;
+  const bool second = n1 < p.N;
   const size_t pix = ((size_t)(tc.b0 + lb) * p.H + (tc.h0 + lh)) * p.W + (tc.w0 + lw);
-  const float* src = p.partial + (size_t)tile * p.ksplit * UNIT_FLOATS + ((size_t)c * BM + row) * 32 + g * 8;
-  const float* hsrc = p.partial + (size_t)tile * p.ksplit * UNIT_FLOATS + ((size_t)(BN / 32) * BM + row) * 32 +
-                      (p.group_n > 0 ? (tc.n0 / p.group_n) * p.rank : 0);
+  const float* src = p.partial + (size_t)tile * p.ksplit * UNIT_FLOATS + ((size_t)c * BM + row) * PCW + pc * 4;
+  const int hoff = p.group_n > 0 ? (tc.n0 / p.group_n) * p.rank : 0;
+  const float* hsrc = p.partial + (size_t)tile * p.ksplit * UNIT_FLOATS + ((size_t)(NCHUNK - 1) * BM + row) * PCW + hoff;
   float o[8];
   float hv[R4 > 0 ? 4 * R4 : 1];
 #pragma unroll
   for (int k = 0; k < 8; ++k) o[k] = 0.f;
 #pragma unroll
   for (int j = 0; j < (R4 > 0 ? 4 * R4 : 1); ++j) hv[j] = 0.f;
-#pragma unroll 4
-  for (int s = 0; s < p.ksplit; ++s) {
-    const float4 a = __ldcg(reinterpret_cast<const float4*>(src + (size_t)s * UNIT_FLOATS));
-    const float4 b = __ldcg(reinterpret_cast<const float4*>(src + (size_t)s * UNIT_FLOATS) + 1);
-    o[0] += a.x; o[1] += a.y; o[2] += a.z; o[3] += a.w;
-    o[4] += b.x; o[5] += b.y; o[6] += b.z; o[7] += b.w;
-    if (R4 > 0) {
+  // branch-free loop bodies (the second chunk of a ragged tile re-reads the first and is discarded), so that the
+  // unrolled loads of several splits are in flight together: the kernel is pure L2 latency otherwise
+  const float* srcb = second ? src + (size_t)HC * BM * PCW : src;
+  if (R4 == 0 || (hoff & 3) == 0) {
+#pragma unroll 6
+    for (int s = 0; s < p.ksplit; ++s) {
+      const float4 a = __ldcg(reinterpret_cast<const float4*>(src + (size_t)s * UNIT_FLOATS));
+      const float4 b = __ldcg(reinterpret_cast<const float4*>(srcb + (size_t)s * UNIT_FLOATS));
+      o[0] += a.x; o[1] += a.y; o[2] += a.z; o[3] += a.w;
+      o[4] += b.x; o[5] += b.y; o[6] += b.z; o[7] += b.w;
+      if (R4 > 0) {
 #pragma unroll
-      for (int j4 = 0; j4 < R4; ++j4) {
-        const float4 h4 = __ldcg(reinterpret_cast<const float4*>(hsrc + (size_t)s * UNIT_FLOATS) + j4);
-        hv[4 * j4] += h4.x; hv[4 * j4 + 1] += h4.y; hv[4 * j4 + 2] += h4.z; hv[4 * j4 + 3] += h4.w;
+        for (int j4 = 0; j4 < R4; ++j4) {
+          const float4 h4 = __ldcg(reinterpret_cast<const float4*>(hsrc + (size_t)s * UNIT_FLOATS) + j4);
+          hv[4 * j4] += h4.x; hv[4 * j4 + 1] += h4.y; hv[4 * j4 + 2] += h4.z; hv[4 * j4 + 3] += h4.w;
+        }
       }
+    }
+  } else {    // grouped adapters whose h offset is not a multiple of four columns: scalar h loads
+#pragma unroll 2
+    for (int s = 0; s < p.ksplit; ++s) {
+      const float4 a = __ldcg(reinterpret_cast<const float4*>(src + (size_t)s * UNIT_FLOATS));
+      const float4 b = __ldcg(reinterpret_cast<const float4*>(srcb + (size_t)s * UNIT_FLOATS));
+      o[0] += a.x; o[1] += a.y; o[2] += a.z; o[3] += a.w;
+      o[4] += b.x; o[5] += b.y; o[6] += b.z; o[7] += b.w;
+#pragma unroll
+      for (int j = 0; j < (R4 > 0 ? 4 * R4 : 1); ++j)
+        if (R4 > 0 && hoff + j < HCOLS) hv[j] += __ldcg(hsrc + (size_t)s * UNIT_FLOATS + j);
     }
   }
   const T* __restrict__ bias = reinterpret_cast<const T*>(p.bias);
   const T* __restrict__ Bup = reinterpret_cast<const T*>(p.Bup);
 #pragma unroll
-  for (int k = 0; k < 8; ++k) {
-    float a = o[k] + (bias != nullptr ? Elem<T>::to_f(bias[n + k]) : 0.f);
-    if (R4 > 0) {
-      float l = 0.f;
+  for (int half = 0; half < 2; ++half) {
+    if (half == 1 && !second) break;
+    const int n = half == 0 ? n0 : n1;
+    float r[4];
 #pragma unroll
-      for (int j = 0; j < 4 * R4; ++j)
-        if (j < p.rank) l = fmaf(hv[j], Elem<T>::to_f(Bup[(size_t)(n + k) * p.rank + j]), l);
-      a = fmaf(p.s, l, a);
+    for (int k = 0; k < 4; ++k) {
+      float a = o[half * 4 + k] + (bias != nullptr ? Elem<T>::to_f(bias[n + k]) : 0.f);
+      if (R4 > 0) {
+        float l = 0.f;
+#pragma unroll
+        for (int j = 0; j < 4 * R4; ++j)
+          if (j < p.rank) l = fmaf(hv[j], Elem<T>::to_f(Bup[(size_t)(n + k) * p.rank + j]), l);
+        a = fmaf(p.s, l, a);
+      }
+      r[k] = a;
     }
-    o[k] = a;
-  }
-  T* dst = reinterpret_cast<T*>(p.y) + pix * (size_t)p.N + n;
-  if (p.accumulate) {      // y holds the residual: same two roundings as `residual + module(x)` in element dtype
-    float res[8];
+    T* dst = reinterpret_cast<T*>(p.y) + pix * (size_t)p.N + n;
     if (sizeof(T) == 2) {
-      Elem<__nv_bfloat16>::load(reinterpret_cast<const __nv_bfloat16*>(dst), res);
-    } else {
-      const float4 r0 = *reinterpret_cast<const float4*>(dst), r1 = *(reinterpret_cast<const float4*>(dst) + 1);
-      res[0] = r0.x; res[1] = r0.y; res[2] = r0.z; res[3] = r0.w; res[4] = r1.x; res[5] = r1.y; res[6] = r1.z; res[7] = r1.w;
-    }
+      uint2* d2 = reinterpret_cast<uint2*>(dst);
+      if (p.accumulate) {  // y holds the residual: same two roundings as `residual + module(x)` in element dtype
+        const uint2 q = *d2;
+        const float res[4] = {__uint_as_float(q.x << 16), __uint_as_float(q.x & 0xffff0000u),
+                              __uint_as_float(q.y << 16), __uint_as_float(q.y & 0xffff0000u)};
 #pragma unroll
-    for (int k = 0; k < 8; ++k) o[k] = Elem<T>::to_f(Elem<T>::from_f(o[k])) + res[k];
+        for (int k = 0; k < 4; ++k) r[k] = __bfloat162float(__float2bfloat16_rn(r[k])) + res[k];
+      }
+      __nv_bfloat162 lo2 = __floats2bfloat162_rn(r[0], r[1]), hi2 = __floats2bfloat162_rn(r[2], r[3]);
+      *d2 = make_uint2(*reinterpret_cast<uint32_t*>(&lo2), *reinterpret_cast<uint32_t*>(&hi2));
+    } else {
+      float4* d4 = reinterpret_cast<float4*>(dst);
+      if (p.accumulate) {
+        const float4 q = *d4;
+        r[0] += q.x; r[1] += q.y; r[2] += q.z; r[3] += q.w;
+      }
+      *d4 = make_float4(r[0], r[1], r[2], r[3]);
+    }
   }
-  if (sizeof(T) == 2) {
-    Elem<__nv_bfloat16>::store(reinterpret_cast<__nv_bfloat16*>(dst), o);
-  } else {
-    float* d = reinterpret_cast<float*>(dst);
-    *reinterpret_cast<float4*>(d) = make_float4(o[0], o[1], o[2], o[3]);
-    *reinterpret_cast<float4*>(d + 4) = make_float4(o[4], o[5], o[6], o[7]);
-  }
-  if (R4 > 0 && p.h_out != nullptr && tc.n_blk == 0 && c == 0 && g == 0) {
+  if (R4 > 0 && p.h_out != nullptr && tc.n_blk == 0 && c == 0 && pc == 0) {
 #pragma unroll
     for (int j = 0; j < 4 * R4; ++j)
       if (j < p.rank) p.h_out[pix * p.rank + j] = hv[j];
@@ -704,11 +838,11 @@ static int launch_gemm(int r4, const CUtensorMap& a, const CUtensorMap& w, const
   bool done = false;
   for (auto c : configured) done |= (c == (const void*)kern);
   if (!done) {
-    SLIDER_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
+    SLIDER_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gemm_smem_bytes(r4)));
     for (auto& c : configured) if (c == nullptr) { c = (const void*)kern; break; }
   }
   int grid = p.total_units < sm_count() ? p.total_units : sm_count();
-  launch_pdl(kern, dim3(grid), dim3(kGemmThreads), SMEM_BYTES, st, a, w, l, xe, we, my, mp, p);
+  launch_pdl(kern, dim3(grid), dim3(kGemmThreads), gemm_smem_bytes(r4), st, a, w, l, xe, we, my, mp, p);
   int rc = post_launch("lora_gemm_kernel");
   if (rc || p.ksplit == 1) return rc;
   const long long threads = (long long)p.total_tiles * BM * (BN / 8);
@@ -805,6 +939,12 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
     if (ks >= 2) p.ksplit = ks;
   }
   p.total_units = p.total_tiles * p.ksplit;
+  p.fd_n_tiles = FastDiv::make((uint32_t)p.n_tiles);
+  p.fd_mt_w = FastDiv::make((uint32_t)p.mt_w);
+  p.fd_mt_h = FastDiv::make((uint32_t)p.mt_h);
+  p.fd_ksplit = FastDiv::make((uint32_t)p.ksplit);
+  p.fd_per_tap = FastDiv::make((uint32_t)p.per_tap);
+  p.fd_kw = FastDiv::make((uint32_t)p.kw);
   p.trace = g_gemm_trace;
   p.y = y; p.bias = bias; p.Bup = Bup; p.h_out = lora ? h_out : nullptr;
   if (lora) {
@@ -848,15 +988,15 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
   {
     uint64_t dims[4] = {(uint64_t)nn, (uint64_t)g->width, (uint64_t)g->height, (uint64_t)g->batch};
     uint64_t str[3] = {(uint64_t)nn * es, (uint64_t)nn * es * g->width, (uint64_t)nn * es * g->width * g->height};
-    uint32_t box[4] = {32u, (uint32_t)tg.TW, (uint32_t)tg.TH, (uint32_t)tg.TB};
-    if ((rc = make_tmap(&mY, g->dtype, 4, y, dims, str, box, 32 * es))) return rc;
+    uint32_t box[4] = {(uint32_t)(OUT_ROW_BYTES / es), (uint32_t)tg.TW, (uint32_t)tg.TH, (uint32_t)tg.TB};
+    if ((rc = make_tmap(&mY, g->dtype, 4, y, dims, str, box, OUT_ROW_BYTES))) return rc;
   }
   mP = mY;
   if (p.ksplit > 1) {
-    uint64_t dims[2] = {32u, (uint64_t)p.total_units * NCHUNK * BM};
-    uint64_t str[1] = {128u};
-    uint32_t box[2] = {32u, (uint32_t)BM};
-    if ((rc = make_tmap(&mP, SLIDER_F32, 2, ws, dims, str, box, 128))) return rc;
+    uint64_t dims[2] = {(uint64_t)PCW, (uint64_t)p.total_units * NCHUNK * BM};
+    uint64_t str[1] = {(uint64_t)OUT_ROW_BYTES};
+    uint32_t box[2] = {(uint32_t)PCW, (uint32_t)BM};
+    if ((rc = make_tmap(&mP, SLIDER_F32, 2, ws, dims, str, box, OUT_ROW_BYTES))) return rc;
   }
   const int r4 = !lora ? 0 : (g->rank <= 4 ? 1 : (g->rank <= 8 ? 2 : 4));
   if (g->dtype == SLIDER_BF16) return launch_gemm<__nv_bfloat16>(r4, mA, mW, mL, mXe, mWe, mY, mP, p, st);

@@ -7,7 +7,10 @@ from sliders_conceptmod_b200 import ops, _lib
 
 shapes = [tuple(int(v) for v in a.split(",")) for a in sys.argv[1:] if "," in a] or [(1, 1, 8192, 320, 320, 1)]
 dt, r, s = torch.bfloat16, 4, 0.25
-names = ["setup", "first_tma_issue", "first_full", "last_mma_commit", "acc_visible", "epi_done", "exit"]
+if "--nosplit" in sys.argv:
+    _lib.lib().slider_debug_splitk_depth(1000000)
+names = ["setup", "first_tma_issue", "first_full", "last_mma_commit", "acc_visible", "epi_done", "exit",
+         "prod_ready", "after_tma_A", "after_tma_W"]
 for (B, H, W, C, N, k) in shapes:
     x = torch.randn(B, H, W, C, device="cuda", dtype=dt)
     w = (torch.randn(N, k * k, C, device="cuda") / (C * k * k) ** 0.5).to(dt)
@@ -17,14 +20,14 @@ for (B, H, W, C, N, k) in shapes:
     xin = x.reshape(W, C) if (k == 1 and B == 1 and H == 1) else x
     for _ in range(3):
         ops.lora_forward(xin, w, bias, a, b, s, ksize=k)
-    trace = torch.zeros(148 * 8, dtype=torch.int64, device="cuda")
+    trace = torch.zeros(148 * 16, dtype=torch.int64, device="cuda")
     _lib.lib().slider_debug_gemm_trace(trace.data_ptr())
     ops.lora_forward(xin, w, bias, a, b, s, ksize=k)
     torch.cuda.synchronize()
     _lib.lib().slider_debug_gemm_trace(None)
-    t = trace.view(148, 8).cpu()
+    t = trace.view(148, 16).cpu()
     t = t[t[:, 0] > 0]
-    d = (t[:, 1:] - t[:, :1]).double()
+    d = (t[:, 1:11] - t[:, :1]).double()
     print(f"shape {(B, H, W, C, N, k)} ctas {t.shape[0]}: cycles since CTA entry (median / max over CTAs)")
     for i, n in enumerate(names):
         col = d[:, i]
