@@ -116,14 +116,30 @@ def fused_gemm_roofline(engine, pk: dict, reps: int = 5) -> dict:
         calls.append(("grouped", tuple(x.shape), tuple(w_cat.shape), False, a_cat.shape[0], s, groups, x.dtype, False))
         return real_grouped(x, w_cat, a_cat, b_cat, groups, s)
 
-    ops.lora_forward, ops.lora_forward_grouped = spy, spy_grouped
+    real_multi = ops.lora_forward_small_multi
+
+    def spy_multi(x, plan, scales):
+        calls.append(("multi", tuple(x.shape), plan, True, plan.rank, tuple(scales), 1, x.dtype, False))
+        return real_multi(x, plan, scales)
+
+    ops.lora_forward, ops.lora_forward_grouped, ops.lora_forward_small_multi = spy, spy_grouped, spy_multi
     try:
         engine._body_denoise()
     finally:
-        ops.lora_forward, ops.lora_forward_grouped = real, real_grouped
+        ops.lora_forward, ops.lora_forward_grouped, ops.lora_forward_small_multi = real, real_grouped, real_multi
     torch.cuda.synchronize()
     flops, alg_bytes, args = 0.0, 0.0, []
     for (kind, xs, ws, has_b, r, s, k, dt, has_res) in calls:
+        if kind == "multi":         # every time_emb_proj of the forward in one weight-streaming launch
+            plan = ws
+            es = 2 if dt == torch.bfloat16 else 4
+            M, K = xs
+            for n in plan.n:
+                flops += 2.0 * M * n * K + 2.0 * M * r * (K + n)
+                alg_bytes += es * (float(n) * K + M * n)
+            alg_bytes += es * float(M) * K
+            args.append(("multi", torch.randn(xs, device="cuda", dtype=dt), plan, s))
+            continue
         es = 2 if dt == torch.bfloat16 else 4
         alg_bytes += es * (float(torch.Size(xs).numel()) + float(torch.Size(ws).numel()) +
                            float(torch.Size(xs[:-1]).numel()) * ws[0] * (2 if has_res else 1))
@@ -151,6 +167,8 @@ def fused_gemm_roofline(engine, pk: dict, reps: int = 5) -> dict:
         for c in args:
             if c[0] == "grouped":
                 real_grouped(*c[1:])
+            elif c[0] == "multi":
+                real_multi(c[1], c[2], c[3])
             else:
                 real(c[1], c[2], c[3], c[4], c[5], c[6], ksize=c[7], residual=c[8])
     # capture the launch sequence in a CUDA graph so host-side descriptor encoding is not in the timing

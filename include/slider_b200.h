@@ -115,6 +115,20 @@ int slider_lora_forward_grouped(const slider_layer_geom* g, void* y, const void*
                                 size_t ws_bytes, void* stream);
 
 /*
+ * Several SMALL-M Linear adapters on ONE input in one launch: the `time_emb_proj` of every ResnetBlock2D projects the
+ * same silu(temb) rows (M = 2b <= 16; each one a LoRAModule.forward, conceptmod/textsliders/lora.py:94-98,134-138,
+ * reached from the UNet call at train_util.py:290-294).  Host arrays of `layers` (<= 32) device pointers:
+ *   x [M, K]   W[l] [N[l], K]   bias[l] [N[l]] or NULL   A[l] [rank, K] or NULL   B[l] [N[l], rank]   y[l] [M, N[l]]
+ *   y[l] = x . W[l]^T + bias[l] + s[l] * (x . A[l]^T) . B[l]^T        (s[l] == 0 or A[l] == NULL: plain projection)
+ * `bias`, `A`, `B` may be NULL as a whole.  Weight-streaming (HBM-bound) kernel, no tensor cores; no h_out:
+ * inference / no-grad forwards only (the grad forward uses slider_lora_forward per adapter).
+ */
+int slider_lora_forward_small_multi(int dtype, int layers, int M, int K, int rank, const void* x,
+                                    void* const* y, const void* const* W, const void* const* bias,
+                                    const void* const* A, const void* const* B, const int* N,
+                                    const float* s, void* stream);
+
+/*
  * Low-rank part of the backward of the layer above (autograd of lora.py:134-138,
  * triggered by loss.backward() at conceptmod/textsliders/train_lora.py:298):
  *     dh = s * gy . B          [M, rank]  -> dh_out (element dtype, padded to 16)

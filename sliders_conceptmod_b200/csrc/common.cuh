@@ -50,8 +50,7 @@ int sm_count();
 // Every forward-path kernel starts with pdl_trigger() + pdl_wait(): the next kernel in the stream may be made
 // resident while this one still runs (its launch latency and prologue overlap our tail), and nothing of ours
 // touches global memory before the previous kernel has completed and flushed.  Both are no-ops for a launch
-// without the attribute, which is only set when SLIDER_PDL=1 is in the environment (opt-in: the A/B on B200 showed
-// no gain, profiles/r01_ab_pdl.txt).
+// without the attribute, which is set unless SLIDER_PDL=0 is in the environment (A/B: profiles/r01_ab_pdl_v2.txt).
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 bool pdl_enabled();

@@ -16,6 +16,7 @@
 //
 // The same kernel computes the input gradient ("extended-K" mode): activations = gy,
 // weights = Wt, and one extra 16-wide K block per tap whose operands are dh and At.
+#include <stdlib.h>
 #include "common.cuh"
 #include "ptx.cuh"
 #include "tmap.cuh"
@@ -50,6 +51,8 @@ __host__ __device__ constexpr size_t gemm_smem_bytes(int r4) {
 constexpr int PCW = OUT_ROW_BYTES / 4;       // fp32 columns per split-K partial chunk
 constexpr int NCHUNK = BN / PCW + 1;         // partial chunks of a split-K unit (+1 for h)
 constexpr size_t UNIT_FLOATS = (size_t)NCHUNK * BM * PCW;
+constexpr int CPITCH = (BN + HCOLS + 4) * 4;  // bytes per row of a cluster split-K partial tile: 180 words, conflict-free
+constexpr int MAX_CLUSTER = 8;               // portable cluster size = largest in-cluster K split
 constexpr int MAX_UNITS = 160;               // split-K work units the caller workspace must hold
 
 // Division by a launch-constant through a host-computed multiplier (n < 2^31): the producer's tile -> coordinate
@@ -110,6 +113,7 @@ struct GemmParams {
   int per_tap;            // K iterations per tap = cblocks + ext
   int kiters;             // taps * per_tap
   int ksplit;             // K partitions per tile (1 = no split)
+  int cluster;            // split-K partials are reduced inside a thread-block cluster of ksplit CTAs (DSMEM)
   int total_units;        // total_tiles * ksplit
   float* partial;         // split-K partial tiles, [unit][NCHUNK][128][32] fp32
   int accumulate;         // y += result (y holds the residual branch) instead of y = result
@@ -189,7 +193,8 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint64_t* tfull_bar = bars + 2 * NSTAGES;       // [ACC_STAGES] MMA -> epilogue
   uint64_t* tempty_bar = tfull_bar + ACC_STAGES;  // [ACC_STAGES] epilogue -> MMA
   uint64_t* xf_bar = tempty_bar + ACC_STAGES;     // [NSTAGES] hi/lo split done (fp32 only) -> MMA
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(xf_bar + NSTAGES);
+  uint64_t* recv_bar = xf_bar + NSTAGES;          // cluster split-K: bytes pushed by the peer CTAs have landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(recv_bar + 1);
 
   // warp index through a shuffle so that the role branches below are provably warp-uniform
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
@@ -247,7 +252,7 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     ptx::prefetch_tmap(&tmW);
     if (p.lora) ptx::prefetch_tmap(&tmL);
     if (p.ext) { ptx::prefetch_tmap(&tmXe); ptx::prefetch_tmap(&tmWe); }
-    if (p.ksplit > 1) ptx::prefetch_tmap(&tmP); else ptx::prefetch_tmap(&tmY);
+    if (p.ksplit > 1 && !p.cluster) ptx::prefetch_tmap(&tmP); else if (!p.cluster) ptx::prefetch_tmap(&tmY);
     for (int i = 0; i < NSTAGES; ++i) {
       ptx::mbar_init(ptx::smem_u32(full_bar + i), 1);
       ptx::mbar_init(ptx::smem_u32(empty_bar + i), 1);
@@ -257,6 +262,7 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       ptx::mbar_init(ptx::smem_u32(tfull_bar + i), 1);
       ptx::mbar_init(ptx::smem_u32(tempty_bar + i), 8);  // one arrive per epilogue warp
     }
+    ptx::mbar_init(ptx::smem_u32(recv_bar), 1);
     ptx::fence_mbar_init();
   }
   if (warp == 1) {
@@ -400,6 +406,152 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(xf_bar + xs));
           if (++xs == (uint32_t)Tr::kStages) { xs = 0; xphase ^= 1; }
         }
+      }
+      if (p.cluster) {
+        // ---- split-K inside a thread-block cluster (one unit per CTA, cluster rank == split) ----
+        // Every CTA parks its fp32 partial tile (main + h columns) in its own shared memory (the operand stages are
+        // idle once the accumulator is complete), the cluster synchronises, and CTA r reduces rows
+        // [r*R, (r+1)*R) of all partials over distributed shared memory in split order (deterministic), applies the
+        // epilogue and writes y directly: no workspace round trip, no second launch.
+        const TileCoord tc = tile_coord(p, (int)tile);
+        for (int i = et; i < BN; i += kEpiThreads) {
+          const int n = tc.n0 + i;
+          s_bias[i] = (bias != nullptr && n < p.N) ? Elem<T>::to_f(bias[n]) : 0.f;
+          if (R4 > 0) {
+#pragma unroll
+            for (int j = 0; j < 4 * R4; ++j)
+              s_epi[i * (4 * R4) + j] =
+                  (n < p.N && j < p.rank) ? p.s * Elem<T>::to_f(Bup[(size_t)n * p.rank + j]) : 0.f;
+          }
+        }
+        if (et < 32) ptx::mbar_wait(ptx::smem_u32(tfull_bar + as), aphase);
+        asm volatile("bar.sync 2, 256;" ::: "memory");
+        ptx::tc_fence_after();
+        if (et == 0) SLIDER_TRACE(5);
+        const uint32_t t_acc = tmem_base + ((uint32_t)(q * 32) << 16) + as * (BN + HCOLS);
+        const int S = p.ksplit;
+        const int R = (BM + S - 1) / S;                                // rows reduced by one CTA
+        const int r0 = (int)split * R;
+        const int nrows = max(0, min(R, BM - r0));
+        const uint32_t part = smem_base;                               // [128][CPITCH] fp32 partial of this CTA
+        const uint32_t recv = smem_base + (uint32_t)BM * CPITCH;       // [S-1][R][CPITCH] row slices pushed by the peers
+        const uint32_t sums = part + (uint32_t)r0 * CPITCH;            // reduced in place over this CTA's own rows
+        const uint32_t rbar = ptx::smem_u32(recv_bar);
+        {
+          // group 0 parks 16-column pieces 0..5, group 1 pieces 6..10 (the last one is h)
+          const int pc0 = grp == 0 ? 0 : 6, pc1 = grp == 0 ? 6 : (BN + HCOLS) / 16;
+#pragma unroll 1
+          for (int pc = pc0; pc < pc1; ++pc) {
+            uint32_t v[16];
+            ptx::tmem_ld_32x16(t_acc + pc * 16, v);
+            ptx::tmem_ld_wait();
+            const uint32_t dst = part + row * CPITCH + pc * 64;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) ptx::st_shared_v4(dst + k * 16, v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+          }
+        }
+        ptx::tc_fence_before();
+        ptx::fence_proxy_async_smem();          // the partial is read by the bulk-copy (async proxy) below
+        if (et == 0) ptx::mbar_arrive_expect_tx(rbar, (uint32_t)((S - 1) * nrows * CPITCH));
+        // cluster barrier 1: every CTA's partial is parked, its operand stages are idle (they hold the receive
+        // buffer) and its receive barrier is armed
+        ptx::cluster_arrive();
+        ptx::cluster_wait();
+        if (et == 0) {
+          SLIDER_TRACE(11);
+          // push my rows [r*R, ...) to peer r: one bulk DMA per peer, no thread touches remote shared memory
+          for (int r = 0; r < S; ++r) {
+            if (r == (int)split) continue;
+            const int pr0 = r * R, pn = max(0, min(R, BM - pr0));
+            if (pn == 0) continue;
+            const int slot = (int)split < r ? (int)split : (int)split - 1;
+            ptx::bulk_copy_to_peer(ptx::mapa(recv + (uint32_t)(slot * R) * CPITCH, (uint32_t)r),
+                                   part + (uint32_t)pr0 * CPITCH, (uint32_t)(pn * CPITCH), ptx::mapa(rbar, (uint32_t)r));
+          }
+        }
+        if (et < 32) ptx::mbar_wait(rbar, 0);
+        asm volatile("bar.sync 2, 256;" ::: "memory");
+        if (et == 0) SLIDER_TRACE(12);
+        // sum the S row slices in split order (deterministic): mine in place, the peers' from the receive buffer
+        constexpr int PIECES = (BN + HCOLS) / 4;                       // 16-byte pieces per row (44)
+        for (int i = et; i < nrows * PIECES; i += kEpiThreads) {
+          const int rr = i / PIECES, pc = i - rr * PIECES;
+          const uint32_t off = (uint32_t)rr * CPITCH + pc * 16;
+          float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+          for (int sp = 0; sp < MAX_CLUSTER; ++sp) {
+            if (sp < S) {
+              const int slot = sp < (int)split ? sp : sp - 1;
+              const float4 v = ptx::ld_shared_f4(sp == (int)split ? sums + off : recv + (uint32_t)(slot * R) * CPITCH + off);
+              acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+            }
+          }
+          ptx::st_shared_f4(sums + off, acc);
+        }
+        asm volatile("bar.sync 2, 256;" ::: "memory");
+        const int hoff = p.group_n > 0 ? (tc.n0 / p.group_n) * p.rank : 0;
+        for (int i = et; i < nrows * (BN / 8); i += kEpiThreads) {
+          const int rr = i / (BN / 8), g8 = i - rr * (BN / 8);
+          const int n = tc.n0 + g8 * 8;
+          const int trow = r0 + rr;
+          const int lw = trow % p.TW, lh = (trow / p.TW) % p.TH, lb = trow / (p.TW * p.TH);
+          const bool row_ok = trow < p.rows && tc.w0 + lw < p.W && tc.h0 + lh < p.H && tc.b0 + lb < p.B;
+          if (!row_ok || n >= p.N) continue;
+          const size_t pix = ((size_t)(tc.b0 + lb) * p.H + (tc.h0 + lh)) * p.W + (tc.w0 + lw);
+          const uint32_t srow = sums + rr * CPITCH;
+          const float4 a0 = ptx::ld_shared_f4(srow + g8 * 32), a1 = ptx::ld_shared_f4(srow + g8 * 32 + 16);
+          float o[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+          float hv[R4 > 0 ? 4 * R4 : 1];
+          if (R4 > 0) {
+#pragma unroll
+            for (int j = 0; j < 4 * R4; ++j) hv[j] = ptx::ld_shared_f32(srow + (BN + min(hoff + j, HCOLS - 1)) * 4);
+          }
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const int ci = g8 * 8 + k;
+            float a = o[k] + ptx::ld_shared_f32(bias_s + ci * 4);
+            if (R4 > 0) {
+#pragma unroll
+              for (int j4 = 0; j4 < R4; ++j4) {
+                const float4 b = ptx::ld_shared_f4(epi_s + ci * (16 * R4) + j4 * 16);
+                a = fmaf(hv[4 * j4 + 0], b.x, a);
+                a = fmaf(hv[4 * j4 + 1], b.y, a);
+                a = fmaf(hv[4 * j4 + 2], b.z, a);
+                a = fmaf(hv[4 * j4 + 3], b.w, a);
+              }
+            }
+            o[k] = a;
+          }
+          T* dst = reinterpret_cast<T*>(p.y) + pix * (size_t)p.N + n;
+          if (sizeof(T) == 2) {
+            __nv_bfloat16* d16 = reinterpret_cast<__nv_bfloat16*>(dst);
+            if (p.accumulate) {   // y holds the residual: same two roundings as `residual + module(x)` in element dtype
+              float res[8];
+              Elem<__nv_bfloat16>::load(d16, res);
+#pragma unroll
+              for (int k = 0; k < 8; ++k) o[k] = __bfloat162float(__float2bfloat16_rn(o[k])) + res[k];
+            }
+            Elem<__nv_bfloat16>::store(d16, o);
+          } else {
+            float4* d4 = reinterpret_cast<float4*>(dst);
+            if (p.accumulate) {
+              const float4 q0 = d4[0], q1 = d4[1];
+              o[0] += q0.x; o[1] += q0.y; o[2] += q0.z; o[3] += q0.w; o[4] += q1.x; o[5] += q1.y; o[6] += q1.z; o[7] += q1.w;
+            }
+            d4[0] = make_float4(o[0], o[1], o[2], o[3]);
+            d4[1] = make_float4(o[4], o[5], o[6], o[7]);
+          }
+          if (R4 > 0 && p.h_out != nullptr && tc.n_blk == 0 && g8 == 0) {
+#pragma unroll
+            for (int j = 0; j < 4 * R4; ++j)
+              if (j < p.rank) p.h_out[pix * p.rank + j] = hv[j];
+          }
+        }
+        if (et == 0) SLIDER_TRACE(6);
+        // the peers may still be reading this CTA's partial: second cluster barrier before anyone exits
+        ptx::cluster_arrive();
+        ptx::cluster_wait();
+        continue;
       }
       if (p.ksplit > 1) {
         // split-K: park the fp32 partial tile (main + h columns) in the L2-resident workspace,
@@ -551,6 +703,12 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #undef SLIDER_GROUP_BAR
   }
 
+  if (p.cluster && warp < 2) {
+    // cluster split-K: every thread of the cluster takes part in the two cluster barriers of the epilogue
+    // (warps 0/1, whose elected lanes have finished their single unit by now, have nothing to publish)
+    ptx::cluster_arrive(); ptx::cluster_wait();
+    ptx::cluster_arrive(); ptx::cluster_wait();
+  }
   ptx::tc_fence_before();
   __syncthreads();
   if (warp == 1) {
@@ -689,19 +847,30 @@ template <> __device__ inline void Raw16<float>::unpack(const uint4& t, float (&
   v[0] = __uint_as_float(t.x); v[1] = __uint_as_float(t.y); v[2] = __uint_as_float(t.z); v[3] = __uint_as_float(t.w);
 }
 
+// V consecutive fp32 activations from shared memory as 16-byte loads (the scalar form made the small-M kernels
+// shared-memory-issue bound: one LDS.32 per FMA)
+template <int V>
+__device__ __forceinline__ void lds_vec(const float* p, float (&v)[V]) {
+#pragma unroll
+  for (int q = 0; q < V / 4; ++q) {
+    const float4 t = reinterpret_cast<const float4*>(p)[q];
+    v[4 * q] = t.x; v[4 * q + 1] = t.y; v[4 * q + 2] = t.z; v[4 * q + 3] = t.w;
+  }
+}
+
 // KC = 16-byte chunks of a weight row per lane (K <= KC * 32 * kVec).  All global loads of a warp (its W row,
 // its lora_down row) are issued before the first barrier, so the kernel pays ONE DRAM latency, not one per chunk.
 template <typename T, int MT, int KC>
-__global__ void __launch_bounds__(GEMV_WARPS * 32)
-lora_gemv_kernel(T* __restrict__ y, const T* __restrict__ x, const T* __restrict__ W, const T* __restrict__ bias,
-                 const T* __restrict__ A, const T* __restrict__ Bup, float* __restrict__ h_out, int M, int K, int N,
-                 int rank, float s, int lora) {
+__device__ __forceinline__ void
+lora_gemv_body(T* __restrict__ y, const T* __restrict__ x, const T* __restrict__ W, const T* __restrict__ bias,
+               const T* __restrict__ A, const T* __restrict__ Bup, float* __restrict__ h_out, int M, int K, int N,
+               int rank, float s, int lora, int blk) {
   constexpr int V = Elem<T>::kVec;
   extern __shared__ float gemv_smem[];
   float* xs = gemv_smem;                  // [MT][K]
   float* hs = gemv_smem + (size_t)MT * K; // [MT][16]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n = blockIdx.x * GEMV_WARPS + warp;
+  const int n = blk * GEMV_WARPS + warp;
   const bool n_ok = n < N;
   uint4 wreg[KC], areg[KC];
   const int pr0 = warp;                   // first (row m, rank j) pair of this warp for h = x . A^T
@@ -741,24 +910,26 @@ lora_gemv_kernel(T* __restrict__ y, const T* __restrict__ x, const T* __restrict
         for (int c = 0; c < KC; ++c) {
           const int k = (c * 32 + lane) * V;
           if (k < K) {
-            float av[V];
+            float av[V], xv[V];
             Raw16<T>::unpack(areg[c], av);
+            lds_vec<V>(xs + m * K + k, xv);
 #pragma unroll
-            for (int e = 0; e < V; ++e) acc = fmaf(av[e], xs[m * K + k + e], acc);
+            for (int e = 0; e < V; ++e) acc = fmaf(av[e], xv[e], acc);
           }
         }
       } else {
         for (int k = lane * V; k < K; k += 32 * V) {
-          float av[V];
+          float av[V], xv[V];
           Elem<T>::load(A + (size_t)j * K + k, av);
+          lds_vec<V>(xs + m * K + k, xv);
 #pragma unroll
-          for (int e = 0; e < V; ++e) acc = fmaf(av[e], xs[m * K + k + e], acc);
+          for (int e = 0; e < V; ++e) acc = fmaf(av[e], xv[e], acc);
         }
       }
       acc = warp_sum(acc);
       if (lane == 0) {
         hs[m * 16 + j] = acc;
-        if (h_out != nullptr && blockIdx.x == 0 && m < M) h_out[m * rank + j] = acc;
+        if (h_out != nullptr && blk == 0 && m < M) h_out[m * rank + j] = acc;
       }
     }
     __syncthreads();
@@ -775,9 +946,10 @@ lora_gemv_kernel(T* __restrict__ y, const T* __restrict__ x, const T* __restrict
       Raw16<T>::unpack(wreg[c], wv);
 #pragma unroll
       for (int m = 0; m < MT; ++m) {
-        const float* xr = xs + m * K + k;
+        float xv[V];
+        lds_vec<V>(xs + m * K + k, xv);
 #pragma unroll
-        for (int e = 0; e < V; ++e) acc[m] = fmaf(wv[e], xr[e], acc[m]);
+        for (int e = 0; e < V; ++e) acc[m] = fmaf(wv[e], xv[e], acc[m]);
       }
     }
   }
@@ -797,6 +969,133 @@ lora_gemv_kernel(T* __restrict__ y, const T* __restrict__ x, const T* __restrict
   }
 }
 
+template <typename T, int MT, int KC>
+__global__ void __launch_bounds__(GEMV_WARPS * 32)
+lora_gemv_kernel(T* __restrict__ y, const T* __restrict__ x, const T* __restrict__ W, const T* __restrict__ bias,
+                 const T* __restrict__ A, const T* __restrict__ Bup, float* __restrict__ h_out, int M, int K, int N,
+                 int rank, float s, int lora) {
+  lora_gemv_body<T, MT, KC>(y, x, W, bias, A, Bup, h_out, M, K, N, rank, s, lora, (int)blockIdx.x);
+}
+
+// Several small-M adapters on ONE input in one launch (the 16-22 `time_emb_proj` layers of a UNet forward all project
+// the same silu(temb) rows): block b serves layer l with blk_end[l-1] <= b < blk_end[l].
+constexpr int GEMV_MAX_LAYERS = 32;
+struct GemvMultiParams {
+  const void* W[GEMV_MAX_LAYERS];
+  const void* bias[GEMV_MAX_LAYERS];
+  const void* A[GEMV_MAX_LAYERS];
+  const void* Bup[GEMV_MAX_LAYERS];
+  void* y[GEMV_MAX_LAYERS];
+  int N[GEMV_MAX_LAYERS];
+  int blk_end[GEMV_MAX_LAYERS];
+  float s[GEMV_MAX_LAYERS];
+  int layers;
+};
+// Each warp walks `ch` output channels of its layer (stride GEMV_WARPS) with the NEXT channel's weight row in flight
+// while it reduces the current one; the activation rows and h = x . A^T are staged once per block.  Per-channel
+// arithmetic is the single-layer kernel's (same chunk order, same shuffles): results are bit-identical to it.
+template <typename T, int MT, int KC>
+__global__ void __launch_bounds__(GEMV_WARPS * 32)
+lora_gemv_multi_kernel(const T* __restrict__ x, int M, int K, int rank, int ch, const __grid_constant__ GemvMultiParams mp) {
+  constexpr int V = Elem<T>::kVec;
+  extern __shared__ float gemv_smem[];
+  float* xs = gemv_smem;                  // [MT][K]
+  float* hs = gemv_smem + (size_t)MT * K; // [MT][16]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  int l = 0;
+  while (l + 1 < mp.layers && (int)blockIdx.x >= mp.blk_end[l]) ++l;
+  const int blk = (int)blockIdx.x - (l > 0 ? mp.blk_end[l - 1] : 0);
+  const float s = mp.s[l];
+  const int N = mp.N[l];
+  T* __restrict__ y = reinterpret_cast<T*>(mp.y[l]);
+  const T* __restrict__ W = reinterpret_cast<const T*>(mp.W[l]);
+  const T* __restrict__ bias = reinterpret_cast<const T*>(mp.bias[l]);
+  const T* __restrict__ A = reinterpret_cast<const T*>(mp.A[l]);
+  const T* __restrict__ Bup = reinterpret_cast<const T*>(mp.Bup[l]);
+  const bool lora = A != nullptr && s != 0.f;
+  uint4 w0[KC], w1[KC];
+  auto load_row = [&](uint4 (&wr)[KC], int n) {
+    const uint4* wrow = reinterpret_cast<const uint4*>(W + (size_t)n * K);
+#pragma unroll
+    for (int c = 0; c < KC; ++c) {
+      const int k = (c * 32 + lane) * V;
+      wr[c] = k < K ? __ldg(wrow + c * 32 + lane) : make_uint4(0, 0, 0, 0);
+    }
+  };
+  auto reduce_row = [&](const uint4 (&wr)[KC], int n) {
+    float acc[MT];
+#pragma unroll
+    for (int m = 0; m < MT; ++m) acc[m] = 0.f;
+#pragma unroll
+    for (int c = 0; c < KC; ++c) {
+      const int k = (c * 32 + lane) * V;
+      if (k < K) {
+        float wv[V];
+        Raw16<T>::unpack(wr[c], wv);
+#pragma unroll
+        for (int m = 0; m < MT; ++m) {
+          float xv[V];
+          lds_vec<V>(xs + m * K + k, xv);
+#pragma unroll
+          for (int e = 0; e < V; ++e) acc[m] = fmaf(wv[e], xv[e], acc[m]);
+        }
+      }
+    }
+#pragma unroll
+    for (int m = 0; m < MT; ++m) acc[m] = warp_sum(acc[m]);
+    if (lane < MT && lane < M) {
+      float a = 0.f;
+#pragma unroll
+      for (int m = 0; m < MT; ++m) a = (lane == m) ? acc[m] : a;
+      if (bias != nullptr) a += Elem<T>::to_f(bias[n]);
+      if (lora) {
+        float lo = 0.f;
+        for (int j = 0; j < rank; ++j) lo = fmaf(hs[lane * 16 + j], Elem<T>::to_f(Bup[(size_t)n * rank + j]), lo);
+        a = fmaf(s, lo, a);
+      }
+      y[(size_t)lane * N + n] = Elem<T>::from_f(a);
+    }
+  };
+  pdl_trigger();
+  const int n_first = blk * ch * GEMV_WARPS + warp;
+  // frozen weights are never written by a preceding kernel: the first row is requested before the dependency wait
+  if (n_first < N) load_row(w0, n_first);
+  pdl_wait();
+  for (int i = threadIdx.x * V; i < MT * K; i += blockDim.x * V) {
+    const int m = i / K;
+    float v[V];
+    if (m < M) Elem<T>::load(x + i, v);
+#pragma unroll
+    for (int k = 0; k < V; ++k) xs[i + k] = m < M ? v[k] : 0.f;
+  }
+  __syncthreads();
+  if (lora) {
+    for (int pr = warp; pr < MT * rank; pr += GEMV_WARPS) {
+      const int m = pr / rank, j = pr - m * rank;
+      float acc = 0.f;
+      for (int k = lane * V; k < K; k += 32 * V) {
+        float av[V], xv[V];
+        Elem<T>::load(A + (size_t)j * K + k, av);
+        lds_vec<V>(xs + m * K + k, xv);
+#pragma unroll
+        for (int e = 0; e < V; ++e) acc = fmaf(av[e], xv[e], acc);
+      }
+      acc = warp_sum(acc);
+      if (lane == 0) hs[m * 16 + j] = acc;
+    }
+  }
+  __syncthreads();
+  for (int c = 0; c < ch; c += 2) {
+    const int n0 = n_first + c * GEMV_WARPS, n1 = n0 + GEMV_WARPS, n2 = n1 + GEMV_WARPS;
+    if (n0 >= N) break;
+    if (c + 1 < ch && n1 < N) load_row(w1, n1);
+    reduce_row(w0, n0);
+    if (c + 1 >= ch || n1 >= N) break;
+    if (c + 2 < ch && n2 < N) load_row(w0, n2);
+    reduce_row(w1, n1);
+  }
+}
+
 }  // namespace slider
 
 // =================================== host side ===================================
@@ -806,6 +1105,11 @@ struct TileGeom { int TW, TH, TB; };
 
 static long long* g_gemm_trace = nullptr;   // set by slider_debug_gemm_trace (profiling aid)
 static int g_splitk_depth = 6;      // minimum K blocks per split (slider_debug_splitk_depth)
+// 1 = reduce split-K partials inside a thread-block cluster over distributed shared memory (bulk DMA pushes), 0 =
+// workspace + finalize kernel.  Opt-in (SLIDER_SPLITK_CLUSTER=1 / slider_debug_splitk_cluster): measured slower on
+// B200 -- DSMEM moves ~17 B/clk per SM, the 70-80 KB of partial rows a CTA exchanges cost ~5 K cycles against ~1.5 K
+// through L2 -- see profiles/r01_ab_splitk_cluster.txt.
+static int g_splitk_cluster = [] { const char* e = getenv("SLIDER_SPLITK_CLUSTER"); return (e && e[0] == '1') ? 1 : 0; }();
 
 static TileGeom choose_tile(int W, int H, int B) {
   TileGeom t;
@@ -842,6 +1146,21 @@ static int launch_gemm(int r4, const CUtensorMap& a, const CUtensorMap& w, const
     for (auto& c : configured) if (c == nullptr) { c = (const void*)kern; break; }
   }
   int grid = p.total_units < sm_count() ? p.total_units : sm_count();
+  if (p.cluster) {
+    // one unit per CTA, the ksplit CTAs of a tile form one cluster (cluster rank == split)
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(p.total_units); cfg.blockDim = dim3(kGemmThreads);
+    cfg.dynamicSmemBytes = gemm_smem_bytes(r4); cfg.stream = st;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)p.ksplit; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 2 : 1;
+    cudaLaunchKernelEx(&cfg, kern, a, w, l, xe, we, my, mp, p);
+    return post_launch("lora_gemm_kernel (cluster split-K)");
+  }
   launch_pdl(kern, dim3(grid), dim3(kGemmThreads), gemm_smem_bytes(r4), st, a, w, l, xe, we, my, mp, p);
   int rc = post_launch("lora_gemm_kernel");
   if (rc || p.ksplit == 1) return rc;
@@ -929,14 +1248,21 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
   p.kiters = taps * p.per_tap;
   // split-K when the tile count leaves more than half of the SMs idle and K is deep enough
   p.ksplit = 1;
+  p.cluster = 0;
   p.partial = reinterpret_cast<float*>(ws);
-  if (ws != nullptr && ((uintptr_t)ws & 15) == 0 && p.total_tiles * 2 <= sm_count()) {
+  if (p.total_tiles * 2 <= sm_count()) {
     int ks = sm_count() / p.total_tiles;
     const int by_depth = p.kiters / g_splitk_depth;
     if (ks > by_depth) ks = by_depth;
-    const long long cap = (long long)(ws_bytes / (UNIT_FLOATS * sizeof(float)));
-    if ((long long)ks * p.total_tiles > cap) ks = (int)(cap / p.total_tiles);
-    if (ks >= 2) p.ksplit = ks;
+    if (g_splitk_cluster) {
+      // in-cluster reduction over distributed shared memory: no workspace, no second launch
+      if (ks > MAX_CLUSTER) ks = MAX_CLUSTER;
+      if (ks >= 2) { p.ksplit = ks; p.cluster = 1; }
+    } else if (ws != nullptr && ((uintptr_t)ws & 15) == 0) {
+      const long long cap = (long long)(ws_bytes / (UNIT_FLOATS * sizeof(float)));
+      if ((long long)ks * p.total_tiles > cap) ks = (int)(cap / p.total_tiles);
+      if (ks >= 2) p.ksplit = ks;
+    }
   }
   p.total_units = p.total_tiles * p.ksplit;
   p.fd_n_tiles = FastDiv::make((uint32_t)p.n_tiles);
@@ -992,7 +1318,7 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
     if ((rc = make_tmap(&mY, g->dtype, 4, y, dims, str, box, OUT_ROW_BYTES))) return rc;
   }
   mP = mY;
-  if (p.ksplit > 1) {
+  if (p.ksplit > 1 && !p.cluster) {
     uint64_t dims[2] = {(uint64_t)PCW, (uint64_t)p.total_units * NCHUNK * BM};
     uint64_t str[1] = {(uint64_t)OUT_ROW_BYTES};
     uint32_t box[2] = {(uint32_t)PCW, (uint32_t)BM};
@@ -1001,6 +1327,21 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
   const int r4 = !lora ? 0 : (g->rank <= 4 ? 1 : (g->rank <= 8 ? 2 : 4));
   if (g->dtype == SLIDER_BF16) return launch_gemm<__nv_bfloat16>(r4, mA, mW, mL, mXe, mWe, mY, mP, p, st);
   return launch_gemm<float>(r4, mA, mW, mL, mXe, mWe, mY, mP, p, st);
+}
+
+template <typename T>
+static int launch_gemv_multi(const GemvMultiParams& mp, int grid, int ch, const void* x, int M, int K, int rank,
+                             cudaStream_t st) {
+  const int mt = M <= 2 ? 2 : (M <= 4 ? 4 : (M <= 8 ? 8 : 16));
+  const size_t smem = ((size_t)mt * K + (size_t)mt * 16) * sizeof(float);
+  const int V = 16 / (int)sizeof(T);
+  const int kc = (K + 32 * V - 1) / (32 * V);
+#define GEMVM2(MT, KC) launch_pdl(lora_gemv_multi_kernel<T, MT, KC>, dim3(grid), dim3(GEMV_WARPS * 32), smem, st, (const T*)x, M, K, rank, ch, mp)
+#define GEMVM(MT) do { if (kc <= 2) GEMVM2(MT, 2); else if (kc <= 5) GEMVM2(MT, 5); else GEMVM2(MT, 8); } while (0)
+  if (mt == 2) GEMVM(2); else if (mt == 4) GEMVM(4); else if (mt == 8) GEMVM(8); else GEMVM(16);
+#undef GEMVM
+#undef GEMVM2
+  return post_launch("lora_gemv_multi_kernel");
 }
 
 int run_gemm_plain(const slider_layer_geom* g, int kc, int nn, void* y, const void* act, const void* wgt, void* ws,
@@ -1015,6 +1356,7 @@ using namespace slider;
 extern "C" {
 
 int slider_debug_splitk_depth(int d) { g_splitk_depth = d > 0 ? d : 6; return SLIDER_OK; }
+int slider_debug_splitk_cluster(int on) { g_splitk_cluster = on ? 1 : 0; return SLIDER_OK; }
 int slider_debug_gemm_trace(void* buf) { g_gemm_trace = reinterpret_cast<long long*>(buf); return SLIDER_OK; }
 
 size_t slider_gemm_workspace_bytes(void) { return (size_t)MAX_UNITS * UNIT_FLOATS * sizeof(float); }
@@ -1044,6 +1386,48 @@ int slider_lora_forward_grouped(const slider_layer_geom* g, void* y, const void*
   SLIDER_CHECK_ARG(s != 0.f, "lora_forward_grouped: s == 0 (adapter off) is the plain slider_lora_forward call");
   return run_gemm(g, g->cin, g->cout, y, x, W, bias, A, B, nullptr, s, nullptr, nullptr, ws, ws_bytes,
                   (cudaStream_t)stream, groups);
+}
+
+int slider_lora_forward_small_multi(int dtype, int layers, int M, int K, int rank, const void* x, void* const* y,
+                                    const void* const* W, const void* const* bias, const void* const* A,
+                                    const void* const* B, const int* N, const float* s, void* stream) {
+  SLIDER_CHECK_ARG(dtype == SLIDER_BF16 || dtype == SLIDER_F32, "lora_forward_small_multi: unsupported dtype %d", dtype);
+  SLIDER_CHECK_ARG(layers >= 1 && layers <= GEMV_MAX_LAYERS, "lora_forward_small_multi: layers %d not in 1..%d", layers,
+                   GEMV_MAX_LAYERS);
+  SLIDER_CHECK_ARG(x && y && W && N && s, "lora_forward_small_multi: null pointer");
+  SLIDER_CHECK_ARG(M >= 1 && M <= 16, "lora_forward_small_multi: M = %d rows (the weight-streaming path serves 1..16)", M);
+  const int es = esize(dtype);
+  const size_t mt = M <= 2 ? 2 : (M <= 4 ? 4 : (M <= 8 ? 8 : 16));
+  SLIDER_CHECK_ARG(K > 0 && K % 8 == 0 && mt * K * sizeof(float) <= 40 * 1024 && (size_t)K * es <= 8 * 32 * 16,
+                   "lora_forward_small_multi: K = %d out of range", K);
+  SLIDER_CHECK_ARG(rank >= 0 && rank <= 16, "lora_forward_small_multi: rank %d not in 0..16", rank);
+  SLIDER_CHECK_ARG(((uintptr_t)x & 15) == 0, "lora_forward_small_multi: x must be 16-byte aligned");
+  GemvMultiParams mp;
+  for (int l = 0; l < layers; ++l) {
+    SLIDER_CHECK_ARG(y[l] && W[l] && N[l] > 0, "lora_forward_small_multi: layer %d has a null pointer / empty N", l);
+    SLIDER_CHECK_ARG(((uintptr_t)W[l] & 15) == 0, "lora_forward_small_multi: W of layer %d must be 16-byte aligned", l);
+    const bool lora = A && A[l] && rank > 0 && s[l] != 0.f;
+    if (lora) SLIDER_CHECK_ARG(B && B[l] && ((uintptr_t)A[l] & 15) == 0, "lora_forward_small_multi: bad adapter of layer %d", l);
+    mp.W[l] = W[l]; mp.bias[l] = bias ? bias[l] : nullptr;
+    mp.A[l] = lora ? A[l] : nullptr; mp.Bup[l] = lora ? B[l] : nullptr;
+    mp.y[l] = y[l]; mp.N[l] = N[l]; mp.s[l] = s[l];
+  }
+  mp.layers = layers;
+  // channels per warp: the smallest count for which the whole call is ONE wave of 4 resident blocks per SM (64 regs)
+  int ch = 1, blocks = 0;
+  for (; ch <= 16; ++ch) {
+    blocks = 0;
+    for (int l = 0; l < layers; ++l) blocks += (N[l] + GEMV_WARPS * ch - 1) / (GEMV_WARPS * ch);
+    if (blocks <= 4 * sm_count()) break;
+  }
+  if (ch > 16) ch = 16;
+  blocks = 0;
+  for (int l = 0; l < layers; ++l) {
+    blocks += (N[l] + GEMV_WARPS * ch - 1) / (GEMV_WARPS * ch);
+    mp.blk_end[l] = blocks;
+  }
+  if (dtype == SLIDER_BF16) return launch_gemv_multi<__nv_bfloat16>(mp, blocks, ch, x, M, K, rank, (cudaStream_t)stream);
+  return launch_gemv_multi<float>(mp, blocks, ch, x, M, K, rank, (cudaStream_t)stream);
 }
 
 int slider_lora_input_grad(const slider_layer_geom* g, void* dx, const void* gy, const void* Wt, const void* dh,

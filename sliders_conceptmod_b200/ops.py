@@ -111,6 +111,43 @@ def lora_forward_grouped(x: torch.Tensor, w_cat: torch.Tensor, a_cat: torch.Tens
     return y
 
 
+class SmallMultiPlan:
+    """Pointer tables of one `lora_forward_small_multi` call, built once per (layer set, input buffer): the frozen
+    weights, the flat LoRA parameter buffer and the output buffer never move, so a captured launch stays valid."""
+
+    def __init__(self, x_rows: int, k: int, dtype: torch.dtype, device, layers):
+        # layers: list of (w [N,1,K] | [N,K], bias [N] | None, a [r,1,K] | None, b [N,r] | None)
+        self.n = [int(l[0].shape[0]) for l in layers]
+        self.rank = max([0] + [int(l[2].shape[0]) for l in layers if l[2] is not None])
+        self.m, self.k, self.dtype = int(x_rows), int(k), dtype
+        self.out = torch.empty(self.m * sum(self.n), device=device, dtype=dtype)
+        self.views, off = [], 0
+        for n in self.n:
+            self.views.append(self.out[off * self.m:(off + n) * self.m].view(self.m, n))
+            off += n
+        L = len(layers)
+        vp = C.c_void_p * L
+        self.keep = layers
+        self.W = vp(*[l[0].data_ptr() for l in layers])
+        self.bias = vp(*[(l[1].data_ptr() if l[1] is not None else None) for l in layers])
+        self.A = vp(*[(l[2].data_ptr() if l[2] is not None else None) for l in layers])
+        self.B = vp(*[(l[3].data_ptr() if l[3] is not None else None) for l in layers])
+        self.Y = vp(*[v.data_ptr() for v in self.views])
+        self.N = (C.c_int * L)(*self.n)
+        self.L = L
+
+
+def lora_forward_small_multi(x: torch.Tensor, plan: SmallMultiPlan, scales) -> list:
+    """All small-M adapters of `plan` on the same rows x [M <= 16, K] in ONE launch (the time_emb_proj layers of a
+    UNet forward); returns the per-layer outputs (views of the plan's buffer)."""
+    require_cuda(x)
+    assert x.dim() == 2 and x.is_contiguous() and x.shape == (plan.m, plan.k) and x.dtype == plan.dtype
+    s = (C.c_float * plan.L)(*[float(v) for v in scales])
+    check(lib().slider_lora_forward_small_multi(dtype_code(x.dtype), plan.L, plan.m, plan.k, plan.rank, ptr(x),
+                                                plan.Y, plan.W, plan.bias, plan.A, plan.B, plan.N, s, stream_ptr()))
+    return plan.views
+
+
 def lora_input_grad(gy: torch.Tensor, wt: torch.Tensor, dh: torch.Tensor | None, at: torch.Tensor | None,
                     cin: int, ksize: int = 1, rank: int = 0) -> torch.Tensor:
     """dx = convT(gy, W) + convT(dh, A);  wt [Cin, k*k, Cout] flipped taps, at [Cin, k*k, 16]."""

@@ -548,11 +548,43 @@ class UNet2DConditionModel(nn.Module):
         main = torch.cuda.current_stream(dev)
         side.wait_stream(main)
         with torch.cuda.stream(side):
+            m_pad = 2 if emb.shape[0] <= 2 else 4 if emb.shape[0] <= 4 else 8 if emb.shape[0] <= 8 else 16
+            if ("temb_multi" not in _DISABLED and emb.dim() == 2 and emb.shape[0] <= 16 and emb.is_contiguous()
+                    and m_pad * emb.shape[1] * 4 <= 40 * 1024 and emb.shape[1] * emb.element_size() <= 4096
+                    and len(blocks) <= 32):     # the small-M kernel's limits (include/slider_b200.h)
+                # ONE weight-streaming launch for every block's projection (slider_lora_forward_small_multi)
+                ts = self._temb_multi(blocks, emb)
+                ev = torch.cuda.Event()
+                ev.record(side)
+                for rb, t in zip(blocks, ts):
+                    rb.__dict__["_t_ready"] = (ev, t)
+                return
             for rb in blocks:
                 t = rb.time_emb_proj(emb)
                 ev = torch.cuda.Event()
                 ev.record(side)
                 rb.__dict__["_t_ready"] = (ev, t)
+
+    def _temb_multi(self, blocks, emb: torch.Tensor):
+        from . import ops
+        layers, scales = [], []
+        for rb in blocks:
+            lin = rb.time_emb_proj
+            lm = getattr(lin.forward, "__self__", None)
+            if lm is not None and lm.__class__.__name__ == "LoRAModule":      # wrapped: lora.py:94-98,131
+                a_w, b_w = lm.lora_down.weight, lm.lora_up.weight
+                layers.append((lm._packed_base(), lm._bias(), lm._packed_down(a_w), lm._packed_up(b_w)))
+                scales.append(float(lm.multiplier) * float(lm.scale))
+            else:
+                layers.append((lin.weight, lin.bias, None, None))
+                scales.append(0.0)
+        key = (emb.shape[0], emb.dtype, emb.device) + tuple(
+            t.data_ptr() if t is not None else 0 for l in layers for t in l)
+        plan = self.__dict__.get("_temb_plan")
+        if plan is None or plan[0] != key:
+            plan = (key, ops.SmallMultiPlan(emb.shape[0], emb.shape[1], emb.dtype, emb.device, layers))
+            self.__dict__["_temb_plan"] = plan
+        return ops.lora_forward_small_multi(emb, plan[1], scales)
 
     def enable_xformers_memory_efficient_attention(self):  # API parity (train_lora.py:68); SDPA is used
         return None

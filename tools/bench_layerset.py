@@ -36,17 +36,45 @@ def main():
         calls.append(("grouped", tuple(x.shape), tuple(w_cat.shape), False, a_cat.shape[0], s, groups, False))
         return real_grouped(x, w_cat, a_cat, b_cat, groups, s)
 
-    ops.lora_forward, ops.lora_forward_grouped = spy, spy_grouped
+    real_multi = ops.lora_forward_small_multi
+    multi = []
+
+    def spy_multi(x, plan, scales):
+        multi.append((x.clone(), plan, tuple(scales)))
+        return real_multi(x, plan, scales)
+
+    ops.lora_forward, ops.lora_forward_grouped, ops.lora_forward_small_multi = spy, spy_grouped, spy_multi
     try:
         engine._body_denoise()
     finally:
-        ops.lora_forward, ops.lora_forward_grouped = real, real_grouped
+        ops.lora_forward, ops.lora_forward_grouped, ops.lora_forward_small_multi = real, real_grouped, real_multi
     torch.cuda.synchronize()
     sigs = OrderedDict()
     for c in calls:
         sigs[c] = sigs.get(c, 0) + 1
     dt = torch.bfloat16
     rows = []
+    for (x, plan, scales) in multi:
+        def run_m():
+            for _ in range(args.reps):
+                real_multi(x, plan, scales)
+        run_m(); torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            run_m()
+        g.replay(); torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(3):
+            g.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        us = e0.elapsed_time(e1) * 1e3 / (3 * args.reps)
+        M, K = x.shape
+        fl = sum(2.0 * M * n * K + 2.0 * M * plan.rank * (K + n) for n in plan.n)
+        rows.append({"kind": "multi", "x": list(x.shape), "w": [sum(plan.n), 1, K], "k": 1, "res": False,
+                     "rank": plan.rank, "count": 1, "us": round(us, 2), "total_us": round(us, 1),
+                     "gflop": round(fl / 1e9, 2), "tflops": round(fl / us / 1e6, 1)})
     for (kind, xs, ws, has_b, r, s, k, has_res), count in sigs.items():
         M = 1
         for d in xs[:-1]:
@@ -102,7 +130,7 @@ def main():
         r["share"] = round(r["total_us"] / tot, 3)
         print(json.dumps(r))
     print(json.dumps({"total_us": round(tot, 1), "total_gflop": round(totf, 1), "tflops": round(totf / tot * 1e-3, 1),
-                      "launches": len(calls)}))
+                      "launches": len(calls) + len(multi)}))
     if args.json:
         Path(args.json).write_text(json.dumps(rows, indent=1))
 

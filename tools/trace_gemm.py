@@ -10,7 +10,7 @@ dt, r, s = torch.bfloat16, 4, 0.25
 if "--nosplit" in sys.argv:
     _lib.lib().slider_debug_splitk_depth(1000000)
 names = ["setup", "first_tma_issue", "first_full", "last_mma_commit", "acc_visible", "epi_done", "exit",
-         "prod_ready", "after_tma_A", "after_tma_W"]
+         "prod_ready", "after_tma_A", "after_tma_W", "cluster_synced", "cluster_reduced"]
 for (B, H, W, C, N, k) in shapes:
     x = torch.randn(B, H, W, C, device="cuda", dtype=dt)
     w = (torch.randn(N, k * k, C, device="cuda") / (C * k * k) ** 0.5).to(dt)
@@ -27,7 +27,7 @@ for (B, H, W, C, N, k) in shapes:
     _lib.lib().slider_debug_gemm_trace(None)
     t = trace.view(148, 16).cpu()
     t = t[t[:, 0] > 0]
-    d = (t[:, 1:11] - t[:, :1]).double()
+    d = (t[:, 1:13] - t[:, :1]).double()
     print(f"shape {(B, H, W, C, N, k)} ctas {t.shape[0]}: cycles since CTA entry (median / max over CTAs)")
     for i, n in enumerate(names):
         col = d[:, i]
