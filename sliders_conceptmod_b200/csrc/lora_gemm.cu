@@ -1104,7 +1104,9 @@ namespace slider {
 struct TileGeom { int TW, TH, TB; };
 
 static long long* g_gemm_trace = nullptr;   // set by slider_debug_gemm_trace (profiling aid)
-static int g_splitk_depth = 6;      // minimum K blocks per split (slider_debug_splitk_depth)
+// minimum K blocks per split (slider_debug_splitk_depth / SLIDER_SPLITK_DEPTH)
+// 0 = the measured heuristic in run_gemm
+static int g_splitk_depth = [] { const char* e = getenv("SLIDER_SPLITK_DEPTH"); const int v = e ? atoi(e) : 0; return v > 0 ? v : 0; }();
 // 1 = reduce split-K partials inside a thread-block cluster over distributed shared memory (bulk DMA pushes), 0 =
 // workspace + finalize kernel.  Opt-in (SLIDER_SPLITK_CLUSTER=1 / slider_debug_splitk_cluster): measured slower on
 // B200 -- DSMEM moves ~17 B/clk per SM, the 70-80 KB of partial rows a CTA exchanges cost ~5 K cycles against ~1.5 K
@@ -1252,7 +1254,15 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
   p.partial = reinterpret_cast<float*>(ws);
   if (p.total_tiles * 2 <= sm_count()) {
     int ks = sm_count() / p.total_tiles;
-    const int by_depth = p.kiters / g_splitk_depth;
+    // A split costs a second launch plus the partial round trip (~6 us at 32+ tiles, ~2.5 us at <= 12): measured on
+    // the SD-1.4 layer set (profiles/r01_splitk_depth_sweep.txt) it only pays for deep K -- 64+ K blocks at >= 18 per
+    // split, or 40+ at >= 6 per split for the weight-streaming shapes with a handful of tiles.
+    int depth = g_splitk_depth, min_k = 0;
+    if (depth == 0) {
+      depth = p.total_tiles <= 12 ? 6 : 18;
+      min_k = p.total_tiles <= 12 ? 40 : 64;
+    }
+    const int by_depth = p.kiters >= min_k ? p.kiters / depth : 1;
     if (ks > by_depth) ks = by_depth;
     if (g_splitk_cluster) {
       // in-cluster reduction over distributed shared memory: no workspace, no second launch
@@ -1355,7 +1365,7 @@ using namespace slider;
 
 extern "C" {
 
-int slider_debug_splitk_depth(int d) { g_splitk_depth = d > 0 ? d : 6; return SLIDER_OK; }
+int slider_debug_splitk_depth(int d) { g_splitk_depth = d > 0 ? d : 0; return SLIDER_OK; }
 int slider_debug_splitk_cluster(int on) { g_splitk_cluster = on ? 1 : 0; return SLIDER_OK; }
 int slider_debug_gemm_trace(void* buf) { g_gemm_trace = reinterpret_cast<long long*>(buf); return SLIDER_OK; }
 
