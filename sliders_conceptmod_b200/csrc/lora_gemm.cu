@@ -119,6 +119,7 @@ struct GemmParams {
   int accumulate;         // y += result (y holds the residual branch) instead of y = result
   int group_n;            // grouped adapters: output columns per group (0 = one adapter); group g uses h columns [g*rank, (g+1)*rank)
   FastDiv fd_n_tiles, fd_mt_w, fd_mt_h, fd_ksplit, fd_per_tap, fd_kw;
+  int w_prefetch;         // K blocks the weight stream is requested into L2 ahead of the shared-memory pipeline
   long long* trace;       // debug: 16 clock64() stamps per CTA (NULL = off)
   void* y;
   const void* bias;
@@ -202,7 +203,6 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #define SLIDER_TRACE(slot) do { if (p.trace != nullptr) p.trace[blockIdx.x * 16 + (slot)] = clock64(); } while (0)
   pdl_trigger();
   if (threadIdx.x == 0) SLIDER_TRACE(0);
-
   const uint32_t smem_base = ptx::smem_u32(smem);
   const uint32_t main_tx = (uint32_t)(p.rows * ROW_BYTES + B_BYTES + (p.lora ? L_BYTES : 0));
   const uint32_t ext_tx = (uint32_t)((p.rows + BN) * Tr::kExtRowBytes);
@@ -226,6 +226,17 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       pj = pit - ptap * p.per_tap;
     }
   };
+  // Cold weights (in the real forward every layer's weights are cold: 1.7 GB stream through a 126 MB L2): the CTAs
+  // that share an N tile ask for the SAME weight rows, so only n_tiles x stages x 20 KB of distinct HBM requests are
+  // ever in flight and the first stage lands ~2 us late.  The CTA that owns the first pixel tile of an N tile
+  // therefore requests the weight tiles of the next `w_prefetch` K blocks into L2 (TMA tile prefetch, in consumption
+  // order), the first burst before the dependency wait -- frozen weights are never written by a preceding kernel.
+  auto prod_prefetch_w = [&](int it) {
+    const int tap = (int)p.fd_per_tap.div((uint32_t)it);
+    const int j = it - tap * p.per_tap;
+    if (j < p.cblocks) ptx::tma_prefetch_l2_3d(&tmW, j * BK, tap, ptc.n0);
+  };
+  auto prod_owner = [&]() { return p.w_prefetch > 0 && ptc.w0 == 0 && ptc.h0 == 0 && ptc.b0 == 0; };
   auto prod_issue = [&]() {
     const int ty = (int)p.fd_kw.div((uint32_t)ptap);
     const int dy = ty - p.pad, dx = ptap - ty * p.kw - p.pad;
@@ -242,9 +253,15 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       ptx::tma_load_4d(sa, &tmXe, fb, 0, ptc.w0 + dx, ptc.h0 + dy, ptc.b0);
       ptx::tma_load_3d(sa + A_BYTES, &tmWe, fb, 0, ptap, ptc.n0);
     }
+    if (prod_owner() && pit + p.w_prefetch < pit1) prod_prefetch_w(pit + p.w_prefetch);
     if (++pstage == (uint32_t)Tr::kStages) { pstage = 0; pphase ^= 1; }
     if (++pj == p.per_tap) { pj = 0; ++ptap; }
-    if (++pit == pit1) { pu += (int)gridDim.x; prod_begin(); }
+    if (++pit == pit1) {
+      pu += (int)gridDim.x;
+      prod_begin();
+      if (phave && prod_owner())
+        for (int d = 0; d < p.w_prefetch && pit + d < pit1; ++d) prod_prefetch_w(pit + d);
+    }
   };
 
   if (warp == 0 && lane == 0) {
@@ -280,8 +297,9 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     asm volatile("bar.sync 1, %0;" ::"n"(kGemmThreads) : "memory");
   }
   ptx::tc_fence_after();
-  // PDL: nothing of ours reads global memory before the previous kernel has completed and flushed
-  pdl_wait();
+  // PDL: nothing of ours reads what the previous kernel wrote before that kernel has completed and flushed (the
+  // producer warp waits after its first weight-prefetch burst below)
+  if (warp != 0) pdl_wait();
   const uint32_t tmem_base = warp == 0 ? 0u : *tmem_slot;
   if (threadIdx.x == 32) SLIDER_TRACE(1);
 
@@ -292,6 +310,9 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // ===================== TMA producer =====================
     prod_begin();
     SLIDER_TRACE(8);
+    if (phave && prod_owner())
+      for (int d = 0; d < p.w_prefetch && pit + d < pit1; ++d) prod_prefetch_w(pit + d);
+    pdl_wait();
     bool first = true;
     while (phave) {
       prod_issue();
@@ -1111,6 +1132,8 @@ static int g_splitk_depth = [] { const char* e = getenv("SLIDER_SPLITK_DEPTH"); 
 // workspace + finalize kernel.  Opt-in (SLIDER_SPLITK_CLUSTER=1 / slider_debug_splitk_cluster): measured slower on
 // B200 -- DSMEM moves ~17 B/clk per SM, the 70-80 KB of partial rows a CTA exchanges cost ~5 K cycles against ~1.5 K
 // through L2 -- see profiles/r01_ab_splitk_cluster.txt.
+// K blocks of L2 look-ahead on the weight stream (SLIDER_W_PREFETCH, 0 = off)
+static int g_w_prefetch = [] { const char* e = getenv("SLIDER_W_PREFETCH"); return e ? atoi(e) : 12; }();
 static int g_splitk_cluster = [] { const char* e = getenv("SLIDER_SPLITK_CLUSTER"); return (e && e[0] == '1') ? 1 : 0; }();
 
 static TileGeom choose_tile(int W, int H, int B) {
@@ -1282,6 +1305,9 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
   p.fd_per_tap = FastDiv::make((uint32_t)p.per_tap);
   p.fd_kw = FastDiv::make((uint32_t)p.kw);
   p.trace = g_gemm_trace;
+  // only when several pixel tiles share each weight tile: with ONE pixel tile every CTA streams distinct weights and
+  // the pipeline's own requests already fill HBM
+  p.w_prefetch = (p.mt_w * p.mt_h * p.mt_b > 1) ? g_w_prefetch : 0;
   p.y = y; p.bias = bias; p.Bup = Bup; p.h_out = lora ? h_out : nullptr;
   if (lora) {
     SLIDER_CHECK_ARG((g->rank * taps * kc * es) % 16 == 0 && ((uintptr_t)lo & 15) == 0, "lora gemm: lora_down misaligned");

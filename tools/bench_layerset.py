@@ -19,6 +19,7 @@ def main():
     ap.add_argument("--workload", default="sd14_text_slider_rank4_512px")
     ap.add_argument("--reps", type=int, default=20)
     ap.add_argument("--json", default=None)
+    ap.add_argument("--cold", action="store_true", help="rotate over >= 300 MB of weights per signature: every launch streams its weights from HBM, as in the real forward")
     args = ap.parse_args()
     dev = torch.device("cuda", 0)
     wl = workload.WORKLOADS[args.workload]
@@ -82,6 +83,8 @@ def main():
         N, T, C = ws
         # several operand sets so that back-to-back launches do not re-hit the same weights in L2
         nset = max(1, min(8, int(256e6 / max(1, N * T * C * 2))))
+        if args.cold:
+            nset = max(2, min(args.reps, -(-int(300e6) // (N * T * C * 2))))
         sets = []
         for _ in range(nset):
             x = torch.randn(xs, device=dev, dtype=dt)
