@@ -332,7 +332,7 @@ static int groupnorm_cluster_impl(void* y, const void* x, const void* chan_add, 
   static thread_local bool configured = false;
   if (!configured) {
     SLIDER_CUDA(cudaFuncSetAttribute(gn_cluster_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
-    if (cs > 8) SLIDER_CUDA(cudaFuncSetAttribute(gn_cluster_kernel<T>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    SLIDER_CUDA(cudaFuncSetAttribute(gn_cluster_kernel<T>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));   // cs = 16
     configured = true;
   }
   cudaLaunchConfig_t cfg = {};
