@@ -76,14 +76,15 @@ class OracleScheduler:
         self.config = SimpleNamespace(num_train_timesteps=1000)
         self.init_noise_sigma = torch.tensor(1.0)
         self.num_inference_steps = None
-        if kind == "euler_a":
+        if kind in ("euler_a", "lms"):
             self._sig_all = ((1 - self.alphas_cumprod.double()) / self.alphas_cumprod.double()).sqrt().numpy()
             self.set_timesteps(1000)
 
     def set_timesteps(self, n, device=None):
         import numpy as np
         self.num_inference_steps = n
-        if self.kind == "euler_a":
+        self.derivatives = []
+        if self.kind in ("euler_a", "lms"):
             ts = np.linspace(0, 999, n, dtype=float)[::-1].copy()
             sig = np.interp(ts, np.arange(0, 1000), self._sig_all)
             self.sigmas = torch.from_numpy(np.concatenate([sig, [0.0]]).astype(np.float32))
@@ -97,7 +98,7 @@ class OracleScheduler:
         return int((self.timesteps - float(t)).abs().argmin())
 
     def scale_model_input(self, sample, t):
-        if self.kind == "euler_a":
+        if self.kind in ("euler_a", "lms"):
             s = self.sigmas[self._sigma_index(t)]
             return sample / ((s ** 2 + 1) ** 0.5)
         return sample
@@ -111,6 +112,8 @@ class OracleScheduler:
             prev = ddim_prev_step(model_output, int(timestep), self, sample)
         elif self.kind == "ddpm":
             prev = ddpm_step(model_output, int(timestep), self, sample, noise)
+        elif self.kind == "lms":
+            prev = lms_step(model_output, timestep, self, sample)
         else:
             prev = euler_a_step(model_output, timestep, self, sample, noise)
         return SimpleNamespace(prev_sample=prev)
@@ -163,6 +166,42 @@ def euler_a_step(model_output, timestep, scheduler, sample, noise):
     s_down = (s_to ** 2 - s_up ** 2) ** 0.5
     derivative = (sample - x0) / sigma
     return sample + derivative * (s_down - sigma) + noise * s_up
+
+
+def lms_coefficient(scheduler, order, t, current_order):
+    """diffusers 0.20.2 LMSDiscreteScheduler.get_lms_coefficient: integral of the Lagrange basis polynomial of node
+    sigma[t - current_order] over [sigma[t], sigma[t + 1]] (scipy quad, epsrel 1e-4)."""
+    from scipy import integrate
+    sig = scheduler.sigmas.double().numpy()
+
+    def lms_derivative(tau):
+        prod = 1.0
+        for k in range(order):
+            if current_order == k:
+                continue
+            prod *= (tau - sig[t - k]) / (sig[t - current_order] - sig[t - k])
+        return prod
+
+    return integrate.quad(lms_derivative, sig[t], sig[t + 1], epsrel=1e-4)[0]
+
+
+def lms_step(model_output, timestep, scheduler, sample, order=4):
+    """Linear multistep step (diffusers 0.20.2 LMSDiscreteScheduler.step, the scheduler the reference builds at
+    conceptmod/textsliders/model_util.py:415-423 and eval-scripts/generate_images_sd1.py:51): parity unpinned
+    (third-party arithmetic restated from the published rule)."""
+    i = scheduler._sigma_index(timestep)
+    sigma = scheduler.sigmas[i]
+    if scheduler.prediction_type == "v_prediction":
+        x0 = model_output * (-sigma / (sigma ** 2 + 1) ** 0.5) + (sample / (sigma ** 2 + 1))
+    else:
+        x0 = sample - sigma * model_output
+    derivative = (sample - x0) / sigma
+    scheduler.derivatives.append(derivative)
+    if len(scheduler.derivatives) > order:
+        scheduler.derivatives.pop(0)
+    order = min(i + 1, order, len(scheduler.derivatives))
+    coeffs = [lms_coefficient(scheduler, order, i, cur) for cur in range(order)]
+    return sample + sum(c * d for c, d in zip(coeffs, reversed(scheduler.derivatives)))
 
 
 # ----------------------------------------------------------------------------- sampler helpers (a6, a7)

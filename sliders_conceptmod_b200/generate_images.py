@@ -32,13 +32,7 @@ def denoise_with_slider(unet, network: LoRANetwork, scheduler, text_embeddings: 
         x = scheduler.scale_model_input(torch.cat([latents] * 2), t)
         with network:
             eps = unet(x, t, encoder_hidden_states=text_embeddings, **kw).sample.contiguous()
-        c_x, c_e, c_n = scheduler.step_coefficients(t)
-        z = None
-        if c_n != 0.0:
-            z = torch.randn(latents.shape, generator=noise_generator, device=latents.device, dtype=latents.dtype)
-        latents = ops.cfg_step(latents.contiguous(), eps[:b], eps[b:], z, guidance=guidance_scale, c_x=c_x, c_eps=c_e,
-                               c_noise=c_n)
-        scheduler._advance()
+        latents = scheduler.fused_cfg_step(latents, eps[:b], eps[b:], guidance_scale, t, generator=noise_generator)
     return latents
 
 

@@ -12,7 +12,7 @@ from typing import Literal
 
 import torch
 
-from .schedulers import DDIMScheduler, DDPMScheduler, EulerAncestralDiscreteScheduler
+from .schedulers import DDIMScheduler, DDPMScheduler, EulerAncestralDiscreteScheduler, LMSDiscreteScheduler
 from .unet import UNet2DConditionModel, UNetConfig
 
 AVAILABLE_SCHEDULERS = Literal["ddim", "ddpm", "lms", "euler_a"]
@@ -30,7 +30,7 @@ def create_noise_scheduler(scheduler_name: AVAILABLE_SCHEDULERS = "ddpm",
     if name == "euler_a":
         return EulerAncestralDiscreteScheduler(**kw)
     if name == "lms":
-        raise NotImplementedError("LMSDiscreteScheduler (multistep) is a 'next' row of SURVEY.md §8(f3)")
+        return LMSDiscreteScheduler(**kw)
     raise ValueError(f"Unknown scheduler name: {name}")
 
 

@@ -1,4 +1,4 @@
-"""Noise schedulers of the slider path (DDIM / DDPM / Euler-ancestral) as affine latent updates.
+"""Noise schedulers of the slider path (DDIM / DDPM / Euler-ancestral / LMS) as affine latent updates.
 
 The reference builds diffusers==0.20.2 schedulers (conceptmod/textsliders/model_util.py:388-436) and
 calls `.set_timesteps / .scale_model_input / .step / .add_noise / .init_noise_sigma / .timesteps`
@@ -83,6 +83,18 @@ class SchedulerBase:
 
     def _advance(self):
         pass
+
+    def fused_cfg_step(self, latents, eps_u, eps_c, guidance_scale, timestep, generator=None):
+        """CFG combine (train_util.py:296-300) and `scheduler.step` (train_util.py:324) in ONE launch:
+        x' = c_x x + c_eps (eps_u + g (eps_c - eps_u)) + c_noise z."""
+        c_x, c_eps, c_n = self.step_coefficients(timestep)
+        z = None
+        if c_n != 0.0:
+            z = torch.randn(latents.shape, generator=generator, device=latents.device, dtype=latents.dtype)
+        out = ops.cfg_step(latents.contiguous(), eps_u, eps_c, z, guidance=guidance_scale, c_x=c_x, c_eps=c_eps,
+                           c_noise=c_n)
+        self._advance()
+        return out
 
     # -- the arithmetic -------------------------------------------------------------------------
     def step_coefficients(self, timestep) -> tuple[float, float, float]:
@@ -190,4 +202,69 @@ class EulerAncestralDiscreteScheduler(SchedulerBase):
 
     def add_noise(self, original_samples, noise, timesteps):
         s = float(self._sigmas[self._idx(torch.as_tensor(timesteps).reshape(-1)[0])])
+        return ops.cfg_step(original_samples.contiguous(), None, None, noise.contiguous(), c_x=1.0, c_noise=s)
+
+
+class LMSDiscreteScheduler(EulerAncestralDiscreteScheduler):
+    """Linear multistep (order <= 4) scheduler, the SD-1 inference default of the reference
+    (eval-scripts/generate_images_sd1.py:51; constructor args conceptmod/textsliders/model_util.py:415-423).
+    diffusers==0.20.2 arithmetic restated ('linspace' spacing, same sigma table and `scale_model_input` as Euler-a):
+        derivative_t = (x - x0_t) / sigma_t                      (= the CFG-combined eps for epsilon prediction)
+        x' = x + sum_{i < order} c_i * derivative_{t-i},   c_i = integral over [sigma_t, sigma_{t+1}] of the
+        Lagrange basis polynomial of node sigma_{t-i} among the last `order` sigmas.
+    The update needs the derivative history, so it is not a single affine step: one CFG launch produces the
+    derivative, then one axpy launch of the same kernel per history term (<= 4)."""
+
+    order = 4
+
+    def set_timesteps(self, num_inference_steps: int, device=None):
+        super().set_timesteps(num_inference_steps, device)
+        self._sig32 = self._sigmas.astype(np.float32).astype(np.float64)      # diffusers keeps the table in float32
+        self.derivatives = []
+
+    def lms_coefficient(self, order: int, t: int, current_order: int) -> float:
+        from scipy import integrate
+        sig = self._sig32
+
+        def basis(tau):
+            prod = 1.0
+            for k in range(order):
+                if current_order == k:
+                    continue
+                prod *= (tau - sig[t - k]) / (sig[t - current_order] - sig[t - k])
+            return prod
+
+        return float(integrate.quad(basis, sig[t], sig[t + 1], epsrel=1e-4)[0])
+
+    def step_coefficients(self, timestep):
+        raise NotImplementedError("LMS is a multistep rule: use fused_cfg_step / step (no single affine coefficients; "
+                                  "the CUDA-graph engine supports ddim / ddpm / euler_a)")
+
+    def _derivative(self, latents, eps_u, eps_c, guidance_scale, sigma):
+        if self.config.prediction_type == "epsilon":          # x0 = x - sigma e  ->  derivative = e
+            return ops.cfg_step(None, eps_u, eps_c, None, guidance=guidance_scale)
+        if self.config.prediction_type == "v_prediction":     # x0 = -sigma/sqrt(q) v + x/q  ->  (x - x0)/sigma
+            q = sigma * sigma + 1.0
+            return ops.cfg_step(latents.contiguous(), eps_u, eps_c, None, guidance=guidance_scale, c_x=sigma / q,
+                                c_eps=1.0 / q ** 0.5)
+        raise ValueError(self.config.prediction_type)
+
+    def fused_cfg_step(self, latents, eps_u, eps_c, guidance_scale, timestep, generator=None):
+        i = self._idx(timestep)
+        d = self._derivative(latents, eps_u, eps_c, guidance_scale, float(self._sig32[i]))
+        self.derivatives.append(d)
+        if len(self.derivatives) > self.order:
+            self.derivatives.pop(0)
+        order = min(i + 1, self.order, len(self.derivatives))
+        prev = latents.contiguous()
+        for cur, dv in zip(range(order), reversed(self.derivatives)):
+            prev = ops.cfg_step(prev, dv, dv, None, guidance=0.0, c_x=1.0, c_eps=self.lms_coefficient(order, i, cur))
+        return prev
+
+    def step(self, model_output, timestep, sample, order: int = 4, generator=None, noise=None, return_dict=True, **kw):
+        mo = model_output.contiguous()
+        return _StepOutput(prev_sample=self.fused_cfg_step(sample, mo, mo, 0.0, timestep))
+
+    def add_noise(self, original_samples, noise, timesteps):
+        s = float(self._sig32[self._idx(torch.as_tensor(timesteps).reshape(-1)[0])])
         return ops.cfg_step(original_samples.contiguous(), None, None, noise.contiguous(), c_x=1.0, c_noise=s)

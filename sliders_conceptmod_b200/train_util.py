@@ -66,23 +66,17 @@ def predict_noise(unet, scheduler, timestep, latents, text_embeddings, guidance_
 
 
 def _fused_cfg_and_step(scheduler, noise_pred, timestep, latents, guidance_scale):
-    """a6 + a7 in one launch: CFG combine and x' = c_x x + c_eps eps + c_noise z."""
-    c_x, c_eps, c_n = scheduler.step_coefficients(timestep)
-    z = None
-    if c_n != 0.0:
-        z = torch.randn(latents.shape, device=latents.device, dtype=latents.dtype)
+    """a6 + a7 fused: CFG combine and the scheduler's latent update (one launch for the affine rules
+    x' = c_x x + c_eps eps + c_noise z; LMS adds one axpy launch per history term)."""
     noise_pred = noise_pred.contiguous()
     half = noise_pred.shape[0] // 2
-    out = ops.cfg_step(latents.contiguous(), noise_pred[:half], noise_pred[half:], z, guidance=guidance_scale,
-                       c_x=c_x, c_eps=c_eps, c_noise=c_n)
-    scheduler._advance()
-    return out
+    return scheduler.fused_cfg_step(latents, noise_pred[:half], noise_pred[half:], guidance_scale, timestep)
 
 
 @torch.no_grad()
 def diffusion(unet, scheduler, latents, text_embeddings, total_timesteps: int = 1000, start_timesteps=0, **kwargs):
     guidance_scale = kwargs.get("guidance_scale", 7.5)
-    fused = hasattr(scheduler, "step_coefficients")
+    fused = hasattr(scheduler, "fused_cfg_step")
     for timestep in scheduler.timesteps[start_timesteps:total_timesteps]:
         if fused:
             x = _scaled_cfg_input(scheduler, latents, timestep)
@@ -107,7 +101,7 @@ def predict_noise_xl(unet, scheduler, timestep, latents, text_embeddings, add_te
 @torch.no_grad()
 def diffusion_xl(unet, scheduler, latents, text_embeddings, add_text_embeddings, add_time_ids,
                  guidance_scale: float = 1.0, total_timesteps: int = 1000, start_timesteps=0):
-    fused = hasattr(scheduler, "step_coefficients")
+    fused = hasattr(scheduler, "fused_cfg_step")
     added = {"text_embeds": add_text_embeddings, "time_ids": add_time_ids}
     for timestep in scheduler.timesteps[start_timesteps:total_timesteps]:
         if fused:

@@ -72,3 +72,40 @@ def test_adamw_flat_and_clip(dtype):
     c = ops.clip_coef(g, 0.2, 0.5)
     ref = min(1.0, 0.2 / (g.norm().item() * 0.5 + 1e-6)) * 0.5
     assert abs(c.item() - ref) <= 1e-5 * ref
+
+
+@pytest.mark.parametrize("pred", ["epsilon", "v_prediction"])
+def test_lms_trajectory_matches_oracle(pred):
+    """LMSDiscreteScheduler (model_util.py:415-423; SD-1 inference default, generate_images_sd1.py:51): 10 fused
+    CFG + multistep updates on the device against the oracle's restatement of the diffusers rule on the CPU (fp32;
+    the model output is a fixed function of the latents so that errors would compound)."""
+    import sys
+    from pathlib import Path
+    sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+    from oracle import slider_oracle as O
+    from sliders_conceptmod_b200 import model_util
+    s = model_util.create_noise_scheduler("lms", prediction_type=pred)
+    o = O.OracleScheduler("lms", prediction_type=pred)
+    s.set_timesteps(10); o.set_timesteps(10)
+    g = torch.Generator().manual_seed(3)
+    x_c = torch.randn(2, 4, 16, 16, generator=g) * float(o.init_noise_sigma)
+    w_u, w_c = torch.randn(4, 4, generator=g) * 0.3, torch.randn(4, 4, generator=g) * 0.3
+    x_d = x_c.cuda()
+    guidance = 3.0
+
+    def model(x, w):      # channel mix, bounded: stands in for the UNet
+        return torch.tanh(torch.einsum("oc,bchw->bohw", w.to(x.device), x))
+
+    for t in s.timesteps:
+        xin_c = o.scale_model_input(x_c, t)
+        eu, ec = model(xin_c, w_u), model(xin_c, w_c)
+        x_c = o.step(eu + guidance * (ec - eu), t, x_c).prev_sample
+        xin_d = s.scale_model_input(x_d, t)
+        x_d = s.fused_cfg_step(x_d, model(xin_d, w_u).contiguous(), model(xin_d, w_c).contiguous(), guidance, t)
+    torch.cuda.synchronize()
+    err = (x_d.cpu() - x_c).abs().max().item()
+    assert err <= 2e-4 * x_c.abs().max().item(), err
+    # the diffusers-style surface: step(model_output) on an already combined prediction
+    s.set_timesteps(10)
+    y = s.step(torch.ones(1, 4, 8, 8, device="cuda"), s.timesteps[0], torch.zeros(1, 4, 8, 8, device="cuda")).prev_sample
+    assert y.shape == (1, 4, 8, 8)

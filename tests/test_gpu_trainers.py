@@ -193,7 +193,7 @@ def test_image_slider_train_entry_runs_and_saves(tmp_path):
     assert set(sd) == set(network.state_dict()) and all(v.dtype == torch.bfloat16 for v in sd.values())
 
 
-@pytest.mark.parametrize("scheduler,steps", [("ddim", 8), ("euler_a", 6)])
+@pytest.mark.parametrize("scheduler,steps", [("ddim", 8), ("euler_a", 6), ("lms", 8)])
 def test_inference_sweep_matches_oracle(scheduler, steps):
     from helpers import build_pair
     from oracle import slider_oracle

@@ -169,9 +169,29 @@ def test_scheduler_coefficients_match_oracle_steps(kind, pred):
         assert torch.allclose(xin, x * s.input_scale(t), rtol=1e-6, atol=1e-6)
 
 
-def test_lms_is_flagged_next_row():
+def test_lms_scheduler_tables_and_coefficients():
+    """LMS (model_util.py:415-423): sigma table / timesteps / input scale equal the oracle restatement, order-1
+    coefficient is the Euler step sigma[t+1] - sigma[t], the order-k coefficients sum to it (Lagrange bases sum to 1),
+    and they match the oracle's quadrature."""
+    s = model_util.create_noise_scheduler("lms")
+    o = O.OracleScheduler("lms")
+    for n in (30, 50):
+        s.set_timesteps(n); o.set_timesteps(n)
+        assert torch.allclose(s.timesteps, o.timesteps) and torch.allclose(s.sigmas, o.sigmas)
+        assert abs(float(s.init_noise_sigma) - float(o.init_noise_sigma)) < 1e-6
+        sig = s.sigmas.double()
+        for t in (0, 1, 5, n - 1):
+            assert abs(s.lms_coefficient(1, t, 0) - float(sig[t + 1] - sig[t])) < 1e-4 * abs(float(sig[t]))
+            order = min(t + 1, 4)
+            cs = [s.lms_coefficient(order, t, c) for c in range(order)]
+            assert abs(sum(cs) - float(sig[t + 1] - sig[t])) < 1e-3 * abs(float(sig[t]))
+            for c in range(order):
+                assert abs(cs[c] - O.lms_coefficient(o, order, t, c)) < 1e-6 * max(1.0, abs(cs[c]))
+        x = torch.randn(1, 4, 8, 8, dtype=torch.float64)
+        t = s.timesteps[3]
+        assert torch.allclose(o.scale_model_input(x, t), x * s.input_scale(t), rtol=1e-6, atol=1e-6)
     with pytest.raises(NotImplementedError):
-        model_util.create_noise_scheduler("lms")
+        s.step_coefficients(s.timesteps[0])         # multistep: no single affine rule (CUDA-graph engine: ddim/ddpm/euler_a)
     with pytest.raises(ValueError):
         model_util.create_noise_scheduler("nope")
 
