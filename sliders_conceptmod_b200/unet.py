@@ -159,8 +159,9 @@ def fused_linear(mod: nn.Module, x: torch.Tensor, residual: torch.Tensor | None 
     """`mod(x)` (+ `residual`) for an nn.Linear on [..., K] or a 1x1 nn.Conv2d on [B,C,H,W].
 
     On no-grad CUDA forwards every such projection of the UNet runs in libslider's tcgen05 GEMM: LoRA-wrapped modules
-    through their patched forward (adapter fused); frozen un-wrapped ones (attn2, feed-forward, proj_in/out — SURVEY
-    8 f1) stay on cuBLAS unless SLIDER_ENABLE=plain routes them through the same kernel's plain path.  With `residual` the sum is formed by the kernel's store IN PLACE of
+    through their patched forward (adapter fused); frozen un-wrapped 1x1 convolutions (proj_in / proj_out) through the
+    same kernel's plain path; frozen un-wrapped nn.Linear (attn2, feed-forward — SURVEY 8 f1) stay on cuBLAS unless
+    SLIDER_ENABLE=plain (all) / plainres (those with a residual).  With `residual` the sum is formed by the kernel's store IN PLACE of
     `residual` (TMA reduce-add) instead of an elementwise kernel — callers pass a `residual` nobody else reads
     afterwards.  Everything else (CPU oracle, grad-recording forward) is the plain PyTorch expression."""
     fused = _no_grad_cuda(x, residual) and x.dtype == mod.weight.dtype
@@ -172,11 +173,13 @@ def fused_linear(mod: nn.Module, x: torch.Tensor, residual: torch.Tensor | None 
             if out is not None:
                 return out
         fused = False
-    # frozen un-wrapped projections: cuBLAS is measured ~2.5 % faster per denoise forward than the plain path of the
-    # fused kernel on these small shapes (tools/ab_fusions.sh), so this routing is opt-in: SLIDER_ENABLE=plain
-    if fused and lora is None and "plain" in _ENABLED and not mod.weight.requires_grad:
+    # frozen un-wrapped projections.  nn.Linear: cuBLAS (bias in its epilogue) is measured faster per denoise forward
+    # than the plain path of the fused kernel on these small shapes (tools/ab_fusions.sh), so that routing is opt-in
+    # (SLIDER_ENABLE=plain).  1x1 nn.Conv2d (proj_in / proj_out of SD 1.x): cuDNN runs a GEMM plus a separate bias
+    # kernel, and the residual is a third launch — the plain path does all three in one (SLIDER_DISABLE=plainconv).
+    if fused and lora is None and not mod.weight.requires_grad:
         res = residual if "residual" not in _DISABLED else None
-        if isinstance(mod, nn.Linear):
+        if isinstance(mod, nn.Linear) and ("plain" in _ENABLED or (res is not None and "plainres" in _ENABLED)):
             K, N = mod.in_features, mod.out_features
             x2 = x.reshape(-1, K)
             ok = x2.shape[0] > 16 and K % 8 == 0 and N % 8 == 0 and (res is None or res.is_contiguous())
@@ -187,7 +190,8 @@ def fused_linear(mod: nn.Module, x: torch.Tensor, residual: torch.Tensor | None 
                                         residual=None if res is None else res.view(-1, N))
                 y = y.view(*x.shape[:-1], N)
                 return y if (res is not None or residual is None) else residual + y
-        elif isinstance(mod, nn.Conv2d) and mod.kernel_size == (1, 1) and mod.stride == (1, 1) and mod.groups == 1:
+        elif (isinstance(mod, nn.Conv2d) and mod.kernel_size == (1, 1) and mod.stride == (1, 1) and mod.groups == 1
+              and ("plain" in _ENABLED or "plainconv" not in _DISABLED)):
             K, N = mod.in_channels, mod.out_channels
             rn = None if res is None else res.permute(0, 2, 3, 1)
             if K % 8 == 0 and N % 8 == 0 and (rn is None or rn.is_contiguous()):
