@@ -316,6 +316,210 @@ gn_cluster_kernel(T* __restrict__ y, const T* __restrict__ x, const T* __restric
   ptx::cluster_wait();
 }
 
+// ---- single-launch form: one CTA (or a small cluster) per (image, group set) --------------------------------------------
+// The data of GP adjacent groups is a [HW][GP * cpg] slab (rows of GP * cpg * sizeof(T) bytes at a stride of
+// C * sizeof(T)); GP = 1, 2, 4 or 8 is the smallest count that makes a row a whole number of 16-byte vectors (SD 1.x:
+// 320 channels / 32 groups = 20-byte groups -> GP = 4, 80-byte rows).  k = 1 .. 8 CTAs (one cluster) split the rows of a
+// slab so that each holds a few tens of KB of it in shared memory:
+//   1. rows -> shared memory, 16-byte vectors (x is read from global memory ONCE);
+//   2. statistics from the shared copy by 32-bit words: the block size is a multiple of the words per row, so a thread
+//      always sees the same word of a row -> one group, two channels, its {sum, sum of squares} stay in registers;
+//      one warp per group then adds the per-thread pairs in a fixed order (fp64);
+//   3. k > 1: the per-CTA pairs of the peers over distributed shared memory, in rank order (deterministic);
+//   4. scale / shift of the thread's 16-byte column in registers, normalised rows written from the shared copy.
+// No partial-sum workspace, no second launch, no second read: the two-kernel form costs ~13.5 us per GroupNorm in the
+// denoise forward whatever the size (launch + dependent global-load latency), 17 % of it.
+constexpr int GN_GROUP_THREADS = 512;
+constexpr int GN_GROUP_MAXGP = 8;
+
+template <typename T> struct Word;      // the elements of one 32-bit word
+template <> struct Word<__nv_bfloat16> {
+  static constexpr int N = 2;
+  __device__ static inline void unpack(uint32_t w, float (&f)[2]) {
+    f[0] = __uint_as_float(w << 16);
+    f[1] = __uint_as_float(w & 0xffff0000u);
+  }
+  __device__ static inline uint32_t pack(const float (&f)[2]) {
+    const __nv_bfloat162 h = __floats2bfloat162_rn(f[0], f[1]);
+    return *reinterpret_cast<const uint32_t*>(&h);
+  }
+};
+template <> struct Word<float> {
+  static constexpr int N = 1;
+  __device__ static inline void unpack(uint32_t w, float (&f)[2]) { f[0] = __uint_as_float(w); f[1] = 0.f; }
+  __device__ static inline uint32_t pack(const float (&f)[2]) { return __float_as_uint(f[0]); }
+};
+
+struct GnGroupArgs {
+  int k;        // CTAs per slab (cluster size)
+  int gp;       // groups per slab
+  int wr;       // 32-bit words per slab row
+  int rows;     // rows (pixels) per CTA
+  unsigned long long* trace;   // profiling aid (slider_debug_gn_trace): 8 globaltimer stamps per CTA, or nullptr
+};
+
+__device__ __forceinline__ void gn_stamp(unsigned long long* trace, int slot) {
+  if (trace != nullptr && threadIdx.x == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    trace[((size_t)blockIdx.y * gridDim.x + blockIdx.x) * 8 + slot] = t;
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(GN_GROUP_THREADS)
+gn_group_kernel(T* __restrict__ y, const T* __restrict__ x, const T* __restrict__ chan_add,
+                const T* __restrict__ gamma, const T* __restrict__ beta, const GnParams p, const GnGroupArgs ga,
+                float* __restrict__ stats_out) {
+  constexpr int EW = Word<T>::N;
+  extern __shared__ __align__(16) unsigned char gn_gsm[];
+  const int tid = threadIdx.x, nt = blockDim.x, b = blockIdx.y;
+  const int wpr = ga.wr >> 2;                                         // 16-byte vectors per row
+  const int nch = ga.gp * p.cpg;                                      // channels of the slab
+  const int total = ga.rows * wpr;
+  uint4* slab = reinterpret_cast<uint4*>(gn_gsm);
+  float2* s_part = reinterpret_cast<float2*>(gn_gsm + (size_t)total * 16);       // [nt] per-thread pairs
+  double* s_cta = reinterpret_cast<double*>(s_part + GN_GROUP_THREADS);          // [gp][2] this CTA's sums (read by the peers)
+  float* s_sc = reinterpret_cast<float*>(s_cta + 2 * GN_GROUP_MAXGP);            // [nch] gamma, then scale
+  float* s_sh = s_sc + nch;                                                      // [nch] beta, then shift
+  float* s_add = s_sh + nch;                                                     // [nch]
+  float* s_stat = s_add + nch;                                                   // [gp][2] mean, rstd
+  const int set = blockIdx.x / ga.k;
+  const int part = ga.k > 1 ? (int)ptx::cluster_ctarank() : 0;
+  const int c0 = set * nch;
+  pdl_trigger();
+  gn_stamp(ga.trace, 0);
+  for (int c = tid; c < nch; c += nt) {          // frozen parameters: not produced by the previous kernel
+    s_sc[c] = gamma ? Elem<T>::to_f(gamma[c0 + c]) : 1.f;
+    s_sh[c] = beta ? Elem<T>::to_f(beta[c0 + c]) : 0.f;
+  }
+  pdl_wait();
+  gn_stamp(ga.trace, 1);
+  // 1. rows -> shared memory
+  const size_t rstride = (size_t)p.C * sizeof(T) / 16;                // row stride in vectors
+  const size_t base = (((size_t)b * p.HW + (size_t)part * ga.rows) * p.C + c0) * sizeof(T) / 16;
+  const uint4* xg = reinterpret_cast<const uint4*>(x) + base;
+  uint4* yg = reinterpret_cast<uint4*>(y) + base;
+  const int vpos = tid % wpr, vrow = tid / wpr, vstep = nt / wpr;     // nt % wpr == 0: a thread stays in one column
+  {
+    int i = tid, r = vrow;
+#pragma unroll 8
+    for (; i < total; i += nt, r += vstep) slab[i] = xg[(size_t)r * rstride + vpos];
+  }
+  for (int c = tid; c < nch; c += nt)
+    s_add[c] = chan_add ? Elem<T>::to_f(chan_add[(size_t)b * p.C + c0 + c]) : 0.f;
+  __syncthreads();
+  gn_stamp(ga.trace, 2);
+  // 2. statistics by 32-bit words (nt % wr == 0: word `tid % wr` of every row this thread visits)
+  const int warp = tid >> 5, lane = tid & 31, nwarps = nt >> 5;
+  {
+    const int wpos = tid % ga.wr;
+    const int mygi = wpos / (ga.wr / ga.gp);                          // the group of that word
+    const float a0 = s_add[wpos * EW], a1 = EW > 1 ? s_add[wpos * EW + EW - 1] : 0.f;
+    const uint32_t* sw = reinterpret_cast<const uint32_t*>(slab);
+    const int words = ga.rows * ga.wr;
+    float sum = 0.f, sq = 0.f;
+#pragma unroll 8
+    for (int i = tid; i < words; i += nt) {
+      float f[2];
+      Word<T>::unpack(sw[i], f);
+      const float z0 = f[0] + a0;
+      sum += z0; sq = fmaf(z0, z0, sq);
+      if (EW > 1) { const float z1 = f[1] + a1; sum += z1; sq = fmaf(z1, z1, sq); }
+    }
+    // per-warp sums of every group (fixed shuffle tree), then one warp per group over the warps (fp64)
+    for (int gi = 0; gi < ga.gp; ++gi) {
+      const float a = warp_sum(mygi == gi ? sum : 0.f), q = warp_sum(mygi == gi ? sq : 0.f);
+      if (lane == 0) s_part[warp * GN_GROUP_MAXGP + gi] = make_float2(a, q);
+    }
+  }
+  __syncthreads();
+  if (warp < ga.gp) {
+    double a = 0.0, q = 0.0;
+    if (lane < nwarps) { const float2 v = s_part[lane * GN_GROUP_MAXGP + warp]; a = (double)v.x; q = (double)v.y; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      a += __shfl_xor_sync(0xffffffffu, a, o);
+      q += __shfl_xor_sync(0xffffffffu, q, o);
+    }
+    if (lane == 0) { s_cta[2 * warp] = a; s_cta[2 * warp + 1] = q; }
+  }
+  // 3. the peers' pairs: warp gi, lane r reads the pair of peer r; fixed shuffle tree over the ranks
+  gn_stamp(ga.trace, 3);
+  if (ga.k > 1) { ptx::cluster_arrive(); ptx::cluster_wait(); } else { __syncthreads(); }
+  gn_stamp(ga.trace, 4);
+  if (warp < ga.gp) {
+    double a = 0.0, q = 0.0;
+    if (ga.k > 1) {
+      if (lane < ga.k) {
+        const uint32_t peer = ptx::mapa(ptx::smem_u32(s_cta + 2 * warp), (uint32_t)lane);
+        asm volatile("ld.shared::cluster.v2.f64 {%0, %1}, [%2];" : "=d"(a), "=d"(q) : "r"(peer));
+      }
+#pragma unroll
+      for (int o = 8; o > 0; o >>= 1) {
+        a += __shfl_xor_sync(0xffffffffu, a, o);
+        q += __shfl_xor_sync(0xffffffffu, q, o);
+      }
+    } else {
+      a = s_cta[2 * warp]; q = s_cta[2 * warp + 1];
+    }
+    if (lane == 0) {
+      const double n = (double)p.cpg * (double)p.HW;
+      const double mean = a / n;
+      double var = q / n - mean * mean;
+      if (var < 0.0) var = 0.0;
+      const float mf = (float)mean, rf = rsqrtf((float)var + p.eps);
+      s_stat[2 * warp] = mf; s_stat[2 * warp + 1] = rf;
+      if (stats_out != nullptr && part == 0) {               // saved for the backward pass: [B][G]{mean, rstd}
+        const int g = set * ga.gp + warp;
+        stats_out[((size_t)b * p.G + g) * 2] = mf;
+        stats_out[((size_t)b * p.G + g) * 2 + 1] = rf;
+      }
+    }
+  }
+  if (ga.k > 1) ptx::cluster_arrive();    // the peers may still read s_cta: arrive now, wait before exit
+  __syncthreads();
+  gn_stamp(ga.trace, 5);
+  // 4. normalise from the shared copy; the thread's column never changes: its scale / shift stay in registers
+  {
+    constexpr int NE = 4 * EW;          // elements per 16-byte vector
+    float sc[NE], sh[NE];
+    {
+      int c = vpos * NE, gi = c / p.cpg, rem = c - gi * p.cpg;
+#pragma unroll
+      for (int e = 0; e < NE; ++e, ++c) {
+        const float mean = s_stat[2 * gi], rstd = s_stat[2 * gi + 1];
+        sc[e] = rstd * s_sc[c];
+        sh[e] = fmaf(s_add[c] - mean, sc[e], s_sh[c]);
+        if (++rem == p.cpg) { rem = 0; ++gi; }
+      }
+    }
+    int i = tid, r = vrow;
+#pragma unroll 2
+    for (; i < total; i += nt, r += vstep) {
+      const uint4 v = slab[i];
+      const uint32_t in[4] = {v.x, v.y, v.z, v.w};
+      uint32_t out[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float f[2], u[2] = {0.f, 0.f};
+        Word<T>::unpack(in[j], f);
+#pragma unroll
+        for (int e = 0; e < EW; ++e) {
+          float t = fmaf(f[e], sc[j * EW + e], sh[j * EW + e]);
+          if (p.silu) t = __fdividef(t, 1.f + __expf(-t));
+          u[e] = t;
+        }
+        out[j] = Word<T>::pack(u);
+      }
+      yg[(size_t)r * rstride + vpos] = make_uint4(out[0], out[1], out[2], out[3]);
+    }
+  }
+  gn_stamp(ga.trace, 6);
+  if (ga.k > 1) ptx::cluster_wait();
+  gn_stamp(ga.trace, 7);
+}
+
 // thread-block cluster size of the single-launch form (SLIDER_GN_CLUSTER / slider_debug_gn_cluster: 0 = two-kernel
 // form, 8, 16).  Opt-in: measured SLOWER on B200 -- 8 or 16 CTAs per image cannot pull the 2.6 MB of a 64x64x320 image
 // fast enough (denoise forward 4.97 ms two-kernel, 5.29 ms at 16, 5.84 ms at 8; profiles/r01_ab_gn_cluster.txt).
@@ -349,9 +553,74 @@ static int groupnorm_cluster_impl(void* y, const void* x, const void* chan_add, 
   return post_launch("gn_cluster_kernel");
 }
 
+// per-(image, group set) single-launch form: on by default (SLIDER_GN_GROUP=0 / slider_debug_gn_group(0, 0): two-kernel
+// form); SLIDER_GN_GROUP_KB: the slab bytes one CTA may hold before the slab is split over a larger cluster
+static int g_gn_group = [] { const char* e = getenv("SLIDER_GN_GROUP"); return e ? atoi(e) : 1; }();
+static int g_gn_group_kb = [] { const char* e = getenv("SLIDER_GN_GROUP_KB"); const int v = e ? atoi(e) : 24; return v < 4 ? 4 : (v > 128 ? 128 : v); }();
+
+static unsigned long long* g_gn_trace = nullptr;
+
+struct GnGroupPlan { GnGroupArgs a; int threads; size_t smem; };
+
+template <typename T>
+static bool gn_group_plan(const GnParams& p, GnGroupPlan* gp) {
+  if (((size_t)p.cpg * sizeof(T)) % 4 != 0) return false;      // a 32-bit word must not straddle two groups
+  int g = 1;
+  while (g <= GN_GROUP_MAXGP && (((size_t)g * p.cpg * sizeof(T)) % 16 != 0 || p.G % g != 0)) g *= 2;
+  if (g > GN_GROUP_MAXGP) return false;
+  const size_t seg = (size_t)g * p.cpg * sizeof(T);
+  const int wr = (int)(seg / 4);
+  int l = wr;                                   // lcm(32, wr): block sizes that keep a thread on one word of a row
+  while (l % 32 != 0) l += wr;
+  if (l > GN_GROUP_THREADS) return false;
+  const size_t slab = (size_t)p.HW * seg;
+  int k = 1;
+  while (k < 8 && slab / k > (size_t)g_gn_group_kb * 1024) k *= 2;     // clusters of 16 start in waves (measured)
+  while (k > 1 && p.HW % k != 0) k /= 2;
+  if (slab / k > 160 * 1024) return false;
+  gp->a.k = k; gp->a.gp = g; gp->a.wr = wr; gp->a.rows = p.HW / k; gp->a.trace = g_gn_trace;
+  gp->threads = (GN_GROUP_THREADS / l) * l;
+  gp->smem = (size_t)gp->a.rows * seg + GN_GROUP_THREADS * sizeof(float2) + 2 * GN_GROUP_MAXGP * sizeof(double) +
+             ((size_t)3 * g * p.cpg + 2 * GN_GROUP_MAXGP) * sizeof(float);
+  return true;
+}
+
+template <typename T>
+static int gn_group_launch(void* y, const void* x, const void* chan_add, const void* gamma, const void* beta,
+                           const GnParams& p, const GnGroupPlan& gp, cudaStream_t st, float* stats_out) {
+  static thread_local bool configured = false;
+  if (!configured) {
+    SLIDER_CUDA(cudaFuncSetAttribute(gn_group_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 180 * 1024));
+    configured = true;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((p.G / gp.a.gp) * gp.a.k, p.B); cfg.blockDim = dim3(gp.threads); cfg.dynamicSmemBytes = gp.smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (gp.a.k > 1) {
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = (unsigned)gp.a.k; attr[na].val.clusterDim.y = 1; attr[na].val.clusterDim.z = 1;
+    ++na;
+  }
+  if (pdl_enabled()) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = na;
+  cudaLaunchKernelEx(&cfg, gn_group_kernel<T>, (T*)y, (const T*)x, (const T*)chan_add, (const T*)gamma, (const T*)beta, p,
+                     gp.a, stats_out);
+  return post_launch("gn_group_kernel");
+}
+
 template <typename T>
 static int groupnorm_impl(void* y, const void* x, const void* chan_add, const void* gamma, const void* beta,
                           float* ws, GnParams p, cudaStream_t st, float* stats_out = nullptr) {
+  GnGroupPlan gp;
+  if (g_gn_group && g_gn_cluster < 2 && p.B <= 65535 && gn_group_plan<T>(p, &gp))
+    return gn_group_launch<T>(y, x, chan_add, gamma, beta, p, gp, st, stats_out);
   if (g_gn_cluster >= 2 && ((size_t)p.PL * p.C * 2 + (size_t)p.G * 4 + (size_t)p.C * 2) * sizeof(float) + 16 <= 96 * 1024)
     return groupnorm_cluster_impl<T>(y, x, chan_add, gamma, beta, p, st, stats_out);
   // workspace: per-chunk partial sums [B][chunks][G][2]
@@ -639,6 +908,12 @@ extern "C" {
 
 int slider_debug_gn_variant(int v) { g_gn_variant = v; return 0; }
 int slider_debug_gn_cluster(int cs) { g_gn_cluster = (cs == 8 || cs == 16) ? cs : 0; return 0; }
+int slider_debug_gn_trace(void* buf) { g_gn_trace = (unsigned long long*)buf; return 0; }
+int slider_debug_gn_group(int on, int slab_kb) {
+  g_gn_group = on;
+  if (slab_kb >= 4 && slab_kb <= 128) g_gn_group_kb = slab_kb;
+  return 0;
+}
 
 size_t slider_groupnorm_workspace_bytes(int batch, int groups) {
   // tickets + stats + partials (batch * chunks <= 2 * SMs + 2 * batch)

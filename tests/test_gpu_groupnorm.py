@@ -95,3 +95,35 @@ def test_groupnorm_cluster_form_matches_two_kernel_form(cs):
         finally:
             fn(0)
         assert (y.float() - ref.float()).abs().max().item() <= 2e-2 * ref.float().abs().max().item()
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("slab_kb", [4, 16, 48, 128])
+def test_groupnorm_group_form_matches_two_kernel_form(dtype, slab_kb):
+    """The default single-launch form (one CTA or a cluster of 2 / 4 / 8 per (image, group), slider_debug_gn_group) vs
+    the two-kernel form it replaces, over cluster sizes (slab_kb = bytes of a group one CTA may hold) and the saved
+    statistics of the training form."""
+    import ctypes
+    from sliders_conceptmod_b200 import ops, _lib
+    fn = _lib.lib().slider_debug_gn_group
+    fn.argtypes, fn.restype = [ctypes.c_int, ctypes.c_int], ctypes.c_int
+    gen = torch.Generator(device="cuda").manual_seed(13)
+    tol = 2e-2 if dtype == torch.bfloat16 else 2e-5
+    for (B, H, W, C, G) in [(2, 64, 64, 320, 32), (2, 64, 64, 960, 32), (2, 32, 32, 1920, 32), (2, 8, 8, 1280, 32),
+                            (3, 5, 7, 64, 8), (1, 6, 6, 48, 8), (2, 16, 16, 2560, 32), (1, 4, 4, 40, 8), (2, 128, 128, 320, 32)]:
+        x = (torch.randn(B, H, W, C, device="cuda", generator=gen) * 1.7 + 0.3).to(dtype)
+        gamma = (1 + 0.2 * torch.randn(C, device="cuda", generator=gen)).to(dtype)
+        beta = (0.1 * torch.randn(C, device="cuda", generator=gen)).to(dtype)
+        add = torch.randn(B, C, device="cuda", generator=gen).to(dtype)
+        try:
+            fn(0, 0)
+            ref, ref_stats = ops.groupnorm_nhwc(x, G, gamma, beta, 1e-5, True, add, want_stats=True)
+            fn(1, slab_kb)
+            y, stats = ops.groupnorm_nhwc(x, G, gamma, beta, 1e-5, True, add, want_stats=True)
+            y2 = ops.groupnorm_nhwc(x, G, gamma, beta, 1e-5, True, add)
+            torch.cuda.synchronize()
+        finally:
+            fn(1, 48)
+        assert torch.equal(y, y2)       # deterministic
+        assert (y.float() - ref.float()).abs().max().item() <= tol * ref.float().abs().max().item()
+        assert (stats - ref_stats).abs().max().item() <= 1e-4 * max(1.0, ref_stats.abs().max().item())
