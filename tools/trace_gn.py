@@ -12,7 +12,7 @@ from sliders_conceptmod_b200 import _lib, ops
 h = _lib.lib()
 h.slider_debug_gn_trace.argtypes = [ctypes.c_void_p]
 h.slider_debug_gn_group.argtypes = [ctypes.c_int, ctypes.c_int]
-NAMES = ["params", "pdl_wait", "load+sync", "stats+reduce", "cluster/sync", "dsmem+tables", "apply+store", "cluster_wait"]
+NAMES = ["params", "pdl_wait", "load+stats", "reduce", "cluster/sync", "dsmem+stat", "apply+store", "cluster_wait"]
 kb = int(sys.argv[1]) if len(sys.argv) > 1 else 24
 h.slider_debug_gn_group(1, kb)
 for shape in [(2, 64, 64, 320), (2, 64, 64, 960), (2, 32, 32, 640), (2, 16, 16, 1280), (2, 8, 8, 2560)]:
