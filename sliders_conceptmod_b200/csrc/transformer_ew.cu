@@ -8,10 +8,112 @@ template <typename T> struct RowVec {
   static constexpr int V = Elem<T>::kVec;
 };
 
-// ---- LayerNorm over the last dimension: one warp per row ---------------------------------------------
-template <typename T>
+// ---- LayerNorm over the last dimension: one warp per row, the row in registers ---------------------------------------
+// Rows of up to 32 * MAXV 16-byte vectors (every row of the UNets of this path): gamma / beta are frozen parameters and
+// are fetched BEFORE the programmatic-dependent-launch wait, x is read once, and the two reductions and the affine
+// pass work on registers — one exposed global-load latency instead of three.  Same summation order as the streaming
+// form below, so the results are bit-identical.
+template <typename T> struct VecIO;
+template <> struct VecIO<__nv_bfloat16> {
+  __device__ static inline void unpack(const uint4& t, float (&v)[8]) {
+    const uint32_t w[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { v[2 * i] = __uint_as_float(w[i] << 16); v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u); }
+  }
+  __device__ static inline uint4 pack(const float (&v)[8]) {
+    uint32_t w[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+      w[i] = *reinterpret_cast<const uint32_t*>(&h);
+    }
+    return make_uint4(w[0], w[1], w[2], w[3]);
+  }
+};
+template <> struct VecIO<float> {
+  __device__ static inline void unpack(const uint4& t, float (&v)[4]) {
+    v[0] = __uint_as_float(t.x); v[1] = __uint_as_float(t.y); v[2] = __uint_as_float(t.z); v[3] = __uint_as_float(t.w);
+  }
+  __device__ static inline uint4 pack(const float (&v)[4]) {
+    return make_uint4(__float_as_uint(v[0]), __float_as_uint(v[1]), __float_as_uint(v[2]), __float_as_uint(v[3]));
+  }
+};
+
+template <typename T, int MAXV>
 __global__ void __launch_bounds__(256)
 layernorm_kernel(T* __restrict__ y, const T* __restrict__ x, const T* __restrict__ gamma,
+                 const T* __restrict__ beta, int64_t rows, int C, float eps) {
+  pdl_trigger();
+  constexpr int V = Elem<T>::kVec;
+  const int lane = threadIdx.x & 31;
+  const int nv = C / V;
+  uint4 gp[MAXV], bp[MAXV], xp[MAXV];
+#pragma unroll
+  for (int j = 0; j < MAXV; ++j) {
+    const int v = lane + 32 * j;
+    gp[j] = make_uint4(0, 0, 0, 0); bp[j] = make_uint4(0, 0, 0, 0);
+    if (v < nv) {
+      if (gamma) gp[j] = reinterpret_cast<const uint4*>(gamma)[v];
+      if (beta) bp[j] = reinterpret_cast<const uint4*>(beta)[v];
+    }
+  }
+  pdl_wait();
+  const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const uint4* xr = reinterpret_cast<const uint4*>(x + row * C);
+  uint4* yr = reinterpret_cast<uint4*>(y + row * C);
+#pragma unroll
+  for (int j = 0; j < MAXV; ++j) {
+    const int v = lane + 32 * j;
+    xp[j] = make_uint4(0, 0, 0, 0);
+    if (v < nv) xp[j] = xr[v];
+  }
+  float sum = 0.f;
+#pragma unroll
+  for (int j = 0; j < MAXV; ++j) {
+    if (lane + 32 * j < nv) {
+      float xv[V];
+      VecIO<T>::unpack(xp[j], xv);
+#pragma unroll
+      for (int k = 0; k < V; ++k) sum += xv[k];
+    }
+  }
+  const float mean = warp_sum(sum) / (float)C;
+  float sq = 0.f;
+#pragma unroll
+  for (int j = 0; j < MAXV; ++j) {
+    if (lane + 32 * j < nv) {
+      float xv[V];
+      VecIO<T>::unpack(xp[j], xv);
+#pragma unroll
+      for (int k = 0; k < V; ++k) { const float d = xv[k] - mean; sq = fmaf(d, d, sq); }
+    }
+  }
+  const float rstd = rsqrtf(warp_sum(sq) / (float)C + eps);
+#pragma unroll
+  for (int j = 0; j < MAXV; ++j) {
+    const int v = lane + 32 * j;
+    if (v < nv) {
+      float xv[V], gv[V], bv[V], o[V];
+      VecIO<T>::unpack(xp[j], xv);
+      VecIO<T>::unpack(gp[j], gv);
+      VecIO<T>::unpack(bp[j], bv);
+#pragma unroll
+      for (int k = 0; k < V; ++k) {
+        float u = (xv[k] - mean) * rstd;
+        if (gamma) u *= gv[k];
+        if (beta) u += bv[k];
+        o[k] = u;
+      }
+      yr[v] = VecIO<T>::pack(o);
+    }
+  }
+}
+
+// ---- LayerNorm over the last dimension: one warp per row, rows of any length (three passes, the later ones hit L1) ----
+template <typename T>
+__global__ void __launch_bounds__(256)
+layernorm_stream_kernel(T* __restrict__ y, const T* __restrict__ x, const T* __restrict__ gamma,
                  const T* __restrict__ beta, int64_t rows, int C, float eps) {
   pdl_trigger();
   pdl_wait();
@@ -106,13 +208,22 @@ int slider_layernorm(void* y, const void* x, const void* gamma, const void* beta
                    "layernorm: pointers must be 16-byte aligned");
   cudaStream_t st = (cudaStream_t)stream;
   const unsigned grid = (unsigned)((rows + 7) / 8);
-  if (dtype == SLIDER_BF16)
-    launch_pdl(layernorm_kernel<__nv_bfloat16>, dim3(grid), dim3(256), 0, st, (__nv_bfloat16*)y, (const __nv_bfloat16*)x,
-               (const __nv_bfloat16*)gamma, (const __nv_bfloat16*)beta, rows, channels, eps);
-  else if (dtype == SLIDER_F32)
-    launch_pdl(layernorm_kernel<float>, dim3(grid), dim3(256), 0, st, (float*)y, (const float*)x, (const float*)gamma,
-               (const float*)beta, rows, channels, eps);
-  else { set_error("layernorm: unsupported dtype %d", dtype); return SLIDER_ERR_UNSUPPORTED; }
+  if (dtype != SLIDER_BF16 && dtype != SLIDER_F32) { set_error("layernorm: unsupported dtype %d", dtype); return SLIDER_ERR_UNSUPPORTED; }
+  const int per_lane = (channels / (dtype == SLIDER_BF16 ? 8 : 4) + 31) / 32;      // 16-byte vectors per lane
+#define SLIDER_LN_LAUNCH(KERNEL, TYPE)                                                                              \
+  launch_pdl(KERNEL, dim3(grid), dim3(256), 0, st, (TYPE*)y, (const TYPE*)x, (const TYPE*)gamma, (const TYPE*)beta, \
+             rows, channels, eps)
+  if (dtype == SLIDER_BF16) {
+    if (per_lane <= 2) SLIDER_LN_LAUNCH((layernorm_kernel<__nv_bfloat16, 2>), __nv_bfloat16);
+    else if (per_lane <= 3) SLIDER_LN_LAUNCH((layernorm_kernel<__nv_bfloat16, 3>), __nv_bfloat16);
+    else if (per_lane <= 5) SLIDER_LN_LAUNCH((layernorm_kernel<__nv_bfloat16, 5>), __nv_bfloat16);
+    else SLIDER_LN_LAUNCH(layernorm_stream_kernel<__nv_bfloat16>, __nv_bfloat16);
+  } else {
+    if (per_lane <= 3) SLIDER_LN_LAUNCH((layernorm_kernel<float, 3>), float);
+    else if (per_lane <= 5) SLIDER_LN_LAUNCH((layernorm_kernel<float, 5>), float);
+    else SLIDER_LN_LAUNCH(layernorm_stream_kernel<float>, float);
+  }
+#undef SLIDER_LN_LAUNCH
   return post_launch("layernorm_kernel");
 }
 
