@@ -749,7 +749,6 @@ template <typename T, int R4>
 __global__ void __launch_bounds__(256)
 splitk_finalize_kernel(const GemmParams p) {
   pdl_trigger();
-  pdl_wait();
   constexpr int PIECES = PCW / 4;                  // 16-byte pieces per partial row
   constexpr int HC = (NCHUNK - 1) / 2;             // chunk pairs (c, c + HC)
   constexpr int PER_TILE = BM * PIECES * HC;
@@ -768,6 +767,40 @@ splitk_finalize_kernel(const GemmParams p) {
   const float* src = p.partial + (size_t)tile * p.ksplit * UNIT_FLOATS + ((size_t)c * BM + row) * PCW + pc * 4;
   const int hoff = p.group_n > 0 ? (tc.n0 / p.group_n) * p.rank : 0;
   const float* hsrc = p.partial + (size_t)tile * p.ksplit * UNIT_FLOATS + ((size_t)(NCHUNK - 1) * BM + row) * PCW + hoff;
+  const T* __restrict__ bias = reinterpret_cast<const T*>(p.bias);
+  const T* __restrict__ Bup = reinterpret_cast<const T*>(p.Bup);
+  T* const dst0 = reinterpret_cast<T*>(p.y) + pix * (size_t)p.N + n0;
+  T* const dst1 = reinterpret_cast<T*>(p.y) + pix * (size_t)p.N + n1;
+  // Everything the epilogue needs besides the partials is requested BEFORE the split loop, so that its latency hides
+  // behind the partial loads instead of following them: the frozen bias even before the dependent-launch wait, the
+  // rank-4 bf16 up-projection rows (8 bytes per output column) and the residual right after it.
+  float bs[8];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    bs[k] = bias != nullptr ? Elem<T>::to_f(bias[n0 + k]) : 0.f;
+    bs[4 + k] = (bias != nullptr && second) ? Elem<T>::to_f(bias[n1 + k]) : 0.f;
+  }
+  pdl_wait();
+  constexpr bool kPackB = R4 == 1 && sizeof(T) == 2;
+  const bool packb = kPackB && p.rank == 4 && Bup != nullptr;
+  uint2 bq[kPackB ? 8 : 1];
+  if (kPackB && packb) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      bq[k] = *reinterpret_cast<const uint2*>(Bup + (size_t)(n0 + k) * 4);
+      bq[4 + k] = *reinterpret_cast<const uint2*>(Bup + (size_t)(second ? n1 + k : n0 + k) * 4);
+    }
+  }
+  uint4 resq[2] = {make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};       // bf16: .x .y used; fp32: all four
+  if (p.accumulate) {
+    if (sizeof(T) == 2) {
+      const uint2 q0 = *reinterpret_cast<const uint2*>(dst0), q1 = *reinterpret_cast<const uint2*>(second ? dst1 : dst0);
+      resq[0].x = q0.x; resq[0].y = q0.y; resq[1].x = q1.x; resq[1].y = q1.y;
+    } else {
+      resq[0] = *reinterpret_cast<const uint4*>(dst0);
+      resq[1] = *reinterpret_cast<const uint4*>(second ? dst1 : dst0);
+    }
+  }
   float o[8];
   float hv[R4 > 0 ? 4 * R4 : 1];
 #pragma unroll
@@ -804,8 +837,6 @@ splitk_finalize_kernel(const GemmParams p) {
         if (R4 > 0 && hoff + j < HCOLS) hv[j] += __ldcg(hsrc + (size_t)s * UNIT_FLOATS + j);
     }
   }
-  const T* __restrict__ bias = reinterpret_cast<const T*>(p.bias);
-  const T* __restrict__ Bup = reinterpret_cast<const T*>(p.Bup);
 #pragma unroll
   for (int half = 0; half < 2; ++half) {
     if (half == 1 && !second) break;
@@ -813,21 +844,29 @@ splitk_finalize_kernel(const GemmParams p) {
     float r[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-      float a = o[half * 4 + k] + (bias != nullptr ? Elem<T>::to_f(bias[n + k]) : 0.f);
+      float a = o[half * 4 + k] + bs[half * 4 + k];
       if (R4 > 0) {
         float l = 0.f;
+        if (kPackB && packb) {
+          const uint2 q = bq[kPackB ? half * 4 + k : 0];
+          l = fmaf(hv[0], __uint_as_float(q.x << 16), l);
+          l = fmaf(hv[1 % (R4 > 0 ? 4 * R4 : 1)], __uint_as_float(q.x & 0xffff0000u), l);
+          l = fmaf(hv[2 % (R4 > 0 ? 4 * R4 : 1)], __uint_as_float(q.y << 16), l);
+          l = fmaf(hv[3 % (R4 > 0 ? 4 * R4 : 1)], __uint_as_float(q.y & 0xffff0000u), l);
+        } else {
 #pragma unroll
-        for (int j = 0; j < 4 * R4; ++j)
-          if (j < p.rank) l = fmaf(hv[j], Elem<T>::to_f(Bup[(size_t)(n + k) * p.rank + j]), l);
+          for (int j = 0; j < 4 * R4; ++j)
+            if (j < p.rank) l = fmaf(hv[j], Elem<T>::to_f(Bup[(size_t)(n + k) * p.rank + j]), l);
+        }
         a = fmaf(p.s, l, a);
       }
       r[k] = a;
     }
-    T* dst = reinterpret_cast<T*>(p.y) + pix * (size_t)p.N + n;
+    T* dst = half == 0 ? dst0 : dst1;
     if (sizeof(T) == 2) {
       uint2* d2 = reinterpret_cast<uint2*>(dst);
       if (p.accumulate) {  // y holds the residual: same two roundings as `residual + module(x)` in element dtype
-        const uint2 q = *d2;
+        const uint4 q = resq[half];
         const float res[4] = {__uint_as_float(q.x << 16), __uint_as_float(q.x & 0xffff0000u),
                               __uint_as_float(q.y << 16), __uint_as_float(q.y & 0xffff0000u)};
 #pragma unroll
@@ -838,8 +877,8 @@ splitk_finalize_kernel(const GemmParams p) {
     } else {
       float4* d4 = reinterpret_cast<float4*>(dst);
       if (p.accumulate) {
-        const float4 q = *d4;
-        r[0] += q.x; r[1] += q.y; r[2] += q.z; r[3] += q.w;
+        const uint4 q = resq[half];
+        r[0] += __uint_as_float(q.x); r[1] += __uint_as_float(q.y); r[2] += __uint_as_float(q.z); r[3] += __uint_as_float(q.w);
       }
       *d4 = make_float4(r[0], r[1], r[2], r[3]);
     }
