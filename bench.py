@@ -199,9 +199,8 @@ def measured_traffic():
     if not f.exists():
         return None
     try:
-        ks = json.loads(f.read_text())["kernels"]
-        k = next(v for n, v in ks.items() if "lora_gemm_kernel" in n)
-        return round(k["avg_dram_bytes_per_launch"])
+        ks = [v for n, v in json.loads(f.read_text())["kernels"].items() if "lora_gemm_kernel" in n]
+        return round(sum(k["dram_read_bytes"] + k["dram_write_bytes"] for k in ks) / sum(k["launches"] for k in ks))
     except Exception:
         return None
 
