@@ -8,7 +8,7 @@ import torch
 from torch.profiler import profile, ProfilerActivity
 from sliders_conceptmod_b200 import workload
 
-phase = next((a for a in sys.argv[1:] if a in ("denoise", "predict", "train")), "denoise")
+phase = next((a for a in sys.argv[1:] if a in ("denoise", "predict", "train", "predict_train")), "denoise")
 name = sys.argv[sys.argv.index("--workload") + 1] if "--workload" in sys.argv else "sd14_text_slider_rank4_512px"
 wl = workload.WORKLOADS[name]
 engine, unet, network, pairs = workload.build(wl, "cuda", torch.bfloat16, use_graphs=True, lora_b_std=0.02)
