@@ -75,8 +75,8 @@ def test_groupnorm_nhwc_backward_matches_torch_autograd(case, dtype, silu, with_
 
 @pytest.mark.parametrize("cs", [8, 16])
 def test_groupnorm_cluster_form_matches_two_kernel_form(cs):
-    """The opt-in single-launch form (one thread-block cluster per image, slider_debug_gn_cluster) gives the same
-    result as the default two-kernel form up to the order of the partial sums."""
+    """The opt-in one-cluster-per-image form (slider_debug_gn_cluster) gives the same result as the default form (one
+    launch per (image, group set)) up to the order of the partial sums."""
     import ctypes
     from sliders_conceptmod_b200 import ops, _lib
     fn = _lib.lib().slider_debug_gn_cluster
