@@ -256,6 +256,15 @@ int slider_layernorm(void* y, const void* x, const void* gamma, const void* beta
                      int64_t rows, int channels, float eps, int dtype, void* stream);
 int slider_geglu(void* y, const void* x, int64_t rows, int d, int dtype, void* stream);
 
+/*
+ * Nearest-neighbour 2x upsample of an NHWC tensor: y[b, 2h + i, 2w + j, :] = x[b, h, w, :]  (i, j in {0, 1}).
+ * Replaces `F.interpolate(hidden_states, scale_factor=2.0, mode="nearest")` of diffusers' Upsample2D ahead of its
+ * LoRA-wrapped 3x3 convolution (UNet calls at train_util.py:290-294).  x [batch, height, width, channels],
+ * y [batch, 2*height, 2*width, channels]; channels * sizeof(dtype) must be a multiple of 16.
+ */
+int slider_upsample_nearest2x_nhwc(void* y, const void* x, int batch, int height, int width, int channels, int dtype,
+                                   void* stream);
+
 /* x *= *dev_scalar  (chain rule for a non-unit upstream loss gradient). */
 int slider_scale_by_device_scalar(void* x, const float* dev_scalar,
                                   int64_t n_elem, int dtype, void* stream);

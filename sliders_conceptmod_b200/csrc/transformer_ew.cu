@@ -194,6 +194,27 @@ geglu_kernel(T* __restrict__ y, const T* __restrict__ x, int64_t rows, int D) {
   }
 }
 
+
+// ---- nearest-neighbour 2x upsample on NHWC (Upsample2D before its 3x3 convolution) -----------------------------------
+// One thread per 16-byte INPUT vector: read once, stored to the 2 x 2 output pixels (a warp covers 512 contiguous bytes
+// of each).  Pure copy (bit-exact); writes 4x what it reads.
+__global__ void __launch_bounds__(256)
+upsample2x_kernel(uint4* __restrict__ y, const uint4* __restrict__ x, int64_t rows_in /* B*H */, int W, int nv) {
+  pdl_trigger();
+  pdl_wait();
+  const int64_t total = rows_in * W * nv;
+  const int64_t row_out = (int64_t)2 * W * nv;                  // vectors per output row
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % nv);
+    const int64_t pix = i / nv;
+    const int w = (int)(pix % W);
+    const int64_t bh = pix / W;                                  // b * H + h; output rows 2*bh, 2*bh + 1
+    const uint4 v = x[i];
+    uint4* o = y + (2 * bh) * row_out + (int64_t)(2 * w) * nv + c;
+    o[0] = v; o[nv] = v; o[row_out] = v; o[row_out + nv] = v;
+  }
+}
+
 }  // namespace slider
 
 using namespace slider;
@@ -245,6 +266,23 @@ int slider_geglu(void* y, const void* x, int64_t rows, int d, int dtype, void* s
     launch_pdl(geglu_kernel<float>, dim3(gx, (unsigned)gy), dim3(threads), 0, st, (float*)y, (const float*)x, rows, d);
   else { set_error("geglu: unsupported dtype %d", dtype); return SLIDER_ERR_UNSUPPORTED; }
   return post_launch("geglu_kernel");
+}
+
+int slider_upsample_nearest2x_nhwc(void* y, const void* x, int batch, int height, int width, int channels, int dtype,
+                                   void* stream) {
+  SLIDER_CHECK_ARG(y && x && batch > 0 && height > 0 && width > 0 && channels > 0, "upsample2x: bad argument");
+  SLIDER_CHECK_ARG(dtype == SLIDER_BF16 || dtype == SLIDER_F32, "upsample2x: unsupported dtype %d", dtype);
+  const int per = dtype == SLIDER_BF16 ? 8 : 4;
+  SLIDER_CHECK_ARG(channels % per == 0, "upsample2x: channels must fill 16-byte vectors (got %d)", channels);
+  SLIDER_CHECK_ARG((((uintptr_t)y | (uintptr_t)x) & 15) == 0, "upsample2x: pointers must be 16-byte aligned");
+  const int nv = channels / per;
+  const int64_t total = (int64_t)batch * height * width * nv;
+  int64_t blocks = (total + 255) / 256;
+  const int64_t cap = (int64_t)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  launch_pdl(upsample2x_kernel, dim3((unsigned)blocks), dim3(256), 0, (cudaStream_t)stream, (uint4*)y, (const uint4*)x,
+             (int64_t)batch * height, width, nv);
+  return post_launch("upsample2x_kernel");
 }
 
 }  // extern "C"

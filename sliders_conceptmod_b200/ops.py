@@ -299,6 +299,17 @@ def geglu(x: torch.Tensor) -> torch.Tensor:
     return y
 
 
+def upsample_nearest2x_nhwc(x: torch.Tensor) -> torch.Tensor:
+    """F.interpolate(scale_factor=2, mode="nearest") on NHWC data: x [B, H, W, C] contiguous -> [B, 2H, 2W, C]."""
+    require_cuda(x)
+    assert x.dim() == 4 and x.is_contiguous()
+    B, H, W, Cc = x.shape
+    y = torch.empty(B, 2 * H, 2 * W, Cc, device=x.device, dtype=x.dtype)
+    check(lib().slider_upsample_nearest2x_nhwc(ptr(y), ptr(x), int(B), int(H), int(W), int(Cc), dtype_code(x.dtype),
+                                               stream_ptr()))
+    return y
+
+
 def launch_count() -> int:
     return int(lib().slider_launch_count())
 

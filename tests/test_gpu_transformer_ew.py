@@ -31,3 +31,17 @@ def test_geglu(rows, D, dtype):
     yr = a * F.gelu(gate)
     tol = 2e-2 if dtype == torch.bfloat16 else 1e-5
     assert (y.float() - yr).abs().max().item() <= tol * max(1.0, yr.abs().max().item())
+
+
+@pytest.mark.parametrize("shape", [(2, 32, 32, 640), (2, 8, 8, 1280), (1, 3, 5, 8), (6, 16, 16, 1280)])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+def test_upsample_nearest2x_nhwc_is_bit_exact(shape, dtype):
+    """slider_upsample_nearest2x_nhwc vs F.interpolate(scale_factor=2, mode="nearest") (diffusers Upsample2D): a copy."""
+    from sliders_conceptmod_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(5)
+    x = torch.randn(*shape, device="cuda", generator=g).to(dtype)
+    guard = torch.full((shape[0] * 4 * shape[1] * shape[2] * shape[3] + 64,), 7.0, device="cuda", dtype=dtype)
+    y = ops.upsample_nearest2x_nhwc(x)
+    ref = F.interpolate(x.permute(0, 3, 1, 2), scale_factor=2.0, mode="nearest").permute(0, 2, 3, 1)
+    assert y.shape == ref.shape and torch.equal(y, ref.contiguous())
+    assert bool((guard == 7.0).all())
