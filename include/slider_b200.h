@@ -265,6 +265,14 @@ int slider_geglu(void* y, const void* x, int64_t rows, int d, int dtype, void* s
 int slider_upsample_nearest2x_nhwc(void* y, const void* x, int batch, int height, int width, int channels, int dtype,
                                    void* stream);
 
+/*
+ * Channel concatenation of two NHWC tensors: y[p, :ca] = a[p, :], y[p, ca:] = b[p, :] for every pixel p.
+ * Replaces `torch.cat([hidden_states, res_hidden_states], dim=1)` of diffusers' up blocks (the skip connections; UNet
+ * calls at train_util.py:290-294).  channels_a/b * sizeof(dtype) must be multiples of 16.
+ */
+int slider_concat_channels_nhwc(void* y, const void* a, const void* b, int64_t pixels, int channels_a, int channels_b,
+                                int dtype, void* stream);
+
 /* x *= *dev_scalar  (chain rule for a non-unit upstream loss gradient). */
 int slider_scale_by_device_scalar(void* x, const float* dev_scalar,
                                   int64_t n_elem, int dtype, void* stream);

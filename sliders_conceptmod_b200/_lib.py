@@ -49,6 +49,7 @@ _SIGNATURES = {
     "slider_layernorm": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i, _f, _i, _vp]),
     "slider_geglu": (C.c_int, [_vp, _vp, _i64, _i, _i, _vp]),
     "slider_upsample_nearest2x_nhwc": (C.c_int, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "slider_concat_channels_nhwc": (C.c_int, [_vp, _vp, _vp, _i64, _i, _i, _i, _vp]),
     "slider_loss_workspace_bytes": (_sz, []),
     "slider_guidance_loss": (C.c_int, [_fp, _vp, _vp, _vp, _vp, _vp, _i64, _f, _i, _i, _vp, _sz, _vp]),
     "slider_cfg_step": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _f, _f, _f, _f, _fp, _i, _vp]),

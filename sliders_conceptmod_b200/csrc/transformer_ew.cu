@@ -215,6 +215,23 @@ upsample2x_kernel(uint4* __restrict__ y, const uint4* __restrict__ x, int64_t ro
   }
 }
 
+
+// ---- channel concatenation of two NHWC tensors (the skip connections of the up path: cat([h, skip], dim=1)) ----------
+// One thread per 16-byte OUTPUT vector; a pixel's row is the row of a followed by the row of b.  Pure copy.
+__global__ void __launch_bounds__(256)
+concat2_kernel(uint4* __restrict__ y, const uint4* __restrict__ a, const uint4* __restrict__ b, int64_t pixels, int nva,
+               int nvb) {
+  pdl_trigger();
+  pdl_wait();
+  const int nvo = nva + nvb;
+  const int64_t total = pixels * nvo;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t pix = i / nvo;
+    const int c = (int)(i - pix * nvo);
+    y[i] = c < nva ? a[pix * nva + c] : b[pix * nvb + (c - nva)];
+  }
+}
+
 }  // namespace slider
 
 using namespace slider;
@@ -283,6 +300,24 @@ int slider_upsample_nearest2x_nhwc(void* y, const void* x, int batch, int height
   launch_pdl(upsample2x_kernel, dim3((unsigned)blocks), dim3(256), 0, (cudaStream_t)stream, (uint4*)y, (const uint4*)x,
              (int64_t)batch * height, width, nv);
   return post_launch("upsample2x_kernel");
+}
+
+int slider_concat_channels_nhwc(void* y, const void* a, const void* b, int64_t pixels, int channels_a, int channels_b,
+                                int dtype, void* stream) {
+  SLIDER_CHECK_ARG(y && a && b && pixels > 0 && channels_a > 0 && channels_b > 0, "concat: bad argument");
+  SLIDER_CHECK_ARG(dtype == SLIDER_BF16 || dtype == SLIDER_F32, "concat: unsupported dtype %d", dtype);
+  const int per = dtype == SLIDER_BF16 ? 8 : 4;
+  SLIDER_CHECK_ARG(channels_a % per == 0 && channels_b % per == 0,
+                   "concat: channel counts must fill 16-byte vectors (got %d, %d)", channels_a, channels_b);
+  SLIDER_CHECK_ARG((((uintptr_t)y | (uintptr_t)a | (uintptr_t)b) & 15) == 0, "concat: pointers must be 16-byte aligned");
+  const int nva = channels_a / per, nvb = channels_b / per;
+  const int64_t total = pixels * (nva + nvb);
+  int64_t blocks = (total + 255) / 256;
+  const int64_t cap = (int64_t)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  launch_pdl(concat2_kernel, dim3((unsigned)blocks), dim3(256), 0, (cudaStream_t)stream, (uint4*)y, (const uint4*)a,
+             (const uint4*)b, pixels, nva, nvb);
+  return post_launch("concat2_kernel");
 }
 
 }  // extern "C"

@@ -310,6 +310,17 @@ def upsample_nearest2x_nhwc(x: torch.Tensor) -> torch.Tensor:
     return y
 
 
+def concat_channels_nhwc(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
+    """torch.cat([a, b], dim=-1) for NHWC tensors a [..., Ca], b [..., Cb] (same leading shape, contiguous)."""
+    require_cuda(a, b)
+    assert a.is_contiguous() and b.is_contiguous() and a.shape[:-1] == b.shape[:-1] and a.dtype == b.dtype
+    ca, cb = a.shape[-1], b.shape[-1]
+    y = torch.empty(*a.shape[:-1], ca + cb, device=a.device, dtype=a.dtype)
+    check(lib().slider_concat_channels_nhwc(ptr(y), ptr(a), ptr(b), a.numel() // ca, int(ca), int(cb),
+                                            dtype_code(a.dtype), stream_ptr()))
+    return y
+
+
 def launch_count() -> int:
     return int(lib().slider_launch_count())
 

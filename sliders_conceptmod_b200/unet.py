@@ -155,6 +155,17 @@ def _no_grad_cuda(*ts) -> bool:
     return first.is_cuda and not (torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in ts))
 
 
+def _cat_skip(x: torch.Tensor, skip: torch.Tensor) -> torch.Tensor:
+    """torch.cat([x, skip], dim=1) of the up path; on no-grad CUDA forwards with channels_last operands one copy kernel."""
+    if (_no_grad_cuda(x, skip) and "concat" not in _DISABLED and x.dtype == skip.dtype
+            and x.dtype in (torch.bfloat16, torch.float32)
+            and (x.shape[1] * x.element_size()) % 16 == 0 and (skip.shape[1] * x.element_size()) % 16 == 0):
+        xn, sn = x.permute(0, 2, 3, 1), skip.permute(0, 2, 3, 1)
+        if xn.is_contiguous() and sn.is_contiguous():
+            return ops.concat_channels_nhwc(xn, sn).permute(0, 3, 1, 2)
+    return torch.cat([x, skip], dim=1)
+
+
 def fused_linear(mod: nn.Module, x: torch.Tensor, residual: torch.Tensor | None = None) -> torch.Tensor:
     """`mod(x)` (+ `residual`) for an nn.Linear on [..., K] or a 1x1 nn.Conv2d on [B,C,H,W].
 
@@ -459,7 +470,7 @@ class CrossAttnUpBlock2D(nn.Module):
 
     def forward(self, x, skips, temb, context):
         for i, res in enumerate(self.resnets):
-            x = torch.cat([x, skips.pop()], dim=1)
+            x = _cat_skip(x, skips.pop())
             x = res(x, temb)
             if self.has_attn:
                 x = self.attentions[i](x, context)

@@ -45,3 +45,18 @@ def test_upsample_nearest2x_nhwc_is_bit_exact(shape, dtype):
     ref = F.interpolate(x.permute(0, 3, 1, 2), scale_factor=2.0, mode="nearest").permute(0, 2, 3, 1)
     assert y.shape == ref.shape and torch.equal(y, ref.contiguous())
     assert bool((guard == 7.0).all())
+
+
+@pytest.mark.parametrize("shape", [(2, 64, 64, 320, 320), (2, 16, 16, 1280, 640), (1, 3, 5, 8, 24), (6, 8, 8, 1280, 1280)])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+def test_concat_channels_nhwc_is_bit_exact(shape, dtype):
+    """slider_concat_channels_nhwc vs torch.cat (the skip connections of the up path): a copy."""
+    from sliders_conceptmod_b200 import ops
+    B, H, W, ca, cb = shape
+    g = torch.Generator(device="cuda").manual_seed(6)
+    a = torch.randn(B, H, W, ca, device="cuda", generator=g).to(dtype)
+    b = torch.randn(B, H, W, cb, device="cuda", generator=g).to(dtype)
+    guard = torch.full((B * H * W * (ca + cb) + 64,), 7.0, device="cuda", dtype=dtype)
+    y = ops.concat_channels_nhwc(a, b)
+    assert torch.equal(y, torch.cat([a, b], dim=-1))
+    assert bool((guard == 7.0).all())
