@@ -155,6 +155,26 @@ def _no_grad_cuda(*ts) -> bool:
     return first.is_cuda and not (torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in ts))
 
 
+def _sdpa(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor) -> torch.Tensor:
+    """Attention core = library SDPA (not claimed).  torch's default backend choice is the fastest at the UNet's
+    self-attention shapes; at two cross-attention shapes (77 keys) another library kernel is measured faster on B200
+    (tools/bench_sdpa.py: head_dim 160 -> memory-efficient 7.9 vs 10.7 us, 4096 queries -> flash 15.5 vs 17.8 us)."""
+    if q.is_cuda and not torch.is_grad_enabled() and "sdpa_pick" not in _DISABLED and k.shape[-2] <= 128:
+        from torch.nn.attention import SDPBackend, sdpa_kernel
+        pick = None
+        if q.shape[-1] >= 128 and q.shape[-2] <= 1024:
+            pick = SDPBackend.EFFICIENT_ATTENTION
+        elif q.shape[-2] >= 4096 and q.shape[-1] <= 64:
+            pick = SDPBackend.FLASH_ATTENTION
+        if pick is not None:
+            try:
+                with sdpa_kernel(pick):
+                    return F.scaled_dot_product_attention(q, k, v)
+            except RuntimeError:
+                pass
+    return F.scaled_dot_product_attention(q, k, v)
+
+
 def _cat_skip(x: torch.Tensor, skip: torch.Tensor) -> torch.Tensor:
     """torch.cat([x, skip], dim=1) of the up path; on no-grad CUDA forwards with channels_last operands one copy kernel."""
     if (_no_grad_cuda(x, skip) and "concat" not in _DISABLED and x.dtype == skip.dtype
@@ -310,7 +330,7 @@ class Attention(nn.Module):
         q = q.view(B, L, self.heads, -1).transpose(1, 2)
         k = k.view(B, ctx.shape[1], self.heads, -1).transpose(1, 2)
         v = v.view(B, ctx.shape[1], self.heads, -1).transpose(1, 2)
-        o = F.scaled_dot_product_attention(q, k, v)
+        o = _sdpa(q, k, v)
         o = o.transpose(1, 2).reshape(B, L, -1)
         if residual is not None:
             return add_residual(self.to_out[0], o, residual)      # to_out[1] is Dropout(0.0)
