@@ -217,7 +217,11 @@ int slider_cfg_step(void* out, const void* x, const void* eps_u,
  *   silu      != 0 applies SiLU
  *   ws        slider_groupnorm_workspace_bytes(batch, groups) bytes, zero-filled ONCE by the caller
  *             (the kernels leave the ticket words zero); may be shared by calls on one stream.
- * Two launches (statistics, apply); deterministic reduction order.
+ * One launch per call when a group set fits a thread-block cluster's shared memory (a CTA or a cluster of 2 / 4 / 8
+ * per (image, group set): x read once, statistics exchanged over distributed shared memory), otherwise two launches
+ * (per-chunk statistics into ws, apply); deterministic reduction order either way.
+ * gamma / beta are parameters: with programmatic dependent launch on (default) they are read BEFORE the wait on the
+ * preceding kernel, so they must not be the output of a libslider launch issued just before on the same stream.
  */
 size_t slider_groupnorm_workspace_bytes(int batch, int groups);
 int slider_groupnorm_nhwc(void* y, const void* x, const void* chan_add,
@@ -250,7 +254,8 @@ int slider_groupnorm_nhwc_backward(void* dx, void* dadd, const void* gy, const v
  *   slider_layernorm: y = (x - mean) * rstd * gamma + beta over the last dimension of x [rows, channels]
  *                     (the producer of the LoRA-wrapped attn1.to_q/k/v inputs);
  *   slider_geglu:     y[rows, d] = x[:, :d] * gelu(x[:, d:]), x [rows, 2d], exact (erf) GELU.
- * channels and d must be multiples of 8; gamma / beta may be NULL.
+ * channels and d must be multiples of 8; gamma / beta may be NULL (parameters: read before the dependent-launch wait,
+ * see slider_groupnorm_nhwc).
  */
 int slider_layernorm(void* y, const void* x, const void* gamma, const void* beta,
                      int64_t rows, int channels, float eps, int dtype, void* stream);
