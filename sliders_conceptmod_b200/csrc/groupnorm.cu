@@ -607,7 +607,9 @@ static bool gn_group_plan(const GnParams& p, GnGroupPlan* gp) {
   int k = 1;
   while (k < 8 && slab / k > (size_t)g_gn_group_kb * 1024) k *= 2;     // clusters of 16 start in waves (measured)
   while (k > 1 && p.HW % k != 0) k /= 2;
-  if (slab / k > 160 * 1024) return false;
+  // above ~100 KB per CTA only one CTA fits an SM and clusters of 8 start in waves: measured equal to 14 % slower than
+  // the two-kernel form (tools/bench_gn_big.py, profiles/r01_ab_gn_group.txt), which those shapes therefore keep
+  if (slab / k > 100 * 1024) return false;
   gp->a.k = k; gp->a.gp = g; gp->a.wr = wr; gp->a.rows = p.HW / k; gp->a.trace = g_gn_trace;
   gp->threads = (GN_GROUP_THREADS / l) * l;
   gp->smem = (size_t)gp->a.rows * seg + (GN_GROUP_THREADS / 32) * GN_GROUP_MAXGP * sizeof(float2) +
@@ -620,7 +622,7 @@ static int gn_group_launch(void* y, const void* x, const void* chan_add, const v
                            const GnParams& p, const GnGroupPlan& gp, cudaStream_t st, float* stats_out) {
   static thread_local bool configured = false;
   if (!configured) {
-    SLIDER_CUDA(cudaFuncSetAttribute(gn_group_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 180 * 1024));
+    SLIDER_CUDA(cudaFuncSetAttribute(gn_group_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
     configured = true;
   }
   cudaLaunchConfig_t cfg = {};
@@ -938,6 +940,18 @@ extern "C" {
 
 int slider_debug_gn_variant(int v) { g_gn_variant = v; return 0; }
 int slider_debug_gn_cluster(int cs) { g_gn_cluster = (cs == 8 || cs == 16) ? cs : 0; return 0; }
+// host-only view of the single-launch plan (no device needed): 1 and out = {k, gp, words per row, rows per CTA,
+// threads, dynamic smem bytes} when the shape takes the single launch, 0 when it takes the two-kernel form
+int slider_debug_gn_group_plan(int hw, int channels, int groups, int dtype, int* out) {
+  if (hw <= 0 || channels <= 0 || groups <= 0 || channels % groups != 0 || out == nullptr) return -1;
+  GnParams p = {};
+  p.B = 1; p.HW = hw; p.C = channels; p.G = groups; p.cpg = channels / groups;
+  GnGroupPlan gp;
+  const bool ok = dtype == SLIDER_BF16 ? gn_group_plan<__nv_bfloat16>(p, &gp) : gn_group_plan<float>(p, &gp);
+  if (!ok) return 0;
+  out[0] = gp.a.k; out[1] = gp.a.gp; out[2] = gp.a.wr; out[3] = gp.a.rows; out[4] = gp.threads; out[5] = (int)gp.smem;
+  return 1;
+}
 int slider_debug_gn_trace(void* buf) { g_gn_trace = (unsigned long long*)buf; return 0; }
 int slider_debug_gn_group(int on, int slab_kb) {
   g_gn_group = on;

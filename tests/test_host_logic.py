@@ -218,3 +218,41 @@ def test_workload_definitions():
     pairs = workload.prompt_pairs(wl, 768)
     assert len(pairs) == 4 and pairs[0]["target"].shape == (1, 77, 768)
     assert torch.equal(pairs[0]["target"], workload.prompt_pairs(wl, 768)[0]["target"])     # deterministic
+
+
+def test_groupnorm_single_launch_plan_table():
+    """Host-side plan of the single-launch GroupNorm (csrc/groupnorm.cu gn_group_plan; no device needed): groups per
+    slab (rows must be whole 16-byte vectors), cluster size (<= 24 KB of the slab per CTA, at most 8 CTAs), block size
+    (a multiple of the 32-bit words per row, so a thread keeps one column), and the shapes that keep the two-kernel form."""
+    import ctypes
+    from sliders_conceptmod_b200 import _lib
+    fn = _lib.lib().slider_debug_gn_group_plan
+    fn.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_int)]
+    fn.restype = ctypes.c_int
+
+    def plan(hw, c, g, dtype=_lib.SLIDER_BF16):
+        out = (ctypes.c_int * 6)()
+        rc = fn(hw, c, g, dtype, out)
+        return rc, dict(zip(("k", "gp", "wr", "rows", "threads", "smem"), out))
+
+    # SD-1.x / SD-XL shapes (32 groups, bf16): hw, channels -> (groups per slab, cluster size)
+    for hw, c, gp, k in [(4096, 320, 4, 8), (4096, 640, 2, 8), (1024, 640, 2, 4), (1024, 1920, 2, 8),
+                         (256, 1280, 1, 1), (256, 2560, 1, 2), (64, 1280, 1, 1), (64, 2560, 1, 1)]:
+        rc, p = plan(hw, c, 32)
+        assert rc == 1 and (p["gp"], p["k"]) == (gp, k), (hw, c, p)
+        seg = p["gp"] * (c // 32) * 2
+        assert seg % 16 == 0 and p["wr"] == seg // 4 and p["rows"] * p["k"] == hw
+        assert p["threads"] % p["wr"] == 0 and p["threads"] % 32 == 0 and 256 < p["threads"] <= 512
+        assert p["rows"] * seg <= p["smem"] <= p["rows"] * seg + 2048
+    assert plan(4096, 320, 32)[1]["threads"] == 480
+    # more than 100 KB of slab per CTA at k = 8 (one CTA per SM: clusters start in waves) keeps the two-kernel form;
+    # a 10-byte group is not a whole number of 32-bit words; odd pixel counts fall back to smaller clusters
+    assert plan(16384, 320, 32)[0] == 0 and plan(4096, 960, 32)[0] == 0 and plan(16384, 640, 32)[0] == 0
+    rc, p = plan(4096, 640, 32, _lib.SLIDER_F32)
+    assert rc == 1 and p["k"] == 8 and p["rows"] * 160 <= 100 * 1024
+    assert plan(16, 40, 8)[0] == 0
+    rc, p = plan(35, 64, 8)
+    assert rc == 1 and p["k"] == 1 and p["rows"] == 35
+    rc, p = plan(4096, 320, 32, _lib.SLIDER_F32)
+    assert rc == 1 and p["gp"] == 2 and p["k"] == 8
+    assert fn(0, 320, 32, _lib.SLIDER_BF16, (ctypes.c_int * 6)()) == -1
