@@ -25,6 +25,24 @@ def lora_forward(org_forward, lora_down, lora_up, multiplier, scale, x):
     return org_forward(x) + lora_up(lora_down(x)) * multiplier * scale
 
 
+def dora_forward(x, weight, bias, lora_down_w, lora_up_w, dora_scale, multiplier, scale, stride=1, padding=0):
+    """conceptmod/textsliders/dora.py:122-163 (DoRAModule.apply_weight_decompose + forward), same op order:
+    W' = (W + B.A) * (dora_scale / ||W + B.A||) with the norm per INPUT channel over outputs and taps (detached),
+    y = org(x) + ops(x, W' - W) * scale * multiplier."""
+    if weight.dim() == 4:
+        lora_weight = torch.mm(lora_up_w.flatten(start_dim=1), lora_down_w.flatten(start_dim=1)).reshape(weight.shape)
+    else:
+        lora_weight = lora_up_w @ lora_down_w
+    w = weight + lora_weight
+    norm = (w.transpose(0, 1).reshape(w.shape[1], -1).norm(dim=1, keepdim=True)
+            .reshape(w.shape[1], *[1] * (w.dim() - 1)).transpose(0, 1)).detach()
+    delta = (w * (dora_scale / norm) - weight).to(x.dtype)
+    if weight.dim() == 4:
+        return (F.conv2d(x, weight, bias, stride=stride, padding=padding)
+                + F.conv2d(x, delta, padding=padding, stride=stride) * scale * multiplier)
+    return F.linear(x, weight, bias) + F.linear(x, delta) * scale * multiplier
+
+
 def attach(network):
     """Re-point every wrapped layer of a (sliders_conceptmod_b200) LoRANetwork at the oracle arithmetic.
     Module selection / naming stays the product's host logic (pinned separately by golden key lists)."""

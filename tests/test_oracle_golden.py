@@ -112,3 +112,31 @@ def test_train_loop_matches_reference_minitrain():
     sd = net.state_dict()
     for k, v in gold["final"].items():
         assert torch.allclose(sd[k], v, rtol=1e-4, atol=1e-6), k
+
+
+def test_dora_oracle_and_fold_match_reference_vectors():
+    """DoRA ("next" row): the oracle restatement of dora.py:122-163 reproduces the reference module's
+    outputs (tests/golden/make_golden_dora.py), and the per-input-channel fold of sliders_conceptmod_b200/dora.py —
+    one fused base + low-rank pass on the pre-scaled input — equals it."""
+    import torch.nn.functional as F
+    from sliders_conceptmod_b200 import dora
+    cases = torch.load(Path(__file__).parent / "golden" / "reference_dora.pt", weights_only=False)["dora_cases"]
+    assert len(cases) == 4
+    for c in cases:
+        conv = c["W"].dim() == 4
+        stride, padding = (c["stride"], c["padding"]) if conv else (1, 0)
+        y = O.dora_forward(c["x"], c["W"], c["bias"], c["A"], c["B"], c["dora_scale"], c["mult"], c["scale"],
+                           stride=stride, padding=padding)
+        assert torch.allclose(y, c["y"], rtol=0, atol=1e-6), c["kind"]
+        s = c["scale"] * c["mult"]
+        v, a2 = dora.dora_fold(c["W"].double(), c["A"].double(), c["B"].double(), c["dora_scale"].double(), s)
+        x = c["x"].double()
+        bias = None if c["bias"] is None else c["bias"].double()
+        if conv:
+            xv = x * v.reshape(1, -1, 1, 1)
+            h = F.conv2d(xv, a2, stride=stride, padding=padding)
+            yf = F.conv2d(xv, c["W"].double(), bias, stride=stride, padding=padding) + F.conv2d(h, c["B"].double())
+        else:
+            xv = x * v
+            yf = F.linear(xv, c["W"].double(), bias) + F.linear(F.linear(xv, a2), c["B"].double())
+        assert torch.allclose(yf.float(), c["y"], rtol=1e-5, atol=2e-5), (c["kind"], (yf.float() - c["y"]).abs().max())
