@@ -41,9 +41,11 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=WORKLOAD)
+    ap.add_argument("--timesteps-to", type=int, default=TIMESTEPS_TO, help="denoising steps per iteration (headline: 25)")
     ap.add_argument("--no-graphs", action="store_true")
     ap.add_argument("--skip-cpu-baseline", action="store_true")
-    ap.add_argument("--cpu-budget-s", type=float, default=200.0)
+    ap.add_argument("--cpu-budget-s", type=float, default=240.0)
+    ap.add_argument("--skip-eager-baseline", action="store_true")
     return ap.parse_args()
 
 
@@ -186,9 +188,15 @@ def fused_gemm_roofline(engine, pk: dict, reps: int = 5) -> dict:
     sec = e0.elapsed_time(e1) * 1e-3 / reps
     achieved = flops / sec / 1e12
     peak = float(pk.get("bf16_tflops_sustained", pk["bf16_tflops"]))
+    burst = float(pk["bf16_tflops"])
+    traffic, tc_util = measured_traffic()
     return {"bound": "tensor", "kernel": "lora_gemm_kernel", "achieved": round(achieved, 1), "peak": peak,
             "peak_source": pk["source"] + ":bf16_tflops_sustained", "unit": "TFLOP/s", "frac": round(achieved / peak, 4),
-            "traffic": measured_traffic(), "launches": len(calls), "avg_launch_us": round(sec / len(calls) * 1e6, 2),
+            "frac_burst": round(achieved / burst, 4), "peak_burst": burst,
+            "tc_util_pct": tc_util, "tc_util_source": "profiles/gemm_traffic.json: duration-weighted ncu "
+            "sm__pipe_tensor_subpipe_hmma_cycles_active.avg.pct_of_peak_sustained_active over the tensor-core launches of the "
+            "same forward (ncu --set full capture, committed; not measured inside this run)",
+            "traffic": traffic, "launches": len(calls), "avg_launch_us": round(sec / len(calls) * 1e6, 2),
             "flops_per_forward": flops, "algorithmic_bytes_per_launch": round(alg_bytes / len(calls))}
 
 
@@ -197,12 +205,92 @@ def measured_traffic():
     capture of the same forward (tools/profile_forward.py -> tools/ncu_traffic.py -> profiles/gemm_traffic.json)."""
     f = ROOT / "profiles" / "gemm_traffic.json"
     if not f.exists():
-        return None
+        return None, None
     try:
-        ks = [v for n, v in json.loads(f.read_text())["kernels"].items() if "lora_gemm_kernel" in n]
-        return round(sum(k["dram_read_bytes"] + k["dram_write_bytes"] for k in ks) / sum(k["launches"] for k in ks))
+        d = json.loads(f.read_text())
+        ks = [v for n, v in d["kernels"].items() if "lora_gemm_kernel" in n]
+        traffic = round(sum(k["dram_read_bytes"] + k["dram_write_bytes"] for k in ks) / sum(k["launches"] for k in ks))
+        pl = [p for p in d.get("per_launch", []) if "lora_gemm_kernel" in p.get("kernel", "") and "tc_active" in p]
+        tc = round(sum(p["tc_active"] * p["dur"] for p in pl) / sum(p["dur"] for p in pl), 1) if pl else None
+        return traffic, tc
     except Exception:
-        return None
+        return None, None
+
+
+def backward_roofline(engine, pk: dict, reps: int = 5) -> dict:
+    """The LoRA backward launches of one grad step (input-gradient GEMMs + the low-rank gradient kernels), replayed
+    back to back inside a CUDA graph: algorithmic FLOPs 2MNK (dx) + 4Mr(K+N) (dh, dx +=, dA, dB) per wrapped layer."""
+    from sliders_conceptmod_b200 import ops
+    calls = []
+    real_ig, real_g = ops.lora_input_grad, ops.lora_grad
+
+    def spy_ig(gy, wt, dh, at, cin, ksize=1, rank=0, **kw):
+        calls.append(("dx", tuple(gy.shape), tuple(wt.shape), ksize, rank if dh is not None else 0, gy.dtype, dict(kw)))
+        return real_ig(gy, wt, dh, at, cin, ksize, rank, **kw)
+
+    def spy_g(gy, x, h, b, s, ksize, dA, dB, accumulate=False, **kw):
+        calls.append(("grad", tuple(gy.shape), tuple(x.shape), ksize, b.shape[1], gy.dtype, dict(kw)))
+        return real_g(gy, x, h, b, s, ksize, dA, dB, accumulate=accumulate, **kw)
+
+    ops.lora_input_grad, ops.lora_grad = spy_ig, spy_g
+    try:
+        engine._body_train()
+    finally:
+        ops.lora_input_grad, ops.lora_grad = real_ig, real_g
+    torch.cuda.synchronize()
+    flops, args = 0.0, []
+    for kind, gs, other, k, r, dt, kw in calls:
+        M = 1
+        for d in gs[:-1]:
+            M *= d
+        N = gs[-1]
+        if kind == "dx":
+            cin, taps, _ = other
+            stride = kw.get("stride", 1)
+            flops += 2.0 * M * N * taps * cin + (2.0 * M * r * taps * cin if r else 0.0)
+            gy = torch.randn(gs, device="cuda", dtype=dt)
+            wt = torch.randn(other, device="cuda", dtype=dt) * 0.02
+            dh = torch.randn(M, 16, device="cuda", dtype=dt) if r else None
+            at = torch.randn(cin, taps, 16, device="cuda", dtype=dt) * 0.02 if r else None
+            args.append(("dx", gy, wt, dh, at, cin, k, r, kw))
+        else:
+            cin = other[-1]
+            taps = k * k
+            flops += 2.0 * M * r * N * 2 + 2.0 * M * r * taps * cin
+            gy = torch.randn(gs, device="cuda", dtype=dt)
+            x = torch.randn(other, device="cuda", dtype=dt)
+            Mx = x.numel() // cin
+            h = torch.randn(M, r, device="cuda", dtype=torch.float32)
+            b = torch.randn(N, r, device="cuda", dtype=dt) * 0.02
+            dA = torch.zeros(r, taps, cin, device="cuda", dtype=torch.float32)
+            dB = torch.zeros(N, r, device="cuda", dtype=torch.float32)
+            args.append(("grad", gy, x, h, b, k, dA, dB, kw))
+
+    def run():
+        for c in args:
+            if c[0] == "dx":
+                real_ig(c[1], c[2], c[3], c[4], c[5], c[6], c[7], **c[8])
+            else:
+                real_g(c[1], c[2], c[3], c[4], 0.25, c[5], c[6], c[7], accumulate=True, **c[8])
+    n0 = ops.launch_count()
+    run(); torch.cuda.synchronize()
+    launches = ops.launch_count() - n0
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        run()
+    g.replay(); torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        g.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    sec = e0.elapsed_time(e1) * 1e-3 / reps
+    achieved = flops / sec / 1e12
+    peak = float(pk.get("bf16_tflops_sustained", pk["bf16_tflops"]))
+    return {"bound": "tensor", "kernels": "lora_gemm_kernel (dx, extended-K) + low-rank gradient kernels", "achieved": round(achieved, 1),
+            "peak": peak, "unit": "TFLOP/s", "frac": round(achieved / peak, 4), "frac_burst": round(achieved / float(pk["bf16_tflops"]), 4),
+            "entry_calls": len(calls), "launches": int(launches), "ms": round(sec * 1e3, 3), "flops_per_backward": flops}
 
 
 def phase_breakdown(engine, reps: int = 5) -> dict:
@@ -234,76 +322,102 @@ def phase_breakdown(engine, reps: int = 5) -> dict:
     return out
 
 
+def config_dict(wl, n_modules: int, n_params: int, gpus: int) -> dict:
+    """`config` of the JSON line: identical for both arms (the reference arm runs OUR arm's configuration)."""
+    return {"workload": wl.name, "timesteps_to": TIMESTEPS_TO, "rank": wl.rank, "alpha": wl.alpha,
+            "resolution": wl.resolution, "batch_size": wl.batch_size, "lora_modules": n_modules,
+            "lora_params": n_params, "scheduler": wl.scheduler,
+            "parallelism": f"dp{gpus} (prompt pairs sharded, one flat-grad all-reduce)",
+            "l2": "working set (1.7 GB bf16 UNet weights) exceeds the 126 MB L2; no explicit flush"}
+
+
 # --------------------------------------------------------------------------------- CPU arm (oracle port)
-def cpu_reference_sample(wl_name: str, threads: int):
-    """Builds the reference's CPU path for the workload: the oracle arithmetic (oracle/slider_oracle.py) over the
-    same random-init SD-1.4-shaped UNet in fp32 on the host cores.  Returns a closure timing ONE bounded sample:
-    one adapter-on no-grad CFG forward (t_f) and one grad forward + loss + backward (t_fb)."""
-    from oracle import slider_oracle
-    from sliders_conceptmod_b200 import workload
-    from sliders_conceptmod_b200.lora import LoRANetwork
-    from sliders_conceptmod_b200.unet import UNet2DConditionModel
-    torch.set_num_threads(threads)
-    wl = workload.WORKLOADS[wl_name]
-    cfg = workload.unet_config(wl.family)
-    torch.manual_seed(0)
-    unet = UNet2DConditionModel(cfg).eval().requires_grad_(False)
-    net = LoRANetwork(unet, rank=wl.rank, alpha=wl.alpha, target_replace=workload.target_modules(wl.c3lier),
-                      train_method=wl.training_method)
-    slider_oracle.attach(net)
-    sched = slider_oracle.OracleScheduler("ddim")
-    sched.set_timesteps(1000)
-    pair = workload.prompt_pairs(wl, cfg.cross_attention_dim)[0]
-    lat = torch.randn(wl.batch_size, 4, wl.resolution // 8, wl.resolution // 8)
-    emb = torch.cat([pair["unconditional"], pair["target"]])
-    t = sched.timesteps[500]
+class OracleRun:
+    """The reference's iteration (conceptmod/textsliders/train_lora.py:155-309) restated with plain PyTorch ops
+    (oracle/slider_oracle.py) over the same random-init SD-1.4-shaped UNet.  On the host cores in fp32 it is the
+    CPU baseline / `--impl reference` arm; on the GPU in bf16 (`device="cuda"`, cuBLAS / cuDNN / SDPA eager, no
+    libslider kernel) it is the "reference arithmetic through PyTorch eager on the same B200" baseline of SURVEY 8d.
+    `src`: (unet, network) whose parameter values are copied, so that losses are comparable with the CUDA engine."""
 
-    def sample():
+    def __init__(self, wl_name: str, device="cpu", dtype=torch.float32, src=None, threads: int | None = None):
+        from oracle import slider_oracle
+        from sliders_conceptmod_b200 import workload
+        from sliders_conceptmod_b200.lora import LoRANetwork
+        from sliders_conceptmod_b200.unet import UNet2DConditionModel
+        if threads:
+            torch.set_num_threads(threads)
+        self.so, self.device, self.dtype = slider_oracle, torch.device(device), dtype
+        self.wl = wl = workload.WORKLOADS[wl_name]
+        cfg = workload.unet_config(wl.family)
+        torch.manual_seed(0)
+        with torch.device(self.device):
+            unet = UNet2DConditionModel(cfg)
+        unet.to(dtype=dtype).eval().requires_grad_(False)
+        if src is not None:
+            unet.load_state_dict(src[0].state_dict())
+        net = LoRANetwork(unet, rank=wl.rank, alpha=wl.alpha, target_replace=workload.target_modules(wl.c3lier),
+                          train_method=wl.training_method)
+        if src is not None:
+            net.load_state_dict({k: v.detach().to("cpu") for k, v in src[1].state_dict().items()})
+        net.to(self.device, dtype=dtype)
+        slider_oracle.attach(net)
+        self.unet, self.net, self.cfg = unet, net, cfg
+        self.sched = slider_oracle.OracleScheduler(wl.scheduler)
+        self.opt = torch.optim.AdamW(net.prepare_optimizer_params(), lr=wl.lr)
+        self.pairs = workload.prompt_pairs(wl, cfg.cross_attention_dim)
+
+    def iteration(self, pair: dict, latents: torch.Tensor, timesteps_to: int, round_to=None) -> tuple[float, float]:
+        """One full reference iteration incl. AdamW.  Returns (loss, seconds)."""
+        from sliders_conceptmod_b200 import unet as unet_mod
+        rd = (lambda x: x.to(round_to).to(self.dtype)) if round_to is not None else (lambda x: x.to(self.dtype))
+        emb = {k: rd(pair[k]).to(self.device) for k in ("target", "positive", "neutral", "unconditional")}
+        lat = rd(latents).to(self.device)
+        if self.device.type == "cuda":
+            torch.cuda.synchronize()
         t0 = time.perf_counter()
-        with torch.no_grad(), net:
-            slider_oracle.predict_noise(unet, sched, t, lat, emb, 3.0)
-        t1 = time.perf_counter()
-        with net:
-            tgt = slider_oracle.predict_noise(unet, sched, t, lat, emb, 1.0)
-        loss = slider_oracle.guidance_loss(tgt, lat, lat, lat, wl.guidance_scale, wl.action)
-        loss.backward()
-        t2 = time.perf_counter()
-        return t1 - t0, t2 - t1
-
-    return sample
-
-
-def step_seconds_from_sample(t_f: float, t_fb: float) -> float:
-    # train_lora.py:155-309: TIMESTEPS_TO denoise forwards + 3 predictions (no grad) + 1 grad forward/backward
-    return (TIMESTEPS_TO + 3) * t_f + t_fb
+        self.opt.zero_grad()
+        with unet_mod.torch_reference_mode():
+            loss, _ = self.so.train_iteration(self.unet, self.net, self.sched, emb, lat, timesteps_to, self.wl.guidance_scale,
+                                              self.wl.action, max_denoising_steps=self.wl.max_denoising_steps)
+        self.opt.step()
+        val = float(loss.item())          # train_lora.py:292 reads the loss back every iteration
+        return val, time.perf_counter() - t0
 
 
 def run_reference_arm(args):
+    """`--impl reference`: the oracle port on all host cores, REAL iterations (25 adapter-on CFG forwards + 3 adapter-off
+    predictions + grad forward / loss / backward + AdamW each), as many as fit `--cpu-budget-s`; `steps` in the
+    printed line is the number actually timed."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    sample = cpu_reference_sample(args.workload, threads)
+    run = OracleRun(args.workload, "cpu", torch.float32, threads=threads)
+    wl = run.wl
+    gen = torch.Generator().manual_seed(1234)
+    shape = (wl.batch_size, 4, wl.resolution // 8, wl.resolution // 8)
     t_start = time.perf_counter()
-    for _ in range(args.warmup):
-        sample()
-        if time.perf_counter() - t_start > args.cpu_budget_s * 0.3:
-            break
+    n_warm = 0
+    if args.warmup > 0:                      # one real iteration warms the allocator / thread pool
+        run.iteration(run.pairs[0], torch.randn(shape, generator=gen), TIMESTEPS_TO)
+        n_warm = 1
     times = []
-    t_meas = time.perf_counter()
-    for _ in range(args.steps):
-        times.append(step_seconds_from_sample(*sample()))
-        if time.perf_counter() - t_meas > args.cpu_budget_s * 0.7:
+    while len(times) < args.steps:
+        _, sec = run.iteration(run.pairs[len(times) % len(run.pairs)], torch.randn(shape, generator=gen), TIMESTEPS_TO)
+        times.append(sec)
+        spent = time.perf_counter() - t_start
+        if spent + 1.2 * sec > args.cpu_budget_s:
             break
     sec = sum(times) / len(times)
     val = 1.0 / sec
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": args.workload, "timesteps_to": TIMESTEPS_TO, "rank": 4, "resolution": 512},
+            "steps": len(times), "steps_requested": args.steps, "warmup": n_warm, "ms_per_step": sec * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": config_dict(wl, len(run.net.unet_loras), sum(p.numel() for p in run.net.parameters()), args.gpus),
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
-                             "sample": f"per step: 1 no-grad CFG UNet forward + 1 grad forward/loss/backward at full size, "
-                                       f"step time = {TIMESTEPS_TO + 3}*t_fwd + t_fwd_bwd; {len(times)} samples measured"},
+                             "sample": f"{len(times)} full iterations of the oracle port (oracle/slider_oracle.py: "
+                                       f"{TIMESTEPS_TO} adapter-on CFG forwards + 3 predictions + grad forward/loss/backward + "
+                                       f"AdamW), fp32, bounded by --cpu-budget-s {args.cpu_budget_s:.0f}"},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
@@ -358,8 +472,12 @@ def run_ours(args):
         host_loss.copy_(loss.reshape(1), non_blocking=True)
         torch.cuda.current_stream().synchronize()
 
+    loss0 = None
+    init_state = {k: v.detach().clone() for k, v in network.state_dict().items()} if rank == 0 else None
     for i in range(max(args.warmup, 3)):
-        engine.train_step(dev_lat[i % n_lat], TIMESTEPS_TO)
+        l = engine.train_step(dev_lat[i % n_lat], TIMESTEPS_TO)
+        if i == 0:
+            loss0 = float(l.item())      # step 0: weights at their initial values (checked against the oracle below)
     barrier()
     launches0 = engine.kernel_launches
     clocks = ClockSampler(local)
@@ -370,6 +488,10 @@ def run_ours(args):
     sec_e2e = timed(end_to_end, args.steps)
     clk = clocks.stop() if rank == 0 else None
     final_loss = float(host_loss.item())
+    # secondary: the reference's own draw timesteps_to = randint(1, max_denoising_steps)
+    # (train_lora.py:168-170), seeded per rank
+    draws = [int(torch.randint(1, wl.max_denoising_steps, (1,), generator=gen)) for _ in range(args.steps)]
+    sec_rand = timed(lambda i: engine.train_step(dev_lat[args.warmup + i], draws[i]), args.steps)
 
     if rank != 0:
         if world > 1:
@@ -384,34 +506,60 @@ def run_ours(args):
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": sec / args.steps * 1e3, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": args.workload, "timesteps_to": TIMESTEPS_TO, "rank": wl.rank, "alpha": wl.alpha,
-                       "resolution": wl.resolution, "batch_size": wl.batch_size, "lora_modules": len(network.unet_loras),
-                       "lora_params": int(network.flat_param.numel()), "scheduler": wl.scheduler,
-                       "parallelism": f"dp{world} (prompt pairs sharded, one flat-grad all-reduce)",
-                       "cuda_graphs": not args.no_graphs,
-                       "l2": "working set (1.7 GB bf16 UNet weights) exceeds the 126 MB L2; no explicit flush"},
+            "config": config_dict(wl, len(network.unet_loras), int(network.flat_param.numel()), world),
+            "cuda_graphs": not args.no_graphs,
             "e2e": {"value": value_e2e, "unit": UNIT, "h2d_bytes_per_step": lat_bytes, "d2h_bytes_per_step": 4,
                     "ms_per_step": sec_e2e / args.steps * 1e3},
             "gpu_launches": int(launches), "clocks": clk, "roofline": roof, "final_loss": final_loss,
-            "phases_ms": phases}
+            "phases_ms": phases,
+            "secondary": {"metric": "slider_train_steps_per_sec_random_timesteps", "value": world * args.steps / sec_rand,
+                          "unit": UNIT, "timesteps_to": "randint(1, %d) seeded 1234+rank" % wl.max_denoising_steps,
+                          "mean_timesteps_to_rank0": sum(draws) / len(draws)}}
+    if world == 1 and wl.family == "sd14":
+        try:
+            line["roofline_bwd"] = backward_roofline(engine, pk)
+        except Exception as e:      # measurement extra: never lose the headline line to it
+            line["roofline_bwd"] = {"error": str(e)[:200]}
     if not args.skip_cpu_baseline and world == 1:
+        # ONE real iteration of the oracle port on the host cores, on the SAME parameter values and the SAME step-0
+        # inputs as the CUDA engine: it is both the bounded CPU-baseline sample and the check of the benched loss.
         threads = os.cpu_count() or 1
-        sample = cpu_reference_sample(args.workload, threads)
-        t0 = time.perf_counter()
-        vals = []
-        while len(vals) < 2 and time.perf_counter() - t0 < 60.0:
-            vals.append(step_seconds_from_sample(*sample()))
-        s = min(vals)
+        src_net = type("S", (), {"state_dict": staticmethod(lambda: init_state)})
+        cpu = OracleRun(args.workload, "cpu", torch.float32, src=(unet, src_net), threads=threads)
+        loss_c, s = cpu.iteration(pair, host_lat[0], TIMESTEPS_TO, round_to=dtype)
+        rel = abs(loss0 - loss_c) / max(abs(loss_c), 1e-30)
         line["cpu_baseline"] = {"value": 1.0 / s, "unit": UNIT, "cores": threads, "kind": "port",
-                                "sample": f"oracle port, fp32, {len(vals)} samples of (1 no-grad CFG forward + 1 grad "
-                                          f"forward/backward) at full size; step = {TIMESTEPS_TO + 3}*t_fwd + t_fwd_bwd"}
+                                "sample": f"1 full iteration of the oracle port (fp32, {TIMESTEPS_TO} adapter-on CFG forwards + 3 "
+                                          f"predictions + grad forward/loss/backward + AdamW) on the bench's step-0 inputs"}
+        line["loss_check"] = {"step": 0, "oracle_fp32": loss_c, "cuda_bf16": loss0, "rel": rel,
+                              "note": "lora_up = 0 at init (lora.py:124) and target == neutral prompt, so the step-0 loss is "
+                                      "g^2 * mean((positive - unconditional)^2): a difference of two bf16 UNet evaluations"}
+        del cpu
+    if not args.skip_eager_baseline and world == 1:
+        # the reference's arithmetic (plain torch ops: cuBLAS / cuDNN / SDPA, no libslider kernel, no CUDA graph) on the
+        # same GPU in bf16 -- SURVEY 8d's "real bar"
+        src_net = type("S", (), {"state_dict": staticmethod(lambda: init_state)})
+        eager = OracleRun(args.workload, dev, dtype, src=(unet, src_net))
+        eager.iteration(pair, host_lat[0], TIMESTEPS_TO)
+        ts = [eager.iteration(pair, host_lat[1 + k], TIMESTEPS_TO)[1] for k in range(3)]
+        s = sum(ts) / len(ts)
+        line["gpu_eager_baseline"] = {"value": 1.0 / s, "unit": UNIT, "ms_per_step": s * 1e3, "ours_over_eager": value * s,
+                                      "kind": "oracle arithmetic = LoRAModule.forward as 3 torch ops per layer "
+                                              "(lora.py:134-138) + torch AdamW, PyTorch eager bf16 on the same GPU, 3 iterations"}
+        del eager
+        torch.cuda.empty_cache()
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+    chk = line.get("loss_check")
+    if chk is not None and not (chk["rel"] <= 0.5):
+        raise SystemExit(f"bench: step-0 loss {chk['cuda_bf16']} is not the oracle's {chk['oracle_fp32']}")
 
 
 def main():
+    global TIMESTEPS_TO
     args = parse_args()
+    TIMESTEPS_TO = args.timesteps_to
     if args.impl == "reference":
         run_reference_arm(args)
     else:

@@ -212,8 +212,10 @@ class SliderEngine:
                 self.xl["tgt"][key].copy_(torch.cat([cu, ct]))
                 self.xl["pred"][key].copy_(torch.cat([cu, cu, cu, cp, cn, cu]))
 
-    def train_step(self, latents: torch.Tensor, timesteps_to: int) -> torch.Tensor:
-        """latents: initial noise [b,4,h/8,w/8] (host or device).  Returns the device loss (no sync)."""
+    def train_step(self, latents: torch.Tensor, timesteps_to: int, optimizer: bool = True) -> torch.Tensor:
+        """latents: initial noise [b,4,h/8,w/8] (host or device).  Returns the device loss (no sync).
+        `optimizer=False` stops after the backward: the sample's gradient is left in `network.flat_grad` (gradient
+        accumulation over several samples before one `optimizer_step()`; the data-parallel equivalence check)."""
         n_den = self.cfg.max_denoising_steps
         t_tab, c_tab, s_tab, _ = self._table(n_den)
         self.lat.copy_(latents.to(self.dtype), non_blocking=True)
@@ -228,7 +230,8 @@ class SliderEngine:
         else:
             self._exec("predict", self._body_predict)
             self._exec("train", self._body_train)
-        self.optimizer_step()
+        if optimizer:
+            self.optimizer_step()
         return self.loss
 
     # ---- image-pair slider iteration (trainscripts/imagesliders/train_lora-scale.py:196-340) ------------------

@@ -229,7 +229,7 @@ class _QKVGroup:
 
     def __init__(self, loras, a_cat: torch.Tensor, b_cat: torch.Tensor):
         self.loras, self.a_cat, self.b_cat = loras, a_cat, b_cat
-        self._w_cat = None
+        self._w_cat, self._w_key = None, None
 
     def usable(self, x: torch.Tensor) -> bool:
         q = self.loras[0]
@@ -238,8 +238,14 @@ class _QKVGroup:
 
     def forward(self, x: torch.Tensor):
         q = self.loras[0]
-        if self._w_cat is None or self._w_cat.dtype != x.dtype or self._w_cat.device != x.device:
-            self._w_cat = torch.cat([m._packed_base() for m in self.loras]).contiguous()      # frozen: built once
+        # frozen weights: concatenated once, rebuilt when a base weight is replaced or modified in place
+        # (load_state_dict / .to() on the UNet after the first grouped forward)
+        key = tuple((m._org.weight.data_ptr(), m._org.weight._version, m._org.weight.dtype) for m in self.loras)
+        if self._w_cat is None or self._w_key != key:
+            if self._w_cat is not None:
+                ops._retired.append(self._w_cat)      # a captured graph may still reference the old buffer
+            self._w_cat = torch.cat([m._packed_base() for m in self.loras]).contiguous()
+            self._w_key = key
         x2 = x.reshape(-1, q._cin)
         if not x2.is_contiguous():
             x2 = x2.contiguous()

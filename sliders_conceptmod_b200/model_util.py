@@ -78,12 +78,20 @@ def _family(name_or_path: str) -> str:
     return "sdxl" if ("xl" in n) else ("tiny" if "tiny" in n else "sd14")
 
 
+def _seeded_unet(cfg: UNetConfig, seed: int) -> UNet2DConditionModel:
+    """The random-init stand-in replaces a *pretrained* checkpoint, so it is a fixed function of `seed` and must not
+    disturb the caller's RNG stream: the reference trainers are unseeded (train_lora.py:32-76) and a caller-provided
+    seed has to keep governing the LoRA init, the prompt-pair / timestep draws and the noise."""
+    with torch.random.fork_rng(devices=[]):
+        torch.manual_seed(seed)
+        return UNet2DConditionModel(cfg)
+
+
 def load_models(pretrained_model_name_or_path: str, scheduler_name: AVAILABLE_SCHEDULERS, v2: bool = False,
                 v_pred: bool = False, weight_dtype: torch.dtype = torch.float32, seed: int = 0):
     fam = _family(pretrained_model_name_or_path)
     cfg = {"sd14": UNetConfig.sd14, "sdxl": UNetConfig.sdxl, "tiny": UNetConfig.tiny}[fam]()
-    torch.manual_seed(seed)
-    unet = UNet2DConditionModel(cfg)
+    unet = _seeded_unet(cfg, seed)
     scheduler = create_noise_scheduler(scheduler_name, prediction_type="v_prediction" if v_pred else "epsilon")
     return SyntheticTokenizer(), SyntheticTextEncoder(cfg.cross_attention_dim), unet, scheduler
 
@@ -94,8 +102,7 @@ def load_models_xl(pretrained_model_name_or_path: str, scheduler_name: AVAILABLE
         cfg = dataclasses.replace(UNetConfig.tiny(64), addition_embed=True, use_linear_projection=True)
     else:
         cfg = UNetConfig.sdxl()
-    torch.manual_seed(seed)
-    unet = UNet2DConditionModel(cfg)
+    unet = _seeded_unet(cfg, seed)
     scheduler = create_noise_scheduler(scheduler_name)
     enc = SyntheticTextEncoder(cfg.cross_attention_dim, pooled_dim=1280)
     return [SyntheticTokenizer(), SyntheticTokenizer()], [enc, enc], unet, scheduler

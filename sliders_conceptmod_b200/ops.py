@@ -51,6 +51,21 @@ def _ws_key(device: torch.device):
 
 
 _gemm_ws: dict = {}
+# Scratch buffers that were outgrown.  A captured CUDA graph bakes the raw pointer of the buffer it was recorded with,
+# so a buffer that has ever been handed to a launch is never returned to the allocator: it is parked here and the
+# graph that references it keeps replaying over valid memory (a few MB per growth step, a handful of steps per process).
+_retired: list = []
+
+
+def _grow(table: dict, key, need: int, slack: int, zero: bool, device) -> torch.Tensor:
+    ws = table.get(key)
+    if ws is None or ws.numel() < need:
+        if ws is not None:
+            _retired.append(ws)
+        make = torch.zeros if zero else torch.empty
+        ws = make(max(need + slack, 1 << 20), dtype=torch.uint8, device=device)
+        table[key] = ws
+    return ws
 
 
 def _gemm_workspace(device: torch.device) -> torch.Tensor:
@@ -231,12 +246,7 @@ def groupnorm_nhwc(x: torch.Tensor, groups: int, gamma: torch.Tensor | None, bet
     assert x.is_contiguous()
     B, Cc = x.shape[0], x.shape[-1]
     hw = x.numel() // (B * Cc)
-    key = _ws_key(x.device)
-    need = lib().slider_groupnorm_workspace_bytes(int(B), int(groups))
-    ws = _gn_ws.get(key)
-    if ws is None or ws.numel() < need:
-        ws = torch.zeros(max(need, 1 << 20), dtype=torch.uint8, device=x.device)
-        _gn_ws[key] = ws
+    ws = _grow(_gn_ws, _ws_key(x.device), lib().slider_groupnorm_workspace_bytes(int(B), int(groups)), 0, True, x.device)
     if chan_add is not None:
         chan_add = chan_add.contiguous()
         assert chan_add.shape == (B, Cc) and chan_add.dtype == x.dtype
@@ -264,12 +274,8 @@ def groupnorm_nhwc_backward(gy: torch.Tensor, x: torch.Tensor, stats: torch.Tens
     assert x.is_contiguous() and gy.is_contiguous() and gy.shape == x.shape and gy.dtype == x.dtype
     B, Cc = x.shape[0], x.shape[-1]
     hw = x.numel() // (B * Cc)
-    key = _ws_key(x.device)
-    need = lib().slider_groupnorm_bwd_workspace_bytes(int(B), int(Cc), int(groups))
-    ws = _gn_bwd_ws.get(key)
-    if ws is None or ws.numel() < need:
-        ws = torch.empty(max(need, 1 << 20), dtype=torch.uint8, device=x.device)
-        _gn_bwd_ws[key] = ws
+    ws = _grow(_gn_bwd_ws, _ws_key(x.device), lib().slider_groupnorm_bwd_workspace_bytes(int(B), int(Cc), int(groups)),
+               0, False, x.device)
     dx = torch.empty_like(x)
     dadd = torch.empty(B, Cc, device=x.device, dtype=x.dtype) if (want_dadd and chan_add is not None) else None
     check(lib().slider_groupnorm_nhwc_backward(ptr(dx), ptr(dadd), ptr(gy), ptr(x), ptr(chan_add), ptr(gamma), ptr(beta),
@@ -349,12 +355,7 @@ _grad_ws: dict[int, torch.Tensor] = {}
 
 
 def _grad_workspace(device: torch.device, need: int) -> torch.Tensor:
-    key = _ws_key(device)
-    ws = _grad_ws.get(key)
-    if ws is None or ws.numel() < need:
-        ws = torch.empty(need + (1 << 20), dtype=torch.uint8, device=device)
-        _grad_ws[key] = ws
-    return ws
+    return _grow(_grad_ws, _ws_key(device), need, 1 << 20, False, device)
 
 
 def lora_grad(gy: torch.Tensor, x: torch.Tensor, h: torch.Tensor, b: torch.Tensor, s: float, ksize: int,

@@ -103,6 +103,24 @@ _DISABLED = set(filter(None, os.environ.get("SLIDER_DISABLE", "").split(",")))
 _ENABLED = set(filter(None, os.environ.get("SLIDER_ENABLE", "").split(",")))
 
 
+_TORCH_ONLY = False
+
+
+class torch_reference_mode:
+    """Inside this context every layer of the stand-in evaluates with plain PyTorch ops (cuBLAS / cuDNN / SDPA on a
+    GPU): no libslider kernel, no host-level fusion.  It is the substrate of the measurement baseline "the reference's
+    own arithmetic on the same GPU through PyTorch eager"  and of CPU runs; the product path never enters
+    it."""
+
+    def __enter__(self):
+        global _TORCH_ONLY
+        self.prev, _TORCH_ONLY = _TORCH_ONLY, True
+
+    def __exit__(self, *exc):
+        global _TORCH_ONLY
+        _TORCH_ONLY = self.prev
+
+
 def group_norm_act(norm: nn.GroupNorm, x: torch.Tensor, silu: bool, chan_add: torch.Tensor | None = None):
     """act(GroupNorm(x + chan_add[:, :, None, None])) for a [B,C,H,W] tensor.
 
@@ -110,13 +128,15 @@ def group_norm_act(norm: nn.GroupNorm, x: torch.Tensor, silu: bool, chan_add: to
     iteration), this is the fused NHWC kernel pair of libslider_b200 (`slider_groupnorm_nhwc`): the
     result is written directly in the channels-innermost layout the wrapped convolutions load.
     The plain PyTorch ops below serve the CPU oracle and the grad-recording forward."""
-    if x.is_cuda and not (torch.is_grad_enabled() and (x.requires_grad or (chan_add is not None and chan_add.requires_grad))):
+    if _TORCH_ONLY:
+        pass
+    elif x.is_cuda and not (torch.is_grad_enabled() and (x.requires_grad or (chan_add is not None and chan_add.requires_grad))):
         xn = x.permute(0, 2, 3, 1)
         if not xn.is_contiguous():
             xn = xn.contiguous()
         y = ops.groupnorm_nhwc(xn, norm.num_groups, norm.weight, norm.bias, norm.eps, silu, chan_add)
         return y.permute(0, 3, 1, 2)
-    if (x.is_cuda and "gn_train" not in _DISABLED and not norm.weight.requires_grad and x.shape[1] % 8 == 0
+    elif (x.is_cuda and "gn_train" not in _DISABLED and not norm.weight.requires_grad and x.shape[1] % 8 == 0
             and x.dtype == norm.weight.dtype):
         # grad-recording forward: same NHWC kernels + a fused NHWC backward (gamma / beta are frozen)
         y = _GroupNormNHWCFn.apply(x.permute(0, 2, 3, 1), chan_add, norm, silu)
@@ -152,14 +172,15 @@ class _GroupNormNHWCFn(torch.autograd.Function):
 
 def _no_grad_cuda(*ts) -> bool:
     first = ts[0]
-    return first.is_cuda and not (torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in ts))
+    return (first.is_cuda and not _TORCH_ONLY
+            and not (torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in ts)))
 
 
 def _sdpa(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor) -> torch.Tensor:
     """Attention core = library SDPA (not claimed).  torch's default backend choice is the fastest at the UNet's
     self-attention shapes; at two cross-attention shapes (77 keys) another library kernel is measured faster on B200
     (tools/bench_sdpa.py: head_dim 160 -> memory-efficient 7.9 vs 10.7 us, 4096 queries -> flash 15.5 vs 17.8 us)."""
-    if q.is_cuda and not torch.is_grad_enabled() and "sdpa_pick" not in _DISABLED and k.shape[-2] <= 128:
+    if q.is_cuda and not _TORCH_ONLY and not torch.is_grad_enabled() and "sdpa_pick" not in _DISABLED and k.shape[-2] <= 128:
         from torch.nn.attention import SDPBackend, sdpa_kernel
         pick = None
         if q.shape[-1] >= 128 and q.shape[-2] <= 1024:
@@ -620,11 +641,13 @@ class UNet2DConditionModel(nn.Module):
                 scales.append(0.0)
         key = (emb.shape[0], emb.dtype, emb.device) + tuple(
             t.data_ptr() if t is not None else 0 for l in layers for t in l)
-        plan = self.__dict__.get("_temb_plan")
-        if plan is None or plan[0] != key:
-            plan = (key, ops.SmallMultiPlan(emb.shape[0], emb.shape[1], emb.dtype, emb.device, layers))
-            self.__dict__["_temb_plan"] = plan
-        return ops.lora_forward_small_multi(emb, plan[1], scales)
+        # one plan per key, never dropped: a captured CUDA graph (engine 'denoise' at batch 2, 'predict' at batch 6)
+        # bakes the plan's output buffer and pointer tables, so a plan must outlive every graph recorded over it
+        plans = self.__dict__.setdefault("_temb_plans", {})
+        plan = plans.get(key)
+        if plan is None:
+            plan = plans[key] = ops.SmallMultiPlan(emb.shape[0], emb.shape[1], emb.dtype, emb.device, layers)
+        return ops.lora_forward_small_multi(emb, plan, scales)
 
     def enable_xformers_memory_efficient_attention(self):  # API parity (train_lora.py:68); SDPA is used
         return None
@@ -643,7 +666,7 @@ class UNet2DConditionModel(nn.Module):
         # every ResnetBlock2D applies the same SiLU to the same embedding before its time_emb_proj: do it once
         emb = F.silu(emb)
         emb._silu_applied = True
-        if emb.is_cuda and not torch.is_grad_enabled() and "temb_stream" not in _DISABLED:
+        if emb.is_cuda and not _TORCH_ONLY and not torch.is_grad_enabled() and "temb_stream" not in _DISABLED:
             self._prefetch_temb(emb)
         x = self.conv_in(sample.contiguous(memory_format=torch.channels_last))
         skips = [x]

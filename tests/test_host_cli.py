@@ -123,6 +123,24 @@ def test_trainer_builds_on_cpu_and_compute_fails_loudly(tmp_path):
         tr.iteration(0)
 
 
+def test_trainer_seed_governs_lora_init_not_the_unet(tmp_path):
+    """The random-init UNet stand-in is a fixed function of its own seed (it replaces a pretrained checkpoint) and is
+    built under fork_rng: the caller's seed keeps governing the LoRA initialisation and the loop's random draws."""
+    cfg = config_util.load_config_from_yaml(str(_write_yaml(tmp_path)))
+    prompts = prompt_util.load_prompts_from_yaml(cfg.prompts_file, [])
+    trs = [TextSliderTrainer(cfg, prompts, "cpu", seed=s) for s in (1, 2, 1)]
+    flat = [torch.cat([p.detach().flatten() for p in t.network.parameters()]) for t in trs]
+    unets = [torch.cat([p.detach().flatten() for p in t.unet.parameters()]) for t in trs]
+    assert torch.equal(unets[0], unets[1])                  # same substitute "checkpoint" whatever the seed
+    assert not torch.equal(flat[0], flat[1])                # different seeds: different lora_down init
+    assert torch.equal(flat[0], flat[2])                    # same seed: reproducible
+    draws = []
+    for s in (1, 2):
+        TextSliderTrainer(cfg, prompts, "cpu", seed=s)
+        draws.append(torch.randint(1, 50, (4,)).tolist())   # the loop's timesteps_to draws follow the seed too
+    assert draws[0] != draws[1]
+
+
 def test_xl_trainer_keeps_reference_quirks(tmp_path):
     cfg = config_util.load_config_from_yaml(str(_write_yaml(tmp_path, model="tiny-xl", scheduler="euler_a", negative=True)))
     cfg.train.cfg = 2.0
