@@ -191,6 +191,30 @@ int slider_guidance_loss(float* loss_out, void* grad, const void* t,
                          size_t ws_bytes, void* stream);
 
 /*
+ * Allocation-free variant of slider_guidance_loss.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops,
+ * harnesses that forbid allocation).  Same arithmetic, same kernel and same results as slider_guidance_loss; the
+ * reduction scratch (partial sums + ticket, 4752 bytes) is a file-scope `static __device__` array inside the
+ * library instead of a caller workspace, so the call allocates nothing (no cudaMalloc / cudaFree, no allocating
+ * library routine) -- it issues one 16-byte cudaMemsetAsync (the ticket word) and one kernel launch on `stream`.
+ *   limit   n_elem <= SLIDER_NOALLOC_MAX_ELEMS (2^28 elements, the largest size of the bandwidth sweep); larger
+ *           sizes return SLIDER_ERR_UNSUPPORTED with a message naming the limit
+ *           (slider_guidance_loss_noalloc_max_elems() returns it);
+ *   memory  every GPU that loads the library holds the 4752-byte array until exit;
+ *   sharing ALL calls on one device share that array and it keeps the last call's contents (the entry point clears
+ *           what must start at zero): calls that overlap on the GPU (different streams, graph branches, host threads
+ *           without stream ordering between them) RACE -- serialise them on one stream or use slider_guidance_loss
+ *           with separate workspaces.
+ * Inputs and outputs are still the caller's (loss_out one fp32, grad like t or NULL).
+ */
+#define SLIDER_NOALLOC_MAX_ELEMS (1ll << 28)
+int64_t slider_guidance_loss_noalloc_max_elems(void);
+int slider_guidance_loss_noalloc(float* loss_out, void* grad, const void* t,
+                                 const void* p, const void* n, const void* q,
+                                 int64_t n_elem, float g, int sign, int dtype,
+                                 void* stream);
+
+/*
  * Classifier-free guidance + affine scheduler step.  Replaces
  * train_util.predict_noise tail (conceptmod/textsliders/train_util.py:297-300)
  * and scheduler.step (train_util.py:324; DDIM restated in

@@ -52,6 +52,8 @@ _SIGNATURES = {
     "slider_concat_channels_nhwc": (C.c_int, [_vp, _vp, _vp, _i64, _i, _i, _i, _vp]),
     "slider_loss_workspace_bytes": (_sz, []),
     "slider_guidance_loss": (C.c_int, [_fp, _vp, _vp, _vp, _vp, _vp, _i64, _f, _i, _i, _vp, _sz, _vp]),
+    "slider_guidance_loss_noalloc": (C.c_int, [_fp, _vp, _vp, _vp, _vp, _vp, _i64, _f, _i, _i, _vp]),
+    "slider_guidance_loss_noalloc_max_elems": (_i64, []),
     "slider_cfg_step": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _f, _f, _f, _f, _fp, _i, _vp]),
     "slider_scale_by_device_scalar": (C.c_int, [_vp, _fp, _i64, _i, _vp]),
     "slider_adamw_flat": (C.c_int, [_vp, _fp, _fp, _fp, _i64, _f, _f, _f, _f, _f, _i, _fp, _i, _vp]),

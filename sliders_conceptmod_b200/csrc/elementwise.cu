@@ -1,6 +1,7 @@
 // HBM-bound kernels of the slider path: guidance loss (+gradient), CFG + scheduler
 // step, flat AdamW, gradient-norm clip coefficient.  One pass over the data each,
 // 16-byte vector accesses, grid sized in multiples of the SM count.
+#include <mutex>
 #include "common.cuh"
 
 namespace slider {
@@ -233,6 +234,36 @@ clip_coef_kernel(float* __restrict__ out, const float* __restrict__ grad, int64_
 
 static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
+// ---- allocation-free guidance loss: scratch in a file-scope device array --------------------------
+// Reduction scratch of slider_guidance_loss_noalloc: kMaxBlocks partial-sum slots + the ticket word, held by every
+// GPU that loads the library until exit (4752 bytes).  In host code `g_noalloc_scratch` is only a stand-in for the
+// symbol: its device address comes from cudaGetSymbolAddress, once per device, with that device current.
+static __device__ __align__(256) float g_noalloc_scratch[kMaxBlocks + 4];
+constexpr int kNoAllocMaxDevices = 64;
+
+static int noalloc_scratch_ptr(float** out) {
+  static std::mutex mu;
+  static float* per_device[kNoAllocMaxDevices] = {nullptr};
+  int dev = -1;
+  SLIDER_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kNoAllocMaxDevices) {
+    set_error("guidance_loss_noalloc: device ordinal %d outside 0..%d", dev, kNoAllocMaxDevices - 1);
+    return SLIDER_ERR_UNSUPPORTED;
+  }
+  std::lock_guard<std::mutex> lock(mu);
+  if (per_device[dev] == nullptr) {
+    float* ptr = nullptr;
+    SLIDER_CUDA(cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch));
+    if (ptr == nullptr) {
+      set_error("guidance_loss_noalloc: cudaGetSymbolAddress returned a null device address");
+      return SLIDER_ERR_CUDA;
+    }
+    per_device[dev] = ptr;
+  }
+  *out = per_device[dev];
+  return SLIDER_OK;
+}
+
 }  // namespace slider
 
 using namespace slider;
@@ -261,6 +292,37 @@ int slider_guidance_loss(float* loss_out, void* grad, const void* t, const void*
     return launch_loss<__nv_bfloat16>(loss_out, grad, t, p, n, q, n_elem, sg, (float*)ws, st);
   set_error("guidance_loss: unsupported dtype %d", dtype);
   return SLIDER_ERR_UNSUPPORTED;
+}
+
+int64_t slider_guidance_loss_noalloc_max_elems(void) { return (int64_t)SLIDER_NOALLOC_MAX_ELEMS; }
+
+int slider_guidance_loss_noalloc(float* loss_out, void* grad, const void* t, const void* p, const void* n,
+                                 const void* q, int64_t n_elem, float g, int sign, int dtype, void* stream) {
+  SLIDER_CHECK_ARG(loss_out && t && n, "guidance_loss_noalloc: null pointer");
+  SLIDER_CHECK_ARG((p == nullptr) == (q == nullptr), "guidance_loss_noalloc: p and q must both be set or both NULL");
+  SLIDER_CHECK_ARG(n_elem > 0, "guidance_loss_noalloc: n_elem must be positive (got %lld)", (long long)n_elem);
+  if (n_elem > (int64_t)SLIDER_NOALLOC_MAX_ELEMS) {
+    set_error("guidance_loss_noalloc: n_elem %lld exceeds the built-in scratch's limit of %lld elements; use "
+              "slider_guidance_loss with a caller workspace", (long long)n_elem, (long long)SLIDER_NOALLOC_MAX_ELEMS);
+    return SLIDER_ERR_UNSUPPORTED;
+  }
+  SLIDER_CHECK_ARG(sign == 1 || sign == -1, "guidance_loss_noalloc: sign must be +1 or -1");
+  SLIDER_CHECK_ARG(aligned16(t) && aligned16(n) && aligned16(p) && aligned16(q) && aligned16(grad),
+                   "guidance_loss_noalloc: tensors must be 16-byte aligned");
+  if (dtype != SLIDER_F32 && dtype != SLIDER_BF16) {
+    set_error("guidance_loss_noalloc: unsupported dtype %d", dtype);
+    return SLIDER_ERR_UNSUPPORTED;
+  }
+  float* ws = nullptr;
+  int rc = noalloc_scratch_ptr(&ws);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  // the array keeps the previous call's contents: the ticket word must start at zero (the partial slots are
+  // overwritten before they are read).  A stream-ordered 16-byte memset; nothing is allocated.
+  SLIDER_CUDA(cudaMemsetAsync(ws + kMaxBlocks, 0, 4 * sizeof(float), st));
+  const float sg = (float)sign * g;
+  if (dtype == SLIDER_F32) return launch_loss<float>(loss_out, grad, t, p, n, q, n_elem, sg, ws, st);
+  return launch_loss<__nv_bfloat16>(loss_out, grad, t, p, n, q, n_elem, sg, ws, st);
 }
 
 int slider_cfg_step(void* out, const void* x, const void* eps_u, const void* eps_c, const void* noise,
