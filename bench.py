@@ -109,10 +109,10 @@ def fused_gemm_roofline(engine, pk: dict, reps: int = 5) -> dict:
     calls = []
     real, real_grouped = ops.lora_forward, ops.lora_forward_grouped
 
-    def spy(x, w, bias, a, b, s, ksize=1, want_h=False, residual=None):
+    def spy(x, w, bias, a, b, s, ksize=1, want_h=False, residual=None, stride=1):
         calls.append(("single", tuple(x.shape), tuple(w.shape), bias is not None, None if a is None else a.shape[0], s,
-                      ksize, x.dtype, residual is not None))
-        return real(x, w, bias, a, b, s, ksize=ksize, want_h=want_h, residual=residual)
+                      (ksize, stride), x.dtype, residual is not None))
+        return real(x, w, bias, a, b, s, ksize=ksize, want_h=want_h, residual=residual, stride=stride)
 
     def spy_grouped(x, w_cat, a_cat, b_cat, groups, s):
         calls.append(("grouped", tuple(x.shape), tuple(w_cat.shape), False, a_cat.shape[0], s, groups, x.dtype, False))
@@ -143,11 +143,14 @@ def fused_gemm_roofline(engine, pk: dict, reps: int = 5) -> dict:
             args.append(("multi", torch.randn(xs, device="cuda", dtype=dt), plan, s))
             continue
         es = 2 if dt == torch.bfloat16 else 4
+        stride = 1
+        if kind == "single":
+            k, stride = k
+        M = 1                     # OUTPUT pixels (a stride-2 layer produces a quarter of its input's)
+        for i, d in enumerate(xs[:-1]):
+            M *= ((d - 1) // 2 + 1) if (stride == 2 and len(xs) == 4 and i in (1, 2)) else d
         alg_bytes += es * (float(torch.Size(xs).numel()) + float(torch.Size(ws).numel()) +
-                           float(torch.Size(xs[:-1]).numel()) * ws[0] * (2 if has_res else 1))
-        M = 1
-        for d in xs[:-1]:
-            M *= d
+                           float(M) * ws[0] * (2 if has_res else 1))
         N, T, C = ws
         x = torch.randn(xs, device="cuda", dtype=dt)
         w = torch.randn(ws, device="cuda", dtype=dt) * 0.02
@@ -163,7 +166,7 @@ def fused_gemm_roofline(engine, pk: dict, reps: int = 5) -> dict:
         b = torch.randn(N, r, device="cuda", dtype=dt) * 0.02 if r else None
         bias = torch.zeros(N, device="cuda", dtype=dt) if has_b else None
         res = torch.zeros(*xs[:-1], N, device="cuda", dtype=dt) if has_res else None
-        args.append(("single", x, w, bias, a, b, s, k, res))
+        args.append(("single", x, w, bias, a, b, s, k, res, stride))
 
     def run():
         for c in args:
@@ -172,7 +175,7 @@ def fused_gemm_roofline(engine, pk: dict, reps: int = 5) -> dict:
             elif c[0] == "multi":
                 real_multi(c[1], c[2], c[3])
             else:
-                real(c[1], c[2], c[3], c[4], c[5], c[6], ksize=c[7], residual=c[8])
+                real(c[1], c[2], c[3], c[4], c[5], c[6], ksize=c[7], residual=c[8], stride=c[9])
     # capture the launch sequence in a CUDA graph so host-side descriptor encoding is not in the timing
     run(); torch.cuda.synchronize()
     g = torch.cuda.CUDAGraph()
@@ -222,7 +225,11 @@ def backward_roofline(engine, pk: dict, reps: int = 5) -> dict:
     back to back inside a CUDA graph: algorithmic FLOPs 2MNK (dx) + 4Mr(K+N) (dh, dx +=, dA, dB) per wrapped layer."""
     from sliders_conceptmod_b200 import ops
     calls = []
-    real_ig, real_g = ops.lora_input_grad, ops.lora_grad
+    real_ig, real_g, real_f = ops.lora_input_grad, ops.lora_grad, ops.lora_backward_1x1
+
+    def spy_f(gy, x, h, wt, a, b, s, dA, dB, accumulate=False, bt=None):
+        calls.append(("fused", tuple(gy.shape), tuple(wt.shape), 1, b.shape[1], gy.dtype, {"train": dA is not None}))
+        return real_f(gy, x, h, wt, a, b, s, dA, dB, accumulate=accumulate, bt=bt)
 
     def spy_ig(gy, wt, dh, at, cin, ksize=1, rank=0, **kw):
         calls.append(("dx", tuple(gy.shape), tuple(wt.shape), ksize, rank if dh is not None else 0, gy.dtype, dict(kw)))
@@ -232,11 +239,11 @@ def backward_roofline(engine, pk: dict, reps: int = 5) -> dict:
         calls.append(("grad", tuple(gy.shape), tuple(x.shape), ksize, b.shape[1], gy.dtype, dict(kw)))
         return real_g(gy, x, h, b, s, ksize, dA, dB, accumulate=accumulate, **kw)
 
-    ops.lora_input_grad, ops.lora_grad = spy_ig, spy_g
+    ops.lora_input_grad, ops.lora_grad, ops.lora_backward_1x1 = spy_ig, spy_g, spy_f
     try:
         engine._body_train()
     finally:
-        ops.lora_input_grad, ops.lora_grad = real_ig, real_g
+        ops.lora_input_grad, ops.lora_grad, ops.lora_backward_1x1 = real_ig, real_g, real_f
     torch.cuda.synchronize()
     flops, args = 0.0, []
     for kind, gs, other, k, r, dt, kw in calls:
@@ -244,6 +251,19 @@ def backward_roofline(engine, pk: dict, reps: int = 5) -> dict:
         for d in gs[:-1]:
             M *= d
         N = gs[-1]
+        if kind == "fused":       # 1x1: dx + g in one GEMM launch, dA + dB in one reduction launch
+            cin = other[0]
+            flops += 2.0 * M * N * cin + 2.0 * M * r * (N + cin) + (2.0 * M * r * (N + cin) if kw["train"] else 0.0)
+            gy = torch.randn(gs, device="cuda", dtype=dt)
+            x = torch.randn(*gs[:-1], cin, device="cuda", dtype=dt)
+            h = torch.randn(M, r, device="cuda", dtype=torch.float32)
+            wt = torch.randn(other, device="cuda", dtype=dt) * 0.02
+            a = torch.randn(r, 1, cin, device="cuda", dtype=dt) * 0.02
+            b = torch.randn(N, r, device="cuda", dtype=dt) * 0.02
+            dA = torch.zeros(r, 1, cin, device="cuda", dtype=torch.float32) if kw["train"] else None
+            dB = torch.zeros(N, r, device="cuda", dtype=torch.float32) if kw["train"] else None
+            args.append(("fused", gy, x, h, wt, a, b, dA, dB, b.t().contiguous()))
+            continue
         if kind == "dx":
             cin, taps, _ = other
             stride = kw.get("stride", 1)
@@ -268,7 +288,9 @@ def backward_roofline(engine, pk: dict, reps: int = 5) -> dict:
 
     def run():
         for c in args:
-            if c[0] == "dx":
+            if c[0] == "fused":
+                real_f(c[1], c[2], c[3], c[4], c[5], c[6], 0.25, c[7], c[8], accumulate=True, bt=c[9])
+            elif c[0] == "dx":
                 real_ig(c[1], c[2], c[3], c[4], c[5], c[6], c[7], **c[8])
             else:
                 real_g(c[1], c[2], c[3], c[4], 0.25, c[5], c[6], c[7], accumulate=True, **c[8])
@@ -288,7 +310,7 @@ def backward_roofline(engine, pk: dict, reps: int = 5) -> dict:
     sec = e0.elapsed_time(e1) * 1e-3 / reps
     achieved = flops / sec / 1e12
     peak = float(pk.get("bf16_tflops_sustained", pk["bf16_tflops"]))
-    return {"bound": "tensor", "kernels": "lora_gemm_kernel (dx, extended-K) + low-rank gradient kernels", "achieved": round(achieved, 1),
+    return {"bound": "tensor", "kernels": "lora_gemm_kernel (1x1: dx + gy.B fused; 3x3: dx extended-K, dh) + colreduce_kernel (dA, dB)", "achieved": round(achieved, 1),
             "peak": peak, "unit": "TFLOP/s", "frac": round(achieved / peak, 4), "frac_burst": round(achieved / float(pk["bf16_tflops"]), 4),
             "entry_calls": len(calls), "launches": int(launches), "ms": round(sec * 1e3, 3), "flops_per_backward": flops}
 

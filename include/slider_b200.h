@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define SLIDER_ABI_VERSION 2
+#define SLIDER_ABI_VERSION 3
 
 enum slider_dtype { SLIDER_F32 = 0, SLIDER_BF16 = 1 };
 
@@ -46,7 +46,9 @@ int64_t slider_launch_count(void);
 /* ---------------------------------------------------------------------------
  * Layer geometry shared by the LoRA entry points.
  * A Linear layer is the degenerate conv: batch=1, height=1, width=M, kh=kw=1.
- * Only stride-1 convolutions with symmetric padding are handled here.
+ * Symmetric padding; stride 1, or stride 2 for a 3x3 kernel on the forward entry points (the three Downsample2D
+ * convolutions, lora.py:100-114 builds lora_down with the base conv's stride): height / width are the INPUT extent,
+ * the output is [batch, (height-1)/2+1, (width-1)/2+1, cout] and h_out has one row per OUTPUT pixel.
  * ------------------------------------------------------------------------- */
 typedef struct slider_layer_geom {
   int32_t dtype;   /* enum slider_dtype of x / W / A / B / y                 */
@@ -58,6 +60,7 @@ typedef struct slider_layer_geom {
   int32_t kh, kw;  /* 1x1 or 3x3                                             */
   int32_t pad;     /* 0 for 1x1, 1 for 3x3                                   */
   int32_t rank;    /* LoRA rank r, 0..16                                     */
+  int32_t stride;  /* 0 or 1: stride 1;  2: stride 2 (3x3, forward only)     */
 } slider_layer_geom;
 
 /*
@@ -134,19 +137,52 @@ int slider_lora_forward_small_multi(int dtype, int layers, int M, int K, int ran
  *     dh = s * gy . B          [M, rank]  -> dh_out (element dtype, padded to 16)
  *     dB = s * gy^T . h        [cout, rank]
  *     dA = dh^T (*) x          [rank, kh*kw, cin]
- *   gy     [batch,height,width,cout]  upstream gradient
- *   h      [M, rank] fp32 saved by the forward
- *   dA,dB  fp32 accumulators; `accumulate` != 0 adds to their current content
- *          (two-sided image-slider objective, train_lora-scale.py:303-332)
+ *   gy     [batch, out_h, out_w, cout]  upstream gradient (OUTPUT extent; stride 2 is accepted here)
+ *   x      [batch, height, width, cin]
+ *   h      [M, rank] fp32 saved by the forward (M = output pixels)
+ *   dA,dB  fp32; `accumulate` != 0 adds to their current content (flat gradient buffer; two-sided image-slider
+ *          objective, train_lora-scale.py:303-332), 0 overwrites.  Both NULL: only dh is produced (adapter
+ *          frozen, the input gradient still needs it).
  *   dh_out [M, 16] element dtype, columns >= rank are zero; consumed by
  *          slider_lora_input_grad
- *   ws     caller workspace of slider_lora_grad_workspace_bytes(g) bytes
+ *   ws     caller workspace of slider_lora_grad_workspace_bytes(g) bytes, 256-byte aligned; its first 4096
+ *          bytes are zero-filled ONCE by the caller (ticket words; the kernels leave them zero), the rest is
+ *          don't-care.
+ * The reductions over pixels are deterministic (per-CTA partial sums, finished in a fixed order by the last
+ * CTA of a channel block; no floating-point atomics).
  */
 size_t slider_lora_grad_workspace_bytes(const slider_layer_geom* g);
 int slider_lora_grad(const slider_layer_geom* g, float* dA, float* dB,
                      void* dh_out, const void* gy, const void* x,
                      const float* h, const void* B, float s, int accumulate,
                      void* ws, size_t ws_bytes, void* stream);
+
+/*
+ * Whole backward of a 1x1 / Linear adapter layer in two launches (same autograd as above):
+ *   launch 1: the forward tcgen05 kernel on the transposed problem -- activations gy, weights Wt, "lora_down" = B^T,
+ *             "lora_up" = A read as its own transpose -- gives  dx = gy . W + s * (gy . B) . A  and
+ *             g_buf = gy . B  (fp32 [M, rank], unscaled);
+ *   launch 2: one reduction kernel gives  dB = s * gy^T . h  and  dA = s * g_buf^T . x  (deterministic).
+ *   Wt   [cin, 1, cout]   slider_pack_wt of the frozen base weight
+ *   Bt   [>= rank, cout]  B^T, or NULL: packed here from B (one more small launch; slider_transpose_batch builds the
+ *                         B^T of every layer of a network in one launch)
+ *   A    [rank, cin] lora_down.weight;  B [cout, rank] lora_up.weight (only read when Bt == NULL)
+ *   dA, dB NULL: only dx (frozen adapter).  ws as for slider_lora_grad.
+ */
+int slider_lora_backward_1x1(const slider_layer_geom* g, void* dx, float* dA, float* dB, float* g_buf,
+                             const void* gy, const void* x, const float* h, const void* Wt, const void* Bt,
+                             const void* A, const void* B, float s, int accumulate, void* ws, size_t ws_bytes,
+                             void* stream);
+
+/* Batched small transposes, one launch: entry e writes dst[c][r] = src[r][c] for src [rows, cols].  `table_dev` is a
+ * DEVICE array of `entries` records; max_elems = the largest rows*cols (sizes the grid). */
+typedef struct slider_transpose_entry {
+  const void* src;
+  void* dst;
+  int32_t rows, cols;
+} slider_transpose_entry;
+int slider_transpose_batch(const slider_transpose_entry* table_dev, int entries, int max_elems, int dtype,
+                           void* stream);
 
 /*
  * Input gradient:  dx = convT(gy, W) + convT(dh, A)   (one tcgen05 launch).

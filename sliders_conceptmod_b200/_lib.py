@@ -20,7 +20,7 @@ class LayerGeom(C.Structure):
     """Mirror of `slider_layer_geom`."""
 
     _fields_ = [(n, C.c_int32) for n in
-                ("dtype", "batch", "height", "width", "cin", "cout", "kh", "kw", "pad", "rank")]
+                ("dtype", "batch", "height", "width", "cin", "cout", "kh", "kw", "pad", "rank", "stride")]
 
 
 _vp, _fp, _i64, _f, _i, _sz = C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_int, C.c_size_t
@@ -38,6 +38,8 @@ _SIGNATURES = {
     "slider_lora_forward_small_multi": (C.c_int, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "slider_lora_grad_workspace_bytes": (_sz, [_G]),
     "slider_lora_grad": (C.c_int, [_G, _fp, _fp, _vp, _vp, _vp, _fp, _vp, _f, _i, _vp, _sz, _vp]),
+    "slider_lora_backward_1x1": (C.c_int, [_G, _vp, _fp, _fp, _fp, _vp, _vp, _fp, _vp, _vp, _vp, _vp, _f, _i, _vp, _sz, _vp]),
+    "slider_transpose_batch": (C.c_int, [_vp, _i, _i, _i, _vp]),
     "slider_lora_pack_at": (C.c_int, [_G, _vp, _vp, _vp]),
     "slider_lora_input_grad": (C.c_int, [_G, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "slider_pack_wt": (C.c_int, [_G, _vp, _vp, _vp]),

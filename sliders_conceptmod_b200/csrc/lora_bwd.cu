@@ -1,9 +1,15 @@
-// Low-rank side of the backward pass (bandwidth-class work):
-//   dh[p, j]  = s * sum_n gy[p, n] * B[n, j]      tensor cores: the forward GEMM kernel on gy x (s B)^T
-//   colreduce dB[n, j]     = s * sum_p gy[p, n] * h[p, j]
-//             dA[j, t, c]  =     sum_p x[p + d(t), c] * dh[p, j]
-//   pack_at / pack_wt      operand re-layouts for the input-gradient GEMM.
-// The contraction over pixels is split over CTAs and finished with fp32 atomics.
+// Backward of the adapter layer (autograd of lora.py:134-138).
+//
+//   1x1 / Linear layers (100 of the 150 wrapped layers of SD-1.4):  slider_lora_backward_1x1
+//     ONE launch of the forward tcgen05 kernel on (x := gy, W := Wt, lora_down := B^T, lora_up := A^T) gives
+//         dx = gy . W + s * (gy . B) . A      and      g = gy . B   (fp32 [M, r], the kernel's h output)
+//     and ONE reduction launch gives both   dB = s * gy^T . h   and   dA = s * g^T . x.
+//   3x3 layers:  slider_lora_grad (dh = s * gy . B on the tensor cores, then the two reductions) followed by
+//     slider_lora_input_grad (extended-K GEMM).
+//
+// The reductions over pixels (colreduce_kernel) are bandwidth-class work and DETERMINISTIC: every CTA writes its
+// partial sums to the workspace, and the last CTA of a channel block (ticket) adds them up in chunk order -- no
+// floating-point atomics, so two runs give bit-identical LoRA gradients.
 #include "common.cuh"
 
 namespace slider {
@@ -18,25 +24,57 @@ __global__ void pack_bt_kernel(T* __restrict__ Bt, const T* __restrict__ Bup, in
   Bt[i] = j < rank ? Elem<T>::from_f(s * Elem<T>::to_f(Bup[(size_t)n * rank + j])) : Elem<T>::from_f(0.f);
 }
 
+// Batched form for a whole network: entry e transposes src [rows, cols] into dst [cols, rows] (the B^T operands of
+// every 1x1 layer's fused backward launch, rebuilt once per optimizer step from the flat parameter buffer).
+template <typename T>
+__global__ void transpose_batch_kernel(const slider_transpose_entry* __restrict__ tab, int entries) {
+  const int e = blockIdx.y;
+  if (e >= entries) return;
+  const slider_transpose_entry en = tab[e];
+  const T* __restrict__ src = reinterpret_cast<const T*>(en.src);
+  T* __restrict__ dst = reinterpret_cast<T*>(en.dst);
+  const int total = en.rows * en.cols;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int c = i / en.rows, r = i - c * en.rows;      // dst index i = c * rows + r
+    dst[i] = src[(size_t)r * en.cols + c];
+  }
+}
+
 // --------------------------------------------------------------- colreduce
-// out[c, j, t] (generic strides) += scale * sum_p X[p + d(t), c] * V[p, j0 + j],  j = 0..3
+// out[c, j, t] (generic strides) (+)= scale * sum_p X[stride*p + d(t), c] * V[p, j0 + j],  j = 0..3
 // HBM-bound on X (gy for dB, x for dA), which is read exactly once with vector loads:
 //   * a thread owns CH adjacent channels (16-byte loads for 1x1, 8/16-byte for 3x3) and keeps
 //     TAPS x CH x 4 fp32 accumulators; PL pixel lanes share a CTA;
-//   * the V rows (h fp32 / dh) of the CTA's pixel range (+ halo for 3x3) are staged once in shared memory
+//   * the V rows (h / dh) the CTA's pixel range meets (+ halo for 3x3) are staged once in shared memory
 //     as float4, so the inner loop is one broadcast LDS.128 per tap;
 //   * a CTA owns a narrow channel slice (4 vector threads) and 64 pixel lanes; lanes are reduced by warp
-//     shuffles, warps through shared memory, then one fp32 atomicAdd per output element and CTA.
-struct ColReduceParams {
-  int B, H, W, C;        // X is [B,H,W,C]
-  int kw, pad;
-  int rank, vstride;     // V is [pixels, vstride]
-  int NVT;               // channel-vector threads per pixel lane (covering CB = NVT*CH channels per block)
-  int PL;                // pixel lanes
-  int cpi;               // chunks per image
-  int ppc;               // pixels per chunk
+//     shuffles, warps through shared memory; the CTA's sums go to the workspace and the LAST CTA of the channel
+//     block (ticket) adds all chunks' sums in chunk order and updates `out` (deterministic, no float atomics).
+// One launch may carry TWO problems over the same pixels (1x1 layers: dB from (gy, h) and dA from (x, g)):
+// blockIdx.y selects the problem and its channel block.
+struct ColProblem {
+  const void* X;         // [B,H,W,C]
+  const void* V;         // [B*VH*VW, vstride]
+  float* out;
+  int C, cblocks;        // channels; channel blocks (of 4 * CH channels) of this problem
+  int vstride;
   int64_t oc, oj, ot;    // output strides for (channel, rank index, tap)
   float scale;
+};
+struct ColReduceParams {
+  int B, H, W;           // X pixels
+  int VH, VW, stride;    // V pixels; X pixel = stride * V pixel + d(tap)
+  int kw, pad;
+  int rank;
+  int PL;                // pixel lanes
+  int cpi;               // chunks per image
+  int ppc;               // X pixels per chunk
+  int vmax;              // V rows the staging area holds
+  int accumulate;        // out += result instead of out = result
+  int nprob;
+  ColProblem prob[2];
+  float* partial;        // [channel block][chunk][4 * NACC]
+  unsigned* tickets;     // [channel block], zero on entry and on exit
 };
 
 template <typename T, int CH> struct ChanVec;
@@ -63,20 +101,35 @@ template <> struct ChanVec<float, 4> {
   }
 };
 
+constexpr int CR_NVT = 4;          // channel-vector threads per pixel lane (the shuffle reduction relies on it)
+constexpr int CR_MAX_TICKETS = 1024;
+
 template <typename T, typename VT, int TAPS, int CH>
 __global__ void __launch_bounds__(256)
-colreduce_kernel(float* __restrict__ out, const T* __restrict__ X, const VT* __restrict__ V,
-                 const ColReduceParams p, int j0) {
+colreduce_kernel(const ColReduceParams p, int j0) {
   extern __shared__ __align__(16) float cr_smem[];
-  const int HW = p.H * p.W;
+  __shared__ int s_last;
+  const int pi = (p.nprob > 1 && (int)blockIdx.y >= p.prob[0].cblocks) ? 1 : 0;
+  const ColProblem& pr = p.prob[pi];
+  const int yblk = (int)blockIdx.y - (pi ? p.prob[0].cblocks : 0);
+  const T* __restrict__ X = reinterpret_cast<const T*>(pr.X);
+  const VT* __restrict__ V = reinterpret_cast<const VT*>(pr.V);
+  const int HW = p.H * p.W, VHW = p.VH * p.VW;
   const int img = blockIdx.x / p.cpi, chunk = blockIdx.x - img * p.cpi;
   const int q0 = chunk * p.ppc;
   const int q1 = min(HW, q0 + p.ppc);
-  const int halo = TAPS > 1 ? p.pad * (p.W + 1) : 0;
-  const int v0 = max(0, q0 - halo), v1 = min(HW, q1 + halo);   // V pixels staged: [v0, v1) of image img
+  // V pixels staged: [v0, v1) of image img -- every V pixel an X pixel of [q0, q1) can meet through a tap
+  int v0, v1;
+  if (TAPS == 1) { v0 = q0; v1 = q1; }
+  else if (p.stride == 1) { const int halo = p.pad * (p.W + 1); v0 = max(0, q0 - halo); v1 = min(HW, q1 + halo); }
+  else {
+    const int h_lo = q0 / p.W, h_hi = (q1 - 1) / p.W;
+    v0 = (max(0, h_lo - p.pad) / p.stride) * p.VW;
+    v1 = min(p.VH, (h_hi + p.pad) / p.stride + 1) * p.VW;
+  }
   float4* s_v = reinterpret_cast<float4*>(cr_smem);
   for (int i = threadIdx.x; i < v1 - v0; i += blockDim.x) {
-    const VT* vp = V + ((size_t)img * HW + v0 + i) * p.vstride + j0;
+    const VT* vp = V + ((size_t)img * VHW + v0 + i) * pr.vstride + j0;
     float4 f;
     f.x = Elem<VT>::to_f(vp[0]);
     f.y = (j0 + 1 < p.rank) ? Elem<VT>::to_f(vp[1]) : 0.f;
@@ -85,9 +138,9 @@ colreduce_kernel(float* __restrict__ out, const T* __restrict__ X, const VT* __r
     s_v[i] = f;
   }
   __syncthreads();
-  const int pl = threadIdx.x / p.NVT, v = threadIdx.x - pl * p.NVT;
-  const int c = (blockIdx.y * p.NVT + v) * CH;
-  const bool active = pl < p.PL && c < p.C;
+  const int pl = threadIdx.x / CR_NVT, v = threadIdx.x - pl * CR_NVT;
+  const int c = (yblk * CR_NVT + v) * CH;
+  const bool active = pl < p.PL && c < pr.C;
   float acc[TAPS][CH][4];
 #pragma unroll
   for (int t = 0; t < TAPS; ++t)
@@ -96,17 +149,17 @@ colreduce_kernel(float* __restrict__ out, const T* __restrict__ X, const VT* __r
 #pragma unroll
       for (int j = 0; j < 4; ++j) acc[t][k][j] = 0.f;
   if (active) {
-    const T* xb = X + ((size_t)img * HW) * p.C + c;
+    const T* xb = X + ((size_t)img * HW) * pr.C + c;
     // software pipeline: the X vectors of the next two pixels are in flight while this one is consumed
     float xn0[CH], xn1[CH];
     int q = q0 + pl;
-    if (q < q1) ChanVec<T, CH>::load(xb + (size_t)q * p.C, xn0);
-    if (q + p.PL < q1) ChanVec<T, CH>::load(xb + (size_t)(q + p.PL) * p.C, xn1);
+    if (q < q1) ChanVec<T, CH>::load(xb + (size_t)q * pr.C, xn0);
+    if (q + p.PL < q1) ChanVec<T, CH>::load(xb + (size_t)(q + p.PL) * pr.C, xn1);
     for (; q < q1; q += p.PL) {
       float xv[CH];
 #pragma unroll
       for (int k = 0; k < CH; ++k) { xv[k] = xn0[k]; xn0[k] = xn1[k]; }
-      if (q + 2 * p.PL < q1) ChanVec<T, CH>::load(xb + (size_t)(q + 2 * p.PL) * p.C, xn1);
+      if (q + 2 * p.PL < q1) ChanVec<T, CH>::load(xb + (size_t)(q + 2 * p.PL) * pr.C, xn1);
       if (TAPS == 1) {
         const float4 f = s_v[q - v0];
 #pragma unroll
@@ -120,10 +173,12 @@ colreduce_kernel(float* __restrict__ out, const T* __restrict__ X, const VT* __r
         const int h = q / p.W, w = q - h * p.W;
 #pragma unroll
         for (int t = 0; t < TAPS; ++t) {
-          // x[q] meets dh[pv] where q = pv + d(t)  =>  pv = q - d(t)
-          const int ph = h - (t / 3 - p.pad), pw = w - (t % 3 - p.pad);
-          if (ph >= 0 && ph < p.H && pw >= 0 && pw < p.W) {
-            const float4 f = s_v[ph * p.W + pw - v0];
+          // x[q] meets V[pv] where q = stride * pv + d(t)  =>  stride * pv = q - d(t)
+          int ph = h - (t / 3 - p.pad), pw = w - (t % 3 - p.pad);
+          bool ok = ph >= 0 && pw >= 0;
+          if (p.stride == 2) { ok = ok && ((ph | pw) & 1) == 0; ph >>= 1; pw >>= 1; }
+          if (ok && ph < p.VH && pw < p.VW) {
+            const float4 f = s_v[ph * p.VW + pw - v0];
 #pragma unroll
             for (int k = 0; k < CH; ++k) {
               acc[t][k][0] = fmaf(xv[k], f.x, acc[t][k][0]);
@@ -136,9 +191,8 @@ colreduce_kernel(float* __restrict__ out, const T* __restrict__ X, const VT* __r
       }
     }
   }
-  // cross-lane reduction: the 8 pixel lanes of a warp by shuffles (lane = pixel-lane * 4 + channel-vector thread,
-  // NVT == 4), the warps through shared memory (re-using the V staging area), then one fp32 atomicAdd per output
-  // element and CTA.  A CTA covers only NVT * CH channels, so it issues TAPS * NVT * CH * 4 atomics in total.
+  // cross-lane reduction: the 8 pixel lanes of a warp by shuffles (lane = pixel-lane * 4 + channel-vector thread),
+  // the warps through shared memory (re-using the V staging area)
   constexpr int NACC = TAPS * CH * 4;
 #pragma unroll
   for (int t = 0; t < TAPS; ++t)
@@ -164,16 +218,33 @@ colreduce_kernel(float* __restrict__ out, const T* __restrict__ X, const VT* __r
         dst[t * CH + k] = make_float4(acc[t][k][0], acc[t][k][1], acc[t][k][2], acc[t][k][3]);
   }
   __syncthreads();
+  // this CTA's sums -> workspace; the last CTA of the channel block finishes in chunk order
+  const int nchunks = (int)gridDim.x;
+  float* mine = p.partial + ((size_t)blockIdx.y * nchunks + blockIdx.x) * (4 * NACC);
+  for (int i = threadIdx.x; i < 4 * NACC; i += blockDim.x) {
+    float sum = 0.f;
+    for (int w = 0; w < nwarps; ++w) sum += s_red[(size_t)w * 4 * NACC + i];
+    __stcg(mine + i, sum);
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = (atomicAdd(p.tickets + blockIdx.y, 1u) == (unsigned)(nchunks - 1)) ? 1 : 0;
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  const float* all = p.partial + (size_t)blockIdx.y * nchunks * (4 * NACC);
   for (int i = threadIdx.x; i < 4 * NACC; i += blockDim.x) {
     const int vv = i / NACC, rem = i - vv * NACC;
     const int t = rem / (CH * 4), k = (rem >> 2) % CH, j = rem & 3;
-    const int cc = (blockIdx.y * 4 + vv) * CH + k;
-    if (cc < p.C && j0 + j < p.rank) {
+    const int cc = (yblk * 4 + vv) * CH + k;
+    if (cc < pr.C && j0 + j < p.rank) {
       float sum = 0.f;
-      for (int w = 0; w < nwarps; ++w) sum += s_red[(size_t)w * 4 * NACC + i];
-      atomicAdd(out + (int64_t)cc * p.oc + (int64_t)(j0 + j) * p.oj + (int64_t)t * p.ot, sum * p.scale);
+      for (int ch = 0; ch < nchunks; ++ch) sum += __ldcg(all + (size_t)ch * (4 * NACC) + i);
+      float* o = pr.out + (int64_t)cc * pr.oc + (int64_t)(j0 + j) * pr.oj + (int64_t)t * pr.ot;
+      *o = (p.accumulate ? *o : 0.f) + sum * pr.scale;
     }
   }
+  if (threadIdx.x == 0) p.tickets[blockIdx.y] = 0u;
 }
 
 template <typename T>
@@ -204,41 +275,64 @@ __global__ void pack_wt_kernel(T* __restrict__ Wt, const T* __restrict__ W, int 
   }
 }
 
+// Workspace layout of the gradient entry points (caller zero-fills the first CR_TICKET_BYTES once; the kernels
+// leave them zero):  [tickets 4 KB][Bt 16 x cout][colreduce partials][split-K scratch of the GEMM]
+constexpr size_t CR_TICKET_BYTES = CR_MAX_TICKETS * sizeof(unsigned);
+constexpr size_t CR_PARTIAL_BYTES = (size_t)2 << 20;
+static inline size_t bt_bytes_of(int cout) { return (((size_t)16 * cout * 4) + 255) & ~(size_t)255; }
+
+// taps: 1 or 9.  One or two problems over the same pixel set.
 template <typename T, typename VT>
-static int launch_colreduce(float* out, const T* X, const VT* v, ColReduceParams p, int taps, cudaStream_t st) {
+static int launch_colreduce(ColReduceParams p, int taps, float* partial, unsigned* tickets, cudaStream_t st) {
   const int CH = taps == 1 ? 8 : 4;
   const int HW = p.H * p.W;
-  // a CTA = 4 channel-vector threads (NVT, fixed: the shuffle reduction relies on it) x 64 pixel lanes: a narrow
-  // channel slice keeps the per-CTA output (and its atomics) small, the pixel lanes supply the parallelism
+  // a CTA = 4 channel-vector threads x 64 pixel lanes: a narrow channel slice keeps the per-CTA output small, the
+  // pixel lanes supply the parallelism
   const int max_threads = 256;
-  const int nvt_all = (p.C + CH - 1) / CH;
-  const int cblocks = (nvt_all + 3) / 4;
-  p.NVT = 4;
-  p.PL = max_threads / p.NVT;
-  // pixel chunks: ~2 CTAs per SM over (images x chunks x channel blocks); chunks never straddle images
+  int cblocks = 0;
+  for (int i = 0; i < p.nprob; ++i) {
+    const int nvt_all = (p.prob[i].C + CH - 1) / CH;
+    p.prob[i].cblocks = (nvt_all + CR_NVT - 1) / CR_NVT;
+    cblocks += p.prob[i].cblocks;
+  }
+  if (cblocks > CR_MAX_TICKETS) { set_error("colreduce: %d channel blocks exceed %d", cblocks, CR_MAX_TICKETS); return SLIDER_ERR_UNSUPPORTED; }
+  p.PL = max_threads / CR_NVT;
+  const int nacc4 = 4 * taps * CH * 4;
+  // pixel chunks: ~2 CTAs per SM over (images x chunks x channel blocks); chunks never straddle images; bounded by the
+  // partial-sum scratch
   int want = (sm_count() * 2) / (p.B * cblocks);
+  const int cap = (int)(CR_PARTIAL_BYTES / ((size_t)cblocks * nacc4 * sizeof(float))) / p.B;
+  if (want > cap) want = cap;
   if (want < 1) want = 1;
   int ppc = (HW + want - 1) / want;
   if (ppc < p.PL * 2) ppc = p.PL * 2;
   if (ppc > HW) ppc = HW;
   p.ppc = ppc;
   p.cpi = (HW + ppc - 1) / ppc;
-  const int halo = taps > 1 ? p.pad * (p.W + 1) : 0;
-  size_t smem_v = (size_t)(ppc + 2 * halo) * sizeof(float4);
-  size_t smem_r = (size_t)(max_threads / 32) * p.NVT * taps * CH * 4 * sizeof(float);
+  if ((size_t)p.B * p.cpi * cblocks * nacc4 * sizeof(float) > CR_PARTIAL_BYTES) {
+    set_error("colreduce: partial-sum scratch too small for %d x %d CTAs", p.B * p.cpi, cblocks);
+    return SLIDER_ERR_WORKSPACE;
+  }
+  int vmax;
+  if (taps == 1) vmax = ppc;
+  else if (p.stride == 1) vmax = ppc + 2 * p.pad * (p.W + 1);
+  else vmax = (((ppc + p.W - 1) / p.W + 1 + 2 * p.pad) / p.stride + 2) * p.VW;
+  p.vmax = vmax;
+  size_t smem_v = (size_t)vmax * sizeof(float4);
+  size_t smem_r = (size_t)(max_threads / 32) * nacc4 * sizeof(float);
   size_t smem = smem_v > smem_r ? smem_v : smem_r;
   if (smem > 200 * 1024) { set_error("colreduce: shared memory %zu too large", smem); return SLIDER_ERR_UNSUPPORTED; }
-  const int threads = max_threads;
+  p.partial = partial; p.tickets = tickets;
   dim3 grid(p.B * p.cpi, cblocks);
   for (int j0 = 0; j0 < p.rank; j0 += 4) {
     if (taps == 1) {
       auto k = colreduce_kernel<T, VT, 1, 8>;
       if (smem > 48 * 1024) SLIDER_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      k<<<grid, threads, smem, st>>>(out, X, v, p, j0);
+      k<<<grid, max_threads, smem, st>>>(p, j0);
     } else {
       auto k = colreduce_kernel<T, VT, 9, 4>;
       if (smem > 48 * 1024) SLIDER_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      k<<<grid, threads, smem, st>>>(out, X, v, p, j0);
+      k<<<grid, max_threads, smem, st>>>(p, j0);
     }
     int rc = post_launch("colreduce_kernel");
     if (rc) return rc;
@@ -248,39 +342,88 @@ static int launch_colreduce(float* out, const T* X, const VT* v, ColReduceParams
 
 int run_gemm_plain(const slider_layer_geom* g, int kc, int nn, void* y, const void* act, const void* wgt, void* ws,
                    size_t ws_bytes, cudaStream_t st);   // lora_gemm.cu
+int run_gemm_fused_bwd(const slider_layer_geom* g, void* dx, float* g_out, const void* gy, const void* Wt,
+                       const void* Bt, const void* A, float s, void* ws, size_t ws_bytes, cudaStream_t st);   // lora_gemm.cu
+
+static ColProblem make_problem(const void* X, const void* V, float* out, int C, int vstride, int64_t oc, int64_t oj,
+                               int64_t ot, float scale) {
+  ColProblem q;
+  q.X = X; q.V = V; q.out = out; q.C = C; q.cblocks = 0; q.vstride = vstride; q.oc = oc; q.oj = oj; q.ot = ot; q.scale = scale;
+  return q;
+}
+
+struct GradWs {
+  unsigned* tickets; void* bt; float* partial; void* gemm; size_t gemm_bytes;
+};
+static int carve_ws(GradWs* w, void* ws, size_t ws_bytes, int cout, const char* who) {
+  const size_t need = CR_TICKET_BYTES + bt_bytes_of(cout) + CR_PARTIAL_BYTES;
+  if (ws == nullptr || ws_bytes < need || ((uintptr_t)ws & 255) != 0) {
+    set_error("%s: workspace %zu < %zu bytes (or not 256-byte aligned)", who, ws_bytes, need);
+    return SLIDER_ERR_WORKSPACE;
+  }
+  uint8_t* b = reinterpret_cast<uint8_t*>(ws);
+  w->tickets = reinterpret_cast<unsigned*>(b);
+  w->bt = b + CR_TICKET_BYTES;
+  w->partial = reinterpret_cast<float*>(b + CR_TICKET_BYTES + bt_bytes_of(cout));
+  w->gemm = b + need;
+  w->gemm_bytes = ws_bytes - need;
+  return SLIDER_OK;
+}
 
 template <typename T>
 static int lora_grad_impl(const slider_layer_geom* g, float* dA, float* dB, T* dh, const T* gy, const T* x,
                           const float* h, const T* Bup, float s, int accumulate, void* ws, size_t ws_bytes,
                           cudaStream_t st) {
   const int taps = g->kh * g->kw;
-  if (!accumulate) {
-    SLIDER_CUDA(cudaMemsetAsync(dA, 0, sizeof(float) * (size_t)g->rank * taps * g->cin, st));
-    SLIDER_CUDA(cudaMemsetAsync(dB, 0, sizeof(float) * (size_t)g->cout * g->rank, st));
-  }
+  const int stride = g->stride == 2 ? 2 : 1;
+  const int Ho = (g->height + 2 * g->pad - g->kh) / stride + 1, Wo = (g->width + 2 * g->pad - g->kw) / stride + 1;
+  GradWs w;
+  int rc = carve_ws(&w, ws, ws_bytes, g->cout, "lora_grad");
+  if (rc) return rc;
   // dh = gy . (s B): a [pixels, Cout] x [Cout, 16] contraction on the tensor cores (same tcgen05 kernel
   // as the forward, 1x1, no adapter), output already in the zero-padded [pixels, 16] layout.
-  const size_t bt_bytes = (((size_t)16 * g->cout * sizeof(T)) + 255) & ~(size_t)255;
-  if (ws == nullptr || ws_bytes < bt_bytes) {
-    set_error("lora_grad: workspace %zu < %zu bytes", ws_bytes, bt_bytes);
-    return SLIDER_ERR_WORKSPACE;
-  }
-  T* Bt = reinterpret_cast<T*>(ws);
+  T* Bt = reinterpret_cast<T*>(w.bt);
   pack_bt_kernel<T><<<(16 * g->cout + 255) / 256, 256, 0, st>>>(Bt, Bup, g->cout, g->rank, s);
-  int rc = post_launch("pack_bt_kernel");
-  if (rc) return rc;
+  if ((rc = post_launch("pack_bt_kernel"))) return rc;
   slider_layer_geom g1 = *g;
-  g1.kh = g1.kw = 1; g1.pad = 0; g1.rank = 0; g1.cin = g->cout; g1.cout = 16;
-  rc = run_gemm_plain(&g1, g->cout, 16, dh, gy, Bt, reinterpret_cast<uint8_t*>(ws) + bt_bytes, ws_bytes - bt_bytes, st);
-  if (rc) return rc;
+  g1.kh = g1.kw = 1; g1.pad = 0; g1.rank = 0; g1.cin = g->cout; g1.cout = 16; g1.stride = 1; g1.height = Ho; g1.width = Wo;
+  if ((rc = run_gemm_plain(&g1, g->cout, 16, dh, gy, Bt, w.gemm, w.gemm_bytes, st))) return rc;
+  if (dA == nullptr && dB == nullptr) return SLIDER_OK;     // frozen adapter: only dh (for the input gradient)
   ColReduceParams pb;
-  pb.B = g->batch; pb.H = g->height; pb.W = g->width; pb.C = g->cout; pb.kw = 1; pb.pad = 0;
-  pb.rank = g->rank; pb.vstride = g->rank; pb.oc = g->rank; pb.oj = 1; pb.ot = 0; pb.scale = s;
-  if ((rc = launch_colreduce<T, float>(dB, gy, h, pb, 1, st))) return rc;
+  pb.B = g->batch; pb.H = Ho; pb.W = Wo; pb.VH = Ho; pb.VW = Wo; pb.stride = 1; pb.kw = 1; pb.pad = 0;
+  pb.rank = g->rank; pb.accumulate = accumulate; pb.nprob = 1;
+  pb.prob[0] = make_problem(gy, h, dB, g->cout, g->rank, g->rank, 1, 0, s);
+  if ((rc = launch_colreduce<T, float>(pb, 1, w.partial, w.tickets, st))) return rc;
   ColReduceParams pa;
-  pa.B = g->batch; pa.H = g->height; pa.W = g->width; pa.C = g->cin; pa.kw = g->kw; pa.pad = g->pad;
-  pa.rank = g->rank; pa.vstride = 16; pa.oc = 1; pa.oj = (int64_t)taps * g->cin; pa.ot = g->cin; pa.scale = 1.f;
-  return launch_colreduce<T, T>(dA, x, dh, pa, taps, st);
+  pa.B = g->batch; pa.H = g->height; pa.W = g->width; pa.VH = Ho; pa.VW = Wo; pa.stride = stride; pa.kw = g->kw; pa.pad = g->pad;
+  pa.rank = g->rank; pa.accumulate = accumulate; pa.nprob = 1;
+  pa.prob[0] = make_problem(x, dh, dA, g->cin, 16, 1, (int64_t)taps * g->cin, g->cin, 1.f);
+  return launch_colreduce<T, T>(pa, taps, w.partial, w.tickets, st);
+}
+
+// 1x1 layers: one fused GEMM launch (dx and g = gy . B), one reduction launch (dB and dA).
+template <typename T>
+static int lora_backward_1x1_impl(const slider_layer_geom* g, T* dx, float* dA, float* dB, float* gbuf, const T* gy,
+                                  const T* x, const float* h, const T* Wt, const T* Bt, const T* A, const T* Bup,
+                                  float s, int accumulate, void* ws, size_t ws_bytes, cudaStream_t st) {
+  GradWs w;
+  int rc = carve_ws(&w, ws, ws_bytes, g->cout, "lora_backward_1x1");
+  if (rc) return rc;
+  if (Bt == nullptr) {
+    // B^T [16, cout] (rows >= rank zero) for this layer alone; a network-wide pack (slider_transpose_batch) avoids it
+    T* bt = reinterpret_cast<T*>(w.bt);
+    pack_bt_kernel<T><<<(16 * g->cout + 255) / 256, 256, 0, st>>>(bt, Bup, g->cout, g->rank, 1.f);
+    if ((rc = post_launch("pack_bt_kernel"))) return rc;
+    Bt = bt;
+  }
+  if ((rc = run_gemm_fused_bwd(g, dx, gbuf, gy, Wt, Bt, A, s, w.gemm, w.gemm_bytes, st))) return rc;
+  if (dA == nullptr && dB == nullptr) return SLIDER_OK;
+  ColReduceParams p;
+  p.B = g->batch; p.H = g->height; p.W = g->width; p.VH = g->height; p.VW = g->width; p.stride = 1; p.kw = 1; p.pad = 0;
+  p.rank = g->rank; p.accumulate = accumulate; p.nprob = 2;
+  p.prob[0] = make_problem(gy, h, dB, g->cout, g->rank, g->rank, 1, 0, s);
+  p.prob[1] = make_problem(x, gbuf, dA, g->cin, g->rank, 1, g->cin, 0, s);
+  return launch_colreduce<T, float>(p, 1, w.partial, w.tickets, st);
 }
 
 }  // namespace slider
@@ -292,6 +435,7 @@ static int check_geom(const slider_layer_geom* g, const char* who) {
   SLIDER_CHECK_ARG(g->dtype == SLIDER_F32 || g->dtype == SLIDER_BF16, "%s: unsupported dtype %d", who, g->dtype);
   SLIDER_CHECK_ARG(g->kh == g->kw && (g->kh == 1 || g->kh == 3) && g->pad == (g->kh - 1) / 2,
                    "%s: only 1x1/pad0 and 3x3/pad1 kernels", who);
+  SLIDER_CHECK_ARG(g->stride >= 0 && g->stride <= 2 && (g->stride != 2 || g->kh == 3), "%s: stride %d", who, g->stride);
   SLIDER_CHECK_ARG(g->batch > 0 && g->height > 0 && g->width > 0 && g->cin > 0 && g->cout > 0, "%s: empty shape", who);
   SLIDER_CHECK_ARG(g->cin % 8 == 0 && g->cout % 8 == 0, "%s: channels must be multiples of 8", who);
   return SLIDER_OK;
@@ -300,8 +444,7 @@ static int check_geom(const slider_layer_geom* g, const char* who) {
 extern "C" {
 
 size_t slider_lora_grad_workspace_bytes(const slider_layer_geom* g) {
-  const size_t bt = g ? ((((size_t)16 * g->cout * 4) + 255) & ~(size_t)255) : 0;
-  return bt + slider_gemm_workspace_bytes();
+  return CR_TICKET_BYTES + (g ? bt_bytes_of(g->cout) : 0) + CR_PARTIAL_BYTES + slider_gemm_workspace_bytes();
 }
 
 int slider_lora_grad(const slider_layer_geom* g, float* dA, float* dB, void* dh_out, const void* gy, const void* x,
@@ -309,7 +452,8 @@ int slider_lora_grad(const slider_layer_geom* g, float* dA, float* dB, void* dh_
                      void* stream) {
   int rc = check_geom(g, "lora_grad");
   if (rc) return rc;
-  SLIDER_CHECK_ARG(dA && dB && dh_out && gy && x && h && B, "lora_grad: null pointer");
+  SLIDER_CHECK_ARG((dA == nullptr) == (dB == nullptr), "lora_grad: dA and dB must both be set or both NULL");
+  SLIDER_CHECK_ARG(dh_out && gy && B && (dA == nullptr || (x && h)), "lora_grad: null pointer");
   SLIDER_CHECK_ARG(g->rank >= 1 && g->rank <= 16, "lora_grad: rank %d not in 1..16", g->rank);
   cudaStream_t st = (cudaStream_t)stream;
   if (g->dtype == SLIDER_BF16)
@@ -317,6 +461,38 @@ int slider_lora_grad(const slider_layer_geom* g, float* dA, float* dB, void* dh_
                                          (const __nv_bfloat16*)x, h, (const __nv_bfloat16*)B, s, accumulate, ws, ws_bytes, st);
   return lora_grad_impl<float>(g, dA, dB, (float*)dh_out, (const float*)gy, (const float*)x, h, (const float*)B, s,
                                accumulate, ws, ws_bytes, st);
+}
+
+int slider_lora_backward_1x1(const slider_layer_geom* g, void* dx, float* dA, float* dB, float* g_buf, const void* gy,
+                             const void* x, const float* h, const void* Wt, const void* Bt, const void* A,
+                             const void* B, float s, int accumulate, void* ws, size_t ws_bytes, void* stream) {
+  int rc = check_geom(g, "lora_backward_1x1");
+  if (rc) return rc;
+  SLIDER_CHECK_ARG(g->kh == 1 && g->stride != 2, "lora_backward_1x1: 1x1 / Linear layers only");
+  SLIDER_CHECK_ARG((dA == nullptr) == (dB == nullptr), "lora_backward_1x1: dA and dB must both be set or both NULL");
+  SLIDER_CHECK_ARG(dx && g_buf && gy && Wt && A && (Bt || B) && (dA == nullptr || (x && h)), "lora_backward_1x1: null pointer");
+  SLIDER_CHECK_ARG(g->rank >= 1 && g->rank <= 16, "lora_backward_1x1: rank %d not in 1..16", g->rank);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (g->dtype == SLIDER_BF16)
+    return lora_backward_1x1_impl<__nv_bfloat16>(g, (__nv_bfloat16*)dx, dA, dB, g_buf, (const __nv_bfloat16*)gy,
+                                                 (const __nv_bfloat16*)x, h, (const __nv_bfloat16*)Wt,
+                                                 (const __nv_bfloat16*)Bt, (const __nv_bfloat16*)A,
+                                                 (const __nv_bfloat16*)B, s, accumulate, ws, ws_bytes, st);
+  return lora_backward_1x1_impl<float>(g, (float*)dx, dA, dB, g_buf, (const float*)gy, (const float*)x, h,
+                                       (const float*)Wt, (const float*)Bt, (const float*)A, (const float*)B, s,
+                                       accumulate, ws, ws_bytes, st);
+}
+
+int slider_transpose_batch(const slider_transpose_entry* table_dev, int entries, int max_elems, int dtype, void* stream) {
+  SLIDER_CHECK_ARG(table_dev != nullptr && entries > 0 && entries <= 65535 && max_elems > 0, "transpose_batch: bad argument");
+  SLIDER_CHECK_ARG(dtype == SLIDER_F32 || dtype == SLIDER_BF16, "transpose_batch: unsupported dtype %d", dtype);
+  int bx = (max_elems + 255) / 256;
+  if (bx > 32) bx = 32;
+  dim3 grid(bx, entries);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == SLIDER_BF16) transpose_batch_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(table_dev, entries);
+  else transpose_batch_kernel<float><<<grid, 256, 0, st>>>(table_dev, entries);
+  return post_launch("transpose_batch_kernel");
 }
 
 int slider_lora_pack_at(const slider_layer_geom* g, void* At, const void* A, void* stream) {

@@ -1,0 +1,794 @@
+// Fused base + low-rank implicit GEMM for sm_100a (tcgen05 + TMEM + TMA): device code.
+//
+//   y[pix, n] = sum_{tap,c} x[stride*pix + d(tap), c] * W[n, tap, c] + bias[n]
+//             + s * sum_j ( sum_{tap,c} x[stride*pix + d(tap), c] * A[j, tap, c] ) * Bup[n, j]
+//
+// One persistent CTA per SM, 10 warps:
+//   warp 0      TMA producer  (4-D box loads of NHWC activations: padding = TMA out-of-bounds zero fill, a stride-2
+//                              convolution = the activation map's element strides {1, 2, 2, 1};
+//                              3-D box loads of the tap-major weights)
+//   warp 1      TMEM allocator + single-thread tcgen05.mma issuer
+//   warps 2..9  epilogue (two groups of four warps, one column half each):
+//               tcgen05.ld -> registers -> (+bias, + s*h.Bup) -> shared staging -> TMA store
+// The rank-r intermediate h = x (*) A lives in 16 extra TMEM columns next to the main accumulator: the lora_down
+// tile sits behind the W tile in the same shared-memory stage, so ONE tcgen05.mma of N = BN + 16 produces both, and
+// h is folded into the output in the epilogue with r FMAs per element.  The accumulators are double buffered; the
+// epilogue reads a whole accumulator into registers with ONE tcgen05.wait and hands the TMEM stage back before it
+// does any arithmetic, so the main loop of the next tile never waits for stores.
+//
+// Two tile widths are instantiated (lora_gemm_bn160.cu / lora_gemm_bn80.cu): 128 x 160 for launches with enough
+// tiles to fill the GPU, 128 x 80 (six smaller operand stages) for tile-starved ones.
+//
+// The same kernel computes the input gradient ("extended-K" mode): activations = gy, weights = Wt, and one extra
+// 16-wide K block per tap whose operands are dh and At.
+#pragma once
+#include <stdlib.h>
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace slider {
+
+constexpr int BM = 128;          // pixels (GEMM rows) per tile
+constexpr int HCOLS = 16;        // TMEM columns of the low-rank accumulator (rank padded to 16)
+constexpr int ROW_BYTES = 128;   // K-block row = one 128-byte swizzle row
+constexpr int ACC_STAGES = 2;
+constexpr int A_BYTES = BM * ROW_BYTES;      // 16 KB
+constexpr int L_BYTES = HCOLS * ROW_BYTES;   // 2 KB
+constexpr int EXT_ELEMS = 16;    // width of the extended-K operand (dh / At), in elements
+constexpr int kGemmThreads = 320;            // warp 0 TMA, warp 1 MMA, warps 2..9 epilogue (two groups of four)
+constexpr int kEpiThreads = 256;
+constexpr int OUT_ROW_BYTES = 80;            // staging row of one store chunk: 40 bf16 / 20 fp32 columns; an 80-byte
+                                             // pitch makes the 16-byte st.shared of 8 consecutive rows conflict-free
+constexpr int OUT_BYTES = BM * OUT_ROW_BYTES;   // 10 KB per chunk buffer
+constexpr int PCW = OUT_ROW_BYTES / 4;       // fp32 columns per split-K partial chunk
+constexpr int MAX_NSTAGES = 6;
+
+// Everything that depends on the tile width BN (output channels per tile; 160 divides 320/640/960/1280/1920/2560).
+template <int BN_> struct TileCfg {
+  static constexpr int BN = BN_;
+  static constexpr int B_BYTES = BN * ROW_BYTES;                     // 20 KB / 10 KB
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES + L_BYTES;    // 38 KB / 28 KB
+  static constexpr int NSTAGES = BN_ >= 160 ? 4 : 6;
+  static constexpr int HALF_N = BN / 2;                              // output columns owned by one epilogue group
+  static constexpr int ACC_COLS = BN + HCOLS;                        // TMEM columns of one accumulator stage
+  static constexpr int TMEM_COLS = ACC_STAGES * ACC_COLS <= 256 ? 256 : 512;
+  static constexpr int NCHUNK = BN / PCW + 1;                        // partial chunks of a split-K unit (+1 for h)
+  static constexpr size_t UNIT_FLOATS = (size_t)NCHUNK * BM * PCW;
+  // staging buffers per epilogue group: three when the rank table leaves room, else two
+  __host__ __device__ static constexpr int out_bufs(int r4) { return BN_ >= 160 ? (r4 <= 2 ? 3 : 2) : 2; }
+  __host__ __device__ static constexpr int epi_floats(int r4) { return BN * 4 * (r4 > 0 ? r4 : 1) + BN; }   // s*Bup + bias
+  __host__ __device__ static constexpr size_t smem_bytes(int r4) {
+    return 1024 /*align slack*/ + (size_t)NSTAGES * STAGE_BYTES + (size_t)2 * out_bufs(r4) * OUT_BYTES +
+           (size_t)epi_floats(r4) * 4 + 256;
+  }
+};
+
+// Division by a launch-constant through a host-computed multiplier (n < 2^31): the producer's tile -> coordinate
+// chain is on the critical path of every launch and eight hardware divisions cost ~1000 cycles there.
+struct FastDiv {
+  uint32_t d, mul, shr;
+  static FastDiv make(uint32_t d) {
+    FastDiv f; f.d = d; f.mul = 0; f.shr = 0;
+    if (d <= 1) { f.d = 1; return f; }
+    uint32_t l = 0;
+    while ((1u << l) < d) ++l;
+    f.mul = (uint32_t)(((1ull << (31 + l)) + d - 1) / d);
+    f.shr = l - 1;
+    return f;
+  }
+  __device__ __forceinline__ uint32_t div(uint32_t n) const { return d == 1 ? n : (__umulhi(n, mul) >> shr); }
+  __device__ __forceinline__ void divmod(uint32_t n, uint32_t& q, uint32_t& r) const { q = div(n); r = n - q * d; }
+};
+
+template <typename T> struct GemmTraits;
+template <> struct GemmTraits<__nv_bfloat16> {
+  static constexpr int kBK = 64;       // elements per 128-byte row
+  static constexpr uint32_t kFmt = 1;  // bf16
+  static constexpr int kExtRowBytes = EXT_ELEMS * 2;
+  static constexpr bool kSplit3 = false;
+  __device__ static inline void mma(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) {
+    ptx::mma_f16(d, a, b, idesc, acc);
+  }
+};
+template <> struct GemmTraits<float> {
+  static constexpr int kBK = 32;
+  static constexpr uint32_t kFmt = 2;  // tf32
+  static constexpr int kExtRowBytes = EXT_ELEMS * 4;
+  // fp32 storage: error-compensated 3xTF32.  Every landed stage is split in shared memory into
+  // hi = x with the 13 low mantissa bits cleared (exact in tf32) and lo = x - hi (the stage slot behind it),
+  // and each K step issues hi.hi + lo.hi + hi.lo into the same accumulator (~2^-21 rel).  Stages are used in pairs.
+  static constexpr bool kSplit3 = true;
+  __device__ static inline void mma(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) {
+    ptx::mma_tf32(d, a, b, idesc, acc);
+  }
+};
+
+struct GemmParams {
+  int TW, TH, TB, rows;   // tile box in OUTPUT pixels; rows = TW*TH*TB <= 128
+  int W, H, B;            // OUTPUT extent
+  int stride;             // input pixel step per output pixel (1 or 2)
+  int mt_w, mt_h, mt_b;   // number of pixel tiles per dimension
+  int n_tiles, N;
+  int taps, kw, pad, cblocks;
+  int rank;
+  int bup_ld, bup_jd;     // Bup[n, j] sits at n * bup_ld + j * bup_jd elements: (rank, 1) for a lora_up weight [N, r];
+                          // (1, N) reads a lora_down weight [r, N] as its own transpose (fused 1x1 backward)
+  float s;
+  int lora;               // accumulate h and apply it in the epilogue
+  int ext;                // extended-K operand pair present (input-gradient mode)
+  int total_tiles;
+  int per_tap;            // K iterations per tap = cblocks + ext
+  int kiters;             // taps * per_tap
+  int ksplit;             // K partitions per tile (1 = no split)
+  int total_units;        // total_tiles * ksplit
+  float* partial;         // split-K partial tiles, [unit][NCHUNK][128][PCW] fp32
+  int accumulate;         // y += result (y holds the residual branch) instead of y = result
+  int group_n;            // grouped adapters: output columns per group (0 = one adapter); group g uses h columns [g*rank, (g+1)*rank)
+  FastDiv fd_n_tiles, fd_mt_w, fd_mt_h, fd_ksplit, fd_per_tap, fd_kw;
+  int w_prefetch;         // K blocks the weight stream is requested into L2 ahead of the shared-memory pipeline
+  long long* trace;       // debug: 16 clock64() stamps per CTA (NULL = off)
+  void* y;
+  const void* bias;
+  const void* Bup;
+  float* h_out;
+};
+
+struct TileCoord { int w0, h0, b0, n0, n_blk; };
+
+template <int BN>
+__device__ __forceinline__ TileCoord tile_coord(const GemmParams& p, int tile) {
+  TileCoord t;
+  uint32_t mi, nb, wt, ht, bt;
+  p.fd_n_tiles.divmod((uint32_t)tile, mi, nb);
+  p.fd_mt_w.divmod(mi, mi, wt);
+  p.fd_mt_h.divmod(mi, bt, ht);
+  t.n_blk = (int)nb;
+  t.w0 = (int)wt * p.TW; t.h0 = (int)ht * p.TH; t.b0 = (int)bt * p.TB; t.n0 = t.n_blk * BN;
+  return t;
+}
+
+// K-iteration range [it0, it1) of split `split` of a tile
+__device__ __forceinline__ void split_range(const GemmParams& p, uint32_t split, int& it0, int& it1) {
+  it0 = (int)p.fd_ksplit.div(split * (uint32_t)p.kiters);
+  it1 = (int)p.fd_ksplit.div((split + 1) * (uint32_t)p.kiters);
+}
+
+// N consecutive fp32 accumulator columns of this warp's 32 lanes into registers, NO wait (the caller issues every
+// load of a tile and then one tcgen05.wait::ld)
+template <int N> __device__ __forceinline__ void tmem_ld_cols(uint32_t taddr, uint32_t* v);
+template <> __device__ __forceinline__ void tmem_ld_cols<40>(uint32_t taddr, uint32_t* v) {
+  ptx::tmem_ld_x32(taddr, v);
+  ptx::tmem_ld_x8(taddr + 32, v + 32);
+}
+template <> __device__ __forceinline__ void tmem_ld_cols<20>(uint32_t taddr, uint32_t* v) {
+  ptx::tmem_ld_x16(taddr, v);
+  ptx::tmem_ld_x4(taddr + 16, v + 16);
+}
+
+template <typename T, int R4, int BN>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
+                 const __grid_constant__ CUtensorMap tmL, const __grid_constant__ CUtensorMap tmXe,
+                 const __grid_constant__ CUtensorMap tmWe, const __grid_constant__ CUtensorMap tmY,
+                 const __grid_constant__ CUtensorMap tmP, const GemmParams p) {
+  using Tr = GemmTraits<T>;
+  using Cfg = TileCfg<BN>;
+  constexpr int BK = Tr::kBK;
+  constexpr int KSTEPS = ROW_BYTES / 32;   // one tcgen05.mma consumes 32 bytes of K per row
+  constexpr int EXT_KSTEPS = Tr::kExtRowBytes / 32;
+  constexpr int NSTAGES = Cfg::NSTAGES;
+  constexpr int STAGE_BYTES = Cfg::STAGE_BYTES;
+  constexpr int B_BYTES = Cfg::B_BYTES;
+  constexpr int HALF_N = Cfg::HALF_N;
+  constexpr int ACC_COLS = Cfg::ACC_COLS;
+  constexpr int NCHUNK = Cfg::NCHUNK;
+  constexpr int kStages = Tr::kSplit3 ? NSTAGES / 2 : NSTAGES;            // fp32: hi / lo planes take two slots
+  constexpr int kStageStride = Tr::kSplit3 ? 2 * STAGE_BYTES : STAGE_BYTES;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  constexpr int NB = Cfg::out_bufs(R4);                    // staging buffers per epilogue group
+  uint8_t* s_out = smem + (size_t)NSTAGES * STAGE_BYTES;   // 2 x NB x 10 KB staging of the TMA-store epilogue
+  float* s_epi = reinterpret_cast<float*>(s_out + (size_t)2 * NB * OUT_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_epi + Cfg::epi_floats(R4));
+  uint64_t* full_bar = bars;                      // [NSTAGES]  TMA -> MMA
+  uint64_t* empty_bar = bars + NSTAGES;           // [NSTAGES]  MMA -> TMA
+  uint64_t* tfull_bar = bars + 2 * NSTAGES;       // [ACC_STAGES] MMA -> epilogue
+  uint64_t* tempty_bar = tfull_bar + ACC_STAGES;  // [ACC_STAGES] epilogue -> MMA
+  uint64_t* xf_bar = tempty_bar + ACC_STAGES;     // [NSTAGES] hi/lo split done (fp32 only) -> MMA
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(xf_bar + NSTAGES);
+
+  // warp index through a shuffle so that the role branches below are provably warp-uniform
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
+  const int lane = threadIdx.x & 31;
+#define SLIDER_TRACE(slot) do { if (p.trace != nullptr) p.trace[blockIdx.x * 16 + (slot)] = clock64(); } while (0)
+  pdl_trigger();
+  if (threadIdx.x == 0) SLIDER_TRACE(0);
+  const uint32_t smem_base = ptx::smem_u32(smem);
+  const uint32_t main_tx = (uint32_t)(p.rows * ROW_BYTES + B_BYTES + (p.lora ? L_BYTES : 0));
+  const uint32_t ext_tx = (uint32_t)((p.rows + BN) * Tr::kExtRowBytes);
+
+  // ---- TMA producer state (one elected thread).
+  int pu = (int)blockIdx.x, pit = 0, pit1 = 0, ptap = 0, pj = 0;
+  uint32_t pstage = 0, pphase = 0;
+  TileCoord ptc = {0, 0, 0, 0, 0};
+  bool phave = false;
+  auto prod_begin = [&]() {
+    phave = pu < p.total_units;
+    if (!phave) return;
+    uint32_t tile = (uint32_t)pu, split = 0;
+    if (p.ksplit > 1) p.fd_ksplit.divmod((uint32_t)pu, tile, split);
+    ptc = tile_coord<BN>(p, (int)tile);
+    pit = 0; pit1 = p.kiters; ptap = 0; pj = 0;
+    if (p.ksplit > 1) {
+      split_range(p, split, pit, pit1);
+      ptap = (int)p.fd_per_tap.div((uint32_t)pit);
+      pj = pit - ptap * p.per_tap;
+    }
+  };
+  // Cold weights (in the real forward every layer's weights are cold: 1.7 GB stream through a 126 MB L2): the CTAs
+  // that share an N tile ask for the SAME weight rows, so only n_tiles x stages x 20 KB of distinct HBM requests are
+  // ever in flight and the first stage lands ~2 us late.  The CTA that owns the first pixel tile of an N tile
+  // therefore requests the weight tiles of the next `w_prefetch` K blocks into L2 (TMA tile prefetch, in consumption
+  // order), the first burst before the dependency wait -- frozen weights are never written by a preceding kernel.
+  auto prod_prefetch_w = [&](int it) {
+    const int tap = (int)p.fd_per_tap.div((uint32_t)it);
+    const int j = it - tap * p.per_tap;
+    if (j < p.cblocks) ptx::tma_prefetch_l2_3d(&tmW, j * BK, tap, ptc.n0);
+  };
+  auto prod_owner = [&]() { return p.w_prefetch > 0 && ptc.w0 == 0 && ptc.h0 == 0 && ptc.b0 == 0; };
+  auto prod_issue = [&]() {
+    const int ty = (int)p.fd_kw.div((uint32_t)ptap);
+    const int dy = ty - p.pad, dx = ptap - ty * p.kw - p.pad;
+    ptx::mbar_wait(ptx::smem_u32(empty_bar + pstage), pphase ^ 1);
+    const uint32_t sa = smem_base + pstage * kStageStride;
+    const uint32_t fb = ptx::smem_u32(full_bar + pstage);
+    if (pj < p.cblocks) {
+      ptx::mbar_arrive_expect_tx(fb, main_tx);
+      // stride 2: the activation map samples every second pixel (element strides {1, 2, 2, 1}), so the box that
+      // starts at input pixel (2*w0 + dx, 2*h0 + dy) lands the TW x TH output pixels' operands densely
+      ptx::tma_load_4d(sa, &tmA, fb, pj * BK, ptc.w0 * p.stride + dx, ptc.h0 * p.stride + dy, ptc.b0);
+      ptx::tma_load_3d(sa + A_BYTES, &tmW, fb, pj * BK, ptap, ptc.n0);
+      if (p.lora) ptx::tma_load_3d(sa + A_BYTES + B_BYTES, &tmL, fb, pj * BK, ptap, 0);
+    } else {
+      ptx::mbar_arrive_expect_tx(fb, ext_tx);
+      ptx::tma_load_4d(sa, &tmXe, fb, 0, ptc.w0 + dx, ptc.h0 + dy, ptc.b0);
+      ptx::tma_load_3d(sa + A_BYTES, &tmWe, fb, 0, ptap, ptc.n0);
+    }
+    if (prod_owner() && pit + p.w_prefetch < pit1) prod_prefetch_w(pit + p.w_prefetch);
+    if (++pstage == (uint32_t)kStages) { pstage = 0; pphase ^= 1; }
+    if (++pj == p.per_tap) { pj = 0; ++ptap; }
+    if (++pit == pit1) {
+      pu += (int)gridDim.x;
+      prod_begin();
+      if (phave && prod_owner())
+        for (int d = 0; d < p.w_prefetch && pit + d < pit1; ++d) prod_prefetch_w(pit + d);
+    }
+  };
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tmA);
+    ptx::prefetch_tmap(&tmW);
+    if (p.lora) ptx::prefetch_tmap(&tmL);
+    if (p.ext) { ptx::prefetch_tmap(&tmXe); ptx::prefetch_tmap(&tmWe); }
+    if (p.ksplit > 1) ptx::prefetch_tmap(&tmP); else ptx::prefetch_tmap(&tmY);
+    for (int i = 0; i < NSTAGES; ++i) {
+      ptx::mbar_init(ptx::smem_u32(full_bar + i), 1);
+      ptx::mbar_init(ptx::smem_u32(empty_bar + i), 1);
+      ptx::mbar_init(ptx::smem_u32(xf_bar + i), 8);      // one arrive per epilogue warp
+    }
+    for (int i = 0; i < ACC_STAGES; ++i) {
+      ptx::mbar_init(ptx::smem_u32(tfull_bar + i), 1);
+      ptx::mbar_init(ptx::smem_u32(tempty_bar + i), 8);  // one arrive per epilogue warp
+    }
+    ptx::fence_mbar_init();
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(ptx::smem_u32(tmem_slot), Cfg::TMEM_COLS);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  // CTA-wide start barrier.  Warp 0 only ARRIVES (its lane 0 initialised the mbarriers above and is the one
+  // thread that never needs the TMEM base), so the producer starts fetching operands while the TMEM allocation
+  // and the other warps' start-up are still in flight.
+  if (warp == 0) {
+    __syncwarp();
+    asm volatile("bar.arrive 1, %0;" ::"n"(kGemmThreads) : "memory");
+  } else {
+    asm volatile("bar.sync 1, %0;" ::"n"(kGemmThreads) : "memory");
+  }
+  ptx::tc_fence_after();
+  // PDL: nothing of ours reads what the previous kernel wrote before that kernel has completed and flushed (the
+  // producer warp waits after its first weight-prefetch burst below)
+  if (warp != 0) pdl_wait();
+  const uint32_t tmem_base = warp == 0 ? 0u : *tmem_slot;
+  if (threadIdx.x == 32) SLIDER_TRACE(1);
+
+  // The two issuing roles run in ONE ELECTED lane (elect.sync, not `lane == 0`): ptxas then knows a single thread
+  // is active and feeds UTMALDG / UTCHMMA from uniform registers directly instead of wrapping every issue in an
+  // ELECT + R2UR.BROADCAST waterfall loop (which made the producer, ~500 cycles per K block, the main-loop bound).
+  if (warp == 0 && ptx::elect_one()) {
+    // ===================== TMA producer =====================
+    prod_begin();
+    SLIDER_TRACE(8);
+    if (phave && prod_owner())
+      for (int d = 0; d < p.w_prefetch && pit + d < pit1; ++d) prod_prefetch_w(pit + d);
+    pdl_wait();
+    bool first = true;
+    while (phave) {
+      prod_issue();
+      if (first) { SLIDER_TRACE(2); first = false; }
+    }
+  } else if (warp == 1 && ptx::elect_one()) {
+    // ===================== MMA issuer =====================
+    // With the adapter on, W tile (BN rows) and lora_down tile (HCOLS rows) are adjacent in shared
+    // memory and their accumulators adjacent in TMEM: ONE tcgen05.mma of N = BN + HCOLS covers both.
+    constexpr uint32_t idesc_main = ptx::make_idesc(Tr::kFmt, BM, BN);
+    constexpr uint32_t idesc_lora = ptx::make_idesc(Tr::kFmt, BM, BN + HCOLS);
+    const uint32_t idesc = p.lora ? idesc_lora : idesc_main;
+    uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
+    for (int unit = blockIdx.x; unit < p.total_units; unit += gridDim.x) {
+      int it0 = 0, it1 = p.kiters, j = 0;
+      if (p.ksplit > 1) {
+        uint32_t tile, split;
+        p.fd_ksplit.divmod((uint32_t)unit, tile, split);
+        split_range(p, split, it0, it1);
+        j = it0 - (int)p.fd_per_tap.div((uint32_t)it0) * p.per_tap;
+      }
+      ptx::mbar_wait(ptx::smem_u32(tempty_bar + as), aphase ^ 1);
+      ptx::tc_fence_after();
+      const uint32_t d_main = tmem_base + as * ACC_COLS;
+      uint32_t acc = 0;
+      for (int it = it0; it < it1; ++it) {
+        ptx::mbar_wait(ptx::smem_u32((Tr::kSplit3 ? xf_bar : full_bar) + stage), phase);
+        ptx::tc_fence_after();
+        if (unit == (int)blockIdx.x && it == it0) SLIDER_TRACE(3);
+        const uint32_t sa = smem_base + stage * kStageStride;
+        const bool main_blk = j < p.cblocks;
+        const uint32_t rb = main_blk ? (uint32_t)ROW_BYTES : (uint32_t)Tr::kExtRowBytes;
+        const uint32_t id = main_blk ? idesc : idesc_main;
+        const int ksteps = main_blk ? KSTEPS : EXT_KSTEPS;
+        const uint64_t da = ptx::smem_desc_kmajor(sa, rb);
+        const uint64_t db = ptx::smem_desc_kmajor(sa + A_BYTES, rb);
+        if (Tr::kSplit3) {
+          const uint64_t da_lo = ptx::smem_desc_kmajor(sa + STAGE_BYTES, rb);
+          const uint64_t db_lo = ptx::smem_desc_kmajor(sa + STAGE_BYTES + A_BYTES, rb);
+          for (int k = 0; k < ksteps; ++k) {
+            Tr::mma(d_main, da_lo + 2 * k, db + 2 * k, id, acc | (uint32_t)k);
+            Tr::mma(d_main, da + 2 * k, db_lo + 2 * k, id, 1u);
+            Tr::mma(d_main, da + 2 * k, db + 2 * k, id, 1u);
+          }
+        } else if (main_blk) {
+#pragma unroll
+          for (int k = 0; k < KSTEPS; ++k) Tr::mma(d_main, da + 2 * k, db + 2 * k, id, acc | (uint32_t)k);
+        } else {
+#pragma unroll
+          for (int k = 0; k < EXT_KSTEPS; ++k) Tr::mma(d_main, da + 2 * k, db + 2 * k, id, acc | (uint32_t)k);
+        }
+        acc = 1;
+        ptx::mma_commit(ptx::smem_u32(empty_bar + stage));
+        if (++stage == (uint32_t)kStages) { stage = 0; phase ^= 1; }
+        if (++j == p.per_tap) j = 0;
+      }
+      ptx::mma_commit(ptx::smem_u32(tfull_bar + as));
+      if (unit == (int)blockIdx.x) SLIDER_TRACE(4);
+      if (++as == ACC_STAGES) { as = 0; aphase ^= 1; }
+    }
+  } else if (warp >= 2) {
+    // ===================== epilogue =====================
+    // Eight warps = two groups of four; a group covers all 128 accumulator rows (one TMEM lane quarter per warp)
+    // and owns HALF_N of the tile's columns.  Per tile a thread reads its row of the group's columns (and the h
+    // columns) with back-to-back tcgen05.ld and ONE wait, hands the accumulator stage back to the MMA warp, and then,
+    // per 80-byte chunk (40 bf16 / 20 fp32 columns): (+bias + s*h.Bup^T, cast) -> shared staging -> one TMA store
+    // (box {chunk, TW, TH, TB}: clips out-of-range pixels/channels).  NB staging buffers and one named barrier per
+    // group: before the barrier of chunk c the group's issuing thread waits until at most NB-2 stores still read
+    // shared memory, so the buffer the group fills next (chunk c+1, last used by store c+1-NB) is free once its
+    // threads pass that barrier.
+    const int q = warp & 3;               // TMEM lane quarter this warp may read
+    const int row = q * 32 + lane;        // tile row == TMEM lane
+    const int et = threadIdx.x - 64;      // 0..255 among epilogue threads
+    const int grp = et >> 7;              // column half owned by this thread's group
+    const int gt = et & 127;
+    constexpr int CW = OUT_ROW_BYTES / (int)sizeof(T);    // columns per store chunk
+    constexpr int CPG = HALF_N / CW;                      // store chunks per group
+    constexpr int PW = 16 / (int)sizeof(T);               // columns per 16-byte piece
+    constexpr int PCPG = HALF_N / PCW;                    // split-K partial chunks per group
+    float* s_bias = s_epi + BN * 4 * (R4 > 0 ? R4 : 1);
+    const uint32_t out_base = ptx::smem_u32(s_out) + (uint32_t)(grp * NB) * OUT_BYTES;
+    const uint32_t epi_s = ptx::smem_u32(s_epi), bias_s = ptx::smem_u32(s_bias);
+    uint32_t as = 0, aphase = 0, ob = 0, xs = 0, xphase = 0;
+    const T* __restrict__ bias = reinterpret_cast<const T*>(p.bias);
+    const T* __restrict__ Bup = reinterpret_cast<const T*>(p.Bup);
+#define SLIDER_GROUP_BAR() asm volatile("bar.sync %0, 128;" ::"r"(3 + grp) : "memory")
+    for (int unit = blockIdx.x; unit < p.total_units; unit += gridDim.x) {
+      uint32_t tile = (uint32_t)unit, split = 0;
+      if (p.ksplit > 1) p.fd_ksplit.divmod((uint32_t)unit, tile, split);
+      if (Tr::kSplit3) {
+        // fp32: split every stage of this unit into hi / lo before the MMA warp may consume it
+        int n_it = p.kiters;
+        if (p.ksplit > 1) {
+          int a0, a1;
+          split_range(p, split, a0, a1);
+          n_it = a1 - a0;
+        }
+        for (int it = 0; it < n_it; ++it) {
+          ptx::mbar_wait(ptx::smem_u32(full_bar + xs), xphase);
+          float4* hi = reinterpret_cast<float4*>(smem + (size_t)xs * kStageStride);
+          float4* lo = reinterpret_cast<float4*>(smem + (size_t)xs * kStageStride + STAGE_BYTES);
+          for (int i = et; i < STAGE_BYTES / 16; i += kEpiThreads) {
+            const float4 v = hi[i];
+            float4 h4, l4;
+            h4.x = __uint_as_float(__float_as_uint(v.x) & 0xffffe000u); l4.x = v.x - h4.x;
+            h4.y = __uint_as_float(__float_as_uint(v.y) & 0xffffe000u); l4.y = v.y - h4.y;
+            h4.z = __uint_as_float(__float_as_uint(v.z) & 0xffffe000u); l4.z = v.z - h4.z;
+            h4.w = __uint_as_float(__float_as_uint(v.w) & 0xffffe000u); l4.w = v.w - h4.w;
+            hi[i] = h4;
+            lo[i] = l4;
+          }
+          ptx::fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(xf_bar + xs));
+          if (++xs == (uint32_t)kStages) { xs = 0; xphase ^= 1; }
+        }
+      }
+      if (p.ksplit > 1) {
+        // split-K: park the fp32 partial tile (main + h columns) in the L2-resident workspace,
+        // [unit][chunk][row][PCW]; splitk_finalize_kernel reduces over the splits in a fixed order.
+        // one warp polls the accumulator-ready mbarrier, the others sleep on the hardware barrier: eight warps
+        // spinning on try_wait steal shared-memory cycles from the operand pipeline for the whole main loop
+        if (et < 32) ptx::mbar_wait(ptx::smem_u32(tfull_bar + as), aphase);
+        asm volatile("bar.sync 2, 256;" ::: "memory");
+        ptx::tc_fence_after();
+        if (et == 0 && unit == (int)blockIdx.x) SLIDER_TRACE(5);
+        const uint32_t t_acc = tmem_base + ((uint32_t)(q * 32) << 16) + as * ACC_COLS;
+        const bool park_h = grp == 0 && R4 > 0;                    // group 0 also parks the h columns
+        uint32_t v[PCPG][PCW];
+        uint32_t hr[16];
+#pragma unroll
+        for (int ci = 0; ci < PCPG; ++ci) tmem_ld_cols<PCW>(t_acc + (grp * PCPG + ci) * PCW, v[ci]);
+        if (park_h) ptx::tmem_ld_x16(t_acc + BN, hr);
+        ptx::tmem_ld_wait();
+        // the accumulator stage is free again as soon as it sits in registers
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(tempty_bar + as));
+        if (++as == ACC_STAGES) { as = 0; aphase ^= 1; }
+#pragma unroll
+        for (int ci = 0; ci <= PCPG; ++ci) {
+          if (ci == PCPG && !park_h) break;
+          const int chunk = ci < PCPG ? grp * PCPG + ci : NCHUNK - 1;
+          const uint32_t dst = out_base + ob * OUT_BYTES + row * OUT_ROW_BYTES;
+          if (ci < PCPG) {
+#pragma unroll
+            for (int k = 0; k < OUT_ROW_BYTES / 16; ++k)
+              ptx::st_shared_v4(dst + k * 16, v[ci % PCPG][4 * k], v[ci % PCPG][4 * k + 1], v[ci % PCPG][4 * k + 2],
+                                v[ci % PCPG][4 * k + 3]);
+          } else {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) ptx::st_shared_v4(dst + k * 16, hr[4 * k], hr[4 * k + 1], hr[4 * k + 2], hr[4 * k + 3]);
+            ptx::st_shared_v4(dst + 64, 0u, 0u, 0u, 0u);
+          }
+          ptx::fence_proxy_async_smem();
+          if (gt == 0) ptx::bulk_wait_read<NB - 2>();   // buffer of chunk c+1 (last read by store c+1-NB) is free past the barrier
+          SLIDER_GROUP_BAR();
+          if (gt == 0) {
+            ptx::tma_store_2d(&tmP, out_base + ob * OUT_BYTES, 0, (unit * NCHUNK + chunk) * BM);
+            ptx::bulk_commit();
+          }
+          if (++ob == (uint32_t)NB) ob = 0;
+        }
+        if (et == 0 && unit == (int)blockIdx.x) SLIDER_TRACE(6);
+        continue;
+      }
+      const TileCoord tc = tile_coord<BN>(p, unit);
+      // stage s*Bup[n0.., :] and bias[n0..] for this tile (fp32) while the MMAs run
+      asm volatile("bar.sync 2, 256;" ::: "memory");
+      for (int i = et; i < BN; i += kEpiThreads) {
+        const int n = tc.n0 + i;
+        s_bias[i] = (bias != nullptr && n < p.N) ? Elem<T>::to_f(bias[n]) : 0.f;
+        if (R4 > 0) {
+#pragma unroll
+          for (int j = 0; j < 4 * R4; ++j)
+            s_epi[i * (4 * R4) + j] =
+                (n < p.N && j < p.rank) ? p.s * Elem<T>::to_f(Bup[(size_t)n * p.bup_ld + (size_t)j * p.bup_jd]) : 0.f;
+        }
+      }
+      // one warp polls the accumulator-ready mbarrier, the others sleep on the hardware barrier (which also
+      // publishes the tables staged above): eight warps spinning on try_wait steal shared-memory cycles from the
+      // operand pipeline for the whole main loop
+      if (et < 32) ptx::mbar_wait(ptx::smem_u32(tfull_bar + as), aphase);
+      asm volatile("bar.sync 2, 256;" ::: "memory");
+      ptx::tc_fence_after();
+      if (et == 0 && unit == (int)blockIdx.x) SLIDER_TRACE(5);
+      const uint32_t t_main = tmem_base + ((uint32_t)(q * 32) << 16) + as * ACC_COLS;
+
+      // every TMEM read of this tile, back to back, ONE wait; then the stage goes back to the MMA warp
+      uint32_t v[CPG][CW];
+      uint32_t hr[16];
+#pragma unroll
+      for (int ci = 0; ci < CPG; ++ci) tmem_ld_cols<CW>(t_main + grp * HALF_N + ci * CW, v[ci]);
+      if (R4 > 0) {
+        // grouped adapters: this tile's group owns `rank` of the 16 h columns, starting at its offset
+        const int hoff = p.group_n > 0 ? (tc.n0 / p.group_n) * p.rank : 0;
+        ptx::tmem_ld_x16(t_main + BN + hoff, hr);
+      }
+      ptx::tmem_ld_wait();
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(tempty_bar + as));
+      if (++as == ACC_STAGES) { as = 0; aphase ^= 1; }
+      if (et == 0 && unit == (int)blockIdx.x) SLIDER_TRACE(9);
+
+      float hv[R4 > 0 ? 4 * R4 : 1];
+      if (R4 > 0) {
+#pragma unroll
+        for (int j = 0; j < 4 * R4; ++j) hv[j] = __uint_as_float(hr[j]);
+        if (p.h_out != nullptr && tc.n_blk == 0 && grp == 1) {
+          const int lw = row % p.TW, lh = (row / p.TW) % p.TH, lb = row / (p.TW * p.TH);
+          const bool row_ok = row < p.rows && tc.w0 + lw < p.W && tc.h0 + lh < p.H && tc.b0 + lb < p.B;
+          const size_t pix = ((size_t)(tc.b0 + lb) * p.H + (tc.h0 + lh)) * p.W + (tc.w0 + lw);
+          if (row_ok) {
+#pragma unroll
+            for (int j = 0; j < 4 * R4; ++j)
+              if (j < p.rank) p.h_out[pix * p.rank + j] = hv[j];
+          }
+        }
+      }
+#pragma unroll
+      for (int ci = 0; ci < CPG; ++ci) {
+        const int col0 = grp * HALF_N + ci * CW;
+        if (tc.n0 + col0 >= p.N) break;              // ragged last column tile (uniform over the group)
+        const uint32_t dst = out_base + ob * OUT_BYTES + row * OUT_ROW_BYTES;
+#pragma unroll
+        for (int pc = 0; pc < OUT_ROW_BYTES / 16; ++pc) {
+          float o[PW];
+#pragma unroll
+          for (int k = 0; k < PW; ++k) {
+            const int i = col0 + pc * PW + k;
+            // explicit ld.shared: the generic pointers derived from the re-aligned base compile to LD.E
+            float a = __uint_as_float(v[ci][pc * PW + k]) + ptx::ld_shared_f32(bias_s + i * 4);
+            if (R4 > 0) {
+#pragma unroll
+              for (int j4 = 0; j4 < R4; ++j4) {
+                const float4 b = ptx::ld_shared_f4(epi_s + i * (16 * R4) + j4 * 16);
+                a = fmaf(hv[4 * j4 + 0], b.x, a);
+                a = fmaf(hv[4 * j4 + 1], b.y, a);
+                a = fmaf(hv[4 * j4 + 2], b.z, a);
+                a = fmaf(hv[4 * j4 + 3], b.w, a);
+              }
+            }
+            o[k] = a;
+          }
+          if (sizeof(T) == 2) {
+            uint32_t w[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              __nv_bfloat162 h2 = __floats2bfloat162_rn(o[(2 * k) % PW], o[(2 * k + 1) % PW]);
+              w[k] = *reinterpret_cast<uint32_t*>(&h2);
+            }
+            ptx::st_shared_v4(dst + pc * 16, w[0], w[1], w[2], w[3]);
+          } else {
+            ptx::st_shared_v4(dst + pc * 16, __float_as_uint(o[0]), __float_as_uint(o[1]), __float_as_uint(o[2 % PW]),
+                              __float_as_uint(o[3 % PW]));
+          }
+        }
+        ptx::fence_proxy_async_smem();
+        if (gt == 0) ptx::bulk_wait_read<NB - 2>();     // buffer of chunk c+1 (last read by store c+1-NB) is free past the barrier
+        SLIDER_GROUP_BAR();
+        if (gt == 0) {
+          if (p.accumulate) ptx::tma_reduce_add_4d(&tmY, out_base + ob * OUT_BYTES, tc.n0 + col0, tc.w0, tc.h0, tc.b0);
+          else ptx::tma_store_4d(&tmY, out_base + ob * OUT_BYTES, tc.n0 + col0, tc.w0, tc.h0, tc.b0);
+          ptx::bulk_commit();
+        }
+        if (++ob == (uint32_t)NB) ob = 0;
+      }
+      if (et == 0 && unit == (int)blockIdx.x) SLIDER_TRACE(6);
+    }
+    if (gt == 0) ptx::bulk_wait_all();    // all TMA stores of this group have landed before the CTA exits
+#undef SLIDER_GROUP_BAR
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+  }
+  if (threadIdx.x == 0) SLIDER_TRACE(7);
+#undef SLIDER_TRACE
+}
+
+// ---------------------------------------------------------------------------------------------
+// Split-K finalize: y = sum_splits(partial) + bias + s * h . Bup^T.  One thread per (row, 4-column piece, chunk c)
+// also owns the same piece of chunk c + 4, so the row's h partials are read once per 8 output columns.
+// Thread order (piece, row, chunk) follows the partial layout, so reads are fully coalesced.
+template <typename T, int R4, int BN>
+__global__ void __launch_bounds__(256)
+splitk_finalize_kernel(const GemmParams p) {
+  constexpr int NCHUNK = TileCfg<BN>::NCHUNK;
+  constexpr size_t UNIT_FLOATS = TileCfg<BN>::UNIT_FLOATS;
+  pdl_trigger();
+  constexpr int PIECES = PCW / 4;                  // 16-byte pieces per partial row
+  constexpr int HC = (NCHUNK - 1) / 2;             // chunk pairs (c, c + HC)
+  constexpr int PER_TILE = BM * PIECES * HC;
+  const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (idx >= (long long)p.total_tiles * PER_TILE) return;
+  const int tile = (int)(idx / PER_TILE);
+  const int rem = (int)(idx - (long long)tile * PER_TILE);
+  const int pc = rem % PIECES, row = (rem / PIECES) & (BM - 1), c = rem / (PIECES * BM);
+  const TileCoord tc = tile_coord<BN>(p, tile);
+  const int lw = row % p.TW, lh = (row / p.TW) % p.TH, lb = row / (p.TW * p.TH);
+  const bool row_ok = row < p.rows && tc.w0 + lw < p.W && tc.h0 + lh < p.H && tc.b0 + lb < p.B;
+  const int n0 = tc.n0 + c * PCW + pc * 4, n1 = n0 + HC * PCW;
+  if (!row_ok || n0 >= p.N) return;
+  const bool second = n1 < p.N;
+  const size_t pix = ((size_t)(tc.b0 + lb) * p.H + (tc.h0 + lh)) * p.W + (tc.w0 + lw);
+  const float* src = p.partial + (size_t)tile * p.ksplit * UNIT_FLOATS + ((size_t)c * BM + row) * PCW + pc * 4;
+  const int hoff = p.group_n > 0 ? (tc.n0 / p.group_n) * p.rank : 0;
+  const float* hsrc = p.partial + (size_t)tile * p.ksplit * UNIT_FLOATS + ((size_t)(NCHUNK - 1) * BM + row) * PCW + hoff;
+  const T* __restrict__ bias = reinterpret_cast<const T*>(p.bias);
+  const T* __restrict__ Bup = reinterpret_cast<const T*>(p.Bup);
+  T* const dst0 = reinterpret_cast<T*>(p.y) + pix * (size_t)p.N + n0;
+  T* const dst1 = reinterpret_cast<T*>(p.y) + pix * (size_t)p.N + n1;
+  // Everything the epilogue needs besides the partials is requested BEFORE the split loop, so that its latency hides
+  // behind the partial loads instead of following them: the frozen bias even before the dependent-launch wait, the
+  // rank-4 bf16 up-projection rows (8 bytes per output column) and the residual right after it.
+  float bs[8];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    bs[k] = bias != nullptr ? Elem<T>::to_f(bias[n0 + k]) : 0.f;
+    bs[4 + k] = (bias != nullptr && second) ? Elem<T>::to_f(bias[n1 + k]) : 0.f;
+  }
+  pdl_wait();
+  constexpr bool kPackB = R4 == 1 && sizeof(T) == 2;
+  const bool packb = kPackB && p.rank == 4 && p.bup_ld == 4 && p.bup_jd == 1 && Bup != nullptr;
+  uint2 bq[kPackB ? 8 : 1];
+  if (kPackB && packb) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      bq[k] = *reinterpret_cast<const uint2*>(Bup + (size_t)(n0 + k) * 4);
+      bq[4 + k] = *reinterpret_cast<const uint2*>(Bup + (size_t)(second ? n1 + k : n0 + k) * 4);
+    }
+  }
+  uint4 resq[2] = {make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};       // bf16: .x .y used; fp32: all four
+  if (p.accumulate) {
+    if (sizeof(T) == 2) {
+      const uint2 q0 = *reinterpret_cast<const uint2*>(dst0), q1 = *reinterpret_cast<const uint2*>(second ? dst1 : dst0);
+      resq[0].x = q0.x; resq[0].y = q0.y; resq[1].x = q1.x; resq[1].y = q1.y;
+    } else {
+      resq[0] = *reinterpret_cast<const uint4*>(dst0);
+      resq[1] = *reinterpret_cast<const uint4*>(second ? dst1 : dst0);
+    }
+  }
+  float o[8];
+  float hv[R4 > 0 ? 4 * R4 : 1];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) o[k] = 0.f;
+#pragma unroll
+  for (int j = 0; j < (R4 > 0 ? 4 * R4 : 1); ++j) hv[j] = 0.f;
+  // branch-free loop bodies (the second chunk of a ragged tile re-reads the first and is discarded), so that the
+  // unrolled loads of several splits are in flight together: the kernel is pure L2 latency otherwise
+  const float* srcb = second ? src + (size_t)HC * BM * PCW : src;
+  if (R4 == 0 || (hoff & 3) == 0) {
+#pragma unroll 6
+    for (int s = 0; s < p.ksplit; ++s) {
+      const float4 a = __ldcg(reinterpret_cast<const float4*>(src + (size_t)s * UNIT_FLOATS));
+      const float4 b = __ldcg(reinterpret_cast<const float4*>(srcb + (size_t)s * UNIT_FLOATS));
+      o[0] += a.x; o[1] += a.y; o[2] += a.z; o[3] += a.w;
+      o[4] += b.x; o[5] += b.y; o[6] += b.z; o[7] += b.w;
+      if (R4 > 0) {
+#pragma unroll
+        for (int j4 = 0; j4 < R4; ++j4) {
+          const float4 h4 = __ldcg(reinterpret_cast<const float4*>(hsrc + (size_t)s * UNIT_FLOATS) + j4);
+          hv[4 * j4] += h4.x; hv[4 * j4 + 1] += h4.y; hv[4 * j4 + 2] += h4.z; hv[4 * j4 + 3] += h4.w;
+        }
+      }
+    }
+  } else {    // grouped adapters whose h offset is not a multiple of four columns: scalar h loads
+#pragma unroll 2
+    for (int s = 0; s < p.ksplit; ++s) {
+      const float4 a = __ldcg(reinterpret_cast<const float4*>(src + (size_t)s * UNIT_FLOATS));
+      const float4 b = __ldcg(reinterpret_cast<const float4*>(srcb + (size_t)s * UNIT_FLOATS));
+      o[0] += a.x; o[1] += a.y; o[2] += a.z; o[3] += a.w;
+      o[4] += b.x; o[5] += b.y; o[6] += b.z; o[7] += b.w;
+#pragma unroll
+      for (int j = 0; j < (R4 > 0 ? 4 * R4 : 1); ++j)
+        if (R4 > 0 && hoff + j < HCOLS) hv[j] += __ldcg(hsrc + (size_t)s * UNIT_FLOATS + j);
+    }
+  }
+#pragma unroll
+  for (int half = 0; half < 2; ++half) {
+    if (half == 1 && !second) break;
+    const int n = half == 0 ? n0 : n1;
+    float r[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      float a = o[half * 4 + k] + bs[half * 4 + k];
+      if (R4 > 0) {
+        float l = 0.f;
+        if (kPackB && packb) {
+          const uint2 q = bq[kPackB ? half * 4 + k : 0];
+          l = fmaf(hv[0], __uint_as_float(q.x << 16), l);
+          l = fmaf(hv[1 % (R4 > 0 ? 4 * R4 : 1)], __uint_as_float(q.x & 0xffff0000u), l);
+          l = fmaf(hv[2 % (R4 > 0 ? 4 * R4 : 1)], __uint_as_float(q.y << 16), l);
+          l = fmaf(hv[3 % (R4 > 0 ? 4 * R4 : 1)], __uint_as_float(q.y & 0xffff0000u), l);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 4 * R4; ++j)
+            if (j < p.rank) l = fmaf(hv[j], Elem<T>::to_f(Bup[(size_t)(n + k) * p.bup_ld + (size_t)j * p.bup_jd]), l);
+        }
+        a = fmaf(p.s, l, a);
+      }
+      r[k] = a;
+    }
+    T* dst = half == 0 ? dst0 : dst1;
+    if (sizeof(T) == 2) {
+      uint2* d2 = reinterpret_cast<uint2*>(dst);
+      if (p.accumulate) {  // y holds the residual: same two roundings as `residual + module(x)` in element dtype
+        const uint4 q = resq[half];
+        const float res[4] = {__uint_as_float(q.x << 16), __uint_as_float(q.x & 0xffff0000u),
+                              __uint_as_float(q.y << 16), __uint_as_float(q.y & 0xffff0000u)};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) r[k] = __bfloat162float(__float2bfloat16_rn(r[k])) + res[k];
+      }
+      __nv_bfloat162 lo2 = __floats2bfloat162_rn(r[0], r[1]), hi2 = __floats2bfloat162_rn(r[2], r[3]);
+      *d2 = make_uint2(*reinterpret_cast<uint32_t*>(&lo2), *reinterpret_cast<uint32_t*>(&hi2));
+    } else {
+      float4* d4 = reinterpret_cast<float4*>(dst);
+      if (p.accumulate) {
+        const uint4 q = resq[half];
+        r[0] += __uint_as_float(q.x); r[1] += __uint_as_float(q.y); r[2] += __uint_as_float(q.z); r[3] += __uint_as_float(q.w);
+      }
+      *d4 = make_float4(r[0], r[1], r[2], r[3]);
+    }
+  }
+  if (R4 > 0 && p.h_out != nullptr && tc.n_blk == 0 && c == 0 && pc == 0) {
+#pragma unroll
+    for (int j = 0; j < 4 * R4; ++j)
+      if (j < p.rank) p.h_out[pix * p.rank + j] = hv[j];
+  }
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// Launch of one tile width (explicitly instantiated in lora_gemm_bn160.cu / lora_gemm_bn80.cu so that the two sets of
+// kernels compile in parallel).
+template <typename T, int BN>
+static int launch_gemm_t(int r4, const CUtensorMap& a, const CUtensorMap& w, const CUtensorMap& l,
+                         const CUtensorMap& xe, const CUtensorMap& we, const CUtensorMap& my, const CUtensorMap& mp,
+                         const GemmParams& p, cudaStream_t st) {
+  using Cfg = TileCfg<BN>;
+  void (*kern)(CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap,
+               GemmParams) = nullptr;
+  void (*fin)(GemmParams) = nullptr;
+  switch (r4) {
+    case 0: kern = lora_gemm_kernel<T, 0, BN>; fin = splitk_finalize_kernel<T, 0, BN>; break;
+    case 1: kern = lora_gemm_kernel<T, 1, BN>; fin = splitk_finalize_kernel<T, 1, BN>; break;
+    case 2: kern = lora_gemm_kernel<T, 2, BN>; fin = splitk_finalize_kernel<T, 2, BN>; break;
+    default: kern = lora_gemm_kernel<T, 4, BN>; fin = splitk_finalize_kernel<T, 4, BN>; break;
+  }
+  static thread_local const void* configured[8] = {nullptr};
+  bool done = false;
+  for (auto c : configured) done |= (c == (const void*)kern);
+  if (!done) {
+    SLIDER_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::smem_bytes(r4)));
+    for (auto& c : configured) if (c == nullptr) { c = (const void*)kern; break; }
+  }
+  const int grid = p.total_units < sm_count() ? p.total_units : sm_count();
+  launch_pdl(kern, dim3(grid), dim3(kGemmThreads), Cfg::smem_bytes(r4), st, a, w, l, xe, we, my, mp, p);
+  int rc = post_launch("lora_gemm_kernel");
+  if (rc || p.ksplit == 1) return rc;
+  const long long threads = (long long)p.total_tiles * BM * (BN / 8);
+  launch_pdl(fin, dim3((unsigned)((threads + 255) / 256)), dim3(256), 0, st, p);
+  return post_launch("splitk_finalize_kernel");
+}
+
+template <int BN>
+int launch_gemm_tile(int dtype, int r4, const CUtensorMap& a, const CUtensorMap& w, const CUtensorMap& l,
+                     const CUtensorMap& xe, const CUtensorMap& we, const CUtensorMap& my, const CUtensorMap& mp,
+                     const GemmParams& p, cudaStream_t st) {
+  if (dtype == SLIDER_BF16) return launch_gemm_t<__nv_bfloat16, BN>(r4, a, w, l, xe, we, my, mp, p, st);
+  return launch_gemm_t<float, BN>(r4, a, w, l, xe, we, my, mp, p, st);
+}
+
+}  // namespace slider

@@ -128,11 +128,12 @@ class SliderEngine:
 
     def _body_train(self):
         self.network.flat_grad.zero_()
-        with self.network:
-            eps = self._unet(self._model_input(2), self.emb_tgt, self.xl and self.xl["tgt"])
-            target = train_util._CFGCombineFn.apply(eps, 1.0)
-        loss = guidance_mse(target, self.positive, self.neutral, self.uncond, self.guidance, self.sign)
-        loss.backward()
+        with self.network.packed_transposes():
+            with self.network:
+                eps = self._unet(self._model_input(2), self.emb_tgt, self.xl and self.xl["tgt"])
+                target = train_util._CFGCombineFn.apply(eps, 1.0)
+            loss = guidance_mse(target, self.positive, self.neutral, self.uncond, self.guidance, self.sign)
+            loss.backward()
         self.loss.copy_(loss.detach())
 
     def _body_predict_train(self):
@@ -147,12 +148,13 @@ class SliderEngine:
         side.wait_stream(main)
         with torch.cuda.stream(side), ops.workspace_lane(1):
             self._body_predict()
-        with self.network:
-            eps = self._unet(self._model_input(2), self.emb_tgt, self.xl and self.xl["tgt"])
-            target = train_util._CFGCombineFn.apply(eps, 1.0)
-        main.wait_stream(side)
-        loss = guidance_mse(target, self.positive, self.neutral, self.uncond, self.guidance, self.sign)
-        loss.backward()
+        with self.network.packed_transposes():
+            with self.network:
+                eps = self._unet(self._model_input(2), self.emb_tgt, self.xl and self.xl["tgt"])
+                target = train_util._CFGCombineFn.apply(eps, 1.0)
+            main.wait_stream(side)
+            loss = guidance_mse(target, self.positive, self.neutral, self.uncond, self.guidance, self.sign)
+            loss.backward()
         self.loss.copy_(loss.detach())
 
     def _run(self, name: str, body):
@@ -251,15 +253,16 @@ class SliderEngine:
         the noise that was added -> backward into the flat gradient buffer (accumulating)."""
         noisy = ops.cfg_step(self.lat, None, None, self.noise, dev_coef=self.coef)
         self.network.set_lora_slider(scale)
-        with self.network:
-            x = torch.cat([noisy] * 2)
-            if self._needs_scale:
-                x = ops.cfg_step(x, None, None, None, dev_coef=self.in_scale)
-            eps = self._unet(x, emb, None)
-            target = train_util._CFGCombineFn.apply(eps, 1.0)
         from .prompt_util import plain_mse
-        loss = plain_mse(target, self.noise)
-        loss.backward()
+        with self.network.packed_transposes():
+            with self.network:
+                x = torch.cat([noisy] * 2)
+                if self._needs_scale:
+                    x = ops.cfg_step(x, None, None, None, dev_coef=self.in_scale)
+                eps = self._unet(x, emb, None)
+                target = train_util._CFGCombineFn.apply(eps, 1.0)
+            loss = plain_mse(target, self.noise)
+            loss.backward()
         return loss.detach()
 
     def image_slider_step(self, lat_low: torch.Tensor, lat_high: torch.Tensor, noise: torch.Tensor, timesteps_to: int,

@@ -10,8 +10,10 @@ plus the extended-K input-gradient GEMM.
 """
 from __future__ import annotations
 
+import contextlib
 import math
 import os
+import types
 from typing import List, Literal, Optional
 
 import torch
@@ -37,10 +39,11 @@ class _FusedLoRAFn(torch.autograd.Function):
         s = float(mod.multiplier) * float(mod.scale)
         k = mod._ksize
         a_p, b_p = mod._packed_down(a_w), mod._packed_up(b_w)
-        need_x, need_a, need_b = ctx.needs_input_grad[0], ctx.needs_input_grad[1], ctx.needs_input_grad[2]
+        need_a, need_b = ctx.needs_input_grad[1], ctx.needs_input_grad[2]
         train_lora = (need_a or need_b) and s != 0.0
-        y, h = ops.lora_forward(x, mod._packed_base(), mod._bias(), a_p, b_p, s, ksize=k, want_h=train_lora)
-        ctx.mod, ctx.s, ctx.train_lora = mod, s, train_lora
+        y, h = ops.lora_forward(x, mod._packed_base(), mod._bias(), a_p, b_p, s, ksize=k, want_h=train_lora,
+                                stride=mod._stride)
+        ctx.mod, ctx.s, ctx.train_lora, ctx.x_shape = mod, s, train_lora, tuple(x.shape)
         ctx.save_for_backward(x if train_lora else None, h, a_p, b_p)
         return y
 
@@ -49,22 +52,44 @@ class _FusedLoRAFn(torch.autograd.Function):
         mod, s = ctx.mod, ctx.s
         x, h, a_p, b_p = ctx.saved_tensors
         gy = gy.contiguous()
-        k, r = mod._ksize, mod.lora_dim
-        dx = ga = gb = dh = None
+        k, r, stride = mod._ksize, mod.lora_dim, mod._stride
+        need_x = ctx.needs_input_grad[0]
+        dx = ga = gb = dA = dB = None
+        flat = mod._flat_grads
         if ctx.train_lora:
-            flat = mod._flat_grads
             if flat is not None:
                 dA, dB = flat
-                dh = ops.lora_grad(gy, x, h, b_p, s, k, dA, dB, accumulate=True)
             else:
                 dA = torch.empty(a_p.shape, device=gy.device, dtype=torch.float32)
                 dB = torch.empty(b_p.shape, device=gy.device, dtype=torch.float32)
-                dh = ops.lora_grad(gy, x, h, b_p, s, k, dA, dB, accumulate=False)
-                ga = mod._unpack_down_grad(dA)
-                gb = dB.to(b_p.dtype).reshape(mod.lora_up.weight.shape)
-        if ctx.needs_input_grad[0]:
-            at = ops.pack_at(a_p, k) if dh is not None else None
-            dx = ops.lora_input_grad(gy, mod._packed_base_t(), dh, at, mod._cin, k, r if dh is not None else 0)
+        acc = ctx.train_lora and flat is not None
+        if k == 1 and need_x and s != 0.0:
+            # 1x1 / Linear: dx and the rank-r gradient g = gy.B from ONE launch, dA and dB from one more
+            dx = ops.lora_backward_1x1(gy, x, h, mod._packed_base_t(), a_p, b_p, s, dA, dB, accumulate=acc,
+                                       bt=mod._bt_ready())
+        else:
+            dh = None
+            if s != 0.0 and (ctx.train_lora or need_x):      # a frozen adapter still contributes s*dh.A to dx
+                xs = x if x is not None else gy.new_empty(ctx.x_shape)       # shape carrier only (dA is None)
+                dh = ops.lora_grad(gy, xs, h, b_p, s, k, dA, dB, accumulate=acc, stride=stride)
+            if need_x:
+                if stride == 2:
+                    # transposed stride-2 convolution = stride-1 input gradient of the zero-stuffed output gradient
+                    # (three Downsample2D layers, once per training step)
+                    Bn, H, W = ctx.x_shape[0], ctx.x_shape[1], ctx.x_shape[2]
+                    Ho, Wo = gy.shape[1], gy.shape[2]
+                    gz = gy.new_zeros(Bn, H, W, gy.shape[-1])
+                    gz[:, ::2, ::2] = gy
+                    gy = gz
+                    if dh is not None:
+                        dz = dh.new_zeros(Bn, H, W, 16)
+                        dz[:, ::2, ::2] = dh.view(Bn, Ho, Wo, 16)
+                        dh = dz.view(-1, 16)
+                at = ops.pack_at(a_p, k) if dh is not None else None
+                dx = ops.lora_input_grad(gy, mod._packed_base_t(), dh, at, mod._cin, k, r if dh is not None else 0)
+        if ctx.train_lora and flat is None:
+            ga = mod._unpack_down_grad(dA)
+            gb = dB.to(b_p.dtype).reshape(mod.lora_up.weight.shape)
         return dx, ga, gb, None
 
 
@@ -115,6 +140,13 @@ class LoRAModule(nn.Module):
         self.org_module = org_module  # removed in apply_to (reference keeps it out of state_dict)
         self._flat_grads = None
         self._cache = {}
+        self._bt = None        # (state, view [r, Cout]) of lora_up^T, filled by LoRANetwork.pack_transposes()
+
+    def _bt_ready(self):
+        """lora_up^T for the fused 1x1 backward when the network has packed it for the current parameters."""
+        if self._bt is not None and self._bt[0].valid:
+            return self._bt[1]
+        return None
 
     def apply_to(self):
         self.org_forward = self.org_module.forward
@@ -183,9 +215,7 @@ class LoRAModule(nn.Module):
             xn = x.permute(0, 2, 3, 1)
             if not xn.is_contiguous():
                 xn = xn.contiguous()
-            y = _FusedLoRAFn.apply(xn, a_w, b_w, self)
-            if self._stride == 2:   # stride-2 pad-1 conv == stride-1 pad-1 conv sampled at even pixels
-                y = y[:, ::2, ::2, :].contiguous()
+            y = _FusedLoRAFn.apply(xn, a_w, b_w, self)      # stride 2: native (TMA element strides), y is [B,H/2,W/2,C]
             return y.permute(0, 3, 1, 2)
         lead = x.shape[:-1]
         x2 = x.reshape(-1, self._cin)
@@ -421,4 +451,40 @@ class LoRANetwork(nn.Module):
                 group = _QKVGroup(unit, flat[start:mid].view(3 * r, 1, K), flat[mid:off].view(3 * N, r))
                 unit[0]._org._qkv_group = group
         self.flat_param, self.flat_grad = flat, gflat
+        # lora_up^T of every 1x1 / Linear adapter (the "lora_down" operand of its fused backward launch) lives in ONE
+        # buffer that ONE batched-transpose launch rebuilds from the flat parameters (pack_transposes)
+        import numpy as np
+        ones = [m for m in self.unet_loras if m._ksize == 1]
+        self._bt_state = types.SimpleNamespace(valid=False)
+        self._bt_buf = torch.empty(sum(m.lora_dim * m._cout for m in ones), device=dev, dtype=dt)
+        rec = np.zeros(len(ones), dtype=[("src", "<u8"), ("dst", "<u8"), ("rows", "<i4"), ("cols", "<i4")])
+        off = 0
+        for i, m in enumerate(ones):
+            n = m.lora_dim * m._cout
+            view = self._bt_buf[off:off + n].view(m.lora_dim, m._cout)
+            m._bt = (self._bt_state, view)
+            rec[i] = (m.lora_up.weight.data_ptr(), view.data_ptr(), m._cout, m.lora_dim)
+            off += n
+        self._bt_entries = len(ones)
+        self._bt_max = max([m.lora_dim * m._cout for m in ones] + [1])
+        self._bt_table = torch.from_numpy(rec.view(np.uint8).copy()).to(dev) if ones else None
         return flat, gflat
+
+    def pack_transposes(self):
+        """Rebuild every 1x1 adapter's lora_up^T from the flat parameter buffer: one launch."""
+        if self._bt_table is not None:
+            ops.transpose_batch(self._bt_table, self._bt_entries, self._bt_max, self._bt_buf.dtype)
+
+    @contextlib.contextmanager
+    def packed_transposes(self):
+        """Scope of ONE forward/backward over fixed parameters (a training-step body): the transposes are packed once
+        on entry and the per-layer backward launches use them instead of packing their own."""
+        if self.flat_param is None or self._bt_table is None:
+            yield
+            return
+        self.pack_transposes()
+        self._bt_state.valid = True
+        try:
+            yield
+        finally:
+            self._bt_state.valid = False

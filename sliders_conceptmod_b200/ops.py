@@ -14,8 +14,8 @@ from ._lib import LayerGeom, check, dtype_code, lib, ptr, require_cuda, stream_p
 
 
 def make_geom(dtype: torch.dtype, batch: int, height: int, width: int, cin: int, cout: int,
-              ksize: int = 1, rank: int = 0) -> LayerGeom:
-    return LayerGeom(dtype_code(dtype), batch, height, width, cin, cout, ksize, ksize, (ksize - 1) // 2, rank)
+              ksize: int = 1, rank: int = 0, stride: int = 1) -> LayerGeom:
+    return LayerGeom(dtype_code(dtype), batch, height, width, cin, cout, ksize, ksize, (ksize - 1) // 2, rank, stride)
 
 
 def _act_dims(x: torch.Tensor) -> tuple[int, int, int]:
@@ -80,26 +80,30 @@ def _gemm_workspace(device: torch.device) -> torch.Tensor:
 
 def lora_forward(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None, a: torch.Tensor | None,
                  b: torch.Tensor | None, s: float, ksize: int = 1, want_h: bool = False,
-                 residual: torch.Tensor | None = None):
+                 residual: torch.Tensor | None = None, stride: int = 1):
     """y = conv(x, w) + bias + s * (conv(x, a) @ b^T).   (lora.py:134-138)
 
     x [B,H,W,Cin] | [M,Cin];  w [Cout, k*k, Cin];  a [r, k*k, Cin];  b [Cout, r].
-    Returns (y, h) with h = conv(x, a) in fp32 ([pixels, r]) when want_h else None.
+    Returns (y, h) with h = conv(x, a) in fp32 ([output pixels, r]) when want_h else None.
     `residual` (contiguous, shaped like y): the result is added INTO it by the store and it is returned as y.
+    `stride` 2 (3x3 only): y is [B, (H-1)//2+1, (W-1)//2+1, Cout].
     """
     require_cuda(x, w, bias, a, b, residual)
     assert x.is_contiguous() and w.is_contiguous()
     B, H, W = _act_dims(x)
     cin, cout = x.shape[-1], w.shape[0]
     rank = 0 if a is None else a.shape[0]
-    g = make_geom(x.dtype, B, H, W, cin, cout, ksize, rank)
+    g = make_geom(x.dtype, B, H, W, cin, cout, ksize, rank, stride)
+    Ho, Wo = ((H - 1) // 2 + 1, (W - 1) // 2 + 1) if stride == 2 else (H, W)
     if residual is not None:
-        if not residual.is_contiguous() or residual.dtype != x.dtype or residual.numel() != B * H * W * cout:
+        if not residual.is_contiguous() or residual.dtype != x.dtype or residual.numel() != B * Ho * Wo * cout:
             raise ValueError("lora_forward: residual must be contiguous, of the activation dtype and shaped like y")
         y = residual
+    elif stride == 2:
+        y = torch.empty(B, Ho, Wo, cout, device=x.device, dtype=x.dtype)
     else:
         y = torch.empty(*x.shape[:-1], cout, device=x.device, dtype=x.dtype)
-    h = torch.empty(B * H * W, rank, device=x.device, dtype=torch.float32) if (want_h and rank > 0) else None
+    h = torch.empty(B * Ho * Wo, rank, device=x.device, dtype=torch.float32) if (want_h and rank > 0) else None
     ws = _gemm_workspace(x.device)
     if residual is not None:
         check(lib().slider_lora_forward_ex(C.byref(g), ptr(y), ptr(x), ptr(w), ptr(bias), ptr(a), ptr(b), ptr(h),
@@ -355,24 +359,58 @@ _grad_ws: dict[int, torch.Tensor] = {}
 
 
 def _grad_workspace(device: torch.device, need: int) -> torch.Tensor:
-    return _grow(_grad_ws, _ws_key(device), need, 1 << 20, False, device)
+    # zero-filled at allocation: the first 4 KB are the reduction tickets, which the kernels leave zero
+    return _grow(_grad_ws, _ws_key(device), need, 1 << 20, True, device)
 
 
-def lora_grad(gy: torch.Tensor, x: torch.Tensor, h: torch.Tensor, b: torch.Tensor, s: float, ksize: int,
-              dA: torch.Tensor, dB: torch.Tensor, accumulate: bool = False) -> torch.Tensor:
-    """Low-rank backward (autograd of lora.py:134-138): fills dA [r,k*k,Cin], dB [Cout,r] (fp32) and
-    returns dh [pixels,16] = s * gy @ B (element dtype, zero padded)."""
+def lora_grad(gy: torch.Tensor, x: torch.Tensor, h: torch.Tensor | None, b: torch.Tensor, s: float, ksize: int,
+              dA: torch.Tensor | None, dB: torch.Tensor | None, accumulate: bool = False, stride: int = 1) -> torch.Tensor:
+    """Low-rank backward (autograd of lora.py:134-138): fills dA [r,k*k,Cin], dB [Cout,r] (fp32; both None: skipped)
+    and returns dh [output pixels,16] = s * gy @ B (element dtype, zero padded).  x [B,H,W,Cin] is the layer input,
+    gy the gradient of its output ([B,H/stride,W/stride,Cout])."""
     require_cuda(gy, x, h, b, dA, dB)
-    assert gy.is_contiguous() and x.is_contiguous() and h.is_contiguous() and b.is_contiguous()
-    assert dA.dtype == torch.float32 and dB.dtype == torch.float32 and dA.is_contiguous() and dB.is_contiguous()
+    assert gy.is_contiguous() and x.is_contiguous() and b.is_contiguous()
+    if dA is not None:
+        assert h is not None and h.is_contiguous()
+        assert dA.dtype == torch.float32 and dB.dtype == torch.float32 and dA.is_contiguous() and dB.is_contiguous()
     B, H, W = _act_dims(x)
     rank = b.shape[1]
-    g = make_geom(x.dtype, B, H, W, x.shape[-1], gy.shape[-1], ksize, rank)
-    dh = torch.empty(B * H * W, 16, device=x.device, dtype=x.dtype)
+    g = make_geom(x.dtype, B, H, W, x.shape[-1], gy.shape[-1], ksize, rank, stride)
+    dh = torch.empty(gy.numel() // gy.shape[-1], 16, device=x.device, dtype=x.dtype)
     ws = _grad_workspace(x.device, lib().slider_lora_grad_workspace_bytes(C.byref(g)))
     check(lib().slider_lora_grad(C.byref(g), ptr(dA), ptr(dB), ptr(dh), ptr(gy), ptr(x), ptr(h), ptr(b), float(s),
                                  int(bool(accumulate)), ptr(ws), ws.numel(), stream_ptr()))
     return dh
+
+
+def lora_backward_1x1(gy: torch.Tensor, x: torch.Tensor | None, h: torch.Tensor | None, wt: torch.Tensor,
+                      a: torch.Tensor, b: torch.Tensor, s: float, dA: torch.Tensor | None, dB: torch.Tensor | None,
+                      accumulate: bool = False, bt: torch.Tensor | None = None) -> torch.Tensor:
+    """Whole backward of a 1x1 / Linear adapter layer: returns dx = gy @ W + s*(gy @ B) @ A and fills dA / dB (fp32;
+    both None: frozen adapter, only dx).  One fused tcgen05 launch + one reduction launch.
+    gy [.., Cout]; x [.., Cin]; h [M, r] fp32 from the forward; wt [Cin, 1, Cout]; a [r, 1, Cin]; b [Cout, r];
+    bt [r, Cout] = b^T when the caller has it (LoRANetwork.pack_transposes), else it is packed here."""
+    require_cuda(gy, x, h, wt, a, b, dA, dB, bt)
+    assert gy.is_contiguous() and wt.is_contiguous() and a.is_contiguous() and b.is_contiguous()
+    B, H, W = _act_dims(gy)
+    rank, cin, cout = b.shape[1], wt.shape[0], gy.shape[-1]
+    g = make_geom(gy.dtype, B, H, W, cin, cout, 1, rank)
+    dx = torch.empty(*gy.shape[:-1], cin, device=gy.device, dtype=gy.dtype)
+    gbuf = torch.empty(B * H * W, rank, device=gy.device, dtype=torch.float32)
+    if dA is not None:
+        assert x is not None and h is not None and x.is_contiguous() and h.is_contiguous()
+        assert dA.dtype == torch.float32 and dB.dtype == torch.float32 and dA.is_contiguous() and dB.is_contiguous()
+    ws = _grad_workspace(gy.device, lib().slider_lora_grad_workspace_bytes(C.byref(g)))
+    check(lib().slider_lora_backward_1x1(C.byref(g), ptr(dx), ptr(dA), ptr(dB), ptr(gbuf), ptr(gy), ptr(x), ptr(h),
+                                         ptr(wt), ptr(bt), ptr(a), ptr(b), float(s), int(bool(accumulate)), ptr(ws),
+                                         ws.numel(), stream_ptr()))
+    return dx
+
+
+def transpose_batch(table: torch.Tensor, entries: int, max_elems: int, dtype: torch.dtype) -> None:
+    """One launch of `entries` small transposes described by a device table of slider_transpose_entry records."""
+    require_cuda(table)
+    check(lib().slider_transpose_batch(ptr(table), int(entries), int(max_elems), dtype_code(dtype), stream_ptr()))
 
 
 def adamw_flat(p: torch.Tensor, grad: torch.Tensor, m: torch.Tensor, v: torch.Tensor, lr: float, beta1: float,

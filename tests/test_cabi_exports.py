@@ -28,7 +28,7 @@ def test_library_builds_and_exports_header_symbols():
 
 def test_version_and_error_string_without_gpu():
     h = _lib.lib()
-    assert h.slider_version() == 2
+    assert h.slider_version() == 3
     assert isinstance(h.slider_last_error(), bytes)
     g = _lib.LayerGeom(1, 1, 1, 8, 8, 8, 5, 5, 2, 4)       # 5x5 kernel: rejected before any CUDA call
     rc = h.slider_lora_forward(ctypes.byref(g), 16, 16, 16, None, None, None, None, 1.0, None, 0, None)
@@ -36,7 +36,8 @@ def test_version_and_error_string_without_gpu():
 
 
 def test_sass_is_blackwell_native():
-    out = subprocess.run(["cuobjdump", "-sass", str(build.PKG_DIR / "build" / "lora_gemm.o")], capture_output=True,
-                         text=True).stdout
-    for mnemonic in ("UTCHMMA", "UTMALDG", "LDTM"):
-        assert mnemonic in out, f"{mnemonic} missing from lora_gemm SASS"
+    for obj in ("lora_gemm_bn160.o", "lora_gemm_bn80.o"):       # the two tile widths of lora_gemm_kernel
+        out = subprocess.run(["cuobjdump", "-sass", str(build.PKG_DIR / "build" / obj)], capture_output=True,
+                             text=True).stdout
+        for mnemonic in ("UTCHMMA", "UTMALDG", "UTMASTG", "LDTM"):
+            assert mnemonic in out, f"{mnemonic} missing from the SASS of {obj}"

@@ -162,3 +162,74 @@ def test_small_multi_matches_per_layer(dtype, M):
             full = full + s * (x.float() @ a[:, 0].float().T) @ b.float().T
         tol = 2e-2 if dtype == torch.bfloat16 else 1e-4
         assert (y.float() - full).abs().max().item() <= tol * full.abs().max().item()
+
+
+@pytest.mark.parametrize("shape", [(2, 64, 64, 320, 320), (2, 32, 32, 640, 640), (2, 16, 16, 1280, 1280),
+                                   (1, 17, 23, 64, 96), (3, 8, 8, 128, 160), (1, 128, 128, 320, 320)])
+@pytest.mark.parametrize("dtype,tol", [(torch.bfloat16, 2e-2), (torch.float32, 5e-5)])
+def test_stride2_conv_native(shape, dtype, tol):
+    """3x3 stride-2 pad-1 convolution with its adapter (the Downsample2D layers; lora.py:100-114 gives lora_down the base
+    conv's stride) computed natively -- the activation TMA map samples every second pixel -- incl. odd extents,
+    split-K shapes and h_out at OUTPUT resolution."""
+    from sliders_conceptmod_b200 import ops
+    B, H, W, C, N = shape
+    g = torch.Generator().manual_seed(sum(shape))
+    x = torch.randn(B, H, W, C, generator=g).cuda().to(dtype)
+    w = (torch.randn(N, 9, C, generator=g) / (9 * C) ** 0.5).cuda().to(dtype)
+    a = (torch.randn(4, 9, C, generator=g) / (9 * C) ** 0.5).cuda().to(dtype)
+    b = (torch.randn(N, 4, generator=g) * 0.3).cuda().to(dtype)
+    bias = torch.randn(N, generator=g).cuda().to(dtype)
+    s = 0.6
+    y, h = ops.lora_forward(x, w, bias, a, b, s, ksize=3, want_h=True, stride=2)
+    Ho, Wo = (H - 1) // 2 + 1, (W - 1) // 2 + 1
+    assert y.shape == (B, Ho, Wo, N) and h.shape == (B * Ho * Wo, 4)
+    xn = x.float().permute(0, 3, 1, 2)
+    wc = w.float().reshape(N, 3, 3, C).permute(0, 3, 1, 2)
+    ac = a.float().reshape(4, 3, 3, C).permute(0, 3, 1, 2)
+    hr = F.conv2d(xn, ac, None, stride=2, padding=1)
+    yr = F.conv2d(xn, wc, bias.float(), stride=2, padding=1) + s * F.conv2d(hr, b.float()[:, :, None, None])
+    yr = yr.permute(0, 2, 3, 1)
+    hr = hr.permute(0, 2, 3, 1).reshape(-1, 4)
+    err = (y.float() - yr).abs().max().item()
+    assert err <= tol * yr.abs().max().item(), f"y max-abs {err:.3e} vs {yr.abs().max().item():.3e}"
+    assert (h - hr).abs().max().item() <= (1e-3 if dtype == torch.bfloat16 else 5e-5) * hr.abs().max().item() + 1e-6
+    # and it equals the stride-1 result sampled at even pixels (what earlier revisions computed)
+    y1, _ = ops.lora_forward(x, w, bias, a, b, s, ksize=3)
+    assert (y.float() - y1[:, ::2, ::2].float()).abs().max().item() <= tol * yr.abs().max().item()
+
+
+@pytest.mark.parametrize("case", [(1, 1, 2048, 640, 640, 1, 4), (2, 16, 16, 1280, 1280, 3, 4), (1, 1, 512, 1280, 1280, 1, 4),
+                                  (2, 32, 32, 640, 640, 3, 8), (1, 1, 300, 64, 72, 1, 4), (1, 1, 128, 320, 1280, 1, 16)])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+def test_narrow_tile_equals_wide_tile(case, dtype):
+    """Tile-starved launches run 128 x 80 tiles instead of 128 x 160 (slider_debug_bn80_tiles is the switch): every
+    output element sees the same MMAs in the same K order, so without split-K the two tilings agree bit for bit."""
+    import ctypes
+    from sliders_conceptmod_b200 import _lib, ops
+    fn = _lib.lib().slider_debug_bn80_tiles
+    fn.argtypes, fn.restype = [ctypes.c_int], ctypes.c_int
+    depth = _lib.lib().slider_debug_splitk_depth
+    depth.argtypes, depth.restype = [ctypes.c_int], ctypes.c_int
+    B, H, W, C, N, k, r = case
+    g = torch.Generator().manual_seed(sum(case))
+    lin = k == 1 and B == 1 and H == 1
+    x = torch.randn(*((W, C) if lin else (B, H, W, C)), generator=g).cuda().to(dtype)
+    w = (torch.randn(N, k * k, C, generator=g) / (C * k * k) ** 0.5).cuda().to(dtype)
+    a = (torch.randn(r, k * k, C, generator=g) / (C * k * k) ** 0.5).cuda().to(dtype)
+    b = (torch.randn(N, r, generator=g) * 0.3).cuda().to(dtype)
+    bias = torch.randn(N, generator=g).cuda().to(dtype)
+    try:
+        depth(1 << 20)                     # no split-K: a split changes the summation order
+        fn(0)
+        y160, h160 = ops.lora_forward(x, w, bias, a, b, 0.7, ksize=k, want_h=True)
+        fn(1 << 20)
+        y80, h80 = ops.lora_forward(x, w, bias, a, b, 0.7, ksize=k, want_h=True)
+        torch.cuda.synchronize()
+        assert torch.equal(y160, y80) and torch.equal(h160, h80)
+        depth(0)                           # with the default split-K plan of each tiling: equal within tolerance
+        y80s, _ = ops.lora_forward(x, w, bias, a, b, 0.7, ksize=k)
+        tol = 2e-2 if dtype == torch.bfloat16 else 5e-5
+        assert (y80s.float() - y160.float()).abs().max().item() <= tol * y160.float().abs().max().item()
+    finally:
+        fn(-1)
+        depth(0)

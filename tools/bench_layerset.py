@@ -28,10 +28,10 @@ def main():
     calls = []
     real, real_grouped = ops.lora_forward, ops.lora_forward_grouped
 
-    def spy(x, w, bias, a, b, s, ksize=1, want_h=False, residual=None):
+    def spy(x, w, bias, a, b, s, ksize=1, want_h=False, residual=None, stride=1):
         calls.append(("single", tuple(x.shape), tuple(w.shape), bias is not None, None if a is None else a.shape[0], s,
-                      ksize, residual is not None))
-        return real(x, w, bias, a, b, s, ksize=ksize, want_h=want_h, residual=residual)
+                      ksize * 10 + stride, residual is not None))
+        return real(x, w, bias, a, b, s, ksize=ksize, want_h=want_h, residual=residual, stride=stride)
 
     def spy_grouped(x, w_cat, a_cat, b_cat, groups, s):
         calls.append(("grouped", tuple(x.shape), tuple(w_cat.shape), False, a_cat.shape[0], s, groups, False))
@@ -77,9 +77,12 @@ def main():
                      "rank": plan.rank, "count": 1, "us": round(us, 2), "total_us": round(us, 1),
                      "gflop": round(fl / 1e9, 2), "tflops": round(fl / us / 1e6, 1)})
     for (kind, xs, ws, has_b, r, s, k, has_res), count in sigs.items():
+        stride = 1
+        if kind == "single":
+            k, stride = k // 10, k % 10
         M = 1
-        for d in xs[:-1]:
-            M *= d
+        for i, d in enumerate(xs[:-1]):
+            M *= ((d - 1) // 2 + 1) if (stride == 2 and i in (1, 2)) else d
         N, T, C = ws
         # several operand sets so that back-to-back launches do not re-hit the same weights in L2
         nset = max(1, min(8, int(256e6 / max(1, N * T * C * 2))))
@@ -97,7 +100,7 @@ def main():
                 a = torch.randn(r, T, C, device=dev, dtype=dt) * 0.02 if r else None
                 b = torch.randn(N, r, device=dev, dtype=dt) * 0.02 if r else None
                 bias = torch.zeros(N, device=dev, dtype=dt) if has_b else None
-                res = torch.zeros(*xs[:-1], N, device=dev, dtype=dt) if has_res else None
+                res = torch.zeros(*xs[:-1], N, device=dev, dtype=dt) if has_res else None     # stride-2 layers never fuse a residual
                 sets.append((x, w, bias, a, b, res))
         if kind == "grouped":
             flops = 2.0 * M * N * C + 2.0 * M * r * C + 2.0 * M * (r // k) * N
@@ -110,7 +113,7 @@ def main():
                 if kind == "grouped":
                     real_grouped(o[0], o[1], o[2], o[3], k, s)
                 else:
-                    real(o[0], o[1], o[2], o[3], o[4], s, ksize=k, residual=o[5])
+                    real(o[0], o[1], o[2], o[3], o[4], s, ksize=k, residual=o[5], stride=stride)
         run(); torch.cuda.synchronize()
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g):
@@ -123,7 +126,7 @@ def main():
         e1.record()
         torch.cuda.synchronize()
         us = e0.elapsed_time(e1) * 1e3 / (3 * args.reps)
-        rows.append({"kind": kind, "x": list(xs), "w": list(ws), "k": k, "res": has_res, "rank": r, "count": count,
+        rows.append({"kind": kind, "x": list(xs), "w": list(ws), "k": k, "stride": stride, "res": has_res, "rank": r, "count": count,
                      "us": round(us, 2), "total_us": round(us * count, 1), "gflop": round(flops / 1e9, 2),
                      "tflops": round(flops / us / 1e6, 1)})
     tot = sum(r["total_us"] for r in rows)
