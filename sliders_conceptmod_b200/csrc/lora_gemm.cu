@@ -395,8 +395,13 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
   // tile width: 160 columns unless that tiling leaves at least half of the SMs without a tile
   int bn = 160;
   {
+    // measured on the SD-1.4 layer set (profiles/r02_layerset_bn80.txt): the narrow tile pays where split-K cannot
+    // supply the parallelism (shallow K) or there is only a handful of tiles; the deep 3x3 convolutions at 16 x 16 /
+    // 32 x 32 are L2-bandwidth bound and lose with it (27 % more operand bytes per FLOP)
     const int thr = g_bn80_tiles < 0 ? sm_count() : g_bn80_tiles;
-    if (m_tiles * ((nn + 159) / 160) * 2 <= thr) bn = 80;
+    const int tiles160 = m_tiles * ((nn + 159) / 160);
+    const int kit = taps * ((kc + bk - 1) / bk + (ext ? 1 : 0));
+    if (g_bn80_tiles < 0 ? (tiles160 <= 12 || (tiles160 * 2 <= thr && kit <= 40)) : tiles160 * 2 <= thr) bn = 80;
   }
   p.n_tiles = (nn + bn - 1) / bn; p.N = nn;
   p.taps = taps; p.kw = g->kw; p.pad = g->pad; p.cblocks = (kc + bk - 1) / bk;
@@ -417,9 +422,10 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
     // the SD-1.4 layer set (profiles/r01_splitk_depth_sweep.txt) it only pays for deep K -- 64+ K blocks at >= 18 per
     // split, or 40+ at >= 6 per split for the weight-streaming shapes with a handful of tiles.
     int depth = g_splitk_depth, min_k = 0;
+    const int tiles_eq = bn == 160 ? p.total_tiles : (p.total_tiles + 1) / 2;     // in 160-column tiles (what the sweep measured)
     if (depth == 0) {
-      depth = p.total_tiles <= 12 ? 6 : 18;
-      min_k = p.total_tiles <= 12 ? 40 : 64;
+      depth = tiles_eq <= 12 ? 6 : 18;
+      min_k = tiles_eq <= 12 ? 40 : 64;
     }
     const int by_depth = p.kiters >= min_k ? p.kiters / depth : 1;
     if (ks > by_depth) ks = by_depth;
@@ -437,6 +443,7 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
   p.fd_per_tap = FastDiv::make((uint32_t)p.per_tap);
   p.fd_kw = FastDiv::make((uint32_t)p.kw);
   p.trace = g_gemm_trace;
+  { static const int skip = [] { const char* e = getenv("SLIDER_DBG_SKIP"); return e ? atoi(e) : 0; }(); p.dbg_skip = skip; }
   // only when several pixel tiles share each weight tile: with ONE pixel tile every CTA streams distinct weights and
   // the pipeline's own requests already fill HBM
   p.w_prefetch = (m_tiles > 1) ? g_w_prefetch : 0;

@@ -127,6 +127,7 @@ struct GemmParams {
   FastDiv fd_n_tiles, fd_mt_w, fd_mt_h, fd_ksplit, fd_per_tap, fd_kw;
   int w_prefetch;         // K blocks the weight stream is requested into L2 ahead of the shared-memory pipeline
   long long* trace;       // debug: 16 clock64() stamps per CTA (NULL = off)
+  int dbg_skip;           // debug (timing experiments only, results are garbage): bit 0 = no A loads, bit 1 = no W loads
   void* y;
   const void* bias;
   const void* Bup;
@@ -244,12 +245,22 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const uint32_t sa = smem_base + pstage * kStageStride;
     const uint32_t fb = ptx::smem_u32(full_bar + pstage);
     if (pj < p.cblocks) {
+      if (p.dbg_skip) {
+        const uint32_t tx = ((p.dbg_skip & 1) ? 0u : (uint32_t)(p.rows * ROW_BYTES)) + ((p.dbg_skip & 2) ? 0u : (uint32_t)B_BYTES) +
+                            (p.lora ? (uint32_t)L_BYTES : 0u);
+        ptx::mbar_arrive_expect_tx(fb, tx);
+        if (!(p.dbg_skip & 1)) ptx::tma_load_4d(sa, &tmA, fb, pj * BK, ptc.w0 * p.stride + dx, ptc.h0 * p.stride + dy, ptc.b0);
+        if (!(p.dbg_skip & 2)) ptx::tma_load_3d(sa + A_BYTES, &tmW, fb, pj * BK, ptap, ptc.n0);
+        if (p.lora) ptx::tma_load_3d(sa + A_BYTES + B_BYTES, &tmL, fb, pj * BK, ptap, 0);
+        if (tx == 0) ptx::mbar_arrive(fb);
+      } else {
       ptx::mbar_arrive_expect_tx(fb, main_tx);
       // stride 2: the activation map samples every second pixel (element strides {1, 2, 2, 1}), so the box that
       // starts at input pixel (2*w0 + dx, 2*h0 + dy) lands the TW x TH output pixels' operands densely
       ptx::tma_load_4d(sa, &tmA, fb, pj * BK, ptc.w0 * p.stride + dx, ptc.h0 * p.stride + dy, ptc.b0);
       ptx::tma_load_3d(sa + A_BYTES, &tmW, fb, pj * BK, ptap, ptc.n0);
       if (p.lora) ptx::tma_load_3d(sa + A_BYTES + B_BYTES, &tmL, fb, pj * BK, ptap, 0);
+      }
     } else {
       ptx::mbar_arrive_expect_tx(fb, ext_tx);
       ptx::tma_load_4d(sa, &tmXe, fb, 0, ptc.w0 + dx, ptc.h0 + dy, ptc.b0);
