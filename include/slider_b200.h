@@ -157,6 +157,13 @@ int slider_lora_grad(const slider_layer_geom* g, float* dA, float* dB,
                      const float* h, const void* B, float s, int accumulate,
                      void* ws, size_t ws_bytes, void* stream);
 
+/* slider_lora_grad with a per-input-channel factor on dA: dA[j,t,c] *= dA_chan_scale[c] (fp32 [cin], NULL = none).
+ * DoRA (conceptmod/textsliders/dora.py:122-163): the low-rank term of W' is scaled per input channel by s*c_c. */
+int slider_lora_grad_ex(const slider_layer_geom* g, float* dA, float* dB,
+                        void* dh_out, const void* gy, const void* x,
+                        const float* h, const void* B, float s, int accumulate,
+                        const float* dA_chan_scale, void* ws, size_t ws_bytes, void* stream);
+
 /*
  * Whole backward of a 1x1 / Linear adapter layer in two launches (same autograd as above):
  *   launch 1: the forward tcgen05 kernel on the transposed problem -- activations gy, weights Wt, "lora_down" = B^T,
@@ -197,6 +204,33 @@ int slider_lora_pack_at(const slider_layer_geom* g, void* At, const void* A,
 int slider_lora_input_grad(const slider_layer_geom* g, void* dx, const void* gy,
                            const void* Wt, const void* dh, const void* At,
                            void* ws, size_t ws_bytes, void* stream);
+
+/*
+ * DoRA on the fused kernel.  Replaces DoRAModule.apply_weight_decompose + forward
+ * (conceptmod/textsliders/dora.py:122-163; selected by train_lora_xl.py:87-90 --peft_type dora):
+ *     W' = (W + B.A) * (m / ||W + B.A||_per input channel, detached),   y = org(x) + s * ops(x, W' - W)
+ * which, with c_i = m_i / n_i and v = 1 - s + s*c, equals  x . (W*v)^T + bias + (x . (A * s*c)^T) . B^T :
+ * slider_lora_forward on W_eff = W*v and A_s = A*(s c) with adapter scale 1.
+ *   slider_dora_prepare: two passes over the frozen weight (column norms; scaling) ->
+ *       W_eff [cout, kh*kw, cin], A_s [rank, kh*kw, cin] (element dtype), c, v, ninv = 1/n (fp32 [cin]).
+ *       W, A tap-major as in slider_lora_forward; dora_scale m [cin] (element dtype).
+ *   slider_dora_finish: tail of the backward.  u = gy.W + (gy.B).A is the input-gradient GEMM of the LoRA path with
+ *       s = 1 (slider_lora_backward_1x1 / slider_lora_input_grad on the UNSCALED W and A); then
+ *           dx[p,i] = v_i * T1 + s c_i * T2        (T1 = gy.W, T2 = u - T1)
+ *           dm[i]   = s/n_i * sum_p x[p,i] * u[p,i]          (gradient of dora_scale; fp32 [cin])
+ *       t1 [M, cin] = gy.W from a second slider_lora_input_grad call (3x3), or NULL for a 1x1 layer, where
+ *       T2 = g_buf . A is formed here from g_buf = gy.B [M, rank] fp32 (slider_lora_backward_1x1's output).
+ *       dx or dm may be NULL.  geometry: batch/height/width = extent of x (the layer INPUT).
+ *   The low-rank gradients come from slider_lora_grad_ex(s = 1, h = the forward's h_out, dA_chan_scale = s*c).
+ *   ws: slider_lora_grad_workspace_bytes(g) bytes, first 4096 zero-filled once (as for slider_lora_grad).
+ * The reference's dense weight gradient (out x in per wrapped layer) is never formed.
+ */
+int slider_dora_prepare(const slider_layer_geom* g, void* W_eff, void* A_s, float* c, float* v, float* ninv,
+                        const void* W, const void* A, const void* B, const void* dora_scale, float s, void* ws,
+                        size_t ws_bytes, void* stream);
+int slider_dora_finish(const slider_layer_geom* g, void* dx, float* dm, const void* u, const void* t1, const void* x,
+                       const float* g_buf, const void* A, const float* c, const float* v, const float* ninv, float s,
+                       int accumulate, void* ws, size_t ws_bytes, void* stream);
 
 /* Profiling aid: when buf != NULL, every lora_gemm_kernel CTA writes 8 clock64()
  * stamps (entry, setup done, first TMA issued, first operands landed, last MMA

@@ -38,6 +38,9 @@ _SIGNATURES = {
     "slider_lora_forward_small_multi": (C.c_int, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "slider_lora_grad_workspace_bytes": (_sz, [_G]),
     "slider_lora_grad": (C.c_int, [_G, _fp, _fp, _vp, _vp, _vp, _fp, _vp, _f, _i, _vp, _sz, _vp]),
+    "slider_lora_grad_ex": (C.c_int, [_G, _fp, _fp, _vp, _vp, _vp, _fp, _vp, _f, _i, _fp, _vp, _sz, _vp]),
+    "slider_dora_prepare": (C.c_int, [_G, _vp, _vp, _fp, _fp, _fp, _vp, _vp, _vp, _vp, _f, _vp, _sz, _vp]),
+    "slider_dora_finish": (C.c_int, [_G, _vp, _fp, _vp, _vp, _vp, _fp, _vp, _fp, _fp, _fp, _f, _i, _vp, _sz, _vp]),
     "slider_lora_backward_1x1": (C.c_int, [_G, _vp, _fp, _fp, _fp, _vp, _vp, _fp, _vp, _vp, _vp, _vp, _f, _i, _vp, _sz, _vp]),
     "slider_transpose_batch": (C.c_int, [_vp, _i, _i, _i, _vp]),
     "slider_lora_pack_at": (C.c_int, [_G, _vp, _vp, _vp]),

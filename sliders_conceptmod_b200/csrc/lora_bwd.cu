@@ -60,6 +60,7 @@ struct ColProblem {
   int vstride;
   int64_t oc, oj, ot;    // output strides for (channel, rank index, tap)
   float scale;
+  const float* cscale;   // optional per-channel factor on top of `scale` (DoRA: dA_i *= s * c_i), or NULL
 };
 struct ColReduceParams {
   int B, H, W;           // X pixels
@@ -241,7 +242,7 @@ colreduce_kernel(const ColReduceParams p, int j0) {
       float sum = 0.f;
       for (int ch = 0; ch < nchunks; ++ch) sum += __ldcg(all + (size_t)ch * (4 * NACC) + i);
       float* o = pr.out + (int64_t)cc * pr.oc + (int64_t)(j0 + j) * pr.oj + (int64_t)t * pr.ot;
-      *o = (p.accumulate ? *o : 0.f) + sum * pr.scale;
+      *o = (p.accumulate ? *o : 0.f) + sum * pr.scale * (pr.cscale != nullptr ? pr.cscale[cc] : 1.f);
     }
   }
   if (threadIdx.x == 0) p.tickets[blockIdx.y] = 0u;
@@ -348,7 +349,7 @@ int run_gemm_fused_bwd(const slider_layer_geom* g, void* dx, float* g_out, const
 static ColProblem make_problem(const void* X, const void* V, float* out, int C, int vstride, int64_t oc, int64_t oj,
                                int64_t ot, float scale) {
   ColProblem q;
-  q.X = X; q.V = V; q.out = out; q.C = C; q.cblocks = 0; q.vstride = vstride; q.oc = oc; q.oj = oj; q.ot = ot; q.scale = scale;
+  q.X = X; q.V = V; q.out = out; q.C = C; q.cblocks = 0; q.vstride = vstride; q.oc = oc; q.oj = oj; q.ot = ot; q.scale = scale; q.cscale = nullptr;
   return q;
 }
 
@@ -372,8 +373,8 @@ static int carve_ws(GradWs* w, void* ws, size_t ws_bytes, int cout, const char* 
 
 template <typename T>
 static int lora_grad_impl(const slider_layer_geom* g, float* dA, float* dB, T* dh, const T* gy, const T* x,
-                          const float* h, const T* Bup, float s, int accumulate, void* ws, size_t ws_bytes,
-                          cudaStream_t st) {
+                          const float* h, const T* Bup, float s, int accumulate, const float* dA_chan_scale, void* ws,
+                          size_t ws_bytes, cudaStream_t st) {
   const int taps = g->kh * g->kw;
   const int stride = g->stride == 2 ? 2 : 1;
   const int Ho = (g->height + 2 * g->pad - g->kh) / stride + 1, Wo = (g->width + 2 * g->pad - g->kw) / stride + 1;
@@ -398,6 +399,7 @@ static int lora_grad_impl(const slider_layer_geom* g, float* dA, float* dB, T* d
   pa.B = g->batch; pa.H = g->height; pa.W = g->width; pa.VH = Ho; pa.VW = Wo; pa.stride = stride; pa.kw = g->kw; pa.pad = g->pad;
   pa.rank = g->rank; pa.accumulate = accumulate; pa.nprob = 1;
   pa.prob[0] = make_problem(x, dh, dA, g->cin, 16, 1, (int64_t)taps * g->cin, g->cin, 1.f);
+  pa.prob[0].cscale = dA_chan_scale;
   return launch_colreduce<T, T>(pa, taps, w.partial, w.tickets, st);
 }
 
@@ -450,6 +452,12 @@ size_t slider_lora_grad_workspace_bytes(const slider_layer_geom* g) {
 int slider_lora_grad(const slider_layer_geom* g, float* dA, float* dB, void* dh_out, const void* gy, const void* x,
                      const float* h, const void* B, float s, int accumulate, void* ws, size_t ws_bytes,
                      void* stream) {
+  return slider_lora_grad_ex(g, dA, dB, dh_out, gy, x, h, B, s, accumulate, nullptr, ws, ws_bytes, stream);
+}
+
+int slider_lora_grad_ex(const slider_layer_geom* g, float* dA, float* dB, void* dh_out, const void* gy, const void* x,
+                        const float* h, const void* B, float s, int accumulate, const float* dA_chan_scale, void* ws,
+                        size_t ws_bytes, void* stream) {
   int rc = check_geom(g, "lora_grad");
   if (rc) return rc;
   SLIDER_CHECK_ARG((dA == nullptr) == (dB == nullptr), "lora_grad: dA and dB must both be set or both NULL");
@@ -458,9 +466,10 @@ int slider_lora_grad(const slider_layer_geom* g, float* dA, float* dB, void* dh_
   cudaStream_t st = (cudaStream_t)stream;
   if (g->dtype == SLIDER_BF16)
     return lora_grad_impl<__nv_bfloat16>(g, dA, dB, (__nv_bfloat16*)dh_out, (const __nv_bfloat16*)gy,
-                                         (const __nv_bfloat16*)x, h, (const __nv_bfloat16*)B, s, accumulate, ws, ws_bytes, st);
+                                         (const __nv_bfloat16*)x, h, (const __nv_bfloat16*)B, s, accumulate,
+                                         dA_chan_scale, ws, ws_bytes, st);
   return lora_grad_impl<float>(g, dA, dB, (float*)dh_out, (const float*)gy, (const float*)x, h, (const float*)B, s,
-                               accumulate, ws, ws_bytes, st);
+                               accumulate, dA_chan_scale, ws, ws_bytes, st);
 }
 
 int slider_lora_backward_1x1(const slider_layer_geom* g, void* dx, float* dA, float* dB, float* g_buf, const void* gy,

@@ -364,7 +364,8 @@ def _grad_workspace(device: torch.device, need: int) -> torch.Tensor:
 
 
 def lora_grad(gy: torch.Tensor, x: torch.Tensor, h: torch.Tensor | None, b: torch.Tensor, s: float, ksize: int,
-              dA: torch.Tensor | None, dB: torch.Tensor | None, accumulate: bool = False, stride: int = 1) -> torch.Tensor:
+              dA: torch.Tensor | None, dB: torch.Tensor | None, accumulate: bool = False, stride: int = 1,
+              dA_chan_scale: torch.Tensor | None = None) -> torch.Tensor:
     """Low-rank backward (autograd of lora.py:134-138): fills dA [r,k*k,Cin], dB [Cout,r] (fp32; both None: skipped)
     and returns dh [output pixels,16] = s * gy @ B (element dtype, zero padded).  x [B,H,W,Cin] is the layer input,
     gy the gradient of its output ([B,H/stride,W/stride,Cout])."""
@@ -378,14 +379,16 @@ def lora_grad(gy: torch.Tensor, x: torch.Tensor, h: torch.Tensor | None, b: torc
     g = make_geom(x.dtype, B, H, W, x.shape[-1], gy.shape[-1], ksize, rank, stride)
     dh = torch.empty(gy.numel() // gy.shape[-1], 16, device=x.device, dtype=x.dtype)
     ws = _grad_workspace(x.device, lib().slider_lora_grad_workspace_bytes(C.byref(g)))
-    check(lib().slider_lora_grad(C.byref(g), ptr(dA), ptr(dB), ptr(dh), ptr(gy), ptr(x), ptr(h), ptr(b), float(s),
-                                 int(bool(accumulate)), ptr(ws), ws.numel(), stream_ptr()))
+    if dA_chan_scale is not None:
+        assert dA_chan_scale.dtype == torch.float32 and dA_chan_scale.numel() == x.shape[-1]
+    check(lib().slider_lora_grad_ex(C.byref(g), ptr(dA), ptr(dB), ptr(dh), ptr(gy), ptr(x), ptr(h), ptr(b), float(s),
+                                    int(bool(accumulate)), ptr(dA_chan_scale), ptr(ws), ws.numel(), stream_ptr()))
     return dh
 
 
 def lora_backward_1x1(gy: torch.Tensor, x: torch.Tensor | None, h: torch.Tensor | None, wt: torch.Tensor,
                       a: torch.Tensor, b: torch.Tensor, s: float, dA: torch.Tensor | None, dB: torch.Tensor | None,
-                      accumulate: bool = False, bt: torch.Tensor | None = None) -> torch.Tensor:
+                      accumulate: bool = False, bt: torch.Tensor | None = None, return_g: bool = False):
     """Whole backward of a 1x1 / Linear adapter layer: returns dx = gy @ W + s*(gy @ B) @ A and fills dA / dB (fp32;
     both None: frozen adapter, only dx).  One fused tcgen05 launch + one reduction launch.
     gy [.., Cout]; x [.., Cin]; h [M, r] fp32 from the forward; wt [Cin, 1, Cout]; a [r, 1, Cin]; b [Cout, r];
@@ -404,6 +407,41 @@ def lora_backward_1x1(gy: torch.Tensor, x: torch.Tensor | None, h: torch.Tensor 
     check(lib().slider_lora_backward_1x1(C.byref(g), ptr(dx), ptr(dA), ptr(dB), ptr(gbuf), ptr(gy), ptr(x), ptr(h),
                                          ptr(wt), ptr(bt), ptr(a), ptr(b), float(s), int(bool(accumulate)), ptr(ws),
                                          ws.numel(), stream_ptr()))
+    return (dx, gbuf) if return_g else dx
+
+
+def dora_prepare(w: torch.Tensor, a: torch.Tensor, b: torch.Tensor, m: torch.Tensor, s: float, ksize: int,
+                 w_eff: torch.Tensor | None = None, a_s: torch.Tensor | None = None):
+    """DoRA operands of one wrapped layer (dora.py:122-131): returns (W_eff = W*v, A_s = A*(s c), c, v, 1/n) with
+    c = m / ||W + B.A|| per input channel, v = 1 - s + s*c.  w [Cout,k*k,Cin], a [r,k*k,Cin], b [Cout,r], m [Cin]."""
+    require_cuda(w, a, b, m, w_eff, a_s)
+    assert w.is_contiguous() and a.is_contiguous() and b.is_contiguous() and m.is_contiguous() and m.dtype == w.dtype
+    cout, taps, cin = w.shape
+    g = make_geom(w.dtype, 1, 1, 1, cin, cout, ksize, a.shape[0])
+    w_eff = torch.empty_like(w) if w_eff is None else w_eff
+    a_s = torch.empty_like(a) if a_s is None else a_s
+    c, v, ninv = (torch.empty(cin, device=w.device, dtype=torch.float32) for _ in range(3))
+    ws = _grad_workspace(w.device, lib().slider_lora_grad_workspace_bytes(C.byref(g)))
+    check(lib().slider_dora_prepare(C.byref(g), ptr(w_eff), ptr(a_s), ptr(c), ptr(v), ptr(ninv), ptr(w), ptr(a), ptr(b),
+                                    ptr(m), float(s), ptr(ws), ws.numel(), stream_ptr()))
+    return w_eff, a_s, c, v, ninv
+
+
+def dora_finish(u: torch.Tensor, t1: torch.Tensor | None, x: torch.Tensor | None, gbuf: torch.Tensor | None,
+                a: torch.Tensor | None, c: torch.Tensor, v: torch.Tensor, ninv: torch.Tensor, s: float,
+                want_dx: bool = True, dm: torch.Tensor | None = None, accumulate: bool = False):
+    """Tail of the DoRA backward: dx = v*T1 + s*c*T2 (T1 = gy.W, T2 = u - T1) and dm_i (+)= s/n_i * sum_p x*u.
+    u, t1, x [.., Cin]; gbuf [M, r] fp32 and a [r, 1, Cin] replace t1 for 1x1 layers.  Returns dx (or None)."""
+    require_cuda(u, t1, x, gbuf, a, c, v, ninv, dm)
+    assert u.is_contiguous() and (t1 is None or t1.is_contiguous()) and (x is None or x.is_contiguous())
+    cin = u.shape[-1]
+    M = u.numel() // cin
+    rank = 0 if a is None else a.shape[0]
+    g = make_geom(u.dtype, 1, 1, M, cin, 8, 1 if t1 is None else 3, rank)
+    dx = torch.empty_like(u) if want_dx else None
+    ws = _grad_workspace(u.device, lib().slider_lora_grad_workspace_bytes(C.byref(g)))
+    check(lib().slider_dora_finish(C.byref(g), ptr(dx), ptr(dm), ptr(u), ptr(t1), ptr(x), ptr(gbuf), ptr(a), ptr(c),
+                                   ptr(v), ptr(ninv), float(s), int(bool(accumulate)), ptr(ws), ws.numel(), stream_ptr()))
     return dx
 
 

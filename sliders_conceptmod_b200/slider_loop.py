@@ -31,7 +31,7 @@ class TextSliderTrainer:
     """State of one training run; `iteration(i)` is one pass of the reference loop body."""
 
     def __init__(self, config: config_util.RootConfig, prompts: list[PromptSettings], device, xl: bool = False,
-                 rank: Optional[int] = None, seed: Optional[int] = None):
+                 rank: Optional[int] = None, seed: Optional[int] = None, peft_type: str = "lora"):
         self.config, self.xl, self.device = config, xl, torch.device(device)
         self.weight_dtype = config_util.parse_precision(config.train.precision)
         self.save_weight_dtype = config_util.parse_precision(config.train.precision)   # save.precision is unused upstream
@@ -56,9 +56,13 @@ class TextSliderTrainer:
         self.unet, self.scheduler = unet, sched
         if xl:
             # train_lora_xl.py:92-105: attention-only targets, alpha default, hard-coded optimizer
-            self.network = LoRANetwork(unet, rank=rank if rank is not None else 4, multiplier=1.0, delimiter="_",
-                                       target_replace=["Attention"], prefix="lora_unet",
-                                       train_method=config.network.training_method).to(self.device, dtype=self.weight_dtype)
+            if peft_type == "dora":                      # train_lora_xl.py:87-90
+                from .dora import DoRANetwork as peft_class
+            else:
+                peft_class = LoRANetwork
+            self.network = peft_class(unet, rank=rank if rank is not None else 4, multiplier=1.0, delimiter="_",
+                                      target_replace=["Attention"], prefix="lora_unet",
+                                      train_method=config.network.training_method).to(self.device, dtype=self.weight_dtype)
             self.optimizer = torch.optim.AdamW(self.network.parameters(), lr=1e-4, weight_decay=1e-6)
             self.lr_scheduler = torch.optim.lr_scheduler.CosineAnnealingLR(self.optimizer, T_max=50, eta_min=1e-6)
             self.max_grad_norm = 0.2

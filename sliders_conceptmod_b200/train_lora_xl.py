@@ -21,9 +21,7 @@ from .slider_loop import TextSliderTrainer
 
 def train(config: RootConfig, prompts: list[PromptSettings], device, on_step_complete: Optional[Callable] = None,
           peft_type: str = "lora", rank: int = 4, save_file: bool = True, seed=None):
-    if peft_type != "lora":
-        raise NotImplementedError("peft_type 'dora' (conceptmod/textsliders/dora.py) is a 'next' row (SURVEY 8 f3)")
-    trainer = TextSliderTrainer(config, prompts, device, xl=True, rank=rank, seed=seed)
+    trainer = TextSliderTrainer(config, prompts, device, xl=True, rank=rank, seed=seed, peft_type=peft_type)
     if config.logging.verbose:
         print(trainer.metadata)
     return trainer.run(on_step_complete=on_step_complete, save_file=save_file, suffix=".safetensors")
@@ -85,7 +83,7 @@ def build_parser() -> argparse.ArgumentParser:
     parser.add_argument("--name", type=str, required=False, default=None, help="Name of the slider.")
     parser.add_argument("--attributes", type=str, required=False, default=None,
                         help="attributes to disentangle (comma separated string)")
-    parser.add_argument("--peft_type", type=str, required=False, default="lora", help="lora (dora: next row)")
+    parser.add_argument("--peft_type", type=str, required=False, default="lora", help="dora or lora (default)")
     return parser
 
 

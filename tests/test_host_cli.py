@@ -56,9 +56,8 @@ def test_train_lora_xl_cli_and_peft_gate(tmp_path):
         p.parse_args(["--alpha", "1.0"])
     a = p.parse_args(["--config_file", "data/config-xl.yaml", "--alpha", "1.0"])
     assert a.config_file == "data/config-xl.yaml" and a.rank == 4 and a.peft_type == "lora"
-    cfg = config_util.load_config_from_yaml(str(_write_yaml(tmp_path, model="tiny-xl", negative=True)))
-    with pytest.raises(NotImplementedError):
-        train_lora_xl.train(cfg, [], "cpu", peft_type="dora")
+    a = p.parse_args(["--config_file", "data/config-xl.yaml", "--alpha", "1.0", "--peft_type", "dora"])
+    assert a.peft_type == "dora"            # train_lora_xl.py:87-90: DoRANetwork instead of LoRANetwork
 
 
 def test_image_slider_cli_and_wrapper():

@@ -256,3 +256,34 @@ def test_groupnorm_single_launch_plan_table():
     rc, p = plan(4096, 320, 32, _lib.SLIDER_F32)
     assert rc == 1 and p["gp"] == 2 and p["k"] == 8
     assert fn(0, 320, 32, _lib.SLIDER_BF16, (ctypes.c_int * 6)()) == -1
+
+
+def test_combine_loras_matches_reference_merge(tmp_path):
+    """f4 edge: sliders_conceptmod_b200/combine_loras.py against the reference's own merge()
+    (tests/golden/make_golden_combine.py ran conceptmod/notrigger/combine_loras.py:26-62), plus the file round trip."""
+    from pathlib import Path
+    from safetensors.torch import load_file, save_file
+    from sliders_conceptmod_b200 import combine_loras
+    gold = torch.load(Path(__file__).parent / "golden" / "reference_combine.pt", weights_only=False)
+    out = {}
+    for fam, sd in gold["sources"].items():
+        combine_loras.merge(out, (combine_loras.BinDataHandler(sd), set(sd.keys())), gold["strengths"][fam], fam)
+    assert set(out) == set(gold["merged"])
+    for k, v in gold["merged"].items():
+        assert torch.equal(out[k], v), k
+    assert combine_loras.rename_key("lora_unet-a-b.lora_down.weight", "transformer") == "transformer.a.b.lora_A.weight"
+    # CLI path: three files in, one file out
+    paths = []
+    for fam, sd in gold["sources"].items():
+        p = tmp_path / f"{fam}.safetensors"
+        save_file({k: v.contiguous() for k, v in sd.items()}, str(p))
+        paths.append(str(p))
+    s = gold["strengths"]
+    combine_loras.main(paths + [str(tmp_path / "merged.safetensors"), str(s["transformer"]), str(s["CLIP"]), str(s["T5"])])
+    merged = load_file(str(tmp_path / "merged.safetensors"))
+    assert set(merged) == set(gold["merged"])
+    for k, v in gold["merged"].items():
+        assert torch.allclose(merged[k], v), k
+    import pytest
+    with pytest.raises(AssertionError):
+        combine_loras.merge({}, (combine_loras.BinDataHandler({"weird": torch.zeros(1)}), {"weird"}), 1.0, "CLIP")

@@ -140,3 +140,11 @@ def test_dora_oracle_and_fold_match_reference_vectors():
             xv = x * v
             yf = F.linear(xv, c["W"].double(), bias) + F.linear(F.linear(xv, a2), c["B"].double())
         assert torch.allclose(yf.float(), c["y"], rtol=1e-5, atol=2e-5), (c["kind"], (yf.float() - c["y"]).abs().max())
+        # operand-side form (what ops.dora_prepare computes on the GPU): W_eff = W*v, A_s = A*(s c), adapter scale 1
+        w_eff, a_s, _, _ = dora.dora_operands(c["W"].double(), c["A"].double(), c["B"].double(), c["dora_scale"].double(), s)
+        if conv:
+            yo = F.conv2d(x, w_eff, bias, stride=stride, padding=padding) + \
+                F.conv2d(F.conv2d(x, a_s, stride=stride, padding=padding), c["B"].double())
+        else:
+            yo = F.linear(x, w_eff, bias) + F.linear(F.linear(x, a_s), c["B"].double())
+        assert torch.allclose(yo.float(), c["y"], rtol=1e-5, atol=2e-5), (c["kind"], (yo.float() - c["y"]).abs().max())
