@@ -354,6 +354,19 @@ int slider_groupnorm_nhwc_backward(void* dx, void* dadd, const void* gy, const v
 int slider_layernorm(void* y, const void* x, const void* gamma, const void* beta,
                      int64_t rows, int channels, float eps, int dtype, void* stream);
 int slider_geglu(void* y, const void* x, int64_t rows, int d, int dtype, void* stream);
+/*
+ * Training forms (the grad-recording forward of train_lora.py:275-289 and its backward at :298; gamma / beta are frozen,
+ * unet.requires_grad_(False) at train_lora.py:69, so only the input gradient exists):
+ *   slider_layernorm_train    = slider_layernorm + stats [rows, 2] fp32 {mean, rstd};
+ *   slider_layernorm_backward : dx = rstd * (ghat - mean(ghat) - xhat * mean(ghat * xhat)), ghat = gy * gamma;
+ *   slider_geglu_backward     : dx[:, :d] = gy * gelu(g), dx[:, d:] = gy * a * gelu'(g) for x = [a | g] (recomputed, no
+ *                               saved activation besides x).
+ */
+int slider_layernorm_train(void* y, float* stats, const void* x, const void* gamma, const void* beta,
+                           int64_t rows, int channels, float eps, int dtype, void* stream);
+int slider_layernorm_backward(void* dx, const void* gy, const void* x, const void* gamma, const float* stats,
+                              int64_t rows, int channels, int dtype, void* stream);
+int slider_geglu_backward(void* dx, const void* gy, const void* x, int64_t rows, int d, int dtype, void* stream);
 
 /*
  * Nearest-neighbour 2x upsample of an NHWC tensor: y[b, 2h + i, 2w + j, :] = x[b, h, w, :]  (i, j in {0, 1}).

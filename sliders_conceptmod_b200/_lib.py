@@ -53,6 +53,9 @@ _SIGNATURES = {
     "slider_groupnorm_nhwc": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _i, _i, _vp, _sz, _vp]),
     "slider_layernorm": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i, _f, _i, _vp]),
     "slider_geglu": (C.c_int, [_vp, _vp, _i64, _i, _i, _vp]),
+    "slider_layernorm_train": (C.c_int, [_vp, _fp, _vp, _vp, _vp, _i64, _i, _f, _i, _vp]),
+    "slider_layernorm_backward": (C.c_int, [_vp, _vp, _vp, _vp, _fp, _i64, _i, _i, _vp]),
+    "slider_geglu_backward": (C.c_int, [_vp, _vp, _vp, _i64, _i, _i, _vp]),
     "slider_upsample_nearest2x_nhwc": (C.c_int, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "slider_concat_channels_nhwc": (C.c_int, [_vp, _vp, _vp, _i64, _i, _i, _i, _vp]),
     "slider_loss_workspace_bytes": (_sz, []),

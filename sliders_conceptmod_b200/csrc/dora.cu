@@ -185,7 +185,13 @@ dora_finish_kernel(T* __restrict__ dx, float* __restrict__ dm, const T* __restri
     const int cc = blockIdx.x * DORA_VL * V + i;
     if (cc < cin) {
       float sum = 0.f;
-      for (int ch = 0; ch < nchunks; ++ch) sum += __ldcg(partial + (size_t)ch * cin + cc);
+      for (int ch0 = 0; ch0 < nchunks; ch0 += 8) {       // chunk order, eight loads in flight
+        float t[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) t[u] = ch0 + u < nchunks ? __ldcg(partial + (size_t)(ch0 + u) * cin + cc) : 0.f;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) sum += t[u];
+      }
       dm[cc] = (accumulate ? dm[cc] : 0.f) + s * ninv[cc] * sum;
     }
   }

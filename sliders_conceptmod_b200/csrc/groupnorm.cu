@@ -193,129 +193,6 @@ gn_apply_kernel(T* __restrict__ y, const T* __restrict__ x, const T* __restrict_
   }
 }
 
-// ---- single-launch form: one thread-block cluster per image ------------------------------------------------------
-// The two-kernel form above spends most of its ~13 us per GroupNorm on launch + dependent-launch latency (each pass
-// moves a few MB at most).  Here the CS CTAs of a cluster own the pixel chunks of ONE image: pass 1 reduces the
-// chunk to per-group {sum, sum of squares} in shared memory, the cluster synchronises, every CTA adds the CS partials
-// over distributed shared memory in rank order (deterministic; 2*G floats per peer), builds its scale / shift tables
-// and applies them to its own chunk, which it re-reads from L2.
-template <typename T>
-__global__ void __launch_bounds__(GN_MAX_THREADS)
-gn_cluster_kernel(T* __restrict__ y, const T* __restrict__ x, const T* __restrict__ chan_add,
-                  const T* __restrict__ gamma, const T* __restrict__ beta, const GnParams p, int cs, int ppc,
-                  float* __restrict__ stats_out) {
-  pdl_trigger();
-  pdl_wait();
-  extern __shared__ __align__(16) float gn_smem[];
-  float* s_sum = gn_smem;                                   // [PL][C]
-  float* s_sq = gn_smem + (size_t)p.PL * p.C;               // [PL][C]
-  float* s_grp = gn_smem + (size_t)2 * p.PL * p.C;          // [G][2] this CTA's partial sums (read by the peers)
-  float* s_stat = s_grp + 2 * p.G;                          // [G][2] mean, rstd
-  float* s_scale = s_stat + 2 * p.G;                        // [C]
-  float* s_shift = s_scale + p.C;                           // [C]
-  const int b = blockIdx.y;
-  const int rank = (int)ptx::cluster_ctarank();
-  const int tid = threadIdx.x;
-  const int pl = tid / p.NV, v = tid - pl * p.NV;
-  const int p0 = min(p.HW, rank * ppc), p1 = min(p.HW, p0 + ppc);
-  if (pl < p.PL) {
-    float add[8], sum[8], sq[8];
-#pragma unroll
-    for (int k = 0; k < 8; ++k) { add[k] = 0.f; sum[k] = 0.f; sq[k] = 0.f; }
-    if (chan_add != nullptr) Vec8<T>::load(chan_add + (size_t)b * p.C + v * 8, add);
-    const T* xb = x + ((size_t)b * p.HW) * p.C + v * 8;
-#pragma unroll 8
-    for (int pix = p0 + pl; pix < p1; pix += p.PL) {
-      float xv[8];
-      Vec8<T>::load(xb + (size_t)pix * p.C, xv);
-#pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        const float z = xv[k] + add[k];
-        sum[k] += z;
-        sq[k] = fmaf(z, z, sq[k]);
-      }
-    }
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      s_sum[pl * p.C + v * 8 + k] = sum[k];
-      s_sq[pl * p.C + v * 8 + k] = sq[k];
-    }
-  }
-  __syncthreads();
-  {
-    const int warp = tid >> 5, lane = tid & 31, nwarps = blockDim.x >> 5;
-    const int per_group = p.PL * p.cpg;
-    for (int g = warp; g < p.G; g += nwarps) {
-      float a = 0.f, q = 0.f;
-      for (int i = lane; i < per_group; i += 32) {
-        const int l = i / p.cpg, c = g * p.cpg + (i - l * p.cpg);
-        a += s_sum[l * p.C + c];
-        q += s_sq[l * p.C + c];
-      }
-      a = warp_sum(a);
-      q = warp_sum(q);
-      if (lane == 0) { s_grp[2 * g] = a; s_grp[2 * g + 1] = q; }
-    }
-  }
-  // cluster barrier 1: every CTA's partial sums are in its shared memory
-  ptx::cluster_arrive();
-  ptx::cluster_wait();
-  if (tid < p.G) {
-    const int g = tid;
-    double a = 0.0, q = 0.0;
-    const uint32_t mine = ptx::smem_u32(s_grp + 2 * g);
-    for (int r = 0; r < cs; ++r) {
-      const uint32_t peer = ptx::mapa(mine, (uint32_t)r);
-      float pa, pq;
-      asm volatile("ld.shared::cluster.v2.f32 {%0, %1}, [%2];" : "=f"(pa), "=f"(pq) : "r"(peer));
-      a += (double)pa; q += (double)pq;
-    }
-    const double n = (double)p.cpg * (double)p.HW;
-    const double mean = a / n;
-    double var = q / n - mean * mean;
-    if (var < 0.0) var = 0.0;
-    s_stat[2 * g] = (float)mean;
-    s_stat[2 * g + 1] = rsqrtf((float)var + p.eps);
-    if (stats_out != nullptr && rank == 0) {                // saved for the backward pass: [B][G]{mean, rstd}
-      stats_out[((size_t)b * p.G + g) * 2] = s_stat[2 * g];
-      stats_out[((size_t)b * p.G + g) * 2 + 1] = s_stat[2 * g + 1];
-    }
-  }
-  // the peers may still read this CTA's partials: arrive now, wait before exit
-  ptx::cluster_arrive();
-  __syncthreads();
-  for (int c = tid; c < p.C; c += blockDim.x) {
-    const int g = c / p.cpg;
-    const float mean = s_stat[2 * g], rstd = s_stat[2 * g + 1];
-    const float ga = gamma ? Elem<T>::to_f(gamma[c]) : 1.f, be = beta ? Elem<T>::to_f(beta[c]) : 0.f;
-    const float add = chan_add ? Elem<T>::to_f(chan_add[(size_t)b * p.C + c]) : 0.f;
-    s_scale[c] = rstd * ga;
-    s_shift[c] = fmaf(add - mean, rstd * ga, be);
-  }
-  __syncthreads();
-  if (pl < p.PL) {
-    const float4 sc0 = *reinterpret_cast<const float4*>(s_scale + v * 8), sc1 = *reinterpret_cast<const float4*>(s_scale + v * 8 + 4);
-    const float4 sh0 = *reinterpret_cast<const float4*>(s_shift + v * 8), sh1 = *reinterpret_cast<const float4*>(s_shift + v * 8 + 4);
-    const float sc[8] = {sc0.x, sc0.y, sc0.z, sc0.w, sc1.x, sc1.y, sc1.z, sc1.w};
-    const float sh[8] = {sh0.x, sh0.y, sh0.z, sh0.w, sh1.x, sh1.y, sh1.z, sh1.w};
-    const T* xb = x + ((size_t)b * p.HW) * p.C + v * 8;
-    T* yb = y + ((size_t)b * p.HW) * p.C + v * 8;
-#pragma unroll 4
-    for (int pix = p0 + pl; pix < p1; pix += p.PL) {
-      float xv[8], o[8];
-      Vec8<T>::load(xb + (size_t)pix * p.C, xv);
-#pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        float u = fmaf(xv[k], sc[k], sh[k]);
-        if (p.silu) u = u / (1.f + __expf(-u));
-        o[k] = u;
-      }
-      Vec8<T>::store(yb + (size_t)pix * p.C, o);
-    }
-  }
-  ptx::cluster_wait();
-}
-
 // ---- single-launch form: one CTA (or a small cluster) per (image, group set) --------------------------------------------
 // The data of GP adjacent groups is a [HW][GP * cpg] slab (rows of GP * cpg * sizeof(T) bytes at a stride of
 // C * sizeof(T)); GP = 1, 2, 4 or 8 is the smallest count that makes a row a whole number of 16-byte vectors (SD 1.x:
@@ -550,39 +427,6 @@ gn_group_kernel(T* __restrict__ y, const T* __restrict__ x, const T* __restrict_
   gn_stamp(ga.trace, 7);
 }
 
-// thread-block cluster size of the single-launch form (SLIDER_GN_CLUSTER / slider_debug_gn_cluster: 0 = two-kernel
-// form, 8, 16).  Opt-in: measured SLOWER on B200 -- 8 or 16 CTAs per image cannot pull the 2.6 MB of a 64x64x320 image
-// fast enough (denoise forward 4.97 ms two-kernel, 5.29 ms at 16, 5.84 ms at 8; profiles/r01_ab_gn_cluster.txt).
-static int g_gn_cluster = [] { const char* e = getenv("SLIDER_GN_CLUSTER"); return e ? atoi(e) : 0; }();
-
-template <typename T>
-static int groupnorm_cluster_impl(void* y, const void* x, const void* chan_add, const void* gamma, const void* beta,
-                                  GnParams p, cudaStream_t st, float* stats_out) {
-  const int cs = g_gn_cluster;
-  const int ppc = (p.HW + cs - 1) / cs;
-  int threads = p.PL * p.NV > p.G ? p.PL * p.NV : p.G;
-  threads = (threads + 31) / 32 * 32;
-  const size_t smem = ((size_t)p.PL * p.C * 2 + (size_t)p.G * 4 + (size_t)p.C * 2) * sizeof(float) + 16;
-  static thread_local bool configured = false;
-  if (!configured) {
-    SLIDER_CUDA(cudaFuncSetAttribute(gn_cluster_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
-    SLIDER_CUDA(cudaFuncSetAttribute(gn_cluster_kernel<T>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));   // cs = 16
-    configured = true;
-  }
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(cs, p.B); cfg.blockDim = dim3(threads); cfg.dynamicSmemBytes = smem; cfg.stream = st;
-  cudaLaunchAttribute attr[2];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = (unsigned)cs; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[1].val.programmaticStreamSerializationAllowed = 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = pdl_enabled() ? 2 : 1;
-  cudaLaunchKernelEx(&cfg, gn_cluster_kernel<T>, (T*)y, (const T*)x, (const T*)chan_add, (const T*)gamma, (const T*)beta, p,
-                     cs, ppc, stats_out);
-  return post_launch("gn_cluster_kernel");
-}
-
 // per-(image, group set) single-launch form: on by default (SLIDER_GN_GROUP=0 / slider_debug_gn_group(0, 0): two-kernel
 // form); SLIDER_GN_GROUP_KB: the slab bytes one CTA may hold before the slab is split over a larger cluster
 static int g_gn_group = [] { const char* e = getenv("SLIDER_GN_GROUP"); return e ? atoi(e) : 1; }();
@@ -651,10 +495,8 @@ template <typename T>
 static int groupnorm_impl(void* y, const void* x, const void* chan_add, const void* gamma, const void* beta,
                           float* ws, GnParams p, cudaStream_t st, float* stats_out = nullptr) {
   GnGroupPlan gp;
-  if (g_gn_group && g_gn_cluster < 2 && p.B <= 65535 && gn_group_plan<T>(p, &gp))
+  if (g_gn_group && p.B <= 65535 && gn_group_plan<T>(p, &gp))
     return gn_group_launch<T>(y, x, chan_add, gamma, beta, p, gp, st, stats_out);
-  if (g_gn_cluster >= 2 && ((size_t)p.PL * p.C * 2 + (size_t)p.G * 4 + (size_t)p.C * 2) * sizeof(float) + 16 <= 96 * 1024)
-    return groupnorm_cluster_impl<T>(y, x, chan_add, gamma, beta, p, st, stats_out);
   // workspace: per-chunk partial sums [B][chunks][G][2]
   float* partial = ws;
   {
@@ -939,7 +781,6 @@ using namespace slider;
 extern "C" {
 
 int slider_debug_gn_variant(int v) { g_gn_variant = v; return 0; }
-int slider_debug_gn_cluster(int cs) { g_gn_cluster = (cs == 8 || cs == 16) ? cs : 0; return 0; }
 // host-only view of the single-launch plan (no device needed): 1 and out = {k, gp, words per row, rows per CTA,
 // threads, dynamic smem bytes} when the shape takes the single launch, 0 when it takes the two-kernel form
 int slider_debug_gn_group_plan(int hw, int channels, int groups, int dtype, int* out) {

@@ -239,8 +239,16 @@ colreduce_kernel(const ColReduceParams p, int j0) {
     const int t = rem / (CH * 4), k = (rem >> 2) % CH, j = rem & 3;
     const int cc = (yblk * 4 + vv) * CH + k;
     if (cc < pr.C && j0 + j < p.rank) {
+      // chunk order (deterministic); eight loads in flight at a time -- one L2 round trip per chunk made this tail
+      // the longest part of the 9-tap launches
       float sum = 0.f;
-      for (int ch = 0; ch < nchunks; ++ch) sum += __ldcg(all + (size_t)ch * (4 * NACC) + i);
+      for (int ch0 = 0; ch0 < nchunks; ch0 += 8) {
+        float t[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) t[u] = ch0 + u < nchunks ? __ldcg(all + (size_t)(ch0 + u) * (4 * NACC) + i) : 0.f;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) sum += t[u];
+      }
       float* o = pr.out + (int64_t)cc * pr.oc + (int64_t)(j0 + j) * pr.oj + (int64_t)t * pr.ot;
       *o = (p.accumulate ? *o : 0.f) + sum * pr.scale * (pr.cscale != nullptr ? pr.cscale[cc] : 1.f);
     }

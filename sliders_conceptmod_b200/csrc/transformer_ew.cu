@@ -42,7 +42,7 @@ template <> struct VecIO<float> {
 template <typename T, int MAXV>
 __global__ void __launch_bounds__(256)
 layernorm_kernel(T* __restrict__ y, const T* __restrict__ x, const T* __restrict__ gamma,
-                 const T* __restrict__ beta, int64_t rows, int C, float eps) {
+                 const T* __restrict__ beta, int64_t rows, int C, float eps, float* __restrict__ stats) {
   pdl_trigger();
   constexpr int V = Elem<T>::kVec;
   const int lane = threadIdx.x & 31;
@@ -90,6 +90,7 @@ layernorm_kernel(T* __restrict__ y, const T* __restrict__ x, const T* __restrict
     }
   }
   const float rstd = rsqrtf(warp_sum(sq) / (float)C + eps);
+  if (stats != nullptr && lane == 0) { stats[2 * row] = mean; stats[2 * row + 1] = rstd; }
 #pragma unroll
   for (int j = 0; j < MAXV; ++j) {
     const int v = lane + 32 * j;
@@ -114,7 +115,7 @@ layernorm_kernel(T* __restrict__ y, const T* __restrict__ x, const T* __restrict
 template <typename T>
 __global__ void __launch_bounds__(256)
 layernorm_stream_kernel(T* __restrict__ y, const T* __restrict__ x, const T* __restrict__ gamma,
-                 const T* __restrict__ beta, int64_t rows, int C, float eps) {
+                 const T* __restrict__ beta, int64_t rows, int C, float eps, float* __restrict__ stats) {
   pdl_trigger();
   pdl_wait();
   constexpr int V = Elem<T>::kVec;
@@ -140,6 +141,7 @@ layernorm_stream_kernel(T* __restrict__ y, const T* __restrict__ x, const T* __r
     for (int k = 0; k < V; ++k) { const float d = xv[k] - mean; sq = fmaf(d, d, sq); }
   }
   const float rstd = rsqrtf(warp_sum(sq) / (float)C + eps);
+  if (stats != nullptr && lane == 0) { stats[2 * row] = mean; stats[2 * row + 1] = rstd; }
   for (int v = lane; v < nv; v += 32) {
     float xv[V], gv[V], bv[V], o[V];
     Elem<T>::load(xr + v * V, xv);
@@ -195,6 +197,79 @@ geglu_kernel(T* __restrict__ y, const T* __restrict__ x, int64_t rows, int D) {
 }
 
 
+// ---- LayerNorm backward for FROZEN gamma / beta (unet.requires_grad_(False), train_lora.py:69): dx only ----------------
+//   ghat = gy * gamma,  xhat = (x - mean) * rstd,  dx = rstd * (ghat - mean(ghat) - xhat * mean(ghat * xhat))
+// One warp per row, two passes over the row (the second one hits L1); mean / rstd come from the training forward.
+template <typename T>
+__global__ void __launch_bounds__(256)
+layernorm_bwd_kernel(T* __restrict__ dx, const T* __restrict__ gy, const T* __restrict__ x, const T* __restrict__ gamma,
+                     const float* __restrict__ stats, int64_t rows, int C) {
+  constexpr int V = Elem<T>::kVec;
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const T* xr = x + row * C;
+  const T* gr = gy + row * C;
+  T* dr = dx + row * C;
+  const int nv = C / V;
+  const float mean = stats[2 * row], rstd = stats[2 * row + 1];
+  float s1 = 0.f, s2 = 0.f;
+  for (int v = lane; v < nv; v += 32) {
+    float xv[V], gv[V], wv[V];
+    Elem<T>::load(xr + v * V, xv);
+    Elem<T>::load(gr + v * V, gv);
+    if (gamma) Elem<T>::load(gamma + v * V, wv);
+#pragma unroll
+    for (int k = 0; k < V; ++k) {
+      const float gh = gamma ? gv[k] * wv[k] : gv[k];
+      s1 += gh;
+      s2 = fmaf(gh, (xv[k] - mean) * rstd, s2);
+    }
+  }
+  s1 = warp_sum(s1) / (float)C;
+  s2 = warp_sum(s2) / (float)C;
+  for (int v = lane; v < nv; v += 32) {
+    float xv[V], gv[V], wv[V], o[V];
+    Elem<T>::load(xr + v * V, xv);
+    Elem<T>::load(gr + v * V, gv);
+    if (gamma) Elem<T>::load(gamma + v * V, wv);
+#pragma unroll
+    for (int k = 0; k < V; ++k) {
+      const float gh = gamma ? gv[k] * wv[k] : gv[k];
+      o[k] = rstd * (gh - s1 - (xv[k] - mean) * rstd * s2);
+    }
+    Elem<T>::store(dr + v * V, o);
+  }
+}
+
+// ---- GEGLU backward: y = a * gelu(g)  ->  da = gy * gelu(g),  dg = gy * a * gelu'(g),
+//      gelu'(g) = 0.5 (1 + erf(g / sqrt 2)) + g * exp(-g^2 / 2) / sqrt(2 pi)
+template <typename T>
+__global__ void __launch_bounds__(256)
+geglu_bwd_kernel(T* __restrict__ dx, const T* __restrict__ gy, const T* __restrict__ x, int64_t rows, int D) {
+  constexpr int V = Elem<T>::kVec;
+  const int nv = D / V;
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= nv) return;
+  for (int64_t r = blockIdx.y; r < rows; r += gridDim.y) {
+    float a[V], g[V], u[V], da[V], dg[V];
+    Elem<T>::load(x + r * 2 * D + v * V, a);
+    Elem<T>::load(x + r * 2 * D + D + v * V, g);
+    Elem<T>::load(gy + r * D + v * V, u);
+#pragma unroll
+    for (int k = 0; k < V; ++k) {
+      const float e = sizeof(T) == 2 ? erf_bf16_grade(g[k] * 0.70710678118654752f) : erff(g[k] * 0.70710678118654752f);
+      const float cdf = 0.5f * (1.f + e);
+      const float pdf = 0.3989422804014327f * __expf(-0.5f * g[k] * g[k]);
+      da[k] = u[k] * g[k] * cdf;
+      dg[k] = u[k] * a[k] * fmaf(g[k], pdf, cdf);
+    }
+    Elem<T>::store(dx + r * 2 * D + v * V, da);
+    Elem<T>::store(dx + r * 2 * D + D + v * V, dg);
+  }
+}
+
+
 // ---- nearest-neighbour 2x upsample on NHWC (Upsample2D before its 3x3 convolution) -----------------------------------
 // One thread per 16-byte INPUT vector: read once, stored to the 2 x 2 output pixels (a warp covers 512 contiguous bytes
 // of each).  Pure copy (bit-exact); writes 4x what it reads.
@@ -240,6 +315,11 @@ extern "C" {
 
 int slider_layernorm(void* y, const void* x, const void* gamma, const void* beta, int64_t rows, int channels,
                      float eps, int dtype, void* stream) {
+  return slider_layernorm_train(y, nullptr, x, gamma, beta, rows, channels, eps, dtype, stream);
+}
+
+int slider_layernorm_train(void* y, float* stats, const void* x, const void* gamma, const void* beta, int64_t rows,
+                           int channels, float eps, int dtype, void* stream) {
   SLIDER_CHECK_ARG(y && x && rows > 0 && channels > 0, "layernorm: bad argument");
   SLIDER_CHECK_ARG(channels % 8 == 0, "layernorm: channels must be a multiple of 8 (got %d)", channels);
   SLIDER_CHECK_ARG((((uintptr_t)y | (uintptr_t)x | (uintptr_t)gamma | (uintptr_t)beta) & 15) == 0,
@@ -250,7 +330,7 @@ int slider_layernorm(void* y, const void* x, const void* gamma, const void* beta
   const int per_lane = (channels / (dtype == SLIDER_BF16 ? 8 : 4) + 31) / 32;      // 16-byte vectors per lane
 #define SLIDER_LN_LAUNCH(KERNEL, TYPE)                                                                              \
   launch_pdl(KERNEL, dim3(grid), dim3(256), 0, st, (TYPE*)y, (const TYPE*)x, (const TYPE*)gamma, (const TYPE*)beta, \
-             rows, channels, eps)
+             rows, channels, eps, stats)
   if (dtype == SLIDER_BF16) {
     if (per_lane <= 2) SLIDER_LN_LAUNCH((layernorm_kernel<__nv_bfloat16, 2>), __nv_bfloat16);
     else if (per_lane <= 3) SLIDER_LN_LAUNCH((layernorm_kernel<__nv_bfloat16, 3>), __nv_bfloat16);
@@ -283,6 +363,43 @@ int slider_geglu(void* y, const void* x, int64_t rows, int d, int dtype, void* s
     launch_pdl(geglu_kernel<float>, dim3(gx, (unsigned)gy), dim3(threads), 0, st, (float*)y, (const float*)x, rows, d);
   else { set_error("geglu: unsupported dtype %d", dtype); return SLIDER_ERR_UNSUPPORTED; }
   return post_launch("geglu_kernel");
+}
+
+int slider_layernorm_backward(void* dx, const void* gy, const void* x, const void* gamma, const float* stats,
+                              int64_t rows, int channels, int dtype, void* stream) {
+  SLIDER_CHECK_ARG(dx && gy && x && stats && rows > 0 && channels > 0 && channels % 8 == 0, "layernorm_backward: bad argument");
+  SLIDER_CHECK_ARG((((uintptr_t)dx | (uintptr_t)gy | (uintptr_t)x | (uintptr_t)gamma) & 15) == 0,
+                   "layernorm_backward: pointers must be 16-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  const unsigned grid = (unsigned)((rows + 7) / 8);
+  if (dtype == SLIDER_BF16)
+    layernorm_bwd_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((__nv_bfloat16*)dx, (const __nv_bfloat16*)gy,
+                                                             (const __nv_bfloat16*)x, (const __nv_bfloat16*)gamma, stats, rows, channels);
+  else if (dtype == SLIDER_F32)
+    layernorm_bwd_kernel<float><<<grid, 256, 0, st>>>((float*)dx, (const float*)gy, (const float*)x, (const float*)gamma,
+                                                     stats, rows, channels);
+  else { set_error("layernorm_backward: unsupported dtype %d", dtype); return SLIDER_ERR_UNSUPPORTED; }
+  return post_launch("layernorm_bwd_kernel");
+}
+
+int slider_geglu_backward(void* dx, const void* gy, const void* x, int64_t rows, int d, int dtype, void* stream) {
+  SLIDER_CHECK_ARG(dx && gy && x && rows > 0 && d > 0 && d % 8 == 0, "geglu_backward: bad argument");
+  SLIDER_CHECK_ARG((((uintptr_t)dx | (uintptr_t)gy | (uintptr_t)x) & 15) == 0, "geglu_backward: pointers must be 16-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int V = dtype == SLIDER_BF16 ? 8 : 4;
+  const int nv = d / V;
+  const int threads = nv >= 256 ? 256 : ((nv + 31) / 32) * 32;
+  const unsigned gx = (unsigned)((nv + threads - 1) / threads);
+  int64_t gyb = ((int64_t)sm_count() * 16 + gx - 1) / gx;
+  if (gyb > rows) gyb = rows;
+  if (gyb > 65535) gyb = 65535;
+  if (dtype == SLIDER_BF16)
+    geglu_bwd_kernel<__nv_bfloat16><<<dim3(gx, (unsigned)gyb), threads, 0, st>>>((__nv_bfloat16*)dx, (const __nv_bfloat16*)gy,
+                                                                               (const __nv_bfloat16*)x, rows, d);
+  else if (dtype == SLIDER_F32)
+    geglu_bwd_kernel<float><<<dim3(gx, (unsigned)gyb), threads, 0, st>>>((float*)dx, (const float*)gy, (const float*)x, rows, d);
+  else { set_error("geglu_backward: unsupported dtype %d", dtype); return SLIDER_ERR_UNSUPPORTED; }
+  return post_launch("geglu_bwd_kernel");
 }
 
 int slider_upsample_nearest2x_nhwc(void* y, const void* x, int batch, int height, int width, int channels, int dtype,

@@ -299,6 +299,39 @@ def layernorm(x: torch.Tensor, gamma: torch.Tensor | None, beta: torch.Tensor | 
     return y
 
 
+def layernorm_train(x: torch.Tensor, gamma, beta, eps: float = 1e-5):
+    """layernorm + the per-row {mean, rstd} (fp32 [rows, 2]) its backward takes back."""
+    require_cuda(x, gamma, beta)
+    assert x.is_contiguous()
+    C_ = x.shape[-1]
+    y = torch.empty_like(x)
+    stats = torch.empty(x.numel() // C_, 2, device=x.device, dtype=torch.float32)
+    check(lib().slider_layernorm_train(ptr(y), ptr(stats), ptr(x), ptr(gamma), ptr(beta), x.numel() // C_, int(C_),
+                                       float(eps), dtype_code(x.dtype), stream_ptr()))
+    return y, stats
+
+
+def layernorm_backward(gy: torch.Tensor, x: torch.Tensor, gamma, stats: torch.Tensor) -> torch.Tensor:
+    """Input gradient of LayerNorm with frozen gamma / beta."""
+    require_cuda(gy, x, gamma, stats)
+    assert gy.is_contiguous() and x.is_contiguous() and gy.shape == x.shape and gy.dtype == x.dtype
+    C_ = x.shape[-1]
+    dx = torch.empty_like(x)
+    check(lib().slider_layernorm_backward(ptr(dx), ptr(gy), ptr(x), ptr(gamma), ptr(stats), x.numel() // C_, int(C_),
+                                          dtype_code(x.dtype), stream_ptr()))
+    return dx
+
+
+def geglu_backward(gy: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
+    """Gradient of geglu(x) w.r.t. x [..., 2d] given gy [..., d]."""
+    require_cuda(gy, x)
+    assert gy.is_contiguous() and x.is_contiguous() and x.shape[-1] == 2 * gy.shape[-1]
+    d = gy.shape[-1]
+    dx = torch.empty_like(x)
+    check(lib().slider_geglu_backward(ptr(dx), ptr(gy), ptr(x), gy.numel() // d, int(d), dtype_code(x.dtype), stream_ptr()))
+    return dx
+
+
 def geglu(x: torch.Tensor) -> torch.Tensor:
     """x[..., :d] * gelu(x[..., d:]) for x [..., 2d] (diffusers GEGLU after its projection)."""
     require_cuda(x)

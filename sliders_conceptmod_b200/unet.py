@@ -262,9 +262,51 @@ def add_residual(mod: nn.Module, x: torch.Tensor, residual: torch.Tensor) -> tor
     return fused_linear(mod, x, residual)
 
 
+class _LayerNormFn(torch.autograd.Function):
+    """LayerNorm with frozen gamma / beta on libslider's forward / backward kernels (grad-recording forward)."""
+
+    @staticmethod
+    def forward(ctx, x, norm):
+        x = x if x.is_contiguous() else x.contiguous()
+        y, stats = ops.layernorm_train(x, norm.weight, norm.bias, norm.eps)
+        ctx.save_for_backward(x, stats)
+        ctx.norm = norm
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, stats = ctx.saved_tensors
+        gy = gy if gy.is_contiguous() else gy.contiguous()
+        return ops.layernorm_backward(gy, x, ctx.norm.weight, stats), None
+
+
+class _GEGLUFn(torch.autograd.Function):
+    """a * gelu(g) for h = [a | g]; the backward recomputes from h (no activation saved besides the input)."""
+
+    @staticmethod
+    def forward(ctx, h):
+        h = h if h.is_contiguous() else h.contiguous()
+        ctx.save_for_backward(h)
+        return ops.geglu(h)
+
+    @staticmethod
+    def backward(ctx, gy):
+        h, = ctx.saved_tensors
+        return ops.geglu_backward(gy if gy.is_contiguous() else gy.contiguous(), h)
+
+
+def _train_cuda(x: torch.Tensor, *params) -> bool:
+    """Grad-recording CUDA forward through a layer whose own parameters are frozen: libslider forward + backward."""
+    return (x.is_cuda and not _TORCH_ONLY and "ew_train" not in _DISABLED and torch.is_grad_enabled() and x.requires_grad
+            and all(p is None or (not p.requires_grad and p.dtype == x.dtype) for p in params)
+            and x.dtype in (torch.bfloat16, torch.float32))
+
+
 def layer_norm_fused(norm: nn.LayerNorm, x: torch.Tensor) -> torch.Tensor:
     if _no_grad_cuda(x) and x.shape[-1] % 8 == 0:
         return ops.layernorm(x.contiguous(), norm.weight, norm.bias, norm.eps)
+    if _train_cuda(x, norm.weight, norm.bias) and x.shape[-1] % 8 == 0:
+        return _LayerNormFn.apply(x, norm)
     return norm(x)
 
 
@@ -367,6 +409,8 @@ class GEGLU(nn.Module):
         h = fused_linear(self.proj, x)
         if _no_grad_cuda(h) and h.shape[-1] % 16 == 0:
             return ops.geglu(h.contiguous())
+        if _train_cuda(h) and h.shape[-1] % 16 == 0:
+            return _GEGLUFn.apply(h)
         x, gate = h.chunk(2, dim=-1)
         return x * F.gelu(gate)
 

@@ -73,30 +73,6 @@ def test_groupnorm_nhwc_backward_matches_torch_autograd(case, dtype, silu, with_
         assert dadd is None
 
 
-@pytest.mark.parametrize("cs", [8, 16])
-def test_groupnorm_cluster_form_matches_two_kernel_form(cs):
-    """The opt-in one-cluster-per-image form (slider_debug_gn_cluster) gives the same result as the default form (one
-    launch per (image, group set)) up to the order of the partial sums."""
-    import ctypes
-    from sliders_conceptmod_b200 import ops, _lib
-    fn = _lib.lib().slider_debug_gn_cluster
-    fn.argtypes, fn.restype = [ctypes.c_int], ctypes.c_int
-    gen = torch.Generator(device="cuda").manual_seed(11)
-    for (B, H, W, C, G) in [(2, 64, 64, 320, 32), (2, 8, 8, 1280, 32), (3, 5, 7, 64, 8)]:
-        x = (torch.randn(B, H, W, C, device="cuda", generator=gen) * 1.7 + 0.3).to(torch.bfloat16)
-        gamma = (1 + 0.2 * torch.randn(C, device="cuda", generator=gen)).to(torch.bfloat16)
-        beta = (0.1 * torch.randn(C, device="cuda", generator=gen)).to(torch.bfloat16)
-        add = torch.randn(B, C, device="cuda", generator=gen).to(torch.bfloat16)
-        ref = ops.groupnorm_nhwc(x, G, gamma, beta, 1e-5, True, add)
-        fn(cs)
-        try:
-            y = ops.groupnorm_nhwc(x, G, gamma, beta, 1e-5, True, add)
-            torch.cuda.synchronize()
-        finally:
-            fn(0)
-        assert (y.float() - ref.float()).abs().max().item() <= 2e-2 * ref.float().abs().max().item()
-
-
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
 @pytest.mark.parametrize("slab_kb", [4, 16, 48, 128])
 def test_groupnorm_group_form_matches_two_kernel_form(dtype, slab_kb):

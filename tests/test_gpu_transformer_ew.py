@@ -60,3 +60,63 @@ def test_concat_channels_nhwc_is_bit_exact(shape, dtype):
     y = ops.concat_channels_nhwc(a, b)
     assert torch.equal(y, torch.cat([a, b], dim=-1))
     assert bool((guard == 7.0).all())
+
+
+@pytest.mark.parametrize("rows,C", [(8192, 320), (512, 1280), (77, 64), (3, 2560)])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+def test_layernorm_train_and_backward_match_autograd(rows, C, dtype):
+    """Training form (stats out) + backward for frozen gamma / beta vs fp32 autograd of F.layer_norm."""
+    from sliders_conceptmod_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(13)
+    x = (torch.randn(rows, C, device="cuda", generator=g) * 2 + 0.5).to(dtype)
+    w = (1 + 0.1 * torch.randn(C, device="cuda", generator=g)).to(dtype)
+    b = (0.1 * torch.randn(C, device="cuda", generator=g)).to(dtype)
+    gy = torch.randn(rows, C, device="cuda", generator=g).to(dtype)
+    y, stats = ops.layernorm_train(x, w, b, 1e-5)
+    assert torch.equal(y, ops.layernorm(x, w, b, 1e-5))
+    xf = x.float().requires_grad_(True)
+    yr = F.layer_norm(xf, (C,), w.float(), b.float(), 1e-5)
+    yr.backward(gy.float())
+    assert (stats[:, 0] - x.float().mean(dim=1)).abs().max().item() <= 1e-4
+    dx = ops.layernorm_backward(gy, x, w, stats)
+    tol = 3e-2 if dtype == torch.bfloat16 else 2e-5
+    err = (dx.float() - xf.grad).abs().max().item()
+    assert err <= tol * max(1.0, xf.grad.abs().max().item()), f"dx max-abs {err}"
+
+
+@pytest.mark.parametrize("rows,D", [(8192, 1280), (512, 5120), (5, 64)])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+def test_geglu_backward_matches_autograd(rows, D, dtype):
+    from sliders_conceptmod_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(14)
+    x = torch.randn(rows, 2 * D, device="cuda", generator=g).to(dtype)
+    gy = torch.randn(rows, D, device="cuda", generator=g).to(dtype)
+    xf = x.float().requires_grad_(True)
+    a, gate = xf.chunk(2, dim=-1)
+    (a * F.gelu(gate)).backward(gy.float())
+    dx = ops.geglu_backward(gy, x)
+    tol = 2e-2 if dtype == torch.bfloat16 else 1e-5
+    err = (dx.float() - xf.grad).abs().max().item()
+    assert err <= tol * max(1.0, xf.grad.abs().max().item()), f"dx max-abs {err}"
+
+
+def test_transformer_block_autograd_functions():
+    """The autograd wrappers the grad-recording UNet forward uses (unet._LayerNormFn / _GEGLUFn) against torch autograd."""
+    from sliders_conceptmod_b200 import unet as U
+    g = torch.Generator(device="cuda").manual_seed(15)
+    norm = torch.nn.LayerNorm(320).cuda().to(torch.bfloat16).requires_grad_(False)
+    with torch.no_grad():
+        norm.weight.add_(0.1 * torch.randn(320, device="cuda", generator=g).to(torch.bfloat16))
+    x = torch.randn(2, 64, 320, device="cuda", generator=g).to(torch.bfloat16).requires_grad_(True)
+    h = torch.randn(2, 64, 640, device="cuda", generator=g).to(torch.bfloat16).requires_grad_(True)
+    y = U.layer_norm_fused(norm, x)
+    assert y.grad_fn is not None and "LayerNormFn" in type(y.grad_fn).__name__
+    z = U._GEGLUFn.apply(h)
+    (y.float().square().mean() + z.float().square().mean()).backward()
+    xr = x.detach().float().requires_grad_(True)
+    hr = h.detach().float().requires_grad_(True)
+    a, gate = hr.chunk(2, dim=-1)
+    (F.layer_norm(xr, (320,), norm.weight.float(), norm.bias.float(), norm.eps).square().mean()
+     + (a * F.gelu(gate)).square().mean()).backward()
+    for got, ref in ((x.grad, xr.grad), (h.grad, hr.grad)):
+        assert (got.float() - ref).abs().max().item() <= 4e-2 * ref.abs().max().item()
