@@ -104,6 +104,19 @@ int slider_lora_forward_ex(const slider_layer_geom* g, void* y, const void* x,
                            void* ws, size_t ws_bytes, void* stream);
 
 /*
+ * Feed-forward projection with its GEGLU gate fused into the store (diffusers GEGLU.forward reached from the UNet call
+ * at train_util.py:290-294: `hidden, gate = proj(x).chunk(2, dim=-1); hidden * gelu(gate)`; frozen, never LoRA-wrapped):
+ *     y[p, c] = (x . W[c]^T + b[c]) * gelu(x . W[d + c]^T + b[d + c]),   c < d,   g->cout = 2 d
+ * One launch of the tcgen05 kernel; the 2d-wide intermediate never reaches memory.  W_perm / bias_perm are the
+ * projection's rows re-ordered ONCE by the caller so that every 160-row block holds [a(40) | g(40) | a(40) | g(40)]:
+ *     perm row 160 t + 80 h + 40 s + i  =  original row  s d + 80 t + 40 h + i     (s = 0 value, 1 gate; h = 0, 1; i < 40)
+ * d must be a multiple of 80, M > 16 rows; y [M, d].  Exact (erf) GELU in fp32, the bf16-grade erf of slider_geglu
+ * for bf16 tensors.
+ */
+int slider_linear_geglu(const slider_layer_geom* g, void* y, const void* x, const void* W_perm,
+                        const void* bias_perm, void* stream);
+
+/*
  * Several adapters on ONE input in one launch: the self-attention to_q / to_k / to_v of a transformer block
  * (three LoRAModule.forward calls on the same x, reference diffusers Attention.forward reached from
  * conceptmod/textsliders/train_util.py:290-294).  Operands are the row-wise concatenations

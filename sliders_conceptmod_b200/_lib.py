@@ -34,6 +34,7 @@ _SIGNATURES = {
     "slider_debug_gemm_trace": (C.c_int, [_vp]),
     "slider_lora_forward": (C.c_int, [_G, _vp, _vp, _vp, _vp, _vp, _vp, _fp, _f, _vp, _sz, _vp]),
     "slider_lora_forward_ex": (C.c_int, [_G, _vp, _vp, _vp, _vp, _vp, _vp, _fp, _f, C.c_uint, _vp, _sz, _vp]),
+    "slider_linear_geglu": (C.c_int, [_G, _vp, _vp, _vp, _vp, _vp]),
     "slider_lora_forward_grouped": (C.c_int, [_G, _vp, _vp, _vp, _vp, _vp, _vp, _i, _f, _vp, _sz, _vp]),
     "slider_lora_forward_small_multi": (C.c_int, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "slider_lora_grad_workspace_bytes": (_sz, [_G]),

@@ -340,7 +340,7 @@ static int launch_gemv(const slider_layer_geom* g, int M, void* y, const void* x
 static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const void* act, const void* wgt,
                     const void* bias, const void* lo, const void* Bup, float* h_out, float s, const void* xe,
                     const void* we, void* ws, size_t ws_bytes, cudaStream_t st, int groups = 1, int accumulate = 0,
-                    int bup_ld = 0, int bup_jd = 1) {
+                    int bup_ld = 0, int bup_jd = 1, int geglu = 0) {
   tmap_cache_trim();
   const int es = esize(g->dtype);
   const int taps = g->kh * g->kw;
@@ -369,12 +369,17 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
     SLIDER_CHECK_ARG((long long)g->batch * g->height * g->width > 16, "grouped lora gemm: needs more than 16 rows");
   }
   if (lora) SLIDER_CHECK_ARG(Bup != nullptr, "lora gemm: lora_up weight is NULL");
+  if (geglu) {
+    SLIDER_CHECK_ARG(!lora && !ext && !accumulate && groups == 1 && taps == 1 && nn % 160 == 0,
+                     "linear_geglu: plain 1x1 layer whose 2*d output columns are a multiple of 160 (got %d)", nn);
+    SLIDER_CHECK_ARG((long long)g->batch * g->height * g->width > 16, "linear_geglu: needs more than 16 rows");
+  }
   {
     // small-M path: a 128-row tensor-core tile would be > 87 % padding and the op is weight-bandwidth bound
     const long long M = (long long)g->batch * g->height * g->width;
     const size_t mt = M <= 2 ? 2 : (M <= 4 ? 4 : (M <= 8 ? 8 : 16));
     if (groups == 1 && !accumulate && !ext && taps == 1 && bup_ld == 0 && M <= 16 && mt * kc * sizeof(float) <= 40 * 1024 &&
-        kc * es <= 8 * 32 * 16 && ((uintptr_t)wgt & 15) == 0 && (lo == nullptr || ((uintptr_t)lo & 15) == 0)) {
+        !geglu && kc * es <= 8 * 32 * 16 && ((uintptr_t)wgt & 15) == 0 && (lo == nullptr || ((uintptr_t)lo & 15) == 0)) {
       if (g->dtype == SLIDER_BF16)
         return launch_gemv<__nv_bfloat16>(g, (int)M, y, act, wgt, bias, lo, Bup, lora ? h_out : nullptr, s, lora, st);
       return launch_gemv<float>(g, (int)M, y, act, wgt, bias, lo, Bup, lora ? h_out : nullptr, s, lora, st);
@@ -401,13 +406,14 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
     const int thr = g_bn80_tiles < 0 ? sm_count() : g_bn80_tiles;
     const int tiles160 = m_tiles * ((nn + 159) / 160);
     const int kit = taps * ((kc + bk - 1) / bk + (ext ? 1 : 0));
-    if (g_bn80_tiles < 0 ? (tiles160 <= 12 || (tiles160 * 2 <= thr && kit <= 40)) : tiles160 * 2 <= thr) bn = 80;
+    if (!geglu && (g_bn80_tiles < 0 ? (tiles160 <= 12 || (tiles160 * 2 <= thr && kit <= 40)) : tiles160 * 2 <= thr)) bn = 80;
   }
   p.n_tiles = (nn + bn - 1) / bn; p.N = nn;
   p.taps = taps; p.kw = g->kw; p.pad = g->pad; p.cblocks = (kc + bk - 1) / bk;
   p.rank = g->rank; p.bup_ld = bup_ld > 0 ? bup_ld : g->rank; p.bup_jd = bup_jd; p.s = s; p.lora = lora ? 1 : 0; p.ext = ext ? 1 : 0;
   p.group_n = groups > 1 ? nn / groups : 0;
   p.accumulate = accumulate ? 1 : 0;
+  p.geglu = geglu ? 1 : 0;
   p.total_tiles = m_tiles * p.n_tiles;
   p.per_tap = p.cblocks + (ext ? 1 : 0);
   p.kiters = taps * p.per_tap;
@@ -416,7 +422,7 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
   p.partial = reinterpret_cast<float*>(ws);
   const size_t unit_floats = bn == 160 ? TileCfg<160>::UNIT_FLOATS : TileCfg<80>::UNIT_FLOATS;
   const int nchunk = bn == 160 ? TileCfg<160>::NCHUNK : TileCfg<80>::NCHUNK;
-  if (p.total_tiles * 2 <= sm_count()) {
+  if (!geglu && p.total_tiles * 2 <= sm_count()) {
     int ks = sm_count() / p.total_tiles;
     // A split costs a second launch plus the partial round trip (~6 us at 32+ tiles, ~2.5 us at <= 12): measured on
     // the SD-1.4 layer set (profiles/r01_splitk_depth_sweep.txt) it only pays for deep K -- 64+ K blocks at >= 18 per
@@ -489,8 +495,9 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
     if (!(mWe = cached_tmap(g->dtype, 3, we, wdims, wstr, wbox, eb))) return SLIDER_ERR_CUDA;
   }
   {
-    uint64_t dims[4] = {(uint64_t)nn, (uint64_t)Wo, (uint64_t)Ho, (uint64_t)g->batch};
-    uint64_t str[3] = {(uint64_t)nn * es, (uint64_t)nn * es * Wo, (uint64_t)nn * es * Wo * Ho};
+    const uint64_t ny = geglu ? (uint64_t)nn / 2 : (uint64_t)nn;       // GEGLU: y holds d = N / 2 columns
+    uint64_t dims[4] = {ny, (uint64_t)Wo, (uint64_t)Ho, (uint64_t)g->batch};
+    uint64_t str[3] = {ny * es, ny * es * Wo, ny * es * Wo * Ho};
     uint32_t box[4] = {(uint32_t)(OUT_ROW_BYTES / es), (uint32_t)tg.TW, (uint32_t)tg.TH, (uint32_t)tg.TB};
     if (!(mY = cached_tmap(g->dtype, 4, y, dims, str, box, OUT_ROW_BYTES))) return SLIDER_ERR_CUDA;
   }
@@ -537,6 +544,14 @@ int run_gemm_fused_bwd(const slider_layer_geom* g, void* dx, float* g_out, const
 }  // namespace slider
 
 using namespace slider;
+
+extern "C" int slider_linear_geglu(const slider_layer_geom* g, void* y, const void* x, const void* W_perm,
+                                   const void* bias_perm, void* stream) {
+  SLIDER_CHECK_ARG(g && y && x && W_perm, "linear_geglu: null pointer");
+  SLIDER_CHECK_ARG(g->kh == 1 && g->kw == 1 && g->stride != 2, "linear_geglu: 1x1 / Linear layers only");
+  return run_gemm(g, g->cin, g->cout, y, x, W_perm, bias_perm, nullptr, nullptr, nullptr, 0.f, nullptr, nullptr, nullptr, 0,
+                  (cudaStream_t)stream, 1, 0, 0, 1, /*geglu=*/1);
+}
 
 extern "C" {
 

@@ -123,6 +123,8 @@ struct GemmParams {
   int total_units;        // total_tiles * ksplit
   float* partial;         // split-K partial tiles, [unit][NCHUNK][128][PCW] fp32
   int accumulate;         // y += result (y holds the residual branch) instead of y = result
+  int geglu;              // feed-forward gate fused into the store: the tile's columns are [a(40) | g(40)] x 2 (weight rows
+                          // permuted by the caller) and the tile writes 80 columns a * gelu(g) of y [.., N / 2]
   int group_n;            // grouped adapters: output columns per group (0 = one adapter); group g uses h columns [g*rank, (g+1)*rank)
   FastDiv fd_n_tiles, fd_mt_w, fd_mt_h, fd_ksplit, fd_per_tap, fd_kw;
   int w_prefetch;         // K blocks the weight stream is requested into L2 ahead of the shared-memory pipeline
@@ -544,6 +546,52 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               if (j < p.rank) p.h_out[pix * p.rank + j] = hv[j];
           }
         }
+      }
+      if (p.geglu) {
+        // GEGLU (diffusers GEGLU.forward: hidden, gate = proj(x).chunk(2); hidden * gelu(gate)): this group's first
+        // CPG/2 chunks are the values, the last CPG/2 the matching gates
+        if (BN == 160) {
+#pragma unroll
+          for (int ci = 0; ci < CPG / 2; ++ci) {
+            const int ca = grp * HALF_N + ci * CW, cg = ca + HALF_N / 2;
+            const uint32_t dst = out_base + ob * OUT_BYTES + row * OUT_ROW_BYTES;
+#pragma unroll
+            for (int pc = 0; pc < OUT_ROW_BYTES / 16; ++pc) {
+              float o[PW];
+#pragma unroll
+              for (int k = 0; k < PW; ++k) {
+                const int i = pc * PW + k;
+                const float av = __uint_as_float(v[ci][i]) + ptx::ld_shared_f32(bias_s + (ca + i) * 4);
+                const float gv = __uint_as_float(v[ci + CPG / 2][i]) + ptx::ld_shared_f32(bias_s + (cg + i) * 4);
+                const float e = sizeof(T) == 2 ? erf_bf16_grade(gv * 0.70710678118654752f) : erff(gv * 0.70710678118654752f);
+                o[k] = av * (0.5f * gv * (1.f + e));
+              }
+              if (sizeof(T) == 2) {
+                uint32_t w[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                  __nv_bfloat162 h2 = __floats2bfloat162_rn(o[(2 * k) % PW], o[(2 * k + 1) % PW]);
+                  w[k] = *reinterpret_cast<uint32_t*>(&h2);
+                }
+                ptx::st_shared_v4(dst + pc * 16, w[0], w[1], w[2], w[3]);
+              } else {
+                ptx::st_shared_v4(dst + pc * 16, __float_as_uint(o[0]), __float_as_uint(o[1]), __float_as_uint(o[2 % PW]),
+                                  __float_as_uint(o[3 % PW]));
+              }
+            }
+            ptx::fence_proxy_async_smem();
+            if (gt == 0) ptx::bulk_wait_read<NB - 2>();
+            SLIDER_GROUP_BAR();
+            if (gt == 0) {
+              ptx::tma_store_4d(&tmY, out_base + ob * OUT_BYTES, tc.n_blk * (BN / 2) + grp * (HALF_N / 2) + ci * CW, tc.w0,
+                                tc.h0, tc.b0);
+              ptx::bulk_commit();
+            }
+            if (++ob == (uint32_t)NB) ob = 0;
+          }
+        }
+        if (et == 0 && unit == (int)blockIdx.x) SLIDER_TRACE(6);
+        continue;
       }
 #pragma unroll
       for (int ci = 0; ci < CPG; ++ci) {

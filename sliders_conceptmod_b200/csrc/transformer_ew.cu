@@ -158,20 +158,6 @@ layernorm_stream_kernel(T* __restrict__ y, const T* __restrict__ x, const T* __r
   }
 }
 
-// erf for bf16 outputs: Abramowitz-Stegun 7.1.26 (|error| <= 1.5e-7, three orders below a bf16 ulp) on the fast
-// exp / reciprocal units; the exact erff costs ~40 instructions per element and made the kernel ALU-bound
-// (0.52 of HBM at 16384 x 5120).  fp32 tensors keep erff.
-__device__ __forceinline__ float erf_bf16_grade(float x) {
-  const float ax = fabsf(x);
-  const float t = __frcp_rn(fmaf(0.3275911f, ax, 1.f));
-  float p = fmaf(1.061405429f, t, -1.453152027f);
-  p = fmaf(p, t, 1.421413741f);
-  p = fmaf(p, t, -0.284496736f);
-  p = fmaf(p, t, 0.254829592f);
-  const float r = 1.f - p * t * __expf(-ax * ax);
-  return copysignf(r, x);
-}
-
 // ---- GEGLU: y[r, c] = x[r, c] * gelu(x[r, D + c]) (erf GELU) -------------------------------------
 template <typename T>
 __global__ void __launch_bounds__(256)

@@ -130,6 +130,29 @@ def lora_forward_grouped(x: torch.Tensor, w_cat: torch.Tensor, a_cat: torch.Tens
     return y
 
 
+def geglu_permutation(d: int, device=None) -> torch.Tensor:
+    """Row order of the GEGLU projection that `linear_geglu` expects: every 160-row block = [a(40) | g(40) | a(40) | g(40)]
+    (a = rows [0, d) of the projection, g = rows [d, 2d))."""
+    assert d % 80 == 0
+    t = torch.arange(d // 80).view(-1, 1, 1, 1)
+    h = torch.arange(2).view(1, -1, 1, 1)
+    s = torch.arange(2).view(1, 1, -1, 1)
+    i = torch.arange(40).view(1, 1, 1, -1)
+    return (s * d + 80 * t + 40 * h + i).reshape(-1).to(device)
+
+
+def linear_geglu(x: torch.Tensor, w_perm: torch.Tensor, bias_perm: torch.Tensor | None) -> torch.Tensor:
+    """(x @ Wa^T + ba) * gelu(x @ Wg^T + bg) in ONE tensor-core launch; w_perm [2d, K] / bias_perm [2d] are the GEGLU
+    projection's rows in `geglu_permutation` order.  x [M, K] -> [M, d]."""
+    require_cuda(x, w_perm, bias_perm)
+    assert x.dim() == 2 and x.is_contiguous() and w_perm.is_contiguous()
+    n2, K = w_perm.shape[0], w_perm.shape[-1]
+    g = make_geom(x.dtype, 1, 1, x.shape[0], K, n2, 1, 0)
+    y = torch.empty(x.shape[0], n2 // 2, device=x.device, dtype=x.dtype)
+    check(lib().slider_linear_geglu(C.byref(g), ptr(y), ptr(x), ptr(w_perm), ptr(bias_perm), stream_ptr()))
+    return y
+
+
 class SmallMultiPlan:
     """Pointer tables of one `lora_forward_small_multi` call, built once per (layer set, input buffer): the frozen
     weights, the flat LoRA parameter buffer and the output buffer never move, so a captured launch stays valid."""

@@ -405,7 +405,30 @@ class GEGLU(nn.Module):
         super().__init__()
         self.proj = nn.Linear(dim_in, dim_out * 2)
 
+    def _perm(self):
+        """Frozen projection re-ordered once for the fused GEMM + gate launch (rebuilt if the weight is replaced)."""
+        w = self.proj.weight
+        key = (w.data_ptr(), w._version, w.dtype)
+        hit = self.__dict__.get("_perm_cache")
+        if hit is None or hit[0] != key:
+            idx = ops.geglu_permutation(w.shape[0] // 2, w.device)
+            b = self.proj.bias
+            if hit is not None:
+                ops._retired.append(hit[1:])          # a captured graph may still read the old buffers
+            hit = (key, w.detach().index_select(0, idx).contiguous(), None if b is None else b.detach().index_select(0, idx).contiguous())
+            self.__dict__["_perm_cache"] = hit
+        return hit[1], hit[2]
+
     def forward(self, x):
+        w = self.proj.weight
+        if (_no_grad_cuda(x) and "ffgeglu" not in _DISABLED and "forward" not in self.proj.__dict__ and not w.requires_grad
+                and x.dtype == w.dtype and (w.shape[0] // 2) % 80 == 0 and w.shape[1] % 8 == 0
+                and x.numel() // x.shape[-1] > 16):
+            # no-grad forward: projection + GEGLU gate in one tensor-core launch, the 2d-wide tensor never materialises
+            wp, bp = self._perm()
+            x2 = x.reshape(-1, x.shape[-1])
+            y = ops.linear_geglu(x2 if x2.is_contiguous() else x2.contiguous(), wp, bp)
+            return y.view(*x.shape[:-1], w.shape[0] // 2)
         h = fused_linear(self.proj, x)
         if _no_grad_cuda(h) and h.shape[-1] % 16 == 0:
             return ops.geglu(h.contiguous())

@@ -120,3 +120,30 @@ def test_transformer_block_autograd_functions():
      + (a * F.gelu(gate)).square().mean()).backward()
     for got, ref in ((x.grad, xr.grad), (h.grad, hr.grad)):
         assert (got.float() - ref).abs().max().item() <= 4e-2 * ref.abs().max().item()
+
+
+@pytest.mark.parametrize("M,K,D", [(8192, 320, 1280), (2048, 640, 2560), (512, 1280, 5120), (128, 1280, 5120), (300, 64, 80)])
+@pytest.mark.parametrize("dtype,tol", [(torch.bfloat16, 2e-2), (torch.float32, 1e-4)])
+def test_linear_geglu_fused(M, K, D, dtype, tol):
+    """slider_linear_geglu (feed-forward projection with the GEGLU gate in the GEMM's store) vs
+    F.linear -> chunk -> a * gelu(g) in fp32, and vs the two-launch product path (GEMM, then slider_geglu)."""
+    from sliders_conceptmod_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(21)
+    x = torch.randn(M, K, device="cuda", generator=g).to(dtype)
+    w = (torch.randn(2 * D, K, device="cuda", generator=g) / K ** 0.5).to(dtype)
+    b = (0.2 * torch.randn(2 * D, device="cuda", generator=g)).to(dtype)
+    idx = ops.geglu_permutation(D, "cuda")
+    assert sorted(idx.tolist()) == list(range(2 * D))
+    y = ops.linear_geglu(x, w.index_select(0, idx).contiguous(), b.index_select(0, idx).contiguous())
+    h = F.linear(x.float(), w.float(), b.float())
+    a, gate = h.chunk(2, dim=-1)
+    ref = a * F.gelu(gate)
+    err = (y.float() - ref).abs().max().item()
+    assert y.shape == (M, D) and err <= tol * ref.abs().max().item(), f"max-abs {err:.3e} vs {ref.abs().max().item():.3e}"
+    two, _ = ops.lora_forward(x, w.view(2 * D, 1, K), b, None, None, 0.0)
+    two = ops.geglu(two)
+    assert (y.float() - two.float()).abs().max().item() <= tol * ref.abs().max().item()
+    # no bias
+    y0 = ops.linear_geglu(x, w.index_select(0, idx).contiguous(), None)
+    a0, g0 = F.linear(x.float(), w.float()).chunk(2, dim=-1)
+    assert (y0.float() - a0 * F.gelu(g0)).abs().max().item() <= tol * ref.abs().max().item()
