@@ -296,6 +296,8 @@ static int g_splitk_depth = [] { const char* e = getenv("SLIDER_SPLITK_DEPTH"); 
 static int g_w_prefetch = [] { const char* e = getenv("SLIDER_W_PREFETCH"); return e ? atoi(e) : 12; }();
 // The 128 x 80 tile serves launches whose 128 x 160 tiling would leave at least half of the SMs without a tile
 // (tiles * 2 <= this threshold; SLIDER_BN80_TILES / slider_debug_bn80_tiles: 0 = never, -1 = the SM count)
+// CTA-pair form (SLIDER_PAIR / slider_debug_pair): 0 = never, 1 = wherever the geometry allows, -1 = the rule in run_gemm
+static int g_pair = [] { const char* e = getenv("SLIDER_PAIR"); return e ? atoi(e) : -1; }();
 static int g_bn80_tiles = [] { const char* e = getenv("SLIDER_BN80_TILES"); return e ? atoi(e) : -1; }();
 
 static TileGeom choose_tile(int W, int H, int B) {
@@ -415,6 +417,11 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
   p.accumulate = accumulate ? 1 : 0;
   p.geglu = geglu ? 1 : 0;
   p.total_tiles = m_tiles * p.n_tiles;
+  p.m_tiles = m_tiles;
+  // CTA pairs: bf16, wide tile, forward geometry; a grouped launch's h columns must not straddle the two halves
+  bool pair = g_pair != 0 && g->dtype == SLIDER_BF16 && bn == 160 && !ext && m_tiles >= 2 &&
+              (groups == 1 || (g->rank <= 8 && 8 % (g->rank > 0 ? g->rank : 1) == 0));
+  if (pair && g_pair < 0) pair = p.total_tiles >= 2 * sm_count();       // L2-bound regime: several waves of tiles
   p.per_tap = p.cblocks + (ext ? 1 : 0);
   p.kiters = taps * p.per_tap;
   // split-K when the tile count leaves more than half of the SMs idle and K is deep enough
@@ -442,6 +449,8 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
     }
   }
   p.total_units = p.total_tiles * p.ksplit;
+  if (p.ksplit > 1 && g_pair < 0) pair = false;
+  p.pair_units = p.n_tiles * ((m_tiles + 1) / 2) * p.ksplit;
   p.fd_n_tiles = FastDiv::make((uint32_t)p.n_tiles);
   p.fd_mt_w = FastDiv::make((uint32_t)p.mt_w);
   p.fd_mt_h = FastDiv::make((uint32_t)p.mt_h);
@@ -472,14 +481,14 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
   {
     uint64_t dims[3] = {(uint64_t)kc, (uint64_t)taps, (uint64_t)nn};
     uint64_t str[2] = {(uint64_t)kc * es, (uint64_t)kc * es * taps};
-    uint32_t box[3] = {(uint32_t)bk, 1u, (uint32_t)bn};
+    uint32_t box[3] = {(uint32_t)bk, 1u, (uint32_t)(pair ? bn / 2 : bn)};      // pair mode: each CTA stages half of the rows
     if (!(mW = cached_tmap(g->dtype, 3, wgt, dims, str, box, ROW_BYTES))) return SLIDER_ERR_CUDA;
   }
   mL = mW; mXe = mA; mWe = mW;
   if (lora) {
     uint64_t dims[3] = {(uint64_t)kc, (uint64_t)taps, (uint64_t)(g->rank * groups)};
     uint64_t str[2] = {(uint64_t)kc * es, (uint64_t)kc * es * taps};
-    uint32_t box[3] = {(uint32_t)bk, 1u, (uint32_t)HCOLS};
+    uint32_t box[3] = {(uint32_t)bk, 1u, (uint32_t)(pair ? HCOLS / 2 : HCOLS)};
     if (!(mL = cached_tmap(g->dtype, 3, lo, dims, str, box, ROW_BYTES))) return SLIDER_ERR_CUDA;
   }
   if (ext) {
@@ -509,6 +518,7 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
     if (!(mP = cached_tmap(SLIDER_F32, 2, ws, dims, str, box, OUT_ROW_BYTES))) return SLIDER_ERR_CUDA;
   }
   const int r4 = !lora ? 0 : (g->rank <= 4 ? 1 : (g->rank <= 8 ? 2 : 4));
+  if (pair) return launch_gemm_pair(r4, *mA, *mW, *mL, *mXe, *mWe, *mY, *mP, p, st);
   if (bn == 160) return launch_gemm_tile<160>(g->dtype, r4, *mA, *mW, *mL, *mXe, *mWe, *mY, *mP, p, st);
   return launch_gemm_tile<80>(g->dtype, r4, *mA, *mW, *mL, *mXe, *mWe, *mY, *mP, p, st);
 }
@@ -557,6 +567,7 @@ extern "C" {
 
 int slider_debug_splitk_depth(int d) { g_splitk_depth = d > 0 ? d : 0; return SLIDER_OK; }
 int slider_debug_bn80_tiles(int tiles) { g_bn80_tiles = tiles; return SLIDER_OK; }
+int slider_debug_pair(int mode) { g_pair = mode; return SLIDER_OK; }
 int slider_debug_gemm_trace(void* buf) { g_gemm_trace = reinterpret_cast<long long*>(buf); return SLIDER_OK; }
 
 size_t slider_gemm_workspace_bytes(void) { return (size_t)160 * TileCfg<160>::UNIT_FLOATS * sizeof(float); }

@@ -117,6 +117,8 @@ struct GemmParams {
   int lora;               // accumulate h and apply it in the epilogue
   int ext;                // extended-K operand pair present (input-gradient mode)
   int total_tiles;
+  int m_tiles;            // pixel tiles (total_tiles / n_tiles)
+  int pair_units;         // CTA-pair mode: work units of a pair = n_tiles * ceil(m_tiles / 2) * ksplit
   int per_tap;            // K iterations per tap = cblocks + ext
   int kiters;             // taps * per_tap
   int ksplit;             // K partitions per tile (1 = no split)
@@ -168,7 +170,13 @@ template <> __device__ __forceinline__ void tmem_ld_cols<20>(uint32_t taddr, uin
   ptx::tmem_ld_x4(taddr + 16, v + 16);
 }
 
-template <typename T, int R4, int BN>
+// TWO = CTA-pair mode (cluster of 2, cta_group::2): the pair owns two M-adjacent tiles of one N tile; each CTA loads its
+// own 128 activation rows and HALF of the weight rows (80 W rows + 8 lora_down rows), the leader issues M = 256 MMAs over
+// both shared memories, each CTA's 128 accumulator rows land in its own TMEM.  27 KB instead of 38 KB of operands per
+// SM and K block: the launches with hundreds of tiles (SD-XL) are bound by L2 -> SM bandwidth, not by the tensor pipe.
+// Accumulator columns in this mode: [0,80) W rows of CTA 0 | [80,88) h 0..7 | [88,168) W rows of CTA 1 | [168,176) h 8..15
+// (adapter off: [0,80) | [80,160)).
+template <typename T, int R4, int BN, bool TWO>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                  const __grid_constant__ CUtensorMap tmL, const __grid_constant__ CUtensorMap tmXe,
@@ -208,20 +216,43 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   pdl_trigger();
   if (threadIdx.x == 0) SLIDER_TRACE(0);
   const uint32_t smem_base = ptx::smem_u32(smem);
-  const uint32_t main_tx = (uint32_t)(p.rows * ROW_BYTES + B_BYTES + (p.lora ? L_BYTES : 0));
+  const uint32_t crank = TWO ? ptx::cluster_ctarank() : 0u;                 // rank in the CTA pair (0 = leader)
+  const int first_unit = TWO ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;    // persistent loop over units / pair units
+  const int unit_step = TWO ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  const int unit_end = TWO ? p.pair_units : p.total_units;
+  constexpr int W_ROWS = TWO ? BN / 2 : BN;                                 // weight rows this CTA stages per K block
+  constexpr int L_OFF = A_BYTES + W_ROWS * ROW_BYTES;                       // lora_down rows sit right behind them
+  // unit -> (tile of THIS CTA, K split, index of the (tile, split) unit in the split-K workspace, phantom tile?)
+  auto unit_map = [&](int u, uint32_t& tile, uint32_t& split, int& real_unit, bool& phantom) {
+    tile = (uint32_t)u; split = 0; phantom = false;
+    if (p.ksplit > 1) p.fd_ksplit.divmod((uint32_t)u, tile, split);
+    if (TWO) {
+      uint32_t mp, nb;
+      p.fd_n_tiles.divmod(tile, mp, nb);
+      const uint32_t mi = 2 * mp + crank;
+      phantom = (int)mi >= p.m_tiles;          // odd tile count: the pair's second CTA computes zeros, stores nothing
+      tile = mi * (uint32_t)p.n_tiles + nb;
+    }
+    real_unit = (int)tile * p.ksplit + (int)split;
+  };
+  const uint32_t main_tx = TWO ? 2u * (uint32_t)(p.rows * ROW_BYTES + W_ROWS * ROW_BYTES + (p.lora ? L_BYTES / 2 : 0))
+                               : (uint32_t)(p.rows * ROW_BYTES + B_BYTES + (p.lora ? L_BYTES : 0));
   const uint32_t ext_tx = (uint32_t)((p.rows + BN) * Tr::kExtRowBytes);
 
   // ---- TMA producer state (one elected thread).
-  int pu = (int)blockIdx.x, pit = 0, pit1 = 0, ptap = 0, pj = 0;
+  int pu = first_unit, pit = 0, pit1 = 0, ptap = 0, pj = 0;
   uint32_t pstage = 0, pphase = 0;
   TileCoord ptc = {0, 0, 0, 0, 0};
-  bool phave = false;
+  bool phave = false, pfirst_m = false;
   auto prod_begin = [&]() {
-    phave = pu < p.total_units;
+    phave = pu < unit_end;
     if (!phave) return;
-    uint32_t tile = (uint32_t)pu, split = 0;
-    if (p.ksplit > 1) p.fd_ksplit.divmod((uint32_t)pu, tile, split);
+    uint32_t tile, split;
+    int ru;
+    bool ph;
+    unit_map(pu, tile, split, ru, ph);
     ptc = tile_coord<BN>(p, (int)tile);
+    pfirst_m = TWO ? (int)tile < 2 * p.n_tiles : (ptc.w0 == 0 && ptc.h0 == 0 && ptc.b0 == 0);
     pit = 0; pit1 = p.kiters; ptap = 0; pj = 0;
     if (p.ksplit > 1) {
       split_range(p, split, pit, pit1);
@@ -237,16 +268,23 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   auto prod_prefetch_w = [&](int it) {
     const int tap = (int)p.fd_per_tap.div((uint32_t)it);
     const int j = it - tap * p.per_tap;
-    if (j < p.cblocks) ptx::tma_prefetch_l2_3d(&tmW, j * BK, tap, ptc.n0);
+    if (j < p.cblocks) ptx::tma_prefetch_l2_3d(&tmW, j * BK, tap, ptc.n0 + (int)crank * W_ROWS);
   };
-  auto prod_owner = [&]() { return p.w_prefetch > 0 && ptc.w0 == 0 && ptc.h0 == 0 && ptc.b0 == 0; };
+  auto prod_owner = [&]() { return p.w_prefetch > 0 && pfirst_m; };
   auto prod_issue = [&]() {
     const int ty = (int)p.fd_kw.div((uint32_t)ptap);
     const int dy = ty - p.pad, dx = ptap - ty * p.kw - p.pad;
     ptx::mbar_wait(ptx::smem_u32(empty_bar + pstage), pphase ^ 1);
     const uint32_t sa = smem_base + pstage * kStageStride;
     const uint32_t fb = ptx::smem_u32(full_bar + pstage);
-    if (pj < p.cblocks) {
+    if (TWO) {
+      // both CTAs' loads complete on the LEADER's barrier, which expects the bytes of both
+      const uint32_t fbl = ptx::mapa(fb, 0u);
+      if (crank == 0) ptx::mbar_arrive_expect_tx(fb, main_tx);
+      ptx::tma_load_4d_2cta(sa, &tmA, fbl, pj * BK, ptc.w0 * p.stride + dx, ptc.h0 * p.stride + dy, ptc.b0);
+      ptx::tma_load_3d_2cta(sa + A_BYTES, &tmW, fbl, pj * BK, ptap, ptc.n0 + (int)crank * W_ROWS);
+      if (p.lora) ptx::tma_load_3d_2cta(sa + L_OFF, &tmL, fbl, pj * BK, ptap, (int)crank * (HCOLS / 2));
+    } else if (pj < p.cblocks) {
       if (p.dbg_skip) {
         const uint32_t tx = ((p.dbg_skip & 1) ? 0u : (uint32_t)(p.rows * ROW_BYTES)) + ((p.dbg_skip & 2) ? 0u : (uint32_t)B_BYTES) +
                             (p.lora ? (uint32_t)L_BYTES : 0u);
@@ -272,7 +310,7 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if (++pstage == (uint32_t)kStages) { pstage = 0; pphase ^= 1; }
     if (++pj == p.per_tap) { pj = 0; ++ptap; }
     if (++pit == pit1) {
-      pu += (int)gridDim.x;
+      pu += unit_step;
       prod_begin();
       if (phave && prod_owner())
         for (int d = 0; d < p.w_prefetch && pit + d < pit1; ++d) prod_prefetch_w(pit + d);
@@ -292,19 +330,24 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
     for (int i = 0; i < ACC_STAGES; ++i) {
       ptx::mbar_init(ptx::smem_u32(tfull_bar + i), 1);
-      ptx::mbar_init(ptx::smem_u32(tempty_bar + i), 8);  // one arrive per epilogue warp
+      ptx::mbar_init(ptx::smem_u32(tempty_bar + i), TWO ? 16 : 8);  // one arrive per epilogue warp (of both CTAs)
     }
     ptx::fence_mbar_init();
   }
   if (warp == 1) {
-    ptx::tmem_alloc(ptx::smem_u32(tmem_slot), Cfg::TMEM_COLS);
-    ptx::tmem_relinquish();
+    if (TWO) { ptx::tmem_alloc_2cta(ptx::smem_u32(tmem_slot), Cfg::TMEM_COLS); ptx::tmem_relinquish_2cta(); }
+    else { ptx::tmem_alloc(ptx::smem_u32(tmem_slot), Cfg::TMEM_COLS); ptx::tmem_relinquish(); }
   }
   ptx::tc_fence_before();
   // CTA-wide start barrier.  Warp 0 only ARRIVES (its lane 0 initialised the mbarriers above and is the one
   // thread that never needs the TMEM base), so the producer starts fetching operands while the TMEM allocation
   // and the other warps' start-up are still in flight.
-  if (warp == 0) {
+  if (TWO) {
+    // pair mode: nobody may signal the peer's barriers or write its shared memory before the peer has initialised
+    __syncthreads();
+    ptx::cluster_arrive();
+    ptx::cluster_wait();
+  } else if (warp == 0) {
     __syncwarp();
     asm volatile("bar.arrive 1, %0;" ::"n"(kGemmThreads) : "memory");
   } else {
@@ -332,15 +375,15 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       prod_issue();
       if (first) { SLIDER_TRACE(2); first = false; }
     }
-  } else if (warp == 1 && ptx::elect_one()) {
-    // ===================== MMA issuer =====================
+  } else if (warp == 1 && (!TWO || crank == 0) && ptx::elect_one()) {
+    // ===================== MMA issuer (pair mode: the leader only) =====================
     // With the adapter on, W tile (BN rows) and lora_down tile (HCOLS rows) are adjacent in shared
     // memory and their accumulators adjacent in TMEM: ONE tcgen05.mma of N = BN + HCOLS covers both.
-    constexpr uint32_t idesc_main = ptx::make_idesc(Tr::kFmt, BM, BN);
-    constexpr uint32_t idesc_lora = ptx::make_idesc(Tr::kFmt, BM, BN + HCOLS);
+    constexpr uint32_t idesc_main = ptx::make_idesc(Tr::kFmt, TWO ? 2 * BM : BM, BN);
+    constexpr uint32_t idesc_lora = ptx::make_idesc(Tr::kFmt, TWO ? 2 * BM : BM, BN + HCOLS);
     const uint32_t idesc = p.lora ? idesc_lora : idesc_main;
     uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
-    for (int unit = blockIdx.x; unit < p.total_units; unit += gridDim.x) {
+    for (int unit = first_unit; unit < unit_end; unit += unit_step) {
       int it0 = 0, it1 = p.kiters, j = 0;
       if (p.ksplit > 1) {
         uint32_t tile, split;
@@ -355,7 +398,7 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       for (int it = it0; it < it1; ++it) {
         ptx::mbar_wait(ptx::smem_u32((Tr::kSplit3 ? xf_bar : full_bar) + stage), phase);
         ptx::tc_fence_after();
-        if (unit == (int)blockIdx.x && it == it0) SLIDER_TRACE(3);
+        if (unit == first_unit && it == it0) SLIDER_TRACE(3);
         const uint32_t sa = smem_base + stage * kStageStride;
         const bool main_blk = j < p.cblocks;
         const uint32_t rb = main_blk ? (uint32_t)ROW_BYTES : (uint32_t)Tr::kExtRowBytes;
@@ -371,6 +414,9 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             Tr::mma(d_main, da + 2 * k, db_lo + 2 * k, id, 1u);
             Tr::mma(d_main, da + 2 * k, db + 2 * k, id, 1u);
           }
+        } else if (TWO) {
+#pragma unroll
+          for (int k = 0; k < KSTEPS; ++k) ptx::mma_f16_2cta(d_main, da + 2 * k, db + 2 * k, id, acc | (uint32_t)k);
         } else if (main_blk) {
 #pragma unroll
           for (int k = 0; k < KSTEPS; ++k) Tr::mma(d_main, da + 2 * k, db + 2 * k, id, acc | (uint32_t)k);
@@ -379,12 +425,14 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           for (int k = 0; k < EXT_KSTEPS; ++k) Tr::mma(d_main, da + 2 * k, db + 2 * k, id, acc | (uint32_t)k);
         }
         acc = 1;
-        ptx::mma_commit(ptx::smem_u32(empty_bar + stage));
+        if (TWO) ptx::mma_commit_2cta(ptx::smem_u32(empty_bar + stage), 3);     // frees the stage in BOTH CTAs
+        else ptx::mma_commit(ptx::smem_u32(empty_bar + stage));
         if (++stage == (uint32_t)kStages) { stage = 0; phase ^= 1; }
         if (++j == p.per_tap) j = 0;
       }
-      ptx::mma_commit(ptx::smem_u32(tfull_bar + as));
-      if (unit == (int)blockIdx.x) SLIDER_TRACE(4);
+      if (TWO) ptx::mma_commit_2cta(ptx::smem_u32(tfull_bar + as), 3);
+      else ptx::mma_commit(ptx::smem_u32(tfull_bar + as));
+      if (unit == first_unit) SLIDER_TRACE(4);
       if (++as == ACC_STAGES) { as = 0; aphase ^= 1; }
     }
   } else if (warp >= 2) {
@@ -413,9 +461,22 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const T* __restrict__ bias = reinterpret_cast<const T*>(p.bias);
     const T* __restrict__ Bup = reinterpret_cast<const T*>(p.Bup);
 #define SLIDER_GROUP_BAR() asm volatile("bar.sync %0, 128;" ::"r"(3 + grp) : "memory")
-    for (int unit = blockIdx.x; unit < p.total_units; unit += gridDim.x) {
-      uint32_t tile = (uint32_t)unit, split = 0;
-      if (p.ksplit > 1) p.fd_ksplit.divmod((uint32_t)unit, tile, split);
+    // pair mode: accumulator column of this group's first output column / of h column j (see the layout above)
+    const uint32_t grp_col = TWO ? (uint32_t)grp * (uint32_t)(HALF_N + (p.lora ? HCOLS / 2 : 0)) : (uint32_t)(grp * HALF_N);
+    auto tempty_arrive = [&](uint32_t stage) {      // one arrive per epilogue warp, on the LEADER's barrier in pair mode
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        const uint32_t bar = ptx::smem_u32(tempty_bar + stage);
+        if (TWO && crank != 0) ptx::mbar_arrive_cluster(ptx::mapa(bar, 0u));
+        else ptx::mbar_arrive(bar);
+      }
+    };
+    for (int unit = first_unit; unit < unit_end; unit += unit_step) {
+      uint32_t tile, split;
+      int real_unit;
+      bool phantom;
+      unit_map(unit, tile, split, real_unit, phantom);
       if (Tr::kSplit3) {
         // fp32: split every stage of this unit into hi / lo before the MMA warp may consume it
         int n_it = p.kiters;
@@ -452,20 +513,22 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (et < 32) ptx::mbar_wait(ptx::smem_u32(tfull_bar + as), aphase);
         asm volatile("bar.sync 2, 256;" ::: "memory");
         ptx::tc_fence_after();
-        if (et == 0 && unit == (int)blockIdx.x) SLIDER_TRACE(5);
+        if (et == 0 && unit == first_unit) SLIDER_TRACE(5);
         const uint32_t t_acc = tmem_base + ((uint32_t)(q * 32) << 16) + as * ACC_COLS;
         const bool park_h = grp == 0 && R4 > 0;                    // group 0 also parks the h columns
         uint32_t v[PCPG][PCW];
         uint32_t hr[16];
 #pragma unroll
-        for (int ci = 0; ci < PCPG; ++ci) tmem_ld_cols<PCW>(t_acc + (grp * PCPG + ci) * PCW, v[ci]);
-        if (park_h) ptx::tmem_ld_x16(t_acc + BN, hr);
+        for (int ci = 0; ci < PCPG; ++ci) tmem_ld_cols<PCW>(t_acc + grp_col + ci * PCW, v[ci]);
+        if (park_h) {
+          if (TWO) { ptx::tmem_ld_x8(t_acc + HALF_N, hr); ptx::tmem_ld_x8(t_acc + BN + HCOLS / 2, hr + 8); }
+          else ptx::tmem_ld_x16(t_acc + BN, hr);
+        }
         ptx::tmem_ld_wait();
         // the accumulator stage is free again as soon as it sits in registers
-        ptx::tc_fence_before();
-        __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(tempty_bar + as));
+        tempty_arrive(as);
         if (++as == ACC_STAGES) { as = 0; aphase ^= 1; }
+        if (TWO && phantom) continue;                               // uniform over the CTA: nothing to park
 #pragma unroll
         for (int ci = 0; ci <= PCPG; ++ci) {
           if (ci == PCPG && !park_h) break;
@@ -485,15 +548,15 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           if (gt == 0) ptx::bulk_wait_read<NB - 2>();   // buffer of chunk c+1 (last read by store c+1-NB) is free past the barrier
           SLIDER_GROUP_BAR();
           if (gt == 0) {
-            ptx::tma_store_2d(&tmP, out_base + ob * OUT_BYTES, 0, (unit * NCHUNK + chunk) * BM);
+            ptx::tma_store_2d(&tmP, out_base + ob * OUT_BYTES, 0, (real_unit * NCHUNK + chunk) * BM);
             ptx::bulk_commit();
           }
           if (++ob == (uint32_t)NB) ob = 0;
         }
-        if (et == 0 && unit == (int)blockIdx.x) SLIDER_TRACE(6);
+        if (et == 0 && unit == first_unit) SLIDER_TRACE(6);
         continue;
       }
-      const TileCoord tc = tile_coord<BN>(p, unit);
+      const TileCoord tc = tile_coord<BN>(p, (int)tile);
       // stage s*Bup[n0.., :] and bias[n0..] for this tile (fp32) while the MMAs run
       asm volatile("bar.sync 2, 256;" ::: "memory");
       for (int i = et; i < BN; i += kEpiThreads) {
@@ -512,25 +575,25 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       if (et < 32) ptx::mbar_wait(ptx::smem_u32(tfull_bar + as), aphase);
       asm volatile("bar.sync 2, 256;" ::: "memory");
       ptx::tc_fence_after();
-      if (et == 0 && unit == (int)blockIdx.x) SLIDER_TRACE(5);
+      if (et == 0 && unit == first_unit) SLIDER_TRACE(5);
       const uint32_t t_main = tmem_base + ((uint32_t)(q * 32) << 16) + as * ACC_COLS;
 
       // every TMEM read of this tile, back to back, ONE wait; then the stage goes back to the MMA warp
       uint32_t v[CPG][CW];
       uint32_t hr[16];
 #pragma unroll
-      for (int ci = 0; ci < CPG; ++ci) tmem_ld_cols<CW>(t_main + grp * HALF_N + ci * CW, v[ci]);
+      for (int ci = 0; ci < CPG; ++ci) tmem_ld_cols<CW>(t_main + grp_col + ci * CW, v[ci]);
       if (R4 > 0) {
         // grouped adapters: this tile's group owns `rank` of the 16 h columns, starting at its offset
         const int hoff = p.group_n > 0 ? (tc.n0 / p.group_n) * p.rank : 0;
-        ptx::tmem_ld_x16(t_main + BN + hoff, hr);
+        if (!TWO) ptx::tmem_ld_x16(t_main + BN + hoff, hr);
+        else if (R4 > 2) { ptx::tmem_ld_x8(t_main + HALF_N, hr); ptx::tmem_ld_x8(t_main + BN + HCOLS / 2, hr + 8); }
+        else ptx::tmem_ld_x8(t_main + (hoff < HCOLS / 2 ? HALF_N + hoff : BN + hoff), hr);   // host: a group's h never straddles
       }
       ptx::tmem_ld_wait();
-      ptx::tc_fence_before();
-      __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(tempty_bar + as));
+      tempty_arrive(as);
       if (++as == ACC_STAGES) { as = 0; aphase ^= 1; }
-      if (et == 0 && unit == (int)blockIdx.x) SLIDER_TRACE(9);
+      if (et == 0 && unit == first_unit) SLIDER_TRACE(9);
 
       float hv[R4 > 0 ? 4 * R4 : 1];
       if (R4 > 0) {
@@ -590,7 +653,7 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             if (++ob == (uint32_t)NB) ob = 0;
           }
         }
-        if (et == 0 && unit == (int)blockIdx.x) SLIDER_TRACE(6);
+        if (et == 0 && unit == first_unit) SLIDER_TRACE(6);
         continue;
       }
 #pragma unroll
@@ -641,7 +704,7 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
         if (++ob == (uint32_t)NB) ob = 0;
       }
-      if (et == 0 && unit == (int)blockIdx.x) SLIDER_TRACE(6);
+      if (et == 0 && unit == first_unit) SLIDER_TRACE(6);
     }
     if (gt == 0) ptx::bulk_wait_all();    // all TMA stores of this group have landed before the CTA exits
 #undef SLIDER_GROUP_BAR
@@ -649,9 +712,14 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   ptx::tc_fence_before();
   __syncthreads();
+  if (TWO) {      // the peer may still signal this CTA's barriers / the leader's MMAs may still read its operands
+    ptx::cluster_arrive();
+    ptx::cluster_wait();
+  }
   if (warp == 1) {
     ptx::tc_fence_after();
-    ptx::tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+    if (TWO) ptx::tmem_dealloc_2cta(tmem_base, Cfg::TMEM_COLS);
+    else ptx::tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
   }
   if (threadIdx.x == 0) SLIDER_TRACE(7);
 #undef SLIDER_TRACE
@@ -812,7 +880,7 @@ splitk_finalize_kernel(const GemmParams p) {
 // ---------------------------------------------------------------------------------------------
 // Launch of one tile width (explicitly instantiated in lora_gemm_bn160.cu / lora_gemm_bn80.cu so that the two sets of
 // kernels compile in parallel).
-template <typename T, int BN>
+template <typename T, int BN, bool TWO>
 static int launch_gemm_t(int r4, const CUtensorMap& a, const CUtensorMap& w, const CUtensorMap& l,
                          const CUtensorMap& xe, const CUtensorMap& we, const CUtensorMap& my, const CUtensorMap& mp,
                          const GemmParams& p, cudaStream_t st) {
@@ -821,10 +889,10 @@ static int launch_gemm_t(int r4, const CUtensorMap& a, const CUtensorMap& w, con
                GemmParams) = nullptr;
   void (*fin)(GemmParams) = nullptr;
   switch (r4) {
-    case 0: kern = lora_gemm_kernel<T, 0, BN>; fin = splitk_finalize_kernel<T, 0, BN>; break;
-    case 1: kern = lora_gemm_kernel<T, 1, BN>; fin = splitk_finalize_kernel<T, 1, BN>; break;
-    case 2: kern = lora_gemm_kernel<T, 2, BN>; fin = splitk_finalize_kernel<T, 2, BN>; break;
-    default: kern = lora_gemm_kernel<T, 4, BN>; fin = splitk_finalize_kernel<T, 4, BN>; break;
+    case 0: kern = lora_gemm_kernel<T, 0, BN, TWO>; fin = splitk_finalize_kernel<T, 0, BN>; break;
+    case 1: kern = lora_gemm_kernel<T, 1, BN, TWO>; fin = splitk_finalize_kernel<T, 1, BN>; break;
+    case 2: kern = lora_gemm_kernel<T, 2, BN, TWO>; fin = splitk_finalize_kernel<T, 2, BN>; break;
+    default: kern = lora_gemm_kernel<T, 4, BN, TWO>; fin = splitk_finalize_kernel<T, 4, BN>; break;
   }
   static thread_local const void* configured[8] = {nullptr};
   bool done = false;
@@ -833,8 +901,24 @@ static int launch_gemm_t(int r4, const CUtensorMap& a, const CUtensorMap& w, con
     SLIDER_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::smem_bytes(r4)));
     for (auto& c : configured) if (c == nullptr) { c = (const void*)kern; break; }
   }
-  const int grid = p.total_units < sm_count() ? p.total_units : sm_count();
-  launch_pdl(kern, dim3(grid), dim3(kGemmThreads), Cfg::smem_bytes(r4), st, a, w, l, xe, we, my, mp, p);
+  if (TWO) {
+    // one cluster of 2 per pair of SMs; a pair walks the pair units
+    const int pairs = p.pair_units < sm_count() / 2 ? p.pair_units : sm_count() / 2;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * pairs); cfg.blockDim = dim3(kGemmThreads);
+    cfg.dynamicSmemBytes = Cfg::smem_bytes(r4); cfg.stream = st;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 2 : 1;
+    cudaLaunchKernelEx(&cfg, kern, a, w, l, xe, we, my, mp, p);
+  } else {
+    const int grid = p.total_units < sm_count() ? p.total_units : sm_count();
+    launch_pdl(kern, dim3(grid), dim3(kGemmThreads), Cfg::smem_bytes(r4), st, a, w, l, xe, we, my, mp, p);
+  }
   int rc = post_launch("lora_gemm_kernel");
   if (rc || p.ksplit == 1) return rc;
   const long long threads = (long long)p.total_tiles * BM * (BN / 8);
@@ -846,8 +930,13 @@ template <int BN>
 int launch_gemm_tile(int dtype, int r4, const CUtensorMap& a, const CUtensorMap& w, const CUtensorMap& l,
                      const CUtensorMap& xe, const CUtensorMap& we, const CUtensorMap& my, const CUtensorMap& mp,
                      const GemmParams& p, cudaStream_t st) {
-  if (dtype == SLIDER_BF16) return launch_gemm_t<__nv_bfloat16, BN>(r4, a, w, l, xe, we, my, mp, p, st);
-  return launch_gemm_t<float, BN>(r4, a, w, l, xe, we, my, mp, p, st);
+  if (dtype == SLIDER_BF16) return launch_gemm_t<__nv_bfloat16, BN, false>(r4, a, w, l, xe, we, my, mp, p, st);
+  return launch_gemm_t<float, BN, false>(r4, a, w, l, xe, we, my, mp, p, st);
 }
+
+// CTA-pair form: bf16 storage, 128 x 160 tiles (instantiated in lora_gemm_pair.cu)
+int launch_gemm_pair(int r4, const CUtensorMap& a, const CUtensorMap& w, const CUtensorMap& l, const CUtensorMap& xe,
+                     const CUtensorMap& we, const CUtensorMap& my, const CUtensorMap& mp, const GemmParams& p,
+                     cudaStream_t st);
 
 }  // namespace slider

@@ -233,3 +233,110 @@ def test_narrow_tile_equals_wide_tile(case, dtype):
     finally:
         fn(-1)
         depth(0)
+
+
+def _pair_switch():
+    import ctypes
+    from sliders_conceptmod_b200 import _lib
+    fn = _lib.lib().slider_debug_pair
+    fn.argtypes, fn.restype = [ctypes.c_int], ctypes.c_int
+    depth = _lib.lib().slider_debug_splitk_depth
+    depth.argtypes, depth.restype = [ctypes.c_int], ctypes.c_int
+    return fn, depth
+
+
+PAIR_CASES = [
+    # B, H, W, Cin, Cout, k, rank
+    (1, 1, 2048, 1280, 1280, 1, 4),      # SD-XL to_out: 16 x 8 tiles
+    (1, 1, 8192, 640, 640, 1, 4),
+    (2, 64, 64, 320, 320, 3, 4),
+    (1, 1, 384, 128, 160, 1, 4),         # 3 pixel tiles: odd count -> phantom tile in the last pair
+    (1, 1, 300, 64, 72, 1, 8),           # ragged rows and columns
+    (3, 24, 40, 64, 200, 3, 16),         # rank 16: h columns in both halves; ragged last N tile
+    (2, 32, 32, 640, 640, 3, 4),
+    (1, 1, 640, 320, 320, 1, 0),         # no adapter
+]
+
+
+@pytest.mark.parametrize("case", PAIR_CASES)
+def test_cta_pair_form_equals_single_cta_form(case):
+    """lora_gemm_kernel in CTA-pair form (cluster of 2, cta_group::2: each CTA stages half of the weight rows, the
+    leader issues M = 256 MMAs) vs the single-CTA form: same MMAs per output element in the same K order -> without
+    split-K bit-identical y and h; also with a residual store, adapter off, stride 2 and split-K (tolerance)."""
+    from sliders_conceptmod_b200 import ops
+    pair, depth = _pair_switch()
+    B, H, W, C, N, k, r = case
+    dtype = torch.bfloat16
+    g = torch.Generator().manual_seed(sum(case))
+    lin = k == 1 and B == 1 and H == 1
+    x = torch.randn(*((W, C) if lin else (B, H, W, C)), generator=g).cuda().to(dtype)
+    w = (torch.randn(N, k * k, C, generator=g) / (C * k * k) ** 0.5).cuda().to(dtype)
+    a = (torch.randn(r, k * k, C, generator=g) / (C * k * k) ** 0.5).cuda().to(dtype) if r else None
+    b = (torch.randn(N, r, generator=g) * 0.3).cuda().to(dtype) if r else None
+    bias = torch.randn(N, generator=g).cuda().to(dtype)
+    res = torch.randn(*x.shape[:-1], N, generator=g).cuda().to(dtype)
+    s = 0.7 if r else 0.0
+    try:
+        depth(1 << 20)
+        pair(0)
+        y1, h1 = ops.lora_forward(x, w, bias, a, b, s, ksize=k, want_h=bool(r))
+        y1r, _ = ops.lora_forward(x, w, bias, a, b, s, ksize=k, residual=res.clone())
+        y1o, _ = ops.lora_forward(x, w, bias, a, b, 0.0, ksize=k)
+        pair(1)
+        y2, h2 = ops.lora_forward(x, w, bias, a, b, s, ksize=k, want_h=bool(r))
+        y2r, _ = ops.lora_forward(x, w, bias, a, b, s, ksize=k, residual=res.clone())
+        y2o, _ = ops.lora_forward(x, w, bias, a, b, 0.0, ksize=k)
+        torch.cuda.synchronize()
+        assert torch.equal(y1, y2), f"y differs: {(y1.float() - y2.float()).abs().max().item()}"
+        if r:
+            assert torch.equal(h1, h2)
+        assert torch.equal(y1r, y2r) and torch.equal(y1o, y2o)
+        if k == 3:
+            pair(0)
+            ys1, hs1 = ops.lora_forward(x, w, bias, a, b, s, ksize=3, want_h=True, stride=2)
+            pair(1)
+            ys2, hs2 = ops.lora_forward(x, w, bias, a, b, s, ksize=3, want_h=True, stride=2)
+            assert torch.equal(ys1, ys2) and torch.equal(hs1, hs2)
+        depth(0)                            # default split-K plan under the pair form: summation order changes
+        y3, _ = ops.lora_forward(x, w, bias, a, b, s, ksize=k)
+        assert (y3.float() - y1.float()).abs().max().item() <= 2e-2 * y1.float().abs().max().item()
+    finally:
+        pair(-1)
+        depth(0)
+
+
+def test_cta_pair_form_grouped_geglu_and_fused_backward():
+    """The other callers of the wide tile under the pair form: grouped q/k/v (SD-XL shape), the GEGLU store, the fused
+    1x1 backward (lora_up read as lora_down^T)."""
+    from sliders_conceptmod_b200 import ops
+    pair, depth = _pair_switch()
+    dtype = torch.bfloat16
+    g = torch.Generator().manual_seed(5)
+    M, K, Ng, r = 2048, 1280, 1280, 4
+    x = torch.randn(M, K, generator=g).cuda().to(dtype)
+    W = (torch.randn(3 * Ng, 1, K, generator=g) / K ** 0.5).cuda().to(dtype)
+    A = (torch.randn(3 * r, 1, K, generator=g) / K ** 0.5).cuda().to(dtype)
+    Bm = (torch.randn(3 * Ng, r, generator=g) * 0.3).cuda().to(dtype)
+    D = 640
+    wg = (torch.randn(2 * D, K, generator=g) / K ** 0.5).cuda().to(dtype)
+    bg = torch.randn(2 * D, generator=g).cuda().to(dtype)
+    idx = ops.geglu_permutation(D, "cuda")
+    wgp, bgp = wg.index_select(0, idx).contiguous(), bg.index_select(0, idx).contiguous()
+    gy = torch.randn(M, Ng, generator=g).cuda().to(dtype)
+    w1, a1, b1 = W[:Ng].contiguous(), A[:r].contiguous(), Bm[:Ng].contiguous()
+    wt = ops.pack_wt(w1, 1)
+    outs = []
+    try:
+        depth(1 << 20)
+        for mode in (0, 1):
+            pair(mode)
+            yq = ops.lora_forward_grouped(x, W, A, Bm, 3, 0.6)
+            yg = ops.linear_geglu(x, wgp, bgp)
+            dx, gb = ops.lora_backward_1x1(gy, None, None, wt, a1, b1, 0.5, None, None, return_g=True)
+            outs.append((yq, yg, dx, gb))
+        torch.cuda.synchronize()
+        for t0, t1, name in zip(outs[0], outs[1], ("grouped", "geglu", "dx", "g")):
+            assert torch.equal(t0, t1), f"{name}: {(t0.float() - t1.float()).abs().max().item()}"
+    finally:
+        pair(-1)
+        depth(0)
