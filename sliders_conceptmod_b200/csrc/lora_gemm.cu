@@ -421,7 +421,11 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
   // CTA pairs: bf16, wide tile, forward geometry; a grouped launch's h columns must not straddle the two halves
   bool pair = g_pair != 0 && g->dtype == SLIDER_BF16 && bn == 160 && !ext && m_tiles >= 2 &&
               (groups == 1 || (g->rank <= 8 && 8 % (g->rank > 0 ? g->rank : 1) == 0));
-  if (pair && g_pair < 0) pair = p.total_tiles >= 2 * sm_count();       // L2-bound regime: several waves of tiles
+  // measured per signature (profiles/r02_ab_pair.txt): the pair form gains 5-15 % on the 3x3 convolutions with >= 8
+  // pixel tiles and 7 % on the SD-XL q/k/v launch (20 K blocks, 384 tiles); its cluster start-up / tear-down costs
+  // 1-1.5 us, which loses on launches with a handful of K blocks
+  if (pair && g_pair < 0)
+    pair = (taps == 9 && m_tiles >= 8) || (taps * p.cblocks >= 18 && p.total_tiles >= 2 * sm_count());
   p.per_tap = p.cblocks + (ext ? 1 : 0);
   p.kiters = taps * p.per_tap;
   // split-K when the tile count leaves more than half of the SMs idle and K is deep enough
@@ -449,7 +453,6 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
     }
   }
   p.total_units = p.total_tiles * p.ksplit;
-  if (p.ksplit > 1 && g_pair < 0) pair = false;
   p.pair_units = p.n_tiles * ((m_tiles + 1) / 2) * p.ksplit;
   p.fd_n_tiles = FastDiv::make((uint32_t)p.n_tiles);
   p.fd_mt_w = FastDiv::make((uint32_t)p.mt_w);
