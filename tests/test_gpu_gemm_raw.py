@@ -210,6 +210,9 @@ def test_narrow_tile_equals_wide_tile(case, dtype):
     fn.argtypes, fn.restype = [ctypes.c_int], ctypes.c_int
     depth = _lib.lib().slider_debug_splitk_depth
     depth.argtypes, depth.restype = [ctypes.c_int], ctypes.c_int
+    pair = _lib.lib().slider_debug_pair         # the pair form of the wide tile has its own epilogue arithmetic
+    pair.argtypes, pair.restype = [ctypes.c_int], ctypes.c_int
+    pair(0)
     B, H, W, C, N, k, r = case
     g = torch.Generator().manual_seed(sum(case))
     lin = k == 1 and B == 1 and H == 1
@@ -233,6 +236,7 @@ def test_narrow_tile_equals_wide_tile(case, dtype):
     finally:
         fn(-1)
         depth(0)
+        pair(-1)
 
 
 def _pair_switch():
@@ -287,16 +291,20 @@ def test_cta_pair_form_equals_single_cta_form(case):
         y2r, _ = ops.lora_forward(x, w, bias, a, b, s, ksize=k, residual=res.clone())
         y2o, _ = ops.lora_forward(x, w, bias, a, b, 0.0, ksize=k)
         torch.cuda.synchronize()
-        assert torch.equal(y1, y2), f"y differs: {(y1.float() - y2.float()).abs().max().item()}"
+        # the MMAs are identical (h and the adapter-off result agree bit for bit); with the adapter on the single-CTA
+        # form adds bias + s*h.B^T through one more bf16 MMA while the pair form adds them in fp32 registers
+        scale = y1.float().abs().max().item()
+        same = lambda u, t: (u.float() - t.float()).abs().max().item() <= (0.0 if (r == 0 or r > 8) else 1e-2 * scale)
+        assert same(y1, y2), f"y differs: {(y1.float() - y2.float()).abs().max().item()}"
         if r:
             assert torch.equal(h1, h2)
-        assert torch.equal(y1r, y2r) and torch.equal(y1o, y2o)
+        assert same(y1r, y2r) and torch.equal(y1o, y2o)
         if k == 3:
             pair(0)
             ys1, hs1 = ops.lora_forward(x, w, bias, a, b, s, ksize=3, want_h=True, stride=2)
             pair(1)
             ys2, hs2 = ops.lora_forward(x, w, bias, a, b, s, ksize=3, want_h=True, stride=2)
-            assert torch.equal(ys1, ys2) and torch.equal(hs1, hs2)
+            assert same(ys1, ys2) and torch.equal(hs1, hs2)
         depth(0)                            # default split-K plan under the pair form: summation order changes
         y3, _ = ops.lora_forward(x, w, bias, a, b, s, ksize=k)
         assert (y3.float() - y1.float()).abs().max().item() <= 2e-2 * y1.float().abs().max().item()
@@ -336,7 +344,9 @@ def test_cta_pair_form_grouped_geglu_and_fused_backward():
             outs.append((yq, yg, dx, gb))
         torch.cuda.synchronize()
         for t0, t1, name in zip(outs[0], outs[1], ("grouped", "geglu", "dx", "g")):
-            assert torch.equal(t0, t1), f"{name}: {(t0.float() - t1.float()).abs().max().item()}"
+            d = (t0.float() - t1.float()).abs().max().item()
+            exact = name in ("geglu", "g")      # no adapter epilogue / the fp32 h output: identical MMAs
+            assert d <= (0.0 if exact else 1e-2 * t0.float().abs().max().item()), f"{name}: {d}"
     finally:
         pair(-1)
         depth(0)

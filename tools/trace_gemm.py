@@ -10,7 +10,7 @@ dt, r, s = torch.bfloat16, 4, 0.25
 if "--nosplit" in sys.argv:
     _lib.lib().slider_debug_splitk_depth(1000000)
 names = ["setup", "first_tma_issue", "first_full", "last_mma_commit", "acc_visible", "epi_done", "exit",
-         "prod_ready", "after_tma_A", "after_tma_W", "cluster_synced", "cluster_reduced"]
+         "prod_ready", "tmem_in_regs", "chunk0_math_sts", "chunk0_fence", "chunk0_group_bar"]
 for (B, H, W, C, N, k) in shapes:
     x = torch.randn(B, H, W, C, device="cuda", dtype=dt)
     w = (torch.randn(N, k * k, C, device="cuda") / (C * k * k) ** 0.5).to(dt)
