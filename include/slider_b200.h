@@ -28,7 +28,9 @@ extern "C" {
 
 #define SLIDER_ABI_VERSION 3
 
-enum slider_dtype { SLIDER_F32 = 0, SLIDER_BF16 = 1 };
+/* SLIDER_F16: forward / inference entry points only (the reference's inference scripts run in fp16,
+ * eval-scripts/generate_images_xl.py:443); the training entry points return SLIDER_ERR_UNSUPPORTED for it. */
+enum slider_dtype { SLIDER_F32 = 0, SLIDER_BF16 = 1, SLIDER_F16 = 2 };
 
 enum slider_status {
   SLIDER_OK = 0,

@@ -13,7 +13,7 @@ import torch
 PKG_DIR = Path(__file__).resolve().parent
 LIB_PATH = PKG_DIR / "libslider_b200.so"
 
-SLIDER_F32, SLIDER_BF16 = 0, 1
+SLIDER_F32, SLIDER_BF16, SLIDER_F16 = 0, 1, 2
 
 
 class LayerGeom(C.Structure):
@@ -100,7 +100,9 @@ def dtype_code(dt: torch.dtype) -> int:
         return SLIDER_F32
     if dt == torch.bfloat16:
         return SLIDER_BF16
-    raise TypeError(f"libslider_b200 supports float32 and bfloat16, got {dt}")
+    if dt == torch.float16:      # forward / inference entry points only; the training entry points reject it
+        return SLIDER_F16
+    raise TypeError(f"libslider_b200 supports float32, bfloat16 and (inference) float16, got {dt}")
 
 
 def ptr(t: torch.Tensor | None):

@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <stdarg.h>
@@ -81,6 +82,10 @@ template <> struct Elem<float> {
   }
   __device__ static inline float to_f(float x) { return x; }
   __device__ static inline float from_f(float x) { return x; }
+  // 16-bit pair helpers: unused for fp32 (present so that dtype-generic code compiles)
+  __device__ static inline uint32_t pack2(float a, float) { return __float_as_uint(a); }
+  __device__ static inline void unpack2(uint32_t w, float& a, float& b) { a = __uint_as_float(w); b = 0.f; }
+  __device__ static inline float round(float x) { return x; }
 };
 template <> struct Elem<__nv_bfloat16> {
   static constexpr int kVec = 8;
@@ -104,6 +109,40 @@ template <> struct Elem<__nv_bfloat16> {
   }
   __device__ static inline float to_f(__nv_bfloat16 x) { return __bfloat162float(x); }
   __device__ static inline __nv_bfloat16 from_f(float x) { return __float2bfloat16_rn(x); }
+  __device__ static inline uint32_t pack2(float a, float b) {
+    const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<const uint32_t*>(&h);
+  }
+  __device__ static inline void unpack2(uint32_t w, float& a, float& b) {
+    a = __uint_as_float(w << 16); b = __uint_as_float(w & 0xffff0000u);
+  }
+  __device__ static inline float round(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
+};
+template <> struct Elem<__half> {
+  static constexpr int kVec = 8;
+  __device__ static inline uint32_t pack2(float a, float b) {
+    const __half2 h = __floats2half2_rn(a, b);
+    return *reinterpret_cast<const uint32_t*>(&h);
+  }
+  __device__ static inline void unpack2(uint32_t w, float& a, float& b) {
+    const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w));
+    a = f.x; b = f.y;
+  }
+  __device__ static inline float round(float x) { return __half2float(__float2half_rn(x)); }
+  __device__ static inline void load(const __half* p, float (&v)[8]) {
+    const uint4 t = *reinterpret_cast<const uint4*>(p);
+    const uint32_t w[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) unpack2(w[i], v[2 * i], v[2 * i + 1]);
+  }
+  __device__ static inline void store(__half* p, const float (&v)[8]) {
+    uint32_t w[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) w[i] = pack2(v[2 * i], v[2 * i + 1]);
+    *reinterpret_cast<uint4*>(p) = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+  __device__ static inline float to_f(__half x) { return __half2float(x); }
+  __device__ static inline __half from_f(float x) { return __float2half_rn(x); }
 };
 
 // erf for bf16 outputs: Abramowitz-Stegun 7.1.26 (|error| <= 1.5e-7, three orders below a bf16 ulp) on the fast

@@ -344,6 +344,11 @@ int slider_cfg_step(void* out, const void* x, const void* eps_u, const void* eps
     const int grid = grid_for(n_elem / 8, 2);
     launch_pdl(cfg_step_kernel<T>, dim3(grid), dim3(kThreads), 0, st, (T*)out, (const T*)x, (const T*)eps_u,
                (const T*)eps_c, (const T*)noise, n_elem, g, c_x, c_eps, c_noise, dev_coef);
+  } else if (dtype == SLIDER_F16) {
+    typedef __half T;
+    const int grid = grid_for(n_elem / 8, 2);
+    launch_pdl(cfg_step_kernel<T>, dim3(grid), dim3(kThreads), 0, st, (T*)out, (const T*)x, (const T*)eps_u,
+               (const T*)eps_c, (const T*)noise, n_elem, g, c_x, c_eps, c_noise, dev_coef);
   } else {
     set_error("cfg_step: unsupported dtype %d", dtype);
     return SLIDER_ERR_UNSUPPORTED;

@@ -35,6 +35,10 @@ template <> struct Vec8<__nv_bfloat16> {
   __device__ static inline void load(const __nv_bfloat16* p, float (&v)[8]) { Elem<__nv_bfloat16>::load(p, v); }
   __device__ static inline void store(__nv_bfloat16* p, const float (&v)[8]) { Elem<__nv_bfloat16>::store(p, v); }
 };
+template <> struct Vec8<__half> {
+  __device__ static inline void load(const __half* p, float (&v)[8]) { Elem<__half>::load(p, v); }
+  __device__ static inline void store(__half* p, const float (&v)[8]) { Elem<__half>::store(p, v); }
+};
 template <> struct Vec8<float> {
   __device__ static inline void load(const float* p, float (&v)[8]) {
     const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
@@ -230,6 +234,11 @@ template <> struct Word<__nv_bfloat16> {
     const __nv_bfloat162 h = __floats2bfloat162_rn(f[0], f[1]);
     return *reinterpret_cast<const uint32_t*>(&h);
   }
+};
+template <> struct Word<__half> {
+  static constexpr int N = 2;
+  __device__ static inline void unpack(uint32_t w, float (&f)[2]) { Elem<__half>::unpack2(w, f[0], f[1]); }
+  __device__ static inline uint32_t pack(const float (&f)[2]) { return Elem<__half>::pack2(f[0], f[1]); }
 };
 template <> struct Word<float> {
   static constexpr int N = 1;
@@ -788,7 +797,7 @@ int slider_debug_gn_group_plan(int hw, int channels, int groups, int dtype, int*
   GnParams p = {};
   p.B = 1; p.HW = hw; p.C = channels; p.G = groups; p.cpg = channels / groups;
   GnGroupPlan gp;
-  const bool ok = dtype == SLIDER_BF16 ? gn_group_plan<__nv_bfloat16>(p, &gp) : gn_group_plan<float>(p, &gp);
+  const bool ok = dtype == SLIDER_F32 ? gn_group_plan<float>(p, &gp) : gn_group_plan<__nv_bfloat16>(p, &gp);   // 16-bit types share the plan
   if (!ok) return 0;
   out[0] = gp.a.k; out[1] = gp.a.gp; out[2] = gp.a.wr; out[3] = gp.a.rows; out[4] = gp.threads; out[5] = (int)gp.smem;
   return 1;
@@ -825,6 +834,7 @@ int slider_groupnorm_nhwc(void* y, const void* x, const void* chan_add, const vo
   cudaStream_t st = (cudaStream_t)stream;
   if (dtype == SLIDER_BF16) return groupnorm_impl<__nv_bfloat16>(y, x, chan_add, gamma, beta, (float*)ws, p, st);
   if (dtype == SLIDER_F32) return groupnorm_impl<float>(y, x, chan_add, gamma, beta, (float*)ws, p, st);
+  if (dtype == SLIDER_F16) return groupnorm_impl<__half>(y, x, chan_add, gamma, beta, (float*)ws, p, st);
   set_error("groupnorm: unsupported dtype %d", dtype);
   return SLIDER_ERR_UNSUPPORTED;
 }

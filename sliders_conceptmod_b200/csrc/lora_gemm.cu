@@ -28,6 +28,11 @@ template <> __device__ inline void Raw16<__nv_bfloat16>::unpack(const uint4& t, 
 #pragma unroll
   for (int i = 0; i < 4; ++i) { v[2 * i] = __uint_as_float(w[i] << 16); v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u); }
 }
+template <> __device__ inline void Raw16<__half>::unpack(const uint4& t, float (&v)[8]) {
+  const uint32_t w[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) Elem<__half>::unpack2(w[i], v[2 * i], v[2 * i + 1]);
+}
 template <> __device__ inline void Raw16<float>::unpack(const uint4& t, float (&v)[4]) {
   v[0] = __uint_as_float(t.x); v[1] = __uint_as_float(t.y); v[2] = __uint_as_float(t.z); v[3] = __uint_as_float(t.w);
 }
@@ -312,7 +317,7 @@ static TileGeom choose_tile(int W, int H, int B) {
   return t;
 }
 
-static inline int esize(int dtype) { return dtype == SLIDER_BF16 ? 2 : 4; }
+static inline int esize(int dtype) { return dtype == SLIDER_F32 ? 4 : 2; }
 
 template <typename T>
 static int launch_gemv(const slider_layer_geom* g, int M, void* y, const void* x, const void* W, const void* bias,
@@ -348,7 +353,8 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
   const int taps = g->kh * g->kw;
   const int bk = ROW_BYTES / es;
   const int stride = g->stride == 2 ? 2 : 1;
-  SLIDER_CHECK_ARG(g->dtype == SLIDER_BF16 || g->dtype == SLIDER_F32, "lora gemm: unsupported dtype %d", g->dtype);
+  SLIDER_CHECK_ARG(g->dtype == SLIDER_BF16 || g->dtype == SLIDER_F32 || g->dtype == SLIDER_F16, "lora gemm: unsupported dtype %d", g->dtype);
+  SLIDER_CHECK_ARG(g->dtype != SLIDER_F16 || xe == nullptr, "lora gemm: fp16 storage is forward / inference only");
   SLIDER_CHECK_ARG(g->kh == g->kw && (g->kh == 1 || g->kh == 3) && g->pad == (g->kh - 1) / 2,
                    "lora gemm: only 1x1/pad0 and 3x3/pad1 kernels (got %dx%d pad %d)", g->kh, g->kw, g->pad);
   SLIDER_CHECK_ARG(g->stride >= 0 && g->stride <= 2 && (stride == 1 || g->kh == 3),
@@ -384,6 +390,8 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
         !geglu && kc * es <= 8 * 32 * 16 && ((uintptr_t)wgt & 15) == 0 && (lo == nullptr || ((uintptr_t)lo & 15) == 0)) {
       if (g->dtype == SLIDER_BF16)
         return launch_gemv<__nv_bfloat16>(g, (int)M, y, act, wgt, bias, lo, Bup, lora ? h_out : nullptr, s, lora, st);
+      if (g->dtype == SLIDER_F16)
+        return launch_gemv<__half>(g, (int)M, y, act, wgt, bias, lo, Bup, lora ? h_out : nullptr, s, lora, st);
       return launch_gemv<float>(g, (int)M, y, act, wgt, bias, lo, Bup, lora ? h_out : nullptr, s, lora, st);
     }
   }
@@ -521,6 +529,7 @@ static int run_gemm(const slider_layer_geom* g, int kc, int nn, void* y, const v
     if (!(mP = cached_tmap(SLIDER_F32, 2, ws, dims, str, box, OUT_ROW_BYTES))) return SLIDER_ERR_CUDA;
   }
   const int r4 = !lora ? 0 : (g->rank <= 4 ? 1 : (g->rank <= 8 ? 2 : 4));
+  if (g->dtype == SLIDER_F16) return launch_gemm_f16(bn, r4, *mA, *mW, *mL, *mXe, *mWe, *mY, *mP, p, st);
   if (pair) return launch_gemm_pair(r4, *mA, *mW, *mL, *mXe, *mWe, *mY, *mP, p, st);
   if (bn == 160) return launch_gemm_tile<160>(g->dtype, r4, *mA, *mW, *mL, *mXe, *mWe, *mY, *mP, p, st);
   return launch_gemm_tile<80>(g->dtype, r4, *mA, *mW, *mL, *mXe, *mWe, *mY, *mP, p, st);
@@ -605,7 +614,7 @@ int slider_lora_forward_grouped(const slider_layer_geom* g, void* y, const void*
 int slider_lora_forward_small_multi(int dtype, int layers, int M, int K, int rank, const void* x, void* const* y,
                                     const void* const* W, const void* const* bias, const void* const* A,
                                     const void* const* B, const int* N, const float* s, void* stream) {
-  SLIDER_CHECK_ARG(dtype == SLIDER_BF16 || dtype == SLIDER_F32, "lora_forward_small_multi: unsupported dtype %d", dtype);
+  SLIDER_CHECK_ARG(dtype == SLIDER_BF16 || dtype == SLIDER_F32 || dtype == SLIDER_F16, "lora_forward_small_multi: unsupported dtype %d", dtype);
   SLIDER_CHECK_ARG(layers >= 1 && layers <= GEMV_MAX_LAYERS, "lora_forward_small_multi: layers %d not in 1..%d", layers,
                    GEMV_MAX_LAYERS);
   SLIDER_CHECK_ARG(x && y && W && N && s, "lora_forward_small_multi: null pointer");
@@ -641,6 +650,7 @@ int slider_lora_forward_small_multi(int dtype, int layers, int M, int K, int ran
     mp.blk_end[l] = blocks;
   }
   if (dtype == SLIDER_BF16) return launch_gemv_multi<__nv_bfloat16>(mp, blocks, ch, x, M, K, rank, (cudaStream_t)stream);
+  if (dtype == SLIDER_F16) return launch_gemv_multi<__half>(mp, blocks, ch, x, M, K, rank, (cudaStream_t)stream);
   return launch_gemv_multi<float>(mp, blocks, ch, x, M, K, rank, (cudaStream_t)stream);
 }
 

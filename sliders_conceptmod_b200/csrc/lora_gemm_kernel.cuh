@@ -93,6 +93,15 @@ template <> struct GemmTraits<__nv_bfloat16> {
     ptx::mma_f16(d, a, b, idesc, acc);
   }
 };
+template <> struct GemmTraits<__half> {
+  static constexpr int kBK = 64;
+  static constexpr uint32_t kFmt = 0;  // f16
+  static constexpr int kExtRowBytes = EXT_ELEMS * 2;
+  static constexpr bool kSplit3 = false;
+  __device__ static inline void mma(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) {
+    ptx::mma_f16(d, a, b, idesc, acc);
+  }
+};
 template <> struct GemmTraits<float> {
   static constexpr int kBK = 32;
   static constexpr uint32_t kFmt = 2;  // tf32
@@ -587,8 +596,7 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               }
               e[u] = f;
             }
-            const __nv_bfloat162 h2 = __floats2bfloat162_rn(e[0], e[1]);
-            wv[k] = *reinterpret_cast<const uint32_t*>(&h2);
+            wv[k] = Elem<T>::pack2(e[0], e[1]);
           }
           // K-major rows of 32 bytes, 32-byte swizzle (16-byte chunk index ^= bit 2 of the row): the layout the
           // extended-K operand is landed in by TMA
@@ -628,8 +636,7 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               const int j = 2 * k + u;
               e[u] = j < p.rank ? __uint_as_float(hr[j]) : (j == p.rank ? 1.f : 0.f);
             }
-            const __nv_bfloat162 h2 = __floats2bfloat162_rn(e[0], e[1]);
-            av[k] = *reinterpret_cast<const uint32_t*>(&h2);
+            av[k] = Elem<T>::pack2(e[0], e[1]);
           }
           ptx::tmem_st_x8(t_fold, av);
           ptx::tmem_st_wait();
@@ -664,9 +671,8 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             uint32_t w[4];
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-              __nv_bfloat162 h2 = __floats2bfloat162_rn(__uint_as_float(v[ci][(pc * PW + 2 * k) % CW]),
-                                                        __uint_as_float(v[ci][(pc * PW + 2 * k + 1) % CW]));
-              w[k] = *reinterpret_cast<uint32_t*>(&h2);
+              w[k] = Elem<T>::pack2(__uint_as_float(v[ci][(pc * PW + 2 * k) % CW]),
+                                    __uint_as_float(v[ci][(pc * PW + 2 * k + 1) % CW]));
             }
             ptx::st_shared_v4(dst + pc * 16, w[0], w[1], w[2], w[3]);
           }
@@ -768,8 +774,7 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 uint32_t w[4];
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
-                  __nv_bfloat162 h2 = __floats2bfloat162_rn(o[(2 * k) % PW], o[(2 * k + 1) % PW]);
-                  w[k] = *reinterpret_cast<uint32_t*>(&h2);
+                  w[k] = Elem<T>::pack2(o[(2 * k) % PW], o[(2 * k + 1) % PW]);
                 }
                 ptx::st_shared_v4(dst + pc * 16, w[0], w[1], w[2], w[3]);
               } else {
@@ -836,8 +841,7 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             uint32_t w[4];
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-              __nv_bfloat162 h2 = __floats2bfloat162_rn(o[(2 * k) % PW], o[(2 * k + 1) % PW]);
-              w[k] = *reinterpret_cast<uint32_t*>(&h2);
+              w[k] = Elem<T>::pack2(o[(2 * k) % PW], o[(2 * k + 1) % PW]);
             }
             ptx::st_shared_v4(dst + pc * 16, w[0], w[1], w[2], w[3]);
           } else {
@@ -991,10 +995,13 @@ splitk_finalize_kernel(const GemmParams p) {
         float l = 0.f;
         if (kPackB && packb) {
           const uint2 q = bq[kPackB ? half * 4 + k : 0];
-          l = fmaf(hv[0], __uint_as_float(q.x << 16), l);
-          l = fmaf(hv[1 % (R4 > 0 ? 4 * R4 : 1)], __uint_as_float(q.x & 0xffff0000u), l);
-          l = fmaf(hv[2 % (R4 > 0 ? 4 * R4 : 1)], __uint_as_float(q.y << 16), l);
-          l = fmaf(hv[3 % (R4 > 0 ? 4 * R4 : 1)], __uint_as_float(q.y & 0xffff0000u), l);
+          float b0, b1, b2, b3;
+          Elem<T>::unpack2(q.x, b0, b1);
+          Elem<T>::unpack2(q.y, b2, b3);
+          l = fmaf(hv[0], b0, l);
+          l = fmaf(hv[1 % (R4 > 0 ? 4 * R4 : 1)], b1, l);
+          l = fmaf(hv[2 % (R4 > 0 ? 4 * R4 : 1)], b2, l);
+          l = fmaf(hv[3 % (R4 > 0 ? 4 * R4 : 1)], b3, l);
         } else {
 #pragma unroll
           for (int j = 0; j < 4 * R4; ++j)
@@ -1009,13 +1016,13 @@ splitk_finalize_kernel(const GemmParams p) {
       uint2* d2 = reinterpret_cast<uint2*>(dst);
       if (p.accumulate) {  // y holds the residual: same two roundings as `residual + module(x)` in element dtype
         const uint4 q = resq[half];
-        const float res[4] = {__uint_as_float(q.x << 16), __uint_as_float(q.x & 0xffff0000u),
-                              __uint_as_float(q.y << 16), __uint_as_float(q.y & 0xffff0000u)};
+        float res[4];
+        Elem<T>::unpack2(q.x, res[0], res[1]);
+        Elem<T>::unpack2(q.y, res[2], res[3]);
 #pragma unroll
-        for (int k = 0; k < 4; ++k) r[k] = __bfloat162float(__float2bfloat16_rn(r[k])) + res[k];
+        for (int k = 0; k < 4; ++k) r[k] = Elem<T>::round(r[k]) + res[k];
       }
-      __nv_bfloat162 lo2 = __floats2bfloat162_rn(r[0], r[1]), hi2 = __floats2bfloat162_rn(r[2], r[3]);
-      *d2 = make_uint2(*reinterpret_cast<uint32_t*>(&lo2), *reinterpret_cast<uint32_t*>(&hi2));
+      *d2 = make_uint2(Elem<T>::pack2(r[0], r[1]), Elem<T>::pack2(r[2], r[3]));
     } else {
       float4* d4 = reinterpret_cast<float4*>(dst);
       if (p.accumulate) {
@@ -1089,6 +1096,11 @@ int launch_gemm_tile(int dtype, int r4, const CUtensorMap& a, const CUtensorMap&
   if (dtype == SLIDER_BF16) return launch_gemm_t<__nv_bfloat16, BN, false>(r4, a, w, l, xe, we, my, mp, p, st);
   return launch_gemm_t<float, BN, false>(r4, a, w, l, xe, we, my, mp, p, st);
 }
+
+// fp16 storage (forward / inference): instantiated in lora_gemm_f16.cu
+int launch_gemm_f16(int bn, int r4, const CUtensorMap& a, const CUtensorMap& w, const CUtensorMap& l, const CUtensorMap& xe,
+                    const CUtensorMap& we, const CUtensorMap& my, const CUtensorMap& mp, const GemmParams& p,
+                    cudaStream_t st);
 
 // CTA-pair form: bf16 storage, 128 x 160 tiles (instantiated in lora_gemm_pair.cu)
 int launch_gemm_pair(int r4, const CUtensorMap& a, const CUtensorMap& w, const CUtensorMap& l, const CUtensorMap& xe,

@@ -52,7 +52,8 @@ inline int make_tmap(CUtensorMap* out, int dtype, int rank, const void* base, co
                           : inner_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
                           : inner_bytes == 32 ? CU_TENSOR_MAP_SWIZZLE_32B
                                               : CU_TENSOR_MAP_SWIZZLE_NONE;
-  CUtensorMapDataType dt = dtype == SLIDER_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+  CUtensorMapDataType dt = dtype == SLIDER_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
+                           : dtype == SLIDER_F16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
   CUresult r = fn(out, dt, (cuuint32_t)rank, const_cast<void*>(base), gdim, gstr, bdim, estr,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);

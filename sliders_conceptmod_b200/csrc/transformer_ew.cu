@@ -30,6 +30,17 @@ template <> struct VecIO<__nv_bfloat16> {
     return make_uint4(w[0], w[1], w[2], w[3]);
   }
 };
+template <> struct VecIO<__half> {
+  __device__ static inline void unpack(const uint4& t, float (&v)[8]) {
+    const uint32_t w[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) Elem<__half>::unpack2(w[i], v[2 * i], v[2 * i + 1]);
+  }
+  __device__ static inline uint4 pack(const float (&v)[8]) {
+    return make_uint4(Elem<__half>::pack2(v[0], v[1]), Elem<__half>::pack2(v[2], v[3]), Elem<__half>::pack2(v[4], v[5]),
+                      Elem<__half>::pack2(v[6], v[7]));
+  }
+};
 template <> struct VecIO<float> {
   __device__ static inline void unpack(const uint4& t, float (&v)[4]) {
     v[0] = __uint_as_float(t.x); v[1] = __uint_as_float(t.y); v[2] = __uint_as_float(t.z); v[3] = __uint_as_float(t.w);
@@ -312,8 +323,9 @@ int slider_layernorm_train(void* y, float* stats, const void* x, const void* gam
                    "layernorm: pointers must be 16-byte aligned");
   cudaStream_t st = (cudaStream_t)stream;
   const unsigned grid = (unsigned)((rows + 7) / 8);
-  if (dtype != SLIDER_BF16 && dtype != SLIDER_F32) { set_error("layernorm: unsupported dtype %d", dtype); return SLIDER_ERR_UNSUPPORTED; }
-  const int per_lane = (channels / (dtype == SLIDER_BF16 ? 8 : 4) + 31) / 32;      // 16-byte vectors per lane
+  if (dtype != SLIDER_BF16 && dtype != SLIDER_F32 && dtype != SLIDER_F16) { set_error("layernorm: unsupported dtype %d", dtype); return SLIDER_ERR_UNSUPPORTED; }
+  SLIDER_CHECK_ARG(dtype != SLIDER_F16 || stats == nullptr, "layernorm_train: fp16 storage is forward / inference only");
+  const int per_lane = (channels / (dtype == SLIDER_F32 ? 4 : 8) + 31) / 32;      // 16-byte vectors per lane
 #define SLIDER_LN_LAUNCH(KERNEL, TYPE)                                                                              \
   launch_pdl(KERNEL, dim3(grid), dim3(256), 0, st, (TYPE*)y, (const TYPE*)x, (const TYPE*)gamma, (const TYPE*)beta, \
              rows, channels, eps, stats)
@@ -322,6 +334,11 @@ int slider_layernorm_train(void* y, float* stats, const void* x, const void* gam
     else if (per_lane <= 3) SLIDER_LN_LAUNCH((layernorm_kernel<__nv_bfloat16, 3>), __nv_bfloat16);
     else if (per_lane <= 5) SLIDER_LN_LAUNCH((layernorm_kernel<__nv_bfloat16, 5>), __nv_bfloat16);
     else SLIDER_LN_LAUNCH(layernorm_stream_kernel<__nv_bfloat16>, __nv_bfloat16);
+  } else if (dtype == SLIDER_F16) {
+    if (per_lane <= 2) SLIDER_LN_LAUNCH((layernorm_kernel<__half, 2>), __half);
+    else if (per_lane <= 3) SLIDER_LN_LAUNCH((layernorm_kernel<__half, 3>), __half);
+    else if (per_lane <= 5) SLIDER_LN_LAUNCH((layernorm_kernel<__half, 5>), __half);
+    else SLIDER_LN_LAUNCH(layernorm_stream_kernel<__half>, __half);
   } else {
     if (per_lane <= 3) SLIDER_LN_LAUNCH((layernorm_kernel<float, 3>), float);
     else if (per_lane <= 5) SLIDER_LN_LAUNCH((layernorm_kernel<float, 5>), float);
@@ -335,7 +352,7 @@ int slider_geglu(void* y, const void* x, int64_t rows, int d, int dtype, void* s
   SLIDER_CHECK_ARG(y && x && rows > 0 && d > 0 && d % 8 == 0, "geglu: bad argument");
   SLIDER_CHECK_ARG((((uintptr_t)y | (uintptr_t)x) & 15) == 0, "geglu: pointers must be 16-byte aligned");
   cudaStream_t st = (cudaStream_t)stream;
-  const int V = dtype == SLIDER_BF16 ? 8 : 4;
+  const int V = dtype == SLIDER_F32 ? 4 : 8;
   const int nv = d / V;
   const int threads = nv >= 256 ? 256 : ((nv + 31) / 32) * 32;
   const unsigned gx = (unsigned)((nv + threads - 1) / threads);
@@ -345,6 +362,8 @@ int slider_geglu(void* y, const void* x, int64_t rows, int d, int dtype, void* s
   if (dtype == SLIDER_BF16)
     launch_pdl(geglu_kernel<__nv_bfloat16>, dim3(gx, (unsigned)gy), dim3(threads), 0, st, (__nv_bfloat16*)y,
                (const __nv_bfloat16*)x, rows, d);
+  else if (dtype == SLIDER_F16)
+    launch_pdl(geglu_kernel<__half>, dim3(gx, (unsigned)gy), dim3(threads), 0, st, (__half*)y, (const __half*)x, rows, d);
   else if (dtype == SLIDER_F32)
     launch_pdl(geglu_kernel<float>, dim3(gx, (unsigned)gy), dim3(threads), 0, st, (float*)y, (const float*)x, rows, d);
   else { set_error("geglu: unsupported dtype %d", dtype); return SLIDER_ERR_UNSUPPORTED; }
@@ -391,8 +410,8 @@ int slider_geglu_backward(void* dx, const void* gy, const void* x, int64_t rows,
 int slider_upsample_nearest2x_nhwc(void* y, const void* x, int batch, int height, int width, int channels, int dtype,
                                    void* stream) {
   SLIDER_CHECK_ARG(y && x && batch > 0 && height > 0 && width > 0 && channels > 0, "upsample2x: bad argument");
-  SLIDER_CHECK_ARG(dtype == SLIDER_BF16 || dtype == SLIDER_F32, "upsample2x: unsupported dtype %d", dtype);
-  const int per = dtype == SLIDER_BF16 ? 8 : 4;
+  SLIDER_CHECK_ARG(dtype == SLIDER_BF16 || dtype == SLIDER_F32 || dtype == SLIDER_F16, "upsample2x: unsupported dtype %d", dtype);
+  const int per = dtype == SLIDER_F32 ? 4 : 8;
   SLIDER_CHECK_ARG(channels % per == 0, "upsample2x: channels must fill 16-byte vectors (got %d)", channels);
   SLIDER_CHECK_ARG((((uintptr_t)y | (uintptr_t)x) & 15) == 0, "upsample2x: pointers must be 16-byte aligned");
   const int nv = channels / per;
@@ -408,8 +427,8 @@ int slider_upsample_nearest2x_nhwc(void* y, const void* x, int batch, int height
 int slider_concat_channels_nhwc(void* y, const void* a, const void* b, int64_t pixels, int channels_a, int channels_b,
                                 int dtype, void* stream) {
   SLIDER_CHECK_ARG(y && a && b && pixels > 0 && channels_a > 0 && channels_b > 0, "concat: bad argument");
-  SLIDER_CHECK_ARG(dtype == SLIDER_BF16 || dtype == SLIDER_F32, "concat: unsupported dtype %d", dtype);
-  const int per = dtype == SLIDER_BF16 ? 8 : 4;
+  SLIDER_CHECK_ARG(dtype == SLIDER_BF16 || dtype == SLIDER_F32 || dtype == SLIDER_F16, "concat: unsupported dtype %d", dtype);
+  const int per = dtype == SLIDER_F32 ? 4 : 8;
   SLIDER_CHECK_ARG(channels_a % per == 0 && channels_b % per == 0,
                    "concat: channel counts must fill 16-byte vectors (got %d, %d)", channels_a, channels_b);
   SLIDER_CHECK_ARG((((uintptr_t)y | (uintptr_t)a | (uintptr_t)b) & 15) == 0, "concat: pointers must be 16-byte aligned");

@@ -199,7 +199,7 @@ def _sdpa(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor) -> torch.Tensor:
 def _cat_skip(x: torch.Tensor, skip: torch.Tensor) -> torch.Tensor:
     """torch.cat([x, skip], dim=1) of the up path; on no-grad CUDA forwards with channels_last operands one copy kernel."""
     if (_no_grad_cuda(x, skip) and "concat" not in _DISABLED and x.dtype == skip.dtype
-            and x.dtype in (torch.bfloat16, torch.float32)
+            and x.dtype in (torch.bfloat16, torch.float32, torch.float16)
             and (x.shape[1] * x.element_size()) % 16 == 0 and (skip.shape[1] * x.element_size()) % 16 == 0):
         xn, sn = x.permute(0, 2, 3, 1), skip.permute(0, 2, 3, 1)
         if xn.is_contiguous() and sn.is_contiguous():
@@ -351,7 +351,7 @@ class Upsample2D(nn.Module):
         self.conv = nn.Conv2d(ch, ch, 3, padding=1)
 
     def forward(self, x):
-        if (_no_grad_cuda(x) and "upsample" not in _DISABLED and x.dtype in (torch.bfloat16, torch.float32)
+        if (_no_grad_cuda(x) and "upsample" not in _DISABLED and x.dtype in (torch.bfloat16, torch.float32, torch.float16)
                 and (x.shape[1] * x.element_size()) % 16 == 0):
             xn = x.permute(0, 2, 3, 1)          # a view when x is channels_last (what the fused convs produce)
             if xn.is_contiguous():
