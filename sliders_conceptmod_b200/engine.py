@@ -59,9 +59,13 @@ class SliderEngine:
         self.emb_den = mk(2 * batch_size, *embed_shape)
         self.emb_pred = mk(6 * batch_size, *embed_shape)
         self.emb_tgt = mk(2 * batch_size, *embed_shape)
-        self.t_dev = torch.zeros(1, device=self.device, dtype=torch.float32)
-        self.coef = torch.zeros(4, device=self.device, dtype=torch.float32)
-        self.in_scale = torch.ones(4, device=self.device, dtype=torch.float32)   # {_, c_x, 0, 0} for scale_model_input
+        # per-step scheduler state: ONE 12-float device row {t, -, -, -, g, c_x, c_eps, c_noise, _, input scale, 0, 0} so
+        # that a denoising step costs one small device copy (row of the table -> here) before its graph replay
+        self.step_row = torch.zeros(12, device=self.device, dtype=torch.float32)
+        self.step_row[8:12] = 1.0
+        self.t_dev = self.step_row[0:1]
+        self.coef = self.step_row[4:8]
+        self.in_scale = self.step_row[8:12]                                      # {_, c_x, 0, 0} for scale_model_input
         self.positive = mk(*lat_shape)
         self.neutral = mk(*lat_shape)
         self.uncond = mk(*lat_shape)
@@ -93,9 +97,12 @@ class SliderEngine:
                 c_x, c_e, c_n = self.sched.step_coefficients(t)
                 rows.append([self.cfg.denoise_guidance, c_x, c_e, c_n])
                 scales.append([0.0, self.sched.input_scale(t), 0.0, 0.0])
-            tab = (torch.tensor(ts, device=self.device, dtype=torch.float32),
-                   torch.tensor(rows, device=self.device, dtype=torch.float32),
-                   torch.tensor(scales, device=self.device, dtype=torch.float32), ts)
+            t_t = torch.tensor(ts, device=self.device, dtype=torch.float32)
+            c_t = torch.tensor(rows, device=self.device, dtype=torch.float32)
+            s_t = torch.tensor(scales, device=self.device, dtype=torch.float32)
+            packed = torch.zeros(len(ts), 12, device=self.device, dtype=torch.float32)       # rows of `step_row`
+            packed[:, 0] = t_t; packed[:, 4:8] = c_t; packed[:, 8:12] = s_t
+            tab = (t_t, c_t, s_t, ts, packed)
             self._tables[n_steps] = tab
         return tab
 
@@ -219,12 +226,12 @@ class SliderEngine:
         `optimizer=False` stops after the backward: the sample's gradient is left in `network.flat_grad` (gradient
         accumulation over several samples before one `optimizer_step()`; the data-parallel equivalence check)."""
         n_den = self.cfg.max_denoising_steps
-        t_tab, c_tab, s_tab, _ = self._table(n_den)
+        packed = self._table(n_den)[4]
         self.lat.copy_(latents.to(self.dtype), non_blocking=True)
         for i in range(timesteps_to):                                   # train_lora.py:195-207
-            self.t_dev.copy_(t_tab[i:i + 1]); self.coef.copy_(c_tab[i]); self.in_scale.copy_(s_tab[i])
+            self.step_row.copy_(packed[i])
             self._exec("denoise", self._body_denoise, restore=(self.lat,))
-        t1000, _, s1000, ts = self._table(1000)                        # train_lora.py:209-213
+        t1000, _, s1000, ts = self._table(1000)[:4]                    # train_lora.py:209-213
         idx = int(timesteps_to * 1000 / n_den)
         self.t_dev.copy_(t1000[idx:idx + 1]); self.in_scale.copy_(s1000[idx])
         if self.cfg.use_graphs and self.cfg.overlap_predict:
@@ -279,7 +286,7 @@ class SliderEngine:
         if self._needs_scale:
             raise NotImplementedError("image_slider_step: add_noise of the sigma-parameterised schedulers is not tabled")
         a = float(self.sched._ac[int(t_add)])
-        t1000, _, s1000, _ = self._table(1000)
+        t1000, _, s1000, _ = self._table(1000)[:4]
         idx = int(timesteps_to * 1000 / n_den)
         self.t_dev.copy_(t1000[idx:idx + 1]); self.in_scale.copy_(s1000[idx])
         self.coef.copy_(torch.tensor([0.0, a ** 0.5, 0.0, (1.0 - a) ** 0.5]), non_blocking=True)

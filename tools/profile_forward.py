@@ -13,7 +13,7 @@ wl = workload.WORKLOADS[sys.argv[sys.argv.index("--workload") + 1] if "--workloa
 engine, unet, network, pairs = workload.build(wl, "cuda", torch.bfloat16, use_graphs=False, lora_b_std=0.02)
 workload.load_pair(engine, wl, pairs[0])
 engine.lat.normal_()
-t_tab, c_tab, s_tab, _ = engine._table(wl.max_denoising_steps)
+t_tab, c_tab, s_tab = engine._table(wl.max_denoising_steps)[:3]
 engine.t_dev.copy_(t_tab[0:1]); engine.coef.copy_(c_tab[0]); engine.in_scale.copy_(s_tab[0])
 for _ in range(2):
     engine._body_denoise()
