@@ -173,6 +173,20 @@ __device__ __forceinline__ float erf_bf16_grade(float x) {
   return copysignf(r, x);
 }
 
+// gelu for 16-bit outputs without the erf detour: with x = |g| / sqrt(2) and A&S 7.1.26 erf(x) = 1 - poly(t) exp(-x^2),
+//   gelu(g) = 0.5 g (1 + sign(g) erf(x)) = relu(g) - |g| * (0.5 poly(t)) * exp(-g^2 / 2),   t = 1 / (1 + 0.3275911 x)
+// 12 FP32 instructions + 2 MUFU per value (the erf form took 19 + 2), and no cancellation for negative g.
+__device__ __forceinline__ float gelu_bf16_grade(float g) {
+  const float ag = fabsf(g);
+  const float t = rcp_approx(fmaf(ag, 0.3275911f * 0.70710678118654752f, 1.f));
+  const float e = ex2_approx(g * g * (-0.5f * 1.4426950408889634f));
+  float p = fmaf(0.5f * 1.061405429f, t, 0.5f * -1.453152027f);
+  p = fmaf(p, t, 0.5f * 1.421413741f);
+  p = fmaf(p, t, 0.5f * -0.284496736f);
+  p = fmaf(p, t, 0.5f * 0.254829592f);
+  return fmaf(-ag, p * t * e, fmaxf(g, 0.f));
+}
+
 __device__ inline float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

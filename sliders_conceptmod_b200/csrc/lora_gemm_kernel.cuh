@@ -767,8 +767,7 @@ lora_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 const int i = pc * PW + k;
                 const float av = __uint_as_float(v[ci][i]) + ba[k];
                 const float gv = __uint_as_float(v[ci + CPG / 2][i]) + bg[k];
-                const float e = sizeof(T) == 2 ? erf_bf16_grade(gv * 0.70710678118654752f) : erff(gv * 0.70710678118654752f);
-                o[k] = av * (0.5f * gv * (1.f + e));
+                o[k] = av * (sizeof(T) == 2 ? gelu_bf16_grade(gv) : 0.5f * gv * (1.f + erff(gv * 0.70710678118654752f)));
               }
               if (sizeof(T) == 2) {
                 uint32_t w[4];

@@ -186,8 +186,7 @@ geglu_kernel(T* __restrict__ y, const T* __restrict__ x, int64_t rows, int D) {
     Elem<T>::load(x + r * 2 * D + D + v * V, g);
 #pragma unroll
     for (int k = 0; k < V; ++k) {
-      const float e = sizeof(T) == 2 ? erf_bf16_grade(g[k] * 0.70710678118654752f) : erff(g[k] * 0.70710678118654752f);
-      o[k] = a[k] * (0.5f * g[k] * (1.f + e));
+      o[k] = a[k] * (sizeof(T) == 2 ? gelu_bf16_grade(g[k]) : 0.5f * g[k] * (1.f + erff(g[k] * 0.70710678118654752f)));
     }
     Elem<T>::store(y + r * D + v * V, o);
   }

@@ -25,17 +25,17 @@ def stamp():
     return [int(d[:, i].median().item()) for i in range(7)], t.shape[0]
 
 
-def spy(x, w, bias, a, b, s, ksize=1, want_h=False, residual=None):
+def spy(x, w, bias, a, b, s, ksize=1, want_h=False, residual=None, stride=1):
     torch.cuda.synchronize()
     trace.zero_()
     _lib.lib().slider_debug_gemm_trace(trace.data_ptr())
-    out = real(x, w, bias, a, b, s, ksize=ksize, want_h=want_h, residual=None if residual is None else residual)
+    out = real(x, w, bias, a, b, s, ksize=ksize, want_h=want_h, residual=None if residual is None else residual, stride=stride)
     torch.cuda.synchronize()
     cold, n = stamp()
     res2 = None if residual is None else residual.clone()
     for _ in range(2):
         trace.zero_()
-        real(x, w, bias, a, b, s, ksize=ksize, want_h=want_h, residual=res2)
+        real(x, w, bias, a, b, s, ksize=ksize, want_h=want_h, residual=res2, stride=stride)
         torch.cuda.synchronize()
     warm, _ = stamp()
     _lib.lib().slider_debug_gemm_trace(None)
