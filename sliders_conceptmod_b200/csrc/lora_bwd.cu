@@ -256,6 +256,215 @@ colreduce_kernel(const ColReduceParams p, int j0) {
   if (threadIdx.x == 0) p.tickets[blockIdx.y] = 0u;
 }
 
+// --------------------------------------------------------------- colreduce on the tensor cores (bf16 storage)
+// The same contraction as a GEMM over the pixels:   out[c, j, t] = scale * sum_q X[q, c] * Vs[(t, j), q],
+//   Vs[(t, j), q] = V[p(q, t), j]   (the V pixel the X pixel q meets through tap t; 0 where the tap leaves the image)
+// so the taps shift the SMALL operand (rank columns) and X is read exactly once.  The SIMT form above keeps
+// TAPS x CH x 4 accumulators per thread and spends most of a 3x3 launch reducing them across 64 pixel lanes (33 us per
+// launch in the SD-1.4 train step, r02 launch list); here a warp owns 8 channels over the CTA's whole pixel chunk, so
+// nothing is reduced inside the CTA at all.
+//   CTA = (chunk of spc x 128 pixels of one image) x (64-channel slice), 8 warps, mma.sync m16n8k16 (bf16, fp32 accum)
+//   A (shared): [MT * 16 rows = (tap, j)][128 pixels] bf16, row stride 272 bytes  -> ldmatrix.x4
+//   B (shared): [128 pixels][64 channels] bf16, row stride 144 bytes              -> ldmatrix.x2.trans
+// The padded strides keep both ldmatrix patterns conflict-free.  V is rounded to bf16 (what the reference's autograd in
+// bf16 does with the lora_down output); fp32 storage keeps the SIMT kernel.  Cross-chunk reduction as above: per-CTA
+// partials + ticket + the last CTA adds in chunk order (deterministic).
+constexpr int TC_PIX = 128;                 // pixels per staged sub-chunk
+constexpr int TC_CH = 64;                   // channels per CTA
+constexpr int TC_A_STRIDE = TC_PIX * 2 + 16;
+constexpr int TC_B_STRIDE = TC_CH * 2 + 16;
+
+__device__ __forceinline__ void ldmatrix_x4(uint32_t addr, uint32_t (&r)[4]) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void ldmatrix_x2_trans(uint32_t addr, uint32_t (&r)[2]) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x2.trans.shared.b16 {%0, %1}, [%2];" : "=r"(r[0]), "=r"(r[1]) : "r"(addr));
+}
+__device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+}
+
+template <typename VT, int MT, int TAPS>
+__global__ void __launch_bounds__(256)
+tc_colreduce_kernel(const ColReduceParams p) {
+  using T = __nv_bfloat16;
+  extern __shared__ __align__(16) unsigned char tc_smem[];
+  __shared__ int s_last;
+  unsigned char* sA = tc_smem;                                   // [MT * 16][TC_A_STRIDE]
+  unsigned char* sB = tc_smem + (size_t)MT * 16 * TC_A_STRIDE;   // [TC_PIX][TC_B_STRIDE]
+  pdl_trigger();
+  const int pi = (p.nprob > 1 && (int)blockIdx.y >= p.prob[0].cblocks) ? 1 : 0;
+  const ColProblem& pr = p.prob[pi];
+  const int yblk = (int)blockIdx.y - (pi ? p.prob[0].cblocks : 0);
+  const T* __restrict__ X = reinterpret_cast<const T*>(pr.X);
+  const VT* __restrict__ V = reinterpret_cast<const VT*>(pr.V);
+  const int HW = p.H * p.W, VHW = p.VH * p.VW;
+  const int img = blockIdx.x / p.cpi, chunk = blockIdx.x - img * p.cpi;
+  const int q0 = chunk * p.ppc, q1 = min(HW, q0 + p.ppc);
+  const int c0 = yblk * TC_CH;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int R = p.rank, rows = TAPS * R;                          // live rows of A: m = t * R + j
+  float acc[MT][4];
+#pragma unroll
+  for (int m = 0; m < MT; ++m)
+#pragma unroll
+    for (int k = 0; k < 4; ++k) acc[m][k] = 0.f;
+  // rows >= TAPS * rank never change: zero once
+  for (int i = tid; i < (MT * 16 - rows) * (TC_PIX / 2); i += 256) {
+    const int m = rows + i / (TC_PIX / 2), w = i - (i / (TC_PIX / 2)) * (TC_PIX / 2);
+    *reinterpret_cast<uint32_t*>(sA + (size_t)m * TC_A_STRIDE + w * 4) = 0u;
+  }
+  pdl_wait();
+  const uint32_t sA_u = (uint32_t)__cvta_generic_to_shared(sA), sB_u = (uint32_t)__cvta_generic_to_shared(sB);
+  constexpr int B_ITEMS = TC_PIX * (TC_CH / 8) / 256;            // 16-byte X vectors per thread and sub-chunk (4)
+  constexpr int A_ITEMS = (TC_PIX * TAPS + 255) / 256;           // (tap, pixel) items per thread and sub-chunk (5 / 1)
+  const bool vec4 = R == 4 && (pr.vstride & 3) == 0 && ((uintptr_t)V & 15) == 0;
+  for (int s0 = q0; s0 < q1; s0 += TC_PIX) {
+    // every global load of the sub-chunk is issued before the first shared-memory store: ONE memory round trip
+    // ---- B: X[s0 .. s0+127, c0 .. c0+63] (16-byte vectors; rows past the chunk and channels past C are zero)
+    uint4 xb[B_ITEMS];
+#pragma unroll
+    for (int u = 0; u < B_ITEMS; ++u) {
+      const int i = tid + u * 256;
+      const int r = i >> 3, v = i & 7;
+      const int q = s0 + r, c = c0 + v * 8;
+      xb[u] = make_uint4(0u, 0u, 0u, 0u);
+      if (q < q1 && c < pr.C) xb[u] = *reinterpret_cast<const uint4*>(X + ((size_t)img * HW + q) * pr.C + c);
+    }
+    // ---- A: Vs[(t, j), q] for the 128 pixels
+    int apv[A_ITEMS];
+    float av[A_ITEMS][4];
+#pragma unroll
+    for (int u = 0; u < A_ITEMS; ++u) {
+      const int i = tid + u * 256;
+      const int t = i / TC_PIX, r = i - t * TC_PIX;
+      const int q = s0 + r;
+      int pv = -1;
+      if (i < TC_PIX * TAPS && q < q1) {
+        if (TAPS == 1) pv = q;
+        else {
+          const int h = q / p.W, w = q - h * p.W;
+          int ph = h - (t / 3 - p.pad), pw = w - (t % 3 - p.pad);
+          bool ok = ph >= 0 && pw >= 0;
+          if (p.stride == 2) { ok = ok && ((ph | pw) & 1) == 0; ph >>= 1; pw >>= 1; }
+          if (ok && ph < p.VH && pw < p.VW) pv = ph * p.VW + pw;
+        }
+      }
+      apv[u] = pv;
+      av[u][0] = av[u][1] = av[u][2] = av[u][3] = 0.f;
+      if (vec4 && pv >= 0) {
+        const VT* vp = V + ((size_t)img * VHW + pv) * pr.vstride;
+        if (sizeof(VT) == 4) {
+          const float4 f = *reinterpret_cast<const float4*>(vp);
+          av[u][0] = f.x; av[u][1] = f.y; av[u][2] = f.z; av[u][3] = f.w;
+        } else {
+          const uint2 w2 = *reinterpret_cast<const uint2*>(vp);
+          av[u][0] = __uint_as_float(w2.x << 16); av[u][1] = __uint_as_float(w2.x & 0xffff0000u);
+          av[u][2] = __uint_as_float(w2.y << 16); av[u][3] = __uint_as_float(w2.y & 0xffff0000u);
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < B_ITEMS; ++u) {
+      const int i = tid + u * 256;
+      *reinterpret_cast<uint4*>(sB + (size_t)(i >> 3) * TC_B_STRIDE + (i & 7) * 16) = xb[u];
+    }
+#pragma unroll
+    for (int u = 0; u < A_ITEMS; ++u) {
+      const int i = tid + u * 256;
+      if (i >= TC_PIX * TAPS) break;
+      const int t = i / TC_PIX, r = i - t * TC_PIX;
+      if (vec4) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          *reinterpret_cast<T*>(sA + (size_t)(t * 4 + j) * TC_A_STRIDE + r * 2) = __float2bfloat16_rn(av[u][j]);
+      } else {
+        const int pv = apv[u];
+        const VT* vp = V + ((size_t)img * VHW + (pv < 0 ? 0 : pv)) * pr.vstride;
+        for (int j = 0; j < R; ++j) {
+          const float f = pv < 0 ? 0.f : Elem<VT>::to_f(vp[j]);
+          *reinterpret_cast<T*>(sA + (size_t)(t * R + j) * TC_A_STRIDE + r * 2) = __float2bfloat16_rn(f);
+        }
+      }
+    }
+    __syncthreads();
+#pragma unroll 2
+    for (int ks = 0; ks < TC_PIX / 16; ++ks) {
+      uint32_t b[2];
+      ldmatrix_x2_trans(sB_u + (uint32_t)((ks * 16 + (lane & 15)) * TC_B_STRIDE + warp * 16), b);
+#pragma unroll
+      for (int m = 0; m < MT; ++m) {
+        uint32_t a[4];
+        ldmatrix_x4(sA_u + (uint32_t)((m * 16 + (lane & 15)) * TC_A_STRIDE + (ks * 16 + (lane >> 4) * 8) * 2), a);
+        mma_bf16_16816(acc[m], a, b);
+      }
+    }
+    __syncthreads();
+  }
+  // ---- this CTA's sums -> workspace [channel block][chunk][MT * 16 rows][64 channels]
+  constexpr int NOUT = MT * 16 * TC_CH;
+  const int nchunks = (int)gridDim.x;
+  float* mine = p.partial + ((size_t)blockIdx.y * nchunks + blockIdx.x) * NOUT;
+  {
+    const int g = lane >> 2, tq = lane & 3;
+#pragma unroll
+    for (int m = 0; m < MT; ++m) {
+      const int col = warp * 8 + 2 * tq;
+      __stcg(reinterpret_cast<float2*>(mine + (size_t)(m * 16 + g) * TC_CH + col), make_float2(acc[m][0], acc[m][1]));
+      __stcg(reinterpret_cast<float2*>(mine + (size_t)(m * 16 + g + 8) * TC_CH + col), make_float2(acc[m][2], acc[m][3]));
+    }
+  }
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) s_last = (atomicAdd(p.tickets + blockIdx.y, 1u) == (unsigned)(nchunks - 1)) ? 1 : 0;
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  // chunk order per output (deterministic).  A thread owns up to three 16-byte output pieces at a time and keeps the
+  // loads of eight chunks of each in flight: the tail is a handful of L2 round trips instead of one per chunk and output
+  const float4* all = reinterpret_cast<const float4*>(p.partial + (size_t)blockIdx.y * nchunks * NOUT);
+  const int nq = rows * TC_CH / 4;
+  for (int base = tid; base < nq; base += 3 * 256) {
+    float4 sum[3];
+#pragma unroll
+    for (int u = 0; u < 3; ++u) sum[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int ch0 = 0; ch0 < nchunks; ch0 += 8) {
+      float4 v8[3][8];
+#pragma unroll
+      for (int u = 0; u < 3; ++u)
+#pragma unroll
+        for (int w = 0; w < 8; ++w) {
+          const int idx = base + u * 256;
+          v8[u][w] = (idx < nq && ch0 + w < nchunks) ? __ldcg(all + (size_t)(ch0 + w) * (NOUT / 4) + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+      for (int u = 0; u < 3; ++u)
+#pragma unroll
+        for (int w = 0; w < 8; ++w) { sum[u].x += v8[u][w].x; sum[u].y += v8[u][w].y; sum[u].z += v8[u][w].z; sum[u].w += v8[u][w].w; }
+    }
+#pragma unroll
+    for (int u = 0; u < 3; ++u) {
+      const int idx = base + u * 256;
+      if (idx >= nq) break;
+      const int i = idx * 4;
+      const int m = i / TC_CH, cl = i - m * TC_CH;
+      const int t = m / R, j = m - t * R;
+      const float r4[4] = {sum[u].x, sum[u].y, sum[u].z, sum[u].w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int cc = c0 + cl + e;
+        if (cc >= pr.C) break;
+        float* o = pr.out + (int64_t)cc * pr.oc + (int64_t)j * pr.oj + (int64_t)t * pr.ot;
+        *o = (p.accumulate ? *o : 0.f) + r4[e] * pr.scale * (pr.cscale != nullptr ? pr.cscale[cc] : 1.f);
+      }
+    }
+  }
+  if (tid == 0) p.tickets[blockIdx.y] = 0u;
+}
+
 template <typename T>
 __global__ void pack_at_kernel(T* __restrict__ At, const T* __restrict__ A, int cin, int taps, int rank) {
   const int64_t total = (int64_t)cin * taps * 16;
@@ -290,9 +499,63 @@ constexpr size_t CR_TICKET_BYTES = CR_MAX_TICKETS * sizeof(unsigned);
 constexpr size_t CR_PARTIAL_BYTES = (size_t)2 << 20;
 static inline size_t bt_bytes_of(int cout) { return (((size_t)16 * cout * 4) + 255) & ~(size_t)255; }
 
+// bf16 storage: the tensor-core form (SLIDER_COLREDUCE_TC=0: the SIMT kernel, for A/B measurements)
+static int g_colreduce_tc = [] { const char* e = getenv("SLIDER_COLREDUCE_TC"); return e ? atoi(e) : 1; }();
+
+template <typename VT>
+static int launch_tc_colreduce(ColReduceParams p, int taps, float* partial, unsigned* tickets, cudaStream_t st) {
+  const int HW = p.H * p.W;
+  const int rows = taps * p.rank;
+  const int mt = (rows + 15) / 16;
+  int cblocks = 0;
+  for (int i = 0; i < p.nprob; ++i) {
+    p.prob[i].cblocks = (p.prob[i].C + TC_CH - 1) / TC_CH;
+    cblocks += p.prob[i].cblocks;
+  }
+  if (cblocks > CR_MAX_TICKETS) { set_error("colreduce: %d channel blocks exceed %d", cblocks, CR_MAX_TICKETS); return SLIDER_ERR_UNSUPPORTED; }
+  const int MT = taps == 1 ? 1 : (mt <= 1 ? 1 : (mt <= 2 ? 2 : (mt <= 3 ? 3 : (mt <= 5 ? 5 : 9))));
+  const size_t nout_bytes = (size_t)MT * 16 * TC_CH * sizeof(float);
+  // pixel chunks of spc x 128 pixels: ~2 CTAs per SM over (images x chunks x channel blocks), bounded by the scratch
+  const int nsub = (HW + TC_PIX - 1) / TC_PIX;
+  int want = (sm_count() * 2) / (p.B * cblocks);
+  if (want < 1) want = 1;
+  int spc = (nsub + want - 1) / want;
+  if (spc < 1) spc = 1;
+  while ((size_t)cblocks * p.B * ((nsub + spc - 1) / spc) * nout_bytes > CR_PARTIAL_BYTES && spc < nsub) ++spc;
+  p.ppc = spc * TC_PIX;
+  p.cpi = (HW + p.ppc - 1) / p.ppc;
+  if ((size_t)cblocks * p.B * p.cpi * nout_bytes > CR_PARTIAL_BYTES) {
+    set_error("colreduce: partial-sum scratch too small for %d x %d CTAs", p.B * p.cpi, cblocks);
+    return SLIDER_ERR_WORKSPACE;
+  }
+  p.PL = 0; p.vmax = 0;
+  p.partial = partial; p.tickets = tickets;
+  const dim3 grid(p.B * p.cpi, cblocks);
+  const size_t smem = (size_t)MT * 16 * TC_A_STRIDE + (size_t)TC_PIX * TC_B_STRIDE;
+#define SLIDER_TC_LAUNCH(MTV, TAPSV)                                                                              \
+  do {                                                                                                            \
+    auto k = tc_colreduce_kernel<VT, MTV, TAPSV>;                                                                 \
+    if (smem > 48 * 1024) SLIDER_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    launch_pdl(k, grid, dim3(256), smem, st, p);                                                                  \
+  } while (0)
+  if (taps == 1) SLIDER_TC_LAUNCH(1, 1);
+  else if (MT == 1) SLIDER_TC_LAUNCH(1, 9);
+  else if (MT == 2) SLIDER_TC_LAUNCH(2, 9);
+  else if (MT == 3) SLIDER_TC_LAUNCH(3, 9);
+  else if (MT == 5) SLIDER_TC_LAUNCH(5, 9);
+  else SLIDER_TC_LAUNCH(9, 9);
+#undef SLIDER_TC_LAUNCH
+  return post_launch("tc_colreduce_kernel");
+}
+
 // taps: 1 or 9.  One or two problems over the same pixel set.
 template <typename T, typename VT>
 static int launch_colreduce(ColReduceParams p, int taps, float* partial, unsigned* tickets, cudaStream_t st) {
+  if constexpr (sizeof(T) == 2) if (g_colreduce_tc && taps * p.rank <= 144 && p.rank <= 16) {
+    bool ok = true;
+    for (int i = 0; i < p.nprob; ++i) ok = ok && p.prob[i].C % 8 == 0 && ((uintptr_t)p.prob[i].X & 15) == 0;
+    if (ok) return launch_tc_colreduce<VT>(p, taps, partial, tickets, st);
+  }
   const int CH = taps == 1 ? 8 : 4;
   const int HW = p.H * p.W;
   // a CTA = 4 channel-vector threads x 64 pixel lanes: a narrow channel slice keeps the per-CTA output small, the
