@@ -722,10 +722,264 @@ gn_bwd_apply_kernel(T* __restrict__ dx, T* __restrict__ dadd, const T* __restric
   }
 }
 
+// Single-launch backward on the forward's slab plan (gn_group_plan): the CTAs of a cluster hold the (image, group set)
+// slab of BOTH x and gy in shared memory, so the two tensors are read from global memory once, the group sums
+// {s1, s2} travel through the cluster like the forward's statistics, and dx is formed from the shared copies.  The
+// two-kernel form above reads x and gy twice and pays two launches with three dependent global round trips each
+// (12.6 + 9.8 us per layer inside the train graph, r02 torch profile).
+//   dadd[b, c] = sum over the image's pixels of dx[., c]: per-thread column sums -> shared [row lane][channel] ->
+//   per-CTA sums (fixed order) -> rank 0 of the cluster adds the peers' arrays in rank order (deterministic).
+template <typename T>
+__global__ void __launch_bounds__(GN_GROUP_THREADS, 1)
+gn_bwd_group_kernel(T* __restrict__ dx, T* __restrict__ dadd, const T* __restrict__ gy, const T* __restrict__ x,
+                    const T* __restrict__ chan_add, const T* __restrict__ gamma, const T* __restrict__ beta,
+                    const float* __restrict__ stats, const GnParams p, const GnGroupArgs ga) {
+  constexpr int EW = Word<T>::N, NE = 4 * EW;
+  extern __shared__ __align__(16) unsigned char gn_gsm[];
+  const int tid = threadIdx.x, nt = blockDim.x, b = blockIdx.y;
+  const int warp = tid >> 5, lane = tid & 31, nwarps = nt >> 5;
+  const int wpr = ga.wr >> 2;
+  const int nch = ga.gp * p.cpg;
+  const int total = ga.rows * wpr;
+  uint4* slab_x = reinterpret_cast<uint4*>(gn_gsm);
+  uint4* slab_g = slab_x + total;
+  float2* s_part = reinterpret_cast<float2*>(gn_gsm + (size_t)2 * total * 16);
+  double* s_cta = reinterpret_cast<double*>(s_part + (GN_GROUP_THREADS / 32) * GN_GROUP_MAXGP);
+  float* s_c = reinterpret_cast<float*>(s_cta + 2 * GN_GROUP_MAXGP);            // [gp][2] s1 / n, s2 / n
+  float* s_colsum = s_c + 2 * GN_GROUP_MAXGP;                                   // [nch] this CTA's column sums of dx
+  float* s_col = s_colsum + nch;                                                // [vstep][nch] per row-lane sums
+  const int set = blockIdx.x / ga.k;
+  const int part = ga.k > 1 ? (int)ptx::cluster_ctarank() : 0;
+  const int c0 = set * nch;
+  const int vpos = tid % wpr, vrow = tid / wpr, vstep = nt / wpr;
+  pdl_trigger();
+  float add[NE], rs[NE], sh[NE], gam[NE], bet[NE], sd[NE], sdx[NE];
+  int ge[NE];
+  {
+    int c = vpos * NE, gi = c / p.cpg, rem = c - gi * p.cpg;
+#pragma unroll
+    for (int e = 0; e < NE; ++e) {
+      add[e] = 0.f; sd[e] = 0.f; sdx[e] = 0.f;
+      ge[e] = gi;
+      if (++rem == p.cpg) { rem = 0; ++gi; }
+    }
+  }
+  {
+    uint4 graw = make_uint4(0, 0, 0, 0), braw = make_uint4(0, 0, 0, 0);
+    if (gamma != nullptr) graw = *reinterpret_cast<const uint4*>(gamma + c0 + vpos * NE);
+    if (beta != nullptr) braw = *reinterpret_cast<const uint4*>(beta + c0 + vpos * NE);
+    const uint32_t gw[4] = {graw.x, graw.y, graw.z, graw.w}, bw[4] = {braw.x, braw.y, braw.z, braw.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float f[2], h[2];
+      Word<T>::unpack(gw[j], f);
+      Word<T>::unpack(bw[j], h);
+#pragma unroll
+      for (int e = 0; e < EW; ++e) { gam[j * EW + e] = gamma != nullptr ? f[e] : 1.f; bet[j * EW + e] = h[e]; }
+    }
+  }
+  pdl_wait();
+  if (chan_add != nullptr) Elem<T>::load(chan_add + (size_t)b * p.C + c0 + vpos * NE, add);
+#pragma unroll
+  for (int e = 0; e < NE; ++e) {
+    const int g = set * ga.gp + ge[e];
+    const float mean = stats[((size_t)b * p.G + g) * 2], rstd = stats[((size_t)b * p.G + g) * 2 + 1];
+    rs[e] = rstd;
+    sh[e] = (add[e] - mean) * rstd;
+  }
+  const size_t rstride = (size_t)p.C * sizeof(T) / 16;
+  const size_t base = (((size_t)b * p.HW + (size_t)part * ga.rows) * p.C + c0) * sizeof(T) / 16;
+  const uint4* xg = reinterpret_cast<const uint4*>(x) + base + vpos;
+  const uint4* gg = reinterpret_cast<const uint4*>(gy) + base + vpos;
+  uint4* dg = reinterpret_cast<uint4*>(dx) + base + vpos;
+  // 1. rows of x and gy -> shared memory, {sum d, sum d * xhat} of the column on the way
+  {
+    int i = tid, r = vrow;
+#pragma unroll 4
+    for (; i < total; i += nt, r += vstep) {
+      const uint4 vx = xg[(size_t)r * rstride], vg = gg[(size_t)r * rstride];
+      slab_x[i] = vx;
+      slab_g[i] = vg;
+      const uint32_t ix[4] = {vx.x, vx.y, vx.z, vx.w}, ig[4] = {vg.x, vg.y, vg.z, vg.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float fx[2], fg[2];
+        Word<T>::unpack(ix[j], fx);
+        Word<T>::unpack(ig[j], fg);
+#pragma unroll
+        for (int e = 0; e < EW; ++e) {
+          const int k = j * EW + e;
+          const float xh = fmaf(fx[e], rs[k], sh[k]);
+          float d = fg[e] * gam[k];
+          if (p.silu) d *= silu_grad(fmaf(xh, gam[k], bet[k]));
+          sd[k] += d;
+          sdx[k] = fmaf(d, xh, sdx[k]);
+        }
+      }
+    }
+  }
+  // 2. group sums: warp -> CTA (fp64) -> cluster, as in the forward
+  for (int gi = 0; gi < ga.gp; ++gi) {
+    float a = 0.f, q = 0.f;
+#pragma unroll
+    for (int e = 0; e < NE; ++e) {
+      a += ge[e] == gi ? sd[e] : 0.f;
+      q += ge[e] == gi ? sdx[e] : 0.f;
+    }
+    a = warp_sum(a);
+    q = warp_sum(q);
+    if (lane == 0) s_part[warp * GN_GROUP_MAXGP + gi] = make_float2(a, q);
+  }
+  __syncthreads();
+  if (warp < ga.gp) {
+    double a = 0.0, q = 0.0;
+    if (lane < nwarps) { const float2 v = s_part[lane * GN_GROUP_MAXGP + warp]; a = (double)v.x; q = (double)v.y; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      a += __shfl_xor_sync(0xffffffffu, a, o);
+      q += __shfl_xor_sync(0xffffffffu, q, o);
+    }
+    if (lane == 0) { s_cta[2 * warp] = a; s_cta[2 * warp + 1] = q; }
+  }
+  if (ga.k > 1) { ptx::cluster_arrive(); ptx::cluster_wait(); } else { __syncthreads(); }
+  if (warp < ga.gp) {
+    double a = 0.0, q = 0.0;
+    if (ga.k > 1) {
+      if (lane < ga.k) {
+        const uint32_t peer = ptx::mapa(ptx::smem_u32(s_cta + 2 * warp), (uint32_t)lane);
+        asm volatile("ld.shared::cluster.v2.f64 {%0, %1}, [%2];" : "=d"(a), "=d"(q) : "r"(peer));
+      }
+#pragma unroll
+      for (int o = 8; o > 0; o >>= 1) {
+        a += __shfl_xor_sync(0xffffffffu, a, o);
+        q += __shfl_xor_sync(0xffffffffu, q, o);
+      }
+    } else {
+      a = s_cta[2 * warp]; q = s_cta[2 * warp + 1];
+    }
+    if (lane == 0) {
+      const double n = (double)p.cpg * (double)p.HW;
+      s_c[2 * warp] = (float)(a / n); s_c[2 * warp + 1] = (float)(q / n);
+    }
+  }
+  __syncthreads();
+  // 3. dx from the shared copies; column sums of dx for dadd
+  float c1[NE], c2[NE], dcol[NE];
+#pragma unroll
+  for (int e = 0; e < NE; ++e) { c1[e] = s_c[2 * ge[e]]; c2[e] = s_c[2 * ge[e] + 1]; dcol[e] = 0.f; }
+  {
+    int i = tid, r = vrow;
+#pragma unroll 2
+    for (; i < total; i += nt, r += vstep) {
+      const uint4 vx = slab_x[i], vg = slab_g[i];
+      const uint32_t ix[4] = {vx.x, vx.y, vx.z, vx.w}, ig[4] = {vg.x, vg.y, vg.z, vg.w};
+      uint32_t out[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float fx[2], fg[2], u[2] = {0.f, 0.f};
+        Word<T>::unpack(ix[j], fx);
+        Word<T>::unpack(ig[j], fg);
+#pragma unroll
+        for (int e = 0; e < EW; ++e) {
+          const int k = j * EW + e;
+          const float xh = fmaf(fx[e], rs[k], sh[k]);
+          float d = fg[e] * gam[k];
+          if (p.silu) d *= silu_grad(fmaf(xh, gam[k], bet[k]));
+          const float o = rs[k] * (d - c1[k] - xh * c2[k]);
+          u[e] = o;
+          dcol[k] += o;
+        }
+        out[j] = Word<T>::pack(u);
+      }
+      dg[(size_t)r * rstride] = make_uint4(out[0], out[1], out[2], out[3]);
+    }
+  }
+  if (dadd != nullptr) {
+#pragma unroll
+    for (int e = 0; e < NE; ++e) s_col[(size_t)vrow * nch + vpos * NE + e] = dcol[e];
+    __syncthreads();
+    for (int c = tid; c < nch; c += nt) {
+      float a = 0.f;
+      for (int l = 0; l < vstep; ++l) a += s_col[(size_t)l * nch + c];
+      s_colsum[c] = a;
+    }
+    if (ga.k > 1) { ptx::cluster_arrive(); ptx::cluster_wait(); } else { __syncthreads(); }
+    if (part == 0) {
+      for (int c = tid; c < nch; c += nt) {
+        float a = 0.f;
+        if (ga.k > 1) {
+          for (int r = 0; r < ga.k; ++r) {
+            float v;
+            const uint32_t peer = ptx::mapa(ptx::smem_u32(s_colsum + c), (uint32_t)r);
+            asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(peer));
+            a += v;
+          }
+        } else {
+          a = s_colsum[c];
+        }
+        dadd[(size_t)b * p.C + c0 + c] = Elem<T>::from_f(a);
+      }
+    }
+  }
+  // the peers may still read this CTA's shared memory
+  if (ga.k > 1) { ptx::cluster_arrive(); ptx::cluster_wait(); }
+}
+
+static int g_gn_bwd_group = [] { const char* e = getenv("SLIDER_GN_BWD_GROUP"); return e ? atoi(e) : 1; }();
+
+template <typename T>
+static bool gn_bwd_group_launch(int* rc, void* dx, void* dadd, const void* gy, const void* x, const void* chan_add,
+                                const void* gamma, const void* beta, const float* stats, const GnParams& p,
+                                cudaStream_t st) {
+  GnGroupPlan gp;
+  if (!g_gn_bwd_group || p.B > 65535 || !gn_group_plan<T>(p, &gp)) return false;
+  const int nch = gp.a.gp * p.cpg;
+  const int wpr = gp.a.wr >> 2;
+  const int vstep = gp.threads / wpr;
+  const size_t seg = (size_t)gp.a.wr * 4;
+  const size_t smem = 2 * (size_t)gp.a.rows * seg + (GN_GROUP_THREADS / 32) * GN_GROUP_MAXGP * sizeof(float2) +
+                      2 * GN_GROUP_MAXGP * sizeof(double) + 2 * GN_GROUP_MAXGP * sizeof(float) +
+                      (size_t)nch * sizeof(float) + (size_t)vstep * nch * sizeof(float);
+  if (smem > 200 * 1024) return false;
+  static thread_local size_t configured = 0;
+  if (smem > 48 * 1024 && smem > configured) {
+    if (cudaFuncSetAttribute(gn_bwd_group_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
+      cudaGetLastError();
+      return false;
+    }
+    configured = smem;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((p.G / gp.a.gp) * gp.a.k, p.B); cfg.blockDim = dim3(gp.threads); cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (gp.a.k > 1) {
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = (unsigned)gp.a.k; attr[na].val.clusterDim.y = 1; attr[na].val.clusterDim.z = 1;
+    ++na;
+  }
+  if (pdl_enabled()) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = na;
+  cudaLaunchKernelEx(&cfg, gn_bwd_group_kernel<T>, (T*)dx, (T*)dadd, (const T*)gy, (const T*)x, (const T*)chan_add,
+                     (const T*)gamma, (const T*)beta, stats, p, gp.a);
+  *rc = post_launch("gn_bwd_group_kernel");
+  return true;
+}
+
 template <typename T>
 static int groupnorm_bwd_impl(void* dx, void* dadd, const void* gy, const void* x, const void* chan_add,
                               const void* gamma, const void* beta, const float* stats, float* ws, GnParams p,
                               cudaStream_t st) {
+  {
+    int rc = SLIDER_OK;
+    if (gn_bwd_group_launch<T>(&rc, dx, dadd, gy, x, chan_add, gamma, beta, stats, p, st)) return rc;
+  }
   float* partial_g = ws;                                             // [B][chunks][G][2]
   float* partial_c = ws + (size_t)p.B * p.chunks * p.G * 2;          // [B][chunks][C][2]
   const bool want_add = dadd != nullptr;
