@@ -1,8 +1,8 @@
 """ncu target: the bandwidth-class kernels of the slider path, each launched twice at n = 2^26 (HBM regime, distinct
 buffers per launch) and twice at the SD-1.4 native size (16 384-element latents; 2.9 M LoRA parameters for the
-optimizer): guidance_loss_kernel, cfg_step_kernel, adamw_flat_kernel, clip_coef_kernel, colreduce_kernel (one 1x1 and
-one 3x3 layer through slider_lora_backward_1x1 / slider_lora_grad).  Run plain first, then under
-  ncu --set full --clock-control none -k regex:'guidance_loss|cfg_step|adamw|clip_coef|colreduce' ..."""
+optimizer): guidance_loss_kernel, cfg_step_kernel, adamw_flat_kernel, clip_coef_kernel, tc_colreduce_kernel (one 1x1 and
+one 3x3 layer through slider_lora_backward_1x1 / slider_lora_grad), gn_group_kernel / gn_bwd_group_kernel.  Run plain first, then under
+  ncu --set full --clock-control none -k regex:'guidance_loss|cfg_step|adamw|clip_coef|colreduce|gn_group|gn_bwd' ..."""
 import sys
 from pathlib import Path
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
@@ -35,5 +35,12 @@ for rep in range(2):
     x4 = torch.randn(2, 64, 64, C, device="cuda").to(dt); gy4 = torch.randn(2, 64, 64, N, device="cuda").to(dt)
     dA9 = torch.zeros(r, 9, C, device="cuda")
     ops.lora_grad(gy4, x4, h, b, 0.25, 3, dA9, dB)
+# GroupNorm (+SiLU, + per-channel pre-add) training forward and its single-launch backward at the level-0 size
+for rep in range(2):
+    xg = torch.randn(2, 64, 64, 320, device="cuda").to(dt); gyg = torch.randn(2, 64, 64, 320, device="cuda").to(dt)
+    gam = torch.randn(320, device="cuda").to(dt); bet = torch.randn(320, device="cuda").to(dt)
+    add = torch.randn(2, 320, device="cuda").to(dt)
+    yg, st = ops.groupnorm_nhwc(xg, 32, gam, bet, 1e-5, True, add, want_stats=True)
+    ops.groupnorm_nhwc_backward(gyg, xg, st, 32, gam, bet, True, add, want_dadd=True)
 torch.cuda.synchronize()
 print("done")
