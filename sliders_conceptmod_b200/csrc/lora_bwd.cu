@@ -405,7 +405,8 @@ tc_colreduce_kernel(const ColReduceParams p) {
     __syncthreads();
   }
   // ---- this CTA's sums -> workspace [channel block][chunk][MT * 16 rows][64 channels]
-  constexpr int NOUT = MT * 16 * TC_CH;
+  const int rows8 = (rows + 7) & ~7;                 // only the live rows (rounded to the fragment's 8) travel
+  const int NOUT = rows8 * TC_CH;
   const int nchunks = (int)gridDim.x;
   float* mine = p.partial + ((size_t)blockIdx.y * nchunks + blockIdx.x) * NOUT;
   {
@@ -413,8 +414,10 @@ tc_colreduce_kernel(const ColReduceParams p) {
 #pragma unroll
     for (int m = 0; m < MT; ++m) {
       const int col = warp * 8 + 2 * tq;
-      __stcg(reinterpret_cast<float2*>(mine + (size_t)(m * 16 + g) * TC_CH + col), make_float2(acc[m][0], acc[m][1]));
-      __stcg(reinterpret_cast<float2*>(mine + (size_t)(m * 16 + g + 8) * TC_CH + col), make_float2(acc[m][2], acc[m][3]));
+      if (m * 16 + g < rows8)
+        __stcg(reinterpret_cast<float2*>(mine + (size_t)(m * 16 + g) * TC_CH + col), make_float2(acc[m][0], acc[m][1]));
+      if (m * 16 + g + 8 < rows8)
+        __stcg(reinterpret_cast<float2*>(mine + (size_t)(m * 16 + g + 8) * TC_CH + col), make_float2(acc[m][2], acc[m][3]));
     }
   }
   __threadfence();
@@ -423,42 +426,70 @@ tc_colreduce_kernel(const ColReduceParams p) {
   __syncthreads();
   if (!s_last) return;
   __threadfence();
-  // chunk order per output (deterministic).  A thread owns up to three 16-byte output pieces at a time and keeps the
-  // loads of eight chunks of each in flight: the tail is a handful of L2 round trips instead of one per chunk and output
+  // Fixed summation order per output (deterministic).  Few outputs (rank rows of a 1x1 problem: 64 pieces): the chunks
+  // are dealt to `groups` thread groups (chunk c -> group c % groups, added in increasing c), whose sums meet in shared
+  // memory in group order.  Many outputs: a thread owns up to three 16-byte pieces at a time.  Either way eight chunk
+  // loads per piece are in flight, so the tail is a handful of L2 round trips.
   const float4* all = reinterpret_cast<const float4*>(p.partial + (size_t)blockIdx.y * nchunks * NOUT);
   const int nq = rows * TC_CH / 4;
-  for (int base = tid; base < nq; base += 3 * 256) {
-    float4 sum[3];
+  auto emit = [&](int idx, const float4& sm) {
+    const int i = idx * 4;
+    const int m = i / TC_CH, cl = i - m * TC_CH;
+    const int t = m / R, j = m - t * R;
+    const float r4[4] = {sm.x, sm.y, sm.z, sm.w};
 #pragma unroll
-    for (int u = 0; u < 3; ++u) sum[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int ch0 = 0; ch0 < nchunks; ch0 += 8) {
-      float4 v8[3][8];
-#pragma unroll
-      for (int u = 0; u < 3; ++u)
-#pragma unroll
-        for (int w = 0; w < 8; ++w) {
-          const int idx = base + u * 256;
-          v8[u][w] = (idx < nq && ch0 + w < nchunks) ? __ldcg(all + (size_t)(ch0 + w) * (NOUT / 4) + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
-        }
-#pragma unroll
-      for (int u = 0; u < 3; ++u)
-#pragma unroll
-        for (int w = 0; w < 8; ++w) { sum[u].x += v8[u][w].x; sum[u].y += v8[u][w].y; sum[u].z += v8[u][w].z; sum[u].w += v8[u][w].w; }
+    for (int e = 0; e < 4; ++e) {
+      const int cc = c0 + cl + e;
+      if (cc >= pr.C) break;
+      float* o = pr.out + (int64_t)cc * pr.oc + (int64_t)j * pr.oj + (int64_t)t * pr.ot;
+      *o = (p.accumulate ? *o : 0.f) + r4[e] * pr.scale * (pr.cscale != nullptr ? pr.cscale[cc] : 1.f);
     }
+  };
+  if (nq <= 128) {
+    const int groups = nq <= 64 ? 4 : 2;
+    const int idx = tid % nq, cg = tid / nq;
+    float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (cg < groups) {
+      for (int ch0 = cg; ch0 < nchunks; ch0 += 8 * groups) {
+        float4 v8[8];
 #pragma unroll
-    for (int u = 0; u < 3; ++u) {
-      const int idx = base + u * 256;
-      if (idx >= nq) break;
-      const int i = idx * 4;
-      const int m = i / TC_CH, cl = i - m * TC_CH;
-      const int t = m / R, j = m - t * R;
-      const float r4[4] = {sum[u].x, sum[u].y, sum[u].z, sum[u].w};
+        for (int w = 0; w < 8; ++w)
+          v8[w] = ch0 + w * groups < nchunks ? __ldcg(all + (size_t)(ch0 + w * groups) * (NOUT / 4) + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const int cc = c0 + cl + e;
-        if (cc >= pr.C) break;
-        float* o = pr.out + (int64_t)cc * pr.oc + (int64_t)j * pr.oj + (int64_t)t * pr.ot;
-        *o = (p.accumulate ? *o : 0.f) + r4[e] * pr.scale * (pr.cscale != nullptr ? pr.cscale[cc] : 1.f);
+        for (int w = 0; w < 8; ++w) { sum.x += v8[w].x; sum.y += v8[w].y; sum.z += v8[w].z; sum.w += v8[w].w; }
+      }
+    }
+    float4* s_red = reinterpret_cast<float4*>(tc_smem);      // the operand tiles are dead: [groups][nq]
+    if (cg < groups) s_red[cg * nq + idx] = sum;
+    __syncthreads();
+    if (cg == 0) {
+      for (int g = 1; g < groups; ++g) { const float4 o = s_red[g * nq + idx]; sum.x += o.x; sum.y += o.y; sum.z += o.z; sum.w += o.w; }
+      emit(idx, sum);
+    }
+  } else {
+    for (int base = tid; base < nq; base += 3 * 256) {
+      float4 sum[3];
+#pragma unroll
+      for (int u = 0; u < 3; ++u) sum[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int ch0 = 0; ch0 < nchunks; ch0 += 8) {
+        float4 v8[3][8];
+#pragma unroll
+        for (int u = 0; u < 3; ++u)
+#pragma unroll
+          for (int w = 0; w < 8; ++w) {
+            const int idx = base + u * 256;
+            v8[u][w] = (idx < nq && ch0 + w < nchunks) ? __ldcg(all + (size_t)(ch0 + w) * (NOUT / 4) + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+#pragma unroll
+        for (int u = 0; u < 3; ++u)
+#pragma unroll
+          for (int w = 0; w < 8; ++w) { sum[u].x += v8[u][w].x; sum[u].y += v8[u][w].y; sum[u].z += v8[u][w].z; sum[u].w += v8[u][w].w; }
+      }
+#pragma unroll
+      for (int u = 0; u < 3; ++u) {
+        const int idx = base + u * 256;
+        if (idx >= nq) break;
+        emit(idx, sum[u]);
       }
     }
   }
@@ -514,10 +545,12 @@ static int launch_tc_colreduce(ColReduceParams p, int taps, float* partial, unsi
   }
   if (cblocks > CR_MAX_TICKETS) { set_error("colreduce: %d channel blocks exceed %d", cblocks, CR_MAX_TICKETS); return SLIDER_ERR_UNSUPPORTED; }
   const int MT = taps == 1 ? 1 : (mt <= 1 ? 1 : (mt <= 2 ? 2 : (mt <= 3 ? 3 : (mt <= 5 ? 5 : 9))));
-  const size_t nout_bytes = (size_t)MT * 16 * TC_CH * sizeof(float);
+  const size_t nout_bytes = (size_t)((rows + 7) & ~7) * TC_CH * sizeof(float);      // live rows only (kernel: rows8)
   // pixel chunks of spc x 128 pixels: ~2 CTAs per SM over (images x chunks x channel blocks), bounded by the scratch
   const int nsub = (HW + TC_PIX - 1) / TC_PIX;
-  int want = (sm_count() * 2) / (p.B * cblocks);
+  // (3x3: two CTAs per SM; 1x1: four -- one staged sub-chunk per CTA where it fits, the round trips of co-resident CTAs
+  // overlap and the finish deals the chunks over four thread groups)
+  int want = (sm_count() * (taps == 1 ? 4 : 2)) / (p.B * cblocks);
   if (want < 1) want = 1;
   int spc = (nsub + want - 1) / want;
   if (spc < 1) spc = 1;
