@@ -7,17 +7,21 @@ from torch.nn.attention import SDPBackend, sdpa_kernel
 dev, dt = "cuda", torch.bfloat16
 
 
-def timed(fn, reps=20):
+def timed(fn, reps=10):
+    """Sum of the CUDA kernel durations per call (torch profiler): the eager call itself is host-launch bound."""
+    from torch.profiler import profile, ProfilerActivity
     for _ in range(3):
         fn()
     torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(reps):
-        fn()
-    e1.record()
-    torch.cuda.synchronize()
-    return e0.elapsed_time(e1) * 1e3 / reps
+    with profile(activities=[ProfilerActivity.CUDA]) as prof:
+        for _ in range(reps):
+            fn()
+        torch.cuda.synchronize()
+    tot = 0.0
+    for ev in prof.events():
+        if ev.device_type == torch.autograd.DeviceType.CUDA:
+            tot += ev.device_time_total if hasattr(ev, "device_time_total") else ev.cuda_time_total
+    return tot / reps
 
 
 for (L, S, d) in [(4096, 4096, 40), (1024, 1024, 80), (256, 256, 160), (64, 64, 160), (4096, 77, 40), (1024, 77, 80), (256, 77, 160)]:
