@@ -83,15 +83,22 @@ class NoTriggerTrainer:
             raise NotImplementedError(f"model {model}: SD3 / FLUX.1 are other model families (out of scope)")
         self.config, self.device, self.index = config, torch.device(device), clip_index
         self.dtype = config_util.parse_precision(config.train.precision)
-        # two copies of the encoders, one adapted and one static (:96-117); same weights (a pretrained checkpoint)
+        # The reference loads the checkpoint twice (:96-117): one copy gets the adapter, the other stays static and
+        # supplies the target / neutral encodings.  Here the STATIC encodings come from the adapted copy with the
+        # adapter switched off (multiplier 0): the reference's static encoder and its adapter-off adapted encoder are
+        # the same arithmetic, and its objective relies on it — at iteration 0 (lora_up = 0) the moved encoding must
+        # equal the neutral one EXACTLY, because the sign-agreement term `_cos` is differentiated at v = moved - neutral
+        # and a rounding-noise v turns that derivative (analytically 0) into O(1) cancellation noise.  A static copy
+        # evaluated by cuBLAS next to an adapted copy evaluated by the fused kernel differs in the last bits; the
+        # same kernel with and without the rank-r term does not (s * h . 0 adds exact zeros).
         tok_a, enc_a = encoders[0] if encoders is not None else load_text_encoders(model, seed)
-        tok_b, enc_b = encoders[1] if encoders is not None else load_text_encoders(model, seed)
-        for enc in list(enc_a) + list(enc_b):
+        tok_b = encoders[1][0] if encoders is not None else tok_a
+        for enc in list(enc_a):
             enc.to(self.device, dtype=self.dtype)
             enc.requires_grad_(False)
             enc.eval()
         self.prefix = ["lora_te1", "lora_te2"][clip_index]
-        self.peft_encoder, self.static_encoder = enc_a[clip_index], enc_b[clip_index]
+        self.peft_encoder = enc_a[clip_index]
         net_cls = DoRANetwork if peft_type == "dora" else LoRANetwork
         self.network = net_cls(self.peft_encoder, rank=rank, multiplier=1.0, delimiter="_", alpha=config.network.alpha,
                                target_replace=["CLIPAttention", "CLIPSdpaAttention"], prefix=self.prefix,
@@ -118,10 +125,11 @@ class NoTriggerTrainer:
         self.positive = positive if positive else None
         self.negative = negative if negative else None
         with torch.no_grad():
+            self._set_multiplier(0.0)           # adapter off: the static encoder of the reference
             self.neu_tokens = text_tokenize(tok_a[clip_index], [""]).to(self.device)
-            self.neutral = hidden(self.static_encoder, self.neu_tokens)
-            self.pos = hidden(self.static_encoder, text_tokenize(tok_b[clip_index], [self.positive])) if self.positive else None
-            self.neg = hidden(self.static_encoder, text_tokenize(tok_b[clip_index], [self.negative])) if self.negative else None
+            self.neutral = hidden(self.peft_encoder, self.neu_tokens)
+            self.pos = hidden(self.peft_encoder, text_tokenize(tok_b[clip_index], [self.positive])) if self.positive else None
+            self.neg = hidden(self.peft_encoder, text_tokenize(tok_b[clip_index], [self.negative])) if self.negative else None
         if self.pos is None and self.neg is None:
             raise ValueError("train_notrigger: give --positive and / or --negative")
         self.lam = config.train.lambda_similarity
