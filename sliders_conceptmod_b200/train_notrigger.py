@@ -78,7 +78,7 @@ class NoTriggerTrainer:
     """State of train_notrigger.train (:67-465) with the loop body as `iteration(i)`."""
 
     def __init__(self, config: RootConfig, device, clip_index: int = 0, peft_type: str = "lora", rank: int = 4,
-                 model: str = "SDXL", positive=None, negative=None, encoders=None, seed: int = 0):
+                 model: str = "SDXL", positive=None, negative=None, encoders=None, seed: int = 0, engine: bool = False):
         if model not in ("SDXL", "PonyXL"):
             raise NotImplementedError(f"model {model}: SD3 / FLUX.1 are other model families (out of scope)")
         self.config, self.device, self.index = config, torch.device(device), clip_index
@@ -135,13 +135,22 @@ class NoTriggerTrainer:
         self.lam = config.train.lambda_similarity
         self.distance1 = self.distance2 = None
         self.last = {}
+        # engine mode (LoRA on CUDA): flat parameter / fp32 gradient buffers, the whole iteration replayed as one graph
+        self.engine = bool(engine) and self.device.type == "cuda" and peft_type != "dora"
+        self._graph, self._capturable = None, True
+        if self.engine:
+            self.network.flatten()
+            self._neg_lr = torch.zeros((), device=self.device, dtype=torch.float32)
+            self._obj = torch.zeros((), device=self.device, dtype=torch.float32)
 
     def _set_multiplier(self, m: float) -> None:
         for lora in self.network.unet_loras:
             lora.multiplier = m
 
-    def iteration(self, i: int) -> float:
-        """One pass of the loop body (:293-445).  Returns the value that was back-propagated."""
+    def _objective(self, i: int, on_device: bool = False) -> torch.Tensor:
+        """Forward passes and the scalar that is back-propagated (:293-432).  `on_device`: no host read of a tensor
+        (the curriculum's `min(0.95, t)` becomes a clamp with the same value and gradient), so the body can be captured
+        in a CUDA graph."""
         pos, neg, neutral = self.pos, self.neg, self.neutral
         preg = nreg = None
         with self.network:
@@ -162,26 +171,77 @@ class NoTriggerTrainer:
                 if pos is not None:
                     nreg = direction_regulariser(e_n, neg, pos, neutral)
         if pos is None:
-            objective = nloss
-        elif neg is None:
-            objective = ploss
-        else:
-            # remaining fractions of the initial distances (:393-404), then the curriculum (:413-432)
-            nperc = torch.norm(neg - e_n).mean() / (self.distance2 * SPLIT)
-            pperc = torch.norm(pos - e_p).mean() / (self.distance1 * SPLIT)
-            loss, similarity, w = curriculum(pperc, nperc, self.lam * preg + self.lam * nreg)
-            objective = loss + similarity
-            self.last = {k: float(torch.as_tensor(v).detach()) for k, v in
-                         (("w_p", w[0]), ("w_n", w[1]), ("w_r", w[2]), ("pperc", pperc), ("nperc", nperc))}
-        objective.backward()
-        torch.nn.utils.clip_grad_value_(self.network.parameters(), clip_value=1.0)       # :437
-        self.optimizer.step()
-        # no zero_grad in the reference loop: gradients ACCUMULATE across iterations (:293-445 never clears them)
+            return nloss
+        if neg is None:
+            return ploss
+        # remaining fractions of the initial distances (:393-404), then the curriculum (:413-432)
+        nperc = torch.norm(neg - e_n).mean() / (self.distance2 * SPLIT)
+        pperc = torch.norm(pos - e_p).mean() / (self.distance1 * SPLIT)
+        similarity = self.lam * preg + self.lam * nreg
+        if on_device:
+            gap = torch.abs(pperc - nperc)
+            boost = 1 + 4 * (1 - torch.exp(-gap / 0.05))
+            w_p = (pperc * boost) / (pperc * boost + nperc * boost)
+            w_n = (nperc * boost) / (pperc * boost + nperc * boost)
+            w_r = torch.clamp((nperc + pperc) / 2, max=0.95)
+            return w_p * pperc + w_n * nperc + (1.0 - w_r) * similarity
+        loss, similarity, w = curriculum(pperc, nperc, similarity)
+        self.last = {k: float(torch.as_tensor(v).detach()) for k, v in
+                     (("w_p", w[0]), ("w_n", w[1]), ("w_r", w[2]), ("pperc", pperc), ("nperc", nperc))}
+        return loss + similarity
+
+    def _step_schedule(self, i: int) -> None:
         if i < WARMUP_STEPS:
             self.scheduler.step()
         else:
             self.lr_scheduler.step()
+
+    def iteration(self, i: int):
+        """One pass of the loop body (:293-445).  Returns the value that was back-propagated (a float; with
+        `engine=True` the 0-dim device tensor it was copied to, so that nothing waits for the GPU)."""
+        if self.engine:
+            return self._engine_iteration(i)
+        objective = self._objective(i)
+        objective.backward()
+        torch.nn.utils.clip_grad_value_(self.network.parameters(), clip_value=1.0)       # :437
+        self.optimizer.step()
+        # no zero_grad in the reference loop: gradients ACCUMULATE across iterations (:293-445 never clears them)
+        self._step_schedule(i)
         return float(objective.detach())
+
+    # ---- engine: the iteration as ONE replayed CUDA graph over the flat parameter / gradient buffers ----------------
+    def _engine_body(self, i: int) -> None:
+        net = self.network
+        with net.packed_transposes():
+            objective = self._objective(i, on_device=True)
+            objective.backward()            # the fused backward launches accumulate straight into net.flat_grad (fp32)
+        net.flat_grad.clamp_(-1.0, 1.0)                                                   # clip_grad_value_(1.0)
+        net.flat_param.add_((net.flat_grad * self._neg_lr).to(net.flat_param.dtype))      # SGD: p -= lr * g
+        self._obj.copy_(objective.detach())
+
+    def _engine_iteration(self, i: int):
+        net = self.network
+        self._neg_lr.fill_(-float(self.optimizer.param_groups[0]["lr"]))      # the schedule objects stay the lr source
+        if i == 0 or self._graph is None and not self._capturable:
+            self._engine_body(i)            # iteration 0 fixes the reference distances (data-dependent init): eager
+        elif self._graph is None:
+            saved = (net.flat_param.clone(), net.flat_grad.clone())
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                for _ in range(2):          # warm-up outside capture (lazy inits, cudaFuncSetAttribute)
+                    self._engine_body(i)
+            torch.cuda.current_stream().wait_stream(side)
+            torch.cuda.synchronize()
+            net.flat_param.copy_(saved[0]); net.flat_grad.copy_(saved[1])
+            self._graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self._graph):
+                self._engine_body(i)
+            self._graph.replay()
+        else:
+            self._graph.replay()
+        self._step_schedule(i)
+        return self._obj
 
     def state_dict(self, dtype=None):
         return self.network.get_state_dict(dtype)
@@ -189,14 +249,14 @@ class NoTriggerTrainer:
 
 def train(config: RootConfig, prompts: list, device, on_step_complete=None, save_file: bool = True,
           clip_index: int = 0, peft_type: str = "lora", rank: int = 4, model: str = "SDXL", attributes=None,
-          positive=None, negative=None, encoders=None, seed: int = 0):
-    """train_notrigger.train (:67-486), same arguments.  `prompts` and `attributes` are accepted and unused, as in the
+          positive=None, negative=None, encoders=None, seed: int = 0, engine: bool = False):
+    """train_notrigger.train (:67-486), same arguments (+ `engine`: replay the iteration as one CUDA graph).  `prompts` and `attributes` are accepted and unused, as in the
     reference (its attribute list is reset to [] at :266, so the stabilising term is always zero).  `encoders`
     (two (tokenizers, text_encoders) pairs) replaces the checkpoint load for callers that bring their own models."""
     save_path = Path(config.save.path)
     save_dtype = config_util.parse_precision(config.train.precision)        # the reference saves in the TRAIN precision (:93)
     trainer = NoTriggerTrainer(config, device, clip_index=clip_index, peft_type=peft_type, rank=rank, model=model,
-                               positive=positive, negative=negative, encoders=encoders, seed=seed)
+                               positive=positive, negative=negative, encoders=encoders, seed=seed, engine=engine)
     last_recon = None
     for i in range(config.train.iterations):
         trainer.iteration(i)
@@ -273,6 +333,8 @@ def build_parser() -> argparse.ArgumentParser:
     ap.add_argument("--model", type=str, required=False, default="SDXL", help="model SDXL or SD3-Medium")
     ap.add_argument("--negative", type=str, required=False, default=None, help="negative term(s)")
     ap.add_argument("--clip_index", type=int, required=True, help="0 based clip index (sdxl has two)")
+    ap.add_argument("--engine", action="store_true",
+                    help="(not in the reference) replay each iteration as one CUDA graph over flat parameter buffers")
     return ap
 
 
@@ -283,7 +345,8 @@ def main(args) -> None:
     # the reference passes `--negative` (a plain string) straight to ", ".join (:279): its characters get joined by
     # ", " — reproduced by handing the string over unchanged
     train(config, [], device, on_step_complete=None, positive=args.positive, negative=args.negative,
-          clip_index=args.clip_index, peft_type=args.peft_type, rank=args.rank, model=args.model)
+          clip_index=args.clip_index, peft_type=args.peft_type, rank=args.rank, model=args.model,
+          engine=getattr(args, "engine", False))
 
 
 if __name__ == "__main__":

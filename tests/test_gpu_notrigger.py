@@ -16,7 +16,7 @@ def _encoders(seed):
     return [load_text_encoders("SDXL", seed=seed, tiny=True), load_text_encoders("SDXL", seed=seed, tiny=True)]
 
 
-def _run(gold, case, precision):
+def _run(gold, case, precision, engine=False):
     from sliders_conceptmod_b200 import config_util, ops, train_notrigger
     c = gold["cases"][case]
     cfg = dict(gold["config"])
@@ -25,7 +25,7 @@ def _run(gold, case, precision):
     torch.manual_seed(c["torch_seed"])
     n0 = ops.launch_count()
     sd = train_notrigger.train(config, [], "cuda", save_file=False, clip_index=c["clip_index"], peft_type="lora", rank=4,
-                               model="SDXL", encoders=_encoders(gold["seed_model"]), **c["kw"])
+                               model="SDXL", encoders=_encoders(gold["seed_model"]), engine=engine, **c["kw"])
     return sd, c["final"], ops.launch_count() - n0
 
 
@@ -67,3 +67,17 @@ def test_dora_variant_trains(tmp_path):
     assert any("dora_scale" in k for k in sd) and all(torch.isfinite(v.float()).all() for v in sd.values())
     up = torch.cat([v.float().flatten() for k, v in sd.items() if "lora_up" in k])
     assert up.norm() > 0
+
+
+@pytest.mark.parametrize("case", ["both_te1", "both_te2", "negative_only_te1"])
+def test_engine_graph_replay_matches_reference_and_eager_loop(case):
+    """engine=True: flat parameter / fp32 gradient buffers, iterations 1.. replayed as ONE CUDA graph (forward passes,
+    objective, backward, clip, SGD) — same final state as the reference run and as the eager loop."""
+    gold = torch.load(GOLD)
+    sd_e, ref, _ = _run(gold, case, "float32", engine=True)
+    sd_p, _, _ = _run(gold, case, "float32", engine=False)
+    assert list(sd_e.keys()) == list(ref.keys())
+    for k in ref:
+        scale = ref[k].abs().max().item() + 1e-12
+        assert (sd_e[k].float().cpu() - ref[k]).abs().max().item() <= 2e-3 * scale, k
+        assert (sd_e[k].float() - sd_p[k].float()).abs().max().item() <= 1e-3 * scale, k

@@ -19,12 +19,12 @@ cfg = {"prompts_file": "unused.yaml", "pretrained_model": {"name_or_path": "stan
        "logging": {"use_wandb": False, "verbose": False}, "other": {"use_xformers": True}}
 
 
-def run(clip_index, eager, iters=30, warm=5):
+def run(clip_index, eager, iters=30, warm=5, engine=False):
     config = config_util.RootConfig(**cfg)
     torch.manual_seed(0)
     t = train_notrigger.NoTriggerTrainer(config, "cuda", clip_index=clip_index, peft_type="lora", rank=4,
                                          encoders=[load_text_encoders("SDXL", seed=1), load_text_encoders("SDXL", seed=1)],
-                                         positive=["happy", "smiling"], negative=["sad", "frowning"])
+                                         positive=["happy", "smiling"], negative=["sad", "frowning"], engine=engine)
     if eager:
         slider_oracle.attach(t.network)
     for i in range(warm):
@@ -41,7 +41,10 @@ def run(clip_index, eager, iters=30, warm=5):
 
 for ci, name in ((0, "CLIP-L 12 layers x 768"), (1, "CLIP-G 32 layers x 1280")):
     ours, launches, mods = run(ci, False)
+    eng, _, _ = run(ci, False, iters=100, engine=True)
     eager, _, _ = run(ci, True)
     print(json.dumps({"workload": f"notrigger_te{ci + 1}", "encoder": name, "lora_modules": mods, "dtype": "bf16",
-                      "iterations_per_sec": round(ours, 2), "libslider_launches_per_iteration": launches,
-                      "torch_eager_reference_arithmetic_it_per_sec": round(eager, 2), "ratio": round(ours / eager, 2)}))
+                      "iterations_per_sec_engine": round(eng, 2), "iterations_per_sec_eager_loop": round(ours, 2),
+                      "libslider_launches_per_iteration": launches,
+                      "torch_eager_reference_arithmetic_it_per_sec": round(eager, 2),
+                      "engine_over_reference_arithmetic": round(eng / eager, 2)}))
