@@ -68,9 +68,13 @@ class SyntheticTextEncoder(torch.nn.Module):
         return torch.stack(outs).to(self._anchor.device, self._anchor.dtype)
 
 
-def encode_prompts(tokenizer, text_encoder: SyntheticTextEncoder, prompts: list[str]) -> torch.Tensor:
-    """train_util.encode_prompts (:125-136) for the synthetic encoder."""
-    return text_encoder.encode(list(prompts))
+def encode_prompts(tokenizer, text_encoder, prompts: list[str]) -> torch.Tensor:
+    """train_util.encode_prompts (:123-134): the synthetic encoder maps prompt strings directly; a CLIP stand-in
+    (text_encoder.CLIPTextModel, `load_models(..., clip_stand_in=True)`) goes through tokenizer + transformer."""
+    if isinstance(text_encoder, SyntheticTextEncoder):
+        return text_encoder.encode(list(prompts))
+    from .text_encoder import encode_prompts as clip_encode_prompts
+    return clip_encode_prompts(tokenizer, text_encoder, list(prompts))
 
 
 def _family(name_or_path: str) -> str:
@@ -88,11 +92,16 @@ def _seeded_unet(cfg: UNetConfig, seed: int) -> UNet2DConditionModel:
 
 
 def load_models(pretrained_model_name_or_path: str, scheduler_name: AVAILABLE_SCHEDULERS, v2: bool = False,
-                v_pred: bool = False, weight_dtype: torch.dtype = torch.float32, seed: int = 0):
+                v_pred: bool = False, weight_dtype: torch.dtype = torch.float32, seed: int = 0,
+                clip_stand_in: bool = False):
     fam = _family(pretrained_model_name_or_path)
     cfg = {"sd14": UNetConfig.sd14, "sdxl": UNetConfig.sdxl, "tiny": UNetConfig.tiny}[fam]()
     unet = _seeded_unet(cfg, seed)
     scheduler = create_noise_scheduler(scheduler_name, prediction_type="v_prediction" if v_pred else "epsilon")
+    if clip_stand_in and fam == "sd14":       # CLIP-L architecture, random init: 768-wide states = the UNet's context width
+        from .text_encoder import load_text_encoders
+        toks, encs = load_text_encoders("SD", seed=seed)
+        return toks[0], encs[0], unet, scheduler
     return SyntheticTokenizer(), SyntheticTextEncoder(cfg.cross_attention_dim), unet, scheduler
 
 

@@ -144,7 +144,7 @@ class CLIPTextModel(nn.Module):
     def dtype(self):
         return self.text_model.final_layer_norm.weight.dtype
 
-    def forward(self, input_ids, output_hidden_states: bool = False, **_):
+    def _encode(self, input_ids, output_hidden_states):
         tm = self.text_model
         x = tm.embeddings(input_ids)
         hidden = [x]
@@ -153,8 +153,36 @@ class CLIPTextModel(nn.Module):
             hidden.append(x)
         last = _layer_norm(tm.final_layer_norm, x)
         pooled = last[torch.arange(last.shape[0], device=last.device), input_ids.argmax(dim=-1)]   # EOS = highest id
-        return SimpleNamespace(last_hidden_state=last, pooler_output=pooled,
-                               hidden_states=tuple(hidden) if output_hidden_states else None)
+        return last, pooled, (tuple(hidden) if output_hidden_states else None)
+
+    def forward(self, input_ids, output_hidden_states: bool = False, **_):
+        last, pooled, hidden = self._encode(input_ids, output_hidden_states)
+        return TextModelOutput(("last_hidden_state", "pooler_output"), last_hidden_state=last, pooler_output=pooled,
+                               hidden_states=hidden)
+
+
+class TextModelOutput(SimpleNamespace):
+    """Attribute access plus the positional indexing of transformers' ModelOutput (`out[0]`)."""
+
+    def __init__(self, order, **kw):
+        super().__init__(**kw)
+        self._order = order
+
+    def __getitem__(self, i):
+        return getattr(self, self._order[i])
+
+
+class CLIPTextModelWithProjection(CLIPTextModel):
+    """SD-XL's second encoder: `out[0]` = text_embeds = text_projection(pooled) (train_util.py:147-150 reads it)."""
+
+    def __init__(self, cfg: CLIPTextConfig, projection_dim: int | None = None):
+        super().__init__(cfg)
+        self.text_projection = nn.Linear(cfg.hidden_size, projection_dim or cfg.hidden_size, bias=False)
+
+    def forward(self, input_ids, output_hidden_states: bool = False, **_):
+        last, pooled, hidden = self._encode(input_ids, output_hidden_states)
+        return TextModelOutput(("text_embeds", "last_hidden_state"), text_embeds=self.text_projection(pooled),
+                               last_hidden_state=last, hidden_states=hidden)
 
 
 class HashTokenizer:
@@ -192,5 +220,37 @@ def load_text_encoders(model: str = "SDXL", seed: int = 0, tiny: bool = False):
         cfgs = cfgs[:1]
     with torch.random.fork_rng(devices=[]):
         torch.manual_seed(seed)
-        encoders = [CLIPTextModel(c) for c in cfgs]
+        # SD-XL: text_encoder is a CLIPTextModel, text_encoder_2 a CLIPTextModelWithProjection
+        encoders = [CLIPTextModel(c) if i == 0 else CLIPTextModelWithProjection(c) for i, c in enumerate(cfgs)]
     return [HashTokenizer(c.vocab_size) for c in cfgs], encoders
+
+
+def text_encode(text_encoder, tokens):
+    """conceptmod/textsliders/train_util.py:119-120."""
+    return text_encoder(tokens.to(text_encoder.device))[0]
+
+
+def encode_prompts(tokenizer, text_encoder, prompts: list[str]):
+    """train_util.py:123-134."""
+    return text_encode(text_encoder, text_tokenize(tokenizer, prompts))
+
+
+def text_encode_xl(text_encoder, tokens, num_images_per_prompt: int = 1):
+    """train_util.py:138-154: penultimate hidden state + `out[0]` (the projected pooled embedding for text_encoder_2)."""
+    out = text_encoder(tokens.to(text_encoder.device), output_hidden_states=True)
+    pooled = out[0]
+    embeds = out.hidden_states[-2]
+    bs, seq, _ = embeds.shape
+    embeds = embeds.repeat(1, num_images_per_prompt, 1).view(bs * num_images_per_prompt, seq, -1)
+    return embeds, pooled
+
+
+def encode_prompts_xl(tokenizers, text_encoders, prompts: list[str], num_images_per_prompt: int = 1):
+    """train_util.py:224-247: both encoders' penultimate states concatenated on the feature axis, text_encoder_2's pool."""
+    parts, pooled = [], None
+    for tokenizer, text_encoder in zip(tokenizers, text_encoders):
+        embeds, pooled = text_encode_xl(text_encoder, text_tokenize(tokenizer, prompts), num_images_per_prompt)
+        parts.append(embeds)
+    bs = pooled.shape[0]
+    pooled = pooled.repeat(1, num_images_per_prompt).view(bs * num_images_per_prompt, -1)
+    return torch.concat(parts, dim=-1), pooled

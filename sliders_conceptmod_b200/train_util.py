@@ -181,3 +181,8 @@ def get_random_resolution_in_bucket(bucket_resolution: int = 512) -> tuple[int, 
     height = torch.randint(min_step, max_step, (1,)).item() * 64
     width = torch.randint(min_step, max_step, (1,)).item() * 64
     return height, width
+
+
+# prompt encoding on a CLIP text model (reference train_util.py:108-154, 224-247) — see text_encoder.py
+from .text_encoder import (encode_prompts, encode_prompts_xl, text_encode, text_encode_xl,  # noqa: E402,F401
+                           text_tokenize)

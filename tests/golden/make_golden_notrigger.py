@@ -14,7 +14,8 @@ What is substituted (cannot exist here: no diffusers, no pretrained weights, no 
   debug_util / wandb        -> empty stubs
 
 Pinned: the LoRA state dict returned by train(save_file=False) after ITERATIONS iterations for three cases (both
-sides, positive only, negative only), and fixed_distance_loss on a random triple.
+sides, positive only, negative only) on both encoders, fixed_distance_loss on a random triple, and the outputs of the
+reference's text_tokenize / encode_prompts / encode_prompts_xl on the stand-ins.
 """
 import importlib.util
 import sys
@@ -93,6 +94,17 @@ def main():
     val = ref.fixed_distance_loss(a, b, d)
     grad, = torch.autograd.grad(val, a)
     out["fixed_distance"] = {"a": a.detach(), "b": b, "d": d, "value": val.detach(), "grad": grad}
+    # prompt encoding (conceptmod/textsliders/train_util.py:108-154, 224-247) by the reference's own functions
+    toks, encs = te.load_text_encoders("SDXL", seed=SEED_MODEL, tiny=True)
+    for e in encs:
+        e.eval()
+    prompts = ["a photo of a person", "old person, wrinkles"]
+    with torch.no_grad():
+        xl_embeds, xl_pooled = ref.train_util.encode_prompts_xl(toks, encs, prompts, num_images_per_prompt=2)
+        sd_embeds = ref.train_util.encode_prompts(toks[0], encs[0], prompts)
+    out["encode"] = {"prompts": prompts, "tokens": ref.train_util.text_tokenize(toks[0], prompts), "xl_embeds": xl_embeds,
+                     "xl_pooled": xl_pooled, "sd_embeds": sd_embeds}
+    print("encode_prompts_xl", tuple(xl_embeds.shape), tuple(xl_pooled.shape), "encode_prompts", tuple(sd_embeds.shape))
     torch.save(out, HERE / "reference_notrigger.pt")
     print("wrote", HERE / "reference_notrigger.pt")
 

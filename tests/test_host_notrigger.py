@@ -73,3 +73,19 @@ def test_other_model_families_are_rejected():
     gold = torch.load(GOLD)
     with pytest.raises(NotImplementedError):
         train_notrigger.train(config_util.RootConfig(**gold["config"]), [], "cpu", model="FLUX.1", positive=["x"])
+
+
+def test_prompt_encoding_matches_reference_functions(gold):
+    """text_tokenize / encode_prompts / encode_prompts_xl (train_util.py:108-154, 224-247) on the CLIP stand-ins."""
+    from sliders_conceptmod_b200 import text_encoder as te
+    enc = gold["encode"]
+    toks, encs = te.load_text_encoders("SDXL", seed=gold["seed_model"], tiny=True)
+    for e in encs:
+        e.eval()
+    assert torch.equal(te.text_tokenize(toks[0], enc["prompts"]), enc["tokens"])
+    with torch.no_grad():
+        xl_embeds, xl_pooled = te.encode_prompts_xl(toks, encs, enc["prompts"], num_images_per_prompt=2)
+        sd_embeds = te.encode_prompts(toks[0], encs[0], enc["prompts"])
+    assert xl_embeds.shape == (4, 77, 64 + 128) and xl_pooled.shape == (4, 128)
+    assert torch.equal(xl_embeds, enc["xl_embeds"]) and torch.equal(xl_pooled, enc["xl_pooled"])
+    assert torch.equal(sd_embeds, enc["sd_embeds"])
