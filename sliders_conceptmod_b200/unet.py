@@ -101,6 +101,7 @@ class TimestepEmbedding(nn.Module):
 # A/B switch for measurements: SLIDER_DISABLE=residual,qkv,kvcache turns individual host-level fusions off
 _DISABLED = set(filter(None, os.environ.get("SLIDER_DISABLE", "").split(",")))
 _ENABLED = set(filter(None, os.environ.get("SLIDER_ENABLE", "").split(",")))
+_PLAIN_MAX_FLOP = float(os.environ.get("SLIDER_PLAIN_MAX_GFLOP", "8")) * 1e9
 
 
 _TORCH_ONLY = False
@@ -211,9 +212,9 @@ def fused_linear(mod: nn.Module, x: torch.Tensor, residual: torch.Tensor | None 
     """`mod(x)` (+ `residual`) for an nn.Linear on [..., K] or a 1x1 nn.Conv2d on [B,C,H,W].
 
     On no-grad CUDA forwards every such projection of the UNet runs in libslider's tcgen05 GEMM: LoRA-wrapped modules
-    through their patched forward (adapter fused); frozen un-wrapped 1x1 convolutions (proj_in / proj_out) through the
-    same kernel's plain path; frozen un-wrapped nn.Linear (attn2, feed-forward — SURVEY 8 f1) stay on cuBLAS unless
-    SLIDER_ENABLE=plain (all) / plainres (those with a residual).  With `residual` the sum is formed by the kernel's store IN PLACE of
+    through their patched forward (adapter fused); frozen un-wrapped 1x1 convolutions (proj_in / proj_out) and frozen
+    un-wrapped nn.Linear (attn2.to_q / to_out, the second feed-forward Linear — SURVEY 8 f1) through the same kernel's
+    plain path (SLIDER_DISABLE=plain: cuBLAS).  With `residual` the sum is formed by the kernel's store IN PLACE of
     `residual` (TMA reduce-add) instead of an elementwise kernel — callers pass a `residual` nobody else reads
     afterwards.  Everything else (CPU oracle, grad-recording forward) is the plain PyTorch expression."""
     fused = _no_grad_cuda(x, residual) and x.dtype == mod.weight.dtype
@@ -225,16 +226,24 @@ def fused_linear(mod: nn.Module, x: torch.Tensor, residual: torch.Tensor | None 
             if out is not None:
                 return out
         fused = False
-    # frozen un-wrapped projections.  nn.Linear: cuBLAS (bias in its epilogue) is measured faster per denoise forward
-    # than the plain path of the fused kernel on these small shapes (tools/ab_fusions.sh), so that routing is opt-in
-    # (SLIDER_ENABLE=plain).  1x1 nn.Conv2d (proj_in / proj_out of SD 1.x): cuDNN runs a GEMM plus a separate bias
-    # kernel, and the residual is a third launch — the plain path does all three in one (SLIDER_DISABLE=plainconv).
-    if fused and lora is None and not mod.weight.requires_grad:
+    # frozen un-wrapped projections go through the plain path of the fused kernel (bias and residual in its store).
+    # nn.Linear (attn2.to_q / to_out, the second feed-forward Linear): r01 measured cuBLAS faster on these small shapes
+    # (tools/ab_fusions.sh); with the narrow tile, the fold epilogue and the in-store residual of r02 the fused kernel
+    # wins three interleaved A/B rounds by 0.5-1.7 % of the step (profiles/r02_ab_plain_linear.txt) and the 32
+    # residual add kernels per forward disappear — SLIDER_DISABLE=plain puts them back on cuBLAS (+ add).  1x1
+    # nn.Conv2d (proj_in / proj_out of SD 1.x): cuDNN runs a GEMM plus a separate bias kernel, and the residual is a
+    # third launch — the plain path does all three in one (SLIDER_DISABLE=plainconv).
+    # (a module whose forward is patched by ANY adapter class — LoRAModule registers itself above, DoRAModule does
+    # not — must keep that forward)
+    if fused and lora is None and not mod.weight.requires_grad and "forward" not in mod.__dict__:
         res = residual if "residual" not in _DISABLED else None
-        if isinstance(mod, nn.Linear) and ("plain" in _ENABLED or (res is not None and "plainres" in _ENABLED)):
+        if isinstance(mod, nn.Linear) and "plain" not in _DISABLED:
             K, N = mod.in_features, mod.out_features
             x2 = x.reshape(-1, K)
-            ok = x2.shape[0] > 16 and K % 8 == 0 and N % 8 == 0 and (res is None or res.is_contiguous())
+            # up to ~8 GFLOP per launch (every such layer of SD 1.x); the 27-GFLOP feed-forward Linear of SD-XL is
+            # faster on cuBLAS + add (SD-XL step 4.54 -> 4.44 steps/s with everything routed here)
+            ok = (x2.shape[0] > 16 and K % 8 == 0 and N % 8 == 0 and (res is None or res.is_contiguous())
+                  and 2.0 * x2.shape[0] * K * N <= _PLAIN_MAX_FLOP)
             if ok:
                 if not x2.is_contiguous():
                     x2 = x2.contiguous()
