@@ -29,6 +29,9 @@ for shape in [(2, 64, 64, 320), (2, 64, 64, 960), (2, 32, 32, 640), (2, 16, 16, 
     h.slider_debug_gn_trace(None)
     t = buf.view(-1, 8).cpu()
     t = t[t[:, 0] > 0].double()
+    if t.numel() == 0:
+        print(shape, "takes the two-kernel form (no single-launch plan): no trace")
+        continue
     span = (t[:, 7].max() - t[:, 0].min()).item() / 1e3
     start_spread = (t[:, 0].max() - t[:, 0].min()).item() / 1e3
     d = (t[:, 1:] - t[:, :-1]) / 1e3
