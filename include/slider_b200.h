@@ -400,6 +400,18 @@ int slider_upsample_nearest2x_nhwc(void* y, const void* x, int batch, int height
 int slider_concat_channels_nhwc(void* y, const void* a, const void* b, int64_t pixels, int channels_a, int channels_b,
                                 int dtype, void* stream);
 
+/*
+ * Cross-attention core for short key sets: o = softmax(q k^T / sqrt(head_dim)) v per (batch, head), kv_len <= 80 (the
+ * 77 prompt tokens of the UNet's attn2 layers; UNet calls at train_util.py:290-294, diffusers Attention with
+ * encoder_hidden_states).  q, o: [batch, q_len, heads * head_dim], k, v: [batch, kv_len, heads * head_dim]
+ * — the layout the q / k / v / out projections produce and consume, no head transposes.  16-bit storage (SLIDER_BF16 /
+ * SLIDER_F16), fp32 accumulation and softmax; head_dim a multiple of 8 up to 160.  kv_static != 0 promises that k and v
+ * are not written by any kernel still in flight on the stream (cached per prompt), so they are staged before the
+ * dependent-launch wait.  No-grad forwards only (no backward form).  SLIDER_ERR_BAD_ARG outside these limits.
+ */
+int slider_cross_attention(void* o, const void* q, const void* k, const void* v, int batch, int q_len, int kv_len,
+                           int heads, int head_dim, int dtype, int kv_static, void* stream);
+
 /* x *= *dev_scalar  (chain rule for a non-unit upstream loss gradient). */
 int slider_scale_by_device_scalar(void* x, const float* dev_scalar,
                                   int64_t n_elem, int dtype, void* stream);

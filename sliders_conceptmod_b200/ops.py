@@ -387,6 +387,20 @@ def concat_channels_nhwc(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
     return y
 
 
+def cross_attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int, kv_static: bool = False) -> torch.Tensor:
+    """softmax(q k^T / sqrt(d)) v per head for q [B, L, H*d], k / v [B, S <= 80, H*d] (contiguous, 16-bit): the attn2
+    core with the 77 prompt tokens resident in shared memory; returns o [B, L, H*d] (no head transposes)."""
+    require_cuda(q, k, v)
+    assert q.is_contiguous() and k.is_contiguous() and v.is_contiguous() and q.dtype == k.dtype == v.dtype
+    B, L, HD = q.shape
+    S = k.shape[1]
+    assert k.shape == v.shape == (B, S, HD) and HD % heads == 0
+    o = torch.empty_like(q)
+    check(lib().slider_cross_attention(ptr(o), ptr(q), ptr(k), ptr(v), int(B), int(L), int(S), int(heads), int(HD // heads),
+                                       dtype_code(q.dtype), int(bool(kv_static)), stream_ptr()))
+    return o
+
+
 def launch_count() -> int:
     return int(lib().slider_launch_count())
 

@@ -1,0 +1,95 @@
+"""Cross-attention core for short key sets (slider_cross_attention) against fp32 softmax attention."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+# (batch, queries, keys, heads, head_dim): the attn2 layers of SD-1.4 (8 heads, d = 40 / 80 / 160), SD-XL (d = 64), ragged
+CASES = [(2, 4096, 77, 8, 40), (2, 1024, 77, 8, 80), (2, 256, 77, 8, 160), (2, 64, 77, 8, 160), (6, 1024, 77, 8, 80),
+         (2, 4096, 77, 10, 64), (2, 1024, 77, 20, 64), (1, 100, 77, 4, 48), (3, 65, 5, 2, 8), (1, 1, 80, 1, 128),
+         (2, 300, 1, 3, 24)]
+
+
+def _ref(q, k, v, heads):
+    B, L, HD = q.shape
+    d = HD // heads
+    qf, kf, vf = (t.float().view(B, -1, heads, d).transpose(1, 2) for t in (q, k, v))
+    p = torch.softmax(qf @ kf.transpose(-1, -2) / d ** 0.5, dim=-1)
+    return (p @ vf).transpose(1, 2).reshape(B, L, HD)
+
+
+@pytest.mark.parametrize("case", CASES)
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("kv_static", [False, True])
+def test_cross_attention_matches_fp32_softmax_attention(case, dtype, kv_static):
+    from sliders_conceptmod_b200 import ops
+    B, L, S, H, d = case
+    g = torch.Generator(device="cuda").manual_seed(L * 7 + S + d)
+    q = (torch.randn(B, L, H * d, device="cuda", generator=g) * 1.5).to(dtype)
+    k = (torch.randn(B, S, H * d, device="cuda", generator=g) * 1.5).to(dtype)
+    v = torch.randn(B, S, H * d, device="cuda", generator=g).to(dtype)
+    o = ops.cross_attention(q, k, v, H, kv_static=kv_static)
+    ref = _ref(q, k, v, H)
+    assert o.shape == q.shape and o.dtype == dtype
+    tol = 2e-2 if dtype == torch.bfloat16 else 4e-3            # P and o are rounded to the storage type
+    err = (o.float() - ref).abs().max().item()
+    assert err <= tol * max(1.0, ref.abs().max().item()), f"max err {err}"
+    # against the library kernel at the same precision: same order of error
+    lib = torch.nn.functional.scaled_dot_product_attention(
+        *(t.view(B, -1, H, d).transpose(1, 2) for t in (q, k, v))).transpose(1, 2).reshape(B, L, H * d)
+    assert err <= 2.0 * (lib.float() - ref).abs().max().item() + 1e-3
+
+
+def test_peaked_softmax_and_masked_tail():
+    """One key dominates (large logits): no overflow, and the zero rows behind kv_len take no weight."""
+    from sliders_conceptmod_b200 import ops
+    B, L, S, H, d = 1, 70, 77, 2, 40
+    q = torch.zeros(B, L, H * d, device="cuda", dtype=torch.bfloat16)
+    k = torch.zeros(B, S, H * d, device="cuda", dtype=torch.bfloat16)
+    v = torch.randn(B, S, H * d, device="cuda").bfloat16()
+    q[..., 0] = 30.0; q[..., d] = 30.0
+    k[:, 5, 0] = 30.0; k[:, 9, d] = 30.0                       # head 0 attends key 5, head 1 key 9
+    o = ops.cross_attention(q, k, v, H)
+    assert torch.isfinite(o.float()).all()
+    assert torch.allclose(o[0, :, :d].float(), v[0, 5, :d].float().expand(L, d), atol=1e-2)
+    assert torch.allclose(o[0, :, d:].float(), v[0, 9, d:].float().expand(L, d), atol=1e-2)
+    # uniform attention (all logits equal) = the mean of the LIVE keys only
+    q.zero_()
+    o = ops.cross_attention(q, k, v, H)
+    assert torch.allclose(o[0, 0].float(), v[0].float().mean(0), atol=2e-2)
+
+
+def test_limits_are_reported():
+    from sliders_conceptmod_b200 import ops
+    q = torch.zeros(1, 8, 64, device="cuda", dtype=torch.bfloat16)
+    kv = torch.zeros(1, 81, 64, device="cuda", dtype=torch.bfloat16)
+    with pytest.raises(RuntimeError, match="keys"):
+        ops.cross_attention(q, kv, kv, 2)
+    with pytest.raises(Exception):
+        ops.cross_attention(q.float(), kv[:, :77].float(), kv[:, :77].float(), 2)
+
+
+def test_unet_attention_layer_uses_it_and_matches_the_library_path():
+    """Attention.forward with a 77-token context on a no-grad bf16 forward: same result as the SDPA route."""
+    import importlib
+    from sliders_conceptmod_b200 import ops, unet
+    torch.manual_seed(0)
+    att = unet.Attention(320, 768, 8, 40).cuda().bfloat16().requires_grad_(False)
+    x = torch.randn(2, 1024, 320, device="cuda").bfloat16()
+    ctx = torch.randn(2, 77, 768, device="cuda").bfloat16()
+    calls = []
+    real = ops.cross_attention
+    ops.cross_attention = lambda *a, **k: (calls.append(1), real(*a, **k))[1]
+    try:
+        with torch.no_grad():
+            y = att(x, ctx)
+    finally:
+        ops.cross_attention = real
+    assert calls, "the attn2 layer did not take the short-key cross-attention kernel"
+    unet._DISABLED.add("xattn")
+    try:
+        with torch.no_grad():
+            y_lib = att(x, ctx)
+    finally:
+        unet._DISABLED.discard("xattn")
+    assert (y.float() - y_lib.float()).abs().max().item() <= 3e-2 * max(1.0, y_lib.float().abs().max().item())
