@@ -412,6 +412,16 @@ int slider_concat_channels_nhwc(void* y, const void* a, const void* b, int64_t p
 int slider_cross_attention(void* o, const void* q, const void* k, const void* v, int batch, int q_len, int kv_len,
                            int heads, int head_dim, int dtype, int kv_static, void* stream);
 
+/*
+ * The same kernel with explicit row strides (elements): row r of batch item b of a tensor with stride ld starts at
+ * (b * len + r) * ld — dense [batch, len, heads * head_dim] tensors (ld = heads * head_dim) or the q / k / v views of one
+ * fused [batch, len, 3 * heads * head_dim] projection (ld = 3 * heads * head_dim; the 64-token self-attention of the
+ * 8 x 8 level).  Strides are multiples of 8 elements and >= heads * head_dim.
+ */
+int slider_cross_attention_strided(void* o, const void* q, const void* k, const void* v, int batch, int q_len, int kv_len,
+                                   int heads, int head_dim, int ldq, int ldk, int ldv, int ldo, int dtype, int kv_static,
+                                   void* stream);
+
 /* x *= *dev_scalar  (chain rule for a non-unit upstream loss gradient). */
 int slider_scale_by_device_scalar(void* x, const float* dev_scalar,
                                   int64_t n_elem, int dtype, void* stream);

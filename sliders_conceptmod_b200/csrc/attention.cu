@@ -51,7 +51,7 @@ __device__ __forceinline__ void xa_ldmatrix_x2_trans(uint32_t addr, uint32_t (&r
 
 struct XaParams {
   int B, L, S, H, D;      // batch, queries, keys, heads, head dim
-  int ld;                 // row stride of q / k / v / o in elements (= H * D)
+  int ldq, ldk, ldv, ldo; // row strides in elements (H * D for dense tensors; 3 * H * D for the views of a fused q/k/v launch)
   float scale_log2;       // log2(e) / sqrt(D)
   int kv_static;          // k / v are not written by any kernel in flight: stage them before the dependent-launch wait
 };
@@ -85,9 +85,9 @@ cross_attention_kernel(T* __restrict__ o, const T* __restrict__ q, const T* __re
         const int r = i / VPR, c = i - r * VPR;
         kk[u] = make_uint4(0u, 0u, 0u, 0u); vv[u] = kk[u];
         if (i < N && r < p.S && c < dv) {
-          const size_t off = ((size_t)b * p.S + r) * p.ld + (size_t)h * p.D + c * 8;
-          kk[u] = *reinterpret_cast<const uint4*>(k + off);
-          vv[u] = *reinterpret_cast<const uint4*>(v + off);
+          const size_t row = (size_t)b * p.S + r, col = (size_t)h * p.D + c * 8;
+          kk[u] = *reinterpret_cast<const uint4*>(k + row * p.ldk + col);
+          vv[u] = *reinterpret_cast<const uint4*>(v + row * p.ldv + col);
         }
       }
 #pragma unroll
@@ -114,7 +114,7 @@ cross_attention_kernel(T* __restrict__ o, const T* __restrict__ q, const T* __re
         const int r = i / VPR, c = i - r * VPR;
         qq[u] = make_uint4(0u, 0u, 0u, 0u);
         if (i < N && q0 + r < p.L && c < dv)
-          qq[u] = *reinterpret_cast<const uint4*>(q + ((size_t)b * p.L + q0 + r) * p.ld + (size_t)h * p.D + c * 8);
+          qq[u] = *reinterpret_cast<const uint4*>(q + ((size_t)b * p.L + q0 + r) * p.ldq + (size_t)h * p.D + c * 8);
       }
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
@@ -181,8 +181,8 @@ cross_attention_kernel(T* __restrict__ o, const T* __restrict__ q, const T* __re
 
   // ---- O = P V, one 8-wide slice of the head dim at a time
   const int row0 = q0 + warp * 16 + g, row1 = row0 + 8;
-  T* o0 = o + ((size_t)b * p.L + row0) * p.ld + (size_t)h * p.D;
-  T* o1 = o + ((size_t)b * p.L + row1) * p.ld + (size_t)h * p.D;
+  T* o0 = o + ((size_t)b * p.L + row0) * p.ldo + (size_t)h * p.D;
+  T* o1 = o + ((size_t)b * p.L + row1) * p.ldo + (size_t)h * p.D;
 #pragma unroll
   for (int jd = 0; jd < DP / 8; ++jd) {
     if (jd * 8 >= p.D) break;                     // padded columns (uniform over the CTA)
@@ -198,6 +198,7 @@ cross_attention_kernel(T* __restrict__ o, const T* __restrict__ q, const T* __re
     if (row1 < p.L) *reinterpret_cast<uint32_t*>(o1 + d) = Elem<T>::pack2(acc[2] * inv1, acc[3] * inv1);
   }
 }
+
 
 template <typename T, int DS>
 static int launch_xattn(void* o, const void* q, const void* k, const void* v, const XaParams& p, cudaStream_t st) {
@@ -228,24 +229,42 @@ static int xattn_dispatch(void* o, const void* q, const void* k, const void* v, 
 
 using namespace slider;
 
-extern "C" int slider_cross_attention(void* o, const void* q, const void* k, const void* v, int batch, int q_len,
-                                      int kv_len, int heads, int head_dim, int dtype, int kv_static, void* stream) {
-  SLIDER_CHECK_ARG(o && q && k && v, "cross_attention: null pointer");
-  SLIDER_CHECK_ARG(batch > 0 && q_len > 0 && heads > 0, "cross_attention: empty shape");
-  SLIDER_CHECK_ARG(kv_len >= 1 && kv_len <= XA_KEYS, "cross_attention: %d keys (this kernel serves 1..%d; longer key sets are "
-                   "the library attention's job)", kv_len, XA_KEYS);
-  SLIDER_CHECK_ARG(head_dim >= 8 && head_dim <= 160 && head_dim % 8 == 0, "cross_attention: head dim %d not a multiple of 8 in 8..160",
+static int attention_entry(void* o, const void* q, const void* k, const void* v, int batch, int q_len, int kv_len,
+                           int heads, int head_dim, int ldq, int ldk, int ldv, int ldo, int dtype, int kv_static,
+                           void* stream, const char* who) {
+  SLIDER_CHECK_ARG(o && q && k && v, "%s: null pointer", who);
+  SLIDER_CHECK_ARG(batch > 0 && q_len > 0 && heads > 0, "%s: empty shape", who);
+  SLIDER_CHECK_ARG(kv_len >= 1 && kv_len <= XA_KEYS, "%s: %d keys (this kernel serves 1..%d resident keys; longer key sets are "
+                   "the library attention's job)", who, kv_len, XA_KEYS);
+  SLIDER_CHECK_ARG(head_dim >= 8 && head_dim <= 160 && head_dim % 8 == 0, "%s: head dim %d not a multiple of 8 in 8..160", who,
                    head_dim);
-  SLIDER_CHECK_ARG(batch * heads <= 65535, "cross_attention: batch * heads = %d exceeds the grid limit", batch * heads);
-  SLIDER_CHECK_ARG((((uintptr_t)o | (uintptr_t)q | (uintptr_t)k | (uintptr_t)v) & 15) == 0,
-                   "cross_attention: pointers must be 16-byte aligned");
+  SLIDER_CHECK_ARG(batch * heads <= 65535, "%s: batch * heads = %d exceeds the grid limit", who, batch * heads);
+  const int hd = heads * head_dim;
+  SLIDER_CHECK_ARG(ldq >= hd && ldk >= hd && ldv >= hd && ldo >= hd && ((ldq | ldk | ldv | ldo) & 7) == 0,
+                   "%s: row strides must be >= heads * head_dim and multiples of 8 elements", who);
+  SLIDER_CHECK_ARG((((uintptr_t)o | (uintptr_t)q | (uintptr_t)k | (uintptr_t)v) & 15) == 0, "%s: pointers must be 16-byte aligned", who);
   XaParams p;
-  p.B = batch; p.L = q_len; p.S = kv_len; p.H = heads; p.D = head_dim; p.ld = heads * head_dim;
+  p.B = batch; p.L = q_len; p.S = kv_len; p.H = heads; p.D = head_dim;
+  p.ldq = ldq; p.ldk = ldk; p.ldv = ldv; p.ldo = ldo;
   p.scale_log2 = 1.4426950408889634f / sqrtf((float)head_dim);
   p.kv_static = kv_static ? 1 : 0;
   cudaStream_t st = (cudaStream_t)stream;
   if (dtype == SLIDER_BF16) return xattn_dispatch<__nv_bfloat16>(o, q, k, v, p, st);
   if (dtype == SLIDER_F16) return xattn_dispatch<__half>(o, q, k, v, p, st);
-  set_error("cross_attention: unsupported dtype %d (16-bit storage only)", dtype);
+  set_error("%s: unsupported dtype %d (16-bit storage only)", who, dtype);
   return SLIDER_ERR_UNSUPPORTED;
+}
+
+extern "C" int slider_cross_attention(void* o, const void* q, const void* k, const void* v, int batch, int q_len,
+                                      int kv_len, int heads, int head_dim, int dtype, int kv_static, void* stream) {
+  const int hd = heads * head_dim;
+  return attention_entry(o, q, k, v, batch, q_len, kv_len, heads, head_dim, hd, hd, hd, hd, dtype, kv_static, stream,
+                         "cross_attention");
+}
+
+extern "C" int slider_cross_attention_strided(void* o, const void* q, const void* k, const void* v, int batch, int q_len,
+                                              int kv_len, int heads, int head_dim, int ldq, int ldk, int ldv, int ldo,
+                                              int dtype, int kv_static, void* stream) {
+  return attention_entry(o, q, k, v, batch, q_len, kv_len, heads, head_dim, ldq, ldk, ldv, ldo, dtype, kv_static, stream,
+                         "cross_attention_strided");
 }

@@ -401,6 +401,43 @@ def cross_attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: in
     return o
 
 
+def _rows_ld(t: torch.Tensor):
+    """Row stride (elements) of a [B, len, C] tensor whose rows are dense and whose batch items follow each other at
+    len * stride(1) — a dense tensor or a last-dim slice of one; None otherwise."""
+    if t.dim() != 3 or t.stride(2) != 1 or t.stride(1) % 8 or (t.shape[0] > 1 and t.stride(0) != t.shape[1] * t.stride(1)):
+        return None
+    return int(t.stride(1))
+
+
+def attention_usable(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int, max_keys: int = 80) -> bool:
+    if not (q.is_cuda and q.dtype in (torch.bfloat16, torch.float16) and q.dtype == k.dtype == v.dtype):
+        return False
+    d = q.shape[-1] // heads
+    return (d % 8 == 0 and 8 <= d <= 160 and q.shape[-1] == heads * d and k.shape[1] <= min(max_keys, 80) and q.shape[0] * heads <= 65535
+            and all(_rows_ld(t) is not None and t.data_ptr() % 16 == 0 for t in (q, k, v)))
+
+
+def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int, kv_static: bool = False) -> torch.Tensor:
+    """softmax(q k^T / sqrt(d)) v per head for q [B, L, H*d], k / v [B, S <= 80, H*d] (dense, or the views of one fused
+    q/k/v projection), every key resident in shared memory.  Returns a dense o [B, L, H*d]."""
+    require_cuda(q, k, v)
+    B, L, HD = q.shape
+    S = k.shape[1]
+    assert k.shape == v.shape == (B, S, HD) and HD % heads == 0
+    o = torch.empty(B, L, HD, device=q.device, dtype=q.dtype)
+    if S <= 80 and q.is_contiguous() and k.is_contiguous() and v.is_contiguous():
+        check(lib().slider_cross_attention(ptr(o), ptr(q), ptr(k), ptr(v), int(B), int(L), int(S), int(heads), int(HD // heads),
+                                           dtype_code(q.dtype), int(bool(kv_static)), stream_ptr()))
+        return o
+    lds = [_rows_ld(t) for t in (q, k, v)]
+    if any(ld is None for ld in lds):
+        raise ValueError("attention: q / k / v must be [B, len, C] with dense rows (a dense tensor or a last-dim slice of one)")
+    check(lib().slider_cross_attention_strided(ptr(o), ptr(q), ptr(k), ptr(v), int(B), int(L), int(S), int(heads),
+                                               int(HD // heads), lds[0], lds[1], lds[2], int(HD), dtype_code(q.dtype),
+                                               int(bool(kv_static)), stream_ptr()))
+    return o
+
+
 def launch_count() -> int:
     return int(lib().slider_launch_count())
 

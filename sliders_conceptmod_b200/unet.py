@@ -399,13 +399,13 @@ class Attention(nn.Module):
             q, k, v = grp.forward(x)
         else:
             q, k, v = fused_linear(self.to_q, x), fused_linear(self.to_k, ctx), fused_linear(self.to_v, ctx)
-        if (context is not None and ctx.shape[1] <= 80 and "xattn" not in _DISABLED and _no_grad_cuda(q, k, v)
-                and q.dtype in (torch.bfloat16, torch.float16) and q.dtype == k.dtype == v.dtype
-                and (q.shape[-1] // self.heads) % 8 == 0 and q.shape[-1] // self.heads <= 160
-                and q.is_contiguous() and k.is_contiguous() and v.is_contiguous() and B * self.heads <= 65535):
-            # attn2 with the prompt tokens: every key of a head sits in shared memory (one S tile, one softmax), q / k / v /
-            # o stay in the [B, L, heads * d] layout of the projections — no head transposes, no transposing copy of o
-            o = ops.cross_attention(q, k, v, self.heads, kv_static=hit is not None)
+        if "xattn" not in _DISABLED and _no_grad_cuda(q, k, v) and ops.attention_usable(q, k, v, self.heads):
+            # up to 80 keys (attn2 with the 77 prompt tokens; the 64-token self-attention of the 8 x 8 level): every key
+            # of a head resident in shared memory — one S tile, one softmax — and q / k / v / o in the [B, L, heads * d]
+            # layout of the projections (no head transposes, no transposing copy of o).  Longer key sets stay on the
+            # library kernels: a key-block loop on mma.sync measured 51 vs 16 us at 1024 keys
+            # (profiles/r02_ab_cross_attention.txt)
+            o = ops.attention(q, k, v, self.heads, kv_static=hit is not None)
         else:
             q = q.view(B, L, self.heads, -1).transpose(1, 2)
             k = k.view(B, ctx.shape[1], self.heads, -1).transpose(1, 2)

@@ -78,13 +78,13 @@ def test_unet_attention_layer_uses_it_and_matches_the_library_path():
     x = torch.randn(2, 1024, 320, device="cuda").bfloat16()
     ctx = torch.randn(2, 77, 768, device="cuda").bfloat16()
     calls = []
-    real = ops.cross_attention
-    ops.cross_attention = lambda *a, **k: (calls.append(1), real(*a, **k))[1]
+    real = ops.attention
+    ops.attention = lambda *a, **k: (calls.append(1), real(*a, **k))[1]
     try:
         with torch.no_grad():
             y = att(x, ctx)
     finally:
-        ops.cross_attention = real
+        ops.attention = real
     assert calls, "the attn2 layer did not take the short-key cross-attention kernel"
     unet._DISABLED.add("xattn")
     try:
@@ -92,4 +92,42 @@ def test_unet_attention_layer_uses_it_and_matches_the_library_path():
             y_lib = att(x, ctx)
     finally:
         unet._DISABLED.discard("xattn")
+    assert (y.float() - y_lib.float()).abs().max().item() <= 3e-2 * max(1.0, y_lib.float().abs().max().item())
+
+
+
+def test_strided_views_of_a_fused_projection():
+    """The 64-token self-attention of the 8 x 8 level: q / k / v are last-dim slices of one [B, L, 3 * H * d] tensor."""
+    from sliders_conceptmod_b200 import ops
+    B, L, H, d = 2, 64, 8, 160
+    qkv = torch.randn(B, L, 3 * H * d, device="cuda").bfloat16()
+    q, k, v = qkv.split(H * d, dim=-1)
+    assert ops.attention_usable(q, k, v, H)
+    o = ops.attention(q, k, v, H)
+    ref = _ref(q, k, v, H)
+    assert o.is_contiguous() and (o.float() - ref).abs().max().item() <= 2e-2 * max(1.0, ref.abs().max().item())
+    assert not ops.attention_usable(qkv[:, :, :H * d], torch.zeros(B, 81, H * d, device="cuda").bfloat16(),
+                                    torch.zeros(B, 81, H * d, device="cuda").bfloat16(), H)
+
+
+def test_self_attention_layer_routes_by_key_count():
+    """Attention.forward without context: 64 keys -> libslider, 256 keys -> library SDPA."""
+    from sliders_conceptmod_b200 import ops, unet
+    torch.manual_seed(1)
+    att = unet.Attention(1280, None, 8, 160).cuda().bfloat16().requires_grad_(False)
+    calls = []
+    real = ops.attention
+    ops.attention = lambda *a, **k: (calls.append(a[1].shape[1]), real(*a, **k))[1]
+    try:
+        with torch.no_grad():
+            x = torch.randn(2, 64, 1280, device="cuda").bfloat16()
+            y = att(x)
+            unet._DISABLED.add("xattn")
+            y_lib = att(x)
+            unet._DISABLED.discard("xattn")
+            att(torch.randn(2, 256, 1280, device="cuda").bfloat16())
+    finally:
+        ops.attention = real
+        unet._DISABLED.discard("xattn")
+    assert calls == [64]
     assert (y.float() - y_lib.float()).abs().max().item() <= 3e-2 * max(1.0, y_lib.float().abs().max().item())

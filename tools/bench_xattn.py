@@ -31,15 +31,17 @@ def timed(fn, reps=5):
     return e0.elapsed_time(e1) * 1e3 / (reps * ROT)
 
 
-for (B, L, H, d) in [(2, 4096, 8, 40), (2, 1024, 8, 80), (2, 256, 8, 160), (2, 64, 8, 160), (6, 4096, 8, 40), (2, 4096, 10, 64)]:
+CASES = [(2, 4096, 77, 8, 40), (2, 1024, 77, 8, 80), (2, 256, 77, 8, 160), (2, 64, 77, 8, 160), (6, 4096, 77, 8, 40),
+         (2, 4096, 77, 10, 64), (2, 64, 64, 8, 160)]
+for (B, L, S, H, d) in CASES:
     qs = [torch.randn(B, L, H * d, device="cuda").bfloat16() for _ in range(ROT)]
-    ks = [torch.randn(B, 77, H * d, device="cuda").bfloat16() for _ in range(ROT)]
-    vs = [torch.randn(B, 77, H * d, device="cuda").bfloat16() for _ in range(ROT)]
+    ks = [torch.randn(B, S, H * d, device="cuda").bfloat16() for _ in range(ROT)]
+    vs = [torch.randn(B, S, H * d, device="cuda").bfloat16() for _ in range(ROT)]
 
     def lib(i):
         q, k, v = (t.view(B, -1, H, d).transpose(1, 2) for t in (qs[i], ks[i], vs[i]))
         return unet._sdpa(q, k, v).transpose(1, 2).reshape(B, L, H * d)
     with torch.no_grad():
-        t_o = timed(lambda i: ops.cross_attention(qs[i], ks[i], vs[i], H, kv_static=True))
+        t_o = timed(lambda i: ops.attention(qs[i], ks[i], vs[i], H, kv_static=S <= 80))
         t_l = timed(lib)
-    print(f"B={B} L={L:5d} heads={H:2d} d={d:3d}: slider_cross_attention {t_o:6.2f} us   library SDPA route (+ output transpose copy) {t_l:6.2f} us")
+    print(f"B={B} L={L:5d} S={S:5d} heads={H:2d} d={d:3d}: libslider {t_o:7.2f} us   library SDPA route (+ output transpose copy) {t_l:7.2f} us")
