@@ -422,6 +422,15 @@ int slider_cross_attention_strided(void* o, const void* q, const void* k, const 
                                    int heads, int head_dim, int ldq, int ldk, int ldv, int ldo, int dtype, int kv_static,
                                    void* stream);
 
+/*
+ * Backward of slider_cross_attention for FROZEN keys / values (attn2 under the `noxattn` training methods: to_k / to_v
+ * are neither adapted nor trainable and the prompt embeddings carry no gradient — autograd of the attention inside the
+ * UNet call at train_lora.py:244-262): dq only, from dout, q, k, v (dense [batch, len, heads * head_dim]); nothing else
+ * is saved by the forward.  Same limits as the forward.
+ */
+int slider_cross_attention_backward(void* dq, const void* dout, const void* q, const void* k, const void* v, int batch,
+                                    int q_len, int kv_len, int heads, int head_dim, int dtype, void* stream);
+
 /* x *= *dev_scalar  (chain rule for a non-unit upstream loss gradient). */
 int slider_scale_by_device_scalar(void* x, const float* dev_scalar,
                                   int64_t n_elem, int dtype, void* stream);

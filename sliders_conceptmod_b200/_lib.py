@@ -60,6 +60,7 @@ _SIGNATURES = {
     "slider_upsample_nearest2x_nhwc": (C.c_int, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "slider_concat_channels_nhwc": (C.c_int, [_vp, _vp, _vp, _i64, _i, _i, _i, _vp]),
     "slider_cross_attention": (C.c_int, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "slider_cross_attention_backward": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "slider_cross_attention_strided": (C.c_int, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "slider_loss_workspace_bytes": (_sz, []),
     "slider_guidance_loss": (C.c_int, [_fp, _vp, _vp, _vp, _vp, _vp, _i64, _f, _i, _i, _vp, _sz, _vp]),

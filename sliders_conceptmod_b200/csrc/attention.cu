@@ -201,6 +201,191 @@ cross_attention_kernel(T* __restrict__ o, const T* __restrict__ q, const T* __re
 }
 
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Backward for FROZEN keys / values (attn2 under the `noxattn` training methods: to_k / to_v are neither adapted nor
+// trainable and the prompt embeddings carry no gradient): only dq is needed, and with every key resident it is the
+// forward's structure again, nothing saved but q, k, v:
+//   P = softmax(q k^T c) recomputed;  dP = dO V^T;  D_i = sum_j P_ij dP_ij  (= dO_i . O_i, so O is not needed);
+//   dS = P o (dP - D) * c;  dq = dS K.
+// S and dP are two "Q K^T"-type products (dO staged like Q, V read like K), dq one "P V"-type product with K through
+// ldmatrix.trans.  The library's backward for these shapes takes 40-150 us per layer (it also forms dK / dV).
+template <typename T, int DS, int QT>
+__global__ void __launch_bounds__(QT * 2)
+cross_attention_bwd_kernel(T* __restrict__ dq, const T* __restrict__ dout, const T* __restrict__ q,
+                           const T* __restrict__ k, const T* __restrict__ v, const XaParams p) {
+  constexpr int DP = DS * 16;
+  constexpr int PITCH = DP * 2 + 16;
+  constexpr int VPR = DP / 8;
+  constexpr int XA_THREADS = QT * 2;
+  extern __shared__ __align__(16) unsigned char xa_smem[];
+  unsigned char* sK = xa_smem;
+  unsigned char* sV = sK + XA_KEYS * PITCH;
+  unsigned char* sQ = sV + XA_KEYS * PITCH;
+  unsigned char* sG = sQ + QT * PITCH;            // dO tile
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int bh = blockIdx.y, b = bh / p.H, h = bh - b * p.H;
+  const int q0 = blockIdx.x * QT;
+  const int dv = p.D >> 3;
+  {
+    constexpr int N = XA_KEYS * VPR;
+    for (int i0 = tid; i0 < N; i0 += 4 * XA_THREADS) {
+      uint4 kk[4], vv[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + u * XA_THREADS;
+        const int r = i / VPR, c = i - r * VPR;
+        kk[u] = make_uint4(0u, 0u, 0u, 0u); vv[u] = kk[u];
+        if (i < N && r < p.S && c < dv) {
+          const size_t row = (size_t)b * p.S + r, col = (size_t)h * p.D + c * 8;
+          kk[u] = *reinterpret_cast<const uint4*>(k + row * p.ldk + col);
+          vv[u] = *reinterpret_cast<const uint4*>(v + row * p.ldv + col);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + u * XA_THREADS;
+        if (i < N) {
+          *reinterpret_cast<uint4*>(sK + (i / VPR) * PITCH + (i % VPR) * 16) = kk[u];
+          *reinterpret_cast<uint4*>(sV + (i / VPR) * PITCH + (i % VPR) * 16) = vv[u];
+        }
+      }
+    }
+  }
+  {
+    constexpr int N = QT * VPR;
+    for (int i0 = tid; i0 < N; i0 += 4 * XA_THREADS) {
+      uint4 qq[4], gg[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + u * XA_THREADS;
+        const int r = i / VPR, c = i - r * VPR;
+        qq[u] = make_uint4(0u, 0u, 0u, 0u); gg[u] = qq[u];
+        if (i < N && q0 + r < p.L && c < dv) {
+          const size_t row = (size_t)b * p.L + q0 + r, col = (size_t)h * p.D + c * 8;
+          qq[u] = *reinterpret_cast<const uint4*>(q + row * p.ldq + col);
+          gg[u] = *reinterpret_cast<const uint4*>(dout + row * p.ldo + col);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + u * XA_THREADS;
+        if (i < N) {
+          *reinterpret_cast<uint4*>(sQ + (i / VPR) * PITCH + (i % VPR) * 16) = qq[u];
+          *reinterpret_cast<uint4*>(sG + (i / VPR) * PITCH + (i % VPR) * 16) = gg[u];
+        }
+      }
+    }
+  }
+  __syncthreads();
+  const uint32_t sK_u = (uint32_t)__cvta_generic_to_shared(sK), sV_u = (uint32_t)__cvta_generic_to_shared(sV);
+  const uint32_t sQ_u = (uint32_t)__cvta_generic_to_shared(sQ), sG_u = (uint32_t)__cvta_generic_to_shared(sG);
+  const int g = lane >> 2, t = lane & 3;
+  float s[XA_KEYS / 8][4], dp[XA_KEYS / 8][4];
+  {
+    uint32_t qa[DS][4], ga[DS][4];
+#pragma unroll
+    for (int ks = 0; ks < DS; ++ks) {
+      const uint32_t off = (uint32_t)((warp * 16 + (lane & 15)) * PITCH + (ks * 16 + (lane >> 4) * 8) * 2);
+      xa_ldmatrix_x4(sQ_u + off, qa[ks]);
+      xa_ldmatrix_x4(sG_u + off, ga[ks]);
+    }
+#pragma unroll
+    for (int j = 0; j < XA_KEYS / 8; ++j) {
+      s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f;
+      dp[j][0] = dp[j][1] = dp[j][2] = dp[j][3] = 0.f;
+#pragma unroll
+      for (int ks = 0; ks < DS; ++ks) {
+        uint32_t kb[2], vb[2];
+        const uint32_t off = (uint32_t)((j * 8 + (lane & 7)) * PITCH + (ks * 16 + ((lane >> 3) & 1) * 8) * 2);
+        xa_ldmatrix_x2(sK_u + off, kb);
+        xa_ldmatrix_x2(sV_u + off, vb);
+        XaMma<T>::mma(s[j], qa[ks], kb);
+        XaMma<T>::mma(dp[j], ga[ks], vb);
+      }
+    }
+  }
+  float m0 = -INFINITY, m1 = -INFINITY;
+#pragma unroll
+  for (int j = 0; j < XA_KEYS / 8; ++j) {
+    const int key = j * 8 + 2 * t;
+    if (key >= p.S) { s[j][0] = -INFINITY; s[j][2] = -INFINITY; }
+    if (key + 1 >= p.S) { s[j][1] = -INFINITY; s[j][3] = -INFINITY; }
+    m0 = fmaxf(m0, fmaxf(s[j][0], s[j][1]));
+    m1 = fmaxf(m1, fmaxf(s[j][2], s[j][3]));
+  }
+  m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 1)); m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 2));
+  m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 1)); m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 2));
+  float l0 = 0.f, l1 = 0.f, d0 = 0.f, d1 = 0.f;
+#pragma unroll
+  for (int j = 0; j < XA_KEYS / 8; ++j) {
+    s[j][0] = ex2_approx((s[j][0] - m0) * p.scale_log2); s[j][1] = ex2_approx((s[j][1] - m0) * p.scale_log2);
+    s[j][2] = ex2_approx((s[j][2] - m1) * p.scale_log2); s[j][3] = ex2_approx((s[j][3] - m1) * p.scale_log2);
+    l0 += s[j][0] + s[j][1]; l1 += s[j][2] + s[j][3];
+    d0 += s[j][0] * dp[j][0] + s[j][1] * dp[j][1];          // masked keys: p = 0 and dP = dO . 0 = 0
+    d1 += s[j][2] * dp[j][2] + s[j][3] * dp[j][3];
+  }
+  l0 += __shfl_xor_sync(0xffffffffu, l0, 1); l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+  l1 += __shfl_xor_sync(0xffffffffu, l1, 1); l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+  d0 += __shfl_xor_sync(0xffffffffu, d0, 1); d0 += __shfl_xor_sync(0xffffffffu, d0, 2);
+  d1 += __shfl_xor_sync(0xffffffffu, d1, 1); d1 += __shfl_xor_sync(0xffffffffu, d1, 2);
+  const float inv0 = 1.f / l0, inv1 = 1.f / l1;
+  const float D0 = d0 * inv0, D1 = d1 * inv1;               // sum_j P_ij dP_ij with P = e / l
+  const float c = p.scale_log2 * 0.6931471805599453f;       // 1 / sqrt(d)
+  uint32_t da[XA_KEYS / 16][4];                             // dS as A fragments
+#pragma unroll
+  for (int j = 0; j < XA_KEYS / 8; ++j) {
+    const float e0 = s[j][0] * inv0 * (dp[j][0] - D0) * c, e1 = s[j][1] * inv0 * (dp[j][1] - D0) * c;
+    const float e2 = s[j][2] * inv1 * (dp[j][2] - D1) * c, e3 = s[j][3] * inv1 * (dp[j][3] - D1) * c;
+    da[j >> 1][(j & 1) * 2 + 0] = Elem<T>::pack2(e0, e1);
+    da[j >> 1][(j & 1) * 2 + 1] = Elem<T>::pack2(e2, e3);
+  }
+  const int row0 = q0 + warp * 16 + g, row1 = row0 + 8;
+  T* o0 = dq + ((size_t)b * p.L + row0) * p.ldq + (size_t)h * p.D;
+  T* o1 = dq + ((size_t)b * p.L + row1) * p.ldq + (size_t)h * p.D;
+#pragma unroll
+  for (int jd = 0; jd < DP / 8; ++jd) {
+    if (jd * 8 >= p.D) break;
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int kk = 0; kk < XA_KEYS / 16; ++kk) {
+      uint32_t kb[2];
+      xa_ldmatrix_x2_trans(sK_u + (uint32_t)((kk * 16 + (lane & 15)) * PITCH + jd * 16), kb);
+      XaMma<T>::mma(acc, da[kk], kb);
+    }
+    const int d = jd * 8 + 2 * t;
+    if (row0 < p.L) *reinterpret_cast<uint32_t*>(o0 + d) = Elem<T>::pack2(acc[0], acc[1]);
+    if (row1 < p.L) *reinterpret_cast<uint32_t*>(o1 + d) = Elem<T>::pack2(acc[2], acc[3]);
+  }
+}
+
+template <typename T, int DS>
+static int launch_xattn_bwd(void* dq, const void* dout, const void* q, const void* k, const void* v, const XaParams& p,
+                            cudaStream_t st) {
+  constexpr int QT = 64;
+  constexpr int PITCH = DS * 32 + 16;
+  const size_t smem = (size_t)(2 * XA_KEYS + 2 * QT) * PITCH;
+  auto kern = cross_attention_bwd_kernel<T, DS, QT>;
+  static thread_local bool configured = false;
+  if (!configured && smem > 48 * 1024) {
+    SLIDER_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = true;
+  }
+  const dim3 grid((p.L + QT - 1) / QT, p.B * p.H);
+  kern<<<grid, QT * 2, smem, st>>>((T*)dq, (const T*)dout, (const T*)q, (const T*)k, (const T*)v, p);
+  return post_launch("cross_attention_bwd_kernel");
+}
+
+template <typename T>
+static int xattn_bwd_dispatch(void* dq, const void* dout, const void* q, const void* k, const void* v, const XaParams& p,
+                              cudaStream_t st) {
+  const int ds = (p.D + 15) / 16;
+  if (ds <= 3) return launch_xattn_bwd<T, 3>(dq, dout, q, k, v, p, st);
+  if (ds <= 4) return launch_xattn_bwd<T, 4>(dq, dout, q, k, v, p, st);
+  if (ds <= 5) return launch_xattn_bwd<T, 5>(dq, dout, q, k, v, p, st);
+  if (ds <= 8) return launch_xattn_bwd<T, 8>(dq, dout, q, k, v, p, st);
+  return launch_xattn_bwd<T, 10>(dq, dout, q, k, v, p, st);
+}
+
 template <typename T, int DS, int QT>
 static int launch_xattn_q(void* o, const void* q, const void* k, const void* v, const XaParams& p, cudaStream_t st) {
   constexpr int PITCH = DS * 32 + 16;
@@ -276,4 +461,27 @@ extern "C" int slider_cross_attention_strided(void* o, const void* q, const void
                                               int dtype, int kv_static, void* stream) {
   return attention_entry(o, q, k, v, batch, q_len, kv_len, heads, head_dim, ldq, ldk, ldv, ldo, dtype, kv_static, stream,
                          "cross_attention_strided");
+}
+
+extern "C" int slider_cross_attention_backward(void* dq, const void* dout, const void* q, const void* k, const void* v,
+                                               int batch, int q_len, int kv_len, int heads, int head_dim, int dtype,
+                                               void* stream) {
+  SLIDER_CHECK_ARG(dq && dout && q && k && v, "cross_attention_backward: null pointer");
+  SLIDER_CHECK_ARG(batch > 0 && q_len > 0 && heads > 0, "cross_attention_backward: empty shape");
+  SLIDER_CHECK_ARG(kv_len >= 1 && kv_len <= XA_KEYS, "cross_attention_backward: %d keys (1..%d)", kv_len, XA_KEYS);
+  SLIDER_CHECK_ARG(head_dim >= 8 && head_dim <= 160 && head_dim % 8 == 0,
+                   "cross_attention_backward: head dim %d not a multiple of 8 in 8..160", head_dim);
+  SLIDER_CHECK_ARG(batch * heads <= 65535, "cross_attention_backward: batch * heads = %d exceeds the grid limit", batch * heads);
+  SLIDER_CHECK_ARG((((uintptr_t)dq | (uintptr_t)dout | (uintptr_t)q | (uintptr_t)k | (uintptr_t)v) & 15) == 0,
+                   "cross_attention_backward: pointers must be 16-byte aligned");
+  XaParams p;
+  p.B = batch; p.L = q_len; p.S = kv_len; p.H = heads; p.D = head_dim;
+  p.ldq = p.ldk = p.ldv = p.ldo = heads * head_dim;
+  p.scale_log2 = 1.4426950408889634f / sqrtf((float)head_dim);
+  p.kv_static = 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == SLIDER_BF16) return xattn_bwd_dispatch<__nv_bfloat16>(dq, dout, q, k, v, p, st);
+  if (dtype == SLIDER_F16) return xattn_bwd_dispatch<__half>(dq, dout, q, k, v, p, st);
+  set_error("cross_attention_backward: unsupported dtype %d (16-bit storage only)", dtype);
+  return SLIDER_ERR_UNSUPPORTED;
 }

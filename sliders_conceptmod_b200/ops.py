@@ -438,6 +438,17 @@ def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int, kv_
     return o
 
 
+def cross_attention_backward(dout: torch.Tensor, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int) -> torch.Tensor:
+    """dq of attention(q, k, v) for frozen k / v (dense [B, len, H*d] tensors, S <= 80 keys)."""
+    require_cuda(dout, q, k, v)
+    assert all(t.is_contiguous() for t in (dout, q, k, v)) and dout.shape == q.shape and q.dtype == k.dtype == v.dtype == dout.dtype
+    B, L, HD = q.shape
+    dq = torch.empty_like(q)
+    check(lib().slider_cross_attention_backward(ptr(dq), ptr(dout), ptr(q), ptr(k), ptr(v), int(B), int(L), int(k.shape[1]),
+                                                int(heads), int(HD // heads), dtype_code(q.dtype), stream_ptr()))
+    return dq
+
+
 def launch_count() -> int:
     return int(lib().slider_launch_count())
 

@@ -369,6 +369,21 @@ class Upsample2D(nn.Module):
         return self.conv(x)
 
 
+class _ShortKeyAttnFn(torch.autograd.Function):
+    """softmax(q k^T / sqrt(d)) v for at most 80 FROZEN keys / values on libslider (forward + dq-only backward)."""
+
+    @staticmethod
+    def forward(ctx, q, k, v, heads):
+        ctx.save_for_backward(q, k, v)
+        ctx.heads = heads
+        return ops.attention(q, k, v, heads)
+
+    @staticmethod
+    def backward(ctx, do):
+        q, k, v = ctx.saved_tensors
+        return ops.cross_attention_backward(do if do.is_contiguous() else do.contiguous(), q, k, v, ctx.heads), None, None, None
+
+
 class Attention(nn.Module):
     def __init__(self, query_dim: int, cross_dim: int | None, heads: int, dim_head: int):
         super().__init__()
@@ -406,6 +421,11 @@ class Attention(nn.Module):
             # library kernels: a key-block loop on mma.sync measured 51 vs 16 us at 1024 keys
             # (profiles/r02_ab_cross_attention.txt)
             o = ops.attention(q, k, v, self.heads, kv_static=hit is not None)
+        elif ("xattn" not in _DISABLED and "xattn_train" not in _DISABLED and not _TORCH_ONLY and torch.is_grad_enabled()
+              and q.requires_grad and not k.requires_grad and not v.requires_grad and q.is_contiguous() and k.is_contiguous()
+              and v.is_contiguous() and ops.attention_usable(q, k, v, self.heads)):
+            # grad-recording forward with FROZEN keys / values (attn2 under `noxattn`): same kernel, dq-only backward
+            o = _ShortKeyAttnFn.apply(q, k, v, self.heads)
         else:
             q = q.view(B, L, self.heads, -1).transpose(1, 2)
             k = k.view(B, ctx.shape[1], self.heads, -1).transpose(1, 2)

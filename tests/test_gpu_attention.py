@@ -131,3 +131,53 @@ def test_self_attention_layer_routes_by_key_count():
         unet._DISABLED.discard("xattn")
     assert calls == [64]
     assert (y.float() - y_lib.float()).abs().max().item() <= 3e-2 * max(1.0, y_lib.float().abs().max().item())
+
+
+@pytest.mark.parametrize("case", [(2, 4096, 77, 8, 40), (2, 1024, 77, 8, 80), (2, 256, 77, 8, 160), (2, 64, 77, 8, 160),
+                                  (2, 1024, 77, 20, 64), (1, 100, 77, 4, 48), (3, 65, 5, 2, 8), (1, 70, 80, 1, 128)])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_dq_backward_matches_fp32_autograd(case, dtype):
+    """slider_cross_attention_backward (frozen keys / values: dq only) against autograd of fp32 softmax attention."""
+    from sliders_conceptmod_b200 import ops
+    B, L, S, H, d = case
+    g = torch.Generator(device="cuda").manual_seed(L + S + d)
+    q = (torch.randn(B, L, H * d, device="cuda", generator=g) * 1.2).to(dtype)
+    k = (torch.randn(B, S, H * d, device="cuda", generator=g) * 1.2).to(dtype)
+    v = torch.randn(B, S, H * d, device="cuda", generator=g).to(dtype)
+    do = torch.randn(B, L, H * d, device="cuda", generator=g).to(dtype)
+    qf = q.float().requires_grad_(True)
+    _ref(qf, k, v, H).backward(do.float())
+    dq = ops.cross_attention_backward(do, q, k, v, H)
+    tol = 3e-2 if dtype == torch.bfloat16 else 6e-3
+    err = (dq.float() - qf.grad).abs().max().item()
+    assert err <= tol * max(1.0, qf.grad.abs().max().item()), f"max err {err} scale {qf.grad.abs().max().item()}"
+    cos = torch.nn.functional.cosine_similarity(dq.float().flatten(), qf.grad.flatten(), dim=0).item()
+    assert cos > 0.999, cos
+
+
+def test_attn2_layer_trains_through_the_kernel_pair():
+    """Attention.forward with a frozen 77-token context in grad mode: output and input gradient follow the SDPA route."""
+    from sliders_conceptmod_b200 import ops, unet
+    torch.manual_seed(0)
+    att = unet.Attention(640, 768, 8, 80).cuda().bfloat16().requires_grad_(False)
+    ctx = torch.randn(2, 77, 768, device="cuda").bfloat16()
+    x = torch.randn(2, 1024, 640, device="cuda").bfloat16()
+    go = torch.randn(2, 1024, 640, device="cuda").bfloat16()
+    calls = []
+    real = ops.cross_attention_backward
+    ops.cross_attention_backward = lambda *a, **k: (calls.append(1), real(*a, **k))[1]
+    try:
+        x1 = x.clone().requires_grad_(True)
+        att(x1, ctx).backward(go)
+    finally:
+        ops.cross_attention_backward = real
+    assert calls, "the grad-recording attn2 layer did not take the libslider kernel pair"
+    unet._DISABLED.add("xattn")
+    try:
+        x2 = x.clone().requires_grad_(True)
+        att(x2, ctx).backward(go)
+    finally:
+        unet._DISABLED.discard("xattn")
+    cos = torch.nn.functional.cosine_similarity(x1.grad.float().flatten(), x2.grad.float().flatten(), dim=0).item()
+    assert cos > 0.999, cos
+    assert (x1.grad.float() - x2.grad.float()).abs().max().item() <= 4e-2 * x2.grad.float().abs().max().item()
