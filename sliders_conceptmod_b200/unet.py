@@ -105,6 +105,7 @@ _PLAIN_MAX_FLOP = float(os.environ.get("SLIDER_PLAIN_MAX_GFLOP", "8")) * 1e9
 
 
 _TORCH_ONLY = False
+_SC_STREAMS: dict = {}      # per device: side stream of the ResNet shortcut convolutions
 
 
 class torch_reference_mode:
@@ -332,6 +333,21 @@ class ResnetBlock2D(nn.Module):
         self.conv_shortcut = nn.Conv2d(in_ch, out_ch, 1) if in_ch != out_ch else None
 
     def forward(self, x, temb):
+        sc = sc_ev = None
+        if self.conv_shortcut is not None and "scstream" not in _DISABLED and _no_grad_cuda(x):
+            # the 1x1 shortcut depends only on the block input: issue it on a side stream (a parallel branch of the
+            # captured graph) so that it runs beside norm1 / conv1 / norm2 instead of between conv1 and conv2; joined
+            # right before conv2 adds into it.  Every fork waits for the main stream first, which also orders the
+            # side stream's reuse of a freed `sc` block behind its last main-stream reader.
+            main = torch.cuda.current_stream(x.device)
+            side = _SC_STREAMS.get(x.device)
+            if side is None:
+                side = _SC_STREAMS[x.device] = torch.cuda.Stream(device=x.device)
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                sc = self.conv_shortcut(x)
+                sc_ev = torch.cuda.Event()
+                sc_ev.record(side)
         h = self.conv1(group_norm_act(self.norm1, x, True))
         ready = self.__dict__.pop("_t_ready", None)
         if ready is not None:       # projected on the side stream at the start of the forward (UNet._prefetch_temb)
@@ -340,6 +356,9 @@ class ResnetBlock2D(nn.Module):
         else:
             t = self.time_emb_proj(temb if getattr(temb, "_silu_applied", False) else self.nonlinearity(temb))
         h = self.dropout(group_norm_act(self.norm2, h, True, chan_add=t))   # norm2(h + t)
+        if sc is not None:
+            torch.cuda.current_stream(x.device).wait_event(sc_ev)
+            return add_residual(self.conv2, h, sc)
         if self.conv_shortcut is not None:      # fresh tensor: conv2 may accumulate into it
             return add_residual(self.conv2, h, self.conv_shortcut(x))
         return x + self.conv2(h)                # x is a skip connection of the up path: keep it intact
