@@ -46,6 +46,10 @@ class workspace_lane:
         _lane = self.prev
 
 
+def current_lane() -> int:
+    return _lane
+
+
 def _ws_key(device: torch.device):
     return (device.index if device.index is not None else torch.cuda.current_device(), _lane)
 

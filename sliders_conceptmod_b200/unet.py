@@ -339,12 +339,15 @@ class ResnetBlock2D(nn.Module):
             # captured graph) so that it runs beside norm1 / conv1 / norm2 instead of between conv1 and conv2; joined
             # right before conv2 adds into it.  Every fork waits for the main stream first, which also orders the
             # side stream's reuse of a freed `sc` block behind its last main-stream reader.
+            # The two branches run CONCURRENTLY: the shortcut launch gets its own scratch lane (split-K partials and
+            # the like are per (device, lane) buffers, ops.workspace_lane) and a side stream per lane of the caller.
             main = torch.cuda.current_stream(x.device)
-            side = _SC_STREAMS.get(x.device)
+            lane = ops.current_lane()
+            side = _SC_STREAMS.get((x.device, lane))
             if side is None:
-                side = _SC_STREAMS[x.device] = torch.cuda.Stream(device=x.device)
+                side = _SC_STREAMS[(x.device, lane)] = torch.cuda.Stream(device=x.device)
             side.wait_stream(main)
-            with torch.cuda.stream(side):
+            with torch.cuda.stream(side), ops.workspace_lane(lane + 2):
                 sc = self.conv_shortcut(x)
                 sc_ev = torch.cuda.Event()
                 sc_ev.record(side)
