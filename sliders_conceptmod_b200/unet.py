@@ -334,7 +334,7 @@ class ResnetBlock2D(nn.Module):
 
     def forward(self, x, temb):
         sc = sc_ev = None
-        if self.conv_shortcut is not None and "scstream" not in _DISABLED and _no_grad_cuda(x):
+        if "scstream" not in _DISABLED and _no_grad_cuda(x):
             # the 1x1 shortcut depends only on the block input: issue it on a side stream (a parallel branch of the
             # captured graph) so that it runs beside norm1 / conv1 / norm2 instead of between conv1 and conv2; joined
             # right before conv2 adds into it.  Every fork waits for the main stream first, which also orders the
@@ -348,7 +348,9 @@ class ResnetBlock2D(nn.Module):
                 side = _SC_STREAMS[(x.device, lane)] = torch.cuda.Stream(device=x.device)
             side.wait_stream(main)
             with torch.cuda.stream(side), ops.workspace_lane(lane + 2):
-                sc = self.conv_shortcut(x)
+                # no shortcut convolution: x is also a skip connection of the up path and must stay intact, so the
+                # branch makes the private copy that conv2 adds into (instead of an add kernel after conv2)
+                sc = self.conv_shortcut(x) if self.conv_shortcut is not None else x.clone()
                 sc_ev = torch.cuda.Event()
                 sc_ev.record(side)
         h = self.conv1(group_norm_act(self.norm1, x, True))

@@ -6,7 +6,7 @@ timeout 900 python -m pytest tests/test_gpu_fullsize.py tests/test_gpu_network.p
 for round in 1 2; do
 for mode in on off; do
   if [ "$mode" = on ]; then env=""; else env="SLIDER_DISABLE=scstream"; fi
-  env $env timeout 600 python bench.py --steps 6 --warmup 3 --skip-cpu-baseline --skip-eager-baseline > gpurun_out/r43_${mode}_${round}.json 2> gpurun_out/r43_${mode}_${round}.err
+  env $env timeout 600 python bench.py --steps 6 --warmup 3 --skip-cpu-baseline --skip-eager-baseline > gpurun_out/r47_${mode}_${round}.json 2> gpurun_out/r47_${mode}_${round}.err
 done
 done
 python - <<'PY'
@@ -14,7 +14,7 @@ import json
 for mode in ('on','off'):
     for r in (1,2):
         try:
-            d=json.loads(open(f'gpurun_out/r43_{mode}_{r}.json').read().strip().splitlines()[-1])
+            d=json.loads(open(f'gpurun_out/r47_{mode}_{r}.json').read().strip().splitlines()[-1])
             print(mode, r, round(d['value'],3), d['phases_ms'], d.get('final_loss'))
         except Exception as e: print(mode, r, 'failed', e)
 PY
