@@ -13,6 +13,7 @@ hand their input to the TMA-fed implicit-GEMM kernel without a transpose.
 """
 from __future__ import annotations
 
+import contextlib
 import os
 
 import math
@@ -721,6 +722,13 @@ class UNet2DConditionModel(nn.Module):
             m._kv_cache = None
         self._ctx_attn, self._ctx_buffers = [], []
 
+    def _temb_stream(self, dev):
+        streams = self.__dict__.setdefault("_side_streams", {})
+        side = streams.get(dev)
+        if side is None:
+            side = streams[dev] = torch.cuda.Stream(device=dev)
+        return side
+
     def _prefetch_temb(self, emb: torch.Tensor):
         """All `time_emb_proj(silu(temb))` of the forward depend only on the time embedding: issue them (one small
         weight-streaming launch each) on a side stream right away, in the order the ResNet blocks will need them, so
@@ -729,13 +737,10 @@ class UNet2DConditionModel(nn.Module):
         if blocks is None:
             blocks = [m for m in self.modules() if isinstance(m, ResnetBlock2D)]   # registration order == call order
             self.__dict__["_resnet_order"] = blocks
-            self.__dict__["_side_streams"] = {}
         dev = emb.device
-        side = self._side_streams.get(dev)
-        if side is None:
-            side = self._side_streams[dev] = torch.cuda.Stream(device=dev)
+        side = self._temb_stream(dev)
         main = torch.cuda.current_stream(dev)
-        side.wait_stream(main)
+        side.wait_stream(main)          # a no-op when the caller already runs on the side stream
         with torch.cuda.stream(side):
             m_pad = 2 if emb.shape[0] <= 2 else 4 if emb.shape[0] <= 4 else 8 if emb.shape[0] <= 8 else 16
             if ("temb_multi" not in _DISABLED and emb.dim() == 2 and emb.shape[0] <= 16 and emb.is_contiguous()
@@ -785,17 +790,26 @@ class UNet2DConditionModel(nn.Module):
         if not torch.is_tensor(timestep):
             timestep = torch.tensor([timestep], device=sample.device)
         t = timestep.to(sample.device).reshape(-1).expand(B)
-        emb = self.time_embedding(self.time_proj(t).to(sample.dtype))
-        if self.config.addition_embed:
-            te = added_cond_kwargs["text_embeds"]
-            ids = added_cond_kwargs["time_ids"]
-            tid = self.add_time_proj(ids.flatten()).reshape(ids.shape[0], -1)
-            emb = emb + self.add_embedding(torch.cat([te, tid.to(te.dtype)], dim=-1).to(sample.dtype))
-        # every ResnetBlock2D applies the same SiLU to the same embedding before its time_emb_proj: do it once
-        emb = F.silu(emb)
-        emb._silu_applied = True
-        if emb.is_cuda and not _TORCH_ONLY and not torch.is_grad_enabled() and "temb_stream" not in _DISABLED:
-            self._prefetch_temb(emb)
+        # no-grad CUDA forward: the whole time-embedding branch (sinusoid, two Linear layers, SiLU, every block's
+        # time_emb_proj) runs on a side stream beside conv_in and the first block; each ResNet block waits on its event
+        prefetch = sample.is_cuda and not _TORCH_ONLY and not torch.is_grad_enabled() and "temb_stream" not in _DISABLED
+        branch = contextlib.nullcontext()
+        if prefetch and "temb_branch" not in _DISABLED:
+            side = self._temb_stream(sample.device)
+            side.wait_stream(torch.cuda.current_stream(sample.device))
+            branch = torch.cuda.stream(side)
+        with branch:
+            emb = self.time_embedding(self.time_proj(t).to(sample.dtype))
+            if self.config.addition_embed:
+                te = added_cond_kwargs["text_embeds"]
+                ids = added_cond_kwargs["time_ids"]
+                tid = self.add_time_proj(ids.flatten()).reshape(ids.shape[0], -1)
+                emb = emb + self.add_embedding(torch.cat([te, tid.to(te.dtype)], dim=-1).to(sample.dtype))
+            # every ResnetBlock2D applies the same SiLU to the same embedding before its time_emb_proj: do it once
+            emb = F.silu(emb)
+            emb._silu_applied = True
+            if prefetch:
+                self._prefetch_temb(emb)
         x = self.conv_in(sample.contiguous(memory_format=torch.channels_last))
         skips = [x]
         for blk in self.down_blocks:
