@@ -46,6 +46,9 @@ def parse_args():
     ap.add_argument("--skip-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-budget-s", type=float, default=240.0)
     ap.add_argument("--skip-eager-baseline", action="store_true")
+    ap.add_argument("--profile-step", action="store_true",
+                    help="after the timed regions run ONE more step between cudaProfilerStart/Stop, for "
+                         "`ncu --profile-from-start off` (the launch list of this same command; tools/gpu_launch_list_bench.sh)")
     return ap.parse_args()
 
 
@@ -529,6 +532,12 @@ def run_ours(args):
     # (train_lora.py:168-170), seeded per rank
     draws = [int(torch.randint(1, wl.max_denoising_steps, (1,), generator=gen)) for _ in range(args.steps)]
     sec_rand = timed(lambda i: engine.train_step(dev_lat[args.warmup + i], draws[i]), args.steps)
+    if args.profile_step and rank == 0:
+        torch.cuda.synchronize()
+        torch.cuda.profiler.start()
+        engine.train_step(dev_lat[args.warmup], TIMESTEPS_TO)
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
 
     if rank != 0:
         if world > 1:
