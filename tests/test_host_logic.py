@@ -287,3 +287,40 @@ def test_combine_loras_matches_reference_merge(tmp_path):
     import pytest
     with pytest.raises(AssertionError):
         combine_loras.merge({}, (combine_loras.BinDataHandler({"weird": torch.zeros(1)}), {"weird"}), 1.0, "CLIP")
+
+
+def test_attention_view_rule_and_cpu_refusal():
+    """ops._rows_ld / attention_usable decide which q / k / v views the short-key attention kernel takes (dense tensors
+    and last-dim slices of ONE fused projection); nothing on the CPU is ever 'usable' and the op itself refuses CPU
+    tensors instead of falling back."""
+    from sliders_conceptmod_b200 import ops
+    qkv = torch.zeros(2, 64, 3 * 320, dtype=torch.bfloat16)
+    q, k, v = qkv.split(320, dim=-1)
+    assert ops._rows_ld(q) == 960 and ops._rows_ld(k) == 960            # slices of the fused projection: row stride kept
+    assert ops._rows_ld(torch.zeros(2, 64, 320)) == 320
+    assert ops._rows_ld(torch.zeros(64, 320)) is None                   # not [B, len, C]
+    assert ops._rows_ld(torch.zeros(2, 64, 640)[:, :, ::2]) is None     # rows not dense
+    assert ops._rows_ld(torch.zeros(2, 128, 320)[:, ::2]) == 640        # every other row: still ONE row stride over the batch
+    assert ops._rows_ld(torch.zeros(2, 100, 320)[:, :64]) is None       # batch items do not follow each other
+    assert ops._rows_ld(torch.zeros(2, 64, 324)[:, :, :320]) is None    # row stride not a multiple of 16 bytes (bf16)
+    assert not ops.attention_usable(q, k, v, heads=8)                   # CPU tensors
+    with pytest.raises(Exception):
+        ops.attention(q.contiguous(), k.contiguous(), v.contiguous(), 8)
+
+
+def test_workspace_lanes_nest_and_restore():
+    from sliders_conceptmod_b200 import ops
+    assert ops.current_lane() == 0
+    with ops.workspace_lane(1):
+        assert ops.current_lane() == 1
+        with ops.workspace_lane(3):                                     # the shortcut branch of a block on lane 1
+            assert ops.current_lane() == 3
+            assert ops._ws_key(torch.device("cuda", 0)) == (0, 3)
+        assert ops.current_lane() == 1
+    assert ops.current_lane() == 0
+    try:
+        with ops.workspace_lane(2):
+            raise RuntimeError("x")
+    except RuntimeError:
+        pass
+    assert ops.current_lane() == 0                                      # restored on the error path too
