@@ -345,7 +345,9 @@ int slider_groupnorm_nhwc(void* y, const void* x, const void* chan_add,
  *     dadd [batch, channels] or NULL gradient w.r.t. chan_add (= sum of dx over pixels; flows into time_emb_proj's
  *                                    LoRA factors)
  * slider_groupnorm_nhwc_train == slider_groupnorm_nhwc + stats_out [batch, groups, 2] fp32 {mean, rstd}, which the
- * backward takes back as `stats`.  Backward = two launches (per-chunk partial sums, apply), deterministic order;
+ * backward takes back as `stats`.  Backward = ONE launch on the forward's (image, group set) cluster plan when the
+ * slabs of x and gy fit its shared memory (both read once; group sums over distributed shared memory), otherwise two
+ * launches (per-chunk partial sums into ws, apply); deterministic order either way;
  * ws of slider_groupnorm_bwd_workspace_bytes(batch, channels, groups) bytes, contents don't-care.
  */
 int slider_groupnorm_nhwc_train(void* y, float* stats_out, const void* x, const void* chan_add,
