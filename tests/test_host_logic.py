@@ -324,3 +324,14 @@ def test_workspace_lanes_nest_and_restore():
     except RuntimeError:
         pass
     assert ops.current_lane() == 0                                      # restored on the error path too
+
+
+@pytest.mark.parametrize("name,params,tensors", [("sd14", 859_520_964, 686), ("sdxl", 2_567_463_684, 1680)])
+def test_unet_stand_in_has_the_published_size(name, params, tensors):
+    """The random-init stand-in is the architecture the reference loads (`UNet2DConditionModel.from_pretrained`,
+    model_util.py:75-85, 142-186): parameter and tensor counts of the published SD-1.x / SD-XL UNet checkpoints, so the
+    benched FLOPs, the wrapped-layer shapes and the state-dict layout are the real workload's."""
+    with torch.device("meta"):
+        u = UNet2DConditionModel(getattr(UNetConfig, name)())
+    assert sum(p.numel() for p in u.parameters()) == params
+    assert len(u.state_dict()) == tensors

@@ -89,3 +89,22 @@ def test_prompt_encoding_matches_reference_functions(gold):
     assert xl_embeds.shape == (4, 77, 64 + 128) and xl_pooled.shape == (4, 128)
     assert torch.equal(xl_embeds, enc["xl_embeds"]) and torch.equal(xl_pooled, enc["xl_pooled"])
     assert torch.equal(sd_embeds, enc["sd_embeds"])
+
+
+def test_clip_stand_ins_have_the_published_sizes_and_key_layout():
+    """The random-init stand-ins are the architectures the reference loads (model_util.py:117-186: CLIP ViT-L/14 text
+    model and OpenCLIP bigG/14 text model with projection): same parameter counts as the published checkpoints and the
+    transformers key layout that `LoRANetwork(target_replace=[CLIPAttention, CLIPMLP])` walks (train_notrigger.py:134-148)."""
+    from sliders_conceptmod_b200 import text_encoder as te
+    with torch.device("meta"):
+        enc_l = te.CLIPTextModel(te.CLIPTextConfig.clip_l())
+        enc_g = te.CLIPTextModelWithProjection(te.CLIPTextConfig.clip_g())
+    assert sum(p.numel() for p in enc_l.parameters()) == 123_060_480
+    assert sum(p.numel() for p in enc_g.parameters()) == 694_659_840
+    keys = list(enc_g.state_dict())
+    assert keys[0] == "text_model.embeddings.token_embedding.weight" and keys[-1] == "text_projection.weight"
+    assert "text_model.encoder.layers.31.self_attn.out_proj.weight" in keys and "text_model.encoder.layers.31.mlp.fc2.bias" in keys
+    per_layer = {k.split("layers.0.")[1] for k in enc_l.state_dict() if ".layers.0." in k}
+    assert per_layer == {f"self_attn.{p}_proj.{w}" for p in "qkvo".replace("o", "") for w in ("weight", "bias")} | {
+        "self_attn.out_proj.weight", "self_attn.out_proj.bias", "layer_norm1.weight", "layer_norm1.bias",
+        "layer_norm2.weight", "layer_norm2.bias", "mlp.fc1.weight", "mlp.fc1.bias", "mlp.fc2.weight", "mlp.fc2.bias"}
