@@ -41,3 +41,37 @@ def test_sass_is_blackwell_native():
                              text=True).stdout
         for mnemonic in ("UTCHMMA", "UTMALDG", "UTMASTG", "LDTM"):
             assert mnemonic in out, f"{mnemonic} missing from the SASS of {obj}"
+
+
+def test_header_is_plain_c_and_a_c_host_links_and_calls(tmp_path):
+    """The boundary is a C ABI: the header compiles as C11 with no C++ or torch types, and a C host binds the library
+    through the DECLARED prototypes (a mismatch between a prototype and the exported symbol's use shows up here, not in
+    ctypes).  The calls made need no GPU: version, error string, argument validation that fails before any CUDA call."""
+    src = tmp_path / "host.c"
+    src.write_text(r'''
+#include <stdio.h>
+#include <string.h>
+#include "slider_b200.h"
+int main(void) {
+  if (slider_version() != 3) { printf("version %d\n", slider_version()); return 2; }
+  slider_layer_geom g;
+  memset(&g, 0, sizeof g);
+  g.dtype = SLIDER_BF16; g.batch = 1; g.height = 1; g.width = 8; g.cin = 8; g.cout = 8;
+  g.kh = 5; g.kw = 5; g.pad = 2; g.rank = 4;                       /* 5x5 taps: rejected by validation */
+  int rc = slider_lora_forward(&g, (void*)16, (const void*)16, (const void*)16, 0, 0, 0, 0, 1.0f, 0, 0, 0);
+  if (rc == SLIDER_OK) return 3;
+  if (strlen(slider_last_error()) == 0) return 4;
+  rc = slider_cross_attention((void*)16, (const void*)16, (const void*)16, (const void*)16, 1, 64, 4096, 8, 40, SLIDER_BF16, 0, 0);
+  if (rc == SLIDER_OK) return 5;                                    /* 4096 keys: outside the resident-key kernel */
+  printf("ok %s\n", slider_last_error());
+  return 0;
+}
+''')
+    exe = tmp_path / "host"
+    lib = build.build()
+    cmd = ["gcc", "-std=c11", "-Wall", "-Werror", "-pedantic", "-I", str(ROOT / "include"), str(src), "-o", str(exe),
+           "-L", str(lib.parent), "-l:" + lib.name, "-Wl,-rpath," + str(lib.parent)]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    r = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert r.returncode == 0 and r.stdout.startswith("ok "), (r.returncode, r.stdout, r.stderr)
