@@ -335,3 +335,33 @@ def test_unet_stand_in_has_the_published_size(name, params, tensors):
         u = UNet2DConditionModel(getattr(UNetConfig, name)())
     assert sum(p.numel() for p in u.parameters()) == params
     assert len(u.state_dict()) == tensors
+
+
+def test_oracle_is_test_infrastructure_only():
+    """Only tests/, __graft_entry__.smoke() and bench.py's CPU legs may touch oracle/: no module of the product package
+    (nor the C sources) imports, loads or names a file under it, and nothing at run time reads /root/reference."""
+    import ast
+    pkg = ROOT / "sliders_conceptmod_b200"
+    for path in sorted(pkg.glob("*.py")):
+        tree = ast.parse(path.read_text())
+        for node in ast.walk(tree):
+            mods = []
+            if isinstance(node, ast.Import):
+                mods = [a.name for a in node.names]
+            elif isinstance(node, ast.ImportFrom):
+                mods = [node.module or ""]
+            assert not any(m == "oracle" or m.startswith("oracle.") for m in mods), f"{path.name} imports the oracle"
+        docstrings = {id(n.body[0].value) for n in ast.walk(tree)
+                      if isinstance(n, (ast.Module, ast.FunctionDef, ast.ClassDef)) and n.body
+                      and isinstance(n.body[0], ast.Expr) and isinstance(n.body[0].value, ast.Constant)}
+        for node in ast.walk(tree):       # citations in docstrings are fine; a path used as data is not
+            if isinstance(node, ast.Constant) and isinstance(node.value, str) and id(node) not in docstrings:
+                assert "/root/reference" not in node.value, f"{path.name} names the reference checkout"
+    for path in sorted((pkg / "csrc").glob("*")):
+        assert "oracle" not in path.read_text().lower(), f"{path.name} mentions the oracle"
+    entry = ast.parse((ROOT / "__graft_entry__.py").read_text())
+    users = {f.name for f in ast.walk(entry) if isinstance(f, ast.FunctionDef)
+             and any(isinstance(n, (ast.Import, ast.ImportFrom)) and "oracle" in ast.dump(n) for n in ast.walk(f))}
+    assert users <= {"smoke"}, users
+    for name in ("bench.py", "__graft_entry__.py"):
+        assert "/root/reference" not in (ROOT / name).read_text(), f"{name} reads the reference at run time"
