@@ -75,3 +75,15 @@ int main(void) {
     assert r.returncode == 0, r.stderr
     r = subprocess.run([str(exe)], capture_output=True, text=True)
     assert r.returncode == 0 and r.stdout.startswith("ok "), (r.returncode, r.stdout, r.stderr)
+
+
+def test_missing_extension_fails_loudly(monkeypatch, tmp_path):
+    """No fallback: with the shared library absent the first call through the binding raises and names the build command."""
+    import pytest
+    monkeypatch.setattr(_lib, "_lib", None)
+    monkeypatch.setattr(_lib, "LIB_PATH", tmp_path / "libslider_b200.so")
+    with pytest.raises(RuntimeError, match="no fallback"):
+        _lib.lib()
+    with pytest.raises(RuntimeError, match="no fallback"):
+        from sliders_conceptmod_b200 import ops
+        ops.lib().slider_version()
