@@ -158,3 +158,25 @@ def test_xl_trainer_keeps_reference_quirks(tmp_path):
 def test_generate_images_parser_defaults():
     a = generate_images.build_parser().parse_args([])
     assert (a.start_noise, a.guidance_scale, a.ddim_steps, a.scales) == (800, 7.5, 50, "-2,-1,0,1,2")
+
+
+def test_bench_reference_arm_contract_on_cpu():
+    """`bench.py --impl reference` (the oracle port on the host cores): one JSON line with the contract's keys, real
+    iterations counted in `steps`; under torchrun every rank but 0 exits 0 without work or output."""
+    import json
+    import os
+    import subprocess
+    cmd = [sys.executable, str(ROOT / "bench.py"), "--impl", "reference", "--workload", "tiny", "--timesteps-to", "4",
+           "--steps", "2", "--warmup", "1"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, cwd=ROOT)
+    assert r.returncode == 0, r.stderr[-2000:]
+    line = json.loads(r.stdout.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and line["metric"] == "slider_train_steps_per_sec" and line["unit"] == "steps/s"
+    assert line["steps"] == 2 and line["higher_is_better"] is True and line["value"] > 0
+    assert line["cpu_baseline"]["kind"] == "port" and line["cpu_baseline"]["cores"] >= 1
+    assert line["cpu_baseline"]["value"] == line["value"] == line["e2e"]["value"]
+    assert line["e2e"]["h2d_bytes_per_step"] == 0 and line["e2e"]["d2h_bytes_per_step"] == 0
+    assert line["config"]["workload"] == "tiny" and "model" not in line["config"]
+    env = dict(os.environ, RANK="1", LOCAL_RANK="1", WORLD_SIZE="2")
+    r = subprocess.run(cmd + ["--gpus", "2"], capture_output=True, text=True, timeout=120, cwd=ROOT, env=env)
+    assert r.returncode == 0 and r.stdout.strip() == ""
