@@ -7,7 +7,7 @@ from hypothesis import given, settings, strategies as st
 
 from oracle import slider_oracle as O
 
-settings.register_profile("oracle", max_examples=25, deadline=None)
+settings.register_profile("oracle", max_examples=25, deadline=None, derandomize=True, database=None)
 settings.load_profile("oracle")
 F64 = torch.float64
 
